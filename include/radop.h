@@ -1,0 +1,218 @@
+/*
+ * radop.h -- C-ABI of libradop.so: the B200 (sm_100a) implementation of the
+ * per-gate hot path of wolfidan/cosmo_pol.
+ *
+ * What it replaces in the reference (paths relative to the reference root):
+ *   the body of the closure `worker(event, elev, azimuth)` that get_PPI / get_RHI
+ *   map over rays with multiprocess.Pool  (cosmo_pol/radar_operator.py:407-432,
+ *   504-530), i.e.
+ *     get_interpolated_radial   cosmo_pol/interpolation/interpolation.py:91-496
+ *       trilin_interp_radial    cosmo_pol/interpolation/interpolation.py:498-597
+ *       get_all_radar_pts       cosmo_pol/interpolation/interpolation_c.c:12-104   (SWIG, C)
+ *     get_radar_observables     cosmo_pol/scatter/doppler_scatter.py:49-489
+ *       Lookup_table.lookup_line cosmo_pol/lookup/lut.py:309-344
+ *       _Hydrometeor.set_psd/get_N/integrate_V  cosmo_pol/hydrometeors/hydrometeors.py:128-255
+ *       get_pol_from_sz         cosmo_pol/scatter/doppler_scatter.py:491-544
+ *     integrate_radials         cosmo_pol/interpolation/interpolation.py:36-89
+ *     cut_at_sensitivity        cosmo_pol/scatter/doppler_scatter.py:804-862
+ *   One radop_simulate() call processes the WHOLE ray list of a scan instead of
+ *   one pool task per ray.
+ *
+ * Conventions: plain C, plain pointers and sizes, no torch / CUDA types in any
+ * signature.  Every function returns an int status (0 = ok); the text of the
+ * last error of a handle is available through radop_last_error().  Nothing
+ * aborts or throws across the ABI.  Host buffers are owned by the caller and
+ * never retained after a call returns; device memory is owned by the handle.
+ * A handle is bound to one GPU and is not thread-safe.
+ */
+#ifndef RADOP_H
+#define RADOP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RADOP_ABI_VERSION 1
+
+/* ---- status codes ------------------------------------------------------- */
+enum {
+    RADOP_OK = 0,
+    RADOP_ERR_CUDA = 1,          /* a CUDA call failed (see radop_last_error)            */
+    RADOP_ERR_ARG = 2,           /* bad argument                                          -> ValueError */
+    RADOP_ERR_OUT_OF_DOMAIN = 3, /* a gate falls outside the model domain                 -> IndexError
+                                    (cosmo_pol/interpolation/interpolation.py:572-580)   */
+    RADOP_ERR_LUT = 4,           /* lookup table missing / wrong shape                    */
+    RADOP_ERR_STATE = 5,         /* grid / fields / params not uploaded yet               */
+    RADOP_ERR_UNSUPPORTED = 6    /* option not implemented in this build                  */
+};
+
+/* ---- model variables (cosmo_pol/radar_operator.py:35-36) ------------------ */
+enum {
+    RADOP_VAR_U = 0, RADOP_VAR_V, RADOP_VAR_W, RADOP_VAR_T, RADOP_VAR_RHO,
+    RADOP_VAR_QR, RADOP_VAR_QS, RADOP_VAR_QG, RADOP_VAR_QI,          /* 9 one-moment vars */
+    RADOP_VAR_QH, RADOP_VAR_QNR, RADOP_VAR_QNS, RADOP_VAR_QNG, RADOP_VAR_QNI, RADOP_VAR_QNH,
+    RADOP_NVAR_MAX = 16
+};
+
+/* ---- hydrometeor species (order of doppler_scatter.py:99-106) ------------- */
+enum { RADOP_SP_R = 0, RADOP_SP_S, RADOP_SP_G, RADOP_SP_H, RADOP_SP_I, RADOP_NSPECIES_MAX = 5 };
+
+/* PSD families (cosmo_pol/hydrometeors/hydrometeors.py) */
+enum {
+    RADOP_PSD_1MOM_FIXED_N0 = 0, /* Rain :761-772, Graupel :1039-1049                     */
+    RADOP_PSD_1MOM_SNOW = 1,     /* Snow :894-907 (N0 from temperature)                   */
+    RADOP_PSD_1MOM_ICE = 2,      /* IceParticle :1320-1339 (Field et al. 2005 moments)    */
+    RADOP_PSD_2MOM = 3           /* _Hydrometeor.set_psd :224-255, IceParticle :1341-1365 */
+};
+
+/* One species: constants of cosmo_pol/constants/constants_{1,2}mom.py */
+typedef struct {
+    int32_t species;        /* RADOP_SP_*                                                 */
+    int32_t psd;            /* RADOP_PSD_*                                                */
+    int32_t numeric_vn;     /* 1: fall-speed integrals are numeric (IceParticle.integrate_V,
+                               hydrometeors.py:1256-1275, incl. its all-gate np.sum)       */
+    int32_t reserved;
+    double a, b;            /* m(D) = a D^b                                               */
+    double alpha, beta;     /* v(D) = alpha D^beta                                        */
+    double mu, nu;          /* N(D) = N0 D^mu exp(-lambda D^nu)                           */
+    double N0;              /* fixed intercept (1-mom rain / graupel)                     */
+    double lambda_factor, vel_factor, ntot_factor;
+    double x_min, x_max;    /* 2-mom mean-mass limits                                     */
+} RadopSpecies;
+
+/* Scalars the hot path reads from cfg.CONFIG / global_constants */
+typedef struct {
+    int32_t abi_version;          /* RADOP_ABI_VERSION                                    */
+    int32_t n_gates;              /* len(RANGE_RADAR), global_constants.py:186-190        */
+    double radar_lat, radar_lon, radar_alt;   /* CONFIG['radar']['coords']                */
+    double wavelength_mm;         /* constants.WAVELENGTH                                 */
+    double k_squared;             /* CONFIG['radar']['K_squared']                         */
+    double radial_resolution_m;   /* CONFIG['radar']['radial_resolution']                 */
+    int32_t two_moment;           /* CONFIG['microphysics']['scheme'] == '2mom'           */
+    int32_t with_attenuation;     /* CONFIG['microphysics']['with_attenuation']           */
+    int32_t doppler_scheme;       /* CONFIG['doppler']['scheme'] (1 or 2)                 */
+    int32_t sensitivity_mode;     /* 0: no cut; 1: [ZH]; 2: [ZH, range]; cut_at_sensitivity */
+    double sensitivity[3];
+    int32_t output_model_vars;    /* integrate_radials outputs wanted ('all'/'only_model') */
+    int32_t keep_debug;           /* keep per sub-beam-gate indices for radop_debug_*      */
+    int32_t n_species;
+    int32_t reserved;
+    RadopSpecies species[RADOP_NSPECIES_MAX];   /* in summation order                      */
+} RadopParams;
+
+/*
+ * One scan = a list of rays, each with the same fan of sub-beams (quadrature
+ * points, interpolation.py:148-166 + 343-354) and a table of refracted
+ * trajectories (atm_refraction.py:181-220) shared by all rays of one elevation.
+ *   sub-beam q of ray r:  azimuth = ray_az[r] + sub_daz[q]
+ *                         trajectory row = (ray_traj[r] * n_vert + sub_jv[q])
+ */
+typedef struct {
+    int32_t n_rays;
+    int32_t n_sub;
+    int32_t n_traj;
+    int32_t n_vert;
+    const double *ray_az;       /* [n_rays] degrees                                       */
+    const int32_t *ray_traj;    /* [n_rays] trajectory group of the ray                   */
+    const float *ray_nyquist;   /* [n_rays] Nyquist velocity or NULL (no aliasing)        */
+    const double *sub_daz;      /* [n_sub] azimuth offset (pts_hor)                       */
+    const int32_t *sub_jv;      /* [n_sub] vertical quadrature index                      */
+    const double *sub_weight;   /* [n_sub] normalised quadrature weight                   */
+    const float *traj_s;        /* [n_traj][n_vert][n_gates] ground distance [m]          */
+    const float *traj_h;        /* [n_traj][n_vert][n_gates] height [m]                   */
+    const float *traj_e;        /* [n_traj][n_vert][n_gates] incidence elevation [deg]    */
+} RadopScan;
+
+/* radar observables, linear units (doppler_scatter.py:446-460) */
+enum {
+    RADOP_OUT_ZH = 0, RADOP_OUT_ZDR, RADOP_OUT_ZV, RADOP_OUT_KDP, RADOP_OUT_DELTA_HV,
+    RADOP_OUT_PHIDP, RADOP_OUT_RHOHV, RADOP_OUT_ATT_H, RADOP_OUT_ATT_V, RADOP_OUT_RVEL,
+    RADOP_N_OUT = 10
+};
+
+/* Caller-allocated HOST buffers, each [n_rays][n_gates]; NULL = not wanted. */
+typedef struct {
+    float *obs[RADOP_N_OUT];
+    float *mask;                      /* averaged sub-beam mask, doppler_scatter.py:472-477 */
+    double *lat, *lon;                /* central sub-beam gate positions (WGS84)           */
+    float *model[RADOP_NVAR_MAX];     /* integrate_radials of each uploaded variable       */
+} RadopOut;
+
+typedef struct RadopHandle_ RadopHandle;
+
+/* ---- life cycle ----------------------------------------------------------- */
+int radop_create(int device, RadopHandle **out);
+int radop_destroy(RadopHandle *h);
+const char *radop_last_error(const RadopHandle *h);
+int radop_abi_version(void);
+
+/* ---- configuration and one-time uploads ----------------------------------- */
+int radop_set_params(RadopHandle *h, const RadopParams *p);
+
+/* Model grid: z-levels [nz][ny][nx] float32 (level 0 = model top), lower-left and
+ * upper-right corners (Lo, La) and resolution (dlon, dlat) in rotated degrees,
+ * rotated south pole (lat, lon).  interpolation.py:547-568. */
+int radop_upload_grid(RadopHandle *h, int nz, int ny, int nx, const float *zlevels,
+                      const float llc[2], const float urc[2], const float res[2],
+                      const double south_pole[2]);
+/* One model variable [nz][ny][nx] float32 (var.data, interpolation.py:585). */
+int radop_upload_field(RadopHandle *h, int var_id, const float *data);
+
+/* One scattering table (lut.Lookup_table): value_table [ne][nt][nd][12] float64,
+ * axis minimum and step as float32 (axes_limits / axes_step), diameters [nd] float32. */
+int radop_upload_lut(RadopHandle *h, int species, const double *value_table,
+                     int ne, int nt, int nd, float e_min, float e_step,
+                     float t_min, float t_step, const float *d_axis);
+
+/* ---- the hot path ---------------------------------------------------------- */
+/* host in -> device -> host out (the reference-facing call) */
+int radop_simulate(RadopHandle *h, const RadopScan *scan, const RadopOut *out);
+/* the same in three steps (used to time the device part alone) */
+int radop_stage_scan(RadopHandle *h, const RadopScan *scan);   /* H2D                    */
+int radop_execute(RadopHandle *h);                              /* kernels, asynchronous  */
+int radop_fetch(RadopHandle *h, const RadopOut *out);           /* sync + D2H             */
+int radop_synchronize(RadopHandle *h);
+
+/* Device-resident results of the last radop_execute (for NCCL gathers): pointer to
+ * float32 [RADOP_N_OUT + 1][n_rays][n_gates] (observables then mask). */
+int radop_device_outputs(RadopHandle *h, void **dev_ptr, int64_t *n_rays, int64_t *n_gates);
+/* cudaStream_t of the handle (as void*), to record events on. */
+int radop_get_stream(RadopHandle *h, void **stream);
+
+/* ---- introspection ---------------------------------------------------------- */
+typedef struct {
+    int64_t n_subbeam_gates;      /* rays x sub-beams x gates of the last execute         */
+    int64_t n_active_pairs;       /* (sub-beam gate, species) pairs with Q > 0            */
+    int64_t n_lut_bins;           /* distinct (species, e, t) bins touched                */
+    int64_t n_tiles;              /* work tiles of the PSD-integration kernel             */
+    int64_t launches;             /* kernels launched by the last execute                 */
+    float ms_interp, ms_sort, ms_integrate, ms_reduce, ms_total;  /* CUDA-event times     */
+} RadopStats;
+int radop_get_stats(RadopHandle *h, RadopStats *s);
+int radop_enable_timing(RadopHandle *h, int on);
+
+/* Per sub-beam-gate integer decisions of the last execute (params.keep_debug = 1):
+ * cell [n][2] (lat idx, lon idx), level [n][4], status [n] (0 ok, 1 above top,
+ * -1 below topography), lut_e / lut_t [n][n_species] (-1 = species inactive),
+ * values [n][n_uploaded_vars] interpolated variables; n = rays*sub*gates. NULL = skip. */
+int radop_debug_indices(RadopHandle *h, int32_t *cell, int32_t *level, int32_t *status,
+                        int32_t *lut_e, int32_t *lut_t, float *values, double *rot_coords);
+
+/* Measured FP32 FMA throughput of this GPU [TFLOP/s] (roofline denominator). */
+int radop_measure_fp32_peak(RadopHandle *h, double *tflops);
+
+/* ---- compatibility shims over the kernels (same data contract as the SWIG
+ *      functions they replace; used for A/B tests against the gcc build) -------- */
+/* interpolation_c.c:12  get_all_radar_pts(len, coords[n][2], heights[n], data, z, llc, res) */
+int radop_get_all_radar_pts(RadopHandle *h, int n, const float *coords_rad_pts,
+                            const float *radar_heights, const float *model_data,
+                            const float *model_heights, int nz, int ny, int nx,
+                            const float *llc_cosmo, const float *res_cosmo, float *output);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RADOP_H */
