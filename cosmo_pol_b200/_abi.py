@@ -1,0 +1,395 @@
+# -*- coding: utf-8 -*-
+"""_abi.py -- ctypes binding of libradop.so (include/radop.h) and the ``Engine`` that the
+Python host layer drives.  There is NO CPU fallback: a missing library or a missing GPU
+raises, loudly."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libradop.so')
+
+RADOP_ABI_VERSION = 1
+NSPECIES_MAX = 5
+NVAR_MAX = 16
+N_OUT = 10
+OUT_NAMES = ['ZH', 'ZDR', 'ZV', 'KDP', 'DELTA_HV', 'PHIDP', 'RHOHV', 'ATT_H', 'ATT_V', 'RVEL']
+VAR_IDS = {'U': 0, 'V': 1, 'W': 2, 'T': 3, 'RHO': 4, 'QR_v': 5, 'QS_v': 6, 'QG_v': 7, 'QI_v': 8, 'QH_v': 9,
+           'QNR_v': 10, 'QNS_v': 11, 'QNG_v': 12, 'QNI_v': 13, 'QNH_v': 14}
+VAR_NAMES = {v: k for k, v in VAR_IDS.items()}
+SPECIES_IDS = {'R': 0, 'S': 1, 'G': 2, 'H': 3, 'I': 4}
+
+EXPORTS = ['radop_abi_version', 'radop_create', 'radop_destroy', 'radop_last_error', 'radop_set_params',
+           'radop_upload_grid', 'radop_upload_field', 'radop_upload_lut', 'radop_simulate', 'radop_stage_scan',
+           'radop_execute', 'radop_fetch', 'radop_synchronize', 'radop_device_outputs', 'radop_get_stream',
+           'radop_get_stats', 'radop_enable_timing', 'radop_debug_indices', 'radop_measure_fp32_peak',
+           'radop_get_all_radar_pts']
+
+(RADOP_OK, RADOP_ERR_CUDA, RADOP_ERR_ARG, RADOP_ERR_OUT_OF_DOMAIN, RADOP_ERR_LUT, RADOP_ERR_STATE,
+ RADOP_ERR_UNSUPPORTED) = range(7)
+
+
+class RadopSpecies(C.Structure):
+    _fields_ = [('species', C.c_int32), ('psd', C.c_int32), ('numeric_vn', C.c_int32), ('reserved', C.c_int32),
+                ('a', C.c_double), ('b', C.c_double), ('alpha', C.c_double), ('beta', C.c_double),
+                ('mu', C.c_double), ('nu', C.c_double), ('N0', C.c_double), ('lambda_factor', C.c_double),
+                ('vel_factor', C.c_double), ('ntot_factor', C.c_double), ('x_min', C.c_double), ('x_max', C.c_double)]
+
+
+class RadopParams(C.Structure):
+    _fields_ = [('abi_version', C.c_int32), ('n_gates', C.c_int32),
+                ('radar_lat', C.c_double), ('radar_lon', C.c_double), ('radar_alt', C.c_double),
+                ('wavelength_mm', C.c_double), ('k_squared', C.c_double), ('radial_resolution_m', C.c_double),
+                ('two_moment', C.c_int32), ('with_attenuation', C.c_int32), ('doppler_scheme', C.c_int32),
+                ('sensitivity_mode', C.c_int32), ('sensitivity', C.c_double * 3),
+                ('output_model_vars', C.c_int32), ('keep_debug', C.c_int32), ('n_species', C.c_int32),
+                ('reserved', C.c_int32), ('species', RadopSpecies * NSPECIES_MAX)]
+
+
+class RadopScan(C.Structure):
+    _fields_ = [('n_rays', C.c_int32), ('n_sub', C.c_int32), ('n_traj', C.c_int32), ('n_vert', C.c_int32),
+                ('ray_az', C.c_void_p), ('ray_traj', C.c_void_p), ('ray_nyquist', C.c_void_p),
+                ('sub_daz', C.c_void_p), ('sub_jv', C.c_void_p), ('sub_weight', C.c_void_p),
+                ('traj_s', C.c_void_p), ('traj_h', C.c_void_p), ('traj_e', C.c_void_p)]
+
+
+class RadopOut(C.Structure):
+    _fields_ = [('obs', C.c_void_p * N_OUT), ('mask', C.c_void_p), ('lat', C.c_void_p), ('lon', C.c_void_p),
+                ('model', C.c_void_p * NVAR_MAX)]
+
+
+class RadopStats(C.Structure):
+    _fields_ = [('n_subbeam_gates', C.c_int64), ('n_active_pairs', C.c_int64), ('n_lut_bins', C.c_int64),
+                ('n_tiles', C.c_int64), ('launches', C.c_int64), ('ms_interp', C.c_float), ('ms_sort', C.c_float),
+                ('ms_integrate', C.c_float), ('ms_reduce', C.c_float), ('ms_total', C.c_float)]
+
+
+class RadopError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen libradop.so; raises if it has not been built (python __graft_entry__.py / build())."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RadopError('libradop.so is missing: build it with `python -c "import __graft_entry__ as g; g.build()"` '
+                         '(nvcc, sm_100a). There is no CPU fallback.')
+    lib = C.CDLL(LIB_PATH)
+    for name in EXPORTS:
+        getattr(lib, name)           # AttributeError if an export is missing
+        getattr(lib, name).restype = C.c_int
+    lib.radop_last_error.restype = C.c_char_p
+    lib.radop_last_error.argtypes = [C.c_void_p]
+    lib.radop_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    lib.radop_destroy.argtypes = [C.c_void_p]
+    lib.radop_set_params.argtypes = [C.c_void_p, C.POINTER(RadopParams)]
+    lib.radop_upload_grid.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p]
+    lib.radop_upload_field.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    lib.radop_upload_lut.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
+                                     C.c_float, C.c_float, C.c_void_p]
+    lib.radop_simulate.argtypes = [C.c_void_p, C.POINTER(RadopScan), C.POINTER(RadopOut)]
+    lib.radop_stage_scan.argtypes = [C.c_void_p, C.POINTER(RadopScan)]
+    lib.radop_execute.argtypes = [C.c_void_p]
+    lib.radop_fetch.argtypes = [C.c_void_p, C.POINTER(RadopOut)]
+    lib.radop_synchronize.argtypes = [C.c_void_p]
+    lib.radop_device_outputs.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    lib.radop_get_stream.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+    lib.radop_get_stats.argtypes = [C.c_void_p, C.POINTER(RadopStats)]
+    lib.radop_enable_timing.argtypes = [C.c_void_p, C.c_int]
+    lib.radop_debug_indices.argtypes = [C.c_void_p] + [C.c_void_p] * 7
+    lib.radop_measure_fp32_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+    lib.radop_get_all_radar_pts.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    if lib.radop_abi_version() != RADOP_ABI_VERSION:
+        raise RadopError('libradop.so ABI version mismatch')
+    _lib = lib
+    return lib
+
+
+def _ptr(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(None)
+
+
+class Scan(object):
+    """Host arrays of one scan (RadopScan) plus bookkeeping for the result assembly."""
+
+    def __init__(self, ray_az, ray_el, ray_traj, ray_nyquist, fan, traj_s, traj_h, traj_e):
+        self.ray_az = np.ascontiguousarray(ray_az, dtype=np.float64)
+        self.ray_el = np.ascontiguousarray(ray_el, dtype=np.float64)
+        self.ray_traj = np.ascontiguousarray(ray_traj, dtype=np.int32)
+        self.ray_nyquist = None if ray_nyquist is None else np.ascontiguousarray(ray_nyquist, dtype=np.float32)
+        self.fan = fan
+        self.sub_daz = np.ascontiguousarray(fan.daz, dtype=np.float64)
+        self.sub_jv = np.ascontiguousarray(fan.j_ver, dtype=np.int32)
+        self.sub_weight = np.ascontiguousarray(fan.weight, dtype=np.float64)
+        self.traj_s = np.ascontiguousarray(traj_s, dtype=np.float32)
+        self.traj_h = np.ascontiguousarray(traj_h, dtype=np.float32)
+        self.traj_e = np.ascontiguousarray(traj_e, dtype=np.float32)
+        self.n_rays = len(self.ray_az)
+        self.n_sub = fan.n_sub
+        self.n_traj, self.n_vert, self.n_gates = self.traj_s.shape
+
+    def as_struct(self):
+        s = RadopScan()
+        s.n_rays, s.n_sub, s.n_traj, s.n_vert = self.n_rays, self.n_sub, self.n_traj, self.n_vert
+        s.ray_az, s.ray_traj, s.ray_nyquist = _ptr(self.ray_az), _ptr(self.ray_traj), _ptr(self.ray_nyquist)
+        s.sub_daz, s.sub_jv, s.sub_weight = _ptr(self.sub_daz), _ptr(self.sub_jv), _ptr(self.sub_weight)
+        s.traj_s, s.traj_h, s.traj_e = _ptr(self.traj_s), _ptr(self.traj_h), _ptr(self.traj_e)
+        return s
+
+    @property
+    def n_subbeam_gates(self):
+        return self.n_rays * self.n_sub * self.n_gates
+
+    def bytes_in(self):
+        return sum(a.nbytes for a in (self.ray_az, self.ray_traj, self.sub_daz, self.sub_jv, self.sub_weight,
+                                      self.traj_s, self.traj_h, self.traj_e)) + (
+            self.ray_nyquist.nbytes if self.ray_nyquist is not None else 0)
+
+
+class Engine(object):
+    """One handle = one GPU.  Owns the device-resident model fields and lookup tables."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.radop_create(int(device), C.byref(h))
+        if rc != RADOP_OK or not h:
+            raise RadopError('radop_create failed on device {} (code {}): no usable CUDA GPU. '
+                             'The hot path has no CPU fallback.'.format(device, rc))
+        self.h = h
+        self.device = device
+        self.params = None
+        self.uploaded_vars = []
+        self._pinned = {}
+        self._keep = []
+
+    def close(self):
+        if getattr(self, 'h', None):
+            self.lib.radop_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------------------------
+    def _check(self, rc):
+        if rc == RADOP_OK:
+            return
+        msg = self.lib.radop_last_error(self.h)
+        msg = msg.decode() if msg else ''
+        if rc == RADOP_ERR_OUT_OF_DOMAIN:
+            # same exception type as interpolation.py:572-580
+            raise IndexError('ERROR: RADAR DOMAIN IS NOT ENTIRELY CONTAINED IN COSMO SIMULATION DOMAIN: ABORTING (' + msg + ')')
+        if rc in (RADOP_ERR_ARG, RADOP_ERR_UNSUPPORTED):
+            raise ValueError(msg)
+        raise RadopError('libradop error {}: {}'.format(rc, msg))
+
+    # ------------------------------------------------------------------------------------
+    def set_params(self, config, constants, hydrometeors, n_gates, output_model_vars=False, keep_debug=False,
+                   sensitivity_cut=True):
+        """config: cfg.CONFIG-like dict; constants: global_constants; hydrometeors: ordered
+        list of species objects (summation order of doppler_scatter.py:99-106)."""
+        p = RadopParams()
+        p.abi_version = RADOP_ABI_VERSION
+        p.n_gates = int(n_gates)
+        r = config['radar']
+        p.radar_lat, p.radar_lon, p.radar_alt = float(r['coords'][0]), float(r['coords'][1]), float(r['coords'][2])
+        p.wavelength_mm = float(constants.WAVELENGTH)
+        p.k_squared = float(r['K_squared'])
+        p.radial_resolution_m = float(r['radial_resolution'])
+        p.two_moment = 1 if config['microphysics']['scheme'] == '2mom' else 0
+        p.with_attenuation = int(config['microphysics']['with_attenuation'])
+        p.doppler_scheme = int(config['doppler']['scheme'])
+        sens = r['sensitivity']
+        sens = list(sens) if isinstance(sens, (list, tuple)) else [sens]
+        if not sensitivity_cut:
+            p.sensitivity_mode = 0
+        elif len(sens) in (1, 2):
+            p.sensitivity_mode = len(sens)
+            for i, v in enumerate(sens):
+                p.sensitivity[i] = float(v)
+        else:
+            raise ValueError('3-element sensitivity [dBm, gain, snr] is not supported by the GPU path')
+        p.output_model_vars = 1 if output_model_vars else 0
+        p.keep_debug = 1 if keep_debug else 0
+        p.n_species = len(hydrometeors)
+        for i, hy in enumerate(hydrometeors):
+            for k, v in hy.abi_fields().items():
+                setattr(p.species[i], k, v)
+        self._check(self.lib.radop_set_params(self.h, C.byref(p)))
+        self.params = p
+        self.species_order = [hy.kind for hy in hydrometeors]
+
+    def upload_model(self, dic_vars):
+        first = next(iter(dic_vars.values()))
+        z = np.ascontiguousarray(first.attributes['z-levels'], dtype=np.float32)
+        proj = first.attributes['proj_info']
+        res = first.attributes['resolution']
+        llc = np.asarray((float(proj['Lo1']), float(proj['La1']))).astype('float32')
+        urc = np.asarray((float(proj['Lo2']), float(proj['La2']))).astype('float32')
+        res32 = np.asarray(res, dtype=np.float32)
+        sp = np.asarray([float(proj['Latitude_of_southern_pole']), float(proj['Longitude_of_southern_pole'])],
+                        dtype=np.float64)
+        nz, ny, nx = z.shape
+        self._check(self.lib.radop_upload_grid(self.h, nz, ny, nx, _ptr(z), _ptr(llc), _ptr(urc), _ptr(res32), _ptr(sp)))
+        self.uploaded_vars = []
+        for name, var in dic_vars.items():
+            if name not in VAR_IDS:
+                continue
+            d = np.ascontiguousarray(var.data, dtype=np.float32)
+            if d.shape != z.shape:
+                raise ValueError('variable {} does not have the shape of the z-levels'.format(name))
+            self._check(self.lib.radop_upload_field(self.h, VAR_IDS[name], _ptr(d)))
+            self.uploaded_vars.append(name)
+        self.uploaded_vars.sort(key=lambda n: VAR_IDS[n])
+        self.grid_shape = (nz, ny, nx)
+
+    def upload_luts(self, lut_sz):
+        for h, lut in lut_sz.items():
+            if h not in SPECIES_IDS:
+                continue
+            if h not in self.species_order:
+                continue
+            vt = np.ascontiguousarray(lut.value_table, dtype=np.float64)
+            names = lut.axes_names
+            ie, it, idd = names['e'], names['t'], names['d']
+            if (ie, it, idd) != (0, 1, 2) or vt.ndim != 4 or vt.shape[3] != 12:
+                raise ValueError('lookup table of {} must have axes (e, t, d, sz[12])'.format(h))
+            d_axis = np.ascontiguousarray(lut.axes[idd], dtype=np.float32)
+            self._check(self.lib.radop_upload_lut(
+                self.h, SPECIES_IDS[h], _ptr(vt), vt.shape[0], vt.shape[1], vt.shape[2],
+                C.c_float(np.float32(lut.axes_limits[ie][0])), C.c_float(np.float32(lut.axes_step[ie])),
+                C.c_float(np.float32(lut.axes_limits[it][0])), C.c_float(np.float32(lut.axes_step[it])), _ptr(d_axis)))
+
+    # ------------------------------------------------------------------------------------
+    def _host_buffer(self, key, shape, dtype):
+        """Pinned host buffer (through torch when CUDA is there), cached per key."""
+        n = int(np.prod(shape))
+        ent = self._pinned.get(key)
+        if ent is not None and ent[1].size == n and ent[1].dtype == np.dtype(dtype):
+            return ent[1].reshape(shape)
+        arr = None
+        try:
+            import torch
+            if torch.cuda.is_available():
+                t = torch.empty(n, dtype={np.dtype('float32'): torch.float32, np.dtype('float64'): torch.float64}[np.dtype(dtype)],
+                                pin_memory=True)
+                arr = t.numpy()
+                self._pinned[key] = (t, arr)
+        except Exception:
+            arr = None
+        if arr is None:
+            arr = np.empty(n, dtype=dtype)
+            self._pinned[key] = (None, arr)
+        return arr.reshape(shape)
+
+    def make_out(self, scan, want_latlon=True, want_model=False):
+        shape = (scan.n_rays, scan.n_gates)
+        out = RadopOut()
+        arrays = {}
+        for i, name in enumerate(OUT_NAMES):
+            a = self._host_buffer(('obs', i), shape, np.float32)
+            arrays[name] = a
+            out.obs[i] = a.ctypes.data
+        a = self._host_buffer('mask', shape, np.float32)
+        arrays['mask'] = a
+        out.mask = a.ctypes.data
+        if want_latlon:
+            for k in ('lat', 'lon'):
+                a = self._host_buffer(k, shape, np.float64)
+                arrays[k] = a
+                setattr(out, k, a.ctypes.data)
+        if want_model:
+            for name in self.uploaded_vars:
+                a = self._host_buffer(('model', name), shape, np.float32)
+                arrays[name] = a
+                out.model[VAR_IDS[name]] = a.ctypes.data
+        return out, arrays
+
+    def simulate(self, scan, want_latlon=True, want_model=False):
+        """The reference-facing call: host in -> host out."""
+        out, arrays = self.make_out(scan, want_latlon, want_model)
+        s = scan.as_struct()
+        self._check(self.lib.radop_simulate(self.h, C.byref(s), C.byref(out)))
+        return arrays
+
+    def stage(self, scan):
+        s = scan.as_struct()
+        self._check(self.lib.radop_stage_scan(self.h, C.byref(s)))
+
+    def execute(self):
+        self._check(self.lib.radop_execute(self.h))
+
+    def synchronize(self):
+        self._check(self.lib.radop_synchronize(self.h))
+
+    def fetch(self, scan, want_latlon=True, want_model=False):
+        out, arrays = self.make_out(scan, want_latlon, want_model)
+        self._check(self.lib.radop_fetch(self.h, C.byref(out)))
+        return arrays
+
+    def enable_timing(self, on=True):
+        self._check(self.lib.radop_enable_timing(self.h, 1 if on else 0))
+
+    def stats(self):
+        s = RadopStats()
+        self._check(self.lib.radop_get_stats(self.h, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in RadopStats._fields_}
+
+    def stream_ptr(self):
+        p = C.c_void_p()
+        self._check(self.lib.radop_get_stream(self.h, C.byref(p)))
+        return p.value
+
+    def device_outputs(self):
+        p = C.c_void_p()
+        nr, ng = C.c_int64(), C.c_int64()
+        self._check(self.lib.radop_device_outputs(self.h, C.byref(p), C.byref(nr), C.byref(ng)))
+        return p.value, nr.value, ng.value
+
+    def measure_fp32_peak(self):
+        v = C.c_double()
+        self._check(self.lib.radop_measure_fp32_peak(self.h, C.byref(v)))
+        return v.value
+
+    def debug_indices(self, scan):
+        n = scan.n_subbeam_gates
+        nsp = self.params.n_species
+        nv = len(self.uploaded_vars)
+        d = {'cell': np.zeros((n, 2), np.int32), 'level': np.zeros((n, 4), np.int32), 'status': np.zeros(n, np.int32),
+             'lut_e': np.zeros((n, nsp), np.int32), 'lut_t': np.zeros((n, nsp), np.int32),
+             'values': np.zeros((n, nv), np.float32), 'rot': np.zeros((n, 2), np.float64)}
+        self._check(self.lib.radop_debug_indices(self.h, _ptr(d['cell']), _ptr(d['level']), _ptr(d['status']),
+                                                 _ptr(d['lut_e']), _ptr(d['lut_t']), _ptr(d['values']), _ptr(d['rot'])))
+        shp = (scan.n_rays, scan.n_sub, scan.n_gates)
+        for k in d:
+            d[k] = d[k].reshape(shp + d[k].shape[1:])
+        d['var_names'] = list(self.uploaded_vars)
+        return d
+
+    def get_all_radar_pts(self, coords, heights_gates, model_data, model_heights, llc, res):
+        """Compatibility shim with the data contract of the SWIG function
+        (interpolation.py:584-595): returns the interpolated profile."""
+        coords = np.ascontiguousarray(coords, dtype=np.float32)
+        hg = np.ascontiguousarray(heights_gates, dtype=np.float32)
+        data = np.ascontiguousarray(model_data, dtype=np.float32)
+        mh = np.ascontiguousarray(model_heights, dtype=np.float32)
+        llc = np.ascontiguousarray(llc, dtype=np.float32)
+        res = np.ascontiguousarray(res, dtype=np.float32)
+        n = coords.shape[0]
+        out = np.zeros(n, dtype=np.float32)
+        nz, ny, nx = data.shape
+        self._check(self.lib.radop_get_all_radar_pts(self.h, n, _ptr(coords), _ptr(hg), _ptr(data), _ptr(mh),
+                                                     nz, ny, nx, _ptr(llc), _ptr(res), _ptr(out)))
+        return out

@@ -1,0 +1,705 @@
+// radop_api.cu -- host side of libradop.so: the C-ABI declared in include/radop.h.
+// Owns device memory, the private CUDA stream, the one-time layout transforms and the
+// launch sequence of the hot path.  No CPU fallback exists: every entry point needs a GPU.
+#include "radop_kernels.cu"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace {
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct LutHost {
+    bool loaded = false;
+    int ne = 0, nt = 0, nd = 0, mode = 0, ncol = 8, cost = 9;
+    float e_min = 0, e_step = 1, t_min = 0, t_step = 1, dD_geo = 0, dD_ref = 0;
+    RadopSpecies packed_for;   // constants the table was premultiplied with
+    DevBuf table, aux;
+};
+
+}  // namespace
+
+struct RadopHandle_ {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    int n_sm = 148;
+    // configuration
+    bool have_params = false, have_grid = false;
+    RadopParams p;
+    int nz = 0, ny = 0, nx = 0;
+    float llc[2], urc[2], res[2];
+    double rot[9];
+    uint32_t var_mask = 0;
+    DevBuf z_t, fields, stage;
+    LutHost lut[RADOP_NSPECIES_MAX];   // indexed by RADOP_SP_*
+    // scan
+    bool have_scan = false, executed = false;
+    int n_rays = 0, n_sub = 0, n_traj = 0, n_vert = 0, center_sub = 0;
+    bool have_nyquist = false;
+    long long n_sbg = 0;
+    void *pinned = nullptr;
+    size_t pinned_cap = 0;
+    DevBuf scan_blob;
+    ScanDev scan;
+    const float *d_nyquist = nullptr;
+    // work buffers
+    DevBuf mask, active, wind, sinth, vsum, nsum, key, p0, p1, vals, lat, lon, hist, flags;
+    DevBuf bin_start, tile_start, cost_start, cursor, totals, rec, sz_out, ice_vn, ice_tot, comb, out, model_out;
+    DevBuf dbg_cell, dbg_level, dbg_status, dbg_e, dbg_t, dbg_rot;
+    DevConfig cfg;
+    int k2_blocks = 0;
+    size_t k2_smem = 0;
+    // timing
+    bool timing = false;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    RadopStats stats;
+
+    int fail(int code, const std::string &msg)
+    {
+        err = msg;
+        return code;
+    }
+};
+
+#define CU(h, expr)                                                                                   \
+    do {                                                                                              \
+        cudaError_t e__ = (expr);                                                                     \
+        if (e__ != cudaSuccess) {                                                                     \
+            char buf__[512];                                                                          \
+            snprintf(buf__, sizeof buf__, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__),   \
+                     __FILE__, __LINE__);                                                             \
+            return (h)->fail(RADOP_ERR_CUDA, buf__);                                                  \
+        }                                                                                             \
+    } while (0)
+
+static int species_vars(int sp, int *qm, int *qn)
+{
+    switch (sp) {
+    case RADOP_SP_R: *qm = RADOP_VAR_QR; *qn = RADOP_VAR_QNR; return 0;
+    case RADOP_SP_S: *qm = RADOP_VAR_QS; *qn = RADOP_VAR_QNS; return 0;
+    case RADOP_SP_G: *qm = RADOP_VAR_QG; *qn = RADOP_VAR_QNG; return 0;
+    case RADOP_SP_H: *qm = RADOP_VAR_QH; *qn = RADOP_VAR_QNH; return 0;
+    case RADOP_SP_I: *qm = RADOP_VAR_QI; *qn = RADOP_VAR_QNI; return 0;
+    }
+    return -1;
+}
+
+extern "C" {
+
+int radop_abi_version(void) { return RADOP_ABI_VERSION; }
+
+int radop_create(int device, RadopHandle **out)
+{
+    if (!out) return RADOP_ERR_ARG;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0 || device < 0 || device >= count) {
+        cudaGetLastError();
+        return RADOP_ERR_CUDA;   // no GPU: there is no CPU fallback
+    }
+    RadopHandle *h = new RadopHandle_();
+    h->device = device;
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete h;
+        return RADOP_ERR_CUDA;
+    }
+    cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, device);
+    for (auto &e : h->ev) cudaEventCreate(&e);
+    memset(&h->stats, 0, sizeof h->stats);
+    memset(&h->p, 0, sizeof h->p);
+    *out = h;
+    return RADOP_OK;
+}
+
+int radop_destroy(RadopHandle *h)
+{
+    if (!h) return RADOP_OK;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    DevBuf *bufs[] = {&h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
+                      &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
+                      &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
+                      &h->ice_vn, &h->ice_tot, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
+                      &h->dbg_status, &h->dbg_e, &h->dbg_t, &h->dbg_rot};
+    for (DevBuf *b : bufs) b->release();
+    for (auto &l : h->lut) { l.table.release(); l.aux.release(); }
+    if (h->pinned) cudaFreeHost(h->pinned);
+    for (auto &e : h->ev) if (e) cudaEventDestroy(e);
+    cudaStreamDestroy(h->stream);
+    delete h;
+    return RADOP_OK;
+}
+
+const char *radop_last_error(const RadopHandle *h) { return h ? h->err.c_str() : "null handle"; }
+
+int radop_set_params(RadopHandle *h, const RadopParams *p)
+{
+    if (!h || !p) return RADOP_ERR_ARG;
+    if (p->abi_version != RADOP_ABI_VERSION) return h->fail(RADOP_ERR_ARG, "RadopParams.abi_version mismatch");
+    if (p->n_gates <= 0) return h->fail(RADOP_ERR_ARG, "n_gates must be positive");
+    if (p->n_species <= 0 || p->n_species > RADOP_NSPECIES_MAX) return h->fail(RADOP_ERR_ARG, "bad n_species");
+    if (p->doppler_scheme != 1)
+        return h->fail(RADOP_ERR_UNSUPPORTED, "only doppler scheme 1 is implemented on the GPU in this build");
+    if (p->sensitivity_mode < 0 || p->sensitivity_mode > 2)
+        return h->fail(RADOP_ERR_UNSUPPORTED, "sensitivity must be [ZH] or [ZH, range]");
+    for (int s = 0; s < p->n_species; ++s) {
+        int qm, qn;
+        if (species_vars(p->species[s].species, &qm, &qn)) return h->fail(RADOP_ERR_ARG, "unknown species id");
+        if (p->species[s].psd < 0 || p->species[s].psd > RADOP_PSD_2MOM) return h->fail(RADOP_ERR_ARG, "unknown psd family");
+    }
+    h->p = *p;
+    h->have_params = true;
+    h->executed = false;
+    return RADOP_OK;
+}
+
+int radop_upload_grid(RadopHandle *h, int nz, int ny, int nx, const float *zlevels, const float llc[2],
+                      const float urc[2], const float res[2], const double south_pole[2])
+{
+    if (!h || !zlevels || !llc || !urc || !res || !south_pole) return RADOP_ERR_ARG;
+    if (nz < 4 || ny < 2 || nx < 2) return h->fail(RADOP_ERR_ARG, "grid too small (nz >= 4, ny, nx >= 2)");
+    CU(h, cudaSetDevice(h->device));
+    size_t n = (size_t)nz * ny * nx;
+    CU(h, h->z_t.reserve(n * 4));
+    CU(h, h->fields.reserve(n * RADOP_NVP * 4));
+    CU(h, h->stage.reserve(n * 4));
+    CU(h, cudaMemsetAsync(h->fields.p, 0, n * RADOP_NVP * 4, h->stream));
+    CU(h, cudaMemcpyAsync(h->stage.p, zlevels, n * 4, cudaMemcpyHostToDevice, h->stream));
+    k_pack_zlevels<<<h->n_sm * 8, 256, 0, h->stream>>>(h->stage.as<float>(), h->z_t.as<float>(), nz, ny, nx);
+    CU(h, cudaGetLastError());
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->nz = nz; h->ny = ny; h->nx = nx;
+    for (int i = 0; i < 2; ++i) { h->llc[i] = llc[i]; h->urc[i] = urc[i]; h->res[i] = res[i]; }
+    // rotation geographic -> rotated pole: about z by the pole longitude, about y by 90 + pole latitude
+    const double d2r = 0.017453292519943295;
+    double th = (90.0 + south_pole[0]) * d2r, ph = south_pole[1] * d2r;
+    double ct = cos(th), st = sin(th), cp = cos(ph), sp = sin(ph);
+    double R[9] = {ct * cp, ct * sp, st, -sp, cp, 0.0, -st * cp, -st * sp, ct};
+    memcpy(h->rot, R, sizeof R);
+    h->var_mask = 0;
+    h->have_grid = true;
+    h->executed = false;
+    return RADOP_OK;
+}
+
+int radop_upload_field(RadopHandle *h, int var_id, const float *data)
+{
+    if (!h || !data) return RADOP_ERR_ARG;
+    if (!h->have_grid) return h->fail(RADOP_ERR_STATE, "upload the grid before the fields");
+    if (var_id < 0 || var_id >= RADOP_NVAR_MAX - 1) return h->fail(RADOP_ERR_ARG, "unknown variable id");
+    CU(h, cudaSetDevice(h->device));
+    size_t n = (size_t)h->nz * h->ny * h->nx;
+    CU(h, cudaMemcpyAsync(h->stage.p, data, n * 4, cudaMemcpyHostToDevice, h->stream));
+    k_pack_field<<<h->n_sm * 8, 256, 0, h->stream>>>(h->stage.as<float>(), h->fields.as<float>(), h->nz, h->ny, h->nx, var_id);
+    CU(h, cudaGetLastError());
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->var_mask |= (1u << var_id);
+    h->executed = false;
+    return RADOP_OK;
+}
+
+int radop_upload_lut(RadopHandle *h, int species, const double *value_table, int ne, int nt, int nd, float e_min,
+                     float e_step, float t_min, float t_step, const float *d_axis)
+{
+    if (!h || !value_table || !d_axis) return RADOP_ERR_ARG;
+    if (!h->have_params) return h->fail(RADOP_ERR_STATE, "set the parameters (species constants) before the tables");
+    if (species < 0 || species >= RADOP_NSPECIES_MAX) return h->fail(RADOP_ERR_ARG, "unknown species id");
+    if (ne <= 0 || nt <= 0 || nd < 2 || (nd % 4) != 0) return h->fail(RADOP_ERR_LUT, "bad table shape (nd must be a multiple of 4)");
+    const RadopSpecies *S = nullptr;
+    for (int s = 0; s < h->p.n_species; ++s)
+        if (h->p.species[s].species == species) S = &h->p.species[s];
+    if (!S) return h->fail(RADOP_ERR_ARG, "species is not part of the current parameters");
+    CU(h, cudaSetDevice(h->device));
+    LutHost &L = h->lut[species];
+    // uniformity of the diameter grid (np.linspace in compute_lut_sz.py:398)
+    double d0 = d_axis[0], dD = ((double)d_axis[nd - 1] - d0) / (nd - 1), dev = 0;
+    for (int k = 0; k < nd; ++k) dev = std::max(dev, fabs((double)d_axis[k] - (d0 + k * dD)));
+    bool uniform = dev <= 4e-7 * std::max(1.0, fabs((double)d_axis[nd - 1])) + 1e-12;
+    if (S->psd == RADOP_PSD_1MOM_ICE) {
+        if (!uniform) return h->fail(RADOP_ERR_LUT, "1-mom ice needs a uniform diameter axis");
+        L.mode = MODE_ICE1; L.ncol = 12; L.cost = 15;
+    } else if (S->numeric_vn) {
+        L.mode = MODE_GEN12; L.ncol = 12; L.cost = 15;
+    } else if (S->nu == 1.0 && uniform && (nd % RADOP_HBLOCK) == 0) {
+        L.mode = MODE_GEO8; L.ncol = 8; L.cost = 9;
+    } else {
+        L.mode = MODE_GEN8; L.ncol = 8; L.cost = 11;
+    }
+    L.ne = ne; L.nt = nt; L.nd = nd;
+    L.e_min = e_min; L.e_step = e_step; L.t_min = t_min; L.t_step = t_step;
+    L.dD_geo = (float)dD;
+    L.dD_ref = d_axis[1] - d_axis[0];
+    L.packed_for = *S;
+    size_t rows = (size_t)ne * nt * nd;
+    DevBuf raw, dax;
+    CU(h, raw.reserve(rows * 12 * 8));
+    CU(h, dax.reserve((size_t)nd * 4));
+    CU(h, L.table.reserve(rows * L.ncol * 4));
+    CU(h, L.aux.reserve((size_t)3 * nd * 4));
+    CU(h, cudaMemcpyAsync(raw.p, value_table, rows * 12 * 8, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(dax.p, d_axis, (size_t)nd * 4, cudaMemcpyHostToDevice, h->stream));
+    k_pack_lut<<<h->n_sm * 8, 256, 0, h->stream>>>(raw.as<double>(), L.table.as<float>(), dax.as<float>(), rows, nd,
+                                                  L.ncol, L.mode, S->mu, (double)L.dD_ref, S->alpha, S->beta, S->a, S->b);
+    CU(h, cudaGetLastError());
+    k_pack_aux<<<(nd + 255) / 256, 256, 0, h->stream>>>(dax.as<float>(), L.aux.as<float>(), nd, S->nu);
+    CU(h, cudaGetLastError());
+    CU(h, cudaStreamSynchronize(h->stream));
+    raw.release();
+    dax.release();
+    L.loaded = true;
+    h->executed = false;
+    return RADOP_OK;
+}
+
+static int ensure_pinned(RadopHandle *h, size_t bytes)
+{
+    if (bytes <= h->pinned_cap) return RADOP_OK;
+    if (h->pinned) cudaFreeHost(h->pinned);
+    h->pinned = nullptr;
+    h->pinned_cap = 0;
+    CU(h, cudaHostAlloc(&h->pinned, bytes + bytes / 4 + 4096, cudaHostAllocDefault));
+    h->pinned_cap = bytes + bytes / 4 + 4096;
+    return RADOP_OK;
+}
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+int radop_stage_scan(RadopHandle *h, const RadopScan *sc)
+{
+    if (!h || !sc) return RADOP_ERR_ARG;
+    if (!h->have_params) return h->fail(RADOP_ERR_STATE, "parameters not set");
+    if (sc->n_rays <= 0 || sc->n_sub <= 0 || sc->n_traj <= 0 || sc->n_vert <= 0)
+        return h->fail(RADOP_ERR_ARG, "empty scan");
+    if (!sc->ray_az || !sc->ray_traj || !sc->sub_daz || !sc->sub_jv || !sc->sub_weight || !sc->traj_s || !sc->traj_h || !sc->traj_e)
+        return h->fail(RADOP_ERR_ARG, "null scan array");
+    for (int r = 0; r < sc->n_rays; ++r)
+        if (sc->ray_traj[r] < 0 || sc->ray_traj[r] >= sc->n_traj) return h->fail(RADOP_ERR_ARG, "ray_traj out of range");
+    for (int q = 0; q < sc->n_sub; ++q)
+        if (sc->sub_jv[q] < 0 || sc->sub_jv[q] >= sc->n_vert) return h->fail(RADOP_ERR_ARG, "sub_jv out of range");
+    CU(h, cudaSetDevice(h->device));
+    const int ng = h->p.n_gates;
+    const size_t ntr = (size_t)sc->n_traj * sc->n_vert * ng;
+    // one pinned blob, one H2D copy
+    size_t off = 0, o_az, o_tr, o_ny, o_daz, o_jv, o_w, o_s, o_h, o_e;
+    o_az = off; off = align_up(off + (size_t)sc->n_rays * 8, 256);
+    o_tr = off; off = align_up(off + (size_t)sc->n_rays * 4, 256);
+    o_ny = off; off = align_up(off + (size_t)sc->n_rays * 4, 256);
+    o_daz = off; off = align_up(off + (size_t)sc->n_sub * 8, 256);
+    o_jv = off; off = align_up(off + (size_t)sc->n_sub * 4, 256);
+    o_w = off; off = align_up(off + (size_t)sc->n_sub * 8, 256);
+    o_s = off; off = align_up(off + ntr * 4, 256);
+    o_h = off; off = align_up(off + ntr * 4, 256);
+    o_e = off; off = align_up(off + ntr * 4, 256);
+    int rc = ensure_pinned(h, off);
+    if (rc) return rc;
+    CU(h, h->scan_blob.reserve(off));
+    CU(h, cudaStreamSynchronize(h->stream));   // the pinned blob may still be in flight
+    char *P = (char *)h->pinned;
+    memcpy(P + o_az, sc->ray_az, (size_t)sc->n_rays * 8);
+    memcpy(P + o_tr, sc->ray_traj, (size_t)sc->n_rays * 4);
+    if (sc->ray_nyquist) memcpy(P + o_ny, sc->ray_nyquist, (size_t)sc->n_rays * 4);
+    memcpy(P + o_daz, sc->sub_daz, (size_t)sc->n_sub * 8);
+    memcpy(P + o_jv, sc->sub_jv, (size_t)sc->n_sub * 4);
+    memcpy(P + o_w, sc->sub_weight, (size_t)sc->n_sub * 8);
+    memcpy(P + o_s, sc->traj_s, ntr * 4);
+    memcpy(P + o_h, sc->traj_h, ntr * 4);
+    memcpy(P + o_e, sc->traj_e, ntr * 4);
+    CU(h, cudaMemcpyAsync(h->scan_blob.p, P, off, cudaMemcpyHostToDevice, h->stream));
+    char *D = (char *)h->scan_blob.p;
+    h->scan.ray_az = (const double *)(D + o_az);
+    h->scan.ray_traj = (const int *)(D + o_tr);
+    h->d_nyquist = sc->ray_nyquist ? (const float *)(D + o_ny) : nullptr;
+    h->scan.sub_daz = (const double *)(D + o_daz);
+    h->scan.sub_jv = (const int *)(D + o_jv);
+    h->scan.sub_weight = (const double *)(D + o_w);
+    h->scan.traj_s = (const float *)(D + o_s);
+    h->scan.traj_h = (const float *)(D + o_h);
+    h->scan.traj_e = (const float *)(D + o_e);
+    h->n_rays = sc->n_rays; h->n_sub = sc->n_sub; h->n_traj = sc->n_traj; h->n_vert = sc->n_vert;
+    h->center_sub = sc->n_sub / 2;          // idx_0 = int(num_beams / 2), doppler_scatter.py:89
+    h->n_sbg = (long long)sc->n_rays * sc->n_sub * ng;
+    h->have_scan = true;
+    h->executed = false;
+    return RADOP_OK;
+}
+
+static int prepare(RadopHandle *h)
+{
+    if (!h->have_params || !h->have_grid || !h->have_scan) return h->fail(RADOP_ERR_STATE, "params, grid and scan are needed before execute");
+    const RadopParams &p = h->p;
+    DevConfig &c = h->cfg;
+    memset(&c, 0, sizeof c);
+    c.n_rays = h->n_rays; c.n_sub = h->n_sub; c.n_gates = p.n_gates; c.n_vert = h->n_vert; c.center_sub = h->center_sub;
+    c.radar_lat = p.radar_lat; c.radar_lon = p.radar_lon;
+    c.nz = h->nz; c.ny = h->ny; c.nx = h->nx;
+    for (int i = 0; i < 2; ++i) { c.llc[i] = h->llc[i]; c.urc[i] = h->urc[i]; c.res[i] = h->res[i]; }
+    memcpy(c.rot, h->rot, sizeof c.rot);
+    c.var_mask = h->var_mask;
+    c.n_species = p.n_species;
+    c.two_moment = p.two_moment; c.doppler_scheme = p.doppler_scheme; c.with_attenuation = p.with_attenuation;
+    c.sensitivity_mode = p.sensitivity_mode; c.output_model_vars = p.output_model_vars; c.keep_debug = p.keep_debug;
+    c.wavelength = (float)p.wavelength_mm; c.k_squared = (float)p.k_squared; c.radial_res = (float)p.radial_resolution_m;
+    c.sens0 = (float)p.sensitivity[0]; c.sens1 = (float)p.sensitivity[1];
+    c.ice_numeric = -1;
+    uint32_t need = (1u << RADOP_VAR_U) | (1u << RADOP_VAR_V) | (1u << RADOP_VAR_W) | (1u << RADOP_VAR_T);
+    int bins = 0;
+    size_t smem = 0;
+    for (int s = 0; s < p.n_species; ++s) {
+        const RadopSpecies &S = p.species[s];
+        const LutHost &L = h->lut[S.species];
+        if (!L.loaded) return h->fail(RADOP_ERR_LUT, "a lookup table is missing for one of the species");
+        if (memcmp(&L.packed_for, &S, sizeof S) != 0)
+            return h->fail(RADOP_ERR_LUT, "species constants changed since the table upload: upload the table again");
+        SpeciesDev &d = c.sp[s];
+        d.species = S.species; d.psd = S.psd; d.mode = L.mode; d.ncol = L.ncol; d.numeric_vn = S.numeric_vn;
+        d.ne = L.ne; d.nt = L.nt; d.nd = L.nd;
+        d.e_min = L.e_min; d.e_step = L.e_step; d.t_min = L.t_min; d.t_step = L.t_step;
+        d.bin_base = bins; d.cost = L.cost;
+        species_vars(S.species, &d.qm_var, &d.qn_var);
+        need |= (1u << d.qm_var);
+        if (S.psd == RADOP_PSD_2MOM) need |= (1u << d.qn_var);
+        d.dD_geo = L.dD_geo; d.dD_ref = L.dD_ref;
+        d.table = L.table.as<float>(); d.aux = L.aux.as<float>();
+        d.a = S.a; d.b = S.b; d.alpha = S.alpha; d.beta = S.beta; d.mu = S.mu; d.nu = S.nu; d.N0 = S.N0;
+        d.lambda_factor = S.lambda_factor; d.vel_factor = S.vel_factor; d.ntot_factor = S.ntot_factor;
+        d.x_min = S.x_min; d.x_max = S.x_max;
+        if (S.numeric_vn) {
+            if (c.ice_numeric >= 0) return h->fail(RADOP_ERR_UNSUPPORTED, "only one species may have numeric fall-speed moments");
+            c.ice_numeric = s;
+        }
+        bins += L.ne * L.nt;
+        smem = std::max(smem, (size_t)L.nd * L.ncol * 4 + (size_t)L.nd * 4);
+    }
+    if ((h->var_mask & need) != need) return h->fail(RADOP_ERR_STATE, "a model variable needed by the configuration was not uploaded");
+    if (bins >= 0xFFFF) return h->fail(RADOP_ERR_LUT, "too many (species, e, t) bins");
+    if (bins * 4 > 200 * 1024) return h->fail(RADOP_ERR_LUT, "bin histogram does not fit shared memory");
+    c.total_bins = bins;
+    if (h->n_sbg * p.n_species >= 0x7fffffffLL || h->n_sbg >= 0xfffffff0LL)
+        return h->fail(RADOP_ERR_ARG, "scan too large for one call (rays x sub-beams x gates x species >= 2^31)");
+    h->k2_smem = smem;
+    return RADOP_OK;
+}
+
+int radop_execute(RadopHandle *h)
+{
+    if (!h) return RADOP_ERR_ARG;
+    int rc = prepare(h);
+    if (rc) return rc;
+    CU(h, cudaSetDevice(h->device));
+    const DevConfig &c = h->cfg;
+    const long long n = h->n_sbg;
+    const int nsp = c.n_species, ng = c.n_gates;
+    const size_t n_rg = (size_t)c.n_rays * ng;
+    const bool want_vals = c.output_model_vars || c.keep_debug;
+    CU(h, h->mask.reserve(n));
+    CU(h, h->active.reserve(n));
+    CU(h, h->wind.reserve(n * 4));
+    CU(h, h->sinth.reserve(n * 4));
+    CU(h, h->vsum.reserve(n * 4));
+    CU(h, h->nsum.reserve(n * 4));
+    CU(h, h->key.reserve((size_t)n * nsp * 2));
+    CU(h, h->p0.reserve((size_t)n * nsp * 4));
+    CU(h, h->p1.reserve((size_t)n * nsp * 4));
+    if (want_vals) CU(h, h->vals.reserve((size_t)n * RADOP_NVP * 4));
+    CU(h, h->lat.reserve(n_rg * 8));
+    CU(h, h->lon.reserve(n_rg * 8));
+    CU(h, h->hist.reserve((size_t)c.total_bins * 4));
+    CU(h, h->flags.reserve(16));
+    CU(h, h->bin_start.reserve((size_t)(c.total_bins + 1) * 4));
+    CU(h, h->tile_start.reserve((size_t)(c.total_bins + 1) * 4));
+    CU(h, h->cost_start.reserve((size_t)(c.total_bins + 1) * 8));
+    CU(h, h->cursor.reserve((size_t)c.total_bins * 4));
+    CU(h, h->totals.reserve(4 * 8));
+    CU(h, h->rec.reserve((size_t)n * nsp * sizeof(PairRec)));
+    CU(h, h->sz_out.reserve((size_t)n * nsp * 8 * 4));
+    CU(h, h->ice_vn.reserve((size_t)n * 8));
+    CU(h, h->ice_tot.reserve((size_t)c.n_rays * c.n_sub * 3 * 4));
+    CU(h, h->comb.reserve(n_rg * 8 * 4));
+    CU(h, h->out.reserve(n_rg * (RADOP_N_OUT + 1) * 4));
+    if (c.output_model_vars) CU(h, h->model_out.reserve(n_rg * RADOP_NVP * 4));
+    if (c.keep_debug) {
+        CU(h, h->dbg_cell.reserve((size_t)n * 2 * 4));
+        CU(h, h->dbg_level.reserve((size_t)n * 4 * 4));
+        CU(h, h->dbg_status.reserve((size_t)n * 4));
+        CU(h, h->dbg_e.reserve((size_t)n * nsp * 4));
+        CU(h, h->dbg_t.reserve((size_t)n * nsp * 4));
+        CU(h, h->dbg_rot.reserve((size_t)n * 2 * 8));
+    }
+    static bool attr_done[64] = {false};
+    if (!attr_done[h->device & 63]) {
+        CU(h, cudaFuncSetAttribute(k_integrate, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(h, cudaFuncSetAttribute(k_interp_psd, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(h, cudaFuncSetAttribute(k_scatter_pairs, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_done[h->device & 63] = true;
+    }
+    int occ = 1;
+    CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_integrate, RADOP_TILE_THREADS, h->k2_smem));
+    h->k2_blocks = std::max(1, occ) * h->n_sm;
+
+    cudaStream_t st = h->stream;
+    int launches = 0;
+    if (h->timing) CU(h, cudaEventRecord(h->ev[0], st));
+    CU(h, cudaMemsetAsync(h->hist.p, 0, (size_t)c.total_bins * 4, st));
+    CU(h, cudaMemsetAsync(h->flags.p, 0, 16, st));
+
+    K1Out o;
+    memset(&o, 0, sizeof o);
+    o.mask = h->mask.as<int8_t>(); o.active = h->active.as<uint8_t>();
+    o.wind = h->wind.as<float>(); o.sinth = h->sinth.as<float>(); o.vsum = h->vsum.as<float>(); o.nsum = h->nsum.as<float>();
+    o.key = h->key.as<uint16_t>(); o.p0 = h->p0.as<float>(); o.p1 = h->p1.as<float>();
+    o.vals = want_vals ? h->vals.as<float>() : nullptr;
+    o.lat = h->lat.as<double>(); o.lon = h->lon.as<double>();
+    o.hist = h->hist.as<int>(); o.flags = h->flags.as<int>();
+    if (c.keep_debug) {
+        o.dbg_cell = h->dbg_cell.as<int>(); o.dbg_level = h->dbg_level.as<int>(); o.dbg_status = h->dbg_status.as<int>();
+        o.dbg_e = h->dbg_e.as<int>(); o.dbg_t = h->dbg_t.as<int>(); o.dbg_rot = h->dbg_rot.as<double>();
+    }
+    const size_t hist_smem = (size_t)c.total_bins * 4;
+    k_interp_psd<<<(unsigned)((n + 127) / 128), 128, hist_smem, st>>>(c, h->scan, h->z_t.as<float>(), h->fields.as<float>(), o, n);
+    CU(h, cudaGetLastError()); ++launches;
+    if (h->timing) CU(h, cudaEventRecord(h->ev[1], st));
+
+    k_scan_bins<<<1, 1024, 0, st>>>(c, h->hist.as<int>(), h->bin_start.as<int>(), h->tile_start.as<int>(),
+                                     h->cost_start.as<long long>(), h->cursor.as<int>(), h->totals.as<long long>());
+    CU(h, cudaGetLastError()); ++launches;
+    k_scatter_pairs<<<(unsigned)((n + 255) / 256), 256, hist_smem, st>>>(c, h->key.as<uint16_t>(), h->p0.as<float>(), h->p1.as<float>(),
+                                                                          h->scan.sub_weight, h->cursor.as<int>(), h->rec.as<PairRec>(), n);
+    CU(h, cudaGetLastError()); ++launches;
+    if (h->timing) CU(h, cudaEventRecord(h->ev[2], st));
+
+    K2Args a2;
+    a2.hist = h->hist.as<int>(); a2.bin_start = h->bin_start.as<int>(); a2.tile_start = h->tile_start.as<int>();
+    a2.cost_start = h->cost_start.as<long long>(); a2.totals = h->totals.as<long long>();
+    a2.rec = h->rec.as<PairRec>(); a2.sz_out = h->sz_out.as<float>(); a2.ice_vn = h->ice_vn.as<float2>();
+    k_integrate<<<h->k2_blocks, RADOP_TILE_THREADS, h->k2_smem, st>>>(c, a2);
+    CU(h, cudaGetLastError()); ++launches;
+    if (h->timing) CU(h, cudaEventRecord(h->ev[3], st));
+
+    if (c.ice_numeric >= 0 && c.doppler_scheme == 1) {
+        int warps = c.n_rays * c.n_sub;
+        k_ice_totals<<<(warps * 32 + 127) / 128, 128, 0, st>>>(c, h->active.as<uint8_t>(), h->ice_vn.as<float2>(), h->ice_tot.as<float>());
+        CU(h, cudaGetLastError()); ++launches;
+    }
+    K3Args a3;
+    a3.mask = h->mask.as<int8_t>(); a3.active = h->active.as<uint8_t>();
+    a3.wind = h->wind.as<float>(); a3.sinth = h->sinth.as<float>(); a3.vsum = h->vsum.as<float>(); a3.nsum = h->nsum.as<float>();
+    a3.sz_out = h->sz_out.as<float>(); a3.ice_tot = h->ice_tot.as<float>();
+    a3.vals = want_vals ? h->vals.as<float>() : nullptr;
+    a3.sub_weight = h->scan.sub_weight; a3.ray_nyquist = h->d_nyquist;
+    a3.comb = h->comb.as<float>(); a3.out = h->out.as<float>();
+    a3.model_out = c.output_model_vars ? h->model_out.as<float>() : nullptr;
+    k_reduce_subbeams<<<(unsigned)((n_rg + 127) / 128), 128, 0, st>>>(c, a3);
+    CU(h, cudaGetLastError()); ++launches;
+    k_ray_epilogue<<<(c.n_rays * 32 + 127) / 128, 128, 0, st>>>(c, a3);
+    CU(h, cudaGetLastError()); ++launches;
+    if (h->timing) CU(h, cudaEventRecord(h->ev[4], st));
+    h->stats.launches = launches;
+    h->stats.n_subbeam_gates = n;
+    h->executed = true;
+    return RADOP_OK;
+}
+
+int radop_synchronize(RadopHandle *h)
+{
+    if (!h) return RADOP_ERR_ARG;
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return RADOP_OK;
+}
+
+static int finish(RadopHandle *h)
+{   // after the stream has drained: flags + statistics
+    long long tot[4];
+    int flags[4];
+    CU(h, cudaMemcpy(tot, h->totals.p, sizeof tot, cudaMemcpyDeviceToHost));
+    CU(h, cudaMemcpy(flags, h->flags.p, sizeof flags, cudaMemcpyDeviceToHost));
+    h->stats.n_active_pairs = tot[0];
+    h->stats.n_tiles = tot[1];
+    h->stats.n_lut_bins = tot[3];
+    if (h->timing) {
+        cudaEventElapsedTime(&h->stats.ms_interp, h->ev[0], h->ev[1]);
+        cudaEventElapsedTime(&h->stats.ms_sort, h->ev[1], h->ev[2]);
+        cudaEventElapsedTime(&h->stats.ms_integrate, h->ev[2], h->ev[3]);
+        cudaEventElapsedTime(&h->stats.ms_reduce, h->ev[3], h->ev[4]);
+        cudaEventElapsedTime(&h->stats.ms_total, h->ev[0], h->ev[4]);
+    }
+    if (flags[0] & 1)
+        return h->fail(RADOP_ERR_OUT_OF_DOMAIN, "radar domain is not entirely contained in the model domain");
+    return RADOP_OK;
+}
+
+int radop_fetch(RadopHandle *h, const RadopOut *out)
+{
+    if (!h) return RADOP_ERR_ARG;
+    if (!h->executed) return h->fail(RADOP_ERR_STATE, "nothing executed");
+    CU(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    const size_t n_rg = (size_t)h->cfg.n_rays * h->cfg.n_gates;
+    if (out) {
+        for (int v = 0; v < RADOP_N_OUT; ++v)
+            if (out->obs[v]) CU(h, cudaMemcpyAsync(out->obs[v], h->out.as<float>() + (size_t)v * n_rg, n_rg * 4, cudaMemcpyDeviceToHost, st));
+        if (out->mask) CU(h, cudaMemcpyAsync(out->mask, h->out.as<float>() + (size_t)RADOP_N_OUT * n_rg, n_rg * 4, cudaMemcpyDeviceToHost, st));
+        if (out->lat) CU(h, cudaMemcpyAsync(out->lat, h->lat.p, n_rg * 8, cudaMemcpyDeviceToHost, st));
+        if (out->lon) CU(h, cudaMemcpyAsync(out->lon, h->lon.p, n_rg * 8, cudaMemcpyDeviceToHost, st));
+        for (int v = 0; v < RADOP_NVAR_MAX; ++v)
+            if (out->model[v]) {
+                if (!h->cfg.output_model_vars || !(h->var_mask & (1u << v))) return h->fail(RADOP_ERR_ARG, "model output requested but not computed");
+                CU(h, cudaMemcpyAsync(out->model[v], h->model_out.as<float>() + (size_t)v * n_rg, n_rg * 4, cudaMemcpyDeviceToHost, st));
+            }
+    }
+    CU(h, cudaStreamSynchronize(st));
+    return finish(h);
+}
+
+int radop_simulate(RadopHandle *h, const RadopScan *scan, const RadopOut *out)
+{
+    int rc = radop_stage_scan(h, scan);
+    if (rc) return rc;
+    rc = radop_execute(h);
+    if (rc) return rc;
+    return radop_fetch(h, out);
+}
+
+int radop_device_outputs(RadopHandle *h, void **dev_ptr, int64_t *n_rays, int64_t *n_gates)
+{
+    if (!h || !dev_ptr) return RADOP_ERR_ARG;
+    if (!h->executed) return h->fail(RADOP_ERR_STATE, "nothing executed");
+    *dev_ptr = h->out.p;
+    if (n_rays) *n_rays = h->cfg.n_rays;
+    if (n_gates) *n_gates = h->cfg.n_gates;
+    return RADOP_OK;
+}
+
+int radop_get_stream(RadopHandle *h, void **stream)
+{
+    if (!h || !stream) return RADOP_ERR_ARG;
+    *stream = (void *)h->stream;
+    return RADOP_OK;
+}
+
+int radop_enable_timing(RadopHandle *h, int on)
+{
+    if (!h) return RADOP_ERR_ARG;
+    h->timing = on != 0;
+    return RADOP_OK;
+}
+
+int radop_get_stats(RadopHandle *h, RadopStats *s)
+{
+    if (!h || !s) return RADOP_ERR_ARG;
+    *s = h->stats;
+    return RADOP_OK;
+}
+
+int radop_debug_indices(RadopHandle *h, int32_t *cell, int32_t *level, int32_t *status, int32_t *lut_e,
+                        int32_t *lut_t, float *values, double *rot_coords)
+{
+    if (!h) return RADOP_ERR_ARG;
+    if (!h->executed || !h->cfg.keep_debug) return h->fail(RADOP_ERR_STATE, "execute with keep_debug = 1 first");
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaStreamSynchronize(h->stream));
+    const size_t n = (size_t)h->n_sbg;
+    const int nsp = h->cfg.n_species;
+    if (cell) CU(h, cudaMemcpy(cell, h->dbg_cell.p, n * 2 * 4, cudaMemcpyDeviceToHost));
+    if (level) CU(h, cudaMemcpy(level, h->dbg_level.p, n * 4 * 4, cudaMemcpyDeviceToHost));
+    if (status) CU(h, cudaMemcpy(status, h->dbg_status.p, n * 4, cudaMemcpyDeviceToHost));
+    if (lut_e) CU(h, cudaMemcpy(lut_e, h->dbg_e.p, n * nsp * 4, cudaMemcpyDeviceToHost));
+    if (lut_t) CU(h, cudaMemcpy(lut_t, h->dbg_t.p, n * nsp * 4, cudaMemcpyDeviceToHost));
+    if (rot_coords) CU(h, cudaMemcpy(rot_coords, h->dbg_rot.p, n * 2 * 8, cudaMemcpyDeviceToHost));
+    if (values) {
+        // compact [n][n_uploaded] in ascending variable id
+        std::vector<float> tmp(n * RADOP_NVP);
+        CU(h, cudaMemcpy(tmp.data(), h->vals.p, n * RADOP_NVP * 4, cudaMemcpyDeviceToHost));
+        int nv = 0;
+        int ids[RADOP_NVP];
+        for (int v = 0; v < RADOP_NVP; ++v)
+            if (h->var_mask & (1u << v)) ids[nv++] = v;
+        for (size_t i = 0; i < n; ++i)
+            for (int j = 0; j < nv; ++j) values[i * nv + j] = tmp[i * RADOP_NVP + ids[j]];
+    }
+    return RADOP_OK;
+}
+
+int radop_measure_fp32_peak(RadopHandle *h, double *tflops)
+{
+    if (!h || !tflops) return RADOP_ERR_ARG;
+    CU(h, cudaSetDevice(h->device));
+    const int blocks = h->n_sm * 8, threads = 256, iters = 20000;
+    DevBuf sink;
+    CU(h, sink.reserve((size_t)blocks * threads * 4));
+    cudaEvent_t a, b;
+    CU(h, cudaEventCreate(&a));
+    CU(h, cudaEventCreate(&b));
+    double best = 0;
+    for (int rep = 0; rep < 4; ++rep) {
+        CU(h, cudaEventRecord(a, h->stream));
+        k_fma_probe<<<blocks, threads, 0, h->stream>>>(sink.as<float>(), iters, 0.5f);
+        CU(h, cudaGetLastError());
+        CU(h, cudaEventRecord(b, h->stream));
+        CU(h, cudaEventSynchronize(b));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, a, b);
+        double fl = (double)blocks * threads * 16.0 * 8.0 * iters * 2.0;
+        if (rep > 0) best = std::max(best, fl / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    sink.release();
+    *tflops = best;
+    return RADOP_OK;
+}
+
+int radop_get_all_radar_pts(RadopHandle *h, int n, const float *coords, const float *heights_gates, const float *data,
+                            const float *model_heights, int nz, int ny, int nx, const float *llc, const float *res,
+                            float *output)
+{
+    if (!h || !coords || !heights_gates || !data || !model_heights || !llc || !res || !output || n <= 0)
+        return RADOP_ERR_ARG;
+    CU(h, cudaSetDevice(h->device));
+    DevBuf dc, dh, dd, dz, dout;
+    size_t cells = (size_t)nz * ny * nx;
+    CU(h, dc.reserve((size_t)n * 8));
+    CU(h, dh.reserve((size_t)n * 4));
+    CU(h, dd.reserve(cells * 4));
+    CU(h, dz.reserve(cells * 4));
+    CU(h, dout.reserve((size_t)n * 4));
+    CU(h, cudaMemcpyAsync(dc.p, coords, (size_t)n * 8, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(dh.p, heights_gates, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(dd.p, data, cells * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(dz.p, model_heights, cells * 4, cudaMemcpyHostToDevice, h->stream));
+    k_interp_compat<<<(n + 127) / 128, 128, 0, h->stream>>>(n, dc.as<float>(), dh.as<float>(), dd.as<float>(), dz.as<float>(), nz, ny, nx,
+                                                           llc[0], llc[1], res[0], res[1], dout.as<float>());
+    CU(h, cudaGetLastError());
+    CU(h, cudaMemcpyAsync(output, dout.p, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    dc.release(); dh.release(); dd.release(); dz.release(); dout.release();
+    return RADOP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,1231 @@
+// radop_kernels.cu -- hand-written sm_100a kernels of the radar forward operator hot path.
+//
+//  K0  k_pack_*            one-time: transpose model fields into a column-major,
+//                          variable-interleaved layout; combine + premultiply LUT columns
+//  K1  k_interp_psd        per sub-beam gate: geolocation, trilinear interpolation of all
+//                          variables (bit-exact restatement of interpolation_c.c), PSD
+//                          parameters, LUT bin keys, analytic Doppler moments, histogram
+//  K1b k_scan_bins / k_scatter_pairs    counting sort of the active pairs by LUT bin
+//  K2  k_integrate         PSD x scattering-table contraction over 1024 diameters
+//                          (the FLOP carrier): LUT slice staged in shared memory by TMA
+//                          bulk copy, register-tiled blocked-Horner evaluation
+//  K3  k_ice_totals / k_reduce_subbeams / k_ray_epilogue
+//                          quadrature + species sums, polarimetric observables,
+//                          PHIDP / attenuation prefix scans with warp shuffles
+#include "radop_kernels.cuh"
+#include <math.h>
+
+// ------------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float ex2f_approx(float x)
+{
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ uint32_t smem_u32(const void *p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok)
+                     : "r"(smem_u32(bar)), "r"(parity)
+                     : "memory");
+    } while (!ok);
+}
+// 1-D TMA bulk copy global -> shared, completion signalled on an mbarrier
+__device__ __forceinline__ void tma_bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async()
+{
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// ------------------------------------------------------------------------------------------
+// K0: one-time layout transforms
+// ------------------------------------------------------------------------------------------
+// z-levels [nz][ny][nx] -> [ny][nx][nz]
+__global__ void k_pack_zlevels(const float *__restrict__ src, float *__restrict__ dst, int nz, int ny, int nx)
+{
+    size_t n = (size_t)nz * ny * nx;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        size_t col = i % ((size_t)ny * nx);
+        size_t l = i / ((size_t)ny * nx);
+        dst[col * nz + l] = src[i];
+    }
+}
+// variable [nz][ny][nx] -> fields[ny][nx][nz][NVP] at slot var
+__global__ void k_pack_field(const float *__restrict__ src, float *__restrict__ dst, int nz, int ny, int nx, int var)
+{
+    size_t n = (size_t)nz * ny * nx;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        size_t col = i % ((size_t)ny * nx);
+        size_t l = i / ((size_t)ny * nx);
+        dst[(col * nz + l) * RADOP_NVP + var] = src[i];
+    }
+}
+
+// LUT value_table [ne][nt][nd][12] float64 -> combined float32 [ne][nt][nd][ncol]
+// columns: 0: b = s0-s1-s2+s3   1: c = s0+s1+s2+s3   2: p = s4+s7   3: q = s6-s5
+//          4: kd = s10-s8       5: s9                6: s11         7: spare
+// (all the reference derives from the 12 columns is linear in them and enters
+//  get_pol_from_sz only through these seven combinations, doppler_scatter.py:516-542;
+//  forming s10-s8 in float64 BEFORE the integral removes the KDP cancellation)
+// premultiplied by  D^mu * dD  (GEO/GEN modes) or dD (ICE1, whose shape function is
+// evaluated in the kernel); 12-column modes add 7: v(D), 8: 1, 9: m(D) (ICE1 only).
+__global__ void k_pack_lut(const double *__restrict__ src, float *__restrict__ dst, const float *__restrict__ d_axis,
+                           size_t n_rows, int nd, int ncol, int mode, double mu, double dD, double alpha,
+                           double beta, double a_m, double b_m)
+{
+    for (size_t r = blockIdx.x * (size_t)blockDim.x + threadIdx.x; r < n_rows;
+         r += (size_t)gridDim.x * blockDim.x) {
+        int k = (int)(r % nd);
+        const double *s = src + r * 12;
+        double D = (double)d_axis[k];
+        double pre = (mode == MODE_ICE1) ? dD : pow(D, mu) * dD;
+        float *o = dst + r * ncol;
+        o[0] = (float)((s[0] - s[1] - s[2] + s[3]) * pre);
+        o[1] = (float)((s[0] + s[1] + s[2] + s[3]) * pre);
+        o[2] = (float)((s[4] + s[7]) * pre);
+        o[3] = (float)((s[6] - s[5]) * pre);
+        o[4] = (float)((s[10] - s[8]) * pre);
+        o[5] = (float)(s[9] * pre);
+        o[6] = (float)(s[11] * pre);
+        if (ncol == 8) {
+            o[7] = 0.f;
+        } else {
+            o[7] = (float)(alpha * pow(D, beta) * pre);
+            o[8] = (float)pre;
+            o[9] = (mode == MODE_ICE1) ? (float)(a_m * pow(D, b_m) * pre) : 0.f;
+            o[10] = 0.f;
+            o[11] = 0.f;
+        }
+    }
+}
+// aux[0][k] = D_k, aux[1][k] = D_k^nu, aux[2][k] = D_k^0.6357
+__global__ void k_pack_aux(const float *__restrict__ d_axis, float *__restrict__ aux, int nd, double nu)
+{
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < nd) {
+        double D = (double)d_axis[k];
+        aux[k] = d_axis[k];
+        aux[nd + k] = (float)pow(D, nu);
+        aux[2 * nd + k] = (float)pow(D, 0.6357);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// geometry: WGS84 direct geodesic (Vincenty) + rotated-pole rotation, all float64
+// (stand-ins for pyproj.Geod.fwd and pycosmo.WGS_to_COSMO, interpolation.py:526-568)
+// ------------------------------------------------------------------------------------------
+#define WGS84_A 6378137.0
+#define WGS84_F (1.0 / 298.257223563)
+#define DEG2RAD 0.017453292519943295
+#define RAD2DEG 57.29577951308232
+
+struct AzimuthConsts {   // everything of the direct problem that depends on the azimuth only
+    double sinA1, cosA1, sinU1, cosU1, sigma1, sinAlpha, cosSqAlpha, A, B, C;
+};
+
+__device__ __forceinline__ void geod_prepare(double lat0_deg, double az_deg, AzimuthConsts &k)
+{
+    const double f = WGS84_F, a = WGS84_A, b = (1.0 - f) * a;
+    double phi1 = lat0_deg * DEG2RAD, alpha1 = az_deg * DEG2RAD;
+    sincos(alpha1, &k.sinA1, &k.cosA1);
+    double tanU1 = (1.0 - f) * tan(phi1);
+    k.cosU1 = 1.0 / sqrt(1.0 + tanU1 * tanU1);
+    k.sinU1 = tanU1 * k.cosU1;
+    k.sigma1 = atan2(tanU1, k.cosA1);
+    k.sinAlpha = k.cosU1 * k.sinA1;
+    k.cosSqAlpha = 1.0 - k.sinAlpha * k.sinAlpha;
+    double uSq = k.cosSqAlpha * (a * a - b * b) / (b * b);
+    k.A = 1.0 + uSq / 16384.0 * (4096.0 + uSq * (-768.0 + uSq * (320.0 - 175.0 * uSq)));
+    k.B = uSq / 1024.0 * (256.0 + uSq * (-128.0 + uSq * (74.0 - 47.0 * uSq)));
+    k.C = f / 16.0 * k.cosSqAlpha * (4.0 + f * (4.0 - 3.0 * k.cosSqAlpha));
+}
+
+__device__ __forceinline__ void geod_forward(const AzimuthConsts &k, double lon0_deg, double dist, double &lon,
+                                             double &lat)
+{
+    const double f = WGS84_F, b = (1.0 - f) * WGS84_A;
+    double sig0 = dist / (b * k.A), sigma = sig0;
+    double cos2SigmaM, sinSigma, cosSigma;
+#pragma unroll 1
+    for (int it = 0; it < 5; ++it) {
+        cos2SigmaM = cos(2.0 * k.sigma1 + sigma);
+        sincos(sigma, &sinSigma, &cosSigma);
+        double dS = k.B * sinSigma *
+                    (cos2SigmaM + k.B / 4.0 *
+                                      (cosSigma * (-1.0 + 2.0 * cos2SigmaM * cos2SigmaM) -
+                                       k.B / 6.0 * cos2SigmaM * (-3.0 + 4.0 * sinSigma * sinSigma) *
+                                           (-3.0 + 4.0 * cos2SigmaM * cos2SigmaM)));
+        sigma = sig0 + dS;
+    }
+    cos2SigmaM = cos(2.0 * k.sigma1 + sigma);
+    sincos(sigma, &sinSigma, &cosSigma);
+    double tmp = k.sinU1 * sinSigma - k.cosU1 * cosSigma * k.cosA1;
+    double phi2 = atan2(k.sinU1 * cosSigma + k.cosU1 * sinSigma * k.cosA1,
+                        (1.0 - f) * sqrt(k.sinAlpha * k.sinAlpha + tmp * tmp));
+    double lam = atan2(sinSigma * k.sinA1, k.cosU1 * cosSigma - k.sinU1 * sinSigma * k.cosA1);
+    double L = lam - (1.0 - k.C) * f * k.sinAlpha *
+                         (sigma + k.C * sinSigma *
+                                      (cos2SigmaM + k.C * cosSigma * (-1.0 + 2.0 * cos2SigmaM * cos2SigmaM)));
+    lon = lon0_deg + L * RAD2DEG;
+    lat = phi2 * RAD2DEG;
+}
+
+__device__ __forceinline__ void rotate_pole(const double *__restrict__ R, double lat_deg, double lon_deg,
+                                            double &rlat, double &rlon)
+{
+    double sl, cl, sp, cp;
+    sincos(lon_deg * DEG2RAD, &sl, &cl);
+    sincos(lat_deg * DEG2RAD, &sp, &cp);
+    double x = cl * cp, y = sl * cp, z = sp;
+    double xn = R[0] * x + R[1] * y + R[2] * z;
+    double yn = R[3] * x + R[4] * y + R[5] * z;
+    double zn = R[6] * x + R[7] * y + R[8] * z;
+    rlon = atan2(yn, xn) * RAD2DEG;
+    rlat = asin(zn) * RAD2DEG;
+}
+
+// ------------------------------------------------------------------------------------------
+// trilinear interpolation: bit-exact restatement of interpolation_c.c:42-103, 108-164
+// on the transposed layout z_t[col][level]
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int column_search(const float *__restrict__ col, int dim, float key)
+{
+    if (key > __ldg(col)) return -1;
+    if (key < __ldg(col + dim - 1)) return -2;
+    int hi = 0, lo = dim - 1;
+    while (hi < lo) {
+        int mid = (hi + lo) / 2;
+        float c = __ldg(col + mid);
+        if (c == key) return mid;
+        if (lo == mid || hi == mid) return hi;
+        if (c < key) lo = mid;
+        else if (c > key) hi = mid;
+    }
+    return hi;
+}
+
+struct CellGeom {
+    int iy, ix;         // lat index, lon index of the lower-left neighbour
+    int y0, y1, x0, x1; // memory-safe (clamped) neighbour indices
+    float x, y, dx, dy; // fractional position and complements
+    int status;         // 0 ok, 1 above model top, -1 below topography
+    int level[4];       // upper level used in each neighbour column
+};
+
+// pos0 / pos1 are the float32 grid positions ((coord - llc)/res evaluated in float32)
+__device__ __forceinline__ void locate_cell(const float *__restrict__ z_t, int nz, int ny, int nx, float pos0,
+                                            float pos1, float h, CellGeom &c)
+{
+    c.iy = (int)floorf(pos0);
+    c.ix = (int)floorf(pos1);
+    c.x = fmodf(pos0, 1.0f);
+    c.y = fmodf(pos1, 1.0f);
+    c.dx = __fsub_rn(1.0f, c.x);
+    c.dy = __fsub_rn(1.0f, c.y);
+    // memory-safe neighbour indices (the reference reads out of bounds on the last row/col)
+    const int y0 = min(max(c.iy, 0), ny - 1), y1 = min(max(c.iy + 1, 0), ny - 1);
+    const int x0 = min(max(c.ix, 0), nx - 1), x1 = min(max(c.ix + 1, 0), nx - 1);
+    c.y0 = y0; c.y1 = y1; c.x0 = x0; c.x1 = x1;
+    const float *col[4] = {z_t + ((size_t)y0 * nx + x0) * nz, z_t + ((size_t)y0 * nx + x1) * nz,
+                           z_t + ((size_t)y1 * nx + x0) * nz, z_t + ((size_t)y1 * nx + x1) * nz};
+    float t0 = __ldg(col[0] + nz - 1), t1 = __ldg(col[1] + nz - 1);
+    float t2 = __ldg(col[2] + nz - 1), t3 = __ldg(col[3] + nz - 1);
+    // interp_topo = dx*dy*v0 + x*v2*dy + dx*v1*y + x*y*v3   (left to right, no contraction)
+    float topo = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(__fmul_rn(c.dx, c.dy), t0),
+                                               __fmul_rn(__fmul_rn(c.x, t2), c.dy)),
+                                     __fmul_rn(__fmul_rn(c.dx, t1), c.y)),
+                           __fmul_rn(__fmul_rn(c.x, c.y), t3));
+    c.level[0] = c.level[1] = c.level[2] = c.level[3] = -1;
+    if (!(topo < h)) { c.status = -1; return; }
+    c.status = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        int idx = column_search(col[k], nz, h);
+        if (idx == -1) { c.status = 1; break; }
+        if (idx == -2) idx = nz - 3;
+        else if (idx == nz - 2) idx--;
+        c.level[k] = idx;
+    }
+    if (c.status != 0) c.level[0] = c.level[1] = c.level[2] = c.level[3] = -1;
+}
+
+// vertical interpolation in one column: v2 - (v2 - v1)/(c1 - c2) * (h - c2)
+__device__ __forceinline__ float vlerp(float v1, float v2, float c1, float c2, float h)
+{
+    return __fsub_rn(v2, __fmul_rn(__fdiv_rn(__fsub_rn(v2, v1), __fsub_rn(c1, c2)), __fsub_rn(h, c2)));
+}
+
+// compatibility kernel: same data contract as get_all_radar_pts (reference layout [nz][ny][nx])
+__global__ void k_interp_compat(int n, const float *__restrict__ coords, const float *__restrict__ hg,
+                                const float *__restrict__ data, const float *__restrict__ heights, int nz, int ny,
+                                int nx, float llc0, float llc1, float res0, float res1, float *__restrict__ out)
+{
+    int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    float pos0 = __fdiv_rn(__fsub_rn(coords[2 * g], llc1), res1);
+    float pos1 = __fdiv_rn(__fsub_rn(coords[2 * g + 1], llc0), res0);
+    float h = hg[g];
+    int iy = (int)floorf(pos0), ix = (int)floorf(pos1);
+    float x = fmodf(pos0, 1.0f), y = fmodf(pos1, 1.0f);
+    float dx = __fsub_rn(1.0f, x), dy = __fsub_rn(1.0f, y);
+    size_t plane = (size_t)ny * nx;
+    int y0 = min(max(iy, 0), ny - 1), y1 = min(max(iy + 1, 0), ny - 1);
+    int x0 = min(max(ix, 0), nx - 1), x1 = min(max(ix + 1, 0), nx - 1);
+    size_t off[4] = {(size_t)y0 * nx + x0, (size_t)y0 * nx + x1, (size_t)y1 * nx + x0, (size_t)y1 * nx + x1};
+    float t[4];
+    for (int k = 0; k < 4; ++k) t[k] = heights[(size_t)(nz - 1) * plane + off[k]];
+    float topo = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(__fmul_rn(dx, dy), t[0]), __fmul_rn(__fmul_rn(x, t[2]), dy)),
+                                     __fmul_rn(__fmul_rn(dx, t[1]), y)),
+                           __fmul_rn(__fmul_rn(x, y), t[3]));
+    if (!(topo < h)) { out[g] = __int_as_float(0x7fc00000); return; }
+    float vv[4];
+    for (int k = 0; k < 4; ++k) {
+        const float *hc = heights + off[k];
+        int hi = 0, lo = nz - 1, idx;
+        if (h > hc[0]) { out[g] = -9999.0f; return; }
+        if (h < hc[(size_t)(nz - 1) * plane]) idx = -2;
+        else {
+            idx = 0;
+            while (hi < lo) {
+                int mid = (hi + lo) / 2;
+                float c = hc[(size_t)mid * plane];
+                if (c == h) { idx = mid; break; }
+                if (lo == mid || hi == mid) { idx = hi; break; }
+                if (c < h) lo = mid;
+                else if (c > h) hi = mid;
+                idx = hi;
+            }
+        }
+        if (idx == -2) idx = nz - 3;
+        else if (idx == nz - 2) idx--;
+        float c1 = hc[(size_t)idx * plane], c2 = hc[(size_t)(idx + 1) * plane];
+        float v1 = data[(size_t)idx * plane + off[k]], v2 = data[(size_t)(idx + 1) * plane + off[k]];
+        vv[k] = vlerp(v1, v2, c1, c2, h);
+    }
+    out[g] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(__fmul_rn(dx, dy), vv[0]), __fmul_rn(__fmul_rn(x, vv[2]), dy)),
+                                 __fmul_rn(__fmul_rn(dx, vv[1]), y)),
+                       __fmul_rn(__fmul_rn(x, y), vv[3]));
+}
+
+// ------------------------------------------------------------------------------------------
+// K1: per sub-beam gate
+// ------------------------------------------------------------------------------------------
+struct ScanDev {
+    const double *ray_az;
+    const int *ray_traj;
+    const double *sub_daz;
+    const int *sub_jv;
+    const double *sub_weight;
+    const float *traj_s, *traj_h, *traj_e;
+};
+
+struct K1Out {
+    int8_t *mask;          // [sbg]
+    uint8_t *active;       // [sbg] bit per species
+    float *wind;           // [sbg] (U sin phi + V cos phi) cos theta + W sin theta
+    float *sinth;          // [sbg]
+    float *vsum, *nsum;    // [sbg] analytic fall-speed moments (non-numeric species)
+    uint16_t *key;         // [species][sbg]
+    float *p0, *p1;        // [species][sbg]
+    float *vals;           // [sbg][NVP] interpolated variables (model output / debug) or null
+    double *lat, *lon;     // [ray][gate] central sub-beam
+    int *hist;             // [total_bins]
+    int *flags;            // [0]: out-of-domain
+    // debug
+    int *dbg_cell, *dbg_level, *dbg_status, *dbg_e, *dbg_t;
+    double *dbg_rot;
+};
+
+__device__ __forceinline__ double ice_mom2(double T, double QM)
+{   // hydrometeors.py:1277-1299 (Field et al. 2005), n = 3
+    const double n = 3.0;
+    T = T - 273.15;
+    double a = 5.065339 - 0.062659 * T - 3.032362 * n + 0.029469 * T * n - 0.000285 * T * T + 0.312550 * n * n +
+               0.000204 * T * T * n + 0.003199 * T * n * n - 0.015952 * n * n * n;
+    a = pow(10.0, a);
+    double b = 0.476221 - 0.015896 * T + 0.165977 * n + 0.007468 * T * n - 0.000141 * T * T + 0.060366 * n * n +
+               0.000079 * T * T * n + 0.000594 * T * n * n - 0.003577 * n * n * n;
+    return pow(QM / a, 1.0 / b);
+}
+
+__device__ __forceinline__ int lut_bin(float x, float lo, float step, int dim)
+{   // lut.py:336-341: floor((x - lo)/step) in float32, clamped
+    float f = floorf(__fdiv_rn(__fsub_rn(x, lo), step));
+    int i = (int)f;
+    if (f < 0.f) i = 0;
+    if (f >= (float)dim) i = dim - 1;
+    return i;
+}
+
+extern __shared__ int s_hist[];
+
+__global__ void __launch_bounds__(128)
+k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const float *__restrict__ z_t,
+             const float *__restrict__ fields, K1Out o, long long n_sbg)
+{
+    const int tid = threadIdx.x;
+    for (int b = tid; b < cfg.total_bins; b += blockDim.x) s_hist[b] = 0;
+    __syncthreads();
+
+    long long sbg = (long long)blockIdx.x * blockDim.x + tid;
+    const bool in_range = sbg < n_sbg;
+    uint32_t keys[RADOP_NSPECIES_MAX];
+#pragma unroll
+    for (int s = 0; s < RADOP_NSPECIES_MAX; ++s) keys[s] = RADOP_KEY_NONE;
+
+    if (in_range) {
+        const int ng = cfg.n_gates;
+        int g = (int)(sbg % ng);
+        long long rq = sbg / ng;
+        int q = (int)(rq % cfg.n_sub);
+        int ray = (int)(rq / cfg.n_sub);
+        double az = scan.ray_az[ray] + scan.sub_daz[q];
+        size_t trow = ((size_t)scan.ray_traj[ray] * cfg.n_vert + scan.sub_jv[q]) * ng + g;
+        float s_g = __ldg(scan.traj_s + trow), h_g = __ldg(scan.traj_h + trow), e_g = __ldg(scan.traj_e + trow);
+
+        // --- geolocation ------------------------------------------------------------------
+        AzimuthConsts kc;
+        geod_prepare(cfg.radar_lat, az, kc);
+        double lon, lat, rlat, rlon;
+        geod_forward(kc, cfg.radar_lon, (double)s_g, lon, lat);
+        rotate_pole(cfg.rot, lat, lon, rlat, rlon);
+        if (q == cfg.center_sub && o.lat) {
+            o.lat[(size_t)ray * ng + g] = lat;
+            o.lon[(size_t)ray * ng + g] = lon;
+        }
+        // domain check on float64 coordinates against float32 corners (interpolation.py:572-575)
+        if (rlon < (double)cfg.llc[0] || rlat < (double)cfg.llc[1] || rlon > (double)cfg.urc[0] ||
+            rlat > (double)cfg.urc[1])
+            atomicOr(o.flags, 1);
+        // SWIG typemap casts the coordinates to float32 (interpolation_c.i:16)
+        float crlat = (float)rlat, crlon = (float)rlon;
+        float pos0 = __fdiv_rn(__fsub_rn(crlat, cfg.llc[1]), cfg.res[1]);
+        float pos1 = __fdiv_rn(__fsub_rn(crlon, cfg.llc[0]), cfg.res[0]);
+        CellGeom c;
+        locate_cell(z_t, cfg.nz, cfg.ny, cfg.nx, pos0, pos1, h_g, c);
+        o.mask[sbg] = (int8_t)c.status;
+        if (o.dbg_cell) {
+            o.dbg_cell[2 * sbg] = c.iy;
+            o.dbg_cell[2 * sbg + 1] = c.ix;
+            for (int k = 0; k < 4; ++k) o.dbg_level[4 * sbg + k] = c.level[k];
+            o.dbg_status[sbg] = c.status;
+            o.dbg_rot[2 * sbg] = rlat;
+            o.dbg_rot[2 * sbg + 1] = rlon;
+            for (int s = 0; s < cfg.n_species; ++s) { o.dbg_e[sbg * cfg.n_species + s] = -1; o.dbg_t[sbg * cfg.n_species + s] = -1; }
+        }
+
+        float val[RADOP_NVP];
+        const float qnan = __int_as_float(0x7fc00000);
+        uint8_t active = 0;
+        float wind = qnan, sinth = 0.f, vsum = 0.f, nsum = 0.f;
+        if (c.status == 0) {
+            // --- interpolate every variable with the same 8 corner weights ----------------
+            const int nvec = cfg.two_moment ? 4 : 3;
+            const int ys[4] = {c.y0, c.y0, c.y1, c.y1};
+            const int xs[4] = {c.x0, c.x1, c.x0, c.x1};
+            // accumulation order of the reference: col0, col2, col1, col3
+            const int order[4] = {0, 2, 1, 3};
+#pragma unroll
+            for (int oi = 0; oi < 4; ++oi) {
+                const int k = order[oi];
+                size_t colidx = (size_t)ys[k] * cfg.nx + xs[k];
+                const float *zc = z_t + colidx * cfg.nz + c.level[k];
+                float c1 = __ldg(zc), c2 = __ldg(zc + 1);
+                const float4 *f1 = reinterpret_cast<const float4 *>(fields + (colidx * cfg.nz + c.level[k]) * RADOP_NVP);
+                const float4 *f2 = f1 + RADOP_NVP / 4;
+#pragma unroll
+                for (int v4 = 0; v4 < 4; ++v4) {
+                    if (v4 < nvec) {
+                        float4 a = __ldg(f1 + v4), b = __ldg(f2 + v4);
+                        float vv[4] = {vlerp(a.x, b.x, c1, c2, h_g), vlerp(a.y, b.y, c1, c2, h_g),
+                                       vlerp(a.z, b.z, c1, c2, h_g), vlerp(a.w, b.w, c1, c2, h_g)};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            float term;
+                            if (k == 0) term = __fmul_rn(__fmul_rn(c.dx, c.dy), vv[j]);
+                            else if (k == 2) term = __fmul_rn(__fmul_rn(c.x, vv[j]), c.dy);
+                            else if (k == 1) term = __fmul_rn(__fmul_rn(c.dx, vv[j]), c.y);
+                            else term = __fmul_rn(__fmul_rn(c.x, c.y), vv[j]);
+                            val[v4 * 4 + j] = (oi == 0) ? term : __fadd_rn(val[v4 * 4 + j], term);
+                        }
+                    }
+                }
+            }
+            if (!cfg.two_moment)
+                for (int j = 12; j < 16; ++j) val[j] = 0.f;
+
+            // --- incidence elevation folded to [0, 90] (doppler_scatter.py:173-176) ---------
+            float e = e_g;
+            if (e > 90.f) e = __fsub_rn(180.f, e);
+            if (e < 0.f) e = -e;
+            float T = val[RADOP_VAR_T];
+            const double Td = (double)T;
+
+            // --- species: PSD parameters, LUT bin, analytic Doppler moments -----------------
+            for (int s = 0; s < cfg.n_species; ++s) {
+                const SpeciesDev &S = cfg.sp[s];
+                float QMf = val[S.qm_var];
+                if (!(QMf > 0.f)) continue;
+                active |= (uint8_t)(1u << s);
+                double QM = (double)QMf, lam, n0, ntot_2m = 0.0;
+                float p0, p1;
+                if (S.psd == RADOP_PSD_1MOM_FIXED_N0) {
+                    lam = pow(S.lambda_factor / QM, 1.0 / (4.0 + S.mu));
+                    n0 = S.N0;
+                    p0 = (float)lam; p1 = (float)n0;
+                } else if (S.psd == RADOP_PSD_1MOM_SNOW) {
+                    n0 = 13.5 * (5.65e5 * exp(-0.107 * (Td - 273.15))) / 1000.0;
+                    lam = pow(S.a * n0 * S.lambda_factor / QM, 1.0 / (S.b + 1.0));
+                    p0 = (float)lam; p1 = (float)n0;
+                } else if (S.psd == RADOP_PSD_1MOM_ICE) {
+                    double Q2 = ice_mom2(Td, QM / S.b);
+                    lam = pow(Q2 / QM, 1.0 / (S.b - 2.0));
+                    n0 = 0.0;
+                    p0 = (float)(lam / 1000.0); p1 = QMf;
+                } else {
+                    double QN = (double)val[S.qn_var];
+                    ntot_2m = QN;
+                    double xm = fmin(fmax(QM / (QN + 2.220446049250313e-16), S.x_min), S.x_max);
+                    lam = pow(S.lambda_factor * xm, -S.nu / S.b);
+                    n0 = (S.nu / S.ntot_factor) * QN * pow(lam, (S.mu + 1.0) / S.nu);
+                    n0 = n0 * pow(1000.0, -(1.0 + S.mu));
+                    lam = lam * pow(1000.0, -S.nu);
+                    p0 = (float)lam; p1 = (float)n0;
+                }
+                int ie = lut_bin(e, S.e_min, S.e_step, S.ne);
+                int it = lut_bin(T, S.t_min, S.t_step, S.nt);
+                keys[s] = (uint32_t)(S.bin_base + ie * S.nt + it);
+                o.p0[(size_t)s * n_sbg + sbg] = p0;
+                o.p1[(size_t)s * n_sbg + sbg] = p1;
+                if (o.dbg_e) { o.dbg_e[sbg * cfg.n_species + s] = ie; o.dbg_t[sbg * cfg.n_species + s] = it; }
+                if (cfg.doppler_scheme == 1 && !S.numeric_vn) {
+                    // _Hydrometeor.integrate_V, hydrometeors.py:178-199
+                    double v = S.vel_factor * n0 * S.alpha / S.nu * pow(lam, -(S.beta + S.mu + 1.0) / S.nu);
+                    double n = (S.psd == RADOP_PSD_2MOM)
+                                   ? ntot_2m
+                                   : S.ntot_factor * n0 / S.nu * pow(lam, -(S.mu + 1.0) / S.nu);
+                    vsum += (float)v;
+                    nsum += (float)n;
+                }
+            }
+            // --- wind projection (proj_vel, doppler_scatter.py:30-47; theta is the folded e) --
+            float theta = e * 0.017453292519943295f;
+            float st, ct;
+            sincosf(theta, &st, &ct);
+            double sphi, cphi;
+            sincos(az * DEG2RAD, &sphi, &cphi);
+            wind = (float)(((double)val[RADOP_VAR_U] * sphi + (double)val[RADOP_VAR_V] * cphi) * (double)ct +
+                           (double)val[RADOP_VAR_W] * (double)st);
+            sinth = st;
+        } else {
+#pragma unroll
+            for (int j = 0; j < RADOP_NVP; ++j) val[j] = qnan;
+        }
+        o.active[sbg] = active;
+        o.wind[sbg] = wind;
+        o.sinth[sbg] = sinth;
+        o.vsum[sbg] = vsum;
+        o.nsum[sbg] = nsum;
+        if (o.vals) {
+            float4 *dst = reinterpret_cast<float4 *>(o.vals + (size_t)sbg * RADOP_NVP);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dst[j] = make_float4(val[4 * j], val[4 * j + 1], val[4 * j + 2], val[4 * j + 3]);
+        }
+        for (int s = 0; s < cfg.n_species; ++s) o.key[(size_t)s * n_sbg + sbg] = (uint16_t)keys[s];
+    }
+
+    // --- warp-aggregated shared-memory histogram of the LUT bins -----------------------------
+    const unsigned lane = tid & 31;
+    for (int s = 0; s < cfg.n_species; ++s) {
+        uint32_t key = keys[s];
+        unsigned peers = __match_any_sync(0xffffffffu, key);
+        if (key != RADOP_KEY_NONE && lane == (unsigned)(__ffs(peers) - 1)) atomicAdd(&s_hist[key], __popc(peers));
+    }
+    __syncthreads();
+    for (int b = tid; b < cfg.total_bins; b += blockDim.x) {
+        int cnt = s_hist[b];
+        if (cnt) atomicAdd(&o.hist[b], cnt);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K1b: counting sort by bin
+// ------------------------------------------------------------------------------------------
+// One block.  bin_start = exclusive scan of the counts; tile_start = exclusive scan of
+// ceil(count/TILE); cost_start = exclusive scan of tiles*cost; totals[] = {pairs, tiles, cost, bins}
+__global__ void k_scan_bins(const __grid_constant__ DevConfig cfg, const int *__restrict__ hist, int *bin_start,
+                            int *tile_start, long long *cost_start, int *cursor, long long *totals)
+{
+    __shared__ long long s_tot[3];
+    __shared__ int s_warp[3][32];
+    __shared__ long long s_warpc[32];
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    if (tid == 0) { s_tot[0] = s_tot[1] = s_tot[2] = 0; }
+    __shared__ int s_bins;
+    if (tid == 0) s_bins = 0;
+    __syncthreads();
+    for (int base = 0; base < cfg.total_bins; base += nthr) {
+        int b = base + tid;
+        int cnt = 0, tiles = 0;
+        long long cost = 0;
+        if (b < cfg.total_bins) {
+            cnt = hist[b];
+            tiles = (cnt + RADOP_TILE - 1) / RADOP_TILE;
+            int s = 0;
+            while (s + 1 < cfg.n_species && b >= cfg.sp[s + 1].bin_base) ++s;
+            cost = (long long)tiles * cfg.sp[s].cost;
+        }
+        // block-wide inclusive scans (warp shuffle + shared)
+        int v0 = cnt, v1 = tiles;
+        long long v2 = cost;
+        const int lane = tid & 31, wid = tid >> 5;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int t0 = __shfl_up_sync(0xffffffffu, v0, d), t1 = __shfl_up_sync(0xffffffffu, v1, d);
+            long long t2 = __shfl_up_sync(0xffffffffu, v2, d);
+            if (lane >= d) { v0 += t0; v1 += t1; v2 += t2; }
+        }
+        if (lane == 31) { s_warp[0][wid] = v0; s_warp[1][wid] = v1; s_warpc[wid] = v2; }
+        __syncthreads();
+        if (wid == 0) {
+            int nw = nthr >> 5;
+            int w0 = lane < nw ? s_warp[0][lane] : 0, w1 = lane < nw ? s_warp[1][lane] : 0;
+            long long w2 = lane < nw ? s_warpc[lane] : 0;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int t0 = __shfl_up_sync(0xffffffffu, w0, d), t1 = __shfl_up_sync(0xffffffffu, w1, d);
+                long long t2 = __shfl_up_sync(0xffffffffu, w2, d);
+                if (lane >= d) { w0 += t0; w1 += t1; w2 += t2; }
+            }
+            s_warp[0][lane] = w0; s_warp[1][lane] = w1; s_warpc[lane] = w2;
+        }
+        __syncthreads();
+        int off0 = (wid ? s_warp[0][wid - 1] : 0), off1 = (wid ? s_warp[1][wid - 1] : 0);
+        long long off2 = (wid ? s_warpc[wid - 1] : 0);
+        if (b < cfg.total_bins) {
+            int bs = (int)s_tot[0] + off0 + v0 - cnt;
+            bin_start[b] = bs;
+            cursor[b] = bs;
+            tile_start[b] = (int)s_tot[1] + off1 + v1 - tiles;
+            cost_start[b] = s_tot[2] + off2 + v2 - cost;
+            if (cnt) atomicAdd(&s_bins, 1);
+        }
+        __syncthreads();
+        if (tid == nthr - 1) {
+            s_tot[0] += off0 + v0;
+            s_tot[1] += off1 + v1;
+            s_tot[2] += off2 + v2;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        bin_start[cfg.total_bins] = (int)s_tot[0];
+        tile_start[cfg.total_bins] = (int)s_tot[1];
+        cost_start[cfg.total_bins] = s_tot[2];
+        totals[0] = s_tot[0];
+        totals[1] = s_tot[1];
+        totals[2] = s_tot[2];
+        totals[3] = s_bins;
+    }
+}
+
+// scatter the active pairs into bin order (positions inside a bin are arbitrary; every
+// result is written back to its own (sub-beam gate, species) slot, so the output does not
+// depend on them)
+__global__ void __launch_bounds__(256)
+k_scatter_pairs(const __grid_constant__ DevConfig cfg, const uint16_t *__restrict__ key, const float *__restrict__ p0,
+                const float *__restrict__ p1, const double *__restrict__ sub_weight, int *cursor,
+                PairRec *__restrict__ rec, long long n_sbg)
+{
+    const int tid = threadIdx.x;
+    for (int b = tid; b < cfg.total_bins; b += blockDim.x) s_hist[b] = 0;
+    __syncthreads();
+    long long sbg = (long long)blockIdx.x * blockDim.x + tid;
+    const bool in_range = sbg < n_sbg;
+    const unsigned lane = tid & 31;
+    uint32_t keys[RADOP_NSPECIES_MAX];
+    int rank[RADOP_NSPECIES_MAX];
+    for (int s = 0; s < cfg.n_species; ++s) {
+        uint32_t k = in_range ? (uint32_t)key[(size_t)s * n_sbg + sbg] : RADOP_KEY_NONE;
+        keys[s] = k;
+        unsigned peers = __match_any_sync(0xffffffffu, k);
+        int leader = __ffs(peers) - 1;
+        int base = 0;
+        if (k != RADOP_KEY_NONE && (int)lane == leader) base = atomicAdd(&s_hist[k], __popc(peers));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        rank[s] = base + __popc(peers & ((1u << lane) - 1u));
+    }
+    __syncthreads();
+    for (int b = tid; b < cfg.total_bins; b += blockDim.x) {
+        int cnt = s_hist[b];
+        if (cnt) s_hist[b] = atomicAdd(&cursor[b], cnt);
+    }
+    __syncthreads();
+    if (in_range) {
+        int q = (int)((sbg / cfg.n_gates) % cfg.n_sub);
+        float w = (float)sub_weight[q];
+        for (int s = 0; s < cfg.n_species; ++s) {
+            if (keys[s] == RADOP_KEY_NONE) continue;
+            PairRec r;
+            r.sbg = (uint32_t)sbg;
+            r.p0 = p0[(size_t)s * n_sbg + sbg];
+            r.p1 = p1[(size_t)s * n_sbg + sbg];
+            r.w = w;
+            rec[s_hist[keys[s]] + rank[s]] = r;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K2: PSD x scattering-table contraction
+// ------------------------------------------------------------------------------------------
+#define LOG2E 1.4426950408889634f
+
+template <int G>
+__device__ __forceinline__ void integrate_geo8(const float4 *__restrict__ tab, int nd, const float *__restrict__ Dg,
+                                               float dD, const float (&a)[G], float (&acc)[G][8])
+{
+    float r[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g) r[g] = ex2f_approx(a[g] * dD);
+    for (int k0 = 0; k0 < nd; k0 += RADOP_HBLOCK) {
+        float P[G][8];
+        {
+            float4 t0 = tab[(k0 + RADOP_HBLOCK - 1) * 2], t1 = tab[(k0 + RADOP_HBLOCK - 1) * 2 + 1];
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                P[g][0] = t0.x; P[g][1] = t0.y; P[g][2] = t0.z; P[g][3] = t0.w;
+                P[g][4] = t1.x; P[g][5] = t1.y; P[g][6] = t1.z; P[g][7] = t1.w;
+            }
+        }
+#pragma unroll
+        for (int j = RADOP_HBLOCK - 2; j >= 0; --j) {
+            float4 t0 = tab[(k0 + j) * 2], t1 = tab[(k0 + j) * 2 + 1];
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                P[g][0] = fmaf(P[g][0], r[g], t0.x); P[g][1] = fmaf(P[g][1], r[g], t0.y);
+                P[g][2] = fmaf(P[g][2], r[g], t0.z); P[g][3] = fmaf(P[g][3], r[g], t0.w);
+                P[g][4] = fmaf(P[g][4], r[g], t1.x); P[g][5] = fmaf(P[g][5], r[g], t1.y);
+                P[g][6] = fmaf(P[g][6], r[g], t1.z); P[g][7] = fmaf(P[g][7], r[g], t1.w);
+            }
+        }
+        float d0 = __ldg(Dg + k0);
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            float R = ex2f_approx(a[g] * d0);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) acc[g][c] = fmaf(P[g][c], R, acc[g][c]);
+        }
+    }
+}
+
+template <int G, int NC>
+__device__ __forceinline__ void integrate_gen(const float4 *__restrict__ tab, const float *__restrict__ U, int nd,
+                                              const float (&a)[G], float (&acc)[G][NC])
+{
+#pragma unroll 4
+    for (int k = 0; k < nd; ++k) {
+        float u = U[k];
+        float t[NC];
+#pragma unroll
+        for (int v = 0; v < NC / 4; ++v) {
+            float4 x = tab[k * (NC / 4) + v];
+            t[4 * v] = x.x; t[4 * v + 1] = x.y; t[4 * v + 2] = x.z; t[4 * v + 3] = x.w;
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            float E = ex2f_approx(a[g] * u);
+#pragma unroll
+            for (int c = 0; c < NC; ++c) acc[g][c] = fmaf(E, t[c], acc[g][c]);
+        }
+    }
+}
+
+// 1-mom ice: N(D) = N0 * (490.6 exp(-20.78 x) + 17.46 x^0.6357 exp(-3.29 x)), x = lam' D
+// (constants_1mom.py:103-104); both exponentials are geometric on the uniform grid and are
+// advanced by multiplication, re-anchored with ex2 every RADOP_HBLOCK diameters.
+template <int G>
+__device__ __forceinline__ void integrate_ice1(const float4 *__restrict__ tab, const float *__restrict__ Dp, int nd,
+                                               const float *__restrict__ Dg, float dD, const float (&lam)[G],
+                                               float (&acc)[G][12])
+{
+    float a1[G], a2[G], r1[G], r2[G], c2[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        a1[g] = -20.78f * LOG2E * lam[g];
+        a2[g] = -3.290f * LOG2E * lam[g];
+        r1[g] = ex2f_approx(a1[g] * dD);
+        r2[g] = ex2f_approx(a2[g] * dD);
+        c2[g] = 17.46f * exp2f(0.6357f * log2f(lam[g]));
+    }
+    for (int k0 = 0; k0 < nd; k0 += RADOP_HBLOCK) {
+        float d0 = __ldg(Dg + k0);
+        float E1[G], E2[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            E1[g] = 490.6f * ex2f_approx(a1[g] * d0);
+            E2[g] = c2[g] * ex2f_approx(a2[g] * d0);
+        }
+        const int kend = min(k0 + RADOP_HBLOCK, nd);
+#pragma unroll 4
+        for (int k = k0; k < kend; ++k) {
+            float dp = Dp[k];
+            float4 t0 = tab[k * 3], t1 = tab[k * 3 + 1], t2 = tab[k * 3 + 2];
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                float w = fmaf(dp, E2[g], E1[g]);
+                acc[g][0] = fmaf(w, t0.x, acc[g][0]); acc[g][1] = fmaf(w, t0.y, acc[g][1]);
+                acc[g][2] = fmaf(w, t0.z, acc[g][2]); acc[g][3] = fmaf(w, t0.w, acc[g][3]);
+                acc[g][4] = fmaf(w, t1.x, acc[g][4]); acc[g][5] = fmaf(w, t1.y, acc[g][5]);
+                acc[g][6] = fmaf(w, t1.z, acc[g][6]); acc[g][7] = fmaf(w, t1.w, acc[g][7]);
+                acc[g][8] = fmaf(w, t2.x, acc[g][8]); acc[g][9] = fmaf(w, t2.y, acc[g][9]);
+                E1[g] *= r1[g];
+                E2[g] *= r2[g];
+            }
+        }
+    }
+}
+
+struct K2Args {
+    const int *hist, *bin_start, *tile_start;
+    const long long *cost_start;
+    const long long *totals;
+    const PairRec *rec;
+    float *sz_out;      // [sbg][n_species][8]
+    float2 *ice_vn;     // [sbg] numeric fall-speed moments of the ice species
+};
+
+extern __shared__ __align__(128) unsigned char s_k2[];
+
+__global__ void __launch_bounds__(RADOP_TILE_THREADS)
+k_integrate(const __grid_constant__ DevConfig cfg, K2Args A)
+{
+    constexpr int G = RADOP_TILE_G;
+    __shared__ uint64_t s_bar;
+    float4 *s_tab = reinterpret_cast<float4 *>(s_k2);
+    const int tid = threadIdx.x;
+    const long long total_cost = A.totals[2];
+    if (total_cost == 0) return;
+    const long long lo = total_cost * blockIdx.x / gridDim.x, hi = total_cost * (blockIdx.x + 1) / gridDim.x;
+    if (lo >= hi) return;
+    const int nbins = cfg.total_bins;
+
+    // first tile whose virtual (cost-weighted) start is >= lo
+    int b;
+    {
+        int l = 0, r = nbins;       // largest b with cost_start[b] <= lo
+        while (r - l > 1) {
+            int m = (l + r) >> 1;
+            if (A.cost_start[m] <= lo) l = m; else r = m;
+        }
+        b = l;
+    }
+    int s = 0;
+    while (s + 1 < cfg.n_species && b >= cfg.sp[s + 1].bin_base) ++s;
+    int j;
+    {
+        long long cs = A.cost_start[b];
+        int cost = cfg.sp[s].cost;
+        j = (int)((lo - cs + cost - 1) / cost);
+    }
+    if (tid == 0) mbar_init(&s_bar, 1);
+    __syncthreads();
+    uint32_t phase = 0;
+    int staged_bin = -1;
+
+    while (b < nbins) {
+        int cnt = A.hist[b];
+        int tiles = (cnt + RADOP_TILE - 1) / RADOP_TILE;
+        if (j >= tiles) {
+            ++b; j = 0;
+            while (s + 1 < cfg.n_species && b >= cfg.sp[s + 1].bin_base) ++s;
+            continue;
+        }
+        const SpeciesDev &S = cfg.sp[s];
+        if (A.cost_start[b] + (long long)j * S.cost >= hi) break;
+
+        // ---- stage the LUT slice of this bin (TMA bulk copy, mbarrier completion) ----------
+        const int nd = S.nd;
+        float *s_aux = reinterpret_cast<float *>(s_k2 + (size_t)nd * S.ncol * 4);
+        if (b != staged_bin) {
+            __syncthreads();     // everybody is done with the previous slice
+            if (tid == 0) {
+                fence_proxy_async();
+                const uint32_t tab_bytes = (uint32_t)nd * S.ncol * 4;
+                const bool need_aux = (S.mode != MODE_GEO8);
+                mbar_expect_tx(&s_bar, tab_bytes + (need_aux ? (uint32_t)nd * 4 : 0));
+                const char *src = reinterpret_cast<const char *>(S.table + (size_t)(b - S.bin_base) * nd * S.ncol);
+                for (uint32_t off = 0; off < tab_bytes; off += 16384) {
+                    uint32_t n = min(16384u, tab_bytes - off);
+                    tma_bulk_g2s(s_k2 + off, src + off, n, &s_bar);
+                }
+                if (need_aux) {
+                    const float *asrc = S.aux + (S.mode == MODE_ICE1 ? 2 * nd : nd);
+                    tma_bulk_g2s(s_aux, asrc, (uint32_t)nd * 4, &s_bar);
+                }
+            }
+            mbar_wait(&s_bar, phase);
+            phase ^= 1;
+            staged_bin = b;
+        }
+
+        // ---- this thread's G pairs -----------------------------------------------------------
+        const int first = A.bin_start[b] + j * RADOP_TILE;
+        const int n_here = min(RADOP_TILE, cnt - j * RADOP_TILE);
+        PairRec rec[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            int i = tid + g * RADOP_TILE_THREADS;
+            if (i < n_here) rec[g] = A.rec[first + i];
+            else { rec[g].sbg = 0xFFFFFFFFu; rec[g].p0 = 0.f; rec[g].p1 = 0.f; rec[g].w = 0.f; }
+        }
+        const int nsp = cfg.n_species;
+        if (S.mode == MODE_GEO8) {
+            float a[G], acc[G][8];
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                a[g] = -LOG2E * rec[g].p0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) acc[g][c] = 0.f;
+            }
+            integrate_geo8<G>(s_tab, nd, S.aux, S.dD_geo, a, acc);
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                if (rec[g].sbg == 0xFFFFFFFFu) continue;
+                float pre = rec[g].p1 * rec[g].w;
+                float4 *dst = reinterpret_cast<float4 *>(A.sz_out + ((size_t)rec[g].sbg * nsp + s) * 8);
+                dst[0] = make_float4(acc[g][0] * pre, acc[g][1] * pre, acc[g][2] * pre, acc[g][3] * pre);
+                dst[1] = make_float4(acc[g][4] * pre, acc[g][5] * pre, acc[g][6] * pre, acc[g][7] * pre);
+            }
+        } else if (S.mode == MODE_GEN8) {
+            float a[G], acc[G][8];
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                a[g] = -LOG2E * rec[g].p0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) acc[g][c] = 0.f;
+            }
+            integrate_gen<G, 8>(s_tab, s_aux, nd, a, acc);
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                if (rec[g].sbg == 0xFFFFFFFFu) continue;
+                float pre = rec[g].p1 * rec[g].w;
+                float4 *dst = reinterpret_cast<float4 *>(A.sz_out + ((size_t)rec[g].sbg * nsp + s) * 8);
+                dst[0] = make_float4(acc[g][0] * pre, acc[g][1] * pre, acc[g][2] * pre, acc[g][3] * pre);
+                dst[1] = make_float4(acc[g][4] * pre, acc[g][5] * pre, acc[g][6] * pre, acc[g][7] * pre);
+            }
+        } else if (S.mode == MODE_GEN12) {
+            float a[G], acc[G][12];
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                a[g] = -LOG2E * rec[g].p0;
+#pragma unroll
+                for (int c = 0; c < 12; ++c) acc[g][c] = 0.f;
+            }
+            integrate_gen<G, 12>(s_tab, s_aux, nd, a, acc);
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                if (rec[g].sbg == 0xFFFFFFFFu) continue;
+                float n0 = rec[g].p1, pre = n0 * rec[g].w;
+                float4 *dst = reinterpret_cast<float4 *>(A.sz_out + ((size_t)rec[g].sbg * nsp + s) * 8);
+                dst[0] = make_float4(acc[g][0] * pre, acc[g][1] * pre, acc[g][2] * pre, acc[g][3] * pre);
+                dst[1] = make_float4(acc[g][4] * pre, acc[g][5] * pre, acc[g][6] * pre, 0.f);
+                A.ice_vn[rec[g].sbg] = make_float2(acc[g][7] * n0, acc[g][8] * n0);
+            }
+        } else {   // MODE_ICE1
+            float lam[G], acc[G][12];
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                lam[g] = (rec[g].sbg == 0xFFFFFFFFu) ? 1.0f : rec[g].p0;
+#pragma unroll
+                for (int c = 0; c < 12; ++c) acc[g][c] = 0.f;
+            }
+            integrate_ice1<G>(s_tab, s_aux, nd, S.aux, S.dD_geo, lam, acc);
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                if (rec[g].sbg == 0xFFFFFFFFu) continue;
+                // N0 renormalised so that the mass integral equals QM (hydrometeors.py:1330-1339)
+                float n0 = rec[g].p1 / acc[g][9], pre = n0 * rec[g].w;
+                float4 *dst = reinterpret_cast<float4 *>(A.sz_out + ((size_t)rec[g].sbg * nsp + s) * 8);
+                dst[0] = make_float4(acc[g][0] * pre, acc[g][1] * pre, acc[g][2] * pre, acc[g][3] * pre);
+                dst[1] = make_float4(acc[g][4] * pre, acc[g][5] * pre, acc[g][6] * pre, 0.f);
+                A.ice_vn[rec[g].sbg] = make_float2(acc[g][7] * n0, acc[g][8] * n0);
+            }
+        }
+        ++j;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K3: quadrature / species sums and the per-ray epilogue
+// ------------------------------------------------------------------------------------------
+// IceParticle.integrate_V sums over ALL valid gates of a sub-beam and the total lands on the
+// first valid gate (hydrometeors.py:1256-1275 + utilities.py:231-261 zero padding): one warp
+// per (ray, sub-beam) computes that total in a fixed order.
+__global__ void k_ice_totals(const __grid_constant__ DevConfig cfg, const uint8_t *__restrict__ active,
+                             const float2 *__restrict__ ice_vn, float *__restrict__ tot /* [ray*sub][3] */)
+{
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    int n_rq = cfg.n_rays * cfg.n_sub;
+    if (warp >= n_rq) return;
+    const uint8_t bit = (uint8_t)(1u << cfg.ice_numeric);
+    size_t base = (size_t)warp * cfg.n_gates;
+    float v = 0.f, n = 0.f;
+    int first = 0x7fffffff;
+    for (int g = lane; g < cfg.n_gates; g += 32) {
+        if (active[base + g] & bit) {
+            float2 x = ice_vn[base + g];
+            v += x.x; n += x.y;
+            first = min(first, g);
+        }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        v += __shfl_xor_sync(0xffffffffu, v, d);
+        n += __shfl_xor_sync(0xffffffffu, n, d);
+        first = min(first, __shfl_xor_sync(0xffffffffu, first, d));
+    }
+    if (lane == 0) {
+        tot[3 * warp] = v;
+        tot[3 * warp + 1] = n;
+        tot[3 * warp + 2] = __int_as_float(first);
+    }
+}
+
+struct K3Args {
+    const int8_t *mask;
+    const uint8_t *active;
+    const float *wind, *sinth, *vsum, *nsum;
+    const float *sz_out;
+    const float *ice_tot;
+    const float *vals;
+    const double *sub_weight;
+    const float *ray_nyquist;
+    float *comb;        // [ray][gate][8]: b c p q kd s9 s11 rvel
+    float *out;         // [N_OUT+1][ray][gate]
+    float *model_out;   // [NVP][ray][gate]
+};
+
+// thread per (ray, gate): sums over sub-beams and species in the reference's order
+// (doppler_scatter.py:148-158, 259-268, 313-333, 400-401, 472-477)
+__global__ void __launch_bounds__(128)
+k_reduce_subbeams(const __grid_constant__ DevConfig cfg, K3Args A)
+{
+    long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    long long n_rg = (long long)cfg.n_rays * cfg.n_gates;
+    if (idx >= n_rg) return;
+    const int g = (int)(idx % cfg.n_gates);
+    const int ray = (int)(idx / cfg.n_gates);
+    const int nsp = cfg.n_species;
+    float comb[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float rsum = 0.f, wsum = 0.f, msum = 0.f;
+    float mv[RADOP_NVP];
+    float sumw_all = 0.f;
+    if (A.model_out) {
+#pragma unroll
+        for (int v = 0; v < RADOP_NVP; ++v) mv[v] = 0.f;
+        for (int q = 0; q < cfg.n_sub; ++q) sumw_all += (float)A.sub_weight[q];
+    }
+    for (int q = 0; q < cfg.n_sub; ++q) {
+        size_t sbg = ((size_t)ray * cfg.n_sub + q) * cfg.n_gates + g;
+        int m = A.mask[sbg];
+        msum += (float)m;
+        if (m != 0) continue;
+        float w = (float)A.sub_weight[q];
+        uint8_t act = A.active[sbg];
+        for (int s = 0; s < nsp; ++s) {
+            if (!(act & (1u << s))) continue;
+            const float4 *row = reinterpret_cast<const float4 *>(A.sz_out + (sbg * nsp + s) * 8);
+            float4 r0 = __ldg(row), r1 = __ldg(row + 1);
+            comb[0] += r0.x; comb[1] += r0.y; comb[2] += r0.z; comb[3] += r0.w;
+            comb[4] += r1.x; comb[5] += r1.y; comb[6] += r1.z;
+        }
+        if (cfg.doppler_scheme == 1) {
+            float vs = A.vsum[sbg], ns = A.nsum[sbg];
+            if (cfg.ice_numeric >= 0 && (act & (1u << cfg.ice_numeric))) {
+                const float *t = A.ice_tot + 3 * ((size_t)ray * cfg.n_sub + q);
+                if (__float_as_int(t[2]) == g) { vs += t[0]; ns += t[1]; }
+            }
+            float vh = vs / ns;                              // 0/0 -> NaN where no hydrometeor (Q7)
+            float rv = A.wind[sbg] - vh * A.sinth[sbg];
+            if (!isnan(rv)) { rsum += rv * w; wsum += w; }
+        }
+        if (A.model_out) {
+            const float4 *vp = reinterpret_cast<const float4 *>(A.vals + sbg * RADOP_NVP);
+#pragma unroll
+            for (int v4 = 0; v4 < 4; ++v4) {
+                float4 x = __ldg(vp + v4);
+                float wn = w / sumw_all;
+                if (!isnan(x.x)) mv[4 * v4] += x.x * wn;
+                if (!isnan(x.y)) mv[4 * v4 + 1] += x.y * wn;
+                if (!isnan(x.z)) mv[4 * v4 + 2] += x.z * wn;
+                if (!isnan(x.w)) mv[4 * v4 + 3] += x.w * wn;
+            }
+        }
+    }
+    float4 *dst = reinterpret_cast<float4 *>(A.comb + idx * 8);
+    dst[0] = make_float4(comb[0], comb[1], comb[2], comb[3]);
+    dst[1] = make_float4(comb[4], comb[5], comb[6], rsum / wsum);
+    float mk = msum / (float)cfg.n_sub;
+    if (mk > -1.f && mk <= 0.f) mk = 0.f;
+    A.out[(size_t)RADOP_N_OUT * n_rg + idx] = mk;
+    if (A.model_out) {
+#pragma unroll
+        for (int v = 0; v < RADOP_NVP; ++v)
+            if (cfg.var_mask & (1u << v)) A.model_out[(size_t)v * n_rg + idx] = mv[v];
+    }
+}
+
+__device__ __forceinline__ float warp_scan_add(float v, int lane)
+{
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        float t = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += t;
+    }
+    return v;
+}
+__device__ __forceinline__ float warp_scan_mul(float v, int lane)
+{
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        float t = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v *= t;
+    }
+    return v;
+}
+
+// one warp per ray: observables (get_pol_from_sz, doppler_scatter.py:491-544), inclusive
+// scans along the ray with warp shuffles (doppler_scatter.py:406-415; utilities.py:175-199),
+// aliasing (utilities.py:142-155) and the sensitivity cut (doppler_scatter.py:804-862)
+__global__ void __launch_bounds__(128)
+k_ray_epilogue(const __grid_constant__ DevConfig cfg, K3Args A)
+{
+    const int ray = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (ray >= cfg.n_rays) return;
+    const int ng = cfg.n_gates;
+    const size_t n_rg = (size_t)cfg.n_rays * ng;
+    const float qnan = __int_as_float(0x7fc00000);
+    const float PI = 3.14159265358979323846f;
+    const float wl = cfg.wavelength;
+    const float zfac = (float)((double)wl * wl * wl * wl / (9.869604401089358 * 9.869604401089358 * 3.141592653589793 * (double)cfg.k_squared));
+    const float kfac = (float)(1e-3 * (180.0 / 3.141592653589793) * (double)wl);
+    const float dr_km = cfg.radial_res / 1000.f;
+    float carry_phi = 0.f, carry_h = 1.f, carry_v = 1.f;
+    const float nyq = A.ray_nyquist ? A.ray_nyquist[ray] : 0.f;
+    for (int g0 = 0; g0 < ng; g0 += 32) {
+        int g = g0 + lane;
+        bool ok = g < ng;
+        float c[8];
+        if (ok) {
+            const float4 *src = reinterpret_cast<const float4 *>(A.comb + ((size_t)ray * ng + g) * 8);
+            float4 a = src[0], b = src[1];
+            c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b.x; c[5] = b.y; c[6] = b.z; c[7] = b.w;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) c[i] = 0.f;
+        }
+        // exact zeros -> NaN (doppler_scatter.py:401)
+#pragma unroll
+        for (int i = 0; i < 7; ++i)
+            if (c[i] == 0.f) c[i] = qnan;
+        float rxh = 2.f * PI * c[0], rxv = 2.f * PI * c[1];
+        float zh = zfac * rxh, zv = zfac * rxv;
+        float zdr = rxh / rxv;
+        float kdp = kfac * c[4];
+        float ah = 4.343e-3f * (2.f * wl * c[6]);
+        float av = 4.343e-3f * (2.f * wl * c[5]);
+        float rho = sqrtf((c[2] * c[2] + c[3] * c[3]) / (c[0] * c[1]));
+        float dhv = atan2f(-c[3], -c[2]);
+        // PHIDP = nan_cumsum(2 KDP) * dr/1000 + DELTA_HV
+        float t = isnan(kdp) ? 0.f : 2.f * kdp;
+        if (!ok) t = 0.f;
+        float sc = warp_scan_add(t, lane) + carry_phi;
+        carry_phi = __shfl_sync(0xffffffffu, sc, 31);
+        float phidp = sc * dr_km + dhv;
+        if (cfg.with_attenuation) {
+            float fh = isnan(ah) ? 1.f : exp10f(-0.1f * ah * dr_km);
+            float fv = isnan(av) ? 1.f : exp10f(-0.1f * av * dr_km);
+            if (!ok) { fh = 1.f; fv = 1.f; }
+            float ph = warp_scan_mul(fh, lane) * carry_h;
+            float pv = warp_scan_mul(fv, lane) * carry_v;
+            carry_h = __shfl_sync(0xffffffffu, ph, 31);
+            carry_v = __shfl_sync(0xffffffffu, pv, 31);
+            zdr = (zh * ph) / (zv * pv);
+        }
+        float rvel = c[7];
+        if (A.ray_nyquist && cfg.doppler_scheme != 0) {
+            float th = (rvel + nyq) / (2.f * nyq) * PI - PI / 2.f;
+            float tf = atanf(tanf(th));
+            rvel = (tf + PI / 2.f) * (2.f * nyq) / PI - nyq;
+        }
+        if (cfg.sensitivity_mode && ok) {
+            float thr;
+            if (cfg.sensitivity_mode == 1) thr = cfg.sens0;
+            else thr = (cfg.sens0 - 20.f * log10f(cfg.sens1 / 1000.f)) + 20.f * log10f((cfg.radial_res * (float)g) / 1000.f);
+            if (10.f * log10f(zh) < thr) {
+                zh = qnan; rvel = qnan; zv = qnan; phidp = qnan; zdr = qnan; rho = qnan; kdp = qnan;
+            }
+        }
+        if (ok) {
+            size_t o = (size_t)ray * ng + g;
+            A.out[RADOP_OUT_ZH * n_rg + o] = zh;
+            A.out[RADOP_OUT_ZDR * n_rg + o] = zdr;
+            A.out[RADOP_OUT_ZV * n_rg + o] = zv;
+            A.out[RADOP_OUT_KDP * n_rg + o] = kdp;
+            A.out[RADOP_OUT_DELTA_HV * n_rg + o] = dhv;
+            A.out[RADOP_OUT_PHIDP * n_rg + o] = phidp;
+            A.out[RADOP_OUT_RHOHV * n_rg + o] = rho;
+            A.out[RADOP_OUT_ATT_H * n_rg + o] = ah;
+            A.out[RADOP_OUT_ATT_V * n_rg + o] = av;
+            A.out[RADOP_OUT_RVEL * n_rg + o] = rvel;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// FP32 FMA throughput probe (roofline denominator): 16 independent FFMA chains per thread
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_fma_probe(float *out, int iters, float seed)
+{
+    float a[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) a[i] = seed + (float)(threadIdx.x + i);
+    float m = 0.999f + seed * 1e-9f, c = 1e-3f;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) a[i] = fmaf(a[i], m, c);
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += a[i];
+    if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}

@@ -1,0 +1,59 @@
+// radop_kernels.cuh -- device-side data structures shared by the kernels of libradop.so
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/radop.h"
+
+#define RADOP_NVP 16            // floats per (column, level) in the interleaved field layout
+#define RADOP_TILE_THREADS 128  // threads of one PSD-integration CTA
+#define RADOP_TILE_G 4          // (sub-beam gate, species) pairs per thread
+#define RADOP_TILE (RADOP_TILE_THREADS * RADOP_TILE_G)
+#define RADOP_HBLOCK 32         // diameters per Horner block (re-anchoring period)
+#define RADOP_KEY_NONE 0xFFFFu
+
+// integration modes of the PSD x LUT contraction
+enum { MODE_GEO8 = 0,       // nu == 1 on a uniform D grid: blocked Horner, 8 columns
+       MODE_GEN8 = 1,       // general nu: one ex2 per diameter, 8 columns
+       MODE_ICE1 = 2,       // 1-mom ice (Field 2005 double exponential), 12 columns
+       MODE_GEN12 = 3 };    // general nu with numeric fall-speed integrals, 12 columns
+
+struct SpeciesDev {
+    int species, psd, mode, ncol;
+    int numeric_vn;
+    int ne, nt, nd;
+    float e_min, e_step, t_min, t_step;
+    int bin_base;               // first global bin id of this species
+    int cost;                   // relative cost of one tile (for work partitioning)
+    int qm_var, qn_var;         // RADOP_VAR_* holding mass / number density
+    float dD_geo;               // (D[nd-1]-D[0])/(nd-1) computed in double
+    float dD_ref;               // D[1]-D[0] in float32 (doppler_scatter.py:224)
+    const float *table;         // [ne][nt][nd][ncol] combined + premultiplied columns
+    const float *aux;           // [3][nd]: D, D^nu, D^0.6357
+    double a, b, alpha, beta, mu, nu, N0, lambda_factor, vel_factor, ntot_factor, x_min, x_max;
+};
+
+struct DevConfig {
+    // radar / scan geometry
+    int n_rays, n_sub, n_gates, n_vert, center_sub;
+    double radar_lat, radar_lon;
+    // model grid
+    int nz, ny, nx;
+    float llc[2], urc[2], res[2];
+    double rot[9];              // rotation matrix geographic -> rotated pole
+    uint32_t var_mask;          // uploaded variables
+    // microphysics
+    int n_species, total_bins;
+    int two_moment, doppler_scheme, with_attenuation, sensitivity_mode;
+    int output_model_vars, keep_debug, ice_numeric;   // ice_numeric: species index with numeric v,n or -1
+    float wavelength, k_squared, radial_res;
+    float sens0, sens1;
+    SpeciesDev sp[RADOP_NSPECIES_MAX];
+};
+
+// sorted work record of one active (sub-beam gate, species) pair
+struct __align__(16) PairRec {
+    uint32_t sbg;   // sub-beam gate index
+    float p0;       // lambda (GEO/GEN) or lambda/1000 (ICE1)
+    float p1;       // N0 (GEO/GEN) or QM (ICE1)
+    float w;        // quadrature weight of the sub-beam
+};

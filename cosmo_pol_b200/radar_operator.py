@@ -1,0 +1,414 @@
+# -*- coding: utf-8 -*-
+"""radar_operator.py -- the public API: ``RadarOperator`` with the interface of
+cosmo_pol/radar_operator.py:46-677 (config property, set_lut, load_model_file, get_PPI,
+get_RHI, get_VPROF).
+
+What changed underneath: the ``for e in elevations: pool.map(worker, azimuths)`` block of the
+reference (radar_operator.py:402-435, 498-533) is ONE batched call into libradop.so with the
+whole ray list of the scan; fields and lookup tables are uploaded once and stay resident in
+HBM until the model file or the configuration changes; with torch.distributed initialised the
+ray list is sharded over the ranks and the outputs are all-gathered."""
+import copy
+import os
+
+import numpy as np
+
+from . import parallel
+from ._abi import Engine, Scan, OUT_NAMES, VAR_IDS
+from .config import cfg
+from .constants import global_constants as constants
+from .hydrometeors import create_hydrometeor
+from .interpolation.atm_refraction import compute_trajectory_radial
+from .interpolation.quadrature import subbeam_fan
+from .interpolation.radial import Radial
+from .interpolation import interpolation as _interp_mod
+from .lookup import load_all_lut
+
+BASE_VARIABLES = ['U', 'V', 'W', 'QR_v', 'QS_v', 'QG_v', 'QI_v', 'RHO', 'T']
+BASE_VARIABLES_2MOM = ['QH_v', 'QNH_v', 'QNR_v', 'QNS_v', 'QNG_v', 'QNI_v']
+
+
+class SimulatedScan(object):
+    """Result of get_PPI / get_RHI.
+
+    ``fields[name]`` : float32 [n_sweeps, n_rays_per_sweep, n_gates], linear units
+    ``data``         : the reference's list (sweeps) of lists (rays) of ``Radial``, built on
+                        first access (radar_operator.py:447-451 hands this list to PyartRadop)
+    """
+
+    def __init__(self, scan_type, elevations, azimuths, ranges, pos_time, fields, mask, lats, lons, dist, heights):
+        self.scan_type = scan_type
+        self.elevations, self.azimuths, self.ranges, self.pos_time = elevations, azimuths, ranges, pos_time
+        self.fields, self.mask, self.lats, self.lons, self.dist, self.heights = fields, mask, lats, lons, dist, heights
+        self._data = None
+
+    @property
+    def data(self):
+        if self._data is None:
+            ns, nr = self.mask.shape[:2]
+            self._data = [[Radial({k: v[i, j] for k, v in self.fields.items()}, self.mask[i, j],
+                                  self.lats[i, j], self.lons[i, j], self.dist[i, j], self.heights[i, j])
+                           for j in range(nr)] for i in range(ns)]
+        return self._data
+
+    def as_sweep_dict(self):
+        return {'elevations': self.elevations, 'azimuths': self.azimuths, 'ranges': self.ranges,
+                'pos_time': self.pos_time, 'data': self.data}
+
+    def to_pyart(self):
+        raise NotImplementedError('the Py-ART adapter (PyartRadop) is outside the hot path (SURVEY.md 8f N2)')
+
+
+class RadarOperator(object):
+    def __init__(self, options_file=None, output_variables='all', device=None, lut_folder=None):
+        print('Reading options defined in options file')
+        cfg.init(options_file)
+        self.current_microphys_scheme = '1mom'
+        self.dic_vars = None
+        self.N = 0
+        self.lut_sz = None
+        self.lut_folder = lut_folder
+        if device is None:
+            device = int(os.environ.get('LOCAL_RANK', 0))
+        self.device = device
+        self._engine = None
+        self._dirty = {'params': True, 'model': True, 'lut': True}
+        self._engine_flags = None
+        self.config = cfg.CONFIG
+        if output_variables in ('all', 'only_model', 'only_radar'):
+            self.output_variables = output_variables
+        else:
+            self.output_variables = 'all'
+            print("Invalid output_variables input, must be either 'all', 'only_model' or 'only_radar'")
+        _interp_mod._set_active_operator(self)
+
+    # ---------------------------------------------------------------------------- config
+    def close(self):
+        if self._engine is not None:
+            self._engine.close()
+            self._engine = None
+        self.__config = None
+        cfg.CONFIG = None
+
+    @property
+    def config(self):
+        return copy.deepcopy(self.__config)
+
+    @config.setter
+    def config(self, config_dic):
+        print('Loading new configuration...')
+        checked = cfg.sanity_check(config_dic)
+        reload_lut = True
+        old = getattr(self, '_RadarOperator__config', None)
+        if old is not None and self.lut_sz:
+            reload_lut = (checked['radar']['frequency'] != old['radar']['frequency'] or
+                          checked['microphysics']['with_melting'] != old['microphysics']['with_melting'])
+        self.__config = checked
+        cfg.CONFIG = checked
+        constants.update()
+        self._dirty['params'] = True
+        if reload_lut:
+            self.set_lut()
+
+    def set_lut(self, lut_sz=None):
+        """Load the scattering tables of the current configuration (radar_operator.py:161-182),
+        or install in-memory tables (dict species -> Lookup_table)."""
+        if lut_sz is not None:
+            self.lut_sz = lut_sz
+            self._dirty['lut'] = True
+            return
+        c = self.__config
+        list_hydrom = self._species_for_lut()
+        try:
+            self.lut_sz = load_all_lut(self.current_microphys_scheme, list_hydrom, c['radar']['frequency'],
+                                       c['microphysics']['scattering'], folder=self.lut_folder)
+            self._dirty['lut'] = True
+        except IOError as e:
+            # the reference ships no tables either (.gitignore:3); they must be provided
+            print('Lookup tables not found ({}); install them with set_lut(dict) or lut_folder='.format(e))
+            self.lut_sz = None
+
+    def _species_for_lut(self):
+        c = self.__config
+        h = ['R', 'S', 'G']
+        if self.current_microphys_scheme == '2mom':
+            h.append('H')
+        if c['microphysics']['with_melting']:
+            h.extend(['mS', 'mG'])
+        if c['microphysics']['with_ice_crystals']:
+            h.append('I')
+        return h
+
+    def _species_order(self):
+        """Summation order of doppler_scatter.py:99-106."""
+        c = self.__config
+        h = ['R', 'S', 'G']
+        if c['microphysics']['with_melting']:
+            raise NotImplementedError('the melting scheme is not part of this build (SURVEY.md 8f N1)')
+        if c['microphysics']['scheme'] == '2mom':
+            h.append('H')
+        if c['microphysics']['with_ice_crystals']:
+            h.append('I')
+        return h
+
+    def get_pos_and_time(self):
+        c = self.__config['radar']['coords']
+        return {'latitude': c[0], 'longitude': c[1], 'altitude': c[2],
+                'time': self.dic_vars['T'].attributes.get('time')}
+
+    # ----------------------------------------------------------------------------- model
+    def load_model(self, dic_vars):
+        """Install an in-memory model dictionary: name -> object with ``.data`` [nz,ny,nx] and
+        ``.attributes`` {'z-levels','proj_info','resolution','time'} (what pycosmo returns to
+        the reference, radar_operator.py:290-292)."""
+        missing = [v for v in BASE_VARIABLES if v not in dic_vars]
+        if missing:
+            raise ValueError('Not all necessary variables could be found: missing {}'.format(missing))
+        two = all(v in dic_vars for v in BASE_VARIABLES_2MOM)
+        scheme = '2mom' if two else '1mom'
+        print('Using {}-moment scheme'.format(2 if two else 1))
+        self.dic_vars = dic_vars
+        self._dirty['model'] = True
+        changed = scheme != self.current_microphys_scheme
+        self.current_microphys_scheme = scheme
+        self.__config['microphysics']['scheme'] = scheme
+        cfg.CONFIG = self.__config
+        self._dirty['params'] = True
+        if (changed or not self.lut_sz) and self.output_variables != 'only_model':
+            self.set_lut()
+
+    def load_model_file(self, filename, cfilename=None):
+        """COSMO GRIB through pycosmo when that library is installed (radar_operator.py:217-309);
+        ``.npz`` archives written by ``save_model_npz`` otherwise."""
+        if str(filename).endswith('.npz'):
+            return self.load_model(load_model_npz(filename))
+        try:
+            import pycosmo as pc
+        except ImportError:
+            raise ImportError('pycosmo is needed to read COSMO GRIB files; use load_model(dict) or an .npz archive')
+        file_h = pc.open_file(filename)
+        names = list(BASE_VARIABLES)
+        if file_h.check_if_variables_in_file(['QH', 'QNH', 'QNR', 'QNS', 'QNG']):
+            names += BASE_VARIABLES_2MOM
+        loaded = file_h.get_variable(names, get_proj_info=True, shared_heights=False, assign_heights=True,
+                                     cfile_name=cfilename)
+        file_h.close()
+        self.load_model(loaded)
+
+    # ---------------------------------------------------------------------------- engine
+    def _prepare_engine(self, keep_debug=False):
+        if self.dic_vars is None:
+            raise ValueError('No model file has been loaded! Aborting...')
+        want_radar = self.output_variables in ('all', 'only_radar')
+        if want_radar and not self.lut_sz:
+            raise IOError('no lookup tables loaded')
+        if self._engine is None:
+            self._engine = Engine(self.device)
+            self._dirty = {'params': True, 'model': True, 'lut': True}
+        eng = self._engine
+        c = self.__config
+        flags = (bool(keep_debug), self.output_variables)
+        if self._dirty['params'] or flags != self._engine_flags:
+            order = self._species_order()
+            hyd = []
+            for h in order:
+                hy = create_hydrometeor(h, c['microphysics']['scheme'])
+                hyd.append(hy)
+            eng.set_params(c, constants, hyd, len(constants.RANGE_RADAR),
+                           output_model_vars=self.output_variables in ('all', 'only_model'),
+                           keep_debug=keep_debug, sensitivity_cut=True)
+            self._engine_flags = flags
+            self._dirty['params'] = False
+            self._dirty['lut'] = True       # tables are premultiplied with the species constants
+        if self._dirty['model']:
+            eng.upload_model(self.dic_vars)
+            self._dirty['model'] = False
+        if self._dirty['lut']:
+            eng.upload_luts(self.lut_sz)
+            self._dirty['lut'] = False
+        return eng
+
+    def build_scan(self, ray_az, ray_el):
+        """Host-side scan description: quadrature fan, one trajectory group per distinct
+        elevation (the refraction depends on the elevation only, atm_refraction.py:181-220),
+        Nyquist velocity of the central sub-beam (doppler_scatter.py:432-437)."""
+        c = self.__config
+        fan = subbeam_fan(c)
+        ray_az = np.asarray(ray_az, dtype=np.float64)
+        ray_el = np.asarray(ray_el, dtype=np.float64)
+        uniq, inv = np.unique(ray_el, return_inverse=True)
+        rr = constants.RANGE_RADAR
+        ng, nv = len(rr), len(fan.pts_ver)
+        ts = np.empty((len(uniq), nv, ng), np.float32)
+        th = np.empty_like(ts)
+        te = np.empty_like(ts)
+        for i, el in enumerate(uniq):
+            for j, pt in enumerate(fan.pts_ver):
+                ts[i, j], th[i, j], te[i, j] = compute_trajectory_radial(rr, pt + el, c['radar']['coords'],
+                                                                          c['refraction']['scheme'], self.N)
+        nyq = None
+        f = c['radar']['nyquist_velocity']
+        if f is not None:
+            el0 = ray_el + fan.dele[fan.center]
+            az0 = ray_az + fan.daz[fan.center]
+            cache = {}
+            nyq = np.empty(len(ray_az), np.float32)
+            for i, (e0, a0) in enumerate(zip(el0, az0)):
+                key = (e0, a0) if callable(f) else None
+                if callable(f):
+                    if e0 not in cache:
+                        cache[e0] = f(e0, a0)
+                    nyq[i] = cache[e0]
+                else:
+                    nyq[i] = float(f)
+        return Scan(ray_az, ray_el, inv.astype(np.int32), nyq, fan, ts, th, te)
+
+    def simulate_rays(self, ray_az, ray_el, keep_debug=False, distributed=True):
+        """Batched hot path over an arbitrary ray list; returns dict name -> [n_rays, n_gates].
+        With torch.distributed initialised (and distributed=True) the rays are sharded over the
+        ranks and every rank receives the full result."""
+        eng = self._prepare_engine(keep_debug=keep_debug)
+        ray_az = np.asarray(ray_az, dtype=np.float64)
+        ray_el = np.asarray(ray_el, dtype=np.float64)
+        n_total = len(ray_az)
+        rank, world = parallel.dist_info() if distributed else (0, 1)
+        want_model = self.output_variables in ('all', 'only_model')
+        if world == 1:
+            scan = self.build_scan(ray_az, ray_el)
+            self._last_scan = scan
+            arrays = eng.simulate(scan, want_latlon=True, want_model=want_model)
+            out = {k: np.array(v, copy=True) for k, v in arrays.items()}
+            out['dist'] = scan.traj_s[scan.ray_traj, scan.fan.j_ver[scan.fan.center]]
+            out['heights'] = scan.traj_h[scan.ray_traj, scan.fan.j_ver[scan.fan.center]]
+            return out
+        return self._simulate_sharded(eng, ray_az, ray_el, rank, world, want_model)
+
+    def _simulate_sharded(self, eng, ray_az, ray_el, rank, world, want_model):
+        import torch
+        n_total = len(ray_az)
+        lo, hi = parallel.shard_bounds(n_total, rank, world)
+        scan = self.build_scan(ray_az[lo:hi], ray_el[lo:hi])
+        self._last_scan = scan
+        eng.stage(scan)
+        eng.execute()
+        eng.synchronize()
+        ptr, nr, ng = eng.device_outputs()
+        local = parallel.device_tensor(ptr, (len(OUT_NAMES) + 1, nr, ng), eng.device)
+        full = parallel.all_gather_rays(local, n_total)
+        host = full.cpu().numpy()
+        out = {name: host[i] for i, name in enumerate(OUT_NAMES)}
+        out['mask'] = host[len(OUT_NAMES)]
+        # geometry of every ray is cheap host arithmetic: recompute instead of gathering
+        arrays = eng.fetch(scan, want_latlon=True, want_model=want_model)
+        lat = torch.from_numpy(np.array(arrays['lat'], copy=True)[None]).cuda(eng.device)
+        lon = torch.from_numpy(np.array(arrays['lon'], copy=True)[None]).cuda(eng.device)
+        out['lat'] = parallel.all_gather_rays(lat, n_total)[0].cpu().numpy()
+        out['lon'] = parallel.all_gather_rays(lon, n_total)[0].cpu().numpy()
+        if want_model:
+            names = list(eng.uploaded_vars)
+            loc = torch.from_numpy(np.stack([arrays[n] for n in names])).cuda(eng.device)
+            g = parallel.all_gather_rays(loc, n_total).cpu().numpy()
+            for i, n in enumerate(names):
+                out[n] = g[i]
+        full_scan = self.build_scan(ray_az, ray_el)
+        out['dist'] = full_scan.traj_s[full_scan.ray_traj, full_scan.fan.j_ver[full_scan.fan.center]]
+        out['heights'] = full_scan.traj_h[full_scan.ray_traj, full_scan.fan.j_ver[full_scan.fan.center]]
+        return out
+
+    def _assemble(self, scan_type, out, n_sweeps, n_per, elevations, azimuths):
+        names = []
+        if self.output_variables in ('all', 'only_radar'):
+            names += OUT_NAMES
+        if self.output_variables in ('all', 'only_model'):
+            names += [n for n in VAR_IDS if n in out]
+        shp = (n_sweeps, n_per, -1)
+        fields = {n: out[n].reshape(shp) for n in names}
+        return SimulatedScan(scan_type, elevations, azimuths, constants.RANGE_RADAR, self.get_pos_and_time(), fields,
+                             out['mask'].reshape(shp), out['lat'].reshape(shp), out['lon'].reshape(shp),
+                             out['dist'].reshape(shp), out['heights'].reshape(shp))
+
+    # ------------------------------------------------------------------------------ scans
+    def get_PPI(self, elevations, azimuths=None, az_step=None, az_start=0, az_stop=359):
+        """PPI scan(s): one sweep per elevation (radar_operator.py:357-453)."""
+        if np.isscalar(elevations):
+            elevations = [elevations]
+        if az_step is None:
+            az_step = self.__config['radar']['3dB_beamwidth']
+        if azimuths is None:
+            if az_start > az_stop:
+                azimuths = np.hstack((np.arange(az_start, 360., az_step), np.arange(0, az_stop + az_step, az_step)))
+            else:
+                azimuths = np.arange(az_start, az_stop + az_step, az_step)
+        azimuths = np.asarray(azimuths, dtype=np.float64)
+        el = np.repeat(np.asarray(elevations, dtype=np.float64), len(azimuths))
+        az = np.tile(azimuths, len(elevations))
+        out = self.simulate_rays(az, el)
+        return self._assemble('ppi', out, len(elevations), len(azimuths), elevations, azimuths)
+
+    def get_RHI(self, azimuths, elevations=None, elev_step=None, elev_start=0, elev_stop=90):
+        """RHI scan(s): one sweep per azimuth (radar_operator.py:455-549)."""
+        if np.isscalar(azimuths):
+            azimuths = [azimuths]
+        if elevations is None:
+            if elev_step is None:
+                elev_step = self.__config['radar']['3dB_beamwidth']
+            elevations = np.arange(elev_start, elev_stop + elev_step, elev_step)
+        elevations = np.asarray(elevations, dtype=np.float64)
+        az = np.repeat(np.asarray(azimuths, dtype=np.float64), len(elevations))
+        el = np.tile(elevations, len(azimuths))
+        out = self.simulate_rays(az, el)
+        return self._assemble('rhi', out, len(azimuths), len(elevations), elevations, azimuths)
+
+    def get_VPROF(self):
+        """Vertical profile: one ray at 90 degrees elevation (radar_operator.py:311-354)."""
+        out = self.simulate_rays([0.], [90.])
+        return self._assemble('vprof', out, 1, 1, [90.], [0.])
+
+    # ------------------------------------------------------------------- single-ray helpers
+    def _single_ray_subradials(self, azimuth, elevation):
+        eng = self._prepare_engine(keep_debug=True)
+        scan = self.build_scan([azimuth], [elevation])
+        arrays = eng.simulate(scan, want_latlon=True, want_model=self.output_variables in ('all', 'only_model'))
+        dbg = eng.debug_indices(scan)
+        fan = scan.fan
+        subs = []
+        dist_c = scan.traj_s[0, fan.j_ver[fan.center]]
+        h_c = scan.traj_h[0, fan.j_ver[fan.center]]
+        result = Radial({k: np.array(arrays[k][0]) for k in OUT_NAMES}, np.array(arrays['mask'][0]),
+                        np.array(arrays['lat'][0]), np.array(arrays['lon'][0]), dist_c, h_c)
+        model = None
+        if self.output_variables in ('all', 'only_model'):
+            model = Radial({n: np.array(arrays[n][0]) for n in eng.uploaded_vars}, np.array(arrays['mask'][0]),
+                           np.array(arrays['lat'][0]), np.array(arrays['lon'][0]), dist_c, h_c)
+        for q in range(fan.n_sub):
+            vals = {n: dbg['values'][0, q, :, i] for i, n in enumerate(dbg['var_names'])}
+            st = dbg['status'][0, q].astype(np.float64)
+            j = fan.j_ver[q]
+            e = scan.traj_e[0, j].copy()
+            sub = Radial(vals, st, None, None, scan.traj_s[0, j], scan.traj_h[0, j], e,
+                         [azimuth + fan.daz[q], elevation + fan.dele[q]], fan.weight[q])
+            sub._ray_result = result
+            sub._ray_model = model
+            subs.append(sub)
+        return subs
+
+
+# --------------------------------------------------------------------------------- model I/O
+def save_model_npz(filename, dic_vars):
+    first = next(iter(dic_vars.values()))
+    a = first.attributes
+    payload = {'var__' + k: v.data for k, v in dic_vars.items()}
+    payload['z_levels'] = a['z-levels']
+    payload['resolution'] = np.asarray(a['resolution'], dtype=np.float64)
+    payload['proj_keys'] = np.array(list(a['proj_info'].keys()))
+    payload['proj_vals'] = np.array([float(v) for v in a['proj_info'].values()])
+    payload['time'] = np.array(str(a.get('time', '')))
+    np.savez(filename, **payload)
+
+
+def load_model_npz(filename):
+    from .synthetic import ModelVariable
+    z = np.load(filename, allow_pickle=False)
+    proj = {str(k): float(v) for k, v in zip(z['proj_keys'], z['proj_vals'])}
+    attrs = {'z-levels': z['z_levels'], 'proj_info': proj, 'resolution': list(z['resolution']), 'time': str(z['time'])}
+    return {k[5:]: ModelVariable(k[5:], z[k], attrs) for k in z.files if k.startswith('var__')}

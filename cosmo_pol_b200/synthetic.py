@@ -170,7 +170,7 @@ def make_lut(hydrom, frequency=5.6, scheme='1mom', seed=4321, n_e=None, n_t=None
     shh = amp * (1.0 + obl) * wig
     svv = amp * (1.0 - obl) / wig
     dphi = 0.04 * xsz ** 2 * np.cos(e) ** 2 * (1 + 0.002 * (t - 273.15))     # backscatter phase difference
-    rho0 = 1.0 - 0.004 * obl / (sp['obl'] + 1e-12) - 0.002 * xsz ** 2 / (1 + xsz ** 2)
+    rho0 = 0.9985 - 0.004 * obl / (sp['obl'] + 1e-12) - 0.002 * xsz ** 2 / (1 + xsz ** 2)
     shape = (len(elev), len(temp), n_d)
     tab = np.zeros(shape + (12,), dtype=np.float64)
     hh2 = np.broadcast_to(shh ** 2, shape)
@@ -179,7 +179,7 @@ def make_lut(hydrom, frequency=5.6, scheme='1mom', seed=4321, n_e=None, n_t=None
     tab[..., 0] = 0.5 * (hh2 + vv2)                         # Z11
     tab[..., 1] = 0.5 * (vv2 - hh2)                         # Z12
     tab[..., 2] = tab[..., 1]                               # Z21
-    tab[..., 3] = tab[..., 0] * (1.0 - 1e-3)                # Z22
+    tab[..., 3] = tab[..., 0] * (1.0 + 1e-3)                # Z22
     tab[..., 4] = -co * np.cos(dphi)                        # Z33
     tab[..., 5] = 0.5 * co * np.sin(dphi)                   # Z34
     tab[..., 6] = -0.5 * co * np.sin(dphi)                  # Z43
