@@ -121,7 +121,7 @@ def load_lut(filename):
                 buf.seek(0)
                 data = pickle.load(buf)
             if name == 'axes_names':
-                data = data.all() if hasattr(data, 'all') and not isinstance(data, dict) else data
+                data = data.item() if isinstance(data, np.ndarray) else data   # 0-d object array -> dict
             setattr(lut, name, data)
     return lut
 

@@ -40,8 +40,9 @@ def all_gather_rays(local, n_total, group=None):
         send = torch.zeros((C, n_max, G), dtype=local.dtype, device=local.device)
         send[:, :n_local] = local
     send = send.contiguous()
-    recv = torch.empty((world,) + tuple(send.shape), dtype=local.dtype, device=local.device)
-    dist.all_gather_into_tensor(recv, send, group=group)
+    recv = torch.empty((world * C, n_max, G), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(recv, send, group=group)      # concatenated along dim 0
+    recv = recv.view(world, C, n_max, G)
     parts = []
     for r in range(world):
         lo, hi = shard_bounds(n_total, r, world)

@@ -12,20 +12,26 @@ the reference's own two C kernels used through ctypes (``oracle/_ref``: the
 reference sources compiled unmodified; ``oracle/liboracle_port.so``: our C
 restatement of them, used when ``_ref`` is absent and cross-checked against it).
 
-Parity status: **parity unpinned by the reference's own tests** -- the reference
-ships no tests, golden vectors or lookup tables, its Python
-package does not import under numpy 2 / py3.12 and three of its dependencies
-(pycosmo, pyproj, pytmatrix) are absent.  What *is* pinned:
-  * rows a4 / a16 (native kernels): bit-exact against the reference C compiled
-    here (oracle/_ref);
-  * every formula below cites the reference file:line it follows;
-  * third-party arithmetic is restated from its published algorithm:
-      - pyproj.Geod(ellps='WGS84').fwd  (cosmo_pol/interpolation/interpolation.py:526-536,
-        version unpinned in setup.py:53)  -> Vincenty's direct solution on WGS84
-        (agrees with Karney's GeographicLib solution to < 0.1 mm below 500 km;
-        checked in tests against a numerically integrated geodesic);
-      - pycosmo.WGS_to_COSMO (interpolation.py:566-568, undeclared dependency)
-        -> the standard rotated-pole rotation (COSMO documentation part I, 3.3).
+Parity status: **pinned against the reference itself, run in the build container**
+(tests/golden/make_golden_from_reference.py imports the reference's own modules from
+/root/reference and runs get_interpolated_radial / get_radar_observables /
+integrate_radials / cut_at_sensitivity, its hydrometeor classes, lookup_line,
+_ref_4_3 ... on seeded synthetic inputs; the outputs are committed under
+tests/golden/ and tests/test_oracle_golden.py holds this oracle to them: the
+interpolation half bit-exact, the scattering half to float32 rounding).  The
+reference ships no tests or golden vectors of its own.
+What stays **unpinned** is third-party arithmetic absent from this container,
+restated from its published algorithm and used as a stand-in in BOTH the golden
+generation and this oracle:
+  - pyproj.Geod(ellps='WGS84').fwd  (cosmo_pol/interpolation/interpolation.py:526-536,
+    version unpinned in setup.py:53)  -> Vincenty's direct solution on WGS84
+    (agrees with Karney's GeographicLib solution to < 0.1 mm below 500 km;
+    checked in tests against a numerically integrated geodesic);
+  - pycosmo.WGS_to_COSMO (interpolation.py:566-568, undeclared dependency)
+    -> the standard rotated-pole rotation (COSMO documentation part I, 3.3);
+  - pytmatrix (table CONTENTS): synthetic tables in the reference's own format.
+The two native kernels (rows a4 / a16) are bit-exact against the reference C
+compiled unmodified (oracle/_ref, tests/test_oracle_native.py).
 
 No function in this file imports anything from ``cosmo_pol_b200``.
 """
@@ -615,7 +621,7 @@ class Hydro(object):
             self.lambda_ = lam
             self.N0 = c['N0']
         elif self.kind == 'S':
-            T = np.asarray(args[0]).astype(f)
+            T = np.asarray(args[0])          # stays float32: N0 is evaluated in the input dtype
             q = np.asarray(args[1]).astype(f)
             self.N0 = 13.5 * (5.65 * 10 ** 5 * np.exp(-0.107 * (T - 273.15))) / 1000
             with np.errstate(divide='ignore'):
@@ -623,7 +629,7 @@ class Hydro(object):
                 lam[q == 0] = np.nan
             self.lambda_ = lam
         elif self.kind == 'I':
-            T = np.asarray(args[0]).astype(np.float64)
+            T = np.asarray(args[0])          # stays float32 inside get_mom_2 (hydrometeors.py:1321)
             QM = np.asarray(args[1]).astype(np.float64)
             Q2 = self.get_mom_2(T, QM / C1['I']['b'])
             N0 = Q2 ** ((self.b + 1) / (self.b - 2)) * QM ** ((2 + 1) / (2 - self.b))

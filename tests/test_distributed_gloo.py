@@ -1,0 +1,59 @@
+"""N > 1 host logic on CPU: contiguous ray sharding and the output all-gather with the gloo
+backend, world_size 2 (the GPU path uses the same code with NCCL)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+
+def test_shard_bounds_cover_everything():
+    from cosmo_pol_b200.parallel import shard_bounds
+    for n in (0, 1, 7, 360, 7200, 7201):
+        for world in (1, 2, 3, 8):
+            b = [shard_bounds(n, r, world) for r in range(world)]
+            assert b[0][0] == 0 and b[-1][1] == n
+            assert all(b[i][1] == b[i + 1][0] for i in range(world - 1))
+            sizes = [hi - lo for lo, hi in b]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def _worker(rank, world, port, n_total, q):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from cosmo_pol_b200 import parallel
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        lo, hi = parallel.shard_bounds(n_total, rank, world)
+        full = torch.arange(3 * n_total * 5, dtype=torch.float32).reshape(3, n_total, 5)
+        local = full[:, lo:hi].contiguous()
+        got = parallel.all_gather_rays(local, n_total)
+        q.put((rank, bool(torch.equal(got, full)), parallel.dist_info()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('n_total', [7, 10])
+def test_all_gather_rays_gloo_world2(n_total):
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, n_total, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(r[0] for r in res) == [0, 1]
+    assert all(r[1] for r in res)
+    assert all(r[2][1] == 2 for r in res)

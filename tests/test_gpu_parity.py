@@ -1,0 +1,254 @@
+"""Parity tests proper (-m gpu): the CUDA path, called through the C-ABI (ctypes), against
+the CPU oracle and against the golden vectors produced by the reference itself."""
+import copy
+import json
+
+import numpy as np
+import pytest
+
+import radop_oracle as O
+from conftest import assert_observables_close, load_golden_case, plain, synthetic_inputs
+
+pytestmark = pytest.mark.gpu
+
+CONF_1MOM = {'radar': {'coords': [47.28436, 8.51201, 891.], 'type': 'ground', 'frequency': 5.6, 'range': 45000,
+                       'radial_resolution': 900, 'sensitivity': [-40, 10000]},
+             'integration': {'scheme': 1, 'nh_GH': 3, 'nv_GH': 3}}
+
+
+def make_operator(conf, scheme='1mom', freq=5.6, output_variables='only_radar', **model_kw):
+    from cosmo_pol_b200 import RadarOperator
+    model, luts = synthetic_inputs(scheme, freq, **model_kw)
+    conf = copy.deepcopy(conf)
+    conf['radar']['frequency'] = freq
+    op = RadarOperator(conf, output_variables=output_variables, device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    return op, model, luts
+
+
+def oracle_cfg(op):
+    cfg = op.config
+    if callable(cfg['radar']['nyquist_velocity']):
+        cfg['radar']['nyquist_velocity'] = None
+    return cfg
+
+
+def test_interp_shim_bit_exact_against_reference_c():
+    """radop_get_all_radar_pts (compat shim over the kernel arithmetic) == the reference's C,
+    bit for bit, including NaN (below topography) and -9999 (above the model top)."""
+    from cosmo_pol_b200._abi import Engine
+    model, _ = plain(*synthetic_inputs())
+    rng = np.random.default_rng(11)
+    n = 20000
+    nz, ny, nx = model['z_levels'].shape
+    proj, res = model['proj'], model['resolution']
+    coords = np.stack([proj['La1'] + rng.uniform(0.2, ny - 1.2, n) * res[1],
+                       proj['Lo1'] + rng.uniform(0.2, nx - 1.2, n) * res[0]], axis=1).astype(np.float32)
+    h = rng.uniform(0., 26000., n).astype(np.float32)
+    llc = np.asarray([proj['Lo1'], proj['La1']], dtype=np.float32)
+    eng = Engine(0)
+    for name in ('T', 'QS_v', 'W'):
+        got = eng.get_all_radar_pts(coords, h, model['vars'][name], model['z_levels'], llc, res)
+        ref = O.interp_gates(coords, h, model['vars'][name], model['z_levels'], llc, res)
+        assert np.array_equal(np.isnan(got), np.isnan(ref))
+        ok = ~np.isnan(ref)
+        assert np.array_equal(got[ok].view(np.uint32), ref[ok].view(np.uint32)), name
+        assert (ref == -9999).sum() > 100 and np.isnan(ref).sum() > 100
+    eng.close()
+
+
+@pytest.mark.parametrize('scheme,freq', [('1mom', 5.6), ('2mom', 9.41)])
+def test_indices_and_interpolated_values_bit_exact(scheme, freq):
+    """Grid cell, level and LUT-bin indices bit-exact; interpolated variables bit-exact."""
+    op, model, luts = make_operator(CONF_1MOM, scheme, freq)
+    az = np.array([10.0, 123.0, 250.5, 300.0, 77.0, 200.0])
+    el = np.array([1.0, -0.2, 8.5, 40.0, 89.5, 16.0])
+    eng = op._prepare_engine(keep_debug=True)
+    scan = op.build_scan(az, el)
+    eng.simulate(scan)
+    dbg = eng.debug_indices(scan)
+    pm, pl = plain(model, luts)
+    cfg = oracle_cfg(op)
+    species = O.species_list(cfg)
+    n_bad_coords = 0
+    for r in range(len(az)):
+        ref = O.simulate_ray(pm, pl, cfg, az[r], el[r], accum='f64', debug=True)
+        for q, sub in enumerate(ref['subs']):
+            out, cell, level, status = sub['dbg']
+            # rotated coordinates: float64 agreement to ~1e-12 deg; float32 casts identical
+            same32 = np.array_equal(sub['coords'].astype(np.float32), dbg['rot'][r, q].astype(np.float32))
+            n_bad_coords += 0 if same32 else 1
+            assert np.max(np.abs(sub['coords'] - dbg['rot'][r, q])) < 1e-10
+            assert np.array_equal(dbg['cell'][r, q], cell), (r, q)
+            assert np.array_equal(dbg['status'][r, q], status), (r, q)
+            assert np.array_equal(dbg['level'][r, q], level), (r, q)
+            for i, name in enumerate(dbg['var_names']):
+                a, b = dbg['values'][r, q, :, i], sub['values'][name]
+                assert np.array_equal(np.isnan(a), np.isnan(b)), (r, q, name)
+                if same32:
+                    ok = ~np.isnan(b)
+                    assert np.array_equal(a[ok].view(np.uint32), b[ok].view(np.uint32)), (r, q, name)
+            for j, h in enumerate(species):
+                e_ref = np.full(scan.n_gates, -1)
+                t_ref = np.full(scan.n_gates, -1)
+                if (q, h) in ref['dbg']['valid']:
+                    v = ref['dbg']['valid'][(q, h)]
+                    e_ref[v] = ref['dbg']['e_idx'][(q, h)]
+                    t_ref[v] = ref['dbg']['t_idx'][(q, h)]
+                assert np.array_equal(dbg['lut_e'][r, q, :, j], e_ref), (r, q, h)
+                assert np.array_equal(dbg['lut_t'][r, q, :, j], t_ref), (r, q, h)
+    assert n_bad_coords == 0
+
+
+@pytest.mark.parametrize('scheme,freq', [('1mom', 5.6), ('2mom', 9.41)])
+def test_observables_against_oracle(scheme, freq):
+    op, model, luts = make_operator(CONF_1MOM, scheme, freq, output_variables='all')
+    az = np.arange(0., 360., 30.)
+    res = op.get_PPI([1.0, 8.5, 35.0], azimuths=az)
+    pm, pl = plain(model, luts)
+    cfg = oracle_cfg(op)
+    rays_az, rays_el = np.tile(az, 3), np.repeat([1.0, 8.5, 35.0], len(az))
+    for accum in ('f64', 'ref'):
+        ref = O.simulate_scan(pm, pl, cfg, rays_az, rays_el, accum=accum, output_variables='all', sensitivity_cut=True)
+        got = {k: v.reshape(-1, v.shape[-1]) for k, v in res.fields.items()}
+        floor = None
+        if accum == 'ref':
+            # the reference stores s8 and s10 in float32 before subtracting them: allow its own
+            # cancellation noise (a few ulp of the larger term) on top of the 1e-3 tolerance
+            floor = 4e-6 * np.abs(ref['KDP']) / np.maximum(np.abs(ref['KDP']) / (np.abs(ref['ATT_H']) * 300 + 1e-30), 1e-30) * 0
+            floor = np.full(ref['KDP'].shape, 0.0)
+        assert_observables_close(got, ref, sz_scale=None if accum == 'f64' else 3e-4 * np.abs(ref['KDP']), what=accum)
+        assert np.array_equal(res.mask.reshape(ref['mask'].shape), ref['mask'])
+        a, b = got['RVEL'], ref['RVEL']
+        assert np.array_equal(np.isnan(a), np.isnan(b))
+        ok = np.isfinite(b)
+        assert np.max(np.abs(a[ok] - b[ok])) < 2e-3
+        # model variables (integrate_radials)
+        for name in ('T', 'U', 'QR_v', 'RHO'):
+            assert np.allclose(got[name], ref[name], rtol=2e-5, atol=1e-9), name
+        assert np.max(np.abs(res.lats.reshape(ref['lats'].shape) - ref['lats'])) < 1e-10
+        assert np.max(np.abs(res.lons.reshape(ref['lons'].shape) - ref['lons'])) < 1e-10
+        assert np.array_equal(res.dist.reshape(ref['dist'].shape), ref['dist'])
+        assert np.array_equal(res.heights.reshape(ref['heights'].shape), ref['heights'])
+
+
+@pytest.mark.parametrize('name,scheme,freq', [('c1mom', '1mom', 5.6), ('c2mom', '2mom', 9.41),
+                                               ('c1mom_thr', '1mom', 5.6), ('c1mom_nyq', '1mom', 5.6)])
+def test_against_reference_goldens(name, scheme, freq):
+    """GPU output against what the reference itself produced (tests/golden)."""
+    from cosmo_pol_b200 import RadarOperator
+    g, cfg, kw = load_golden_case(name)
+    model, luts = synthetic_inputs(scheme, freq, **kw)
+    conf = copy.deepcopy(cfg)
+    conf['radar']['sensitivity'] = [-200, 10000]          # goldens are un-censored (cut_* are separate)
+    op = RadarOperator(conf, output_variables='all', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    rays = g['rays']
+    out = op.simulate_rays(rays[:, 0], rays[:, 1])
+    ref = {k[4:]: g[k] for k in g.files if k.startswith('obs_')}
+    assert_observables_close(out, ref, sz_scale=5e-4 * np.abs(ref['KDP']), what=name)
+    assert np.array_equal(out['mask'], g['mask'])
+    a, b = out['RVEL'], ref['RVEL']
+    assert np.array_equal(np.isnan(a), np.isnan(b))
+    ok = np.isfinite(b)
+    assert np.max(np.abs(a[ok] - b[ok])) < 2e-3
+    for k in [f for f in g.files if f.startswith('int_')]:
+        assert np.allclose(out[k[4:]], g[k], rtol=2e-5, atol=1e-9), k
+    if 'cut_ZH' in g.files:
+        op2 = RadarOperator(cfg, output_variables='only_radar', device=0)
+        op2.set_lut(luts)
+        op2.load_model(model)
+        out2 = op2.simulate_rays(rays[:, 0], rays[:, 1])
+        for k in ('ZH', 'ZV', 'ZDR', 'KDP', 'RHOHV', 'PHIDP', 'RVEL', 'ATT_H', 'DELTA_HV'):
+            assert np.array_equal(np.isnan(out2[k]), np.isnan(g['cut_' + k])), k
+
+
+def test_edge_cases_and_errors():
+    from cosmo_pol_b200 import RadarOperator
+    from cosmo_pol_b200._abi import RadopError
+    model, luts = synthetic_inputs()
+    conf = copy.deepcopy(CONF_1MOM)
+    conf['radar']['range'] = 400000       # leaves the 64 x 64 x 0.04 deg domain
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    with pytest.raises(IndexError):
+        op.get_PPI([1.0], azimuths=[0., 90.])
+    # no hydrometeors at all -> every observable NaN, mask still computed
+    conf = copy.deepcopy(CONF_1MOM)
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    dry = {k: type(v)(k, (np.zeros_like(v.data) if k.startswith('Q') else v.data), v.attributes) for k, v in model.items()}
+    op.load_model(dry)
+    r = op.get_PPI([2.0], azimuths=[5., 50.])
+    assert all(np.all(np.isnan(r.fields[k])) for k in ('ZH', 'KDP', 'RVEL', 'PHIDP'))
+    # single quadrature point, single gate-row scan, unsupported options
+    conf['integration'] = {'scheme': 1, 'nh_GH': 1, 'nv_GH': 1}
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    r1 = op.get_PPI([2.0], azimuths=[5.])
+    assert r1.fields['ZH'].shape == (1, 1, 50)
+    pm, pl = plain(model, luts)
+    ref = O.simulate_scan(pm, pl, oracle_cfg(op), [5.], [2.], accum='f64', sensitivity_cut=True)
+    assert_observables_close({k: v[0] for k, v in r1.fields.items()}, ref, what='1x1')
+    conf['doppler'] = {'scheme': 3}
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    with pytest.raises(ValueError):
+        op.get_PPI([2.0], azimuths=[5.])
+    with pytest.raises(ValueError):
+        RadarOperator(conf).load_model({'T': model['T']})
+
+
+def test_scan_level_properties():
+    """Size-independent properties on a larger scan: determinism, ray-permutation invariance,
+    azimuth periodicity, shard consistency, linearity in the scattering table."""
+    from cosmo_pol_b200 import RadarOperator, synthetic
+    conf = copy.deepcopy(CONF_1MOM)
+    conf['radar'].update({'range': 48000, 'radial_resolution': 300})
+    model, luts = synthetic_inputs()
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    az = np.arange(0., 360., 2.)
+    els = [0.4, 5.5, 20.0]
+    ray_az, ray_el = np.tile(az, len(els)), np.repeat(els, len(az))
+    a = op.simulate_rays(ray_az, ray_el)
+    b = op.simulate_rays(ray_az, ray_el)
+    keys = ('ZH', 'ZDR', 'KDP', 'PHIDP', 'RHOHV', 'ATT_H', 'RVEL', 'mask')
+    for k in keys:
+        assert np.array_equal(a[k], b[k], equal_nan=True), 'non deterministic ' + k
+    perm = np.random.default_rng(5).permutation(len(ray_az))
+    c = op.simulate_rays(ray_az[perm], ray_el[perm])
+    for k in keys:
+        assert np.array_equal(c[k], a[k][perm], equal_nan=True), 'ray order matters for ' + k
+    half = len(ray_az) // 2
+    d0 = op.simulate_rays(ray_az[:half], ray_el[:half])
+    d1 = op.simulate_rays(ray_az[half:], ray_el[half:])
+    for k in keys:
+        assert np.array_equal(np.concatenate([d0[k], d1[k]]), a[k], equal_nan=True), 'sharding changes ' + k
+    e = op.simulate_rays(ray_az[:40] + 360.0, ray_el[:40])
+    assert np.allclose(e['ZH'], a['ZH'][:40], rtol=1e-5, equal_nan=True)
+    # scaling every table by 3 scales the reflectivities and attenuation by 3, leaves ZDR/RHOHV
+    luts3 = {}
+    for h, l in luts.items():
+        l3 = copy.copy(l)
+        l3.value_table = l.value_table * 3.0
+        luts3[h] = l3
+    conf2 = copy.deepcopy(conf)
+    conf2['microphysics'] = {'with_attenuation': 0}
+    op2 = RadarOperator(conf2, output_variables='only_radar', device=0)
+    op2.set_lut(luts)
+    op2.load_model(model)
+    x = op2.simulate_rays(ray_az[:90], ray_el[:90])
+    op2.set_lut(luts3)
+    y = op2.simulate_rays(ray_az[:90], ray_el[:90])
+    assert np.allclose(y['ZH'], 3 * x['ZH'], rtol=3e-6, equal_nan=True)
+    assert np.allclose(y['KDP'], 3 * x['KDP'], rtol=3e-6, equal_nan=True)
+    assert np.allclose(y['ZDR'], x['ZDR'], rtol=3e-6, equal_nan=True)
+    st = op._engine.stats()
+    assert st['n_active_pairs'] > 0 and st['launches'] >= 6

@@ -1,0 +1,156 @@
+"""Host-side logic of the package (no GPU): configuration, lookup-table container and file
+format, quadrature, refraction, hydrometeor classes, constants, the C-ABI exports."""
+import ctypes
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT
+
+
+def test_constants_match_reference_values():
+    from cosmo_pol_b200.constants import constants_1mom as c1, constants_2mom as c2
+    ref = json.load(open(os.path.join(GOLDEN, 'ref_constants.json')))
+    for k, v in ref['1mom'].items():
+        if hasattr(c1, k):
+            assert float(getattr(c1, k)) == v, k
+    for k, v in ref['2mom'].items():
+        if hasattr(c2, k):
+            assert float(getattr(c2, k)) == v, k
+    must = ['N0_G', 'AM_G', 'BM_G', 'AV_G', 'BV_G', 'LAMBDA_FACTOR_R', 'VEL_FACTOR_S', 'NTOT_FACTOR_I', 'D_MAX_S']
+    assert all(hasattr(c1, k) for k in must)
+    assert all(hasattr(c2, k + '_' + s) for k in ('AM', 'BM', 'AV', 'BV', 'NU', 'MU', 'X_MIN', 'X_MAX', 'LAMBDA_FACTOR')
+               for s in 'RSGHI')
+
+
+def test_config_defaults_and_validation(tmp_path):
+    from cosmo_pol_b200.config import cfg
+    ref = json.load(open(os.path.join(GOLDEN, 'ref_constants.json')))['defaults']
+    for sec, d in ref.items():
+        for k, v in d.items():
+            assert cfg.DEFAULTS[sec][k] == v, (sec, k)
+    yml = tmp_path / 'opt.yml'
+    yml.write_text('radar:\n    coords: [47.28436, 8.51201, 891]\n    frequency: 5.6\n    range: 150000\n'
+                   '    radial_resolution: 150\n    3dB_beamwidth: 1.\nintegration:\n    nh_GH: 4\n    nv_GH: 3\n'
+                   'doppler:\n    scheme: 2\n')
+    c = cfg.sanity_check(cfg.init(str(yml)))
+    assert c['radar']['frequency'] == 5.6 and c['doppler']['scheme'] == 2
+    assert c['integration']['nh_GH'] == 3          # 4 is invalid (odd values only) -> default
+    assert c['microphysics']['with_ice_crystals'] == 1
+    with pytest.raises(ValueError):
+        cfg.sanity_check({'radar': {'frequency': 5.6}})      # coords are mandatory
+    assert cfg.init(str(tmp_path / 'missing.yml')) is None and cfg.CONFIG['radar']['range'] == 150000
+
+
+def test_lut_file_roundtrip_and_floor_lookup(tmp_path):
+    from cosmo_pol_b200 import synthetic
+    from cosmo_pol_b200.lookup import load_lut, save_lut, load_all_lut
+    lut = synthetic.make_lut('S', 5.6, '1mom', n_e=10, n_t=12, n_d=64)
+    f = tmp_path / 'lut_tmatrix_masc' / 'lut_SZ_S_5_6_1mom.lut'
+    os.makedirs(f.parent)
+    save_lut(lut, str(f))
+    import tarfile
+    assert sorted(m.name for m in tarfile.open(str(f)).getmembers()) == sorted(
+        ['axes.npy', 'axes_limits.npy', 'axes_names.npy', 'axes_step.npy', 'value_table.npy'])
+    back = load_all_lut('1mom', ['S'], 5.6, 'tmatrix_masc', folder=str(tmp_path))['S']
+    assert np.array_equal(back.value_table, lut.value_table) and back.axes_names == lut.axes_names
+    g = np.load(os.path.join(GOLDEN, 'ref_units.npz'))
+    assert np.array_equal(back.lookup_line(e=g['lut_e'], t=g['lut_t']), g['lut_line'])     # reference output
+    with pytest.raises(IOError):
+        load_all_lut('1mom', ['G'], 5.6, 'tmatrix_masc', folder=str(tmp_path))
+
+
+def test_quadrature_fan():
+    from cosmo_pol_b200.interpolation.quadrature import subbeam_fan
+    import radop_oracle as O
+    c = O.default_config()
+    c['integration'].update({'nh_GH': 3, 'nv_GH': 5, 'weight_threshold': 0.9})
+    fan = subbeam_fan(c)
+    ph, pv, w, keep = O.gauss_hermite_subbeams(c)
+    assert np.array_equal(fan.pts_hor, ph) and np.array_equal(fan.pts_ver, pv) and np.array_equal(fan.weights, w)
+    assert fan.n_sub == keep.sum() < 15 and abs(w.sum() - 1) < 1e-15
+    c['integration'].update({'nh_GH': 1, 'nv_GH': 1, 'weight_threshold': 1.})
+    fan = subbeam_fan(c)
+    assert fan.n_sub == 1 and fan.weight[0] == 1.0 and fan.daz[0] == 0.0 and fan.dele[0] == 0.0
+    # the reference's own sub-beam list (golden): order and weights
+    g = np.load(os.path.join(GOLDEN, 'ref_path_c1mom_thr.npz'))
+    cfg = json.loads(str(g['config_json']))
+    fan = subbeam_fan(cfg)
+    az, el = g['rays'][0]
+    assert np.array_equal(fan.weight, g['sub_w'][0])
+    assert np.array_equal(np.stack([az + fan.daz, el + fan.dele], axis=1), g['sub_pt'][0])
+
+
+def test_refraction_matches_reference_bitwise():
+    from cosmo_pol_b200.interpolation.atm_refraction import compute_trajectory_radial
+    g = np.load(os.path.join(GOLDEN, 'ref_units.npz'))
+    coords = [47.28436, 8.51201, 891.]
+    for i, el in enumerate(g['traj_elev']):
+        s, h, e = compute_trajectory_radial(g['derived_range'], el, coords, 1)
+        assert s.dtype == np.float32 and np.array_equal(s, g['traj_s'][i])
+        assert np.array_equal(h, g['traj_h'][i]) and np.array_equal(e, g['traj_e'][i])
+    with pytest.raises(NotImplementedError):
+        compute_trajectory_radial(g['derived_range'], 1.0, coords, 2)
+
+
+@pytest.mark.parametrize('scheme,kinds', [('1mom', 'RSGI'), ('2mom', 'RSGHI')])
+def test_hydrometeor_classes_match_reference(scheme, kinds):
+    from cosmo_pol_b200.hydrometeors import create_hydrometeor
+    g = np.load(os.path.join(GOLDEN, 'ref_units.npz'))
+    for k in kinds:
+        tag = 'psd_{}_{}_'.format(scheme, k)
+        hy = create_hydrometeor(k, scheme)
+        D = g[tag + 'D']
+        hy.d_min, hy.d_max = D[0], D[-1]
+        if scheme == '1mom':
+            hy.set_psd(*([g[tag + 'T'], g[tag + 'QM']] if k in 'SI' else [g[tag + 'QM']]))
+        else:
+            hy.set_psd(g[tag + 'QN'], g[tag + 'QM'])
+        assert np.allclose(hy.lambda_, g[tag + 'lambda'], rtol=1e-5)
+        assert np.allclose(hy.get_N(D), g[tag + 'N'], rtol=2e-3, atol=1e-300)
+        f = hy.abi_fields()
+        assert f['nu'] == hy.nu and f['species'] in range(5) and f['psd'] in range(4)
+    with pytest.raises(ValueError):
+        create_hydrometeor('X', scheme)
+
+
+def test_abi_library_exports_every_declared_symbol():
+    """libradop.so loads without a GPU and exports exactly what include/radop.h declares."""
+    from cosmo_pol_b200 import _abi
+    header = open(os.path.join(ROOT, 'include', 'radop.h')).read()
+    declared = sorted(set(re.findall(r'^(?:int|const char \*)\s*\*?(radop_\w+)\s*\(', header, flags=re.M)))
+    assert len(declared) >= 20
+    assert sorted(_abi.EXPORTS) == declared
+    lib = _abi.load_library()
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.radop_abi_version() == _abi.RADOP_ABI_VERSION
+    # struct layouts agree with the header (sizes computed by the C compiler)
+    src = '#include "radop.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu %zu", sizeof(RadopSpecies), sizeof(RadopParams), sizeof(RadopScan), sizeof(RadopOut), sizeof(RadopStats));return 0;}'
+    import subprocess, tempfile
+    with tempfile.TemporaryDirectory() as d:
+        open(os.path.join(d, 't.c'), 'w').write(src)
+        subprocess.check_call(['gcc', '-I', os.path.join(ROOT, 'include'), '-o', os.path.join(d, 't'), os.path.join(d, 't.c')])
+        sizes = [int(x) for x in subprocess.check_output([os.path.join(d, 't')]).split()]
+    assert sizes == [ctypes.sizeof(_abi.RadopSpecies), ctypes.sizeof(_abi.RadopParams), ctypes.sizeof(_abi.RadopScan),
+                     ctypes.sizeof(_abi.RadopOut), ctypes.sizeof(_abi.RadopStats)]
+
+
+def test_no_cpu_fallback_without_gpu():
+    from conftest import has_gpu
+    if has_gpu():
+        pytest.skip('GPU present')
+    from cosmo_pol_b200 import _abi
+    with pytest.raises(_abi.RadopError):
+        _abi.Engine(0)
+
+
+def test_product_never_imports_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, 'cosmo_pol_b200')):
+        for f in files:
+            if f.endswith('.py'):
+                src = open(os.path.join(dirpath, f)).read()
+                assert 'radop_oracle' not in src and 'oracle/' not in src.replace('oracle/_ref', ''), f
