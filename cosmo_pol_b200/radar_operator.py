@@ -125,8 +125,12 @@ class RadarOperator(object):
             self._dirty['lut'] = True
         except IOError as e:
             # the reference ships no tables either (.gitignore:3); they must be provided
-            print('Lookup tables not found ({}); install them with set_lut(dict) or lut_folder='.format(e))
-            self.lut_sz = None
+            if self.lut_sz and all(h in self.lut_sz for h in list_hydrom):
+                print('Lookup table files not found; keeping the tables installed with set_lut(dict)')
+                self._dirty['lut'] = True
+            else:
+                print('Lookup tables not found ({}); install them with set_lut(dict) or lut_folder='.format(e))
+                self.lut_sz = None
 
     def _species_for_lut(self):
         c = self.__config

@@ -1050,11 +1050,11 @@ def simulate_ray(model, luts, cfg, azimuth, elevation, accum='ref', debug=False,
 
 
 def simulate_scan(model, luts, cfg, azimuths, elevations, accum='ref', output_variables='only_radar',
-                  sensitivity_cut=False):
+                  sensitivity_cut=False, debug=False):
     """List of rays given as parallel arrays (az[r], el[r]); returns dict of
     [n_rays, n_gates] arrays."""
     rays = [simulate_ray(model, luts, cfg, a, e, accum=accum, output_variables=output_variables,
-                         sensitivity_cut=sensitivity_cut)
+                         sensitivity_cut=sensitivity_cut, debug=debug)
             for a, e in zip(azimuths, elevations)]
     out = {}
     for k in rays[0]['values'].keys():
@@ -1064,4 +1064,6 @@ def simulate_scan(model, luts, cfg, azimuths, elevations, accum='ref', output_va
     out['lons'] = np.stack([r['lons'] for r in rays])
     out['dist'] = np.stack([r['dist'] for r in rays])
     out['heights'] = np.stack([r['heights'] for r in rays])
+    if debug and 'dbg' in rays[0]:
+        out['sz_total'] = np.stack([r['dbg']['sz_total'] for r in rays])
     return out

@@ -110,16 +110,18 @@ def test_observables_against_oracle(scheme, freq):
     cfg = oracle_cfg(op)
     rays_az, rays_el = np.tile(az, 3), np.repeat([1.0, 8.5, 35.0], len(az))
     for accum in ('f64', 'ref'):
-        ref = O.simulate_scan(pm, pl, cfg, rays_az, rays_el, accum=accum, output_variables='all', sensitivity_cut=True)
+        ref = O.simulate_scan(pm, pl, cfg, rays_az, rays_el, accum=accum, output_variables='all', sensitivity_cut=True,
+                              debug=True)
         got = {k: v.reshape(-1, v.shape[-1]) for k, v in res.fields.items()}
-        floor = None
-        if accum == 'ref':
-            # the reference stores s8 and s10 in float32 before subtracting them: allow its own
-            # cancellation noise (a few ulp of the larger term) on top of the 1e-3 tolerance
-            floor = 4e-6 * np.abs(ref['KDP']) / np.maximum(np.abs(ref['KDP']) / (np.abs(ref['ATT_H']) * 300 + 1e-30), 1e-30) * 0
-            floor = np.full(ref['KDP'].shape, 0.0)
-        assert_observables_close(got, ref, sz_scale=None if accum == 'f64' else 3e-4 * np.abs(ref['KDP']), what=accum)
-        assert np.array_equal(res.mask.reshape(ref['mask'].shape), ref['mask'])
+        # float32 storage of s8 and s10 before their subtraction (doppler_scatter.py:133-134, 527):
+        # a few ulp of the larger term, expressed in KDP units
+        kfac = 1e-3 * (180.0 / np.pi) * O.derived_constants(cfg)['WAVELENGTH']
+        sz = ref['sz_total'].astype(np.float64)
+        floor = 16 * np.finfo(np.float32).eps * kfac * (np.abs(sz[..., 8]) + np.abs(sz[..., 10]))
+        # accum == 'ref': the reference stores s8 and s10 in float32 before subtracting them;
+        # its own cancellation noise is allowed on top of the 1e-3 tolerance
+        assert_observables_close(got, ref, sz_scale=None if accum == 'f64' else floor, what=accum)
+        assert np.array_equal(res.mask.reshape(ref['mask'].shape), ref['mask'].astype(np.float32))
         a, b = got['RVEL'], ref['RVEL']
         assert np.array_equal(np.isnan(a), np.isnan(b))
         ok = np.isfinite(b)
@@ -149,11 +151,15 @@ def test_against_reference_goldens(name, scheme, freq):
     out = op.simulate_rays(rays[:, 0], rays[:, 1])
     ref = {k[4:]: g[k] for k in g.files if k.startswith('obs_')}
     assert_observables_close(out, ref, sz_scale=5e-4 * np.abs(ref['KDP']), what=name)
-    assert np.array_equal(out['mask'], g['mask'])
+    assert np.array_equal(out['mask'], g['mask'].astype(np.float32))
     a, b = out['RVEL'], ref['RVEL']
     assert np.array_equal(np.isnan(a), np.isnan(b))
     ok = np.isfinite(b)
-    assert np.max(np.abs(a[ok] - b[ok])) < 2e-3
+    d = a[ok] - b[ok]
+    nyq = float(g['nyquist'])
+    if nyq > 0:      # folded velocities are compared modulo the Nyquist interval
+        d = (d + nyq) % (2 * nyq) - nyq
+    assert np.max(np.abs(d)) < 2e-3
     for k in [f for f in g.files if f.startswith('int_')]:
         assert np.allclose(out[k[4:]], g[k], rtol=2e-5, atol=1e-9), k
     if 'cut_ZH' in g.files:
@@ -241,14 +247,19 @@ def test_scan_level_properties():
         luts3[h] = l3
     conf2 = copy.deepcopy(conf)
     conf2['microphysics'] = {'with_attenuation': 0}
+    conf2['radar']['sensitivity'] = [-300, 10000]          # no censoring: it is not linear
     op2 = RadarOperator(conf2, output_variables='only_radar', device=0)
     op2.set_lut(luts)
     op2.load_model(model)
     x = op2.simulate_rays(ray_az[:90], ray_el[:90])
     op2.set_lut(luts3)
     y = op2.simulate_rays(ray_az[:90], ray_el[:90])
-    assert np.allclose(y['ZH'], 3 * x['ZH'], rtol=3e-6, equal_nan=True)
-    assert np.allclose(y['KDP'], 3 * x['KDP'], rtol=3e-6, equal_nan=True)
-    assert np.allclose(y['ZDR'], x['ZDR'], rtol=3e-6, equal_nan=True)
+    def relerr(u, v):
+        ok = np.isfinite(v)
+        assert np.array_equal(np.isnan(u), np.isnan(v))
+        return float(np.max(np.abs(u[ok] - v[ok]) / np.abs(v[ok])))
+    assert relerr(y['ZH'], 3 * x['ZH']) < 1e-5, relerr(y['ZH'], 3 * x['ZH'])
+    assert relerr(y['KDP'], 3 * x['KDP']) < 1e-5, relerr(y['KDP'], 3 * x['KDP'])
+    assert relerr(y['ZDR'], x['ZDR']) < 1e-5, relerr(y['ZDR'], x['ZDR'])
     st = op._engine.stats()
     assert st['n_active_pairs'] > 0 and st['launches'] >= 6
