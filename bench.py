@@ -1,0 +1,437 @@
+#!/usr/bin/env python
+# -*- coding: utf-8 -*-
+"""bench.py -- sub-beam gates per second of the forward-operator hot path on a 20-elevation
+C-band volume scan (BASELINE.json metric; SURVEY.md 8d, configuration 3).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one pass of the hot path (radop_execute: interpolation -> PSD parameters ->
+bin sort -> PSD x scattering-table integration -> quadrature/species sums -> ray epilogue)
+over one volume scan: 20 elevations x 360 azimuths x 500 gates x 9 Gauss-Hermite sub-beams
+= 3.24e7 sub-beam gates, 1-moment scheme, species R,S,G,I, seeded synthetic COSMO-shaped
+fields and scattering tables (no data files exist offline).
+
+  value : device-resident inputs (fields, tables, staged ray list); CUDA events on the
+          engine's stream around exactly K steps; max over ranks.
+  e2e   : the same through the reference-facing C-ABI call radop_simulate() with HOST
+          buffers: ray list + trajectories copied H2D, every observable copied D2H, each step.
+  N > 1 : weak scaling.  Rank r simulates its own volume (the azimuths of rank r are offset
+          by r/N of the azimuth step, i.e. the N-rank job is one volume with N x denser
+          azimuth sampling, sharded by ray); fields and tables are replicated; the only
+          exchange is the gather of the observables to rank 0 over NCCL (inside the step).
+
+--impl reference times the CPU restatement of the reference's algorithm (oracle/, a "port":
+the reference package itself needs pycosmo / pyproj / pyart and Python 2 idioms and cannot
+be imported on this image) on the host cores, parallelised as the reference does with a
+process pool over rays (cosmo_pol/radar_operator.py:402,429-432)."""
+from __future__ import print_function
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# the 20 elevations of cosmo_pol/option_files/nyquist_swiss_radars.txt:2-21, in file order
+VOLUME_ELEVATIONS = [-0.2, 0.4, 1.0, 1.6, 2.5, 3.5, 4.5, 5.5, 6.5, 7.5, 8.5, 9.5, 13., 16., 11., 20., 25., 30., 35., 40.]
+FLOP_PER_PAIR = 28672          # 2*1024*12 contraction + 4*1024 PSD evaluation
+METRIC = 'sub-beam gates/sec for a 20-elevation volume scan'
+UNIT = 'sub-beam gates/s'
+
+
+def volume_config():
+    """SURVEY.md 8d radar parameters of configuration 3."""
+    from cosmo_pol_b200 import synthetic
+    return {'radar': {'coords': list(synthetic.ALBIS), 'type': 'ground', 'frequency': 5.6, 'range': 150000,
+                      'radial_resolution': 300, 'sensitivity': [-5, 10000], '3dB_beamwidth': 1.0},
+            'integration': {'scheme': 1, 'nh_GH': 3, 'nv_GH': 3, 'weight_threshold': 1.0},
+            'refraction': {'scheme': 1},
+            'microphysics': {'with_attenuation': 1, 'with_melting': 0, 'with_ice_crystals': 1},
+            'doppler': {'scheme': 1}}
+
+
+def volume_rays(rank=0, world=1, n_az=360):
+    az = np.arange(n_az, dtype=np.float64) * (360.0 / n_az) + (360.0 / n_az) * rank / float(world)
+    el = np.repeat(np.asarray(VOLUME_ELEVATIONS, dtype=np.float64), n_az)
+    return np.tile(az, len(VOLUME_ELEVATIONS)), el
+
+
+def workload_config(world, scaling):
+    return {'workload': 'cfg3: 20-elevation C-band (5.6 GHz) volume scan, 1-mom R/S/G/I, 360 az x 500 gates x 3x3 GH '
+                        'sub-beams per GPU, synthetic COSMO grid 60x400x400 @0.02deg',
+            'rays_per_gpu': 7200, 'gates': 500, 'sub_beams': 9, 'species': 'R,S,G,I',
+            'parallelism': 'rays sharded over {} GPU(s), fields+tables replicated, NCCL gather of observables'.format(world)
+                           if world > 1 else 'single GPU',
+            'scaling_mode': scaling,
+            'l2': 'no explicit flush: one step streams ~6 GB of per-gate work buffers plus a 614 MB field '
+                  'array, far larger than the 126 MB L2'}
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, device):
+        self.device, self.proc, self.lines = device, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.device), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, universal_newlines=True)
+            self.thread = threading.Thread(target=self._read)
+            self.thread.daemon = True
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.time(), line.strip()))
+
+    def stop(self, t0=None, t1=None):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons, power = [], [], set(), []
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for ts, line in self.lines:
+            if t0 is not None and not (t0 - 0.05 <= ts <= t1 + 0.15):
+                continue
+            f = [x.strip() for x in line.split(',')]
+            try:
+                sm.append(float(f[0]))
+                smax.append(float(f[1]))
+                power.append(float(f[2]))
+            except Exception:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith('active'):
+                    reasons.add(n)
+        return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': max(smax) if smax else None,
+                'power_w_max': max(power) if power else None, 'samples': len(sm), 'reasons': sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the oracle restatement of the reference's algorithm on the host cores
+# ------------------------------------------------------------------------------------------
+_CPU = {}
+
+
+def _cpu_ray(args):
+    O = _CPU['O']
+    az, el = args
+    r = O.simulate_ray(_CPU['model'], _CPU['luts'], _CPU['cfg'], az, el, accum='ref', sensitivity_cut=True)
+    return float(np.nansum(r['values']['ZH']))
+
+
+def build_inputs(scheme='1mom', freq=5.6):
+    from cosmo_pol_b200 import synthetic
+    model = synthetic.make_model(scheme=scheme)              # 60 x 400 x 400, seed 1234
+    luts = synthetic.make_all_luts(freq, scheme, with_ice=True)   # seed 4321
+    return model, luts
+
+
+def checked_config(conf):
+    from cosmo_pol_b200.config import cfg
+    from cosmo_pol_b200.constants import global_constants as constants
+    cfg.init(conf)
+    c = cfg.sanity_check(cfg.CONFIG)
+    cfg.CONFIG = c
+    constants.update()
+    return c
+
+
+class CpuArm(object):
+    """Process pool over rays, as the reference does (radar_operator.py:402: Pool(cpu_count()))."""
+
+    def __init__(self, model, luts, conf, cores=None):
+        import multiprocessing as mp
+        sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+        import radop_oracle as O
+        from cosmo_pol_b200 import synthetic
+        c = checked_config(conf)
+        c['radar']['nyquist_velocity'] = None
+        _CPU.update(O=O, cfg=c, model=synthetic.model_as_plain(model),
+                    luts={h: synthetic.lut_as_plain(l) for h, l in luts.items()})
+        try:
+            avail = len(os.sched_getaffinity(0))
+        except Exception:
+            avail = os.cpu_count() or 1
+        self.cores = int(cores or avail)
+        self.pool = mp.get_context('fork').Pool(self.cores)
+        self.n_sub = 9
+        self.n_gates = len(np.arange(c['radar']['radial_resolution'] / 2., c['radar']['range'],
+                                     c['radar']['radial_resolution']))
+
+    def sample_rays(self, rays_per_core=8):
+        """Evenly strided sample of the 7200-ray volume (every elevation represented)."""
+        az, el = volume_rays()
+        n = min(len(az), max(40, rays_per_core * self.cores))
+        idx = (np.arange(n) * (len(az) / float(n))).astype(int)
+        # interleave so that neighbouring tasks belong to different elevations (even load)
+        return az[idx], el[idx], n
+
+    def run(self, az, el):
+        t = time.time()
+        self.pool.map(_cpu_ray, list(zip(az, el)), chunksize=1)
+        return time.time() - t
+
+    def close(self):
+        self.pool.terminate()
+        self.pool.join()
+
+
+def cpu_baseline(model, luts, conf, budget_s=20.0):
+    arm = CpuArm(model, luts, conf)
+    az, el, n = arm.sample_rays()
+    arm.run(az[:arm.cores], el[:arm.cores])          # warm the workers (imports, page-in)
+    dt = arm.run(az, el)
+    sbg = n * arm.n_sub * arm.n_gates
+    arm.close()
+    return {'value': sbg / dt, 'unit': UNIT, 'cores': arm.cores, 'kind': 'port',
+            'sample': '{} of the 7200 rays of the volume (even stride over all 20 elevations), '
+                      '{:.1f} s wall on {} processes'.format(n, dt, arm.cores)}
+
+
+def run_reference(args):
+    """--impl reference: K timed steps, each the same bounded ray sample on all host cores."""
+    rank = int(os.environ.get('RANK', 0))
+    if rank != 0:
+        return 0
+    conf = volume_config()
+    model, luts = build_inputs()
+    arm = CpuArm(model, luts, conf)
+    az, el, n = arm.sample_rays()
+    for _ in range(max(1, args.warmup)):
+        arm.run(az[:max(arm.cores, n // 4)], el[:max(arm.cores, n // 4)])
+    t = 0.0
+    for _ in range(args.steps):
+        t += arm.run(az, el)
+    arm.close()
+    sbg = n * arm.n_sub * arm.n_gates
+    value = sbg * args.steps / t
+    sample = ('each step = {} of the 7200 rays of the volume (even stride over all 20 elevations) = {} sub-beam '
+              'gates, numpy oracle port of the reference algorithm, {} worker processes'.format(n, sbg, arm.cores))
+    line = {'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * t / args.steps,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64/f32 (numpy, reference dtypes)',
+            'data': 'synthetic', 'config': workload_config(1, 'weak'),
+            'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': arm.cores, 'kind': 'port', 'sample': sample},
+            'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------
+def fp32_peaks(eng, seconds=1.5):
+    """Measured FP32 FMA throughput (dependent-free FFMA chains, radop_measure_fp32_peak):
+    burst = best of the first calls, sustained = median of back-to-back calls over `seconds`."""
+    burst = max(eng.measure_fp32_peak() for _ in range(2))
+    vals, t0 = [], time.time()
+    while time.time() - t0 < seconds:
+        vals.append(eng.measure_fp32_peak())
+    sustained = float(np.median(vals[len(vals) // 2:])) if vals else burst
+    return burst, sustained
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from cosmo_pol_b200 import RadarOperator
+    from cosmo_pol_b200._abi import OUT_NAMES
+    from cosmo_pol_b200 import parallel
+
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a CUDA GPU: the hot path has no CPU fallback (use --impl reference for the CPU arm)')
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    quiet = open(os.devnull, 'w')
+    stdout, sys.stdout = sys.stdout, quiet            # the host layer prints like the reference does
+
+    conf = volume_config()
+    model, luts = build_inputs()
+    t_up = time.time()
+    op = RadarOperator(conf, output_variables='only_radar', device=local)
+    op.set_lut(luts)
+    op.load_model(model)
+    eng = op._prepare_engine()
+    t_up = time.time() - t_up
+    scaling = args.scaling
+    if scaling == 'weak':
+        az, el = volume_rays(rank, world)
+    else:
+        az, el = volume_rays()
+        lo, hi = parallel.shard_bounds(len(az), rank, world)
+        az, el = az[lo:hi], el[lo:hi]
+    scan = op.build_scan(az, el)
+    eng.stage(scan)
+    stream = torch.cuda.ExternalStream(eng.stream_ptr(), device=torch.device('cuda', local))
+    n_out = len(OUT_NAMES) + 1
+    gather_list = None
+
+    def step():
+        eng.execute()
+        if world > 1:
+            ptr, nr, ng = eng.device_outputs()
+            t = parallel.device_tensor(ptr, (n_out, nr, ng), local)
+            with torch.cuda.stream(stream):
+                dist.gather(t, gather_list if rank == 0 else None, dst=0)
+
+    if world > 1:
+        eng.execute()
+        eng.synchronize()
+        ptr, nr, ng = eng.device_outputs()
+        if rank == 0:
+            lens = [scan.n_rays] * world
+            if scaling == 'strong':
+                lens = [parallel.shard_bounds(7200, r, world)[1] - parallel.shard_bounds(7200, r, world)[0] for r in range(world)]
+            if len(set(lens)) != 1:
+                raise SystemExit('strong scaling needs 7200 divisible by the number of GPUs')
+            gather_list = [torch.empty((n_out, nr, ng), dtype=torch.float32, device='cuda:{}'.format(local))
+                           for _ in range(world)]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        eng.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    eng.enable_timing(True)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    barrier()
+    t1 = time.time()
+    ms = e0.elapsed_time(e1)
+    st = eng.stats()
+    eng.enable_timing(False)
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    launches = int(st['launches']) * args.steps
+
+    # ---- end to end through the C-ABI with host buffers -------------------------------------
+    for _ in range(2):
+        arrays = eng.simulate(scan, want_latlon=True)
+    barrier()
+    te = time.perf_counter()
+    for _ in range(args.steps):
+        arrays = eng.simulate(scan, want_latlon=True)
+    barrier()
+    te = time.perf_counter() - te
+    h2d = scan.bytes_in()
+    d2h = int(sum(a.nbytes for a in arrays.values()))
+    checksum = float(np.nansum(arrays['ZH'][::97]))
+
+    if world > 1:
+        tt = torch.tensor([ms, te], dtype=torch.float64, device='cuda:{}'.format(local))
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms, te = float(tt[0]), float(tt[1])
+        cnt = torch.tensor([scan.n_subbeam_gates, st['n_active_pairs']], dtype=torch.float64, device='cuda:{}'.format(local))
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        total_sbg, total_pairs = float(cnt[0]), float(cnt[1])
+    else:
+        total_sbg, total_pairs = float(scan.n_subbeam_gates), float(st['n_active_pairs'])
+    sys.stdout = stdout
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    burst, sustained = fp32_peaks(eng)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+    except Exception:
+        pass
+    pairs = float(st['n_active_pairs'])
+    flops = FLOP_PER_PAIR * pairs
+    achieved = flops / (st['ms_integrate'] * 1e-3) / 1e12 if st['ms_integrate'] > 0 else None
+    sbg1 = float(scan.n_subbeam_gates)
+    nvar = 9
+    alg_bytes = sbg1 * (nvar * 32 + 32) + scan.n_rays * scan.n_gates * 52 + st['n_lut_bins'] * 49152
+    line = {
+        'metric': METRIC, 'value': total_sbg / (ms * 1e-3 / args.steps), 'unit': UNIT, 'n_gpus': world,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True,
+        'scaling': scaling, 'vs_baseline': None, 'dtype': 'f32 (f64 geodesy and PSD parameters)', 'data': 'synthetic',
+        'config': workload_config(world, scaling),
+        'e2e': {'value': total_sbg / (te / args.steps), 'unit': UNIT, 'h2d_bytes_per_step': h2d,
+                'd2h_bytes_per_step': d2h, 'ms_per_step': 1e3 * te / args.steps,
+                'call': 'radop_simulate (C-ABI, host buffers) per rank'},
+        'gpu_launches': launches,
+        'clocks': clocks,
+        'roofline': {'bound': 'fp32', 'kernel': 'k_integrate', 'achieved': achieved, 'peak': sustained, 'unit': 'TFLOP/s',
+                     'frac': (achieved / sustained) if achieved else None, 'traffic': None,
+                     'peak_kind': 'measured here: dependent-free FFMA probe, sustained (median of back-to-back runs); '
+                                  'burst {:.1f}. MEASURED_PEAKS.json holds no FP32 figure (hbm {} GB/s)'.format(
+                                      burst, peaks.get('hbm_gbs')),
+                     'algorithmic_flop_per_launch': flops, 'flop_per_active_pair': FLOP_PER_PAIR,
+                     'active_pairs_per_launch': pairs, 'kernel_ms': st['ms_integrate'],
+                     'hbm_floor_ms': alg_bytes / (peaks.get('hbm_gbs', 6650.0) * 1e9) * 1e3,
+                     'fp32_floor_ms': flops / (sustained * 1e12) * 1e3},
+        'stages_ms': {'interp_psd': st['ms_interp'], 'bin_sort': st['ms_sort'], 'integrate': st['ms_integrate'],
+                      'reduce_epilogue': st['ms_reduce'], 'total': st['ms_total'], 'n_timed': st['n_timed']},
+        'workload_stats': {'sub_beam_gates_per_gpu': sbg1, 'active_pairs_per_gpu': pairs, 'active_pair_fraction':
+                           pairs / (sbg1 * 4), 'lut_bins_touched': int(st['n_lut_bins']), 'tiles': int(st['n_tiles']),
+                           'one_time_upload_s': t_up, 'checksum': checksum},
+    }
+    if world == 1 and not args.no_cpu:
+        line['cpu_baseline'] = cpu_baseline(model, luts, conf)
+    else:
+        line['cpu_baseline'] = {'value': None, 'unit': UNIT, 'cores': 0, 'kind': 'port',
+                                'sample': 'timed at N=1 only'}
+    print(json.dumps(line))
+    sys.stdout.flush()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--scaling', default='weak', choices=['weak', 'strong'])
+    ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
+    if args.impl == 'reference':
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == '__main__':
+    sys.exit(main())

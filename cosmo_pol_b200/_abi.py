@@ -62,7 +62,8 @@ class RadopOut(C.Structure):
 class RadopStats(C.Structure):
     _fields_ = [('n_subbeam_gates', C.c_int64), ('n_active_pairs', C.c_int64), ('n_lut_bins', C.c_int64),
                 ('n_tiles', C.c_int64), ('launches', C.c_int64), ('ms_interp', C.c_float), ('ms_sort', C.c_float),
-                ('ms_integrate', C.c_float), ('ms_reduce', C.c_float), ('ms_total', C.c_float)]
+                ('ms_integrate', C.c_float), ('ms_reduce', C.c_float), ('ms_total', C.c_float),
+                ('n_timed', C.c_int32), ('reserved', C.c_int32)]
 
 
 class RadopError(RuntimeError):

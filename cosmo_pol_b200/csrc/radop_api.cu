@@ -77,7 +77,8 @@ struct RadopHandle_ {
     size_t k2_smem = 0;
     // timing
     bool timing = false;
-    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    std::vector<cudaEvent_t> ev;   // 5 events per timed execute since radop_enable_timing(1)
+    int n_timed = 0;
     RadopStats stats;
 
     int fail(int code, const std::string &msg)
@@ -130,7 +131,6 @@ int radop_create(int device, RadopHandle **out)
         return RADOP_ERR_CUDA;
     }
     cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, device);
-    for (auto &e : h->ev) cudaEventCreate(&e);
     memset(&h->stats, 0, sizeof h->stats);
     memset(&h->p, 0, sizeof h->p);
     *out = h;
@@ -150,7 +150,7 @@ int radop_destroy(RadopHandle *h)
     for (DevBuf *b : bufs) b->release();
     for (auto &l : h->lut) { l.table.release(); l.aux.release(); }
     if (h->pinned) cudaFreeHost(h->pinned);
-    for (auto &e : h->ev) if (e) cudaEventDestroy(e);
+    for (auto &e : h->ev) cudaEventDestroy(e);
     cudaStreamDestroy(h->stream);
     delete h;
     return RADOP_OK;
@@ -464,7 +464,17 @@ int radop_execute(RadopHandle *h)
 
     cudaStream_t st = h->stream;
     int launches = 0;
-    if (h->timing) CU(h, cudaEventRecord(h->ev[0], st));
+    cudaEvent_t *ev = nullptr;
+    if (h->timing && h->n_timed < 4096) {
+        while ((int)h->ev.size() < 5 * (h->n_timed + 1)) {
+            cudaEvent_t e;
+            CU(h, cudaEventCreate(&e));
+            h->ev.push_back(e);
+        }
+        ev = h->ev.data() + 5 * h->n_timed;
+        ++h->n_timed;
+    }
+    if (ev) CU(h, cudaEventRecord(ev[0], st));
     CU(h, cudaMemsetAsync(h->hist.p, 0, (size_t)c.total_bins * 4, st));
     CU(h, cudaMemsetAsync(h->flags.p, 0, 16, st));
 
@@ -483,7 +493,7 @@ int radop_execute(RadopHandle *h)
     const size_t hist_smem = (size_t)c.total_bins * 4;
     k_interp_psd<<<(unsigned)((n + 127) / 128), 128, hist_smem, st>>>(c, h->scan, h->z_t.as<float>(), h->fields.as<float>(), o, n);
     CU(h, cudaGetLastError()); ++launches;
-    if (h->timing) CU(h, cudaEventRecord(h->ev[1], st));
+    if (ev) CU(h, cudaEventRecord(ev[1], st));
 
     k_scan_bins<<<1, 1024, 0, st>>>(c, h->hist.as<int>(), h->bin_start.as<int>(), h->tile_start.as<int>(),
                                      h->cost_start.as<long long>(), h->cursor.as<int>(), h->totals.as<long long>());
@@ -491,7 +501,7 @@ int radop_execute(RadopHandle *h)
     k_scatter_pairs<<<(unsigned)((n + 255) / 256), 256, hist_smem, st>>>(c, h->key.as<uint16_t>(), h->p0.as<float>(), h->p1.as<float>(),
                                                                           h->scan.sub_weight, h->cursor.as<int>(), h->rec.as<PairRec>(), n);
     CU(h, cudaGetLastError()); ++launches;
-    if (h->timing) CU(h, cudaEventRecord(h->ev[2], st));
+    if (ev) CU(h, cudaEventRecord(ev[2], st));
 
     K2Args a2;
     a2.hist = h->hist.as<int>(); a2.bin_start = h->bin_start.as<int>(); a2.tile_start = h->tile_start.as<int>();
@@ -499,7 +509,7 @@ int radop_execute(RadopHandle *h)
     a2.rec = h->rec.as<PairRec>(); a2.sz_out = h->sz_out.as<float>(); a2.ice_vn = h->ice_vn.as<float2>();
     k_integrate<<<h->k2_blocks, RADOP_TILE_THREADS, h->k2_smem, st>>>(c, a2);
     CU(h, cudaGetLastError()); ++launches;
-    if (h->timing) CU(h, cudaEventRecord(h->ev[3], st));
+    if (ev) CU(h, cudaEventRecord(ev[3], st));
 
     if (c.ice_numeric >= 0 && c.doppler_scheme == 1) {
         int warps = c.n_rays * c.n_sub;
@@ -518,7 +528,7 @@ int radop_execute(RadopHandle *h)
     CU(h, cudaGetLastError()); ++launches;
     k_ray_epilogue<<<(c.n_rays * 32 + 127) / 128, 128, 0, st>>>(c, a3);
     CU(h, cudaGetLastError()); ++launches;
-    if (h->timing) CU(h, cudaEventRecord(h->ev[4], st));
+    if (ev) CU(h, cudaEventRecord(ev[4], st));
     h->stats.launches = launches;
     h->stats.n_subbeam_gates = n;
     h->executed = true;
@@ -533,6 +543,29 @@ int radop_synchronize(RadopHandle *h)
     return RADOP_OK;
 }
 
+// mean CUDA-event time of each stage over the executes recorded since radop_enable_timing(1)
+static void average_timings(RadopHandle *h)
+{
+    if (!h->n_timed) return;
+    double acc[5] = {0, 0, 0, 0, 0};
+    for (int i = 0; i < h->n_timed; ++i) {
+        cudaEvent_t *e = h->ev.data() + 5 * i;
+        float ms[5] = {0, 0, 0, 0, 0};
+        cudaEventElapsedTime(&ms[0], e[0], e[1]);
+        cudaEventElapsedTime(&ms[1], e[1], e[2]);
+        cudaEventElapsedTime(&ms[2], e[2], e[3]);
+        cudaEventElapsedTime(&ms[3], e[3], e[4]);
+        cudaEventElapsedTime(&ms[4], e[0], e[4]);
+        for (int k = 0; k < 5; ++k) acc[k] += ms[k];
+    }
+    h->stats.ms_interp = (float)(acc[0] / h->n_timed);
+    h->stats.ms_sort = (float)(acc[1] / h->n_timed);
+    h->stats.ms_integrate = (float)(acc[2] / h->n_timed);
+    h->stats.ms_reduce = (float)(acc[3] / h->n_timed);
+    h->stats.ms_total = (float)(acc[4] / h->n_timed);
+    h->stats.n_timed = h->n_timed;
+}
+
 static int finish(RadopHandle *h)
 {   // after the stream has drained: flags + statistics
     long long tot[4];
@@ -542,13 +575,7 @@ static int finish(RadopHandle *h)
     h->stats.n_active_pairs = tot[0];
     h->stats.n_tiles = tot[1];
     h->stats.n_lut_bins = tot[3];
-    if (h->timing) {
-        cudaEventElapsedTime(&h->stats.ms_interp, h->ev[0], h->ev[1]);
-        cudaEventElapsedTime(&h->stats.ms_sort, h->ev[1], h->ev[2]);
-        cudaEventElapsedTime(&h->stats.ms_integrate, h->ev[2], h->ev[3]);
-        cudaEventElapsedTime(&h->stats.ms_reduce, h->ev[3], h->ev[4]);
-        cudaEventElapsedTime(&h->stats.ms_total, h->ev[0], h->ev[4]);
-    }
+    average_timings(h);
     if (flags[0] & 1)
         return h->fail(RADOP_ERR_OUT_OF_DOMAIN, "radar domain is not entirely contained in the model domain");
     return RADOP_OK;
@@ -607,12 +634,19 @@ int radop_enable_timing(RadopHandle *h, int on)
 {
     if (!h) return RADOP_ERR_ARG;
     h->timing = on != 0;
+    h->n_timed = 0;              // a new measurement window
     return RADOP_OK;
 }
 
 int radop_get_stats(RadopHandle *h, RadopStats *s)
 {
     if (!h || !s) return RADOP_ERR_ARG;
+    if (h->executed) {     // drain the stream and refresh counters + timings
+        CU(h, cudaSetDevice(h->device));
+        CU(h, cudaStreamSynchronize(h->stream));
+        int rc = finish(h);
+        if (rc != RADOP_OK && rc != RADOP_ERR_OUT_OF_DOMAIN) return rc;
+    }
     *s = h->stats;
     return RADOP_OK;
 }

@@ -189,7 +189,10 @@ typedef struct {
     int64_t n_lut_bins;           /* distinct (species, e, t) bins touched                */
     int64_t n_tiles;              /* work tiles of the PSD-integration kernel             */
     int64_t launches;             /* kernels launched by the last execute                 */
-    float ms_interp, ms_sort, ms_integrate, ms_reduce, ms_total;  /* CUDA-event times     */
+    float ms_interp, ms_sort, ms_integrate, ms_reduce, ms_total;  /* CUDA-event times: mean
+                                     over the executes since radop_enable_timing(h, 1)     */
+    int32_t n_timed;              /* executes in that mean                                  */
+    int32_t reserved;
 } RadopStats;
 int radop_get_stats(RadopHandle *h, RadopStats *s);
 int radop_enable_timing(RadopHandle *h, int on);
