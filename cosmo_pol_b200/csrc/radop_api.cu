@@ -69,7 +69,7 @@ struct RadopHandle_ {
     ScanDev scan;
     const float *d_nyquist = nullptr;
     // work buffers
-    DevBuf mask, active, wind, sinth, vsum, nsum, key, p0, p1, vals, lat, lon, hist, flags;
+    DevBuf geo, mask, active, wind, sinth, vsum, nsum, key, p0, p1, vals, lat, lon, hist, flags;
     DevBuf bin_start, tile_start, cost_start, cursor, totals, rec, sz_out, ice_vn, ice_tot, comb, out, model_out;
     DevBuf dbg_cell, dbg_level, dbg_status, dbg_e, dbg_t, dbg_rot;
     DevConfig cfg;
@@ -142,7 +142,7 @@ int radop_destroy(RadopHandle *h)
     if (!h) return RADOP_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    DevBuf *bufs[] = {&h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
+    DevBuf *bufs[] = {&h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
                       &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
                       &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
                       &h->ice_vn, &h->ice_tot, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
@@ -357,6 +357,7 @@ static int prepare(RadopHandle *h)
     memset(&c, 0, sizeof c);
     c.n_rays = h->n_rays; c.n_sub = h->n_sub; c.n_gates = p.n_gates; c.n_vert = h->n_vert; c.center_sub = h->center_sub;
     c.radar_lat = p.radar_lat; c.radar_lon = p.radar_lon;
+    c.cos_lon0 = cos(p.radar_lon * 0.017453292519943295); c.sin_lon0 = sin(p.radar_lon * 0.017453292519943295);
     c.nz = h->nz; c.ny = h->ny; c.nx = h->nx;
     for (int i = 0; i < 2; ++i) { c.llc[i] = h->llc[i]; c.urc[i] = h->urc[i]; c.res[i] = h->res[i]; }
     memcpy(c.rot, h->rot, sizeof c.rot);
@@ -389,6 +390,20 @@ static int prepare(RadopHandle *h)
         d.a = S.a; d.b = S.b; d.alpha = S.alpha; d.beta = S.beta; d.mu = S.mu; d.nu = S.nu; d.N0 = S.N0;
         d.lambda_factor = S.lambda_factor; d.vel_factor = S.vel_factor; d.ntot_factor = S.ntot_factor;
         d.x_min = S.x_min; d.x_max = S.x_max;
+        {   // log-domain constants (see SpeciesDev)
+            const double ln1000 = 6.907755278982137;
+            d.c_l0 = 0; d.c_inv = 0; d.c_q = 0; d.e_q = 0; d.c_ka = 0; d.c_kb = 0;
+            if (S.psd == RADOP_PSD_1MOM_FIXED_N0) { d.c_l0 = log(S.lambda_factor); d.c_inv = 1.0 / (4.0 + S.mu); }
+            else if (S.psd == RADOP_PSD_1MOM_SNOW) { d.c_l0 = log(S.a * S.lambda_factor); d.c_inv = 1.0 / (S.b + 1.0); }
+            else if (S.psd == RADOP_PSD_1MOM_ICE) { d.c_l0 = log(S.b); d.c_inv = 1.0 / (S.b - 2.0); }
+            else {
+                d.c_inv = -S.nu / S.b;
+                d.c_q = S.nu / S.ntot_factor; d.e_q = (S.mu + 1.0) / S.nu;
+                d.c_ka = (1.0 + S.mu) * ln1000; d.c_kb = S.nu * ln1000;
+            }
+            d.c_v = S.vel_factor * S.alpha / S.nu; d.e_v = -(S.beta + S.mu + 1.0) / S.nu;
+            d.c_n = S.ntot_factor / S.nu; d.e_n = -(S.mu + 1.0) / S.nu;
+        }
         if (S.numeric_vn) {
             if (c.ice_numeric >= 0) return h->fail(RADOP_ERR_UNSUPPORTED, "only one species may have numeric fall-speed moments");
             c.ice_numeric = s;
@@ -417,6 +432,7 @@ int radop_execute(RadopHandle *h)
     const int nsp = c.n_species, ng = c.n_gates;
     const size_t n_rg = (size_t)c.n_rays * ng;
     const bool want_vals = c.output_model_vars || c.keep_debug;
+    CU(h, h->geo.reserve((size_t)c.n_rays * c.n_sub * sizeof(SubGeo)));
     CU(h, h->mask.reserve(n));
     CU(h, h->active.reserve(n));
     CU(h, h->wind.reserve(n * 4));
@@ -491,8 +507,18 @@ int radop_execute(RadopHandle *h)
         o.dbg_e = h->dbg_e.as<int>(); o.dbg_t = h->dbg_t.as<int>(); o.dbg_rot = h->dbg_rot.as<double>();
     }
     const size_t hist_smem = (size_t)c.total_bins * 4;
-    k_interp_psd<<<(unsigned)((n + 127) / 128), 128, hist_smem, st>>>(c, h->scan, h->z_t.as<float>(), h->fields.as<float>(), o, n);
-    CU(h, cudaGetLastError()); ++launches;
+    {
+        const int n_rq = c.n_rays * c.n_sub;
+        k_sub_geometry<<<(n_rq + 127) / 128, 128, 0, st>>>(c.n_rays, c.n_sub, c.radar_lat, h->scan.ray_az, h->scan.sub_daz,
+                                                          h->geo.as<SubGeo>());
+        CU(h, cudaGetLastError()); ++launches;
+        int occ1 = 1;
+        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, k_interp_psd, 128, hist_smem));
+        const long long want = (n + 127) / 128;
+        const unsigned grid1 = (unsigned)std::min<long long>(want, (long long)std::max(1, occ1) * h->n_sm);
+        k_interp_psd<<<grid1, 128, hist_smem, st>>>(c, h->scan, h->geo.as<SubGeo>(), h->z_t.as<float>(), h->fields.as<float>(), o, n);
+        CU(h, cudaGetLastError()); ++launches;
+    }
     if (ev) CU(h, cudaEventRecord(ev[1], st));
 
     k_scan_bins<<<1, 1024, 0, st>>>(c, h->hist.as<int>(), h->bin_start.as<int>(), h->tile_start.as<int>(),

@@ -144,69 +144,154 @@ __global__ void k_pack_aux(const float *__restrict__ d_axis, float *__restrict__
 #define DEG2RAD 0.017453292519943295
 #define RAD2DEG 57.29577951308232
 
-struct AzimuthConsts {   // everything of the direct problem that depends on the azimuth only
-    double sinA1, cosA1, sinU1, cosU1, sigma1, sinAlpha, cosSqAlpha, A, B, C;
+// everything of the direct problem that depends on the azimuth only: one record per
+// (ray, sub-beam), filled by k_sub_geometry, read (warp-broadcast) by every gate
+struct __align__(16) SubGeo {
+    double sinA1, cosA1;     // also the wind projection's sin/cos(phi), proj_vel doppler_scatter.py:30-47
+    double sinU1, cosU1;
+    double s2s1, c2s1;       // sin / cos of 2 sigma1
+    double sinAlpha, B, C;
+    double inv_bA;           // 1 / (b A): sigma0 = s * inv_bA
 };
 
-__device__ __forceinline__ void geod_prepare(double lat0_deg, double az_deg, AzimuthConsts &k)
+__global__ void k_sub_geometry(int n_rays, int n_sub, double lat0_deg, const double *__restrict__ ray_az,
+                               const double *__restrict__ sub_daz, SubGeo *__restrict__ geo)
 {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_rays * n_sub) return;
     const double f = WGS84_F, a = WGS84_A, b = (1.0 - f) * a;
-    double phi1 = lat0_deg * DEG2RAD, alpha1 = az_deg * DEG2RAD;
+    double az = ray_az[i / n_sub] + sub_daz[i % n_sub];
+    double phi1 = lat0_deg * DEG2RAD, alpha1 = az * DEG2RAD;
+    SubGeo k;
     sincos(alpha1, &k.sinA1, &k.cosA1);
     double tanU1 = (1.0 - f) * tan(phi1);
     k.cosU1 = 1.0 / sqrt(1.0 + tanU1 * tanU1);
     k.sinU1 = tanU1 * k.cosU1;
-    k.sigma1 = atan2(tanU1, k.cosA1);
+    double sigma1 = atan2(tanU1, k.cosA1);
+    sincos(2.0 * sigma1, &k.s2s1, &k.c2s1);
     k.sinAlpha = k.cosU1 * k.sinA1;
-    k.cosSqAlpha = 1.0 - k.sinAlpha * k.sinAlpha;
-    double uSq = k.cosSqAlpha * (a * a - b * b) / (b * b);
-    k.A = 1.0 + uSq / 16384.0 * (4096.0 + uSq * (-768.0 + uSq * (320.0 - 175.0 * uSq)));
+    double cosSqAlpha = 1.0 - k.sinAlpha * k.sinAlpha;
+    double uSq = cosSqAlpha * (a * a - b * b) / (b * b);
+    double A = 1.0 + uSq / 16384.0 * (4096.0 + uSq * (-768.0 + uSq * (320.0 - 175.0 * uSq)));
     k.B = uSq / 1024.0 * (256.0 + uSq * (-128.0 + uSq * (74.0 - 47.0 * uSq)));
-    k.C = f / 16.0 * k.cosSqAlpha * (4.0 + f * (4.0 - 3.0 * k.cosSqAlpha));
+    k.C = f / 16.0 * cosSqAlpha * (4.0 + f * (4.0 - 3.0 * cosSqAlpha));
+    k.inv_bA = 1.0 / (b * A);
+    geo[i] = k;
 }
 
-__device__ __forceinline__ void geod_forward(const AzimuthConsts &k, double lon0_deg, double dist, double &lon,
+// sin / cos for |x| <= SMALL_ANGLE by Taylor polynomials (truncation < 1e-19 relative): the
+// arc length of a radar ray is a few hundredths of a radian, so the argument reduction and
+// the slow paths of the library sincos are never needed
+#define SMALL_ANGLE 0.06
+__device__ __forceinline__ void sincos_small(double x, double &s, double &c)
+{
+    const double x2 = x * x;
+    double ps = -1.0 / 39916800.0;
+    ps = fma(ps, x2, 1.0 / 362880.0);
+    ps = fma(ps, x2, -1.0 / 5040.0);
+    ps = fma(ps, x2, 1.0 / 120.0);
+    ps = fma(ps, x2, -1.0 / 6.0);
+    s = fma(x * x2, ps, x);
+    double pc = 1.0 / 479001600.0;
+    pc = fma(pc, x2, -1.0 / 3628800.0);
+    pc = fma(pc, x2, 1.0 / 40320.0);
+    pc = fma(pc, x2, -1.0 / 720.0);
+    pc = fma(pc, x2, 1.0 / 24.0);
+    pc = fma(pc, x2, -0.5);
+    c = fma(x2, pc, 1.0);
+}
+// asin / atan for |x| <= SMALL_RATIO by Taylor polynomials (first neglected term < 3e-18 relative)
+#define SMALL_RATIO 0.125
+__device__ __forceinline__ double asin_small(double z)
+{
+    const double z2 = z * z;
+    double p = 12155.0 / 1245184.0;
+    p = fma(p, z2, 6435.0 / 557056.0);
+    p = fma(p, z2, 143.0 / 10240.0);
+    p = fma(p, z2, 231.0 / 13312.0);
+    p = fma(p, z2, 63.0 / 2816.0);
+    p = fma(p, z2, 35.0 / 1152.0);
+    p = fma(p, z2, 5.0 / 112.0);
+    p = fma(p, z2, 3.0 / 40.0);
+    p = fma(p, z2, 1.0 / 6.0);
+    return fma(z * z2, p, z);
+}
+__device__ __forceinline__ double atan_small(double t)
+{
+    const double t2 = t * t;
+    double p = -1.0 / 19.0;
+    p = fma(p, t2, 1.0 / 17.0);
+    p = fma(p, t2, -1.0 / 15.0);
+    p = fma(p, t2, 1.0 / 13.0);
+    p = fma(p, t2, -1.0 / 11.0);
+    p = fma(p, t2, 1.0 / 9.0);
+    p = fma(p, t2, -1.0 / 7.0);
+    p = fma(p, t2, 1.0 / 5.0);
+    p = fma(p, t2, -1.0 / 3.0);
+    return fma(t * t2, p, t);
+}
+
+// Vincenty direct solution for one gate of a sub-beam: unit vector (cos lat cos lon, ...)
+// of the gate is all the rotated-pole transform needs, so the geographic angles themselves
+// are only formed for the central sub-beam (want_angles), whose lat / lon are outputs.
+// cl0 / sl0: cos / sin of the radar longitude.
+__device__ __forceinline__ void geod_forward(const SubGeo &k, double dist, double cl0, double sl0, double lon0_deg,
+                                             bool want_angles, double &x, double &y, double &z, double &lon,
                                              double &lat)
 {
-    const double f = WGS84_F, b = (1.0 - f) * WGS84_A;
-    double sig0 = dist / (b * k.A), sigma = sig0;
-    double cos2SigmaM, sinSigma, cosSigma;
+    const double f = WGS84_F;
+    const double sig0 = dist * k.inv_bA;
+    double sigma = sig0, sinSigma, cosSigma, c2m;
+    const bool small = sig0 < SMALL_ANGLE - 1e-3;
 #pragma unroll 1
-    for (int it = 0; it < 5; ++it) {
-        cos2SigmaM = cos(2.0 * k.sigma1 + sigma);
-        sincos(sigma, &sinSigma, &cosSigma);
+    for (int it = 0; it < 6; ++it) {      // 5 fixed-point updates, then the evaluation at the result
+        if (small) sincos_small(sigma, sinSigma, cosSigma);
+        else sincos(sigma, &sinSigma, &cosSigma);
+        c2m = k.c2s1 * cosSigma - k.s2s1 * sinSigma;      // cos(2 sigma1 + sigma)
+        if (it == 5) break;
         double dS = k.B * sinSigma *
-                    (cos2SigmaM + k.B / 4.0 *
-                                      (cosSigma * (-1.0 + 2.0 * cos2SigmaM * cos2SigmaM) -
-                                       k.B / 6.0 * cos2SigmaM * (-3.0 + 4.0 * sinSigma * sinSigma) *
-                                           (-3.0 + 4.0 * cos2SigmaM * cos2SigmaM)));
+                    (c2m + k.B / 4.0 *
+                               (cosSigma * (-1.0 + 2.0 * c2m * c2m) -
+                                k.B / 6.0 * c2m * (-3.0 + 4.0 * sinSigma * sinSigma) * (-3.0 + 4.0 * c2m * c2m)));
         sigma = sig0 + dS;
     }
-    cos2SigmaM = cos(2.0 * k.sigma1 + sigma);
-    sincos(sigma, &sinSigma, &cosSigma);
-    double tmp = k.sinU1 * sinSigma - k.cosU1 * cosSigma * k.cosA1;
-    double phi2 = atan2(k.sinU1 * cosSigma + k.cosU1 * sinSigma * k.cosA1,
-                        (1.0 - f) * sqrt(k.sinAlpha * k.sinAlpha + tmp * tmp));
-    double lam = atan2(sinSigma * k.sinA1, k.cosU1 * cosSigma - k.sinU1 * sinSigma * k.cosA1);
-    double L = lam - (1.0 - k.C) * f * k.sinAlpha *
-                         (sigma + k.C * sinSigma *
-                                      (cos2SigmaM + k.C * cosSigma * (-1.0 + 2.0 * cos2SigmaM * cos2SigmaM)));
-    lon = lon0_deg + L * RAD2DEG;
-    lat = phi2 * RAD2DEG;
+    const double tmp = k.sinU1 * sinSigma - k.cosU1 * cosSigma * k.cosA1;
+    const double num = k.sinU1 * cosSigma + k.cosU1 * sinSigma * k.cosA1;
+    const double den = (1.0 - f) * sqrt(k.sinAlpha * k.sinAlpha + tmp * tmp);
+    const double la = sinSigma * k.sinA1, lb = k.cosU1 * cosSigma - k.sinU1 * sinSigma * k.cosA1;
+    const double corr = (1.0 - k.C) * f * k.sinAlpha *
+                        (sigma + k.C * sinSigma * (c2m + k.C * cosSigma * (-1.0 + 2.0 * c2m * c2m)));
+    // sin / cos of latitude and of (lon0 + lam - corr) without forming the angles
+    const double ih1 = rsqrt(num * num + den * den), ih2 = rsqrt(la * la + lb * lb);
+    const double sphi = num * ih1, cphi = den * ih1;
+    const double slam = la * ih2, clam = lb * ih2;
+    double sc, cc;
+    sincos_small(corr, sc, cc);            // |corr| < f * sigma
+    const double sL = slam * cc - clam * sc, cL = clam * cc + slam * sc;
+    const double slon = sl0 * cL + cl0 * sL, clon = cl0 * cL - sl0 * sL;
+    x = clon * cphi;
+    y = slon * cphi;
+    z = sphi;
+    if (want_angles) {
+        lat = atan2(num, den) * RAD2DEG;
+        lon = lon0_deg + (atan2(la, lb) - corr) * RAD2DEG;
+    }
 }
 
-__device__ __forceinline__ void rotate_pole(const double *__restrict__ R, double lat_deg, double lon_deg,
+// geographic unit vector -> rotated-pole (rlat, rlon) in degrees
+__device__ __forceinline__ void rotate_pole(const double *__restrict__ R, double x, double y, double z,
                                             double &rlat, double &rlon)
 {
-    double sl, cl, sp, cp;
-    sincos(lon_deg * DEG2RAD, &sl, &cl);
-    sincos(lat_deg * DEG2RAD, &sp, &cp);
-    double x = cl * cp, y = sl * cp, z = sp;
-    double xn = R[0] * x + R[1] * y + R[2] * z;
-    double yn = R[3] * x + R[4] * y + R[5] * z;
-    double zn = R[6] * x + R[7] * y + R[8] * z;
-    rlon = atan2(yn, xn) * RAD2DEG;
-    rlat = asin(zn) * RAD2DEG;
+    const double xn = R[0] * x + R[1] * y + R[2] * z;
+    const double yn = R[3] * x + R[4] * y + R[5] * z;
+    const double zn = R[6] * x + R[7] * y + R[8] * z;
+    if (xn > 0.0 && fabs(yn) <= SMALL_RATIO * xn && fabs(zn) <= SMALL_RATIO) {
+        rlon = atan_small(yn / xn) * RAD2DEG;
+        rlat = asin_small(zn) * RAD2DEG;
+    } else {
+        rlon = atan2(yn, xn) * RAD2DEG;
+        rlat = asin(zn) * RAD2DEG;
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -361,16 +446,17 @@ struct K1Out {
     double *dbg_rot;
 };
 
-__device__ __forceinline__ double ice_mom2(double T, double QM)
-{   // hydrometeors.py:1277-1299 (Field et al. 2005), n = 3
+// log of the second moment of Field et al. (2005), hydrometeors.py:1277-1299 with n = 3:
+// log Q2 = (log QM' - ln10 * A(T)) / B(T)
+__device__ __forceinline__ double ice_log_mom2(double T, double logQM)
+{
     const double n = 3.0;
     T = T - 273.15;
     double a = 5.065339 - 0.062659 * T - 3.032362 * n + 0.029469 * T * n - 0.000285 * T * T + 0.312550 * n * n +
                0.000204 * T * T * n + 0.003199 * T * n * n - 0.015952 * n * n * n;
-    a = pow(10.0, a);
     double b = 0.476221 - 0.015896 * T + 0.165977 * n + 0.007468 * T * n - 0.000141 * T * T + 0.060366 * n * n +
                0.000079 * T * T * n + 0.000594 * T * n * n - 0.003577 * n * n * n;
-    return pow(QM / a, 1.0 / b);
+    return (logQM - 2.302585092994046 * a) / b;
 }
 
 __device__ __forceinline__ int lut_bin(float x, float lo, float step, int dim)
@@ -384,191 +470,234 @@ __device__ __forceinline__ int lut_bin(float x, float lo, float step, int dim)
 
 extern __shared__ int s_hist[];
 
+// register-resident select (a dynamic index would push the value array to local memory)
+__device__ __forceinline__ float pick_mass(const float (&v)[RADOP_NVP], int var)
+{
+    float r = v[RADOP_VAR_QR];
+    if (var == RADOP_VAR_QS) r = v[RADOP_VAR_QS];
+    if (var == RADOP_VAR_QG) r = v[RADOP_VAR_QG];
+    if (var == RADOP_VAR_QI) r = v[RADOP_VAR_QI];
+    if (var == RADOP_VAR_QH) r = v[RADOP_VAR_QH];
+    return r;
+}
+__device__ __forceinline__ float pick_number(const float (&v)[RADOP_NVP], int var)
+{
+    float r = v[RADOP_VAR_QNR];
+    if (var == RADOP_VAR_QNS) r = v[RADOP_VAR_QNS];
+    if (var == RADOP_VAR_QNG) r = v[RADOP_VAR_QNG];
+    if (var == RADOP_VAR_QNI) r = v[RADOP_VAR_QNI];
+    if (var == RADOP_VAR_QNH) r = v[RADOP_VAR_QNH];
+    return r;
+}
+
+// Persistent blocks: each block walks chunks of 128 consecutive sub-beam gates and keeps
+// one shared-memory histogram of the LUT bins for its whole life (flushed once).
 __global__ void __launch_bounds__(128)
-k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const float *__restrict__ z_t,
-             const float *__restrict__ fields, K1Out o, long long n_sbg)
+k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *__restrict__ geo,
+             const float *__restrict__ z_t, const float *__restrict__ fields, K1Out o, long long n_sbg)
 {
     const int tid = threadIdx.x;
     for (int b = tid; b < cfg.total_bins; b += blockDim.x) s_hist[b] = 0;
     __syncthreads();
+    const unsigned lane = tid & 31;
+    const int ng = cfg.n_gates;
+    const float qnan = __int_as_float(0x7fc00000);
 
-    long long sbg = (long long)blockIdx.x * blockDim.x + tid;
-    const bool in_range = sbg < n_sbg;
-    uint32_t keys[RADOP_NSPECIES_MAX];
+    for (long long base = (long long)blockIdx.x * blockDim.x; base < n_sbg; base += (long long)gridDim.x * blockDim.x) {
+        const long long sbg = base + tid;
+        uint32_t keys[RADOP_NSPECIES_MAX];
 #pragma unroll
-    for (int s = 0; s < RADOP_NSPECIES_MAX; ++s) keys[s] = RADOP_KEY_NONE;
+        for (int s = 0; s < RADOP_NSPECIES_MAX; ++s) keys[s] = RADOP_KEY_NONE;
 
-    if (in_range) {
-        const int ng = cfg.n_gates;
-        int g = (int)(sbg % ng);
-        long long rq = sbg / ng;
-        int q = (int)(rq % cfg.n_sub);
-        int ray = (int)(rq / cfg.n_sub);
-        double az = scan.ray_az[ray] + scan.sub_daz[q];
-        size_t trow = ((size_t)scan.ray_traj[ray] * cfg.n_vert + scan.sub_jv[q]) * ng + g;
-        float s_g = __ldg(scan.traj_s + trow), h_g = __ldg(scan.traj_h + trow), e_g = __ldg(scan.traj_e + trow);
+        if (sbg < n_sbg) {
+            const int g = (int)(sbg % ng);
+            const long long rq = sbg / ng;
+            const int q = (int)(rq % cfg.n_sub);
+            const int ray = (int)(rq / cfg.n_sub);
+            const size_t trow = ((size_t)scan.ray_traj[ray] * cfg.n_vert + scan.sub_jv[q]) * ng + g;
+            const float s_g = __ldg(scan.traj_s + trow), h_g = __ldg(scan.traj_h + trow), e_g = __ldg(scan.traj_e + trow);
 
-        // --- geolocation ------------------------------------------------------------------
-        AzimuthConsts kc;
-        geod_prepare(cfg.radar_lat, az, kc);
-        double lon, lat, rlat, rlon;
-        geod_forward(kc, cfg.radar_lon, (double)s_g, lon, lat);
-        rotate_pole(cfg.rot, lat, lon, rlat, rlon);
-        if (q == cfg.center_sub && o.lat) {
-            o.lat[(size_t)ray * ng + g] = lat;
-            o.lon[(size_t)ray * ng + g] = lon;
-        }
-        // domain check on float64 coordinates against float32 corners (interpolation.py:572-575)
-        if (rlon < (double)cfg.llc[0] || rlat < (double)cfg.llc[1] || rlon > (double)cfg.urc[0] ||
-            rlat > (double)cfg.urc[1])
-            atomicOr(o.flags, 1);
-        // SWIG typemap casts the coordinates to float32 (interpolation_c.i:16)
-        float crlat = (float)rlat, crlon = (float)rlon;
-        float pos0 = __fdiv_rn(__fsub_rn(crlat, cfg.llc[1]), cfg.res[1]);
-        float pos1 = __fdiv_rn(__fsub_rn(crlon, cfg.llc[0]), cfg.res[0]);
-        CellGeom c;
-        locate_cell(z_t, cfg.nz, cfg.ny, cfg.nx, pos0, pos1, h_g, c);
-        o.mask[sbg] = (int8_t)c.status;
-        if (o.dbg_cell) {
-            o.dbg_cell[2 * sbg] = c.iy;
-            o.dbg_cell[2 * sbg + 1] = c.ix;
-            for (int k = 0; k < 4; ++k) o.dbg_level[4 * sbg + k] = c.level[k];
-            o.dbg_status[sbg] = c.status;
-            o.dbg_rot[2 * sbg] = rlat;
-            o.dbg_rot[2 * sbg + 1] = rlon;
-            for (int s = 0; s < cfg.n_species; ++s) { o.dbg_e[sbg * cfg.n_species + s] = -1; o.dbg_t[sbg * cfg.n_species + s] = -1; }
-        }
+            // --- geolocation ------------------------------------------------------------------
+            SubGeo kc;
+            {
+                const double2 *gp = reinterpret_cast<const double2 *>(geo + rq);
+                double2 t0 = __ldg(gp), t1 = __ldg(gp + 1), t2 = __ldg(gp + 2), t3 = __ldg(gp + 3), t4 = __ldg(gp + 4);
+                kc.sinA1 = t0.x; kc.cosA1 = t0.y; kc.sinU1 = t1.x; kc.cosU1 = t1.y; kc.s2s1 = t2.x; kc.c2s1 = t2.y;
+                kc.sinAlpha = t3.x; kc.B = t3.y; kc.C = t4.x; kc.inv_bA = t4.y;
+            }
+            const bool center = (q == cfg.center_sub) && o.lat;
+            double gx, gy, gz, lon = 0.0, lat = 0.0, rlat, rlon;
+            geod_forward(kc, (double)s_g, cfg.cos_lon0, cfg.sin_lon0, cfg.radar_lon, center, gx, gy, gz, lon, lat);
+            rotate_pole(cfg.rot, gx, gy, gz, rlat, rlon);
+            if (center) {
+                o.lat[(size_t)ray * ng + g] = lat;
+                o.lon[(size_t)ray * ng + g] = lon;
+            }
+            // domain check on float64 coordinates against float32 corners (interpolation.py:572-575)
+            if (rlon < (double)cfg.llc[0] || rlat < (double)cfg.llc[1] || rlon > (double)cfg.urc[0] ||
+                rlat > (double)cfg.urc[1])
+                atomicOr(o.flags, 1);
+            // SWIG typemap casts the coordinates to float32 (interpolation_c.i:16)
+            const float crlat = (float)rlat, crlon = (float)rlon;
+            const float pos0 = __fdiv_rn(__fsub_rn(crlat, cfg.llc[1]), cfg.res[1]);
+            const float pos1 = __fdiv_rn(__fsub_rn(crlon, cfg.llc[0]), cfg.res[0]);
+            CellGeom c;
+            locate_cell(z_t, cfg.nz, cfg.ny, cfg.nx, pos0, pos1, h_g, c);
+            o.mask[sbg] = (int8_t)c.status;
+            if (o.dbg_cell) {
+                o.dbg_cell[2 * sbg] = c.iy;
+                o.dbg_cell[2 * sbg + 1] = c.ix;
+                for (int k = 0; k < 4; ++k) o.dbg_level[4 * sbg + k] = c.level[k];
+                o.dbg_status[sbg] = c.status;
+                o.dbg_rot[2 * sbg] = rlat;
+                o.dbg_rot[2 * sbg + 1] = rlon;
+                for (int s = 0; s < cfg.n_species; ++s) { o.dbg_e[sbg * cfg.n_species + s] = -1; o.dbg_t[sbg * cfg.n_species + s] = -1; }
+            }
 
-        float val[RADOP_NVP];
-        const float qnan = __int_as_float(0x7fc00000);
-        uint8_t active = 0;
-        float wind = qnan, sinth = 0.f, vsum = 0.f, nsum = 0.f;
-        if (c.status == 0) {
-            // --- interpolate every variable with the same 8 corner weights ----------------
-            const int nvec = cfg.two_moment ? 4 : 3;
-            const int ys[4] = {c.y0, c.y0, c.y1, c.y1};
-            const int xs[4] = {c.x0, c.x1, c.x0, c.x1};
-            // accumulation order of the reference: col0, col2, col1, col3
-            const int order[4] = {0, 2, 1, 3};
+            float val[RADOP_NVP];
+            uint8_t active = 0;
+            float wind = qnan, sinth = 0.f, vsum = 0.f, nsum = 0.f;
+            if (c.status == 0) {
+                // --- interpolate every variable with the same 8 corner weights ----------------
+                // slots 0..8 are the 1-moment variables: two float4 + one scalar per level;
+                // the 2-moment scheme reads all four float4
+                const int ys[4] = {c.y0, c.y0, c.y1, c.y1};
+                const int xs[4] = {c.x0, c.x1, c.x0, c.x1};
+                const int order[4] = {0, 2, 1, 3};      // accumulation order of the reference
 #pragma unroll
-            for (int oi = 0; oi < 4; ++oi) {
-                const int k = order[oi];
-                size_t colidx = (size_t)ys[k] * cfg.nx + xs[k];
-                const float *zc = z_t + colidx * cfg.nz + c.level[k];
-                float c1 = __ldg(zc), c2 = __ldg(zc + 1);
-                const float4 *f1 = reinterpret_cast<const float4 *>(fields + (colidx * cfg.nz + c.level[k]) * RADOP_NVP);
-                const float4 *f2 = f1 + RADOP_NVP / 4;
+                for (int oi = 0; oi < 4; ++oi) {
+                    const int k = order[oi];
+                    const size_t colidx = (size_t)ys[k] * cfg.nx + xs[k];
+                    const float *zc = z_t + colidx * cfg.nz + c.level[k];
+                    const float c1 = __ldg(zc), c2 = __ldg(zc + 1);
+                    const float den = __fsub_rn(c1, c2), dh = __fsub_rn(h_g, c2);
+                    const float4 *f1 = reinterpret_cast<const float4 *>(fields + (colidx * cfg.nz + c.level[k]) * RADOP_NVP);
+                    const float4 *f2 = f1 + RADOP_NVP / 4;
+                    float w0, w1;      // term = (w0 * v) * w1 in the reference's association
+                    bool v_mid;        // col 1, 2: (w0 * v) * w1 ; col 0, 3: (w0 * w1) * v
+                    if (k == 0) { w0 = __fmul_rn(c.dx, c.dy); w1 = 0.f; v_mid = false; }
+                    else if (k == 2) { w0 = c.x; w1 = c.dy; v_mid = true; }
+                    else if (k == 1) { w0 = c.dx; w1 = c.y; v_mid = true; }
+                    else { w0 = __fmul_rn(c.x, c.y); w1 = 0.f; v_mid = false; }
+                    auto accum = [&](int j, float a, float b) {
+                        float vv = __fsub_rn(b, __fmul_rn(__fdiv_rn(__fsub_rn(b, a), den), dh));
+                        float term = v_mid ? __fmul_rn(__fmul_rn(w0, vv), w1) : __fmul_rn(w0, vv);
+                        val[j] = (oi == 0) ? term : __fadd_rn(val[j], term);
+                    };
 #pragma unroll
-                for (int v4 = 0; v4 < 4; ++v4) {
-                    if (v4 < nvec) {
+                    for (int v4 = 0; v4 < 2; ++v4) {
                         float4 a = __ldg(f1 + v4), b = __ldg(f2 + v4);
-                        float vv[4] = {vlerp(a.x, b.x, c1, c2, h_g), vlerp(a.y, b.y, c1, c2, h_g),
-                                       vlerp(a.z, b.z, c1, c2, h_g), vlerp(a.w, b.w, c1, c2, h_g)};
+                        accum(4 * v4, a.x, b.x); accum(4 * v4 + 1, a.y, b.y);
+                        accum(4 * v4 + 2, a.z, b.z); accum(4 * v4 + 3, a.w, b.w);
+                    }
+                    if (cfg.two_moment) {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            float term;
-                            if (k == 0) term = __fmul_rn(__fmul_rn(c.dx, c.dy), vv[j]);
-                            else if (k == 2) term = __fmul_rn(__fmul_rn(c.x, vv[j]), c.dy);
-                            else if (k == 1) term = __fmul_rn(__fmul_rn(c.dx, vv[j]), c.y);
-                            else term = __fmul_rn(__fmul_rn(c.x, c.y), vv[j]);
-                            val[v4 * 4 + j] = (oi == 0) ? term : __fadd_rn(val[v4 * 4 + j], term);
+                        for (int v4 = 2; v4 < 4; ++v4) {
+                            float4 a = __ldg(f1 + v4), b = __ldg(f2 + v4);
+                            accum(4 * v4, a.x, b.x); accum(4 * v4 + 1, a.y, b.y);
+                            accum(4 * v4 + 2, a.z, b.z); accum(4 * v4 + 3, a.w, b.w);
                         }
+                    } else {
+                        float a = __ldg(reinterpret_cast<const float *>(f1) + 8), b = __ldg(reinterpret_cast<const float *>(f2) + 8);
+                        accum(8, a, b);
                     }
                 }
-            }
-            if (!cfg.two_moment)
-                for (int j = 12; j < 16; ++j) val[j] = 0.f;
-
-            // --- incidence elevation folded to [0, 90] (doppler_scatter.py:173-176) ---------
-            float e = e_g;
-            if (e > 90.f) e = __fsub_rn(180.f, e);
-            if (e < 0.f) e = -e;
-            float T = val[RADOP_VAR_T];
-            const double Td = (double)T;
-
-            // --- species: PSD parameters, LUT bin, analytic Doppler moments -----------------
-            for (int s = 0; s < cfg.n_species; ++s) {
-                const SpeciesDev &S = cfg.sp[s];
-                float QMf = val[S.qm_var];
-                if (!(QMf > 0.f)) continue;
-                active |= (uint8_t)(1u << s);
-                double QM = (double)QMf, lam, n0, ntot_2m = 0.0;
-                float p0, p1;
-                if (S.psd == RADOP_PSD_1MOM_FIXED_N0) {
-                    lam = pow(S.lambda_factor / QM, 1.0 / (4.0 + S.mu));
-                    n0 = S.N0;
-                    p0 = (float)lam; p1 = (float)n0;
-                } else if (S.psd == RADOP_PSD_1MOM_SNOW) {
-                    n0 = 13.5 * (5.65e5 * exp(-0.107 * (Td - 273.15))) / 1000.0;
-                    lam = pow(S.a * n0 * S.lambda_factor / QM, 1.0 / (S.b + 1.0));
-                    p0 = (float)lam; p1 = (float)n0;
-                } else if (S.psd == RADOP_PSD_1MOM_ICE) {
-                    double Q2 = ice_mom2(Td, QM / S.b);
-                    lam = pow(Q2 / QM, 1.0 / (S.b - 2.0));
-                    n0 = 0.0;
-                    p0 = (float)(lam / 1000.0); p1 = QMf;
-                } else {
-                    double QN = (double)val[S.qn_var];
-                    ntot_2m = QN;
-                    double xm = fmin(fmax(QM / (QN + 2.220446049250313e-16), S.x_min), S.x_max);
-                    lam = pow(S.lambda_factor * xm, -S.nu / S.b);
-                    n0 = (S.nu / S.ntot_factor) * QN * pow(lam, (S.mu + 1.0) / S.nu);
-                    n0 = n0 * pow(1000.0, -(1.0 + S.mu));
-                    lam = lam * pow(1000.0, -S.nu);
-                    p0 = (float)lam; p1 = (float)n0;
-                }
-                int ie = lut_bin(e, S.e_min, S.e_step, S.ne);
-                int it = lut_bin(T, S.t_min, S.t_step, S.nt);
-                keys[s] = (uint32_t)(S.bin_base + ie * S.nt + it);
-                o.p0[(size_t)s * n_sbg + sbg] = p0;
-                o.p1[(size_t)s * n_sbg + sbg] = p1;
-                if (o.dbg_e) { o.dbg_e[sbg * cfg.n_species + s] = ie; o.dbg_t[sbg * cfg.n_species + s] = it; }
-                if (cfg.doppler_scheme == 1 && !S.numeric_vn) {
-                    // _Hydrometeor.integrate_V, hydrometeors.py:178-199
-                    double v = S.vel_factor * n0 * S.alpha / S.nu * pow(lam, -(S.beta + S.mu + 1.0) / S.nu);
-                    double n = (S.psd == RADOP_PSD_2MOM)
-                                   ? ntot_2m
-                                   : S.ntot_factor * n0 / S.nu * pow(lam, -(S.mu + 1.0) / S.nu);
-                    vsum += (float)v;
-                    nsum += (float)n;
-                }
-            }
-            // --- wind projection (proj_vel, doppler_scatter.py:30-47; theta is the folded e) --
-            float theta = e * 0.017453292519943295f;
-            float st, ct;
-            sincosf(theta, &st, &ct);
-            double sphi, cphi;
-            sincos(az * DEG2RAD, &sphi, &cphi);
-            wind = (float)(((double)val[RADOP_VAR_U] * sphi + (double)val[RADOP_VAR_V] * cphi) * (double)ct +
-                           (double)val[RADOP_VAR_W] * (double)st);
-            sinth = st;
-        } else {
+                if (!cfg.two_moment) {
 #pragma unroll
-            for (int j = 0; j < RADOP_NVP; ++j) val[j] = qnan;
-        }
-        o.active[sbg] = active;
-        o.wind[sbg] = wind;
-        o.sinth[sbg] = sinth;
-        o.vsum[sbg] = vsum;
-        o.nsum[sbg] = nsum;
-        if (o.vals) {
-            float4 *dst = reinterpret_cast<float4 *>(o.vals + (size_t)sbg * RADOP_NVP);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) dst[j] = make_float4(val[4 * j], val[4 * j + 1], val[4 * j + 2], val[4 * j + 3]);
-        }
-        for (int s = 0; s < cfg.n_species; ++s) o.key[(size_t)s * n_sbg + sbg] = (uint16_t)keys[s];
-    }
+                    for (int j = 9; j < 16; ++j) val[j] = 0.f;
+                }
 
-    // --- warp-aggregated shared-memory histogram of the LUT bins -----------------------------
-    const unsigned lane = tid & 31;
-    for (int s = 0; s < cfg.n_species; ++s) {
-        uint32_t key = keys[s];
-        unsigned peers = __match_any_sync(0xffffffffu, key);
-        if (key != RADOP_KEY_NONE && lane == (unsigned)(__ffs(peers) - 1)) atomicAdd(&s_hist[key], __popc(peers));
+                // --- incidence elevation folded to [0, 90] (doppler_scatter.py:173-176) ---------
+                float e = e_g;
+                if (e > 90.f) e = __fsub_rn(180.f, e);
+                if (e < 0.f) e = -e;
+                const float T = val[RADOP_VAR_T];
+                const double Td = (double)T;
+
+                // --- species: PSD parameters (log domain), LUT bin, analytic Doppler moments ----
+#pragma unroll 1
+                for (int s = 0; s < cfg.n_species; ++s) {
+                    const SpeciesDev &S = cfg.sp[s];
+                    const float QMf = pick_mass(val, S.qm_var);
+                    if (!(QMf > 0.f)) continue;
+                    active |= (uint8_t)(1u << s);
+                    const double lQM = log((double)QMf);
+                    double loglam, logn0 = 0.0, n0 = S.N0, ntot_2m = 0.0;
+                    bool n0_from_log = false;
+                    float p0, p1;
+                    if (S.psd == RADOP_PSD_1MOM_FIXED_N0) {
+                        // lambda = (lambda_factor / QM)^(1/(4+mu)), hydrometeors.py:761-772, 1039-1049
+                        loglam = (S.c_l0 - lQM) * S.c_inv;
+                    } else if (S.psd == RADOP_PSD_1MOM_SNOW) {
+                        // N0 = 13.5 * 5.65e5 * exp(-0.107 (T - 273.15)) / 1000, hydrometeors.py:894-907
+                        logn0 = 8.939515416590824 - 0.107 * (Td - 273.15);      // log(13.5 * 5.65e5 / 1000)
+                        n0_from_log = true;
+                        loglam = (S.c_l0 + logn0 - lQM) * S.c_inv;
+                    } else if (S.psd == RADOP_PSD_1MOM_ICE) {
+                        // lambda = (Q2 / QM)^(1/(b-2)), hydrometeors.py:1320-1339
+                        loglam = (ice_log_mom2(Td, lQM - S.c_l0) - lQM) * S.c_inv - 6.907755278982137;
+                    } else {
+                        // _Hydrometeor.set_psd, hydrometeors.py:224-255
+                        const double QN = (double)pick_number(val, S.qn_var);
+                        ntot_2m = QN;
+                        const double xm = fmin(fmax((double)QMf / (QN + 2.220446049250313e-16), S.x_min), S.x_max);
+                        const double ll0 = S.c_inv * log(S.lambda_factor * xm);
+                        logn0 = log(S.c_q * QN) + S.e_q * ll0 - S.c_ka;
+                        n0_from_log = true;
+                        loglam = ll0 - S.c_kb;
+                    }
+                    const double lam = exp(loglam);
+                    if (n0_from_log) n0 = exp(logn0);
+                    if (S.psd == RADOP_PSD_1MOM_ICE) { p0 = (float)lam; p1 = QMf; }     // lambda / 1000, QM
+                    else { p0 = (float)lam; p1 = (float)n0; }
+                    const int ie = lut_bin(e, S.e_min, S.e_step, S.ne);
+                    const int it = lut_bin(T, S.t_min, S.t_step, S.nt);
+                    keys[s] = (uint32_t)(S.bin_base + ie * S.nt + it);
+                    o.p0[(size_t)s * n_sbg + sbg] = p0;
+                    o.p1[(size_t)s * n_sbg + sbg] = p1;
+                    if (o.dbg_e) { o.dbg_e[sbg * cfg.n_species + s] = ie; o.dbg_t[sbg * cfg.n_species + s] = it; }
+                    if (cfg.doppler_scheme == 1 && !S.numeric_vn) {
+                        // _Hydrometeor.integrate_V, hydrometeors.py:178-199
+                        const double v = S.c_v * n0 * exp(S.e_v * loglam);
+                        const double n = (S.psd == RADOP_PSD_2MOM) ? ntot_2m : S.c_n * n0 * exp(S.e_n * loglam);
+                        vsum += (float)v;
+                        nsum += (float)n;
+                    }
+                }
+                // --- wind projection (proj_vel, doppler_scatter.py:30-47; theta is the folded e) --
+                const float theta = e * 0.017453292519943295f;
+                float st, ct;
+                sincosf(theta, &st, &ct);
+                wind = (float)(((double)val[RADOP_VAR_U] * kc.sinA1 + (double)val[RADOP_VAR_V] * kc.cosA1) * (double)ct +
+                               (double)val[RADOP_VAR_W] * (double)st);
+                sinth = st;
+            } else {
+#pragma unroll
+                for (int j = 0; j < RADOP_NVP; ++j) val[j] = qnan;
+            }
+            o.active[sbg] = active;
+            o.wind[sbg] = wind;
+            o.sinth[sbg] = sinth;
+            o.vsum[sbg] = vsum;
+            o.nsum[sbg] = nsum;
+            if (o.vals) {
+                float4 *dst = reinterpret_cast<float4 *>(o.vals + (size_t)sbg * RADOP_NVP);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dst[j] = make_float4(val[4 * j], val[4 * j + 1], val[4 * j + 2], val[4 * j + 3]);
+            }
+            for (int s = 0; s < cfg.n_species; ++s) o.key[(size_t)s * n_sbg + sbg] = (uint16_t)keys[s];
+        }
+
+        // --- warp-aggregated shared-memory histogram of the LUT bins ---------------------------
+        for (int s = 0; s < cfg.n_species; ++s) {
+            const uint32_t key = keys[s];
+            const unsigned peers = __match_any_sync(0xffffffffu, key);
+            if (key != RADOP_KEY_NONE && lane == (unsigned)(__ffs(peers) - 1)) atomicAdd(&s_hist[key], __popc(peers));
+        }
     }
     __syncthreads();
     for (int b = tid; b < cfg.total_bins; b += blockDim.x) {
-        int cnt = s_hist[b];
+        const int cnt = s_hist[b];
         if (cnt) atomicAdd(&o.hist[b], cnt);
     }
 }

@@ -30,12 +30,21 @@ struct SpeciesDev {
     const float *table;         // [ne][nt][nd][ncol] combined + premultiplied columns
     const float *aux;           // [3][nd]: D, D^nu, D^0.6357
     double a, b, alpha, beta, mu, nu, N0, lambda_factor, vel_factor, ntot_factor, x_min, x_max;
+    // log-domain constants of the PSD parameters (filled by the host, radop_api.cu prepare()):
+    //   log(lambda) = c_inv * (c_l0 [+ log N0(T)] - log QM)          1-mom rain / graupel / snow
+    //   log(lambda) = c_inv * log(lambda_factor * x)                   2-mom (before the mm scaling)
+    double c_l0, c_inv;
+    double c_v, e_v;            // v-moment  = c_v * N0 * lambda^e_v    (_Hydrometeor.integrate_V)
+    double c_n, e_n;            // n-moment  = c_n * N0 * lambda^e_n
+    double c_q, e_q;            // 2-mom N0  = c_q * QN * lambda^e_q * exp(-c_ka); lambda *= exp(-c_kb)
+    double c_ka, c_kb;
 };
 
 struct DevConfig {
     // radar / scan geometry
     int n_rays, n_sub, n_gates, n_vert, center_sub;
     double radar_lat, radar_lon;
+    double cos_lon0, sin_lon0;  // of the radar longitude
     // model grid
     int nz, ny, nx;
     float llc[2], urc[2], res[2];
