@@ -522,7 +522,7 @@ int radop_execute(RadopHandle *h)
     if (ev) CU(h, cudaEventRecord(ev[1], st));
 
     k_scan_bins<<<1, 1024, 0, st>>>(c, h->hist.as<int>(), h->bin_start.as<int>(), h->tile_start.as<int>(),
-                                     h->cost_start.as<long long>(), h->cursor.as<int>(), h->totals.as<long long>());
+                                     h->cost_start.as<int>(), h->cursor.as<int>(), h->totals.as<long long>());
     CU(h, cudaGetLastError()); ++launches;
     k_scatter_pairs<<<(unsigned)((n + 255) / 256), 256, hist_smem, st>>>(c, h->key.as<uint16_t>(), h->p0.as<float>(), h->p1.as<float>(),
                                                                           h->scan.sub_weight, h->cursor.as<int>(), h->rec.as<PairRec>(), n);
@@ -531,7 +531,8 @@ int radop_execute(RadopHandle *h)
 
     K2Args a2;
     a2.hist = h->hist.as<int>(); a2.bin_start = h->bin_start.as<int>(); a2.tile_start = h->tile_start.as<int>();
-    a2.cost_start = h->cost_start.as<long long>(); a2.totals = h->totals.as<long long>();
+    a2.chunk_start = h->cost_start.as<int>(); a2.totals = h->totals.as<long long>();
+    a2.counter = h->flags.as<int>() + 1;
     a2.rec = h->rec.as<PairRec>(); a2.sz_out = h->sz_out.as<float>(); a2.ice_vn = h->ice_vn.as<float2>();
     k_integrate<<<h->k2_blocks, RADOP_TILE_THREADS, h->k2_smem, st>>>(c, a2);
     CU(h, cudaGetLastError()); ++launches;

@@ -706,62 +706,57 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
 // K1b: counting sort by bin
 // ------------------------------------------------------------------------------------------
 // One block.  bin_start = exclusive scan of the counts; tile_start = exclusive scan of
-// ceil(count/TILE); cost_start = exclusive scan of tiles*cost; totals[] = {pairs, tiles, cost, bins}
+// ceil(count/TILE); chunk_start = exclusive scan of ceil(tiles/CHUNK) (the work units the
+// integration kernel hands out dynamically); totals[] = {pairs, tiles, chunks, bins}
 __global__ void k_scan_bins(const __grid_constant__ DevConfig cfg, const int *__restrict__ hist, int *bin_start,
-                            int *tile_start, long long *cost_start, int *cursor, long long *totals)
+                            int *tile_start, int *chunk_start, int *cursor, long long *totals)
 {
-    __shared__ long long s_tot[3];
+    __shared__ int s_tot[3];
     __shared__ int s_warp[3][32];
-    __shared__ long long s_warpc[32];
     const int tid = threadIdx.x, nthr = blockDim.x;
-    if (tid == 0) { s_tot[0] = s_tot[1] = s_tot[2] = 0; }
     __shared__ int s_bins;
-    if (tid == 0) s_bins = 0;
+    if (tid == 0) { s_tot[0] = s_tot[1] = s_tot[2] = 0; s_bins = 0; }
     __syncthreads();
     for (int base = 0; base < cfg.total_bins; base += nthr) {
         int b = base + tid;
-        int cnt = 0, tiles = 0;
-        long long cost = 0;
+        int cnt = 0, tiles = 0, chunks = 0;
         if (b < cfg.total_bins) {
             cnt = hist[b];
             tiles = (cnt + RADOP_TILE - 1) / RADOP_TILE;
-            int s = 0;
-            while (s + 1 < cfg.n_species && b >= cfg.sp[s + 1].bin_base) ++s;
-            cost = (long long)tiles * cfg.sp[s].cost;
+            chunks = (tiles + RADOP_CHUNK - 1) / RADOP_CHUNK;
         }
         // block-wide inclusive scans (warp shuffle + shared)
-        int v0 = cnt, v1 = tiles;
-        long long v2 = cost;
+        int v0 = cnt, v1 = tiles, v2 = chunks;
         const int lane = tid & 31, wid = tid >> 5;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             int t0 = __shfl_up_sync(0xffffffffu, v0, d), t1 = __shfl_up_sync(0xffffffffu, v1, d);
-            long long t2 = __shfl_up_sync(0xffffffffu, v2, d);
+            int t2 = __shfl_up_sync(0xffffffffu, v2, d);
             if (lane >= d) { v0 += t0; v1 += t1; v2 += t2; }
         }
-        if (lane == 31) { s_warp[0][wid] = v0; s_warp[1][wid] = v1; s_warpc[wid] = v2; }
+        if (lane == 31) { s_warp[0][wid] = v0; s_warp[1][wid] = v1; s_warp[2][wid] = v2; }
         __syncthreads();
         if (wid == 0) {
             int nw = nthr >> 5;
             int w0 = lane < nw ? s_warp[0][lane] : 0, w1 = lane < nw ? s_warp[1][lane] : 0;
-            long long w2 = lane < nw ? s_warpc[lane] : 0;
+            int w2 = lane < nw ? s_warp[2][lane] : 0;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 int t0 = __shfl_up_sync(0xffffffffu, w0, d), t1 = __shfl_up_sync(0xffffffffu, w1, d);
-                long long t2 = __shfl_up_sync(0xffffffffu, w2, d);
+                int t2 = __shfl_up_sync(0xffffffffu, w2, d);
                 if (lane >= d) { w0 += t0; w1 += t1; w2 += t2; }
             }
-            s_warp[0][lane] = w0; s_warp[1][lane] = w1; s_warpc[lane] = w2;
+            s_warp[0][lane] = w0; s_warp[1][lane] = w1; s_warp[2][lane] = w2;
         }
         __syncthreads();
         int off0 = (wid ? s_warp[0][wid - 1] : 0), off1 = (wid ? s_warp[1][wid - 1] : 0);
-        long long off2 = (wid ? s_warpc[wid - 1] : 0);
+        int off2 = (wid ? s_warp[2][wid - 1] : 0);
         if (b < cfg.total_bins) {
-            int bs = (int)s_tot[0] + off0 + v0 - cnt;
+            int bs = s_tot[0] + off0 + v0 - cnt;
             bin_start[b] = bs;
             cursor[b] = bs;
-            tile_start[b] = (int)s_tot[1] + off1 + v1 - tiles;
-            cost_start[b] = s_tot[2] + off2 + v2 - cost;
+            tile_start[b] = s_tot[1] + off1 + v1 - tiles;
+            chunk_start[b] = s_tot[2] + off2 + v2 - chunks;
             if (cnt) atomicAdd(&s_bins, 1);
         }
         __syncthreads();
@@ -773,9 +768,9 @@ __global__ void k_scan_bins(const __grid_constant__ DevConfig cfg, const int *__
         __syncthreads();
     }
     if (tid == 0) {
-        bin_start[cfg.total_bins] = (int)s_tot[0];
-        tile_start[cfg.total_bins] = (int)s_tot[1];
-        cost_start[cfg.total_bins] = s_tot[2];
+        bin_start[cfg.total_bins] = s_tot[0];
+        tile_start[cfg.total_bins] = s_tot[1];
+        chunk_start[cfg.total_bins] = s_tot[2];
         totals[0] = s_tot[0];
         totals[1] = s_tot[1];
         totals[2] = s_tot[2];
@@ -835,21 +830,25 @@ k_scatter_pairs(const __grid_constant__ DevConfig cfg, const uint16_t *__restric
 // ------------------------------------------------------------------------------------------
 #define LOG2E 1.4426950408889634f
 
+// nu == 1 on a uniform grid: N(D_k) = N0 D^mu exp(-lambda D_k) is geometric in k, so the
+// integral over one block of RADOP_HBLOCK diameters is a polynomial in r = exp(-lambda dD)
+// evaluated by Horner's rule (one FFMA per diameter and column), re-anchored with one ex2
+// per block.  Rows hold 8 floats (two LDS.128); column 7 is padding and is not computed.
 template <int G>
 __device__ __forceinline__ void integrate_geo8(const float4 *__restrict__ tab, int nd, const float *__restrict__ Dg,
-                                               float dD, const float (&a)[G], float (&acc)[G][8])
+                                               float dD, const float (&a)[G], float (&acc)[G][RADOP_NC])
 {
     float r[G];
 #pragma unroll
     for (int g = 0; g < G; ++g) r[g] = ex2f_approx(a[g] * dD);
     for (int k0 = 0; k0 < nd; k0 += RADOP_HBLOCK) {
-        float P[G][8];
+        float P[G][RADOP_NC];
         {
             float4 t0 = tab[(k0 + RADOP_HBLOCK - 1) * 2], t1 = tab[(k0 + RADOP_HBLOCK - 1) * 2 + 1];
 #pragma unroll
             for (int g = 0; g < G; ++g) {
                 P[g][0] = t0.x; P[g][1] = t0.y; P[g][2] = t0.z; P[g][3] = t0.w;
-                P[g][4] = t1.x; P[g][5] = t1.y; P[g][6] = t1.z; P[g][7] = t1.w;
+                P[g][4] = t1.x; P[g][5] = t1.y; P[g][6] = t1.z;
             }
         }
 #pragma unroll
@@ -860,7 +859,7 @@ __device__ __forceinline__ void integrate_geo8(const float4 *__restrict__ tab, i
                 P[g][0] = fmaf(P[g][0], r[g], t0.x); P[g][1] = fmaf(P[g][1], r[g], t0.y);
                 P[g][2] = fmaf(P[g][2], r[g], t0.z); P[g][3] = fmaf(P[g][3], r[g], t0.w);
                 P[g][4] = fmaf(P[g][4], r[g], t1.x); P[g][5] = fmaf(P[g][5], r[g], t1.y);
-                P[g][6] = fmaf(P[g][6], r[g], t1.z); P[g][7] = fmaf(P[g][7], r[g], t1.w);
+                P[g][6] = fmaf(P[g][6], r[g], t1.z);
             }
         }
         float d0 = __ldg(Dg + k0);
@@ -868,22 +867,23 @@ __device__ __forceinline__ void integrate_geo8(const float4 *__restrict__ tab, i
         for (int g = 0; g < G; ++g) {
             float R = ex2f_approx(a[g] * d0);
 #pragma unroll
-            for (int c = 0; c < 8; ++c) acc[g][c] = fmaf(P[g][c], R, acc[g][c]);
+            for (int c = 0; c < RADOP_NC; ++c) acc[g][c] = fmaf(P[g][c], R, acc[g][c]);
         }
     }
 }
 
-template <int G, int NC>
+// general nu: one ex2 per diameter; NC = columns computed, ROW = floats per table row
+template <int G, int NC, int ROW>
 __device__ __forceinline__ void integrate_gen(const float4 *__restrict__ tab, const float *__restrict__ U, int nd,
                                               const float (&a)[G], float (&acc)[G][NC])
 {
 #pragma unroll 4
     for (int k = 0; k < nd; ++k) {
         float u = U[k];
-        float t[NC];
+        float t[ROW];
 #pragma unroll
-        for (int v = 0; v < NC / 4; ++v) {
-            float4 x = tab[k * (NC / 4) + v];
+        for (int v = 0; v < ROW / 4; ++v) {
+            float4 x = tab[k * (ROW / 4) + v];
             t[4 * v] = x.x; t[4 * v + 1] = x.y; t[4 * v + 2] = x.z; t[4 * v + 3] = x.w;
         }
 #pragma unroll
@@ -941,9 +941,9 @@ __device__ __forceinline__ void integrate_ice1(const float4 *__restrict__ tab, c
 }
 
 struct K2Args {
-    const int *hist, *bin_start, *tile_start;
-    const long long *cost_start;
+    const int *hist, *bin_start, *tile_start, *chunk_start;
     const long long *totals;
+    int *counter;       // dynamic work-unit counter (zeroed before the launch)
     const PairRec *rec;
     float *sz_out;      // [sbg][n_species][8]
     float2 *ice_vn;     // [sbg] numeric fall-speed moments of the ice species
@@ -951,58 +951,58 @@ struct K2Args {
 
 extern __shared__ __align__(128) unsigned char s_k2[];
 
+template <int G>
+__device__ __forceinline__ void store_sz(float *sz_out, int nsp, int s, const PairRec &rec, const float *acc, float pre)
+{
+    float4 *dst = reinterpret_cast<float4 *>(sz_out + ((size_t)rec.sbg * nsp + s) * 8);
+    dst[0] = make_float4(acc[0] * pre, acc[1] * pre, acc[2] * pre, acc[3] * pre);
+    dst[1] = make_float4(acc[4] * pre, acc[5] * pre, acc[6] * pre, 0.f);
+}
+
+// Persistent CTAs pull work units (RADOP_CHUNK consecutive tiles of one LUT bin) from a global
+// counter, the most expensive species first, so that the CTAs drain together whatever the
+// mix of species; the bin's table slice is staged in shared memory by TMA bulk copies.
 __global__ void __launch_bounds__(RADOP_TILE_THREADS)
 k_integrate(const __grid_constant__ DevConfig cfg, K2Args A)
 {
     constexpr int G = RADOP_TILE_G;
     __shared__ uint64_t s_bar;
+    __shared__ int s_unit;
     float4 *s_tab = reinterpret_cast<float4 *>(s_k2);
     const int tid = threadIdx.x;
-    const long long total_cost = A.totals[2];
-    if (total_cost == 0) return;
-    const long long lo = total_cost * blockIdx.x / gridDim.x, hi = total_cost * (blockIdx.x + 1) / gridDim.x;
-    if (lo >= hi) return;
+    const int total_units = (int)A.totals[2];
     const int nbins = cfg.total_bins;
-
-    // first tile whose virtual (cost-weighted) start is >= lo
-    int b;
-    {
-        int l = 0, r = nbins;       // largest b with cost_start[b] <= lo
-        while (r - l > 1) {
-            int m = (l + r) >> 1;
-            if (A.cost_start[m] <= lo) l = m; else r = m;
-        }
-        b = l;
-    }
-    int s = 0;
-    while (s + 1 < cfg.n_species && b >= cfg.sp[s + 1].bin_base) ++s;
-    int j;
-    {
-        long long cs = A.cost_start[b];
-        int cost = cfg.sp[s].cost;
-        j = (int)((lo - cs + cost - 1) / cost);
-    }
+    const int nsp = cfg.n_species;
     if (tid == 0) mbar_init(&s_bar, 1);
-    __syncthreads();
     uint32_t phase = 0;
     int staged_bin = -1;
 
-    while (b < nbins) {
-        int cnt = A.hist[b];
-        int tiles = (cnt + RADOP_TILE - 1) / RADOP_TILE;
-        if (j >= tiles) {
-            ++b; j = 0;
-            while (s + 1 < cfg.n_species && b >= cfg.sp[s + 1].bin_base) ++s;
-            continue;
+    for (;;) {
+        __syncthreads();         // the previous unit (and its reads of s_unit / the slice) is finished
+        if (tid == 0) s_unit = atomicAdd(A.counter, 1);
+        __syncthreads();
+        const int unit = total_units - 1 - s_unit;      // bins of the costliest species come last
+        if (unit < 0) break;
+        int b;
+        {   // bin with chunk_start[b] <= unit < chunk_start[b + 1]
+            int l = 0, r = nbins;
+            while (r - l > 1) {
+                int m = (l + r) >> 1;
+                if (A.chunk_start[m] <= unit) l = m; else r = m;
+            }
+            b = l;
         }
+        int s = 0;
+        while (s + 1 < nsp && b >= cfg.sp[s + 1].bin_base) ++s;
         const SpeciesDev &S = cfg.sp[s];
-        if (A.cost_start[b] + (long long)j * S.cost >= hi) break;
+        const int cnt = A.hist[b];
+        const int tiles = (cnt + RADOP_TILE - 1) / RADOP_TILE;
+        const int j0 = (unit - A.chunk_start[b]) * RADOP_CHUNK, j1 = min(tiles, j0 + RADOP_CHUNK);
 
-        // ---- stage the LUT slice of this bin (TMA bulk copy, mbarrier completion) ----------
+        // ---- stage the LUT slice of this bin (TMA bulk copy, mbarrier completion) --------------
         const int nd = S.nd;
         float *s_aux = reinterpret_cast<float *>(s_k2 + (size_t)nd * S.ncol * 4);
         if (b != staged_bin) {
-            __syncthreads();     // everybody is done with the previous slice
             if (tid == 0) {
                 fence_proxy_async();
                 const uint32_t tab_bytes = (uint32_t)nd * S.ncol * 4;
@@ -1023,90 +1023,65 @@ k_integrate(const __grid_constant__ DevConfig cfg, K2Args A)
             staged_bin = b;
         }
 
-        // ---- this thread's G pairs -----------------------------------------------------------
-        const int first = A.bin_start[b] + j * RADOP_TILE;
-        const int n_here = min(RADOP_TILE, cnt - j * RADOP_TILE);
-        PairRec rec[G];
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
-            int i = tid + g * RADOP_TILE_THREADS;
-            if (i < n_here) rec[g] = A.rec[first + i];
-            else { rec[g].sbg = 0xFFFFFFFFu; rec[g].p0 = 0.f; rec[g].p1 = 0.f; rec[g].w = 0.f; }
-        }
-        const int nsp = cfg.n_species;
-        if (S.mode == MODE_GEO8) {
-            float a[G], acc[G][8];
+        for (int j = j0; j < j1; ++j) {
+            // ---- this thread's G pairs -------------------------------------------------------
+            const int first = A.bin_start[b] + j * RADOP_TILE;
+            const int n_here = min(RADOP_TILE, cnt - j * RADOP_TILE);
+            PairRec rec[G];
 #pragma unroll
             for (int g = 0; g < G; ++g) {
-                a[g] = -LOG2E * rec[g].p0;
-#pragma unroll
-                for (int c = 0; c < 8; ++c) acc[g][c] = 0.f;
+                int i = tid + g * RADOP_TILE_THREADS;
+                if (i < n_here) rec[g] = A.rec[first + i];
+                else { rec[g].sbg = 0xFFFFFFFFu; rec[g].p0 = 0.f; rec[g].p1 = 0.f; rec[g].w = 0.f; }
             }
-            integrate_geo8<G>(s_tab, nd, S.aux, S.dD_geo, a, acc);
+            if (S.mode == MODE_GEO8 || S.mode == MODE_GEN8) {
+                float a[G], acc[G][RADOP_NC];
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                if (rec[g].sbg == 0xFFFFFFFFu) continue;
-                float pre = rec[g].p1 * rec[g].w;
-                float4 *dst = reinterpret_cast<float4 *>(A.sz_out + ((size_t)rec[g].sbg * nsp + s) * 8);
-                dst[0] = make_float4(acc[g][0] * pre, acc[g][1] * pre, acc[g][2] * pre, acc[g][3] * pre);
-                dst[1] = make_float4(acc[g][4] * pre, acc[g][5] * pre, acc[g][6] * pre, acc[g][7] * pre);
-            }
-        } else if (S.mode == MODE_GEN8) {
-            float a[G], acc[G][8];
+                for (int g = 0; g < G; ++g) {
+                    a[g] = -LOG2E * rec[g].p0;
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                a[g] = -LOG2E * rec[g].p0;
+                    for (int c = 0; c < RADOP_NC; ++c) acc[g][c] = 0.f;
+                }
+                if (S.mode == MODE_GEO8) integrate_geo8<G>(s_tab, nd, S.aux, S.dD_geo, a, acc);
+                else integrate_gen<G, RADOP_NC, 8>(s_tab, s_aux, nd, a, acc);
 #pragma unroll
-                for (int c = 0; c < 8; ++c) acc[g][c] = 0.f;
-            }
-            integrate_gen<G, 8>(s_tab, s_aux, nd, a, acc);
+                for (int g = 0; g < G; ++g)
+                    if (rec[g].sbg != 0xFFFFFFFFu) store_sz<G>(A.sz_out, nsp, s, rec[g], acc[g], rec[g].p1 * rec[g].w);
+            } else if (S.mode == MODE_GEN12) {
+                float a[G], acc[G][9];
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                if (rec[g].sbg == 0xFFFFFFFFu) continue;
-                float pre = rec[g].p1 * rec[g].w;
-                float4 *dst = reinterpret_cast<float4 *>(A.sz_out + ((size_t)rec[g].sbg * nsp + s) * 8);
-                dst[0] = make_float4(acc[g][0] * pre, acc[g][1] * pre, acc[g][2] * pre, acc[g][3] * pre);
-                dst[1] = make_float4(acc[g][4] * pre, acc[g][5] * pre, acc[g][6] * pre, acc[g][7] * pre);
-            }
-        } else if (S.mode == MODE_GEN12) {
-            float a[G], acc[G][12];
+                for (int g = 0; g < G; ++g) {
+                    a[g] = -LOG2E * rec[g].p0;
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                a[g] = -LOG2E * rec[g].p0;
+                    for (int c = 0; c < 9; ++c) acc[g][c] = 0.f;
+                }
+                integrate_gen<G, 9, 12>(s_tab, s_aux, nd, a, acc);
 #pragma unroll
-                for (int c = 0; c < 12; ++c) acc[g][c] = 0.f;
-            }
-            integrate_gen<G, 12>(s_tab, s_aux, nd, a, acc);
+                for (int g = 0; g < G; ++g) {
+                    if (rec[g].sbg == 0xFFFFFFFFu) continue;
+                    const float n0 = rec[g].p1;
+                    store_sz<G>(A.sz_out, nsp, s, rec[g], acc[g], n0 * rec[g].w);
+                    A.ice_vn[rec[g].sbg] = make_float2(acc[g][7] * n0, acc[g][8] * n0);
+                }
+            } else {   // MODE_ICE1
+                float lam[G], acc[G][12];
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                if (rec[g].sbg == 0xFFFFFFFFu) continue;
-                float n0 = rec[g].p1, pre = n0 * rec[g].w;
-                float4 *dst = reinterpret_cast<float4 *>(A.sz_out + ((size_t)rec[g].sbg * nsp + s) * 8);
-                dst[0] = make_float4(acc[g][0] * pre, acc[g][1] * pre, acc[g][2] * pre, acc[g][3] * pre);
-                dst[1] = make_float4(acc[g][4] * pre, acc[g][5] * pre, acc[g][6] * pre, 0.f);
-                A.ice_vn[rec[g].sbg] = make_float2(acc[g][7] * n0, acc[g][8] * n0);
-            }
-        } else {   // MODE_ICE1
-            float lam[G], acc[G][12];
+                for (int g = 0; g < G; ++g) {
+                    lam[g] = (rec[g].sbg == 0xFFFFFFFFu) ? 1.0f : rec[g].p0;
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                lam[g] = (rec[g].sbg == 0xFFFFFFFFu) ? 1.0f : rec[g].p0;
+                    for (int c = 0; c < 12; ++c) acc[g][c] = 0.f;
+                }
+                integrate_ice1<G>(s_tab, s_aux, nd, S.aux, S.dD_geo, lam, acc);
 #pragma unroll
-                for (int c = 0; c < 12; ++c) acc[g][c] = 0.f;
-            }
-            integrate_ice1<G>(s_tab, s_aux, nd, S.aux, S.dD_geo, lam, acc);
-#pragma unroll
-            for (int g = 0; g < G; ++g) {
-                if (rec[g].sbg == 0xFFFFFFFFu) continue;
-                // N0 renormalised so that the mass integral equals QM (hydrometeors.py:1330-1339)
-                float n0 = rec[g].p1 / acc[g][9], pre = n0 * rec[g].w;
-                float4 *dst = reinterpret_cast<float4 *>(A.sz_out + ((size_t)rec[g].sbg * nsp + s) * 8);
-                dst[0] = make_float4(acc[g][0] * pre, acc[g][1] * pre, acc[g][2] * pre, acc[g][3] * pre);
-                dst[1] = make_float4(acc[g][4] * pre, acc[g][5] * pre, acc[g][6] * pre, 0.f);
-                A.ice_vn[rec[g].sbg] = make_float2(acc[g][7] * n0, acc[g][8] * n0);
+                for (int g = 0; g < G; ++g) {
+                    if (rec[g].sbg == 0xFFFFFFFFu) continue;
+                    // N0 renormalised so that the mass integral equals QM (hydrometeors.py:1330-1339)
+                    const float n0 = rec[g].p1 / acc[g][9];
+                    store_sz<G>(A.sz_out, nsp, s, rec[g], acc[g], n0 * rec[g].w);
+                    A.ice_vn[rec[g].sbg] = make_float2(acc[g][7] * n0, acc[g][8] * n0);
+                }
             }
         }
-        ++j;
     }
 }
 

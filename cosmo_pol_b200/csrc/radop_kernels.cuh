@@ -9,6 +9,8 @@
 #define RADOP_TILE_G 4          // (sub-beam gate, species) pairs per thread
 #define RADOP_TILE (RADOP_TILE_THREADS * RADOP_TILE_G)
 #define RADOP_HBLOCK 32         // diameters per Horner block (re-anchoring period)
+#define RADOP_CHUNK 4           // tiles per dynamically scheduled work unit of the integration kernel
+#define RADOP_NC 7              // combined columns that carry data (the 8th of a row is padding)
 #define RADOP_KEY_NONE 0xFFFFu
 
 // integration modes of the PSD x LUT contraction
