@@ -24,7 +24,7 @@ EXPORTS = ['radop_abi_version', 'radop_create', 'radop_destroy', 'radop_last_err
            'radop_upload_grid', 'radop_upload_field', 'radop_upload_lut', 'radop_simulate', 'radop_stage_scan',
            'radop_execute', 'radop_fetch', 'radop_synchronize', 'radop_device_outputs', 'radop_get_stream',
            'radop_get_stats', 'radop_enable_timing', 'radop_debug_indices', 'radop_measure_fp32_peak',
-           'radop_get_all_radar_pts']
+           'radop_get_all_radar_pts', 'radop_selftest_division']
 
 (RADOP_OK, RADOP_ERR_CUDA, RADOP_ERR_ARG, RADOP_ERR_OUT_OF_DOMAIN, RADOP_ERR_LUT, RADOP_ERR_STATE,
  RADOP_ERR_UNSUPPORTED) = range(7)
@@ -106,6 +106,7 @@ def load_library():
     lib.radop_enable_timing.argtypes = [C.c_void_p, C.c_int]
     lib.radop_debug_indices.argtypes = [C.c_void_p] + [C.c_void_p] * 7
     lib.radop_measure_fp32_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+    lib.radop_selftest_division.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.radop_get_all_radar_pts.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     if lib.radop_abi_version() != RADOP_ABI_VERSION:
@@ -358,6 +359,11 @@ class Engine(object):
         nr, ng = C.c_int64(), C.c_int64()
         self._check(self.lib.radop_device_outputs(self.h, C.byref(p), C.byref(nr), C.byref(ng)))
         return p.value, nr.value, ng.value
+
+    def selftest_division(self, n_samples=1 << 26, seed=1):
+        bad = C.c_uint64(0)
+        self._check(self.lib.radop_selftest_division(self.h, C.c_uint64(n_samples), C.c_uint64(seed), C.byref(bad)))
+        return int(bad.value)
 
     def measure_fp32_peak(self):
         v = C.c_double()

@@ -56,6 +56,7 @@ struct RadopHandle_ {
     float llc[2], urc[2], res[2];
     double rot[9];
     uint32_t var_mask = 0;
+    int z_strict = 0;
     DevBuf z_t, fields, stage;
     LutHost lut[RADOP_NSPECIES_MAX];   // indexed by RADOP_SP_*
     // scan
@@ -193,6 +194,16 @@ int radop_upload_grid(RadopHandle *h, int nz, int ny, int nx, const float *zleve
     CU(h, cudaMemcpyAsync(h->stage.p, zlevels, n * 4, cudaMemcpyHostToDevice, h->stream));
     k_pack_zlevels<<<h->n_sm * 8, 256, 0, h->stream>>>(h->stage.as<float>(), h->z_t.as<float>(), nz, ny, nx);
     CU(h, cudaGetLastError());
+    {   // strictly descending columns allow the fast column search of k_interp_psd
+        CU(h, h->flags.reserve(16));
+        CU(h, cudaMemsetAsync(h->flags.p, 0, 16, h->stream));
+        k_check_columns<<<h->n_sm * 8, 256, 0, h->stream>>>(h->z_t.as<float>(), nz, (size_t)ny * nx, h->flags.as<int>());
+        CU(h, cudaGetLastError());
+        int bad = 0;
+        CU(h, cudaMemcpyAsync(&bad, h->flags.p, 4, cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));
+        h->z_strict = bad ? 0 : 1;
+    }
     CU(h, cudaStreamSynchronize(h->stream));
     h->nz = nz; h->ny = ny; h->nx = nx;
     for (int i = 0; i < 2; ++i) { h->llc[i] = llc[i]; h->urc[i] = urc[i]; h->res[i] = res[i]; }
@@ -362,6 +373,7 @@ static int prepare(RadopHandle *h)
     for (int i = 0; i < 2; ++i) { c.llc[i] = h->llc[i]; c.urc[i] = h->urc[i]; c.res[i] = h->res[i]; }
     memcpy(c.rot, h->rot, sizeof c.rot);
     c.var_mask = h->var_mask;
+    c.z_strict = h->z_strict;
     c.n_species = p.n_species;
     c.two_moment = p.two_moment; c.doppler_scheme = p.doppler_scheme; c.with_attenuation = p.with_attenuation;
     c.sensitivity_mode = p.sensitivity_mode; c.output_model_vars = p.output_model_vars; c.keep_debug = p.keep_debug;
@@ -733,6 +745,26 @@ int radop_measure_fp32_peak(RadopHandle *h, double *tflops)
     cudaEventDestroy(b);
     sink.release();
     *tflops = best;
+    return RADOP_OK;
+}
+
+int radop_selftest_division(RadopHandle *h, uint64_t n_samples, uint64_t seed, uint64_t *mismatches)
+{
+    if (!h || !mismatches) return RADOP_ERR_ARG;
+    CU(h, cudaSetDevice(h->device));
+    DevBuf cnt;
+    CU(h, cnt.reserve(8));
+    CU(h, cudaMemsetAsync(cnt.p, 0, 8, h->stream));
+    for (int mode = 0; mode < 3; ++mode) {
+        k_selftest_division<<<h->n_sm * 8, 256, 0, h->stream>>>((unsigned long long)n_samples, (unsigned long long)seed + mode, mode,
+                                                               cnt.as<unsigned long long>());
+        CU(h, cudaGetLastError());
+    }
+    unsigned long long bad = 0;
+    CU(h, cudaMemcpyAsync(&bad, cnt.p, 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    cnt.release();
+    *mismatches = bad;
     return RADOP_OK;
 }
 

@@ -314,6 +314,70 @@ __device__ __forceinline__ int column_search(const float *__restrict__ col, int 
     return hi;
 }
 
+// Correctly rounded float32 quotient n / den from y = RN(1 / den) (Markstein's theorem:
+// q0 = RN(n y) is within one ulp, r = n - den q0 is exact in an FMA, RN(q0 + r y) is the
+// correctly rounded quotient).  One reciprocal serves all the variables interpolated in a
+// column.  Zero, infinite, NaN and tiny quotients (where the residual could underflow) take
+// the IEEE division instead; radop_selftest_division checks the equivalence on the GPU.
+__device__ __forceinline__ bool div_den_safe(float den)
+{   // the residual n - den q0 is exact when |den| >= 2^-3 and |q| >= 1e-30 (no bits below 2^-149)
+    const float ad = fabsf(den);
+    return ad >= 0.125f && ad <= 1e15f;
+}
+__device__ __forceinline__ float div_shared_rcp(float n, float den, float y, bool den_safe)
+{
+    const float q0 = __fmul_rn(n, y);
+    const float r = __fmaf_rn(-den, q0, n);
+    float q = __fmaf_rn(r, y, q0);
+    const float aq = fabsf(q);
+    if (!den_safe || !(aq <= 1e30f) || (aq < 1e-30f && n != 0.f)) q = __fdiv_rn(n, den);
+    return q;
+}
+
+__global__ void k_selftest_division(unsigned long long n, unsigned long long seed, int mode,
+                                    unsigned long long *mismatch)
+{
+    unsigned long long bad = 0;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        // splitmix64
+        unsigned long long z = seed + (i + 1) * 0x9E3779B97F4A7C15ull;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        unsigned a = (unsigned)z, b = (unsigned)(z >> 32);
+        float num, den;
+        if (mode == 0) {            // arbitrary bit patterns
+            num = __uint_as_float(a);
+            den = __uint_as_float(b);
+        } else if (mode == 1) {     // level spacings 1 .. 4096 m, field differences of any magnitude
+            den = __uint_as_float(0x3f800000u + (b % (12u << 23)));
+            num = __uint_as_float(a);
+        } else {                    // numerators with few significant bits, zeros, exact multiples
+            den = __uint_as_float(0x3f800000u + (b % (12u << 23)));
+            unsigned k = a & 0xffu;
+            num = (k == 0) ? 0.f : den * (float)((int)(a >> 8 & 0xfff) - 2048) * exp2f((float)((int)(k % 80) - 40));
+        }
+        float y = __frcp_rn(den);
+        float q1 = div_shared_rcp(num, den, y, div_den_safe(den)), q2 = __fdiv_rn(num, den);
+        bool same = (__float_as_uint(q1) == __float_as_uint(q2)) || (isnan(q1) && isnan(q2));
+        if (!same) ++bad;
+    }
+    if (bad) atomicAdd(mismatch, bad);
+}
+
+// flag[0] |= 1 when some column of z_t is not strictly descending (the fast search below
+// is then replaced by the reference's probe sequence)
+__global__ void k_check_columns(const float *__restrict__ z_t, int nz, size_t ncol, int *flag)
+{
+    for (size_t c = blockIdx.x * (size_t)blockDim.x + threadIdx.x; c < ncol; c += (size_t)gridDim.x * blockDim.x) {
+        const float *col = z_t + c * nz;
+        bool ok = true;
+        for (int l = 0; l + 1 < nz; ++l) ok = ok && (col[l] > col[l + 1]);
+        if (!ok) atomicOr(flag, 1);
+    }
+}
+
 struct CellGeom {
     int iy, ix;         // lat index, lon index of the lower-left neighbour
     int y0, y1, x0, x1; // memory-safe (clamped) neighbour indices
@@ -322,9 +386,13 @@ struct CellGeom {
     int level[4];       // upper level used in each neighbour column
 };
 
-// pos0 / pos1 are the float32 grid positions ((coord - llc)/res evaluated in float32)
+// pos0 / pos1 are the float32 grid positions ((coord - llc)/res evaluated in float32).
+// strict: every column of z_t is strictly descending (checked at upload).  The reference's
+// binary search (interpolation_c.c:108-135) then returns the largest index i <= nz-2 with
+// col[i] >= h (an exact match is always probed, the last level never is), which the four
+// neighbour columns find together in ceil(log2(nz-1)) rounds of independent loads.
 __device__ __forceinline__ void locate_cell(const float *__restrict__ z_t, int nz, int ny, int nx, float pos0,
-                                            float pos1, float h, CellGeom &c)
+                                            float pos1, float h, bool strict, CellGeom &c)
 {
     c.iy = (int)floorf(pos0);
     c.ix = (int)floorf(pos1);
@@ -348,6 +416,30 @@ __device__ __forceinline__ void locate_cell(const float *__restrict__ z_t, int n
     c.level[0] = c.level[1] = c.level[2] = c.level[3] = -1;
     if (!(topo < h)) { c.status = -1; return; }
     c.status = 0;
+    if (strict) {
+        const float top0 = __ldg(col[0]), top1 = __ldg(col[1]), top2 = __ldg(col[2]), top3 = __ldg(col[3]);
+        if (h > top0 || h > top1 || h > top2 || h > top3) { c.status = 1; return; }
+        const float bot[4] = {t0, t1, t2, t3};
+        int idx[4] = {0, 0, 0, 0};
+        int step = 1;
+        while (2 * step <= nz - 2) step *= 2;
+        for (; step > 0; step >>= 1) {
+            float v[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) v[k] = __ldg(col[k] + min(idx[k] + step, nz - 2));
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (idx[k] + step <= nz - 2 && v[k] >= h) idx[k] += step;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            int i = idx[k];
+            if (h < bot[k]) i = nz - 3;
+            else if (i == nz - 2) i--;
+            c.level[k] = i;
+        }
+        return;
+    }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         int idx = column_search(col[k], nz, h);
@@ -510,10 +602,11 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
         for (int s = 0; s < RADOP_NSPECIES_MAX; ++s) keys[s] = RADOP_KEY_NONE;
 
         if (sbg < n_sbg) {
-            const int g = (int)(sbg % ng);
-            const long long rq = sbg / ng;
-            const int q = (int)(rq % cfg.n_sub);
-            const int ray = (int)(rq / cfg.n_sub);
+            // n_sbg < 2^32 (checked by the host): 32-bit index arithmetic
+            const unsigned rq = (unsigned)sbg / (unsigned)ng;
+            const int g = (int)((unsigned)sbg - rq * (unsigned)ng);
+            const int ray = (int)(rq / (unsigned)cfg.n_sub);
+            const int q = (int)(rq - (unsigned)ray * (unsigned)cfg.n_sub);
             const size_t trow = ((size_t)scan.ray_traj[ray] * cfg.n_vert + scan.sub_jv[q]) * ng + g;
             const float s_g = __ldg(scan.traj_s + trow), h_g = __ldg(scan.traj_h + trow), e_g = __ldg(scan.traj_e + trow);
 
@@ -542,7 +635,7 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
             const float pos0 = __fdiv_rn(__fsub_rn(crlat, cfg.llc[1]), cfg.res[1]);
             const float pos1 = __fdiv_rn(__fsub_rn(crlon, cfg.llc[0]), cfg.res[0]);
             CellGeom c;
-            locate_cell(z_t, cfg.nz, cfg.ny, cfg.nx, pos0, pos1, h_g, c);
+            locate_cell(z_t, cfg.nz, cfg.ny, cfg.nx, pos0, pos1, h_g, cfg.z_strict != 0, c);
             o.mask[sbg] = (int8_t)c.status;
             if (o.dbg_cell) {
                 o.dbg_cell[2 * sbg] = c.iy;
@@ -571,6 +664,8 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                     const float *zc = z_t + colidx * cfg.nz + c.level[k];
                     const float c1 = __ldg(zc), c2 = __ldg(zc + 1);
                     const float den = __fsub_rn(c1, c2), dh = __fsub_rn(h_g, c2);
+                    const float rden = __frcp_rn(den);
+                    const bool den_safe = div_den_safe(den);
                     const float4 *f1 = reinterpret_cast<const float4 *>(fields + (colidx * cfg.nz + c.level[k]) * RADOP_NVP);
                     const float4 *f2 = f1 + RADOP_NVP / 4;
                     float w0, w1;      // term = (w0 * v) * w1 in the reference's association
@@ -580,7 +675,7 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                     else if (k == 1) { w0 = c.dx; w1 = c.y; v_mid = true; }
                     else { w0 = __fmul_rn(c.x, c.y); w1 = 0.f; v_mid = false; }
                     auto accum = [&](int j, float a, float b) {
-                        float vv = __fsub_rn(b, __fmul_rn(__fdiv_rn(__fsub_rn(b, a), den), dh));
+                        float vv = __fsub_rn(b, __fmul_rn(div_shared_rcp(__fsub_rn(b, a), den, rden, den_safe), dh));
                         float term = v_mid ? __fmul_rn(__fmul_rn(w0, vv), w1) : __fmul_rn(w0, vv);
                         val[j] = (oi == 0) ? term : __fadd_rn(val[j], term);
                     };

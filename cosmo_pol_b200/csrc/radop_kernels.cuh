@@ -55,6 +55,7 @@ struct DevConfig {
     // microphysics
     int n_species, total_bins;
     int two_moment, doppler_scheme, with_attenuation, sensitivity_mode;
+    int z_strict;               // every z-level column is strictly descending (fast column search)
     int output_model_vars, keep_debug, ice_numeric;   // ice_numeric: species index with numeric v,n or -1
     float wavelength, k_squared, radial_res;
     float sens0, sens1;

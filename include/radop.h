@@ -207,6 +207,10 @@ int radop_debug_indices(RadopHandle *h, int32_t *cell, int32_t *level, int32_t *
 /* Measured FP32 FMA throughput of this GPU [TFLOP/s] (roofline denominator). */
 int radop_measure_fp32_peak(RadopHandle *h, double *tflops);
 
+/* Self-test of the shared-reciprocal float32 division used by the interpolation kernel
+ * against the IEEE division (3 x n_samples seeded operand pairs); *mismatches must be 0. */
+int radop_selftest_division(RadopHandle *h, uint64_t n_samples, uint64_t seed, uint64_t *mismatches);
+
 /* ---- compatibility shims over the kernels (same data contract as the SWIG
  *      functions they replace; used for A/B tests against the gcc build) -------- */
 /* interpolation_c.c:12  get_all_radar_pts(len, coords[n][2], heights[n], data, z, llc, res) */

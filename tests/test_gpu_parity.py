@@ -58,6 +58,47 @@ def test_interp_shim_bit_exact_against_reference_c():
     eng.close()
 
 
+def test_shared_reciprocal_division_is_ieee():
+    """The interpolation kernel divides by a reciprocal shared by all variables of a column
+    (Markstein correction); it must equal the IEEE float32 division bit for bit."""
+    from cosmo_pol_b200._abi import Engine
+    eng = Engine(0)
+    assert eng.selftest_division(1 << 28, seed=20261104) == 0
+    eng.close()
+
+
+def test_non_monotone_columns_take_reference_search():
+    """Columns that are not strictly descending disable the fast column search: the kernel then
+    follows the reference's probe sequence and still matches the reference C bit for bit."""
+    import copy as _copy
+    op, model, luts = make_operator(CONF_1MOM)
+    z = model['T'].attributes['z-levels'].copy()
+    z[5] = z[6]                      # two equal levels everywhere
+    z[11, ::3] = z[9, ::3] + 1.0     # and some inverted ones
+    attrs = dict(model['T'].attributes)
+    attrs['z-levels'] = z
+    bad = {k: type(v)(k, v.data, attrs) for k, v in model.items()}
+    op.load_model(bad)
+    eng = op._prepare_engine(keep_debug=True)
+    az, el = np.array([33.0, 214.0]), np.array([2.0, 12.0])
+    scan = op.build_scan(az, el)
+    eng.simulate(scan)
+    dbg = eng.debug_indices(scan)
+    pm, pl = plain(bad, luts)
+    cfg = oracle_cfg(op)
+    for r in range(2):
+        ref = O.simulate_ray(pm, pl, cfg, az[r], el[r], accum='f64', debug=True)
+        for q, sub in enumerate(ref['subs']):
+            out, cell, level, status = sub['dbg']
+            assert np.array_equal(dbg['level'][r, q], level), (r, q)
+            assert np.array_equal(dbg['status'][r, q], status), (r, q)
+            for i, name in enumerate(dbg['var_names']):
+                a, b = dbg['values'][r, q, :, i], sub['values'][name]
+                assert np.array_equal(np.isnan(a), np.isnan(b)), (r, q, name)
+                ok = np.isfinite(b) & np.isfinite(a)
+                assert np.array_equal(a[ok].view(np.uint32), b[ok].view(np.uint32)), (r, q, name)
+
+
 @pytest.mark.parametrize('scheme,freq', [('1mom', 5.6), ('2mom', 9.41)])
 def test_indices_and_interpolated_values_bit_exact(scheme, freq):
     """Grid cell, level and LUT-bin indices bit-exact; interpolated variables bit-exact."""
