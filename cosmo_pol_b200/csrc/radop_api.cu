@@ -38,6 +38,7 @@ struct LutHost {
     bool loaded = false;
     int ne = 0, nt = 0, nd = 0, mode = 0, ncol = 8, cost = 9;
     float e_min = 0, e_step = 1, t_min = 0, t_step = 1, dD_geo = 0, dD_ref = 0;
+    double dD_d = 0;
     RadopSpecies packed_for;   // constants the table was premultiplied with
     DevBuf table, aux;
 };
@@ -253,7 +254,8 @@ int radop_upload_lut(RadopHandle *h, int species, const double *value_table, int
     for (int k = 0; k < nd; ++k) dev = std::max(dev, fabs((double)d_axis[k] - (d0 + k * dD)));
     bool uniform = dev <= 4e-7 * std::max(1.0, fabs((double)d_axis[nd - 1])) + 1e-12;
     if (S->psd == RADOP_PSD_1MOM_ICE) {
-        if (!uniform) return h->fail(RADOP_ERR_LUT, "1-mom ice needs a uniform diameter axis");
+        if (!uniform || (nd % RADOP_HBLOCK) != 0)
+            return h->fail(RADOP_ERR_LUT, "1-mom ice needs a uniform diameter axis with a multiple of 32 bins");
         L.mode = MODE_ICE1; L.ncol = 12; L.cost = 15;
     } else if (S->numeric_vn) {
         L.mode = MODE_GEN12; L.ncol = 12; L.cost = 15;
@@ -265,6 +267,7 @@ int radop_upload_lut(RadopHandle *h, int species, const double *value_table, int
     L.ne = ne; L.nt = nt; L.nd = nd;
     L.e_min = e_min; L.e_step = e_step; L.t_min = t_min; L.t_step = t_step;
     L.dD_geo = (float)dD;
+    L.dD_d = dD;
     L.dD_ref = d_axis[1] - d_axis[0];
     L.packed_for = *S;
     size_t rows = (size_t)ne * nt * nd;
@@ -397,7 +400,7 @@ static int prepare(RadopHandle *h)
         species_vars(S.species, &d.qm_var, &d.qn_var);
         need |= (1u << d.qm_var);
         if (S.psd == RADOP_PSD_2MOM) need |= (1u << d.qn_var);
-        d.dD_geo = L.dD_geo; d.dD_ref = L.dD_ref;
+        d.dD_geo = L.dD_geo; d.dD_ref = L.dD_ref; d.dD_d = L.dD_d;
         d.table = L.table.as<float>(); d.aux = L.aux.as<float>();
         d.a = S.a; d.b = S.b; d.alpha = S.alpha; d.beta = S.beta; d.mu = S.mu; d.nu = S.nu; d.N0 = S.N0;
         d.lambda_factor = S.lambda_factor; d.vel_factor = S.vel_factor; d.ntot_factor = S.ntot_factor;

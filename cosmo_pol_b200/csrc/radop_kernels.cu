@@ -925,67 +925,80 @@ k_scatter_pairs(const __grid_constant__ DevConfig cfg, const uint16_t *__restric
 // ------------------------------------------------------------------------------------------
 #define LOG2E 1.4426950408889634f
 
-// nu == 1 on a uniform grid: N(D_k) = N0 D^mu exp(-lambda D_k) is geometric in k, so the
-// integral over one block of RADOP_HBLOCK diameters is a polynomial in r = exp(-lambda dD)
-// evaluated by Horner's rule (one FFMA per diameter and column), re-anchored with one ex2
-// per block.  Rows hold 8 floats (two LDS.128); column 7 is padding and is not computed.
-template <int G>
-__device__ __forceinline__ void integrate_geo8(const float4 *__restrict__ tab, int nd, const float *__restrict__ Dg,
-                                               float dD, const float (&a)[G], float (&acc)[G][RADOP_NC])
+// Packed FP32 (sm_100 FFMA2 / FMUL2).  Two (sub-beam gate, species) pairs of a thread share one
+// 64-bit register pair, the table value enters as a broadcast 32-bit operand.  Every source
+// operand is then an (even, odd) register pair or a scalar, which keeps the register-file
+// banks balanced: scalar FFMA with three distinct sources measured 65 % of the FMA peak here,
+// the packed form 84 % (scripts/probes/probe_ffma.cu), and it needs half the issue slots.
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c)
 {
-    float r[G];
+    unsigned long long ra, rb, rc, rd;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+    float2 d;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b)
+{
+    unsigned long long ra, rb, rd;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+    float2 d;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
+}
+__device__ __forceinline__ float2 bcast2(float x) { return make_float2(x, x); }
+
+// nu == 1 on a uniform grid: N(D_k) = N0 D_k^mu exp(-lambda D_k) is geometric in k, so the
+// integral  sum_k tab[k][c] exp(-lambda D_k) = exp(-lambda D_0) sum_k tab[k][c] rt^k,
+// rt = exp(-lambda dD), is ONE Horner recurrence over all nd diameters: one FMA per diameter
+// and column, no exponential in the loop, nothing but the running sums in registers.
+// The multiplier is the float32 rounding r of rt, except on one row of every RADOP_HBLOCK rows
+// where it is rb = r (rt / r)^HBLOCK (formed in float64 by the caller): the product of the
+// multipliers over a block equals rt^HBLOCK to float32 rounding, so the error of r does not
+// grow with k (it stays below HBLOCK/2 ulp inside a block).
+template <int G, int NC>
+__device__ __forceinline__ void integrate_geo(const float4 *__restrict__ tab, int nd, const float2 (&r2)[G / 2],
+                                              const float2 (&rb2)[G / 2], float2 (&P)[G / 2][NC])
+{
+    for (int k0 = nd - RADOP_HBLOCK; k0 >= 0; k0 -= RADOP_HBLOCK) {
 #pragma unroll
-    for (int g = 0; g < G; ++g) r[g] = ex2f_approx(a[g] * dD);
-    for (int k0 = 0; k0 < nd; k0 += RADOP_HBLOCK) {
-        float P[G][RADOP_NC];
-        {
-            float4 t0 = tab[(k0 + RADOP_HBLOCK - 1) * 2], t1 = tab[(k0 + RADOP_HBLOCK - 1) * 2 + 1];
+        for (int j = RADOP_HBLOCK - 1; j >= 0; --j) {
+            const float4 t0 = tab[(k0 + j) * 2], t1 = tab[(k0 + j) * 2 + 1];
+            const float t[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                P[g][0] = t0.x; P[g][1] = t0.y; P[g][2] = t0.z; P[g][3] = t0.w;
-                P[g][4] = t1.x; P[g][5] = t1.y; P[g][6] = t1.z;
+            for (int g = 0; g < G / 2; ++g) {
+                const float2 m = (j == RADOP_HBLOCK / 2) ? rb2[g] : r2[g];
+#pragma unroll
+                for (int c = 0; c < NC; ++c) P[g][c] = ffma2(P[g][c], m, bcast2(t[c]));
             }
-        }
-#pragma unroll
-        for (int j = RADOP_HBLOCK - 2; j >= 0; --j) {
-            float4 t0 = tab[(k0 + j) * 2], t1 = tab[(k0 + j) * 2 + 1];
-#pragma unroll
-            for (int g = 0; g < G; ++g) {
-                P[g][0] = fmaf(P[g][0], r[g], t0.x); P[g][1] = fmaf(P[g][1], r[g], t0.y);
-                P[g][2] = fmaf(P[g][2], r[g], t0.z); P[g][3] = fmaf(P[g][3], r[g], t0.w);
-                P[g][4] = fmaf(P[g][4], r[g], t1.x); P[g][5] = fmaf(P[g][5], r[g], t1.y);
-                P[g][6] = fmaf(P[g][6], r[g], t1.z);
-            }
-        }
-        float d0 = __ldg(Dg + k0);
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
-            float R = ex2f_approx(a[g] * d0);
-#pragma unroll
-            for (int c = 0; c < RADOP_NC; ++c) acc[g][c] = fmaf(P[g][c], R, acc[g][c]);
         }
     }
 }
 
-// general nu: one ex2 per diameter; NC = columns computed, ROW = floats per table row
+// general nu: one ex2 per diameter and pair; NC = columns computed, ROW = floats per table row
 template <int G, int NC, int ROW>
 __device__ __forceinline__ void integrate_gen(const float4 *__restrict__ tab, const float *__restrict__ U, int nd,
-                                              const float (&a)[G], float (&acc)[G][NC])
+                                              const float (&a)[G], float2 (&acc)[G / 2][NC])
 {
 #pragma unroll 4
     for (int k = 0; k < nd; ++k) {
-        float u = U[k];
+        const float u = U[k];
         float t[ROW];
 #pragma unroll
         for (int v = 0; v < ROW / 4; ++v) {
-            float4 x = tab[k * (ROW / 4) + v];
+            const float4 x = tab[k * (ROW / 4) + v];
             t[4 * v] = x.x; t[4 * v + 1] = x.y; t[4 * v + 2] = x.z; t[4 * v + 3] = x.w;
         }
 #pragma unroll
-        for (int g = 0; g < G; ++g) {
-            float E = ex2f_approx(a[g] * u);
+        for (int g = 0; g < G / 2; ++g) {
+            const float2 E = make_float2(ex2f_approx(a[2 * g] * u), ex2f_approx(a[2 * g + 1] * u));
 #pragma unroll
-            for (int c = 0; c < NC; ++c) acc[g][c] = fmaf(E, t[c], acc[g][c]);
+            for (int c = 0; c < NC; ++c) acc[g][c] = ffma2(E, bcast2(t[c]), acc[g][c]);
         }
     }
 }
@@ -996,40 +1009,42 @@ __device__ __forceinline__ void integrate_gen(const float4 *__restrict__ tab, co
 template <int G>
 __device__ __forceinline__ void integrate_ice1(const float4 *__restrict__ tab, const float *__restrict__ Dp, int nd,
                                                const float *__restrict__ Dg, float dD, const float (&lam)[G],
-                                               float (&acc)[G][12])
+                                               float2 (&acc)[G / 2][10])
 {
-    float a1[G], a2[G], r1[G], r2[G], c2[G];
+    float a1[G], a2[G], c2[G];
+    float2 r1[G / 2], r2[G / 2];
 #pragma unroll
     for (int g = 0; g < G; ++g) {
         a1[g] = -20.78f * LOG2E * lam[g];
         a2[g] = -3.290f * LOG2E * lam[g];
-        r1[g] = ex2f_approx(a1[g] * dD);
-        r2[g] = ex2f_approx(a2[g] * dD);
         c2[g] = 17.46f * exp2f(0.6357f * log2f(lam[g]));
     }
+#pragma unroll
+    for (int g = 0; g < G / 2; ++g) {
+        r1[g] = make_float2(ex2f_approx(a1[2 * g] * dD), ex2f_approx(a1[2 * g + 1] * dD));
+        r2[g] = make_float2(ex2f_approx(a2[2 * g] * dD), ex2f_approx(a2[2 * g + 1] * dD));
+    }
     for (int k0 = 0; k0 < nd; k0 += RADOP_HBLOCK) {
-        float d0 = __ldg(Dg + k0);
-        float E1[G], E2[G];
+        const float d0 = __ldg(Dg + k0);
+        float2 E1[G / 2], E2[G / 2];
 #pragma unroll
-        for (int g = 0; g < G; ++g) {
-            E1[g] = 490.6f * ex2f_approx(a1[g] * d0);
-            E2[g] = c2[g] * ex2f_approx(a2[g] * d0);
+        for (int g = 0; g < G / 2; ++g) {
+            E1[g] = make_float2(490.6f * ex2f_approx(a1[2 * g] * d0), 490.6f * ex2f_approx(a1[2 * g + 1] * d0));
+            E2[g] = make_float2(c2[2 * g] * ex2f_approx(a2[2 * g] * d0), c2[2 * g + 1] * ex2f_approx(a2[2 * g + 1] * d0));
         }
-        const int kend = min(k0 + RADOP_HBLOCK, nd);
-#pragma unroll 4
-        for (int k = k0; k < kend; ++k) {
-            float dp = Dp[k];
-            float4 t0 = tab[k * 3], t1 = tab[k * 3 + 1], t2 = tab[k * 3 + 2];
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                float w = fmaf(dp, E2[g], E1[g]);
-                acc[g][0] = fmaf(w, t0.x, acc[g][0]); acc[g][1] = fmaf(w, t0.y, acc[g][1]);
-                acc[g][2] = fmaf(w, t0.z, acc[g][2]); acc[g][3] = fmaf(w, t0.w, acc[g][3]);
-                acc[g][4] = fmaf(w, t1.x, acc[g][4]); acc[g][5] = fmaf(w, t1.y, acc[g][5]);
-                acc[g][6] = fmaf(w, t1.z, acc[g][6]); acc[g][7] = fmaf(w, t1.w, acc[g][7]);
-                acc[g][8] = fmaf(w, t2.x, acc[g][8]); acc[g][9] = fmaf(w, t2.y, acc[g][9]);
-                E1[g] *= r1[g];
-                E2[g] *= r2[g];
+        for (int j = 0; j < RADOP_HBLOCK; ++j) {
+            const int k = k0 + j;
+            const float dp = Dp[k];
+            const float4 t0 = tab[k * 3], t1 = tab[k * 3 + 1], t2 = tab[k * 3 + 2];
+            const float t[10] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w, t2.x, t2.y};
+#pragma unroll
+            for (int g = 0; g < G / 2; ++g) {
+                const float2 w = ffma2(bcast2(dp), E2[g], E1[g]);
+#pragma unroll
+                for (int c = 0; c < 10; ++c) acc[g][c] = ffma2(w, bcast2(t[c]), acc[g][c]);
+                E1[g] = fmul2(E1[g], r1[g]);
+                E2[g] = fmul2(E2[g], r2[g]);
             }
         }
     }
@@ -1046,21 +1061,32 @@ struct K2Args {
 
 extern __shared__ __align__(128) unsigned char s_k2[];
 
-template <int G>
-__device__ __forceinline__ void store_sz(float *sz_out, int nsp, int s, const PairRec &rec, const float *acc, float pre)
+__device__ __forceinline__ void store_sz(float *sz_out, int nsp, int s, uint32_t sbg, const float (&v)[7], float pre)
 {
-    float4 *dst = reinterpret_cast<float4 *>(sz_out + ((size_t)rec.sbg * nsp + s) * 8);
-    dst[0] = make_float4(acc[0] * pre, acc[1] * pre, acc[2] * pre, acc[3] * pre);
-    dst[1] = make_float4(acc[4] * pre, acc[5] * pre, acc[6] * pre, 0.f);
+    float4 *dst = reinterpret_cast<float4 *>(sz_out + ((size_t)sbg * nsp + s) * 8);
+    dst[0] = make_float4(v[0] * pre, v[1] * pre, v[2] * pre, v[3] * pre);
+    dst[1] = make_float4(v[4] * pre, v[5] * pre, v[6] * pre, 0.f);
+}
+
+#define RADOP_NO_PAIR 0xFFFFFFFFu
+__device__ __forceinline__ PairRec load_pair(const PairRec *__restrict__ rec, int first, int n_here, int i)
+{
+    PairRec r;
+    if (i < n_here) {
+        const float4 x = __ldg(reinterpret_cast<const float4 *>(rec + first + i));
+        r.sbg = __float_as_uint(x.x); r.p0 = x.y; r.p1 = x.z; r.w = x.w;
+    } else { r.sbg = RADOP_NO_PAIR; r.p0 = 0.f; r.p1 = 0.f; r.w = 0.f; }
+    return r;
 }
 
 // Persistent CTAs pull work units (RADOP_CHUNK consecutive tiles of one LUT bin) from a global
 // counter, the most expensive species first, so that the CTAs drain together whatever the
 // mix of species; the bin's table slice is staged in shared memory by TMA bulk copies.
+// A tile is RADOP_TILE pairs: every thread integrates RADOP_TILE_G of them (in one pass of 8
+// or two passes of 4, depending on how many columns the species carries).
 __global__ void __launch_bounds__(RADOP_TILE_THREADS)
 k_integrate(const __grid_constant__ DevConfig cfg, K2Args A)
 {
-    constexpr int G = RADOP_TILE_G;
     __shared__ uint64_t s_bar;
     __shared__ int s_unit;
     float4 *s_tab = reinterpret_cast<float4 *>(s_k2);
@@ -1119,61 +1145,113 @@ k_integrate(const __grid_constant__ DevConfig cfg, K2Args A)
         }
 
         for (int j = j0; j < j1; ++j) {
-            // ---- this thread's G pairs -------------------------------------------------------
             const int first = A.bin_start[b] + j * RADOP_TILE;
             const int n_here = min(RADOP_TILE, cnt - j * RADOP_TILE);
-            PairRec rec[G];
-#pragma unroll
-            for (int g = 0; g < G; ++g) {
-                int i = tid + g * RADOP_TILE_THREADS;
-                if (i < n_here) rec[g] = A.rec[first + i];
-                else { rec[g].sbg = 0xFFFFFFFFu; rec[g].p0 = 0.f; rec[g].p1 = 0.f; rec[g].w = 0.f; }
-            }
-            if (S.mode == MODE_GEO8 || S.mode == MODE_GEN8) {
-                float a[G], acc[G][RADOP_NC];
+            if (S.mode == MODE_GEO8) {
+                constexpr int G = 8;
+                float2 r2[G / 2], rb2[G / 2], P[G / 2][RADOP_NC];
 #pragma unroll
                 for (int g = 0; g < G; ++g) {
-                    a[g] = -LOG2E * rec[g].p0;
-#pragma unroll
-                    for (int c = 0; c < RADOP_NC; ++c) acc[g][c] = 0.f;
+                    const float lam = load_pair(A.rec, first, n_here, tid + g * RADOP_TILE_THREADS).p0;
+                    const float a = -LOG2E * lam;
+                    // rt = exp(-lambda dD) in float64, r = float32(rt), rb = r (rt / r)^HBLOCK
+                    const double rt = exp2((double)a * S.dD_d);
+                    const float r = (float)rt;
+                    const float rb = (float)((double)r + (double)RADOP_HBLOCK * (rt - (double)r));
+                    if (g & 1) { r2[g / 2].y = r; rb2[g / 2].y = rb; }
+                    else { r2[g / 2].x = r; rb2[g / 2].x = rb; }
                 }
-                if (S.mode == MODE_GEO8) integrate_geo8<G>(s_tab, nd, S.aux, S.dD_geo, a, acc);
-                else integrate_gen<G, RADOP_NC, 8>(s_tab, s_aux, nd, a, acc);
 #pragma unroll
-                for (int g = 0; g < G; ++g)
-                    if (rec[g].sbg != 0xFFFFFFFFu) store_sz<G>(A.sz_out, nsp, s, rec[g], acc[g], rec[g].p1 * rec[g].w);
-            } else if (S.mode == MODE_GEN12) {
-                float a[G], acc[G][9];
+                for (int g = 0; g < G / 2; ++g)
+#pragma unroll
+                    for (int c = 0; c < RADOP_NC; ++c) P[g][c] = make_float2(0.f, 0.f);
+                integrate_geo<G, RADOP_NC>(s_tab, nd, r2, rb2, P);
+                const float D0 = __ldg(S.aux);
 #pragma unroll
                 for (int g = 0; g < G; ++g) {
-                    a[g] = -LOG2E * rec[g].p0;
+                    const PairRec rec = load_pair(A.rec, first, n_here, tid + g * RADOP_TILE_THREADS);
+                    if (rec.sbg == RADOP_NO_PAIR) continue;
+                    float v[7];
 #pragma unroll
-                    for (int c = 0; c < 9; ++c) acc[g][c] = 0.f;
+                    for (int c = 0; c < 7; ++c) v[c] = (g & 1) ? P[g / 2][c].y : P[g / 2][c].x;
+                    store_sz(A.sz_out, nsp, s, rec.sbg, v, rec.p1 * rec.w * ex2f_approx(-LOG2E * rec.p0 * D0));
                 }
-                integrate_gen<G, 9, 12>(s_tab, s_aux, nd, a, acc);
+            } else if (S.mode == MODE_GEN8) {
+                constexpr int G = 8;
+                float a[G];
+                float2 acc[G / 2][RADOP_NC];
+#pragma unroll
+                for (int g = 0; g < G; ++g) a[g] = -LOG2E * load_pair(A.rec, first, n_here, tid + g * RADOP_TILE_THREADS).p0;
+#pragma unroll
+                for (int g = 0; g < G / 2; ++g)
+#pragma unroll
+                    for (int c = 0; c < RADOP_NC; ++c) acc[g][c] = make_float2(0.f, 0.f);
+                integrate_gen<G, RADOP_NC, 8>(s_tab, s_aux, nd, a, acc);
 #pragma unroll
                 for (int g = 0; g < G; ++g) {
-                    if (rec[g].sbg == 0xFFFFFFFFu) continue;
-                    const float n0 = rec[g].p1;
-                    store_sz<G>(A.sz_out, nsp, s, rec[g], acc[g], n0 * rec[g].w);
-                    A.ice_vn[rec[g].sbg] = make_float2(acc[g][7] * n0, acc[g][8] * n0);
+                    const PairRec rec = load_pair(A.rec, first, n_here, tid + g * RADOP_TILE_THREADS);
+                    if (rec.sbg == RADOP_NO_PAIR) continue;
+                    float v[7];
+#pragma unroll
+                    for (int c = 0; c < 7; ++c) v[c] = (g & 1) ? acc[g / 2][c].y : acc[g / 2][c].x;
+                    store_sz(A.sz_out, nsp, s, rec.sbg, v, rec.p1 * rec.w);
                 }
-            } else {   // MODE_ICE1
-                float lam[G], acc[G][12];
+            } else {
+                // 12-column species (numeric fall-speed moments): two passes of 4 pairs per thread
+                constexpr int G = 4;
+#pragma unroll 1
+                for (int pass = 0; pass < RADOP_TILE_G / G; ++pass) {
+                    const int i0 = tid + pass * G * RADOP_TILE_THREADS;
+                    if (pass * G * RADOP_TILE_THREADS >= n_here) break;
+                    if (S.mode == MODE_GEN12) {
+                        float a[G];
+                        float2 acc[G / 2][9];
 #pragma unroll
-                for (int g = 0; g < G; ++g) {
-                    lam[g] = (rec[g].sbg == 0xFFFFFFFFu) ? 1.0f : rec[g].p0;
+                        for (int g = 0; g < G; ++g) a[g] = -LOG2E * load_pair(A.rec, first, n_here, i0 + g * RADOP_TILE_THREADS).p0;
 #pragma unroll
-                    for (int c = 0; c < 12; ++c) acc[g][c] = 0.f;
-                }
-                integrate_ice1<G>(s_tab, s_aux, nd, S.aux, S.dD_geo, lam, acc);
+                        for (int g = 0; g < G / 2; ++g)
 #pragma unroll
-                for (int g = 0; g < G; ++g) {
-                    if (rec[g].sbg == 0xFFFFFFFFu) continue;
-                    // N0 renormalised so that the mass integral equals QM (hydrometeors.py:1330-1339)
-                    const float n0 = rec[g].p1 / acc[g][9];
-                    store_sz<G>(A.sz_out, nsp, s, rec[g], acc[g], n0 * rec[g].w);
-                    A.ice_vn[rec[g].sbg] = make_float2(acc[g][7] * n0, acc[g][8] * n0);
+                            for (int c = 0; c < 9; ++c) acc[g][c] = make_float2(0.f, 0.f);
+                        integrate_gen<G, 9, 12>(s_tab, s_aux, nd, a, acc);
+#pragma unroll
+                        for (int g = 0; g < G; ++g) {
+                            const PairRec rec = load_pair(A.rec, first, n_here, i0 + g * RADOP_TILE_THREADS);
+                            if (rec.sbg == RADOP_NO_PAIR) continue;
+                            float v[9];
+#pragma unroll
+                            for (int c = 0; c < 9; ++c) v[c] = (g & 1) ? acc[g / 2][c].y : acc[g / 2][c].x;
+                            const float n0 = rec.p1;
+                            const float v7[7] = {v[0], v[1], v[2], v[3], v[4], v[5], v[6]};
+                            store_sz(A.sz_out, nsp, s, rec.sbg, v7, n0 * rec.w);
+                            A.ice_vn[rec.sbg] = make_float2(v[7] * n0, v[8] * n0);
+                        }
+                    } else {   // MODE_ICE1
+                        float lam[G];
+                        float2 acc[G / 2][10];
+#pragma unroll
+                        for (int g = 0; g < G; ++g) {
+                            const PairRec rec = load_pair(A.rec, first, n_here, i0 + g * RADOP_TILE_THREADS);
+                            lam[g] = (rec.sbg == RADOP_NO_PAIR) ? 1.0f : rec.p0;
+                        }
+#pragma unroll
+                        for (int g = 0; g < G / 2; ++g)
+#pragma unroll
+                            for (int c = 0; c < 10; ++c) acc[g][c] = make_float2(0.f, 0.f);
+                        integrate_ice1<G>(s_tab, s_aux, nd, S.aux, S.dD_geo, lam, acc);
+#pragma unroll
+                        for (int g = 0; g < G; ++g) {
+                            const PairRec rec = load_pair(A.rec, first, n_here, i0 + g * RADOP_TILE_THREADS);
+                            if (rec.sbg == RADOP_NO_PAIR) continue;
+                            float v[10];
+#pragma unroll
+                            for (int c = 0; c < 10; ++c) v[c] = (g & 1) ? acc[g / 2][c].y : acc[g / 2][c].x;
+                            // N0 renormalised so that the mass integral equals QM (hydrometeors.py:1330-1339)
+                            const float n0 = rec.p1 / v[9];
+                            const float v7[7] = {v[0], v[1], v[2], v[3], v[4], v[5], v[6]};
+                            store_sz(A.sz_out, nsp, s, rec.sbg, v7, n0 * rec.w);
+                            A.ice_vn[rec.sbg] = make_float2(v[7] * n0, v[8] * n0);
+                        }
+                    }
                 }
             }
         }

@@ -6,10 +6,10 @@
 
 #define RADOP_NVP 16            // floats per (column, level) in the interleaved field layout
 #define RADOP_TILE_THREADS 128  // threads of one PSD-integration CTA
-#define RADOP_TILE_G 4          // (sub-beam gate, species) pairs per thread
+#define RADOP_TILE_G 8          // (sub-beam gate, species) pairs per thread and tile
 #define RADOP_TILE (RADOP_TILE_THREADS * RADOP_TILE_G)
 #define RADOP_HBLOCK 32         // diameters per Horner block (re-anchoring period)
-#define RADOP_CHUNK 4           // tiles per dynamically scheduled work unit of the integration kernel
+#define RADOP_CHUNK 2           // tiles per dynamically scheduled work unit of the integration kernel
 #define RADOP_NC 7              // combined columns that carry data (the 8th of a row is padding)
 #define RADOP_KEY_NONE 0xFFFFu
 
@@ -29,6 +29,7 @@ struct SpeciesDev {
     int qm_var, qn_var;         // RADOP_VAR_* holding mass / number density
     float dD_geo;               // (D[nd-1]-D[0])/(nd-1) computed in double
     float dD_ref;               // D[1]-D[0] in float32 (doppler_scatter.py:224)
+    double dD_d;                // dD_geo in float64
     const float *table;         // [ne][nt][nd][ncol] combined + premultiplied columns
     const float *aux;           // [3][nd]: D, D^nu, D^0.6357
     double a, b, alpha, beta, mu, nu, N0, lambda_factor, vel_factor, ntot_factor, x_min, x_max;
