@@ -40,6 +40,7 @@ struct LutHost {
     float e_min = 0, e_step = 1, t_min = 0, t_step = 1, dD_geo = 0, dD_ref = 0;
     double dD_d = 0;
     RadopSpecies packed_for;   // constants the table was premultiplied with
+    int packed_doppler = 0;    // Doppler scheme the table was laid out for
     DevBuf table, aux;
 };
 
@@ -72,7 +73,7 @@ struct RadopHandle_ {
     const float *d_nyquist = nullptr;
     // work buffers
     DevBuf geo, mask, active, wind, sinth, vsum, nsum, key, p0, p1, vals, lat, lon, hist, flags;
-    DevBuf bin_start, tile_start, cost_start, cursor, totals, rec, sz_out, ice_vn, ice_tot, comb, out, model_out;
+    DevBuf bin_start, tile_start, cost_start, cursor, totals, rec, sz_out, ice_vn, dop_vn, ice_tot, comb, out, model_out;
     DevBuf dbg_cell, dbg_level, dbg_status, dbg_e, dbg_t, dbg_rot;
     DevConfig cfg;
     int k2_blocks = 0;
@@ -147,7 +148,7 @@ int radop_destroy(RadopHandle *h)
     DevBuf *bufs[] = {&h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
                       &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
                       &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
-                      &h->ice_vn, &h->ice_tot, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
+                      &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
                       &h->dbg_status, &h->dbg_e, &h->dbg_t, &h->dbg_rot};
     for (DevBuf *b : bufs) b->release();
     for (auto &l : h->lut) { l.table.release(); l.aux.release(); }
@@ -166,8 +167,8 @@ int radop_set_params(RadopHandle *h, const RadopParams *p)
     if (p->abi_version != RADOP_ABI_VERSION) return h->fail(RADOP_ERR_ARG, "RadopParams.abi_version mismatch");
     if (p->n_gates <= 0) return h->fail(RADOP_ERR_ARG, "n_gates must be positive");
     if (p->n_species <= 0 || p->n_species > RADOP_NSPECIES_MAX) return h->fail(RADOP_ERR_ARG, "bad n_species");
-    if (p->doppler_scheme != 1)
-        return h->fail(RADOP_ERR_UNSUPPORTED, "only doppler scheme 1 is implemented on the GPU in this build");
+    if (p->doppler_scheme != 1 && p->doppler_scheme != 2)
+        return h->fail(RADOP_ERR_UNSUPPORTED, "doppler schemes 1 and 2 are implemented on the GPU in this build");
     if (p->sensitivity_mode < 0 || p->sensitivity_mode > 2)
         return h->fail(RADOP_ERR_UNSUPPORTED, "sensitivity must be [ZH] or [ZH, range]");
     for (int s = 0; s < p->n_species; ++s) {
@@ -257,7 +258,7 @@ int radop_upload_lut(RadopHandle *h, int species, const double *value_table, int
         if (!uniform || (nd % RADOP_HBLOCK) != 0)
             return h->fail(RADOP_ERR_LUT, "1-mom ice needs a uniform diameter axis with a multiple of 32 bins");
         L.mode = MODE_ICE1; L.ncol = 12; L.cost = 15;
-    } else if (S->numeric_vn) {
+    } else if (S->numeric_vn && h->p.doppler_scheme == 1) {
         L.mode = MODE_GEN12; L.ncol = 12; L.cost = 15;
     } else if (S->nu == 1.0 && uniform && (nd % RADOP_HBLOCK) == 0) {
         L.mode = MODE_GEO8; L.ncol = 8; L.cost = 9;
@@ -270,6 +271,7 @@ int radop_upload_lut(RadopHandle *h, int species, const double *value_table, int
     L.dD_d = dD;
     L.dD_ref = d_axis[1] - d_axis[0];
     L.packed_for = *S;
+    L.packed_doppler = h->p.doppler_scheme;
     size_t rows = (size_t)ne * nt * nd;
     DevBuf raw, dax;
     CU(h, raw.reserve(rows * 12 * 8));
@@ -279,7 +281,8 @@ int radop_upload_lut(RadopHandle *h, int species, const double *value_table, int
     CU(h, cudaMemcpyAsync(raw.p, value_table, rows * 12 * 8, cudaMemcpyHostToDevice, h->stream));
     CU(h, cudaMemcpyAsync(dax.p, d_axis, (size_t)nd * 4, cudaMemcpyHostToDevice, h->stream));
     k_pack_lut<<<h->n_sm * 8, 256, 0, h->stream>>>(raw.as<double>(), L.table.as<float>(), dax.as<float>(), rows, nd,
-                                                  L.ncol, L.mode, S->mu, (double)L.dD_ref, S->alpha, S->beta, S->a, S->b);
+                                                  L.ncol, L.mode, S->mu, (double)L.dD_ref, S->alpha, S->beta, S->a, S->b,
+                                                  h->p.doppler_scheme);
     CU(h, cudaGetLastError());
     k_pack_aux<<<(nd + 255) / 256, 256, 0, h->stream>>>(dax.as<float>(), L.aux.as<float>(), nd, S->nu);
     CU(h, cudaGetLastError());
@@ -390,7 +393,7 @@ static int prepare(RadopHandle *h)
         const RadopSpecies &S = p.species[s];
         const LutHost &L = h->lut[S.species];
         if (!L.loaded) return h->fail(RADOP_ERR_LUT, "a lookup table is missing for one of the species");
-        if (memcmp(&L.packed_for, &S, sizeof S) != 0)
+        if (memcmp(&L.packed_for, &S, sizeof S) != 0 || L.packed_doppler != p.doppler_scheme)
             return h->fail(RADOP_ERR_LUT, "species constants changed since the table upload: upload the table again");
         SpeciesDev &d = c.sp[s];
         d.species = S.species; d.psd = S.psd; d.mode = L.mode; d.ncol = L.ncol; d.numeric_vn = S.numeric_vn;
@@ -419,7 +422,7 @@ static int prepare(RadopHandle *h)
             d.c_v = S.vel_factor * S.alpha / S.nu; d.e_v = -(S.beta + S.mu + 1.0) / S.nu;
             d.c_n = S.ntot_factor / S.nu; d.e_n = -(S.mu + 1.0) / S.nu;
         }
-        if (S.numeric_vn) {
+        if (S.numeric_vn && p.doppler_scheme == 1) {
             if (c.ice_numeric >= 0) return h->fail(RADOP_ERR_UNSUPPORTED, "only one species may have numeric fall-speed moments");
             c.ice_numeric = s;
         }
@@ -470,6 +473,7 @@ int radop_execute(RadopHandle *h)
     CU(h, h->rec.reserve((size_t)n * nsp * sizeof(PairRec)));
     CU(h, h->sz_out.reserve((size_t)n * nsp * 8 * 4));
     CU(h, h->ice_vn.reserve((size_t)n * 8));
+    if (c.doppler_scheme == 2) CU(h, h->dop_vn.reserve((size_t)n * nsp * 8));
     CU(h, h->ice_tot.reserve((size_t)c.n_rays * c.n_sub * 3 * 4));
     CU(h, h->comb.reserve(n_rg * 8 * 4));
     CU(h, h->out.reserve(n_rg * (RADOP_N_OUT + 1) * 4));
@@ -548,7 +552,7 @@ int radop_execute(RadopHandle *h)
     a2.hist = h->hist.as<int>(); a2.bin_start = h->bin_start.as<int>(); a2.tile_start = h->tile_start.as<int>();
     a2.chunk_start = h->cost_start.as<int>(); a2.totals = h->totals.as<long long>();
     a2.counter = h->flags.as<int>() + 1;
-    a2.rec = h->rec.as<PairRec>(); a2.sz_out = h->sz_out.as<float>(); a2.ice_vn = h->ice_vn.as<float2>();
+    a2.rec = h->rec.as<PairRec>(); a2.sz_out = h->sz_out.as<float>(); a2.ice_vn = h->ice_vn.as<float2>(); a2.dop_vn = h->dop_vn.as<float2>();
     k_integrate<<<h->k2_blocks, RADOP_TILE_THREADS, h->k2_smem, st>>>(c, a2);
     CU(h, cudaGetLastError()); ++launches;
     if (ev) CU(h, cudaEventRecord(ev[3], st));
@@ -561,7 +565,7 @@ int radop_execute(RadopHandle *h)
     K3Args a3;
     a3.mask = h->mask.as<int8_t>(); a3.active = h->active.as<uint8_t>();
     a3.wind = h->wind.as<float>(); a3.sinth = h->sinth.as<float>(); a3.vsum = h->vsum.as<float>(); a3.nsum = h->nsum.as<float>();
-    a3.sz_out = h->sz_out.as<float>(); a3.ice_tot = h->ice_tot.as<float>();
+    a3.sz_out = h->sz_out.as<float>(); a3.ice_tot = h->ice_tot.as<float>(); a3.dop_vn = h->dop_vn.as<float2>();
     a3.vals = want_vals ? h->vals.as<float>() : nullptr;
     a3.sub_weight = h->scan.sub_weight; a3.ray_nyquist = h->d_nyquist;
     a3.comb = h->comb.as<float>(); a3.out = h->out.as<float>();

@@ -93,10 +93,12 @@ __global__ void k_pack_field(const float *__restrict__ src, float *__restrict__ 
 //  get_pol_from_sz only through these seven combinations, doppler_scatter.py:516-542;
 //  forming s10-s8 in float64 BEFORE the integral removes the KDP cancellation)
 // premultiplied by  D^mu * dD  (GEO/GEN modes) or dD (ICE1, whose shape function is
-// evaluated in the kernel); 12-column modes add 7: v(D), 8: 1, 9: m(D) (ICE1 only).
+// evaluated in the kernel); column 7 of the 8-column layout is b v(D) (rcs-weighted fall speed,
+// Doppler scheme 2); 12-column modes hold 7: v(D) (scheme 1) or b v(D) (scheme 2), 8: 1,
+// 9: m(D) (ICE1 only).
 __global__ void k_pack_lut(const double *__restrict__ src, float *__restrict__ dst, const float *__restrict__ d_axis,
                            size_t n_rows, int nd, int ncol, int mode, double mu, double dD, double alpha,
-                           double beta, double a_m, double b_m)
+                           double beta, double a_m, double b_m, int doppler_scheme)
 {
     for (size_t r = blockIdx.x * (size_t)blockDim.x + threadIdx.x; r < n_rows;
          r += (size_t)gridDim.x * blockDim.x) {
@@ -112,10 +114,12 @@ __global__ void k_pack_lut(const double *__restrict__ src, float *__restrict__ d
         o[4] = (float)((s[10] - s[8]) * pre);
         o[5] = (float)(s[9] * pre);
         o[6] = (float)(s[11] * pre);
+        // rcs-weighted fall speed (Doppler scheme 2, doppler_scatter.py:286-296): b(D) v(D)
+        const double bv = (s[0] - s[1] - s[2] + s[3]) * alpha * pow(D, beta) * pre;
         if (ncol == 8) {
-            o[7] = 0.f;
+            o[7] = (float)bv;
         } else {
-            o[7] = (float)(alpha * pow(D, beta) * pre);
+            o[7] = (doppler_scheme == 2) ? (float)bv : (float)(alpha * pow(D, beta) * pre);
             o[8] = (float)pre;
             o[9] = (mode == MODE_ICE1) ? (float)(a_m * pow(D, b_m) * pre) : 0.f;
             o[10] = 0.f;
@@ -718,7 +722,7 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                     active |= (uint8_t)(1u << s);
                     const double lQM = log((double)QMf);
                     double loglam, logn0 = 0.0, n0 = S.N0, ntot_2m = 0.0;
-                    bool n0_from_log = false;
+                    bool n0_from_log = false, n0_negative = false;
                     float p0, p1;
                     if (S.psd == RADOP_PSD_1MOM_FIXED_N0) {
                         // lambda = (lambda_factor / QM)^(1/(4+mu)), hydrometeors.py:761-772, 1039-1049
@@ -737,12 +741,15 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                         ntot_2m = QN;
                         const double xm = fmin(fmax((double)QMf / (QN + 2.220446049250313e-16), S.x_min), S.x_max);
                         const double ll0 = S.c_inv * log(S.lambda_factor * xm);
-                        logn0 = log(S.c_q * QN) + S.e_q * ll0 - S.c_ka;
+                        // QN can be negative (extrapolation below the lowest usable level): the
+                        // reference then carries a negative N0 through; keep the sign outside the log
+                        logn0 = log(fabs(S.c_q * QN)) + S.e_q * ll0 - S.c_ka;
                         n0_from_log = true;
+                        n0_negative = (S.c_q * QN) < 0.0;
                         loglam = ll0 - S.c_kb;
                     }
                     const double lam = exp(loglam);
-                    if (n0_from_log) n0 = exp(logn0);
+                    if (n0_from_log) n0 = n0_negative ? -exp(logn0) : exp(logn0);
                     if (S.psd == RADOP_PSD_1MOM_ICE) { p0 = (float)lam; p1 = QMf; }     // lambda / 1000, QM
                     else { p0 = (float)lam; p1 = (float)n0; }
                     const int ie = lut_bin(e, S.e_min, S.e_step, S.ne);
@@ -1057,6 +1064,7 @@ struct K2Args {
     const PairRec *rec;
     float *sz_out;      // [sbg][n_species][8]
     float2 *ice_vn;     // [sbg] numeric fall-speed moments of the ice species
+    float2 *dop_vn;     // [sbg][n_species] rcs-weighted fall-speed moments (Doppler scheme 2)
 };
 
 extern __shared__ __align__(128) unsigned char s_k2[];
@@ -1077,6 +1085,94 @@ __device__ __forceinline__ PairRec load_pair(const PairRec *__restrict__ rec, in
         r.sbg = __float_as_uint(x.x); r.p0 = x.y; r.p1 = x.z; r.w = x.w;
     } else { r.sbg = RADOP_NO_PAIR; r.p0 = 0.f; r.p1 = 0.f; r.w = 0.f; }
     return r;
+}
+
+// Trapezoid rule from a rectangle sum: np.trapz (dx = 1) = sum - (first + last) / 2.
+// Doppler scheme 2 (doppler_scatter.py:286-296): v = trapz(V N rcs), n = trapz(N rcs), rcs = 2 pi b.
+__device__ __forceinline__ float2 doppler2_moments(float sum_b, float sum_bv, float4 row0a, float4 row0b, float4 rowLa,
+                                                   float4 rowLb, float w_first, float w_last, float scale)
+{
+    const float n = sum_b - 0.5f * (row0a.x * w_first + rowLa.x * w_last);
+    const float v = sum_bv - 0.5f * (row0b.w * w_first + rowLb.w * w_last);
+    return make_float2(v * scale, n * scale);
+}
+
+// one tile of a nu == 1 species: 8 pairs per thread, NC = 7 columns (8 with Doppler scheme 2)
+template <int NC>
+__device__ __forceinline__ void tile_geo(const K2Args &A, const SpeciesDev &S, int s, int nsp, int first, int n_here,
+                                         int tid, const float4 *__restrict__ s_tab, int nd)
+{
+    constexpr int G = 8;
+    float2 r2[G / 2], rb2[G / 2], P[G / 2][NC];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const float lam = load_pair(A.rec, first, n_here, tid + g * RADOP_TILE_THREADS).p0;
+        const float a = -LOG2E * lam;
+        // rt = exp(-lambda dD) in float64, r = float32(rt), rb = r (rt / r)^HBLOCK
+        const double rt = exp2((double)a * S.dD_d);
+        const float r = (float)rt;
+        const float rb = (float)((double)r + (double)RADOP_HBLOCK * (rt - (double)r));
+        if (g & 1) { r2[g / 2].y = r; rb2[g / 2].y = rb; }
+        else { r2[g / 2].x = r; rb2[g / 2].x = rb; }
+    }
+#pragma unroll
+    for (int g = 0; g < G / 2; ++g)
+#pragma unroll
+        for (int c = 0; c < NC; ++c) P[g][c] = make_float2(0.f, 0.f);
+    integrate_geo<G, NC>(s_tab, nd, r2, rb2, P);
+    const float D0 = __ldg(S.aux);
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const PairRec rec = load_pair(A.rec, first, n_here, tid + g * RADOP_TILE_THREADS);
+        if (rec.sbg == RADOP_NO_PAIR) continue;
+        float v[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) v[c] = (g & 1) ? P[g / 2][c].y : P[g / 2][c].x;
+        const float a = -LOG2E * rec.p0;
+        const float e0 = ex2f_approx(a * D0);
+        const float v7[7] = {v[0], v[1], v[2], v[3], v[4], v[5], v[6]};
+        store_sz(A.sz_out, nsp, s, rec.sbg, v7, rec.p1 * rec.w * e0);
+        if (NC == 8) {
+            const float w_last = ex2f_approx(a * (float)((double)(nd - 1) * S.dD_d));
+            A.dop_vn[(size_t)rec.sbg * nsp + s] =
+                doppler2_moments(v[0], v[NC - 1], s_tab[0], s_tab[1], s_tab[(nd - 1) * 2], s_tab[(nd - 1) * 2 + 1], 1.f, w_last,
+                                 6.283185307179586f * rec.p1 * e0 / S.dD_ref);
+        }
+    }
+}
+
+// one tile of a general-nu species
+template <int NC>
+__device__ __forceinline__ void tile_gen(const K2Args &A, const SpeciesDev &S, int s, int nsp, int first, int n_here,
+                                         int tid, const float4 *__restrict__ s_tab, const float *__restrict__ s_aux, int nd)
+{
+    constexpr int G = 8;
+    float a[G];
+    float2 acc[G / 2][NC];
+#pragma unroll
+    for (int g = 0; g < G; ++g) a[g] = -LOG2E * load_pair(A.rec, first, n_here, tid + g * RADOP_TILE_THREADS).p0;
+#pragma unroll
+    for (int g = 0; g < G / 2; ++g)
+#pragma unroll
+        for (int c = 0; c < NC; ++c) acc[g][c] = make_float2(0.f, 0.f);
+    integrate_gen<G, NC, 8>(s_tab, s_aux, nd, a, acc);
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const PairRec rec = load_pair(A.rec, first, n_here, tid + g * RADOP_TILE_THREADS);
+        if (rec.sbg == RADOP_NO_PAIR) continue;
+        float v[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) v[c] = (g & 1) ? acc[g / 2][c].y : acc[g / 2][c].x;
+        const float v7[7] = {v[0], v[1], v[2], v[3], v[4], v[5], v[6]};
+        store_sz(A.sz_out, nsp, s, rec.sbg, v7, rec.p1 * rec.w);
+        if (NC == 8) {
+            const float ag = -LOG2E * rec.p0;
+            A.dop_vn[(size_t)rec.sbg * nsp + s] =
+                doppler2_moments(v[0], v[NC - 1], s_tab[0], s_tab[1], s_tab[(nd - 1) * 2], s_tab[(nd - 1) * 2 + 1],
+                                 ex2f_approx(ag * s_aux[0]), ex2f_approx(ag * s_aux[nd - 1]),
+                                 6.283185307179586f * rec.p1 / S.dD_ref);
+        }
+    }
 }
 
 // Persistent CTAs pull work units (RADOP_CHUNK consecutive tiles of one LUT bin) from a global
@@ -1148,54 +1244,11 @@ k_integrate(const __grid_constant__ DevConfig cfg, K2Args A)
             const int first = A.bin_start[b] + j * RADOP_TILE;
             const int n_here = min(RADOP_TILE, cnt - j * RADOP_TILE);
             if (S.mode == MODE_GEO8) {
-                constexpr int G = 8;
-                float2 r2[G / 2], rb2[G / 2], P[G / 2][RADOP_NC];
-#pragma unroll
-                for (int g = 0; g < G; ++g) {
-                    const float lam = load_pair(A.rec, first, n_here, tid + g * RADOP_TILE_THREADS).p0;
-                    const float a = -LOG2E * lam;
-                    // rt = exp(-lambda dD) in float64, r = float32(rt), rb = r (rt / r)^HBLOCK
-                    const double rt = exp2((double)a * S.dD_d);
-                    const float r = (float)rt;
-                    const float rb = (float)((double)r + (double)RADOP_HBLOCK * (rt - (double)r));
-                    if (g & 1) { r2[g / 2].y = r; rb2[g / 2].y = rb; }
-                    else { r2[g / 2].x = r; rb2[g / 2].x = rb; }
-                }
-#pragma unroll
-                for (int g = 0; g < G / 2; ++g)
-#pragma unroll
-                    for (int c = 0; c < RADOP_NC; ++c) P[g][c] = make_float2(0.f, 0.f);
-                integrate_geo<G, RADOP_NC>(s_tab, nd, r2, rb2, P);
-                const float D0 = __ldg(S.aux);
-#pragma unroll
-                for (int g = 0; g < G; ++g) {
-                    const PairRec rec = load_pair(A.rec, first, n_here, tid + g * RADOP_TILE_THREADS);
-                    if (rec.sbg == RADOP_NO_PAIR) continue;
-                    float v[7];
-#pragma unroll
-                    for (int c = 0; c < 7; ++c) v[c] = (g & 1) ? P[g / 2][c].y : P[g / 2][c].x;
-                    store_sz(A.sz_out, nsp, s, rec.sbg, v, rec.p1 * rec.w * ex2f_approx(-LOG2E * rec.p0 * D0));
-                }
+                if (cfg.doppler_scheme == 2) tile_geo<8>(A, S, s, nsp, first, n_here, tid, s_tab, nd);
+                else tile_geo<RADOP_NC>(A, S, s, nsp, first, n_here, tid, s_tab, nd);
             } else if (S.mode == MODE_GEN8) {
-                constexpr int G = 8;
-                float a[G];
-                float2 acc[G / 2][RADOP_NC];
-#pragma unroll
-                for (int g = 0; g < G; ++g) a[g] = -LOG2E * load_pair(A.rec, first, n_here, tid + g * RADOP_TILE_THREADS).p0;
-#pragma unroll
-                for (int g = 0; g < G / 2; ++g)
-#pragma unroll
-                    for (int c = 0; c < RADOP_NC; ++c) acc[g][c] = make_float2(0.f, 0.f);
-                integrate_gen<G, RADOP_NC, 8>(s_tab, s_aux, nd, a, acc);
-#pragma unroll
-                for (int g = 0; g < G; ++g) {
-                    const PairRec rec = load_pair(A.rec, first, n_here, tid + g * RADOP_TILE_THREADS);
-                    if (rec.sbg == RADOP_NO_PAIR) continue;
-                    float v[7];
-#pragma unroll
-                    for (int c = 0; c < 7; ++c) v[c] = (g & 1) ? acc[g / 2][c].y : acc[g / 2][c].x;
-                    store_sz(A.sz_out, nsp, s, rec.sbg, v, rec.p1 * rec.w);
-                }
+                if (cfg.doppler_scheme == 2) tile_gen<8>(A, S, s, nsp, first, n_here, tid, s_tab, s_aux, nd);
+                else tile_gen<RADOP_NC>(A, S, s, nsp, first, n_here, tid, s_tab, s_aux, nd);
             } else {
                 // 12-column species (numeric fall-speed moments): two passes of 4 pairs per thread
                 constexpr int G = 4;
@@ -1249,7 +1302,21 @@ k_integrate(const __grid_constant__ DevConfig cfg, K2Args A)
                             const float n0 = rec.p1 / v[9];
                             const float v7[7] = {v[0], v[1], v[2], v[3], v[4], v[5], v[6]};
                             store_sz(A.sz_out, nsp, s, rec.sbg, v7, n0 * rec.w);
-                            A.ice_vn[rec.sbg] = make_float2(v[7] * n0, v[8] * n0);
+                            if (cfg.doppler_scheme == 2) {
+                                // shape function at the two end diameters (trapezoid correction)
+                                const float D0 = __ldg(S.aux), DL = __ldg(S.aux + nd - 1);
+                                const float c2 = 17.46f * exp2f(0.6357f * log2f(rec.p0));
+                                const float w0 = 490.6f * ex2f_approx(-20.78f * LOG2E * rec.p0 * D0) +
+                                                 c2 * s_aux[0] * ex2f_approx(-3.290f * LOG2E * rec.p0 * D0);
+                                const float wL = 490.6f * ex2f_approx(-20.78f * LOG2E * rec.p0 * DL) +
+                                                 c2 * s_aux[nd - 1] * ex2f_approx(-3.290f * LOG2E * rec.p0 * DL);
+                                const float n_ = v[0] - 0.5f * (s_tab[0].x * w0 + s_tab[(nd - 1) * 3].x * wL);
+                                const float v_ = v[7] - 0.5f * (s_tab[1].w * w0 + s_tab[(nd - 1) * 3 + 1].w * wL);
+                                const float sc = 6.283185307179586f * n0 / S.dD_ref;
+                                A.dop_vn[(size_t)rec.sbg * nsp + s] = make_float2(v_ * sc, n_ * sc);
+                            } else {
+                                A.ice_vn[rec.sbg] = make_float2(v[7] * n0, v[8] * n0);
+                            }
                         }
                     }
                 }
@@ -1300,6 +1367,7 @@ struct K3Args {
     const float *wind, *sinth, *vsum, *nsum;
     const float *sz_out;
     const float *ice_tot;
+    const float2 *dop_vn;
     const float *vals;
     const double *sub_weight;
     const float *ray_nyquist;
@@ -1342,11 +1410,21 @@ k_reduce_subbeams(const __grid_constant__ DevConfig cfg, K3Args A)
             comb[0] += r0.x; comb[1] += r0.y; comb[2] += r0.z; comb[3] += r0.w;
             comb[4] += r1.x; comb[5] += r1.y; comb[6] += r1.z;
         }
-        if (cfg.doppler_scheme == 1) {
-            float vs = A.vsum[sbg], ns = A.nsum[sbg];
-            if (cfg.ice_numeric >= 0 && (act & (1u << cfg.ice_numeric))) {
-                const float *t = A.ice_tot + 3 * ((size_t)ray * cfg.n_sub + q);
-                if (__float_as_int(t[2]) == g) { vs += t[0]; ns += t[1]; }
+        if (cfg.doppler_scheme == 1 || cfg.doppler_scheme == 2) {
+            float vs, ns;
+            if (cfg.doppler_scheme == 1) {
+                vs = A.vsum[sbg]; ns = A.nsum[sbg];
+                if (cfg.ice_numeric >= 0 && (act & (1u << cfg.ice_numeric))) {
+                    const float *t = A.ice_tot + 3 * ((size_t)ray * cfg.n_sub + q);
+                    if (__float_as_int(t[2]) == g) { vs += t[0]; ns += t[1]; }
+                }
+            } else {
+                vs = 0.f; ns = 0.f;
+                for (int s = 0; s < nsp; ++s) {
+                    if (!(act & (1u << s))) continue;
+                    const float2 x = __ldg(A.dop_vn + sbg * nsp + s);
+                    vs += x.x; ns += x.y;
+                }
             }
             float vh = vs / ns;                              // 0/0 -> NaN where no hydrometeor (Q7)
             float rv = A.wind[sbg] - vh * A.sinth[sbg];

@@ -93,7 +93,7 @@ typedef struct {
     double radial_resolution_m;   /* CONFIG['radar']['radial_resolution']                 */
     int32_t two_moment;           /* CONFIG['microphysics']['scheme'] == '2mom'           */
     int32_t with_attenuation;     /* CONFIG['microphysics']['with_attenuation']           */
-    int32_t doppler_scheme;       /* CONFIG['doppler']['scheme'] (1 or 2)                 */
+    int32_t doppler_scheme;       /* CONFIG['doppler']['scheme']: 1 analytic, 2 rcs-weighted    */
     int32_t sensitivity_mode;     /* 0: no cut; 1: [ZH]; 2: [ZH, range]; cut_at_sensitivity */
     double sensitivity[3];
     int32_t output_model_vars;    /* integrate_radials outputs wanted ('all'/'only_model') */

@@ -177,7 +177,8 @@ def test_observables_against_oracle(scheme, freq):
 
 
 @pytest.mark.parametrize('name,scheme,freq', [('c1mom', '1mom', 5.6), ('c2mom', '2mom', 9.41),
-                                               ('c1mom_thr', '1mom', 5.6), ('c1mom_nyq', '1mom', 5.6)])
+                                               ('c1mom_thr', '1mom', 5.6), ('c1mom_nyq', '1mom', 5.6),
+                                               ('c1mom_dop2', '1mom', 5.6)])
 def test_against_reference_goldens(name, scheme, freq):
     """GPU output against what the reference itself produced (tests/golden)."""
     from cosmo_pol_b200 import RadarOperator
@@ -210,6 +211,32 @@ def test_against_reference_goldens(name, scheme, freq):
         out2 = op2.simulate_rays(rays[:, 0], rays[:, 1])
         for k in ('ZH', 'ZV', 'ZDR', 'KDP', 'RHOHV', 'PHIDP', 'RVEL', 'ATT_H', 'DELTA_HV'):
             assert np.array_equal(np.isnan(out2[k]), np.isnan(g['cut_' + k])), k
+
+
+@pytest.mark.parametrize('scheme,freq', [('1mom', 5.6), ('2mom', 9.41)])
+def test_doppler_scheme2_against_oracle(scheme, freq):
+    """rcs-weighted fall speeds (doppler_scatter.py:286-296): trapezoid integrals of V N rcs and
+    N rcs over the diameters, summed over species, per sub-beam."""
+    conf = copy.deepcopy(CONF_1MOM)
+    conf['doppler'] = {'scheme': 2}
+    op, model, luts = make_operator(conf, scheme, freq)
+    az = np.arange(5., 360., 45.)
+    els = [0.4, 6.5, 30.0, 89.0]
+    rays_az, rays_el = np.tile(az, len(els)), np.repeat(els, len(az))
+    out = op.simulate_rays(rays_az, rays_el)
+    pm, pl = plain(model, luts)
+    ref = O.simulate_scan(pm, pl, oracle_cfg(op), rays_az, rays_el, accum='f64', sensitivity_cut=True)
+    assert_observables_close(out, ref, what='dop2 ' + scheme)
+    a, b = out['RVEL'], ref['RVEL']
+    assert np.array_equal(np.isnan(a), np.isnan(b))
+    ok = np.isfinite(b)
+    assert ok.sum() > 200
+    assert np.max(np.abs(a[ok] - b[ok])) < 2e-3, np.max(np.abs(a[ok] - b[ok]))
+    # and it differs from the analytic scheme 1 (the test would otherwise prove nothing)
+    conf1 = copy.deepcopy(CONF_1MOM)
+    op1, _, _ = make_operator(conf1, scheme, freq)
+    out1 = op1.simulate_rays(rays_az, rays_el)
+    assert np.nanmax(np.abs(out1['RVEL'] - a)) > 0.05
 
 
 def test_edge_cases_and_errors():
