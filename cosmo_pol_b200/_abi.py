@@ -10,7 +10,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libradop.so')
 
-RADOP_ABI_VERSION = 1
+RADOP_ABI_VERSION = 2
 NSPECIES_MAX = 5
 NVAR_MAX = 16
 N_OUT = 10
@@ -44,7 +44,8 @@ class RadopParams(C.Structure):
                 ('two_moment', C.c_int32), ('with_attenuation', C.c_int32), ('doppler_scheme', C.c_int32),
                 ('sensitivity_mode', C.c_int32), ('sensitivity', C.c_double * 3),
                 ('output_model_vars', C.c_int32), ('keep_debug', C.c_int32), ('n_species', C.c_int32),
-                ('reserved', C.c_int32), ('species', RadopSpecies * NSPECIES_MAX)]
+                ('reserved', C.c_int32), ('species', RadopSpecies * NSPECIES_MAX),
+                ('n_vel', C.c_int32), ('reserved2', C.c_int32), ('vel_min', C.c_double), ('vel_res', C.c_double)]
 
 
 class RadopScan(C.Structure):
@@ -56,14 +57,14 @@ class RadopScan(C.Structure):
 
 class RadopOut(C.Structure):
     _fields_ = [('obs', C.c_void_p * N_OUT), ('mask', C.c_void_p), ('lat', C.c_void_p), ('lon', C.c_void_p),
-                ('model', C.c_void_p * NVAR_MAX)]
+                ('model', C.c_void_p * NVAR_MAX), ('dspectrum', C.c_void_p)]
 
 
 class RadopStats(C.Structure):
     _fields_ = [('n_subbeam_gates', C.c_int64), ('n_active_pairs', C.c_int64), ('n_lut_bins', C.c_int64),
                 ('n_tiles', C.c_int64), ('launches', C.c_int64), ('ms_interp', C.c_float), ('ms_sort', C.c_float),
                 ('ms_integrate', C.c_float), ('ms_reduce', C.c_float), ('ms_total', C.c_float),
-                ('n_timed', C.c_int32), ('reserved', C.c_int32)]
+                ('n_timed', C.c_int32), ('ms_spectrum', C.c_float)]
 
 
 class RadopError(RuntimeError):
@@ -213,6 +214,15 @@ class Engine(object):
         p.two_moment = 1 if config['microphysics']['scheme'] == '2mom' else 0
         p.with_attenuation = int(config['microphysics']['with_attenuation'])
         p.doppler_scheme = int(config['doppler']['scheme'])
+        if p.doppler_scheme == 3:
+            d = config['doppler']
+            if d.get('turbulence_correction', 0) or d.get('motion_correction', 0):
+                raise ValueError('spectrum broadening (turbulence_correction / motion_correction, '
+                                 'doppler_scatter.py:727-801) is not implemented in the GPU path')
+            # constants.VARRAY = np.arange(-NVEL, NVEL + VRES, VRES), global_constants.py:168-171
+            p.n_vel = len(constants.VARRAY)
+            p.vel_min, p.vel_res = float(-constants.NVEL), float(constants.VRES)
+        self.n_vel = int(p.n_vel)
         sens = r['sensitivity']
         sens = list(sens) if isinstance(sens, (list, tuple)) else [sens]
         if not sensitivity_cut:
@@ -317,6 +327,10 @@ class Engine(object):
                 a = self._host_buffer(('model', name), shape, np.float32)
                 arrays[name] = a
                 out.model[VAR_IDS[name]] = a.ctypes.data
+        if self.params is not None and self.params.doppler_scheme == 3:
+            a = self._host_buffer('dspectrum', shape + (self.n_vel,), np.float32)
+            arrays['DSPECTRUM'] = a
+            out.dspectrum = a.ctypes.data
         return out, arrays
 
     def simulate(self, scan, want_latlon=True, want_model=False):

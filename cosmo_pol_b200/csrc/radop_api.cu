@@ -39,6 +39,7 @@ struct LutHost {
     int ne = 0, nt = 0, nd = 0, mode = 0, ncol = 8, cost = 9;
     float e_min = 0, e_step = 1, t_min = 0, t_step = 1, dD_geo = 0, dD_ref = 0;
     double dD_d = 0;
+    float d_min = 0, d_max = 0, spec_step = 0;
     RadopSpecies packed_for;   // constants the table was premultiplied with
     int packed_doppler = 0;    // Doppler scheme the table was laid out for
     DevBuf table, aux;
@@ -74,13 +75,15 @@ struct RadopHandle_ {
     // work buffers
     DevBuf geo, mask, active, wind, sinth, vsum, nsum, key, p0, p1, vals, lat, lon, hist, flags;
     DevBuf bin_start, tile_start, cost_start, cursor, totals, rec, sz_out, ice_vn, dop_vn, ice_tot, comb, out, model_out;
+    DevBuf d3_uh, d3_w, d3_rho, d3_e, attw, spec_acc, spec_out;
+    size_t k4_smem = 0;
     DevBuf dbg_cell, dbg_level, dbg_status, dbg_e, dbg_t, dbg_rot;
     DevConfig cfg;
     int k2_blocks = 0;
     size_t k2_smem = 0;
     // timing
     bool timing = false;
-    std::vector<cudaEvent_t> ev;   // 5 events per timed execute since radop_enable_timing(1)
+    std::vector<cudaEvent_t> ev;   // 6 events per timed execute since radop_enable_timing(1)
     int n_timed = 0;
     RadopStats stats;
 
@@ -148,7 +151,7 @@ int radop_destroy(RadopHandle *h)
     DevBuf *bufs[] = {&h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
                       &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
                       &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
-                      &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
+                      &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_e, &h->attw, &h->spec_acc, &h->spec_out, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
                       &h->dbg_status, &h->dbg_e, &h->dbg_t, &h->dbg_rot};
     for (DevBuf *b : bufs) b->release();
     for (auto &l : h->lut) { l.table.release(); l.aux.release(); }
@@ -167,8 +170,10 @@ int radop_set_params(RadopHandle *h, const RadopParams *p)
     if (p->abi_version != RADOP_ABI_VERSION) return h->fail(RADOP_ERR_ARG, "RadopParams.abi_version mismatch");
     if (p->n_gates <= 0) return h->fail(RADOP_ERR_ARG, "n_gates must be positive");
     if (p->n_species <= 0 || p->n_species > RADOP_NSPECIES_MAX) return h->fail(RADOP_ERR_ARG, "bad n_species");
-    if (p->doppler_scheme != 1 && p->doppler_scheme != 2)
-        return h->fail(RADOP_ERR_UNSUPPORTED, "doppler schemes 1 and 2 are implemented on the GPU in this build");
+    if (p->doppler_scheme < 1 || p->doppler_scheme > 3)
+        return h->fail(RADOP_ERR_UNSUPPORTED, "doppler scheme must be 1, 2 or 3");
+    if (p->doppler_scheme == 3 && (p->n_vel < 2 || p->n_vel > 4096 || !(p->vel_res > 0.0)))
+        return h->fail(RADOP_ERR_ARG, "doppler scheme 3 needs 2 <= n_vel <= 4096 and vel_res > 0");
     if (p->sensitivity_mode < 0 || p->sensitivity_mode > 2)
         return h->fail(RADOP_ERR_UNSUPPORTED, "sensitivity must be [ZH] or [ZH, range]");
     for (int s = 0; s < p->n_species; ++s) {
@@ -270,6 +275,15 @@ int radop_upload_lut(RadopHandle *h, int species, const double *value_table, int
     L.dD_geo = (float)dD;
     L.dD_d = dD;
     L.dD_ref = d_axis[1] - d_axis[0];
+    L.d_min = d_axis[0]; L.d_max = d_axis[nd - 1];
+    {   // D = np.linspace(d_min, d_max, nd) as the reference forms it for the spectrum
+        // (doppler_scatter.py:686-692): float32 end points give float32 arithmetic,
+        // y = arange(nd) * ((stop - start) / (nd - 1)) + start; step_D = D[1] - D[0]
+        volatile float delta = d_axis[nd - 1] - d_axis[0];
+        volatile float step = delta / (float)(nd - 1);
+        volatile float D1 = step + d_axis[0];
+        L.spec_step = D1 - d_axis[0];
+    }
     L.packed_for = *S;
     L.packed_doppler = h->p.doppler_scheme;
     size_t rows = (size_t)ne * nt * nd;
@@ -385,9 +399,10 @@ static int prepare(RadopHandle *h)
     c.sensitivity_mode = p.sensitivity_mode; c.output_model_vars = p.output_model_vars; c.keep_debug = p.keep_debug;
     c.wavelength = (float)p.wavelength_mm; c.k_squared = (float)p.k_squared; c.radial_res = (float)p.radial_resolution_m;
     c.sens0 = (float)p.sensitivity[0]; c.sens1 = (float)p.sensitivity[1];
+    c.n_vel = p.n_vel; c.vel_min = p.vel_min; c.vel_res = p.vel_res;
     c.ice_numeric = -1;
     uint32_t need = (1u << RADOP_VAR_U) | (1u << RADOP_VAR_V) | (1u << RADOP_VAR_W) | (1u << RADOP_VAR_T);
-    int bins = 0;
+    int bins = 0, nd_max = 0;
     size_t smem = 0;
     for (int s = 0; s < p.n_species; ++s) {
         const RadopSpecies &S = p.species[s];
@@ -404,6 +419,7 @@ static int prepare(RadopHandle *h)
         need |= (1u << d.qm_var);
         if (S.psd == RADOP_PSD_2MOM) need |= (1u << d.qn_var);
         d.dD_geo = L.dD_geo; d.dD_ref = L.dD_ref; d.dD_d = L.dD_d;
+        d.d_min = L.d_min; d.d_max = L.d_max; d.spec_step = L.spec_step;
         d.table = L.table.as<float>(); d.aux = L.aux.as<float>();
         d.a = S.a; d.b = S.b; d.alpha = S.alpha; d.beta = S.beta; d.mu = S.mu; d.nu = S.nu; d.N0 = S.N0;
         d.lambda_factor = S.lambda_factor; d.vel_factor = S.vel_factor; d.ntot_factor = S.ntot_factor;
@@ -426,6 +442,9 @@ static int prepare(RadopHandle *h)
             if (c.ice_numeric >= 0) return h->fail(RADOP_ERR_UNSUPPORTED, "only one species may have numeric fall-speed moments");
             c.ice_numeric = s;
         }
+        if (p.doppler_scheme == 3 && (L.nd % 32) != 0)
+            return h->fail(RADOP_ERR_LUT, "doppler scheme 3 needs a multiple of 32 diameter bins");
+        nd_max = std::max(nd_max, L.nd);
         bins += L.ne * L.nt;
         smem = std::max(smem, (size_t)L.nd * L.ncol * 4 + (size_t)L.nd * 4);
     }
@@ -436,6 +455,7 @@ static int prepare(RadopHandle *h)
     if (h->n_sbg * p.n_species >= 0x7fffffffLL || h->n_sbg >= 0xfffffff0LL)
         return h->fail(RADOP_ERR_ARG, "scan too large for one call (rays x sub-beams x gates x species >= 2^31)");
     h->k2_smem = smem;
+    h->k4_smem = (size_t)4 * nd_max * 4 + (size_t)4 * (nd_max + 32) * 8 + (size_t)4 * std::max(p.n_vel, 1) * 4;
     return RADOP_OK;
 }
 
@@ -474,6 +494,15 @@ int radop_execute(RadopHandle *h)
     CU(h, h->sz_out.reserve((size_t)n * nsp * 8 * 4));
     CU(h, h->ice_vn.reserve((size_t)n * 8));
     if (c.doppler_scheme == 2) CU(h, h->dop_vn.reserve((size_t)n * nsp * 8));
+    if (c.doppler_scheme == 3) {
+        CU(h, h->d3_uh.reserve((size_t)n * 8));
+        CU(h, h->d3_w.reserve((size_t)n * 4));
+        CU(h, h->d3_rho.reserve((size_t)n * 4));
+        CU(h, h->d3_e.reserve((size_t)n * 4));
+        CU(h, h->attw.reserve((size_t)n * 4));
+        CU(h, h->spec_acc.reserve(n_rg * c.n_vel * 8));
+        CU(h, h->spec_out.reserve(n_rg * c.n_vel * 4));
+    }
     CU(h, h->ice_tot.reserve((size_t)c.n_rays * c.n_sub * 3 * 4));
     CU(h, h->comb.reserve(n_rg * 8 * 4));
     CU(h, h->out.reserve(n_rg * (RADOP_N_OUT + 1) * 4));
@@ -491,6 +520,8 @@ int radop_execute(RadopHandle *h)
         CU(h, cudaFuncSetAttribute(k_integrate, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_interp_psd, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_scatter_pairs, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(h, cudaFuncSetAttribute(k_spectrum, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(h, cudaFuncSetAttribute(k_beam_attenuation, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_done[h->device & 63] = true;
     }
     int occ = 1;
@@ -501,12 +532,12 @@ int radop_execute(RadopHandle *h)
     int launches = 0;
     cudaEvent_t *ev = nullptr;
     if (h->timing && h->n_timed < 4096) {
-        while ((int)h->ev.size() < 5 * (h->n_timed + 1)) {
+        while ((int)h->ev.size() < 6 * (h->n_timed + 1)) {
             cudaEvent_t e;
             CU(h, cudaEventCreate(&e));
             h->ev.push_back(e);
         }
-        ev = h->ev.data() + 5 * h->n_timed;
+        ev = h->ev.data() + 6 * h->n_timed;
         ++h->n_timed;
     }
     if (ev) CU(h, cudaEventRecord(ev[0], st));
@@ -521,6 +552,10 @@ int radop_execute(RadopHandle *h)
     o.vals = want_vals ? h->vals.as<float>() : nullptr;
     o.lat = h->lat.as<double>(); o.lon = h->lon.as<double>();
     o.hist = h->hist.as<int>(); o.flags = h->flags.as<int>();
+    if (c.doppler_scheme == 3) {
+        o.d3_uh = h->d3_uh.as<double>(); o.d3_w = h->d3_w.as<float>(); o.d3_rho = h->d3_rho.as<float>();
+        o.d3_e = h->d3_e.as<float>();
+    }
     if (c.keep_debug) {
         o.dbg_cell = h->dbg_cell.as<int>(); o.dbg_level = h->dbg_level.as<int>(); o.dbg_status = h->dbg_status.as<int>();
         o.dbg_e = h->dbg_e.as<int>(); o.dbg_t = h->dbg_t.as<int>(); o.dbg_rot = h->dbg_rot.as<double>();
@@ -575,6 +610,31 @@ int radop_execute(RadopHandle *h)
     k_ray_epilogue<<<(c.n_rays * 32 + 127) / 128, 128, 0, st>>>(c, a3);
     CU(h, cudaGetLastError()); ++launches;
     if (ev) CU(h, cudaEventRecord(ev[4], st));
+    if (c.doppler_scheme == 3) {
+        K4Args a4;
+        a4.mask = h->mask.as<int8_t>(); a4.active = h->active.as<uint8_t>(); a4.sz_out = h->sz_out.as<float>();
+        a4.sub_weight = h->scan.sub_weight;
+        a4.d3_uh = h->d3_uh.as<double>(); a4.d3_w = h->d3_w.as<float>(); a4.d3_rho = h->d3_rho.as<float>();
+        a4.d3_e = h->d3_e.as<float>(); a4.ray_nyquist = h->d_nyquist;
+        a4.attw = h->attw.as<float>(); a4.spec_acc = h->spec_acc.as<double>(); a4.spec_out = h->spec_out.as<float>();
+        a4.out = h->out.as<float>();
+        a4.hist = h->hist.as<int>(); a4.bin_start = h->bin_start.as<int>(); a4.chunk_start = h->cost_start.as<int>();
+        a4.totals = h->totals.as<long long>(); a4.counter = h->flags.as<int>() + 2; a4.rec = h->rec.as<PairRec>();
+        CU(h, cudaMemsetAsync(h->spec_acc.p, 0, n_rg * c.n_vel * 8, st));
+        const int n_rq = c.n_rays * c.n_sub;
+        const size_t smem_a = (size_t)4 * 2 * ng * 4;
+        if (smem_a > 200 * 1024) return h->fail(RADOP_ERR_ARG, "too many gates per ray for the spectrum attenuation scan");
+        k_beam_attenuation<<<(n_rq + 3) / 4, 128, smem_a, st>>>(c, a4);
+        CU(h, cudaGetLastError()); ++launches;
+        if (h->k4_smem > 200 * 1024) return h->fail(RADOP_ERR_ARG, "velocity array / diameter axis too long for the spectrum kernel");
+        int occ4 = 1;
+        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, k_spectrum, 128, h->k4_smem));
+        k_spectrum<<<std::max(1, occ4) * h->n_sm, 128, h->k4_smem, st>>>(c, a4);
+        CU(h, cudaGetLastError()); ++launches;
+        k_spectrum_finish<<<(unsigned)((n_rg * 32 + 127) / 128), 128, 0, st>>>(c, a4);
+        CU(h, cudaGetLastError()); ++launches;
+    }
+    if (ev) CU(h, cudaEventRecord(ev[5], st));
     h->stats.launches = launches;
     h->stats.n_subbeam_gates = n;
     h->executed = true;
@@ -593,22 +653,24 @@ int radop_synchronize(RadopHandle *h)
 static void average_timings(RadopHandle *h)
 {
     if (!h->n_timed) return;
-    double acc[5] = {0, 0, 0, 0, 0};
+    double acc[6] = {0, 0, 0, 0, 0, 0};
     for (int i = 0; i < h->n_timed; ++i) {
-        cudaEvent_t *e = h->ev.data() + 5 * i;
-        float ms[5] = {0, 0, 0, 0, 0};
+        cudaEvent_t *e = h->ev.data() + 6 * i;
+        float ms[6] = {0, 0, 0, 0, 0, 0};
         cudaEventElapsedTime(&ms[0], e[0], e[1]);
         cudaEventElapsedTime(&ms[1], e[1], e[2]);
         cudaEventElapsedTime(&ms[2], e[2], e[3]);
         cudaEventElapsedTime(&ms[3], e[3], e[4]);
-        cudaEventElapsedTime(&ms[4], e[0], e[4]);
-        for (int k = 0; k < 5; ++k) acc[k] += ms[k];
+        cudaEventElapsedTime(&ms[4], e[0], e[5]);
+        cudaEventElapsedTime(&ms[5], e[4], e[5]);
+        for (int k = 0; k < 6; ++k) acc[k] += ms[k];
     }
     h->stats.ms_interp = (float)(acc[0] / h->n_timed);
     h->stats.ms_sort = (float)(acc[1] / h->n_timed);
     h->stats.ms_integrate = (float)(acc[2] / h->n_timed);
     h->stats.ms_reduce = (float)(acc[3] / h->n_timed);
     h->stats.ms_total = (float)(acc[4] / h->n_timed);
+    h->stats.ms_spectrum = (float)(acc[5] / h->n_timed);
     h->stats.n_timed = h->n_timed;
 }
 
@@ -640,6 +702,10 @@ int radop_fetch(RadopHandle *h, const RadopOut *out)
         if (out->mask) CU(h, cudaMemcpyAsync(out->mask, h->out.as<float>() + (size_t)RADOP_N_OUT * n_rg, n_rg * 4, cudaMemcpyDeviceToHost, st));
         if (out->lat) CU(h, cudaMemcpyAsync(out->lat, h->lat.p, n_rg * 8, cudaMemcpyDeviceToHost, st));
         if (out->lon) CU(h, cudaMemcpyAsync(out->lon, h->lon.p, n_rg * 8, cudaMemcpyDeviceToHost, st));
+        if (out->dspectrum) {
+            if (h->cfg.doppler_scheme != 3) return h->fail(RADOP_ERR_ARG, "DSPECTRUM requested but the Doppler scheme is not 3");
+            CU(h, cudaMemcpyAsync(out->dspectrum, h->spec_out.p, n_rg * h->cfg.n_vel * 4, cudaMemcpyDeviceToHost, st));
+        }
         for (int v = 0; v < RADOP_NVAR_MAX; ++v)
             if (out->model[v]) {
                 if (!h->cfg.output_model_vars || !(h->var_mask & (1u << v))) return h->fail(RADOP_ERR_ARG, "model output requested but not computed");

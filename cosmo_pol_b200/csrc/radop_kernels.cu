@@ -531,6 +531,9 @@ struct K1Out {
     float *wind;           // [sbg] (U sin phi + V cos phi) cos theta + W sin theta
     float *sinth;          // [sbg]
     float *vsum, *nsum;    // [sbg] analytic fall-speed moments (non-numeric species)
+    // Doppler scheme 3 (spectrum): horizontal wind along the sub-beam azimuth, W, RHO, folded elevation
+    double *d3_uh;
+    float *d3_w, *d3_rho, *d3_e;
     uint16_t *key;         // [species][sbg]
     float *p0, *p1;        // [species][sbg]
     float *vals;           // [sbg][NVP] interpolated variables (model output / debug) or null
@@ -776,6 +779,15 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
             } else {
 #pragma unroll
                 for (int j = 0; j < RADOP_NVP; ++j) val[j] = qnan;
+            }
+            if (o.d3_uh) {
+                o.d3_uh[sbg] = (double)val[RADOP_VAR_U] * kc.sinA1 + (double)val[RADOP_VAR_V] * kc.cosA1;
+                o.d3_w[sbg] = val[RADOP_VAR_W];
+                o.d3_rho[sbg] = val[RADOP_VAR_RHO];
+                float ef = e_g;
+                if (ef > 90.f) ef = __fsub_rn(180.f, ef);
+                if (ef < 0.f) ef = -ef;
+                o.d3_e[sbg] = ef;
             }
             o.active[sbg] = active;
             o.wind[sbg] = wind;
@@ -1515,7 +1527,8 @@ k_ray_epilogue(const __grid_constant__ DevConfig cfg, K3Args A)
         float kdp = kfac * c[4];
         float ah = 4.343e-3f * (2.f * wl * c[6]);
         float av = 4.343e-3f * (2.f * wl * c[5]);
-        float rho = sqrtf((c[2] * c[2] + c[3] * c[3]) / (c[0] * c[1]));
+        // products of two float32 sums under- / overflow for very weak or strong echoes: float64
+        float rho = (float)sqrt(((double)c[2] * c[2] + (double)c[3] * c[3]) / ((double)c[0] * c[1]));
         float dhv = atan2f(-c[3], -c[2]);
         // PHIDP = nan_cumsum(2 KDP) * dr/1000 + DELTA_HV
         float t = isnan(kdp) ? 0.f : 2.f * kdp;
@@ -1560,6 +1573,311 @@ k_ray_epilogue(const __grid_constant__ DevConfig cfg, K3Args A)
             A.out[RADOP_OUT_ATT_V * n_rg + o] = av;
             A.out[RADOP_OUT_RVEL * n_rg + o] = rvel;
         }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K4: Doppler spectrum (scheme 3; get_doppler_spectrum doppler_scatter.py:598-725,
+//     get_diameter_from_rad_vel :546-595, get_refl doppler_c.c:11-32, attenuation :372-383)
+// ------------------------------------------------------------------------------------------
+struct K4Args {
+    const int8_t *mask;
+    const uint8_t *active;
+    const float *sz_out;
+    const double *sub_weight;
+    const double *d3_uh;
+    const float *d3_w, *d3_rho, *d3_e;
+    const float *ray_nyquist;
+    float *attw;          // [sbg] quadrature weight x attenuation factor of the sub-beam at the gate
+    double *spec_acc;     // [ray][gate][n_vel] float64 accumulator (atomics)
+    float *spec_out;      // [ray][gate][n_vel]
+    float *out;           // [N_OUT+1][ray][gate]
+    // work list of the integration kernel (pairs sorted by LUT bin)
+    const int *hist, *bin_start, *chunk_start;
+    const long long *totals;
+    int *counter;
+    const PairRec *rec;
+};
+
+// One warp per (ray, sub-beam): cumulated one-way attenuation that the reference applies to
+// the sub-beam's spectrum.  Quirk mirrored (doppler_scatter.py:298-311): the specific
+// attenuations of the VALID gates of a species are added to the beam array aligned at gate 0
+// (utilities.nansum_arr zero-pads the shorter array), i.e. gate i receives the value of the
+// i-th valid gate; the cumulative sum runs over that compacted sequence.
+extern __shared__ float s_k4a[];
+__global__ void __launch_bounds__(128)
+k_beam_attenuation(const __grid_constant__ DevConfig cfg, K4Args A)
+{
+    const int warp_in_block = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rq = blockIdx.x * (blockDim.x >> 5) + warp_in_block;
+    if (rq >= cfg.n_rays * cfg.n_sub) return;
+    const int ng = cfg.n_gates, nsp = cfg.n_species;
+    float *tmp = s_k4a + (size_t)warp_in_block * 2 * ng, *total = tmp + ng;
+    const int q = rq % cfg.n_sub;
+    const float w = (float)A.sub_weight[q];
+    const size_t base = (size_t)rq * ng;
+    for (int g = lane; g < ng; g += 32) total[g] = 0.f;
+    if (cfg.with_attenuation) {
+        const float fac = 4.343e-3f * 2.f * cfg.wavelength * (cfg.radial_res / 1000.f);
+        for (int s = 0; s < nsp; ++s) {
+            int cnt = 0;
+            float run = 0.f;
+            for (int g0 = 0; g0 < ng; g0 += 32) {
+                const int g = g0 + lane;
+                const bool valid = g < ng && (A.active[base + g] & (1u << s));
+                float x = valid ? fac * (A.sz_out[((base + g) * nsp + s) * 8 + 6] / w) : 0.f;
+                const unsigned bal = __ballot_sync(0xffffffffu, valid);
+                const int pos = cnt + __popc(bal & ((1u << lane) - 1u));
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const float t = __shfl_up_sync(0xffffffffu, x, d);
+                    if (lane >= d) x += t;
+                }
+                x += run;
+                if (valid) tmp[pos] = x;
+                run = __shfl_sync(0xffffffffu, x, 31);
+                cnt += __popc(bal);
+            }
+            __syncwarp();
+            if (cnt > 0)
+                for (int g = lane; g < ng; g += 32) total[g] += tmp[min(g, cnt - 1)];
+            __syncwarp();
+        }
+    }
+    for (int g = lane; g < ng; g += 32) A.attw[base + g] = w * exp10f(-0.1f * total[g]);
+}
+
+// Spectrum of every active (sub-beam gate, species) pair, one warp per pair.  The work list
+// is the bin-sorted pair list of the integration kernel, so the table column of a bin is staged
+// once in shared memory and reused by all its pairs.
+//   1. bin edges: fall speed needed at every velocity of VARRAY -> diameter (float64 pow, cast
+//      to float32, clipped with the reference's whole-matrix thresholds), float32 index
+//      arithmetic of get_refl for the first / last diameter sample of every velocity bin;
+//   2. prefix sums (float64) over the nd samples N(D_k) rcs(D_k) dD: lane l owns the samples
+//      [l nd/32, (l+1) nd/32), a warp scan joins the lanes;
+//   3. reflectivity of a velocity bin = difference of two prefix values, weighted with the
+//      quadrature weight and the attenuation of the sub-beam, accumulated over sub-beams and
+//      species with float64 atomics.
+extern __shared__ __align__(16) unsigned char s_k4[];
+
+__global__ void __launch_bounds__(128)
+k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
+{
+    __shared__ int s_unit;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int total_units = (int)A.totals[2];
+    const int nbins = cfg.total_bins, nsp = cfg.n_species, ng = cfg.n_gates, nvel = cfg.n_vel;
+    int nd_max = 0;
+    for (int s = 0; s < nsp; ++s) nd_max = max(nd_max, cfg.sp[s].nd);
+    // shared memory carve-up
+    float *s_col0 = reinterpret_cast<float *>(s_k4);            // b D^mu dD   (transposed)
+    float *s_auxp = s_col0 + nd_max;                            // D^nu or D^0.6357
+    float *s_colm = s_auxp + nd_max;                            // a D^b dD (1-mom ice)
+    float *s_dax = s_colm + nd_max;                             // D
+    double *s_C = reinterpret_cast<double *>(s_dax + nd_max) + (size_t)wid * (nd_max + 32);
+    double *s_base = s_C + nd_max;
+    float *s_D = reinterpret_cast<float *>(reinterpret_cast<double *>(s_dax + nd_max) + (size_t)4 * (nd_max + 32)) +
+                 (size_t)wid * nvel;
+    const float zfac3 = (float)((double)cfg.wavelength * cfg.wavelength * cfg.wavelength * cfg.wavelength /
+                                (306.0196847852814 * (double)cfg.k_squared * (double)cfg.k_squared));   // pi^5
+    int staged_bin = -1;
+
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) s_unit = atomicAdd(A.counter, 1);
+        __syncthreads();
+        const int unit = total_units - 1 - s_unit;
+        if (unit < 0) break;
+        int b;
+        {
+            int l = 0, r = nbins;
+            while (r - l > 1) {
+                int m = (l + r) >> 1;
+                if (A.chunk_start[m] <= unit) l = m; else r = m;
+            }
+            b = l;
+        }
+        int s = 0;
+        while (s + 1 < nsp && b >= cfg.sp[s + 1].bin_base) ++s;
+        const SpeciesDev &S = cfg.sp[s];
+        const int nd = S.nd, cpl = nd >> 5;          // samples per lane (nd is a multiple of 32)
+        const int cnt = A.hist[b];
+        const int tiles = (cnt + RADOP_TILE - 1) / RADOP_TILE;
+        const int j0 = (unit - A.chunk_start[b]) * RADOP_CHUNK, j1 = min(tiles, j0 + RADOP_CHUNK);
+        if (b != staged_bin) {
+            const float *tab = S.table + (size_t)(b - S.bin_base) * nd * S.ncol;
+            for (int k = tid; k < nd; k += blockDim.x) {
+                const int addr = (k % cpl) * 32 + (k / cpl);
+                s_col0[addr] = __ldg(tab + (size_t)k * S.ncol);
+                s_dax[addr] = __ldg(S.aux + k);
+                s_auxp[addr] = __ldg(S.aux + (S.mode == MODE_ICE1 ? 2 * nd : nd) + k);
+                s_colm[addr] = (S.mode == MODE_ICE1) ? __ldg(tab + (size_t)k * S.ncol + 9) : 0.f;
+            }
+            staged_bin = b;
+            __syncthreads();
+        }
+        // clip limits of the species that follow s (only the present ones apply, per gate)
+        for (int jt = j0; jt < j1; ++jt) {
+            const int first = A.bin_start[b] + jt * RADOP_TILE;
+            const int n_here = min(RADOP_TILE, cnt - jt * RADOP_TILE);
+            for (int i = wid; i < n_here; i += 4) {
+                const PairRec rec = A.rec[first + i];
+                const uint32_t sbg = rec.sbg;
+                const int g = (int)(sbg % (unsigned)ng);
+                const size_t rg = (size_t)(sbg / (unsigned)ng / (unsigned)cfg.n_sub) * ng + g;
+                const unsigned act = A.active[sbg];
+                // ---- 1. diameters at the velocity-bin edges -----------------------------------
+                {
+                    const float theta = __fmul_rn(A.d3_e[sbg], 0.017453292519943295f);
+                    const double tan_t = (double)(float)tan((double)theta), sin_t = (double)(float)sin((double)theta);
+                    const float rho_corr = sqrtf(__fdiv_rn(A.d3_rho[sbg], A.d3_rho[sbg - g]));
+                    const double inv_rho = (double)__fdiv_rn(1.0f, rho_corr);
+                    const double c0 = (double)A.d3_w[sbg] + A.d3_uh[sbg] / tan_t;
+                    const double inv_beta = 1.0 / S.beta;
+                    for (int j = lane; j < nvel; j += 32) {
+                        const double v = cfg.vel_min + (double)j * cfg.vel_res;
+                        const double wh = inv_rho * (c0 - v / sin_t);
+                        float D = __int_as_float(0x7fc00000);
+                        if (wh >= 0.0) {
+                            D = (float)pow(wh / S.alpha, inv_beta);
+                            for (int t = s; t < nsp; ++t) {
+                                if (!(act & (1u << t))) continue;
+                                if (D >= cfg.sp[t].d_max) D = cfg.sp[t].d_max;
+                                if (D <= cfg.sp[t].d_min) D = cfg.sp[t].d_min;
+                            }
+                        }
+                        s_D[j] = D;
+                    }
+                }
+                // ---- 2. prefix sums of N(D_k) rcs(D_k) dD over this lane's samples ------------
+                double loc = 0.0;
+                float n0 = rec.p1;
+                const int k0 = lane * cpl;
+                if (S.mode == MODE_ICE1) {
+                    const float lam = rec.p0;
+                    const float a1 = -20.78f * LOG2E * lam, a2 = -3.290f * LOG2E * lam;
+                    const float c2 = 17.46f * exp2f(0.6357f * log2f(lam));
+                    const float r1 = ex2f_approx(a1 * S.dD_geo), r2 = ex2f_approx(a2 * S.dD_geo);
+                    const float d0 = s_dax[lane];
+                    float E1 = 490.6f * ex2f_approx(a1 * d0), E2 = c2 * ex2f_approx(a2 * d0);
+                    float mass = 0.f;
+                    for (int ii = 0; ii < cpl; ++ii) {
+                        const int ad = ii * 32 + lane;
+                        const float phi = fmaf(s_auxp[ad], E2, E1);
+                        mass = fmaf(s_colm[ad], phi, mass);
+                        loc += (double)(s_col0[ad] * phi);
+                        s_C[ad] = loc;
+                        E1 *= r1; E2 *= r2;
+                    }
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1) mass += __shfl_xor_sync(0xffffffffu, mass, d);
+                    n0 = rec.p1 / mass;          // hydrometeors.py:1330-1339
+                } else if (S.mode == MODE_GEO8) {
+                    const float a = -LOG2E * rec.p0;
+                    const float r = ex2f_approx(a * S.dD_geo);
+                    float E = ex2f_approx(a * s_dax[lane]);
+                    for (int ii = 0; ii < cpl; ++ii) {
+                        const int ad = ii * 32 + lane;
+                        loc += (double)(s_col0[ad] * E);
+                        s_C[ad] = loc;
+                        E *= r;
+                    }
+                } else {
+                    const float a = -LOG2E * rec.p0;
+                    for (int ii = 0; ii < cpl; ++ii) {
+                        const int ad = ii * 32 + lane;
+                        loc += (double)(s_col0[ad] * ex2f_approx(a * s_auxp[ad]));
+                        s_C[ad] = loc;
+                    }
+                }
+                {   // exclusive scan of the lane totals
+                    double x = loc;
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+                        const double t = __shfl_up_sync(0xffffffffu, x, d);
+                        if (lane >= d) x += t;
+                    }
+                    const double prev = __shfl_up_sync(0xffffffffu, x, 1);
+                    s_base[lane] = lane ? prev : 0.0;
+                }
+                __syncwarp();
+                // ---- 3. velocity bins -----------------------------------------------------------
+                const double scale = 6.283185307179586 * (double)n0 * (double)zfac3 * (double)A.attw[sbg] *
+                                     ((double)S.spec_step / (double)S.dD_ref);
+                double *dst = A.spec_acc + rg * nvel;
+                (void)k0;
+                for (int j = lane; j + 1 < nvel; j += 32) {
+                    const float Dj = s_D[j];
+                    if (isnan(Dj)) continue;
+                    int jn = j + 1;
+                    while (jn < nvel && isnan(s_D[jn])) ++jn;
+                    if (jn >= nvel) continue;
+                    const float Dn = s_D[jn];
+                    const float Da = fminf(Dj, Dn), Db = fmaxf(Dj, Dn);
+                    const int ia = (int)__fdiv_rn(__fsub_rn(Da, S.d_min), S.spec_step);
+                    const int ib = min((int)__fdiv_rn(__fsub_rn(Db, S.d_min), S.spec_step), nd);
+                    if (ib <= ia || ia < 0) continue;
+                    const int kb = ib - 1, ka = ia - 1;
+                    const int lb = kb / cpl, la = (ka >= 0) ? ka / cpl : -1;
+                    const double cb = s_C[(kb % cpl) * 32 + lb];
+                    const double ca = (ka >= 0) ? s_C[(ka % cpl) * 32 + la] : 0.0;
+                    double diff;
+                    if (la == lb) diff = cb - ca;               // same lane: one running sum, exact order
+                    else {
+                        const double hi = s_base[lb] + cb, lo = (ka >= 0) ? s_base[la] + ca : 0.0;
+                        diff = hi - lo;
+                        if (fabs(diff) < 2e-15 * fabs(hi)) diff = 0.0;      // rounding of the lane bases
+                    }
+                    const double val = diff * scale;
+                    if (val != 0.0) atomicAdd(dst + j, val);
+                }
+                __syncwarp();
+            }
+        }
+    }
+}
+
+// One warp per (ray, gate): float32 spectrum, RVEL = sum(v S) / sum(S) (doppler_scatter.py:422-429),
+// aliasing, sensitivity cut of the spectrum bins (doppler_scatter.py:843-849).
+__global__ void __launch_bounds__(128)
+k_spectrum_finish(const __grid_constant__ DevConfig cfg, K4Args A)
+{
+    const long long wg = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const long long n_rg = (long long)cfg.n_rays * cfg.n_gates;
+    if (wg >= n_rg) return;
+    const int g = (int)(wg % cfg.n_gates), ray = (int)(wg / cfg.n_gates);
+    const int nvel = cfg.n_vel;
+    const double *src = A.spec_acc + (size_t)wg * nvel;
+    float *dst = A.spec_out + (size_t)wg * nvel;
+    const float qnan = __int_as_float(0x7fc00000);
+    float thr = 0.f;
+    if (cfg.sensitivity_mode == 1) thr = cfg.sens0;
+    else if (cfg.sensitivity_mode == 2)
+        thr = (cfg.sens0 - 20.f * log10f(cfg.sens1 / 1000.f)) + 20.f * log10f((cfg.radial_res * (float)g) / 1000.f);
+    double sv = 0.0, ss = 0.0;
+    for (int j = lane; j < nvel; j += 32) {
+        const double x = src[j];
+        sv += (cfg.vel_min + (double)j * cfg.vel_res) * x;
+        ss += x;
+        float o = (float)x;
+        if (cfg.sensitivity_mode && 10.f * log10f(o) < thr) o = qnan;
+        dst[j] = o;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        sv += __shfl_xor_sync(0xffffffffu, sv, d);
+        ss += __shfl_xor_sync(0xffffffffu, ss, d);
+    }
+    if (lane == 0) {
+        float rvel = (float)(sv / ss);          // 0/0 -> NaN where nothing falls
+        if (A.ray_nyquist) {
+            const float PI = 3.14159265358979323846f, nyq = A.ray_nyquist[ray];
+            const float th = (rvel + nyq) / (2.f * nyq) * PI - PI / 2.f;
+            rvel = (atanf(tanf(th)) + PI / 2.f) * (2.f * nyq) / PI - nyq;
+        }
+        if (cfg.sensitivity_mode && isnan(A.out[(size_t)RADOP_OUT_ZH * n_rg + wg])) rvel = qnan;
+        A.out[(size_t)RADOP_OUT_RVEL * n_rg + wg] = rvel;
     }
 }
 

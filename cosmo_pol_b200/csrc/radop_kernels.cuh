@@ -29,6 +29,9 @@ struct SpeciesDev {
     int qm_var, qn_var;         // RADOP_VAR_* holding mass / number density
     float dD_geo;               // (D[nd-1]-D[0])/(nd-1) computed in double
     float dD_ref;               // D[1]-D[0] in float32 (doppler_scatter.py:224)
+    float d_min, d_max;         // first / last diameter of the table axis (float32)
+    float spec_step;            // float32(np.linspace(d_min, d_max, nd))[1] - [0]: step_D of the spectrum
+                                // (doppler_scatter.py:686-692; differs from dD_ref by ulps)
     double dD_d;                // dD_geo in float64
     const float *table;         // [ne][nt][nd][ncol] combined + premultiplied columns
     const float *aux;           // [3][nd]: D, D^nu, D^0.6357
@@ -60,6 +63,9 @@ struct DevConfig {
     int output_model_vars, keep_debug, ice_numeric;   // ice_numeric: species index with numeric v,n or -1
     float wavelength, k_squared, radial_res;
     float sens0, sens1;
+    // Doppler spectrum (scheme 3): VARRAY[j] = vel_min + j vel_res, j < n_vel (global_constants.py:168-171)
+    int n_vel;
+    double vel_min, vel_res;
     SpeciesDev sp[RADOP_NSPECIES_MAX];
 };
 

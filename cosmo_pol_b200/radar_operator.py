@@ -308,6 +308,10 @@ class RadarOperator(object):
         lon = torch.from_numpy(np.array(arrays['lon'], copy=True)[None]).cuda(eng.device)
         out['lat'] = parallel.all_gather_rays(lat, n_total)[0].cpu().numpy()
         out['lon'] = parallel.all_gather_rays(lon, n_total)[0].cpu().numpy()
+        if 'DSPECTRUM' in arrays:
+            sp = np.array(arrays['DSPECTRUM'], copy=True)          # [n_local, n_gates, n_vel]
+            loc = torch.from_numpy(np.ascontiguousarray(sp.transpose(2, 0, 1))).cuda(eng.device)
+            out['DSPECTRUM'] = np.ascontiguousarray(parallel.all_gather_rays(loc, n_total).cpu().numpy().transpose(1, 2, 0))
         if want_model:
             names = list(eng.uploaded_vars)
             loc = torch.from_numpy(np.stack([arrays[n] for n in names])).cuda(eng.device)
@@ -327,6 +331,9 @@ class RadarOperator(object):
             names += [n for n in VAR_IDS if n in out]
         shp = (n_sweeps, n_per, -1)
         fields = {n: out[n].reshape(shp) for n in names}
+        if 'DSPECTRUM' in out and self.output_variables in ('all', 'only_radar'):
+            sp = out['DSPECTRUM']
+            fields['DSPECTRUM'] = sp.reshape((n_sweeps, n_per) + sp.shape[1:])
         return SimulatedScan(scan_type, elevations, azimuths, constants.RANGE_RADAR, self.get_pos_and_time(), fields,
                              out['mask'].reshape(shp), out['lat'].reshape(shp), out['lon'].reshape(shp),
                              out['dist'].reshape(shp), out['heights'].reshape(shp))

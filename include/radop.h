@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define RADOP_ABI_VERSION 1
+#define RADOP_ABI_VERSION 2
 
 /* ---- status codes ------------------------------------------------------- */
 enum {
@@ -93,7 +93,8 @@ typedef struct {
     double radial_resolution_m;   /* CONFIG['radar']['radial_resolution']                 */
     int32_t two_moment;           /* CONFIG['microphysics']['scheme'] == '2mom'           */
     int32_t with_attenuation;     /* CONFIG['microphysics']['with_attenuation']           */
-    int32_t doppler_scheme;       /* CONFIG['doppler']['scheme']: 1 analytic, 2 rcs-weighted    */
+    int32_t doppler_scheme;       /* CONFIG['doppler']['scheme']: 1 analytic, 2 rcs-weighted,
+                                     3 full spectrum (get_doppler_spectrum :598-725)       */
     int32_t sensitivity_mode;     /* 0: no cut; 1: [ZH]; 2: [ZH, range]; cut_at_sensitivity */
     double sensitivity[3];
     int32_t output_model_vars;    /* integrate_radials outputs wanted ('all'/'only_model') */
@@ -101,6 +102,11 @@ typedef struct {
     int32_t n_species;
     int32_t reserved;
     RadopSpecies species[RADOP_NSPECIES_MAX];   /* in summation order                      */
+    /* Doppler scheme 3: constants.VARRAY = vel_min + j * vel_res, j < n_vel
+       (np.arange(-NVEL, NVEL + VRES, VRES), global_constants.py:168-171)                  */
+    int32_t n_vel;
+    int32_t reserved2;
+    double vel_min, vel_res;
 } RadopParams;
 
 /*
@@ -139,6 +145,7 @@ typedef struct {
     float *mask;                      /* averaged sub-beam mask, doppler_scatter.py:472-477 */
     double *lat, *lon;                /* central sub-beam gate positions (WGS84)           */
     float *model[RADOP_NVAR_MAX];     /* integrate_radials of each uploaded variable       */
+    float *dspectrum;                 /* [n_rays][n_gates][n_vel] DSPECTRUM (Doppler scheme 3) */
 } RadopOut;
 
 typedef struct RadopHandle_ RadopHandle;
@@ -192,7 +199,7 @@ typedef struct {
     float ms_interp, ms_sort, ms_integrate, ms_reduce, ms_total;  /* CUDA-event times: mean
                                      over the executes since radop_enable_timing(h, 1)     */
     int32_t n_timed;              /* executes in that mean                                  */
-    int32_t reserved;
+    float ms_spectrum;            /* Doppler-spectrum kernels (scheme 3), included in ms_total */
 } RadopStats;
 int radop_get_stats(RadopHandle *h, RadopStats *s);
 int radop_enable_timing(RadopHandle *h, int on);

@@ -239,6 +239,73 @@ def test_doppler_scheme2_against_oracle(scheme, freq):
     assert np.nanmax(np.abs(out1['RVEL'] - a)) > 0.05
 
 
+def _spectrum_close(a, b, zh, what):
+    """DSPECTRUM against the oracle: bin by bin to 1e-4 of the gate's strongest bin, cumulative
+    power along the velocity axis (robust against a diameter sample sitting exactly on a
+    velocity-bin edge, float32 index arithmetic of get_refl, doppler_c.c:23-24) and total power.
+    Gates whose spectrum holds less than 1e-9 of the gate's reflectivity (far PSD tails that
+    underflow float32) are only required to be weak on the GPU as well."""
+    a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    a = np.nan_to_num(a, nan=0.0)        # get_PPI censors empty bins to NaN (doppler_scatter.py:843-849)
+    tot = b.sum(axis=-1)
+    zh = np.nan_to_num(np.asarray(zh, dtype=np.float64))
+    ok = tot > 1e-9 * np.maximum(zh, 1e-30)
+    assert ok.sum() > 10, what
+    assert np.all(a.sum(axis=-1)[tot == 0] == 0), what + ': power where the reference has none'
+    assert np.all(a.sum(axis=-1)[~ok] <= 2e-9 * np.maximum(zh, 1e-30)[~ok]), what
+    ca, cb = np.cumsum(a, axis=-1)[ok], np.cumsum(b, axis=-1)[ok]
+    err = np.max(np.abs(ca - cb), axis=-1) / tot[ok]
+    assert np.max(np.abs(ca[:, -1] - cb[:, -1]) / tot[ok]) < 2e-4, (what, 'total power')
+    assert np.quantile(err, 0.99) < 2e-4 and np.max(err) < 0.05, (what, np.quantile(err, 0.99), np.max(err))
+    exact = np.abs(a[ok] - b[ok]) <= 1e-4 * np.max(b[ok], axis=-1, keepdims=True)
+    assert exact.mean() > 0.999, (what, exact.mean())
+    return ok
+
+
+@pytest.mark.parametrize('scheme,freq', [('1mom', 5.6), ('2mom', 9.41)])
+def test_doppler_spectrum_against_oracle(scheme, freq):
+    """Doppler scheme 3: DSPECTRUM and the spectrum-derived RVEL (doppler_scatter.py:336-383, 422-429,
+    598-725; doppler_c.c)."""
+    conf = copy.deepcopy(CONF_1MOM)
+    conf['doppler'] = {'scheme': 3}
+    conf['radar'].update({'FFT_length': 64, 'sensitivity': [-300, 10000]})
+    op, model, luts = make_operator(conf, scheme, freq)
+    az = np.array([5., 95., 185., 275.])
+    els = [1.0, 8.5, 35.0]
+    rays_az, rays_el = np.tile(az, len(els)), np.repeat(els, len(az))
+    out = op.simulate_rays(rays_az, rays_el)
+    pm, pl = plain(model, luts)
+    ref = O.simulate_scan(pm, pl, oracle_cfg(op), rays_az, rays_el, accum='f64', sensitivity_cut=True)
+    assert_observables_close(out, ref, what='dop3 ' + scheme)
+    strong = _spectrum_close(out['DSPECTRUM'], ref['DSPECTRUM'], ref['ZH'], 'dop3 ' + scheme)
+    a, b = out['RVEL'], ref['RVEL']
+    assert np.all(np.isnan(a[np.isnan(b)])) and np.all(np.isfinite(a[strong]))
+    ok = np.isfinite(b) & strong
+    assert ok.sum() > 100
+    assert np.quantile(np.abs(a[ok] - b[ok]), 0.99) < 1e-3 and np.max(np.abs(a[ok] - b[ok])) < 0.05
+
+
+def test_doppler_spectrum_against_reference_golden():
+    from cosmo_pol_b200 import RadarOperator
+    g, cfg, kw = load_golden_case('c1mom_dop3')
+    model, luts = synthetic_inputs('1mom', 5.6, **kw)
+    conf = copy.deepcopy(cfg)
+    conf['radar']['sensitivity'] = [-300, 10000]
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    rays = g['rays']
+    out = op.simulate_rays(rays[:, 0], rays[:, 1])
+    ref = {k[4:]: g[k] for k in g.files if k.startswith('obs_')}
+    assert_observables_close(out, ref, sz_scale=5e-4 * np.abs(ref['KDP']), what='golden dop3')
+    strong = _spectrum_close(out['DSPECTRUM'], ref['DSPECTRUM'], ref['ZH'], 'golden dop3')
+    a, b = out['RVEL'], ref['RVEL']
+    assert np.all(np.isnan(a[np.isnan(b)])) and np.all(np.isfinite(a[strong]))
+    ok = np.isfinite(b) & strong
+    assert np.max(np.abs(a[ok] - b[ok])) < 0.05
+
+
 def test_edge_cases_and_errors():
     from cosmo_pol_b200 import RadarOperator
     from cosmo_pol_b200._abi import RadopError
@@ -268,7 +335,7 @@ def test_edge_cases_and_errors():
     pm, pl = plain(model, luts)
     ref = O.simulate_scan(pm, pl, oracle_cfg(op), [5.], [2.], accum='f64', sensitivity_cut=True)
     assert_observables_close({k: v[0] for k, v in r1.fields.items()}, ref, what='1x1')
-    conf['doppler'] = {'scheme': 3}
+    conf['doppler'] = {'scheme': 3, 'motion_correction': 1}
     op = RadarOperator(conf, output_variables='only_radar', device=0)
     op.set_lut(luts)
     op.load_model(model)
