@@ -49,7 +49,10 @@ struct LutHost {
 
 struct RadopHandle_ {
     int device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    std::vector<cudaEvent_t> chunk_done;
+    long long chunk_sbg = 8000000;   // sub-beam gates per chunk (0: one chunk)
+    int n_chunks = 1, n_exec_timed = 0;
     std::string err;
     int n_sm = 148;
     // configuration
@@ -132,7 +135,8 @@ int radop_create(int device, RadopHandle **out)
     }
     RadopHandle *h = new RadopHandle_();
     h->device = device;
-    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
         delete h;
         return RADOP_ERR_CUDA;
     }
@@ -157,6 +161,8 @@ int radop_destroy(RadopHandle *h)
     for (auto &l : h->lut) { l.table.release(); l.aux.release(); }
     if (h->pinned) cudaFreeHost(h->pinned);
     for (auto &e : h->ev) cudaEventDestroy(e);
+    for (auto &e : h->chunk_done) cudaEventDestroy(e);
+    cudaStreamDestroy(h->copy_stream);
     cudaStreamDestroy(h->stream);
     delete h;
     return RADOP_OK;
@@ -452,25 +458,62 @@ static int prepare(RadopHandle *h)
     if (bins >= 0xFFFF) return h->fail(RADOP_ERR_LUT, "too many (species, e, t) bins");
     if (bins * 4 > 200 * 1024) return h->fail(RADOP_ERR_LUT, "bin histogram does not fit shared memory");
     c.total_bins = bins;
-    if (h->n_sbg * p.n_species >= 0x7fffffffLL || h->n_sbg >= 0xfffffff0LL)
-        return h->fail(RADOP_ERR_ARG, "scan too large for one call (rays x sub-beams x gates x species >= 2^31)");
     h->k2_smem = smem;
     h->k4_smem = (size_t)4 * nd_max * 4 + (size_t)4 * (nd_max + 32) * 8 + (size_t)4 * std::max(p.n_vel, 1) * 4;
     return RADOP_OK;
 }
 
-int radop_execute(RadopHandle *h)
+// Device -> host copies of the rays [r0, r0 + nr) of every requested output, on stream st.
+static int copy_outputs(RadopHandle *h, const RadopOut *out, int r0, int nr, cudaStream_t st)
 {
-    if (!h) return RADOP_ERR_ARG;
+    const int ng = h->cfg.n_gates;
+    const size_t n_rg = (size_t)h->n_rays * ng, off = (size_t)r0 * ng, cnt = (size_t)nr * ng;
+    for (int v = 0; v < RADOP_N_OUT; ++v)
+        if (out->obs[v]) CU(h, cudaMemcpyAsync(out->obs[v] + off, h->out.as<float>() + (size_t)v * n_rg + off, cnt * 4, cudaMemcpyDeviceToHost, st));
+    if (out->mask) CU(h, cudaMemcpyAsync(out->mask + off, h->out.as<float>() + (size_t)RADOP_N_OUT * n_rg + off, cnt * 4, cudaMemcpyDeviceToHost, st));
+    if (out->lat) CU(h, cudaMemcpyAsync(out->lat + off, h->lat.as<double>() + off, cnt * 8, cudaMemcpyDeviceToHost, st));
+    if (out->lon) CU(h, cudaMemcpyAsync(out->lon + off, h->lon.as<double>() + off, cnt * 8, cudaMemcpyDeviceToHost, st));
+    if (out->dspectrum) {
+        if (h->cfg.doppler_scheme != 3) return h->fail(RADOP_ERR_ARG, "DSPECTRUM requested but the Doppler scheme is not 3");
+        const size_t nv = (size_t)h->cfg.n_vel;
+        CU(h, cudaMemcpyAsync(out->dspectrum + off * nv, h->spec_out.as<float>() + off * nv, cnt * nv * 4, cudaMemcpyDeviceToHost, st));
+    }
+    for (int v = 0; v < RADOP_NVAR_MAX; ++v)
+        if (out->model[v]) {
+            if (!h->cfg.output_model_vars || !(h->var_mask & (1u << v))) return h->fail(RADOP_ERR_ARG, "model output requested but not computed");
+            CU(h, cudaMemcpyAsync(out->model[v] + off, h->model_out.as<float>() + (size_t)v * n_rg + off, cnt * 4, cudaMemcpyDeviceToHost, st));
+        }
+    return RADOP_OK;
+}
+
+// The launch sequence of the hot path.  The ray list is processed in chunks of about
+// h->chunk_sbg sub-beam gates: the work arrays are sized for one chunk, the outputs for the
+// whole scan.  With `out` given, the device -> host copies of a chunk run on a second stream
+// while the next chunk computes.
+static int run_scan(RadopHandle *h, const RadopOut *out)
+{
     int rc = prepare(h);
     if (rc) return rc;
     CU(h, cudaSetDevice(h->device));
-    const DevConfig &c = h->cfg;
-    const long long n = h->n_sbg;
+    DevConfig &c = h->cfg;
     const int nsp = c.n_species, ng = c.n_gates;
-    const size_t n_rg = (size_t)c.n_rays * ng;
+    const int n_rays = h->n_rays;
+    const size_t n_rg = (size_t)n_rays * ng;
     const bool want_vals = c.output_model_vars || c.keep_debug;
-    CU(h, h->geo.reserve((size_t)c.n_rays * c.n_sub * sizeof(SubGeo)));
+    // ---- chunking --------------------------------------------------------------------------
+    const long long per_ray = (long long)c.n_sub * ng;
+    int n_chunks = 1;
+    // without host copies to overlap, chunks only bound the work memory (8x larger chunks)
+    const long long target = out ? h->chunk_sbg : 8 * h->chunk_sbg;
+    if (!c.keep_debug && target > 0)
+        n_chunks = (int)std::min<long long>(n_rays, std::max<long long>(1, (h->n_sbg + target / 2) / target));
+    const int rays_per_chunk = (n_rays + n_chunks - 1) / n_chunks;
+    n_chunks = (n_rays + rays_per_chunk - 1) / rays_per_chunk;
+    const long long n = (long long)rays_per_chunk * per_ray;          // sub-beam gates of the largest chunk
+    const size_t c_rg = (size_t)rays_per_chunk * ng;
+    if (n * nsp >= 0x7fffffffLL || n >= 0xfffffff0LL)
+        return h->fail(RADOP_ERR_ARG, "chunk too large (rays x sub-beams x gates x species >= 2^31): lower the chunk size");
+    CU(h, h->geo.reserve((size_t)rays_per_chunk * c.n_sub * sizeof(SubGeo)));
     CU(h, h->mask.reserve(n));
     CU(h, h->active.reserve(n));
     CU(h, h->wind.reserve(n * 4));
@@ -489,7 +532,7 @@ int radop_execute(RadopHandle *h)
     CU(h, h->tile_start.reserve((size_t)(c.total_bins + 1) * 4));
     CU(h, h->cost_start.reserve((size_t)(c.total_bins + 1) * 8));
     CU(h, h->cursor.reserve((size_t)c.total_bins * 4));
-    CU(h, h->totals.reserve(4 * 8));
+    CU(h, h->totals.reserve((size_t)n_chunks * 4 * 8));
     CU(h, h->rec.reserve((size_t)n * nsp * sizeof(PairRec)));
     CU(h, h->sz_out.reserve((size_t)n * nsp * 8 * 4));
     CU(h, h->ice_vn.reserve((size_t)n * 8));
@@ -500,11 +543,11 @@ int radop_execute(RadopHandle *h)
         CU(h, h->d3_rho.reserve((size_t)n * 4));
         CU(h, h->d3_e.reserve((size_t)n * 4));
         CU(h, h->attw.reserve((size_t)n * 4));
-        CU(h, h->spec_acc.reserve(n_rg * c.n_vel * 8));
+        CU(h, h->spec_acc.reserve(c_rg * c.n_vel * 8));
         CU(h, h->spec_out.reserve(n_rg * c.n_vel * 4));
     }
-    CU(h, h->ice_tot.reserve((size_t)c.n_rays * c.n_sub * 3 * 4));
-    CU(h, h->comb.reserve(n_rg * 8 * 4));
+    CU(h, h->ice_tot.reserve((size_t)rays_per_chunk * c.n_sub * 3 * 4));
+    CU(h, h->comb.reserve(c_rg * 8 * 4));
     CU(h, h->out.reserve(n_rg * (RADOP_N_OUT + 1) * 4));
     if (c.output_model_vars) CU(h, h->model_out.reserve(n_rg * RADOP_NVP * 4));
     if (c.keep_debug) {
@@ -527,118 +570,154 @@ int radop_execute(RadopHandle *h)
     int occ = 1;
     CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_integrate, RADOP_TILE_THREADS, h->k2_smem));
     h->k2_blocks = std::max(1, occ) * h->n_sm;
+    const size_t hist_smem = (size_t)c.total_bins * 4;
+    int occ1 = 1;
+    CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, k_interp_psd, 128, hist_smem));
+    const size_t smem_a = (size_t)4 * 2 * ng * 4;
+    int occ4 = 1;
+    if (c.doppler_scheme == 3) {
+        if (smem_a > 200 * 1024) return h->fail(RADOP_ERR_ARG, "too many gates per ray for the spectrum attenuation scan");
+        if (h->k4_smem > 200 * 1024) return h->fail(RADOP_ERR_ARG, "velocity array / diameter axis too long for the spectrum kernel");
+        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, k_spectrum, 128, h->k4_smem));
+    }
+    while ((int)h->chunk_done.size() < n_chunks) {
+        cudaEvent_t e;
+        CU(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        h->chunk_done.push_back(e);
+    }
 
     cudaStream_t st = h->stream;
     int launches = 0;
-    cudaEvent_t *ev = nullptr;
-    if (h->timing && h->n_timed < 4096) {
-        while ((int)h->ev.size() < 6 * (h->n_timed + 1)) {
-            cudaEvent_t e;
-            CU(h, cudaEventCreate(&e));
-            h->ev.push_back(e);
+    const bool timed = h->timing && h->n_timed + n_chunks <= 16384;
+    if (timed) ++h->n_exec_timed;
+    CU(h, cudaMemsetAsync(h->flags.p, 0, 4, st));
+    c.out_stride = (long long)n_rg;
+
+    for (int ch = 0; ch < n_chunks; ++ch) {
+        const int r0 = ch * rays_per_chunk, nr = std::min(rays_per_chunk, n_rays - r0);
+        c.n_rays = nr;
+        const long long nc = (long long)nr * per_ray;
+        const size_t cc_rg = (size_t)nr * ng, off_rg = (size_t)r0 * ng;
+        cudaEvent_t *ev = nullptr;
+        if (timed) {
+            while ((int)h->ev.size() < 6 * (h->n_timed + 1)) {
+                cudaEvent_t e;
+                CU(h, cudaEventCreate(&e));
+                h->ev.push_back(e);
+            }
+            ev = h->ev.data() + 6 * h->n_timed;
+            ++h->n_timed;
         }
-        ev = h->ev.data() + 6 * h->n_timed;
-        ++h->n_timed;
-    }
-    if (ev) CU(h, cudaEventRecord(ev[0], st));
-    CU(h, cudaMemsetAsync(h->hist.p, 0, (size_t)c.total_bins * 4, st));
-    CU(h, cudaMemsetAsync(h->flags.p, 0, 16, st));
+        if (ev) CU(h, cudaEventRecord(ev[0], st));
+        CU(h, cudaMemsetAsync(h->hist.p, 0, (size_t)c.total_bins * 4, st));
+        CU(h, cudaMemsetAsync(h->flags.as<int>() + 1, 0, 12, st));
+        ScanDev scan = h->scan;
+        scan.ray_az += r0;
+        scan.ray_traj += r0;
+        const float *nyq = h->d_nyquist ? h->d_nyquist + r0 : nullptr;
+        long long *totals = h->totals.as<long long>() + 4 * ch;
 
-    K1Out o;
-    memset(&o, 0, sizeof o);
-    o.mask = h->mask.as<int8_t>(); o.active = h->active.as<uint8_t>();
-    o.wind = h->wind.as<float>(); o.sinth = h->sinth.as<float>(); o.vsum = h->vsum.as<float>(); o.nsum = h->nsum.as<float>();
-    o.key = h->key.as<uint16_t>(); o.p0 = h->p0.as<float>(); o.p1 = h->p1.as<float>();
-    o.vals = want_vals ? h->vals.as<float>() : nullptr;
-    o.lat = h->lat.as<double>(); o.lon = h->lon.as<double>();
-    o.hist = h->hist.as<int>(); o.flags = h->flags.as<int>();
-    if (c.doppler_scheme == 3) {
-        o.d3_uh = h->d3_uh.as<double>(); o.d3_w = h->d3_w.as<float>(); o.d3_rho = h->d3_rho.as<float>();
-        o.d3_e = h->d3_e.as<float>();
-    }
-    if (c.keep_debug) {
-        o.dbg_cell = h->dbg_cell.as<int>(); o.dbg_level = h->dbg_level.as<int>(); o.dbg_status = h->dbg_status.as<int>();
-        o.dbg_e = h->dbg_e.as<int>(); o.dbg_t = h->dbg_t.as<int>(); o.dbg_rot = h->dbg_rot.as<double>();
-    }
-    const size_t hist_smem = (size_t)c.total_bins * 4;
-    {
-        const int n_rq = c.n_rays * c.n_sub;
-        k_sub_geometry<<<(n_rq + 127) / 128, 128, 0, st>>>(c.n_rays, c.n_sub, c.radar_lat, h->scan.ray_az, h->scan.sub_daz,
-                                                          h->geo.as<SubGeo>());
-        CU(h, cudaGetLastError()); ++launches;
-        int occ1 = 1;
-        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, k_interp_psd, 128, hist_smem));
-        const long long want = (n + 127) / 128;
-        const unsigned grid1 = (unsigned)std::min<long long>(want, (long long)std::max(1, occ1) * h->n_sm);
-        k_interp_psd<<<grid1, 128, hist_smem, st>>>(c, h->scan, h->geo.as<SubGeo>(), h->z_t.as<float>(), h->fields.as<float>(), o, n);
-        CU(h, cudaGetLastError()); ++launches;
-    }
-    if (ev) CU(h, cudaEventRecord(ev[1], st));
+        K1Out o;
+        memset(&o, 0, sizeof o);
+        o.mask = h->mask.as<int8_t>(); o.active = h->active.as<uint8_t>();
+        o.wind = h->wind.as<float>(); o.sinth = h->sinth.as<float>(); o.vsum = h->vsum.as<float>(); o.nsum = h->nsum.as<float>();
+        o.key = h->key.as<uint16_t>(); o.p0 = h->p0.as<float>(); o.p1 = h->p1.as<float>();
+        o.vals = want_vals ? h->vals.as<float>() : nullptr;
+        o.lat = h->lat.as<double>() + off_rg; o.lon = h->lon.as<double>() + off_rg;
+        o.hist = h->hist.as<int>(); o.flags = h->flags.as<int>();
+        if (c.doppler_scheme == 3) {
+            o.d3_uh = h->d3_uh.as<double>(); o.d3_w = h->d3_w.as<float>(); o.d3_rho = h->d3_rho.as<float>();
+            o.d3_e = h->d3_e.as<float>();
+        }
+        if (c.keep_debug) {
+            o.dbg_cell = h->dbg_cell.as<int>(); o.dbg_level = h->dbg_level.as<int>(); o.dbg_status = h->dbg_status.as<int>();
+            o.dbg_e = h->dbg_e.as<int>(); o.dbg_t = h->dbg_t.as<int>(); o.dbg_rot = h->dbg_rot.as<double>();
+        }
+        {
+            const int n_rq = nr * c.n_sub;
+            k_sub_geometry<<<(n_rq + 127) / 128, 128, 0, st>>>(nr, c.n_sub, c.radar_lat, scan.ray_az, scan.sub_daz, h->geo.as<SubGeo>());
+            CU(h, cudaGetLastError()); ++launches;
+            const long long want = (nc + 127) / 128;
+            const unsigned grid1 = (unsigned)std::min<long long>(want, (long long)std::max(1, occ1) * h->n_sm);
+            k_interp_psd<<<grid1, 128, hist_smem, st>>>(c, scan, h->geo.as<SubGeo>(), h->z_t.as<float>(), h->fields.as<float>(), o, nc);
+            CU(h, cudaGetLastError()); ++launches;
+        }
+        if (ev) CU(h, cudaEventRecord(ev[1], st));
 
-    k_scan_bins<<<1, 1024, 0, st>>>(c, h->hist.as<int>(), h->bin_start.as<int>(), h->tile_start.as<int>(),
-                                     h->cost_start.as<int>(), h->cursor.as<int>(), h->totals.as<long long>());
-    CU(h, cudaGetLastError()); ++launches;
-    k_scatter_pairs<<<(unsigned)((n + 255) / 256), 256, hist_smem, st>>>(c, h->key.as<uint16_t>(), h->p0.as<float>(), h->p1.as<float>(),
-                                                                          h->scan.sub_weight, h->cursor.as<int>(), h->rec.as<PairRec>(), n);
-    CU(h, cudaGetLastError()); ++launches;
-    if (ev) CU(h, cudaEventRecord(ev[2], st));
+        k_scan_bins<<<1, 1024, 0, st>>>(c, h->hist.as<int>(), h->bin_start.as<int>(), h->tile_start.as<int>(),
+                                         h->cost_start.as<int>(), h->cursor.as<int>(), totals);
+        CU(h, cudaGetLastError()); ++launches;
+        k_scatter_pairs<<<(unsigned)((nc + 255) / 256), 256, hist_smem, st>>>(c, h->key.as<uint16_t>(), h->p0.as<float>(), h->p1.as<float>(),
+                                                                               scan.sub_weight, h->cursor.as<int>(), h->rec.as<PairRec>(), nc);
+        CU(h, cudaGetLastError()); ++launches;
+        if (ev) CU(h, cudaEventRecord(ev[2], st));
 
-    K2Args a2;
-    a2.hist = h->hist.as<int>(); a2.bin_start = h->bin_start.as<int>(); a2.tile_start = h->tile_start.as<int>();
-    a2.chunk_start = h->cost_start.as<int>(); a2.totals = h->totals.as<long long>();
-    a2.counter = h->flags.as<int>() + 1;
-    a2.rec = h->rec.as<PairRec>(); a2.sz_out = h->sz_out.as<float>(); a2.ice_vn = h->ice_vn.as<float2>(); a2.dop_vn = h->dop_vn.as<float2>();
-    k_integrate<<<h->k2_blocks, RADOP_TILE_THREADS, h->k2_smem, st>>>(c, a2);
-    CU(h, cudaGetLastError()); ++launches;
-    if (ev) CU(h, cudaEventRecord(ev[3], st));
+        K2Args a2;
+        a2.hist = h->hist.as<int>(); a2.bin_start = h->bin_start.as<int>(); a2.tile_start = h->tile_start.as<int>();
+        a2.chunk_start = h->cost_start.as<int>(); a2.totals = totals;
+        a2.counter = h->flags.as<int>() + 1;
+        a2.rec = h->rec.as<PairRec>(); a2.sz_out = h->sz_out.as<float>(); a2.ice_vn = h->ice_vn.as<float2>(); a2.dop_vn = h->dop_vn.as<float2>();
+        k_integrate<<<h->k2_blocks, RADOP_TILE_THREADS, h->k2_smem, st>>>(c, a2);
+        CU(h, cudaGetLastError()); ++launches;
+        if (ev) CU(h, cudaEventRecord(ev[3], st));
 
-    if (c.ice_numeric >= 0 && c.doppler_scheme == 1) {
-        int warps = c.n_rays * c.n_sub;
-        k_ice_totals<<<(warps * 32 + 127) / 128, 128, 0, st>>>(c, h->active.as<uint8_t>(), h->ice_vn.as<float2>(), h->ice_tot.as<float>());
+        if (c.ice_numeric >= 0 && c.doppler_scheme == 1) {
+            int warps = nr * c.n_sub;
+            k_ice_totals<<<(warps * 32 + 127) / 128, 128, 0, st>>>(c, h->active.as<uint8_t>(), h->ice_vn.as<float2>(), h->ice_tot.as<float>());
+            CU(h, cudaGetLastError()); ++launches;
+        }
+        K3Args a3;
+        a3.mask = h->mask.as<int8_t>(); a3.active = h->active.as<uint8_t>();
+        a3.wind = h->wind.as<float>(); a3.sinth = h->sinth.as<float>(); a3.vsum = h->vsum.as<float>(); a3.nsum = h->nsum.as<float>();
+        a3.sz_out = h->sz_out.as<float>(); a3.ice_tot = h->ice_tot.as<float>(); a3.dop_vn = h->dop_vn.as<float2>();
+        a3.vals = want_vals ? h->vals.as<float>() : nullptr;
+        a3.sub_weight = scan.sub_weight; a3.ray_nyquist = nyq;
+        a3.comb = h->comb.as<float>(); a3.out = h->out.as<float>() + off_rg;
+        a3.model_out = c.output_model_vars ? h->model_out.as<float>() + off_rg : nullptr;
+        k_reduce_subbeams<<<(unsigned)((cc_rg + 127) / 128), 128, 0, st>>>(c, a3);
         CU(h, cudaGetLastError()); ++launches;
+        k_ray_epilogue<<<(nr * 32 + 127) / 128, 128, 0, st>>>(c, a3);
+        CU(h, cudaGetLastError()); ++launches;
+        if (ev) CU(h, cudaEventRecord(ev[4], st));
+        if (c.doppler_scheme == 3) {
+            K4Args a4;
+            a4.mask = h->mask.as<int8_t>(); a4.active = h->active.as<uint8_t>(); a4.sz_out = h->sz_out.as<float>();
+            a4.sub_weight = scan.sub_weight;
+            a4.d3_uh = h->d3_uh.as<double>(); a4.d3_w = h->d3_w.as<float>(); a4.d3_rho = h->d3_rho.as<float>();
+            a4.d3_e = h->d3_e.as<float>(); a4.ray_nyquist = nyq;
+            a4.attw = h->attw.as<float>(); a4.spec_acc = h->spec_acc.as<double>();
+            a4.spec_out = h->spec_out.as<float>() + off_rg * c.n_vel;
+            a4.out = h->out.as<float>() + off_rg;
+            a4.hist = h->hist.as<int>(); a4.bin_start = h->bin_start.as<int>(); a4.chunk_start = h->cost_start.as<int>();
+            a4.totals = totals; a4.counter = h->flags.as<int>() + 2; a4.rec = h->rec.as<PairRec>();
+            CU(h, cudaMemsetAsync(h->spec_acc.p, 0, cc_rg * c.n_vel * 8, st));
+            k_beam_attenuation<<<(nr * c.n_sub + 3) / 4, 128, smem_a, st>>>(c, a4);
+            CU(h, cudaGetLastError()); ++launches;
+            k_spectrum<<<std::max(1, occ4) * h->n_sm, 128, h->k4_smem, st>>>(c, a4);
+            CU(h, cudaGetLastError()); ++launches;
+            k_spectrum_finish<<<(unsigned)((cc_rg * 32 + 127) / 128), 128, 0, st>>>(c, a4);
+            CU(h, cudaGetLastError()); ++launches;
+        }
+        if (ev) CU(h, cudaEventRecord(ev[5], st));
+        if (out) {
+            CU(h, cudaEventRecord(h->chunk_done[ch], st));
+            CU(h, cudaStreamWaitEvent(h->copy_stream, h->chunk_done[ch], 0));
+            rc = copy_outputs(h, out, r0, nr, h->copy_stream);
+            if (rc) return rc;
+        }
     }
-    K3Args a3;
-    a3.mask = h->mask.as<int8_t>(); a3.active = h->active.as<uint8_t>();
-    a3.wind = h->wind.as<float>(); a3.sinth = h->sinth.as<float>(); a3.vsum = h->vsum.as<float>(); a3.nsum = h->nsum.as<float>();
-    a3.sz_out = h->sz_out.as<float>(); a3.ice_tot = h->ice_tot.as<float>(); a3.dop_vn = h->dop_vn.as<float2>();
-    a3.vals = want_vals ? h->vals.as<float>() : nullptr;
-    a3.sub_weight = h->scan.sub_weight; a3.ray_nyquist = h->d_nyquist;
-    a3.comb = h->comb.as<float>(); a3.out = h->out.as<float>();
-    a3.model_out = c.output_model_vars ? h->model_out.as<float>() : nullptr;
-    k_reduce_subbeams<<<(unsigned)((n_rg + 127) / 128), 128, 0, st>>>(c, a3);
-    CU(h, cudaGetLastError()); ++launches;
-    k_ray_epilogue<<<(c.n_rays * 32 + 127) / 128, 128, 0, st>>>(c, a3);
-    CU(h, cudaGetLastError()); ++launches;
-    if (ev) CU(h, cudaEventRecord(ev[4], st));
-    if (c.doppler_scheme == 3) {
-        K4Args a4;
-        a4.mask = h->mask.as<int8_t>(); a4.active = h->active.as<uint8_t>(); a4.sz_out = h->sz_out.as<float>();
-        a4.sub_weight = h->scan.sub_weight;
-        a4.d3_uh = h->d3_uh.as<double>(); a4.d3_w = h->d3_w.as<float>(); a4.d3_rho = h->d3_rho.as<float>();
-        a4.d3_e = h->d3_e.as<float>(); a4.ray_nyquist = h->d_nyquist;
-        a4.attw = h->attw.as<float>(); a4.spec_acc = h->spec_acc.as<double>(); a4.spec_out = h->spec_out.as<float>();
-        a4.out = h->out.as<float>();
-        a4.hist = h->hist.as<int>(); a4.bin_start = h->bin_start.as<int>(); a4.chunk_start = h->cost_start.as<int>();
-        a4.totals = h->totals.as<long long>(); a4.counter = h->flags.as<int>() + 2; a4.rec = h->rec.as<PairRec>();
-        CU(h, cudaMemsetAsync(h->spec_acc.p, 0, n_rg * c.n_vel * 8, st));
-        const int n_rq = c.n_rays * c.n_sub;
-        const size_t smem_a = (size_t)4 * 2 * ng * 4;
-        if (smem_a > 200 * 1024) return h->fail(RADOP_ERR_ARG, "too many gates per ray for the spectrum attenuation scan");
-        k_beam_attenuation<<<(n_rq + 3) / 4, 128, smem_a, st>>>(c, a4);
-        CU(h, cudaGetLastError()); ++launches;
-        if (h->k4_smem > 200 * 1024) return h->fail(RADOP_ERR_ARG, "velocity array / diameter axis too long for the spectrum kernel");
-        int occ4 = 1;
-        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, k_spectrum, 128, h->k4_smem));
-        k_spectrum<<<std::max(1, occ4) * h->n_sm, 128, h->k4_smem, st>>>(c, a4);
-        CU(h, cudaGetLastError()); ++launches;
-        k_spectrum_finish<<<(unsigned)((n_rg * 32 + 127) / 128), 128, 0, st>>>(c, a4);
-        CU(h, cudaGetLastError()); ++launches;
-    }
-    if (ev) CU(h, cudaEventRecord(ev[5], st));
+    c.n_rays = n_rays;
+    h->n_chunks = n_chunks;
     h->stats.launches = launches;
-    h->stats.n_subbeam_gates = n;
+    h->stats.n_subbeam_gates = h->n_sbg;
     h->executed = true;
     return RADOP_OK;
+}
+
+int radop_execute(RadopHandle *h)
+{
+    if (!h) return RADOP_ERR_ARG;
+    return run_scan(h, nullptr);
 }
 
 int radop_synchronize(RadopHandle *h)
@@ -665,24 +744,28 @@ static void average_timings(RadopHandle *h)
         cudaEventElapsedTime(&ms[5], e[4], e[5]);
         for (int k = 0; k < 6; ++k) acc[k] += ms[k];
     }
-    h->stats.ms_interp = (float)(acc[0] / h->n_timed);
-    h->stats.ms_sort = (float)(acc[1] / h->n_timed);
-    h->stats.ms_integrate = (float)(acc[2] / h->n_timed);
-    h->stats.ms_reduce = (float)(acc[3] / h->n_timed);
-    h->stats.ms_total = (float)(acc[4] / h->n_timed);
-    h->stats.ms_spectrum = (float)(acc[5] / h->n_timed);
-    h->stats.n_timed = h->n_timed;
+    const int ne = std::max(1, h->n_exec_timed);     // event sets are per chunk: sum them per execute
+    h->stats.ms_interp = (float)(acc[0] / ne);
+    h->stats.ms_sort = (float)(acc[1] / ne);
+    h->stats.ms_integrate = (float)(acc[2] / ne);
+    h->stats.ms_reduce = (float)(acc[3] / ne);
+    h->stats.ms_total = (float)(acc[4] / ne);
+    h->stats.ms_spectrum = (float)(acc[5] / ne);
+    h->stats.n_timed = h->n_exec_timed;
 }
 
 static int finish(RadopHandle *h)
 {   // after the stream has drained: flags + statistics
-    long long tot[4];
+    std::vector<long long> tot((size_t)4 * std::max(1, h->n_chunks));
     int flags[4];
-    CU(h, cudaMemcpy(tot, h->totals.p, sizeof tot, cudaMemcpyDeviceToHost));
+    CU(h, cudaMemcpy(tot.data(), h->totals.p, tot.size() * 8, cudaMemcpyDeviceToHost));
     CU(h, cudaMemcpy(flags, h->flags.p, sizeof flags, cudaMemcpyDeviceToHost));
-    h->stats.n_active_pairs = tot[0];
-    h->stats.n_tiles = tot[1];
-    h->stats.n_lut_bins = tot[3];
+    h->stats.n_active_pairs = h->stats.n_tiles = h->stats.n_lut_bins = 0;
+    for (int ch = 0; ch < std::max(1, h->n_chunks); ++ch) {
+        h->stats.n_active_pairs += tot[4 * ch];
+        h->stats.n_tiles += tot[4 * ch + 1];
+        h->stats.n_lut_bins += tot[4 * ch + 3];      // (species, e, t) bins staged, summed over the chunks
+    }
     average_timings(h);
     if (flags[0] & 1)
         return h->fail(RADOP_ERR_OUT_OF_DOMAIN, "radar domain is not entirely contained in the model domain");
@@ -694,35 +777,31 @@ int radop_fetch(RadopHandle *h, const RadopOut *out)
     if (!h) return RADOP_ERR_ARG;
     if (!h->executed) return h->fail(RADOP_ERR_STATE, "nothing executed");
     CU(h, cudaSetDevice(h->device));
-    cudaStream_t st = h->stream;
-    const size_t n_rg = (size_t)h->cfg.n_rays * h->cfg.n_gates;
     if (out) {
-        for (int v = 0; v < RADOP_N_OUT; ++v)
-            if (out->obs[v]) CU(h, cudaMemcpyAsync(out->obs[v], h->out.as<float>() + (size_t)v * n_rg, n_rg * 4, cudaMemcpyDeviceToHost, st));
-        if (out->mask) CU(h, cudaMemcpyAsync(out->mask, h->out.as<float>() + (size_t)RADOP_N_OUT * n_rg, n_rg * 4, cudaMemcpyDeviceToHost, st));
-        if (out->lat) CU(h, cudaMemcpyAsync(out->lat, h->lat.p, n_rg * 8, cudaMemcpyDeviceToHost, st));
-        if (out->lon) CU(h, cudaMemcpyAsync(out->lon, h->lon.p, n_rg * 8, cudaMemcpyDeviceToHost, st));
-        if (out->dspectrum) {
-            if (h->cfg.doppler_scheme != 3) return h->fail(RADOP_ERR_ARG, "DSPECTRUM requested but the Doppler scheme is not 3");
-            CU(h, cudaMemcpyAsync(out->dspectrum, h->spec_out.p, n_rg * h->cfg.n_vel * 4, cudaMemcpyDeviceToHost, st));
-        }
-        for (int v = 0; v < RADOP_NVAR_MAX; ++v)
-            if (out->model[v]) {
-                if (!h->cfg.output_model_vars || !(h->var_mask & (1u << v))) return h->fail(RADOP_ERR_ARG, "model output requested but not computed");
-                CU(h, cudaMemcpyAsync(out->model[v], h->model_out.as<float>() + (size_t)v * n_rg, n_rg * 4, cudaMemcpyDeviceToHost, st));
-            }
+        int rc = copy_outputs(h, out, 0, h->n_rays, h->stream);
+        if (rc) return rc;
     }
-    CU(h, cudaStreamSynchronize(st));
+    CU(h, cudaStreamSynchronize(h->stream));
     return finish(h);
 }
 
 int radop_simulate(RadopHandle *h, const RadopScan *scan, const RadopOut *out)
 {
+    if (!h) return RADOP_ERR_ARG;
     int rc = radop_stage_scan(h, scan);
     if (rc) return rc;
-    rc = radop_execute(h);
+    rc = run_scan(h, out);          // copies of a chunk overlap the kernels of the next one
     if (rc) return rc;
-    return radop_fetch(h, out);
+    CU(h, cudaStreamSynchronize(h->stream));
+    CU(h, cudaStreamSynchronize(h->copy_stream));
+    return finish(h);
+}
+
+int radop_set_chunk(RadopHandle *h, int64_t subbeam_gates_per_chunk)
+{
+    if (!h) return RADOP_ERR_ARG;
+    h->chunk_sbg = subbeam_gates_per_chunk;
+    return RADOP_OK;
 }
 
 int radop_device_outputs(RadopHandle *h, void **dev_ptr, int64_t *n_rays, int64_t *n_gates)
@@ -746,7 +825,8 @@ int radop_enable_timing(RadopHandle *h, int on)
 {
     if (!h) return RADOP_ERR_ARG;
     h->timing = on != 0;
-    h->n_timed = 0;              // a new measurement window
+    h->n_timed = 0;
+    h->n_exec_timed = 0;              // a new measurement window
     return RADOP_OK;
 }
 

@@ -1460,11 +1460,11 @@ k_reduce_subbeams(const __grid_constant__ DevConfig cfg, K3Args A)
     dst[1] = make_float4(comb[4], comb[5], comb[6], rsum / wsum);
     float mk = msum / (float)cfg.n_sub;
     if (mk > -1.f && mk <= 0.f) mk = 0.f;
-    A.out[(size_t)RADOP_N_OUT * n_rg + idx] = mk;
+    A.out[(size_t)RADOP_N_OUT * cfg.out_stride + idx] = mk;
     if (A.model_out) {
 #pragma unroll
         for (int v = 0; v < RADOP_NVP; ++v)
-            if (cfg.var_mask & (1u << v)) A.model_out[(size_t)v * n_rg + idx] = mv[v];
+            if (cfg.var_mask & (1u << v)) A.model_out[(size_t)v * cfg.out_stride + idx] = mv[v];
     }
 }
 
@@ -1496,7 +1496,7 @@ k_ray_epilogue(const __grid_constant__ DevConfig cfg, K3Args A)
     const int ray = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (ray >= cfg.n_rays) return;
     const int ng = cfg.n_gates;
-    const size_t n_rg = (size_t)cfg.n_rays * ng;
+    const size_t n_rg = (size_t)cfg.out_stride;      // rays x gates of the whole scan (this launch may be a chunk)
     const float qnan = __int_as_float(0x7fc00000);
     const float PI = 3.14159265358979323846f;
     const float wl = cfg.wavelength;
@@ -1876,8 +1876,8 @@ k_spectrum_finish(const __grid_constant__ DevConfig cfg, K4Args A)
             const float th = (rvel + nyq) / (2.f * nyq) * PI - PI / 2.f;
             rvel = (atanf(tanf(th)) + PI / 2.f) * (2.f * nyq) / PI - nyq;
         }
-        if (cfg.sensitivity_mode && isnan(A.out[(size_t)RADOP_OUT_ZH * n_rg + wg])) rvel = qnan;
-        A.out[(size_t)RADOP_OUT_RVEL * n_rg + wg] = rvel;
+        if (cfg.sensitivity_mode && isnan(A.out[(size_t)RADOP_OUT_ZH * cfg.out_stride + wg])) rvel = qnan;
+        A.out[(size_t)RADOP_OUT_RVEL * cfg.out_stride + wg] = rvel;
     }
 }
 

@@ -48,7 +48,8 @@ struct SpeciesDev {
 
 struct DevConfig {
     // radar / scan geometry
-    int n_rays, n_sub, n_gates, n_vert, center_sub;
+    int n_rays, n_sub, n_gates, n_vert, center_sub;   // n_rays: rays of this launch (a chunk of the scan)
+    long long out_stride;       // rays x gates of the whole scan: stride between output variables
     double radar_lat, radar_lon;
     double cos_lon0, sin_lon0;  // of the radar longitude
     // model grid

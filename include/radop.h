@@ -182,6 +182,10 @@ int radop_stage_scan(RadopHandle *h, const RadopScan *scan);   /* H2D           
 int radop_execute(RadopHandle *h);                              /* kernels, asynchronous  */
 int radop_fetch(RadopHandle *h, const RadopOut *out);           /* sync + D2H             */
 int radop_synchronize(RadopHandle *h);
+/* The ray list is processed in chunks of about this many sub-beam gates (default 8e6; 0 = one
+ * chunk): work memory is sized for one chunk and, in radop_simulate, the device -> host copies
+ * of a chunk overlap the kernels of the next one.  Results do not depend on the chunking. */
+int radop_set_chunk(RadopHandle *h, int64_t subbeam_gates_per_chunk);
 
 /* Device-resident results of the last radop_execute (for NCCL gathers): pointer to
  * float32 [RADOP_N_OUT + 1][n_rays][n_gates] (observables then mask). */

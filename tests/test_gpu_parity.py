@@ -372,6 +372,13 @@ def test_scan_level_properties():
     d1 = op.simulate_rays(ray_az[half:], ray_el[half:])
     for k in keys:
         assert np.array_equal(np.concatenate([d0[k], d1[k]]), a[k], equal_nan=True), 'sharding changes ' + k
+    # chunked execution (work memory per chunk, copies overlapped with the next chunk): same bits
+    for chunk in (0, 100000, 37 * 9 * 160):
+        op._engine.set_chunk(chunk)
+        f = op.simulate_rays(ray_az, ray_el)
+        for k in keys + ('lat', 'lon'):
+            assert np.array_equal(f[k], a[k], equal_nan=True), 'chunking ({}) changes {}'.format(chunk, k)
+    op._engine.set_chunk(8000000)
     e = op.simulate_rays(ray_az[:40] + 360.0, ray_el[:40])
     assert np.allclose(e['ZH'], a['ZH'][:40], rtol=1e-5, equal_nan=True)
     # scaling every table by 3 scales the reflectivities and attenuation by 3, leaves ZDR/RHOHV
