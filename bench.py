@@ -196,9 +196,10 @@ class CpuArm(object):
         self.pool.join()
 
 
-def cpu_baseline(model, luts, conf, budget_s=20.0):
+def cpu_baseline(model, luts, conf, rays_per_core=64):
+    """About 10-30 s of CPU work: 64 rays per host core, all cores busy."""
     arm = CpuArm(model, luts, conf)
-    az, el, n = arm.sample_rays()
+    az, el, n = arm.sample_rays(rays_per_core)
     arm.run(az[:arm.cores], el[:arm.cores])          # warm the workers (imports, page-in)
     dt = arm.run(az, el)
     sbg = n * arm.n_sub * arm.n_gates
@@ -216,7 +217,7 @@ def run_reference(args):
     conf = volume_config()
     model, luts = build_inputs()
     arm = CpuArm(model, luts, conf)
-    az, el, n = arm.sample_rays()
+    az, el, n = arm.sample_rays(16)
     for _ in range(max(1, args.warmup)):
         arm.run(az[:max(arm.cores, n // 4)], el[:max(arm.cores, n // 4)])
     t = 0.0

@@ -513,6 +513,73 @@ __global__ void k_interp_compat(int n, const float *__restrict__ coords, const f
                        __fmul_rn(__fmul_rn(x, y), vv[3]));
 }
 
+// All variables of one gate from the 8 surrounding grid points, in the reference's order of
+// operations (interpolation_c.c:84-103, 138-164).  EXACT = false: quotients from the reciprocal
+// shared by the variables of a column, no branch; returns true when some quotient needs the
+// IEEE division (see div_shared_rcp), in which case the caller repeats with EXACT = true.
+template <bool EXACT>
+__device__ __forceinline__ bool interp_columns(const DevConfig &cfg, const CellGeom &c, float h_g,
+                                               const float *__restrict__ z_t, const float *__restrict__ fields,
+                                               float (&val)[RADOP_NVP])
+{
+    // slots 0..8 are the 1-moment variables: two float4 + one scalar per level;
+    // the 2-moment scheme reads all four float4
+    const int ys[4] = {c.y0, c.y0, c.y1, c.y1};
+    const int xs[4] = {c.x0, c.x1, c.x0, c.x1};
+    const int order[4] = {0, 2, 1, 3};      // accumulation order of the reference
+    bool rare = false;
+#pragma unroll
+    for (int oi = 0; oi < 4; ++oi) {
+        const int k = order[oi];
+        const size_t colidx = (size_t)ys[k] * cfg.nx + xs[k];
+        const float *zc = z_t + colidx * cfg.nz + c.level[k];
+        const float c1 = __ldg(zc), c2 = __ldg(zc + 1);
+        const float den = __fsub_rn(c1, c2), dh = __fsub_rn(h_g, c2);
+        const float rden = EXACT ? 0.f : __frcp_rn(den);
+        if (!EXACT) rare = rare || !div_den_safe(den);
+        const float4 *f1 = reinterpret_cast<const float4 *>(fields + (colidx * cfg.nz + c.level[k]) * RADOP_NVP);
+        const float4 *f2 = f1 + RADOP_NVP / 4;
+        float w0, w1;      // term = (w0 * v) * w1 in the reference's association
+        bool v_mid;        // col 1, 2: (w0 * v) * w1 ; col 0, 3: (w0 * w1) * v
+        if (k == 0) { w0 = __fmul_rn(c.dx, c.dy); w1 = 0.f; v_mid = false; }
+        else if (k == 2) { w0 = c.x; w1 = c.dy; v_mid = true; }
+        else if (k == 1) { w0 = c.dx; w1 = c.y; v_mid = true; }
+        else { w0 = __fmul_rn(c.x, c.y); w1 = 0.f; v_mid = false; }
+        auto accum = [&](int j, float a, float b) {
+            const float n = __fsub_rn(b, a);
+            float q;
+            if (EXACT) q = __fdiv_rn(n, den);
+            else {
+                const float q0 = __fmul_rn(n, rden);
+                const float r = __fmaf_rn(-den, q0, n);
+                q = __fmaf_rn(r, rden, q0);
+                const float aq = fabsf(q);
+                rare = rare || !(aq <= 1e30f) || (aq < 1e-30f && n != 0.f);
+            }
+            float vv = __fsub_rn(b, __fmul_rn(q, dh));
+            float term = v_mid ? __fmul_rn(__fmul_rn(w0, vv), w1) : __fmul_rn(w0, vv);
+            val[j] = (oi == 0) ? term : __fadd_rn(val[j], term);
+        };
+#pragma unroll
+        for (int v4 = 0; v4 < 2; ++v4) {
+            float4 a = __ldg(f1 + v4), b = __ldg(f2 + v4);
+            accum(4 * v4, a.x, b.x); accum(4 * v4 + 1, a.y, b.y);
+            accum(4 * v4 + 2, a.z, b.z); accum(4 * v4 + 3, a.w, b.w);
+        }
+        if (cfg.two_moment) {
+#pragma unroll
+            for (int v4 = 2; v4 < 4; ++v4) {
+                float4 a = __ldg(f1 + v4), b = __ldg(f2 + v4);
+                accum(4 * v4, a.x, b.x); accum(4 * v4 + 1, a.y, b.y);
+                accum(4 * v4 + 2, a.z, b.z); accum(4 * v4 + 3, a.w, b.w);
+            }
+        } else {
+            float a = __ldg(reinterpret_cast<const float *>(f1) + 8), b = __ldg(reinterpret_cast<const float *>(f2) + 8);
+            accum(8, a, b);
+        }
+    }
+    return rare;
+}
 // ------------------------------------------------------------------------------------------
 // K1: per sub-beam gate
 // ------------------------------------------------------------------------------------------
@@ -659,51 +726,10 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
             float wind = qnan, sinth = 0.f, vsum = 0.f, nsum = 0.f;
             if (c.status == 0) {
                 // --- interpolate every variable with the same 8 corner weights ----------------
-                // slots 0..8 are the 1-moment variables: two float4 + one scalar per level;
-                // the 2-moment scheme reads all four float4
-                const int ys[4] = {c.y0, c.y0, c.y1, c.y1};
-                const int xs[4] = {c.x0, c.x1, c.x0, c.x1};
-                const int order[4] = {0, 2, 1, 3};      // accumulation order of the reference
-#pragma unroll
-                for (int oi = 0; oi < 4; ++oi) {
-                    const int k = order[oi];
-                    const size_t colidx = (size_t)ys[k] * cfg.nx + xs[k];
-                    const float *zc = z_t + colidx * cfg.nz + c.level[k];
-                    const float c1 = __ldg(zc), c2 = __ldg(zc + 1);
-                    const float den = __fsub_rn(c1, c2), dh = __fsub_rn(h_g, c2);
-                    const float rden = __frcp_rn(den);
-                    const bool den_safe = div_den_safe(den);
-                    const float4 *f1 = reinterpret_cast<const float4 *>(fields + (colidx * cfg.nz + c.level[k]) * RADOP_NVP);
-                    const float4 *f2 = f1 + RADOP_NVP / 4;
-                    float w0, w1;      // term = (w0 * v) * w1 in the reference's association
-                    bool v_mid;        // col 1, 2: (w0 * v) * w1 ; col 0, 3: (w0 * w1) * v
-                    if (k == 0) { w0 = __fmul_rn(c.dx, c.dy); w1 = 0.f; v_mid = false; }
-                    else if (k == 2) { w0 = c.x; w1 = c.dy; v_mid = true; }
-                    else if (k == 1) { w0 = c.dx; w1 = c.y; v_mid = true; }
-                    else { w0 = __fmul_rn(c.x, c.y); w1 = 0.f; v_mid = false; }
-                    auto accum = [&](int j, float a, float b) {
-                        float vv = __fsub_rn(b, __fmul_rn(div_shared_rcp(__fsub_rn(b, a), den, rden, den_safe), dh));
-                        float term = v_mid ? __fmul_rn(__fmul_rn(w0, vv), w1) : __fmul_rn(w0, vv);
-                        val[j] = (oi == 0) ? term : __fadd_rn(val[j], term);
-                    };
-#pragma unroll
-                    for (int v4 = 0; v4 < 2; ++v4) {
-                        float4 a = __ldg(f1 + v4), b = __ldg(f2 + v4);
-                        accum(4 * v4, a.x, b.x); accum(4 * v4 + 1, a.y, b.y);
-                        accum(4 * v4 + 2, a.z, b.z); accum(4 * v4 + 3, a.w, b.w);
-                    }
-                    if (cfg.two_moment) {
-#pragma unroll
-                        for (int v4 = 2; v4 < 4; ++v4) {
-                            float4 a = __ldg(f1 + v4), b = __ldg(f2 + v4);
-                            accum(4 * v4, a.x, b.x); accum(4 * v4 + 1, a.y, b.y);
-                            accum(4 * v4 + 2, a.z, b.z); accum(4 * v4 + 3, a.w, b.w);
-                        }
-                    } else {
-                        float a = __ldg(reinterpret_cast<const float *>(f1) + 8), b = __ldg(reinterpret_cast<const float *>(f2) + 8);
-                        accum(8, a, b);
-                    }
-                }
+                // fast pass: shared-reciprocal quotients without a branch; a rare flag (zero /
+                // tiny / non-finite quotient, odd level spacing) sends the gate through the
+                // same code with IEEE divisions
+                if (interp_columns<false>(cfg, c, h_g, z_t, fields, val)) interp_columns<true>(cfg, c, h_g, z_t, fields, val);
                 if (!cfg.two_moment) {
 #pragma unroll
                     for (int j = 9; j < 16; ++j) val[j] = 0.f;
