@@ -396,7 +396,11 @@ static int prepare(RadopHandle *h)
     c.radar_lat = p.radar_lat; c.radar_lon = p.radar_lon;
     c.cos_lon0 = cos(p.radar_lon * 0.017453292519943295); c.sin_lon0 = sin(p.radar_lon * 0.017453292519943295);
     c.nz = h->nz; c.ny = h->ny; c.nx = h->nx;
-    for (int i = 0; i < 2; ++i) { c.llc[i] = h->llc[i]; c.urc[i] = h->urc[i]; c.res[i] = h->res[i]; }
+    for (int i = 0; i < 2; ++i) {
+        c.llc[i] = h->llc[i]; c.urc[i] = h->urc[i]; c.res[i] = h->res[i];
+        c.rres[i] = 1.0f / h->res[i];            // IEEE float32 division: correctly rounded reciprocal
+        if (!(fabsf(h->res[i]) > 1e-6f && fabsf(h->res[i]) < 1e6f)) return h->fail(RADOP_ERR_ARG, "grid resolution out of range");
+    }
     memcpy(c.rot, h->rot, sizeof c.rot);
     c.var_mask = h->var_mask;
     c.z_strict = h->z_strict;
@@ -420,6 +424,9 @@ static int prepare(RadopHandle *h)
         d.species = S.species; d.psd = S.psd; d.mode = L.mode; d.ncol = L.ncol; d.numeric_vn = S.numeric_vn;
         d.ne = L.ne; d.nt = L.nt; d.nd = L.nd;
         d.e_min = L.e_min; d.e_step = L.e_step; d.t_min = L.t_min; d.t_step = L.t_step;
+        d.e_rstep = 1.0f / L.e_step; d.t_rstep = 1.0f / L.t_step;      // correctly rounded float32 reciprocals
+        if (!(fabsf(L.e_step) > 1e-6f && fabsf(L.e_step) < 1e6f && fabsf(L.t_step) > 1e-6f && fabsf(L.t_step) < 1e6f))
+            return h->fail(RADOP_ERR_LUT, "table axis step out of range");
         d.bin_base = bins; d.cost = L.cost;
         species_vars(S.species, &d.qm_var, &d.qn_var);
         need |= (1u << d.qm_var);

@@ -400,8 +400,8 @@ __device__ __forceinline__ void locate_cell(const float *__restrict__ z_t, int n
 {
     c.iy = (int)floorf(pos0);
     c.ix = (int)floorf(pos1);
-    c.x = fmodf(pos0, 1.0f);
-    c.y = fmodf(pos1, 1.0f);
+    c.x = __fsub_rn(pos0, truncf(pos0));      // fmod(pos, 1.0): exact, keeps the sign of pos
+    c.y = __fsub_rn(pos1, truncf(pos1));
     c.dx = __fsub_rn(1.0f, c.x);
     c.dy = __fsub_rn(1.0f, c.y);
     // memory-safe neighbour indices (the reference reads out of bounds on the last row/col)
@@ -625,9 +625,22 @@ __device__ __forceinline__ double ice_log_mom2(double T, double logQM)
     return (logQM - 2.302585092994046 * a) / b;
 }
 
-__device__ __forceinline__ int lut_bin(float x, float lo, float step, int dim)
+// quotient n / den from rden = RN(1 / den) (Markstein, see div_shared_rcp) for divisors that are
+// scan constants (grid resolution, table axis steps): no branch unless the quotient is odd
+__device__ __forceinline__ float div_const(float n, float den, float rden)
+{
+    const float q0 = __fmul_rn(n, rden);
+    const float r = __fmaf_rn(-den, q0, n);
+    float q = __fmaf_rn(r, rden, q0);
+    const float aq = fabsf(q);
+    // the residual is exact when n is not tiny (den is between 1e-6 and 1e6, checked on the host)
+    if (!(aq <= 1e30f) || (fabsf(n) < 1e-25f && n != 0.f)) q = __fdiv_rn(n, den);
+    return q;
+}
+
+__device__ __forceinline__ int lut_bin(float x, float lo, float step, float rstep, int dim)
 {   // lut.py:336-341: floor((x - lo)/step) in float32, clamped
-    float f = floorf(__fdiv_rn(__fsub_rn(x, lo), step));
+    float f = floorf(div_const(__fsub_rn(x, lo), step, rstep));
     int i = (int)f;
     if (f < 0.f) i = 0;
     if (f >= (float)dim) i = dim - 1;
@@ -706,8 +719,8 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                 atomicOr(o.flags, 1);
             // SWIG typemap casts the coordinates to float32 (interpolation_c.i:16)
             const float crlat = (float)rlat, crlon = (float)rlon;
-            const float pos0 = __fdiv_rn(__fsub_rn(crlat, cfg.llc[1]), cfg.res[1]);
-            const float pos1 = __fdiv_rn(__fsub_rn(crlon, cfg.llc[0]), cfg.res[0]);
+            const float pos0 = div_const(__fsub_rn(crlat, cfg.llc[1]), cfg.res[1], cfg.rres[1]);
+            const float pos1 = div_const(__fsub_rn(crlon, cfg.llc[0]), cfg.res[0], cfg.rres[0]);
             CellGeom c;
             locate_cell(z_t, cfg.nz, cfg.ny, cfg.nx, pos0, pos1, h_g, cfg.z_strict != 0, c);
             o.mask[sbg] = (int8_t)c.status;
@@ -781,8 +794,8 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                     if (n0_from_log) n0 = n0_negative ? -exp(logn0) : exp(logn0);
                     if (S.psd == RADOP_PSD_1MOM_ICE) { p0 = (float)lam; p1 = QMf; }     // lambda / 1000, QM
                     else { p0 = (float)lam; p1 = (float)n0; }
-                    const int ie = lut_bin(e, S.e_min, S.e_step, S.ne);
-                    const int it = lut_bin(T, S.t_min, S.t_step, S.nt);
+                    const int ie = lut_bin(e, S.e_min, S.e_step, S.e_rstep, S.ne);
+                    const int it = lut_bin(T, S.t_min, S.t_step, S.t_rstep, S.nt);
                     keys[s] = (uint32_t)(S.bin_base + ie * S.nt + it);
                     o.p0[(size_t)s * n_sbg + sbg] = p0;
                     o.p1[(size_t)s * n_sbg + sbg] = p1;

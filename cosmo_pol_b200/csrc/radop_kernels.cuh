@@ -24,6 +24,7 @@ struct SpeciesDev {
     int numeric_vn;
     int ne, nt, nd;
     float e_min, e_step, t_min, t_step;
+    float e_rstep, t_rstep;     // RN(1 / step), formed in float64 on the host
     int bin_base;               // first global bin id of this species
     int cost;                   // relative cost of one tile (for work partitioning)
     int qm_var, qn_var;         // RADOP_VAR_* holding mass / number density
@@ -55,6 +56,7 @@ struct DevConfig {
     // model grid
     int nz, ny, nx;
     float llc[2], urc[2], res[2];
+    float rres[2];              // RN(1 / res)
     double rot[9];              // rotation matrix geographic -> rotated pole
     uint32_t var_mask;          // uploaded variables
     // microphysics
