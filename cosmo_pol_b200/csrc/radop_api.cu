@@ -433,6 +433,9 @@ static int prepare(RadopHandle *h)
         if (S.psd == RADOP_PSD_2MOM) need |= (1u << d.qn_var);
         d.dD_geo = L.dD_geo; d.dD_ref = L.dD_ref; d.dD_d = L.dD_d;
         d.d_min = L.d_min; d.d_max = L.d_max; d.spec_step = L.spec_step;
+        d.wh_lo = S.alpha * pow((double)L.d_min, S.beta) * (1.0 - 1e-9);
+        d.wh_hi = S.alpha * pow((double)L.d_max, S.beta) * (1.0 + 1e-9);
+        if (!(S.beta > 0.0 && S.alpha > 0.0)) { d.wh_lo = -1e300; d.wh_hi = 1e300; }   // no shortcut
         d.table = L.table.as<float>(); d.aux = L.aux.as<float>();
         d.a = S.a; d.b = S.b; d.alpha = S.alpha; d.beta = S.beta; d.mu = S.mu; d.nu = S.nu; d.N0 = S.N0;
         d.lambda_factor = S.lambda_factor; d.vel_factor = S.vel_factor; d.ntot_factor = S.ntot_factor;

@@ -1766,19 +1766,38 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                 const size_t rg = (size_t)(sbg / (unsigned)ng / (unsigned)cfg.n_sub) * ng + g;
                 const unsigned act = A.active[sbg];
                 // ---- 1. diameters at the velocity-bin edges -----------------------------------
+                int j_a, j_b;
                 {
                     const float theta = __fmul_rn(A.d3_e[sbg], 0.017453292519943295f);
-                    const double tan_t = (double)(float)tan((double)theta), sin_t = (double)(float)sin((double)theta);
+                    double sn, cs;
+                    sincos((double)theta, &sn, &cs);
+                    // np.tan / np.sin of a float32 angle are float32 (doppler_scatter.py:571-575)
+                    const double tan_t = (double)(float)(sn / cs), sin_t = (double)(float)sn;
                     const float rho_corr = sqrtf(__fdiv_rn(A.d3_rho[sbg], A.d3_rho[sbg - g]));
                     const double inv_rho = (double)__fdiv_rn(1.0f, rho_corr);
                     const double c0 = (double)A.d3_w[sbg] + A.d3_uh[sbg] / tan_t;
                     const double inv_beta = 1.0 / S.beta;
-                    for (int j = lane; j < nvel; j += 32) {
+                    const double inv_sin = 1.0 / sin_t;
+                    // wh_j = inv_rho (c0 - v_j / sin) falls with j: only the velocities between
+                    // "faster than the largest particle" (D = d_max, empty bins) and "wh < 0"
+                    // (no bin) can hold power.  Outside the normal case the whole array is done.
+                    j_a = 0; j_b = nvel - 1;
+                    if (sin_t > 0.0 && inv_rho > 0.0 && isfinite(c0)) {
+                        const double ja = floor(((c0 - S.wh_hi / inv_rho) * sin_t - cfg.vel_min) / cfg.vel_res) - 1.0;
+                        const double jb = floor((c0 * sin_t - cfg.vel_min) / cfg.vel_res) + 2.0;
+                        j_a = (int)fmin(fmax(ja, 0.0), (double)(nvel - 1));
+                        j_b = (int)fmin(fmax(jb, 0.0), (double)(nvel - 1));
+                    }
+                    for (int j = j_a + lane; j <= j_b; j += 32) {
                         const double v = cfg.vel_min + (double)j * cfg.vel_res;
-                        const double wh = inv_rho * (c0 - v / sin_t);
+                        const double wh = inv_rho * (c0 - v * inv_sin);
                         float D = __int_as_float(0x7fc00000);
                         if (wh >= 0.0) {
-                            D = (float)pow(wh / S.alpha, inv_beta);
+                            // fall speeds beyond those of the largest / smallest tabulated diameter
+                            // clip to the axis ends whatever the power law gives (margin 1e-9 >> rounding)
+                            if (wh >= S.wh_hi) D = S.d_max;
+                            else if (wh <= S.wh_lo) D = S.d_min;
+                            else D = (float)pow(wh / S.alpha, inv_beta);
                             for (int t = s; t < nsp; ++t) {
                                 if (!(act & (1u << t))) continue;
                                 if (D >= cfg.sp[t].d_max) D = cfg.sp[t].d_max;
@@ -1845,12 +1864,13 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                                      ((double)S.spec_step / (double)S.dD_ref);
                 double *dst = A.spec_acc + rg * nvel;
                 (void)k0;
-                for (int j = lane; j + 1 < nvel; j += 32) {
+                for (int j = j_a + lane; j < j_b; j += 32) {
                     const float Dj = s_D[j];
                     if (isnan(Dj)) continue;
+                    // next valid velocity (rows of the filtered list are paired, doppler_scatter.py:591-593)
                     int jn = j + 1;
-                    while (jn < nvel && isnan(s_D[jn])) ++jn;
-                    if (jn >= nvel) continue;
+                    while (jn <= j_b && isnan(s_D[jn])) ++jn;
+                    if (jn > j_b) continue;
                     const float Dn = s_D[jn];
                     const float Da = fminf(Dj, Dn), Db = fmaxf(Dj, Dn);
                     const int ia = (int)__fdiv_rn(__fsub_rn(Da, S.d_min), S.spec_step);

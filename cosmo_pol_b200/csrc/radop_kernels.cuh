@@ -31,6 +31,7 @@ struct SpeciesDev {
     float dD_geo;               // (D[nd-1]-D[0])/(nd-1) computed in double
     float dD_ref;               // D[1]-D[0] in float32 (doppler_scatter.py:224)
     float d_min, d_max;         // first / last diameter of the table axis (float32)
+    double wh_lo, wh_hi;        // fall speeds alpha D^beta of d_min (x (1 - 1e-9)) and d_max (x (1 + 1e-9))
     float spec_step;            // float32(np.linspace(d_min, d_max, nd))[1] - [0]: step_D of the spectrum
                                 // (doppler_scatter.py:686-692; differs from dD_ref by ulps)
     double dD_d;                // dD_geo in float64
