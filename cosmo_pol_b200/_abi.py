@@ -52,7 +52,8 @@ class RadopScan(C.Structure):
     _fields_ = [('n_rays', C.c_int32), ('n_sub', C.c_int32), ('n_traj', C.c_int32), ('n_vert', C.c_int32),
                 ('ray_az', C.c_void_p), ('ray_traj', C.c_void_p), ('ray_nyquist', C.c_void_p),
                 ('sub_daz', C.c_void_p), ('sub_jv', C.c_void_p), ('sub_weight', C.c_void_p),
-                ('traj_s', C.c_void_p), ('traj_h', C.c_void_p), ('traj_e', C.c_void_p)]
+                ('traj_s', C.c_void_p), ('traj_h', C.c_void_p), ('traj_e', C.c_void_p),
+                ('traj_sin', C.c_void_p), ('traj_tan', C.c_void_p)]
 
 
 class RadopOut(C.Structure):
@@ -136,6 +137,14 @@ class Scan(object):
         self.traj_s = np.ascontiguousarray(traj_s, dtype=np.float32)
         self.traj_h = np.ascontiguousarray(traj_h, dtype=np.float32)
         self.traj_e = np.ascontiguousarray(traj_e, dtype=np.float32)
+        # float32 sin / tan of the folded elevation exactly as numpy forms them in
+        # get_diameter_from_rad_vel (doppler_scatter.py:571-575); read by Doppler scheme 3 only
+        ef = self.traj_e.copy()
+        ef[ef > 90] = 180 - ef[ef > 90]
+        ef[ef < 0] = -ef[ef < 0]
+        th = np.deg2rad(ef)
+        self.traj_sin = np.ascontiguousarray(np.sin(th), dtype=np.float32)
+        self.traj_tan = np.ascontiguousarray(np.tan(th), dtype=np.float32)
         self.n_rays = len(self.ray_az)
         self.n_sub = fan.n_sub
         self.n_traj, self.n_vert, self.n_gates = self.traj_s.shape
@@ -146,6 +155,7 @@ class Scan(object):
         s.ray_az, s.ray_traj, s.ray_nyquist = _ptr(self.ray_az), _ptr(self.ray_traj), _ptr(self.ray_nyquist)
         s.sub_daz, s.sub_jv, s.sub_weight = _ptr(self.sub_daz), _ptr(self.sub_jv), _ptr(self.sub_weight)
         s.traj_s, s.traj_h, s.traj_e = _ptr(self.traj_s), _ptr(self.traj_h), _ptr(self.traj_e)
+        s.traj_sin, s.traj_tan = _ptr(self.traj_sin), _ptr(self.traj_tan)
         return s
 
     @property
@@ -154,7 +164,7 @@ class Scan(object):
 
     def bytes_in(self):
         return sum(a.nbytes for a in (self.ray_az, self.ray_traj, self.sub_daz, self.sub_jv, self.sub_weight,
-                                      self.traj_s, self.traj_h, self.traj_e)) + (
+                                      self.traj_s, self.traj_h, self.traj_e, self.traj_sin, self.traj_tan)) + (
             self.ray_nyquist.nbytes if self.ray_nyquist is not None else 0)
 
 

@@ -78,7 +78,7 @@ struct RadopHandle_ {
     // work buffers
     DevBuf geo, mask, active, wind, sinth, vsum, nsum, key, p0, p1, vals, lat, lon, hist, flags;
     DevBuf bin_start, tile_start, cost_start, cursor, totals, rec, sz_out, ice_vn, dop_vn, ice_tot, comb, out, model_out;
-    DevBuf d3_uh, d3_w, d3_rho, d3_e, attw, spec_acc, spec_out;
+    DevBuf d3_uh, d3_w, d3_rho, d3_st, attw, spec_acc, spec_out;
     size_t k4_smem = 0;
     DevBuf dbg_cell, dbg_level, dbg_status, dbg_e, dbg_t, dbg_rot;
     DevConfig cfg;
@@ -155,7 +155,7 @@ int radop_destroy(RadopHandle *h)
     DevBuf *bufs[] = {&h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
                       &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
                       &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
-                      &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_e, &h->attw, &h->spec_acc, &h->spec_out, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
+                      &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_st, &h->attw, &h->spec_acc, &h->spec_out, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
                       &h->dbg_status, &h->dbg_e, &h->dbg_t, &h->dbg_rot};
     for (DevBuf *b : bufs) b->release();
     for (auto &l : h->lut) { l.table.release(); l.aux.release(); }
@@ -343,7 +343,7 @@ int radop_stage_scan(RadopHandle *h, const RadopScan *sc)
     const int ng = h->p.n_gates;
     const size_t ntr = (size_t)sc->n_traj * sc->n_vert * ng;
     // one pinned blob, one H2D copy
-    size_t off = 0, o_az, o_tr, o_ny, o_daz, o_jv, o_w, o_s, o_h, o_e;
+    size_t off = 0, o_az, o_tr, o_ny, o_daz, o_jv, o_w, o_s, o_h, o_e, o_sin, o_tan;
     o_az = off; off = align_up(off + (size_t)sc->n_rays * 8, 256);
     o_tr = off; off = align_up(off + (size_t)sc->n_rays * 4, 256);
     o_ny = off; off = align_up(off + (size_t)sc->n_rays * 4, 256);
@@ -353,6 +353,9 @@ int radop_stage_scan(RadopHandle *h, const RadopScan *sc)
     o_s = off; off = align_up(off + ntr * 4, 256);
     o_h = off; off = align_up(off + ntr * 4, 256);
     o_e = off; off = align_up(off + ntr * 4, 256);
+    const bool have_trig = sc->traj_sin && sc->traj_tan;
+    o_sin = off; if (have_trig) off = align_up(off + ntr * 4, 256);
+    o_tan = off; if (have_trig) off = align_up(off + ntr * 4, 256);
     int rc = ensure_pinned(h, off);
     if (rc) return rc;
     CU(h, h->scan_blob.reserve(off));
@@ -367,6 +370,7 @@ int radop_stage_scan(RadopHandle *h, const RadopScan *sc)
     memcpy(P + o_s, sc->traj_s, ntr * 4);
     memcpy(P + o_h, sc->traj_h, ntr * 4);
     memcpy(P + o_e, sc->traj_e, ntr * 4);
+    if (have_trig) { memcpy(P + o_sin, sc->traj_sin, ntr * 4); memcpy(P + o_tan, sc->traj_tan, ntr * 4); }
     CU(h, cudaMemcpyAsync(h->scan_blob.p, P, off, cudaMemcpyHostToDevice, h->stream));
     char *D = (char *)h->scan_blob.p;
     h->scan.ray_az = (const double *)(D + o_az);
@@ -378,6 +382,8 @@ int radop_stage_scan(RadopHandle *h, const RadopScan *sc)
     h->scan.traj_s = (const float *)(D + o_s);
     h->scan.traj_h = (const float *)(D + o_h);
     h->scan.traj_e = (const float *)(D + o_e);
+    h->scan.traj_sin = have_trig ? (const float *)(D + o_sin) : nullptr;
+    h->scan.traj_tan = have_trig ? (const float *)(D + o_tan) : nullptr;
     h->n_rays = sc->n_rays; h->n_sub = sc->n_sub; h->n_traj = sc->n_traj; h->n_vert = sc->n_vert;
     h->center_sub = sc->n_sub / 2;          // idx_0 = int(num_beams / 2), doppler_scatter.py:89
     h->n_sbg = (long long)sc->n_rays * sc->n_sub * ng;
@@ -410,6 +416,7 @@ static int prepare(RadopHandle *h)
     c.wavelength = (float)p.wavelength_mm; c.k_squared = (float)p.k_squared; c.radial_res = (float)p.radial_resolution_m;
     c.sens0 = (float)p.sensitivity[0]; c.sens1 = (float)p.sensitivity[1];
     c.n_vel = p.n_vel; c.vel_min = p.vel_min; c.vel_res = p.vel_res;
+    c.inv_vel_res = p.vel_res > 0 ? 1.0 / p.vel_res : 0.0;
     c.ice_numeric = -1;
     uint32_t need = (1u << RADOP_VAR_U) | (1u << RADOP_VAR_V) | (1u << RADOP_VAR_W) | (1u << RADOP_VAR_T);
     int bins = 0, nd_max = 0;
@@ -433,6 +440,7 @@ static int prepare(RadopHandle *h)
         if (S.psd == RADOP_PSD_2MOM) need |= (1u << d.qn_var);
         d.dD_geo = L.dD_geo; d.dD_ref = L.dD_ref; d.dD_d = L.dD_d;
         d.d_min = L.d_min; d.d_max = L.d_max; d.spec_step = L.spec_step;
+        d.inv_beta = 1.0 / S.beta; d.inv_alpha = 1.0 / S.alpha;
         d.wh_lo = S.alpha * pow((double)L.d_min, S.beta) * (1.0 - 1e-9);
         d.wh_hi = S.alpha * pow((double)L.d_max, S.beta) * (1.0 + 1e-9);
         if (!(S.beta > 0.0 && S.alpha > 0.0)) { d.wh_lo = -1e300; d.wh_hi = 1e300; }   // no shortcut
@@ -458,8 +466,8 @@ static int prepare(RadopHandle *h)
             if (c.ice_numeric >= 0) return h->fail(RADOP_ERR_UNSUPPORTED, "only one species may have numeric fall-speed moments");
             c.ice_numeric = s;
         }
-        if (p.doppler_scheme == 3 && (L.nd % 32) != 0)
-            return h->fail(RADOP_ERR_LUT, "doppler scheme 3 needs a multiple of 32 diameter bins");
+        if (p.doppler_scheme == 3 && (L.nd % 128) != 0)
+            return h->fail(RADOP_ERR_LUT, "doppler scheme 3 needs a multiple of 128 diameter bins");
         nd_max = std::max(nd_max, L.nd);
         bins += L.ne * L.nt;
         smem = std::max(smem, (size_t)L.nd * L.ncol * 4 + (size_t)L.nd * 4);
@@ -469,7 +477,8 @@ static int prepare(RadopHandle *h)
     if (bins * 4 > 200 * 1024) return h->fail(RADOP_ERR_LUT, "bin histogram does not fit shared memory");
     c.total_bins = bins;
     h->k2_smem = smem;
-    h->k4_smem = (size_t)4 * nd_max * 4 + (size_t)4 * (nd_max + 32) * 8 + (size_t)4 * std::max(p.n_vel, 1) * 4;
+    // 3 staged columns + per warp: local prefix sums (float), 4 bases per lane (double), edge diameters
+    h->k4_smem = (size_t)3 * nd_max * 4 + (size_t)4 * ((size_t)nd_max * 4 + 128 * 8 + (size_t)((std::max(p.n_vel, 1) + 1) & ~1) * 4);
     return RADOP_OK;
 }
 
@@ -551,7 +560,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         CU(h, h->d3_uh.reserve((size_t)n * 8));
         CU(h, h->d3_w.reserve((size_t)n * 4));
         CU(h, h->d3_rho.reserve((size_t)n * 4));
-        CU(h, h->d3_e.reserve((size_t)n * 4));
+        CU(h, h->d3_st.reserve((size_t)n * 8));
         CU(h, h->attw.reserve((size_t)n * 4));
         CU(h, h->spec_acc.reserve(c_rg * c.n_vel * 8));
         CU(h, h->spec_out.reserve(n_rg * c.n_vel * 4));
@@ -637,7 +646,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         o.hist = h->hist.as<int>(); o.flags = h->flags.as<int>();
         if (c.doppler_scheme == 3) {
             o.d3_uh = h->d3_uh.as<double>(); o.d3_w = h->d3_w.as<float>(); o.d3_rho = h->d3_rho.as<float>();
-            o.d3_e = h->d3_e.as<float>();
+            o.d3_st = h->d3_st.as<float2>();
         }
         if (c.keep_debug) {
             o.dbg_cell = h->dbg_cell.as<int>(); o.dbg_level = h->dbg_level.as<int>(); o.dbg_status = h->dbg_status.as<int>();
@@ -694,7 +703,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             a4.mask = h->mask.as<int8_t>(); a4.active = h->active.as<uint8_t>(); a4.sz_out = h->sz_out.as<float>();
             a4.sub_weight = scan.sub_weight;
             a4.d3_uh = h->d3_uh.as<double>(); a4.d3_w = h->d3_w.as<float>(); a4.d3_rho = h->d3_rho.as<float>();
-            a4.d3_e = h->d3_e.as<float>(); a4.ray_nyquist = nyq;
+            a4.d3_st = h->d3_st.as<float2>(); a4.ray_nyquist = nyq;
             a4.attw = h->attw.as<float>(); a4.spec_acc = h->spec_acc.as<double>();
             a4.spec_out = h->spec_out.as<float>() + off_rg * c.n_vel;
             a4.out = h->out.as<float>() + off_rg;

@@ -590,6 +590,7 @@ struct ScanDev {
     const int *sub_jv;
     const double *sub_weight;
     const float *traj_s, *traj_h, *traj_e;
+    const float *traj_sin, *traj_tan;   // optional (Doppler scheme 3)
 };
 
 struct K1Out {
@@ -600,7 +601,8 @@ struct K1Out {
     float *vsum, *nsum;    // [sbg] analytic fall-speed moments (non-numeric species)
     // Doppler scheme 3 (spectrum): horizontal wind along the sub-beam azimuth, W, RHO, folded elevation
     double *d3_uh;
-    float *d3_w, *d3_rho, *d3_e;
+    float *d3_w, *d3_rho;
+    float2 *d3_st;         // float32 (sin, tan) of the folded elevation
     uint16_t *key;         // [species][sbg]
     float *p0, *p1;        // [species][sbg]
     float *vals;           // [sbg][NVP] interpolated variables (model output / debug) or null
@@ -823,10 +825,15 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                 o.d3_uh[sbg] = (double)val[RADOP_VAR_U] * kc.sinA1 + (double)val[RADOP_VAR_V] * kc.cosA1;
                 o.d3_w[sbg] = val[RADOP_VAR_W];
                 o.d3_rho[sbg] = val[RADOP_VAR_RHO];
-                float ef = e_g;
-                if (ef > 90.f) ef = __fsub_rn(180.f, ef);
-                if (ef < 0.f) ef = -ef;
-                o.d3_e[sbg] = ef;
+                if (scan.traj_sin) o.d3_st[sbg] = make_float2(__ldg(scan.traj_sin + trow), __ldg(scan.traj_tan + trow));
+                else {
+                    float ef = e_g;
+                    if (ef > 90.f) ef = __fsub_rn(180.f, ef);
+                    if (ef < 0.f) ef = -ef;
+                    double sn, cs;
+                    sincos((double)__fmul_rn(ef, 0.017453292519943295f), &sn, &cs);
+                    o.d3_st[sbg] = make_float2((float)sn, (float)(sn / cs));
+                }
             }
             o.active[sbg] = active;
             o.wind[sbg] = wind;
@@ -1625,7 +1632,8 @@ struct K4Args {
     const float *sz_out;
     const double *sub_weight;
     const double *d3_uh;
-    const float *d3_w, *d3_rho, *d3_e;
+    const float *d3_w, *d3_rho;
+    const float2 *d3_st;
     const float *ray_nyquist;
     float *attw;          // [sbg] quadrature weight x attenuation factor of the sub-beam at the gate
     double *spec_acc;     // [ray][gate][n_vel] float64 accumulator (atomics)
@@ -1699,6 +1707,9 @@ k_beam_attenuation(const __grid_constant__ DevConfig cfg, K4Args A)
 //      species with float64 atomics.
 extern __shared__ __align__(16) unsigned char s_k4[];
 
+// running sums of one lane's samples [k0, k0 + cpl): four independent chains of cpl / 4
+// consecutive samples each (latency of the float64 adds), local prefix stored in float32
+#define SPEC_SUB 4
 __global__ void __launch_bounds__(128)
 k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
 {
@@ -1708,15 +1719,15 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
     const int nbins = cfg.total_bins, nsp = cfg.n_species, ng = cfg.n_gates, nvel = cfg.n_vel;
     int nd_max = 0;
     for (int s = 0; s < nsp; ++s) nd_max = max(nd_max, cfg.sp[s].nd);
-    // shared memory carve-up
-    float *s_col0 = reinterpret_cast<float *>(s_k4);            // b D^mu dD   (transposed)
+    // shared memory carve-up (sample k of lane l = k / cpl sits at (k % cpl) * 32 + l)
+    float *s_col0 = reinterpret_cast<float *>(s_k4);            // b D^mu dD
     float *s_auxp = s_col0 + nd_max;                            // D^nu or D^0.6357
     float *s_colm = s_auxp + nd_max;                            // a D^b dD (1-mom ice)
-    float *s_dax = s_colm + nd_max;                             // D
-    double *s_C = reinterpret_cast<double *>(s_dax + nd_max) + (size_t)wid * (nd_max + 32);
-    double *s_base = s_C + nd_max;
-    float *s_D = reinterpret_cast<float *>(reinterpret_cast<double *>(s_dax + nd_max) + (size_t)4 * (nd_max + 32)) +
-                 (size_t)wid * nvel;
+    const size_t per_warp = (size_t)nd_max * 4 + 128 * 8 + (size_t)((nvel + 1) & ~1) * 4;
+    unsigned char *wbase = reinterpret_cast<unsigned char *>(s_colm + nd_max) + (size_t)wid * per_warp;
+    double *s_base = reinterpret_cast<double *>(wbase);         // [32 lanes][SPEC_SUB] exclusive bases
+    float *s_C = reinterpret_cast<float *>(wbase + 128 * 8);    // local inclusive prefix
+    float *s_D = s_C + nd_max;                                  // diameters at the velocity edges
     const float zfac3 = (float)((double)cfg.wavelength * cfg.wavelength * cfg.wavelength * cfg.wavelength /
                                 (306.0196847852814 * (double)cfg.k_squared * (double)cfg.k_squared));   // pi^5
     int staged_bin = -1;
@@ -1740,6 +1751,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
         while (s + 1 < nsp && b >= cfg.sp[s + 1].bin_base) ++s;
         const SpeciesDev &S = cfg.sp[s];
         const int nd = S.nd, cpl = nd >> 5;          // samples per lane (nd is a multiple of 32)
+        const int sub = cpl / SPEC_SUB;              // samples per chain (nd is a multiple of 128 here)
         const int cnt = A.hist[b];
         const int tiles = (cnt + RADOP_TILE - 1) / RADOP_TILE;
         const int j0 = (unit - A.chunk_start[b]) * RADOP_CHUNK, j1 = min(tiles, j0 + RADOP_CHUNK);
@@ -1748,43 +1760,40 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
             for (int k = tid; k < nd; k += blockDim.x) {
                 const int addr = (k % cpl) * 32 + (k / cpl);
                 s_col0[addr] = __ldg(tab + (size_t)k * S.ncol);
-                s_dax[addr] = __ldg(S.aux + k);
                 s_auxp[addr] = __ldg(S.aux + (S.mode == MODE_ICE1 ? 2 * nd : nd) + k);
                 s_colm[addr] = (S.mode == MODE_ICE1) ? __ldg(tab + (size_t)k * S.ncol + 9) : 0.f;
             }
             staged_bin = b;
             __syncthreads();
         }
-        // clip limits of the species that follow s (only the present ones apply, per gate)
+        const float spec_scale = (float)((double)S.spec_step / (double)S.dD_ref);
         for (int jt = j0; jt < j1; ++jt) {
             const int first = A.bin_start[b] + jt * RADOP_TILE;
             const int n_here = min(RADOP_TILE, cnt - jt * RADOP_TILE);
             for (int i = wid; i < n_here; i += 4) {
                 const PairRec rec = A.rec[first + i];
                 const uint32_t sbg = rec.sbg;
-                const int g = (int)(sbg % (unsigned)ng);
-                const size_t rg = (size_t)(sbg / (unsigned)ng / (unsigned)cfg.n_sub) * ng + g;
+                const unsigned rq = sbg / (unsigned)ng;
+                const int g = (int)(sbg - rq * (unsigned)ng);
+                const size_t rg = (size_t)(rq / (unsigned)cfg.n_sub) * ng + g;
                 const unsigned act = A.active[sbg];
                 // ---- 1. diameters at the velocity-bin edges -----------------------------------
                 int j_a, j_b;
                 {
-                    const float theta = __fmul_rn(A.d3_e[sbg], 0.017453292519943295f);
-                    double sn, cs;
-                    sincos((double)theta, &sn, &cs);
-                    // np.tan / np.sin of a float32 angle are float32 (doppler_scatter.py:571-575)
-                    const double tan_t = (double)(float)(sn / cs), sin_t = (double)(float)sn;
+                    // np.sin / np.tan of the float32 angle are float32 (doppler_scatter.py:571-575)
+                    const float2 st = A.d3_st[sbg];
+                    const double sin_t = (double)st.x, inv_sin = 1.0 / sin_t, inv_tan = 1.0 / (double)st.y;
                     const float rho_corr = sqrtf(__fdiv_rn(A.d3_rho[sbg], A.d3_rho[sbg - g]));
-                    const double inv_rho = (double)__fdiv_rn(1.0f, rho_corr);
-                    const double c0 = (double)A.d3_w[sbg] + A.d3_uh[sbg] / tan_t;
-                    const double inv_beta = 1.0 / S.beta;
-                    const double inv_sin = 1.0 / sin_t;
+                    const float inv_rho_f = __fdiv_rn(1.0f, rho_corr);
+                    const double inv_rho = (double)inv_rho_f;
+                    const double c0 = (double)A.d3_w[sbg] + A.d3_uh[sbg] * inv_tan;
                     // wh_j = inv_rho (c0 - v_j / sin) falls with j: only the velocities between
                     // "faster than the largest particle" (D = d_max, empty bins) and "wh < 0"
                     // (no bin) can hold power.  Outside the normal case the whole array is done.
                     j_a = 0; j_b = nvel - 1;
-                    if (sin_t > 0.0 && inv_rho > 0.0 && isfinite(c0)) {
-                        const double ja = floor(((c0 - S.wh_hi / inv_rho) * sin_t - cfg.vel_min) / cfg.vel_res) - 1.0;
-                        const double jb = floor((c0 * sin_t - cfg.vel_min) / cfg.vel_res) + 2.0;
+                    if (sin_t > 0.0 && inv_rho_f > 0.f && isfinite(c0)) {
+                        const double ja = floor(((c0 - S.wh_hi * (double)rho_corr * 1.000001) * sin_t - cfg.vel_min) * cfg.inv_vel_res) - 1.0;
+                        const double jb = floor((c0 * sin_t - cfg.vel_min) * cfg.inv_vel_res) + 2.0;
                         j_a = (int)fmin(fmax(ja, 0.0), (double)(nvel - 1));
                         j_b = (int)fmin(fmax(jb, 0.0), (double)(nvel - 1));
                     }
@@ -1797,7 +1806,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                             // clip to the axis ends whatever the power law gives (margin 1e-9 >> rounding)
                             if (wh >= S.wh_hi) D = S.d_max;
                             else if (wh <= S.wh_lo) D = S.d_min;
-                            else D = (float)pow(wh / S.alpha, inv_beta);
+                            else D = (float)pow(wh * S.inv_alpha, S.inv_beta);
                             for (int t = s; t < nsp; ++t) {
                                 if (!(act & (1u << t))) continue;
                                 if (D >= cfg.sp[t].d_max) D = cfg.sp[t].d_max;
@@ -1808,24 +1817,33 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     }
                 }
                 // ---- 2. prefix sums of N(D_k) rcs(D_k) dD over this lane's samples ------------
-                double loc = 0.0;
+                double loc[SPEC_SUB];
+#pragma unroll
+                for (int u = 0; u < SPEC_SUB; ++u) loc[u] = 0.0;
                 float n0 = rec.p1;
-                const int k0 = lane * cpl;
+                const float *Dax = S.aux + lane * cpl;          // diameters of this lane's samples
                 if (S.mode == MODE_ICE1) {
                     const float lam = rec.p0;
                     const float a1 = -20.78f * LOG2E * lam, a2 = -3.290f * LOG2E * lam;
                     const float c2 = 17.46f * exp2f(0.6357f * log2f(lam));
                     const float r1 = ex2f_approx(a1 * S.dD_geo), r2 = ex2f_approx(a2 * S.dD_geo);
-                    const float d0 = s_dax[lane];
-                    float E1 = 490.6f * ex2f_approx(a1 * d0), E2 = c2 * ex2f_approx(a2 * d0);
-                    float mass = 0.f;
-                    for (int ii = 0; ii < cpl; ++ii) {
-                        const int ad = ii * 32 + lane;
-                        const float phi = fmaf(s_auxp[ad], E2, E1);
-                        mass = fmaf(s_colm[ad], phi, mass);
-                        loc += (double)(s_col0[ad] * phi);
-                        s_C[ad] = loc;
-                        E1 *= r1; E2 *= r2;
+                    float E1[SPEC_SUB], E2[SPEC_SUB], mass = 0.f;
+#pragma unroll
+                    for (int u = 0; u < SPEC_SUB; ++u) {
+                        const float d0 = __ldg(Dax + u * sub);
+                        E1[u] = 490.6f * ex2f_approx(a1 * d0);
+                        E2[u] = c2 * ex2f_approx(a2 * d0);
+                    }
+                    for (int ii = 0; ii < sub; ++ii) {
+#pragma unroll
+                        for (int u = 0; u < SPEC_SUB; ++u) {
+                            const int ad = (u * sub + ii) * 32 + lane;
+                            const float phi = fmaf(s_auxp[ad], E2[u], E1[u]);
+                            mass = fmaf(s_colm[ad], phi, mass);
+                            loc[u] += (double)(s_col0[ad] * phi);
+                            s_C[ad] = (float)loc[u];
+                            E1[u] *= r1; E2[u] *= r2;
+                        }
                     }
 #pragma unroll
                     for (int d = 16; d > 0; d >>= 1) mass += __shfl_xor_sync(0xffffffffu, mass, d);
@@ -1833,37 +1851,46 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                 } else if (S.mode == MODE_GEO8) {
                     const float a = -LOG2E * rec.p0;
                     const float r = ex2f_approx(a * S.dD_geo);
-                    float E = ex2f_approx(a * s_dax[lane]);
-                    for (int ii = 0; ii < cpl; ++ii) {
-                        const int ad = ii * 32 + lane;
-                        loc += (double)(s_col0[ad] * E);
-                        s_C[ad] = loc;
-                        E *= r;
+                    float E[SPEC_SUB];
+#pragma unroll
+                    for (int u = 0; u < SPEC_SUB; ++u) E[u] = ex2f_approx(a * __ldg(Dax + u * sub));
+                    for (int ii = 0; ii < sub; ++ii) {
+#pragma unroll
+                        for (int u = 0; u < SPEC_SUB; ++u) {
+                            const int ad = (u * sub + ii) * 32 + lane;
+                            loc[u] += (double)(s_col0[ad] * E[u]);
+                            s_C[ad] = (float)loc[u];
+                            E[u] *= r;
+                        }
                     }
                 } else {
                     const float a = -LOG2E * rec.p0;
-                    for (int ii = 0; ii < cpl; ++ii) {
-                        const int ad = ii * 32 + lane;
-                        loc += (double)(s_col0[ad] * ex2f_approx(a * s_auxp[ad]));
-                        s_C[ad] = loc;
+                    for (int ii = 0; ii < sub; ++ii) {
+#pragma unroll
+                        for (int u = 0; u < SPEC_SUB; ++u) {
+                            const int ad = (u * sub + ii) * 32 + lane;
+                            loc[u] += (double)(s_col0[ad] * ex2f_approx(a * s_auxp[ad]));
+                            s_C[ad] = (float)loc[u];
+                        }
                     }
                 }
-                {   // exclusive scan of the lane totals
-                    double x = loc;
+                {   // exclusive scan of the lane totals, then the bases of the four chains
+                    const double tot = (loc[0] + loc[1]) + (loc[2] + loc[3]);
+                    double x = tot;
 #pragma unroll
                     for (int d = 1; d < 32; d <<= 1) {
                         const double t = __shfl_up_sync(0xffffffffu, x, d);
                         if (lane >= d) x += t;
                     }
                     const double prev = __shfl_up_sync(0xffffffffu, x, 1);
-                    s_base[lane] = lane ? prev : 0.0;
+                    double bs = lane ? prev : 0.0;
+#pragma unroll
+                    for (int u = 0; u < SPEC_SUB; ++u) { s_base[lane * SPEC_SUB + u] = bs; bs += loc[u]; }
                 }
                 __syncwarp();
                 // ---- 3. velocity bins -----------------------------------------------------------
-                const double scale = 6.283185307179586 * (double)n0 * (double)zfac3 * (double)A.attw[sbg] *
-                                     ((double)S.spec_step / (double)S.dD_ref);
+                const double scale = 6.283185307179586 * (double)n0 * (double)zfac3 * (double)A.attw[sbg] * (double)spec_scale;
                 double *dst = A.spec_acc + rg * nvel;
-                (void)k0;
                 for (int j = j_a + lane; j < j_b; j += 32) {
                     const float Dj = s_D[j];
                     if (isnan(Dj)) continue;
@@ -1877,15 +1904,16 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     const int ib = min((int)__fdiv_rn(__fsub_rn(Db, S.d_min), S.spec_step), nd);
                     if (ib <= ia || ia < 0) continue;
                     const int kb = ib - 1, ka = ia - 1;
-                    const int lb = kb / cpl, la = (ka >= 0) ? ka / cpl : -1;
-                    const double cb = s_C[(kb % cpl) * 32 + lb];
-                    const double ca = (ka >= 0) ? s_C[(ka % cpl) * 32 + la] : 0.0;
+                    // chain index = k / sub; position in shared memory (k % cpl) * 32 + k / cpl
+                    const int cb = kb / sub, ca = (ka >= 0) ? ka / sub : -1;
+                    const double vb = (double)s_C[(kb % cpl) * 32 + kb / cpl];
+                    const double va = (ka >= 0) ? (double)s_C[(ka % cpl) * 32 + ka / cpl] : 0.0;
                     double diff;
-                    if (la == lb) diff = cb - ca;               // same lane: one running sum, exact order
+                    if (ca == cb) diff = vb - va;               // same chain: one running sum
                     else {
-                        const double hi = s_base[lb] + cb, lo = (ka >= 0) ? s_base[la] + ca : 0.0;
+                        const double hi = s_base[cb] + vb, lo = (ka >= 0) ? s_base[ca] + va : 0.0;
                         diff = hi - lo;
-                        if (fabs(diff) < 2e-15 * fabs(hi)) diff = 0.0;      // rounding of the lane bases
+                        if (fabs(diff) < 2e-15 * fabs(hi)) diff = 0.0;      // rounding of the bases
                     }
                     const double val = diff * scale;
                     if (val != 0.0) atomicAdd(dst + j, val);

@@ -31,6 +31,7 @@ struct SpeciesDev {
     float dD_geo;               // (D[nd-1]-D[0])/(nd-1) computed in double
     float dD_ref;               // D[1]-D[0] in float32 (doppler_scatter.py:224)
     float d_min, d_max;         // first / last diameter of the table axis (float32)
+    double inv_beta, inv_alpha;
     double wh_lo, wh_hi;        // fall speeds alpha D^beta of d_min (x (1 - 1e-9)) and d_max (x (1 + 1e-9))
     float spec_step;            // float32(np.linspace(d_min, d_max, nd))[1] - [0]: step_D of the spectrum
                                 // (doppler_scatter.py:686-692; differs from dD_ref by ulps)
@@ -69,7 +70,7 @@ struct DevConfig {
     float sens0, sens1;
     // Doppler spectrum (scheme 3): VARRAY[j] = vel_min + j vel_res, j < n_vel (global_constants.py:168-171)
     int n_vel;
-    double vel_min, vel_res;
+    double vel_min, vel_res, inv_vel_res;
     SpeciesDev sp[RADOP_NSPECIES_MAX];
 };
 

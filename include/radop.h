@@ -130,6 +130,11 @@ typedef struct {
     const float *traj_s;        /* [n_traj][n_vert][n_gates] ground distance [m]          */
     const float *traj_h;        /* [n_traj][n_vert][n_gates] height [m]                   */
     const float *traj_e;        /* [n_traj][n_vert][n_gates] incidence elevation [deg]    */
+    /* Doppler scheme 3 only, optional (NULL: computed on the device): float32 sine and tangent
+     * of the elevation folded to [0, 90] deg, as numpy gives them for a float32 angle
+     * (get_diameter_from_rad_vel, doppler_scatter.py:571-575), same shape as traj_e         */
+    const float *traj_sin;
+    const float *traj_tan;
 } RadopScan;
 
 /* radar observables, linear units (doppler_scatter.py:446-460) */
