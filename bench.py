@@ -379,6 +379,9 @@ def run_ours(args):
     pairs = float(st['n_active_pairs'])
     flops = FLOP_PER_PAIR * pairs
     achieved = flops / (st['ms_integrate'] * 1e-3) / 1e12 if st['ms_integrate'] > 0 else None
+    # what the kernel really executes (7 combined columns, Horner recurrence): FP32 lane operations
+    exec_flops = float(sum(n * f for n, f in zip(st['pairs_by_species'], st['exec_flop_per_pair'])))
+    executed = exec_flops / (st['ms_integrate'] * 1e-3) / 1e12 if st['ms_integrate'] > 0 else None
     sbg1 = float(scan.n_subbeam_gates)
     nvar = 9
     alg_bytes = sbg1 * (nvar * 32 + 32) + scan.n_rays * scan.n_gates * 52 + st['n_lut_bins'] * 49152
@@ -397,6 +400,14 @@ def run_ours(args):
                      'peak_kind': 'measured here: dependent-free FFMA probe, sustained (median of back-to-back runs); '
                                   'burst {:.1f}. MEASURED_PEAKS.json holds no FP32 figure (hbm {} GB/s)'.format(
                                       burst, peaks.get('hbm_gbs')),
+                     'note': 'achieved counts the ALGORITHMIC 28672 flop per active pair (SURVEY.md 8d: 12-column '
+                             'contraction + per-diameter PSD evaluation); the kernel executes fewer (7 linear '
+                             'combinations of the 12 columns, geometric recurrence instead of exp per diameter), so '
+                             'frac can exceed 1. executed_* is the FP32 work actually issued against the same peak.',
+                     'executed_tflops': executed, 'executed_frac': (executed / sustained) if executed else None,
+                     'executed_flop_per_launch': exec_flops,
+                     'pairs_by_species': dict(zip(eng.species_order, st['pairs_by_species'])),
+                     'step_frac_of_fp32_floor': (flops / (sustained * 1e12) * 1e3) / (ms / args.steps),
                      'algorithmic_flop_per_launch': flops, 'flop_per_active_pair': FLOP_PER_PAIR,
                      'active_pairs_per_launch': pairs, 'kernel_ms': st['ms_integrate'],
                      'hbm_floor_ms': alg_bytes / (peaks.get('hbm_gbs', 6650.0) * 1e9) * 1e3,

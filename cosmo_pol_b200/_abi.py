@@ -65,7 +65,8 @@ class RadopStats(C.Structure):
     _fields_ = [('n_subbeam_gates', C.c_int64), ('n_active_pairs', C.c_int64), ('n_lut_bins', C.c_int64),
                 ('n_tiles', C.c_int64), ('launches', C.c_int64), ('ms_interp', C.c_float), ('ms_sort', C.c_float),
                 ('ms_integrate', C.c_float), ('ms_reduce', C.c_float), ('ms_total', C.c_float),
-                ('n_timed', C.c_int32), ('ms_spectrum', C.c_float)]
+                ('n_timed', C.c_int32), ('ms_spectrum', C.c_float),
+                ('pairs_by_species', C.c_int64 * NSPECIES_MAX), ('exec_flop_per_pair', C.c_double * NSPECIES_MAX)]
 
 
 class RadopError(RuntimeError):
@@ -372,7 +373,10 @@ class Engine(object):
     def stats(self):
         s = RadopStats()
         self._check(self.lib.radop_get_stats(self.h, C.byref(s)))
-        return {k: getattr(s, k) for k, _ in RadopStats._fields_}
+        d = {k: getattr(s, k) for k, _ in RadopStats._fields_}
+        d['pairs_by_species'] = [int(x) for x in s.pairs_by_species]
+        d['exec_flop_per_pair'] = [float(x) for x in s.exec_flop_per_pair]
+        return d
 
     def stream_ptr(self):
         p = C.c_void_p()

@@ -47,6 +47,8 @@ struct LutHost {
 
 }  // namespace
 
+#define RADOP_TOTALS 16      // slots of the per-chunk totals written by k_scan_bins
+
 struct RadopHandle_ {
     int device = 0;
     cudaStream_t stream = nullptr, copy_stream = nullptr;
@@ -551,7 +553,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     CU(h, h->tile_start.reserve((size_t)(c.total_bins + 1) * 4));
     CU(h, h->cost_start.reserve((size_t)(c.total_bins + 1) * 8));
     CU(h, h->cursor.reserve((size_t)c.total_bins * 4));
-    CU(h, h->totals.reserve((size_t)n_chunks * 4 * 8));
+    CU(h, h->totals.reserve((size_t)n_chunks * RADOP_TOTALS * 8));
     CU(h, h->rec.reserve((size_t)n * nsp * sizeof(PairRec)));
     CU(h, h->sz_out.reserve((size_t)n * nsp * 8 * 4));
     CU(h, h->ice_vn.reserve((size_t)n * 8));
@@ -634,7 +636,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         scan.ray_az += r0;
         scan.ray_traj += r0;
         const float *nyq = h->d_nyquist ? h->d_nyquist + r0 : nullptr;
-        long long *totals = h->totals.as<long long>() + 4 * ch;
+        long long *totals = h->totals.as<long long>() + RADOP_TOTALS * ch;
 
         K1Out o;
         memset(&o, 0, sizeof o);
@@ -775,15 +777,30 @@ static void average_timings(RadopHandle *h)
 
 static int finish(RadopHandle *h)
 {   // after the stream has drained: flags + statistics
-    std::vector<long long> tot((size_t)4 * std::max(1, h->n_chunks));
+    std::vector<long long> tot((size_t)RADOP_TOTALS * std::max(1, h->n_chunks));
     int flags[4];
     CU(h, cudaMemcpy(tot.data(), h->totals.p, tot.size() * 8, cudaMemcpyDeviceToHost));
     CU(h, cudaMemcpy(flags, h->flags.p, sizeof flags, cudaMemcpyDeviceToHost));
     h->stats.n_active_pairs = h->stats.n_tiles = h->stats.n_lut_bins = 0;
+    for (int s = 0; s < RADOP_NSPECIES_MAX; ++s) h->stats.pairs_by_species[s] = 0;
     for (int ch = 0; ch < std::max(1, h->n_chunks); ++ch) {
-        h->stats.n_active_pairs += tot[4 * ch];
-        h->stats.n_tiles += tot[4 * ch + 1];
-        h->stats.n_lut_bins += tot[4 * ch + 3];      // (species, e, t) bins staged, summed over the chunks
+        const long long *t = tot.data() + (size_t)RADOP_TOTALS * ch;
+        h->stats.n_active_pairs += t[0];
+        h->stats.n_tiles += t[1];
+        h->stats.n_lut_bins += t[3];      // (species, e, t) bins staged, summed over the chunks
+        for (int s = 0; s < RADOP_NSPECIES_MAX; ++s) h->stats.pairs_by_species[s] += t[4 + s];
+    }
+    // FP32 operations the integration kernel executes per pair (2 per FMA lane): columns x diameters
+    for (int s = 0; s < RADOP_NSPECIES_MAX; ++s) h->stats.exec_flop_per_pair[s] = 0;
+    for (int s = 0; s < h->cfg.n_species; ++s) {
+        const SpeciesDev &S = h->cfg.sp[s];
+        const int extra = h->cfg.doppler_scheme == 2 ? 1 : 0;
+        double per_d = 0;
+        if (S.mode == MODE_GEO8) per_d = 2.0 * (RADOP_NC + extra);
+        else if (S.mode == MODE_GEN8) per_d = 2.0 * (RADOP_NC + extra) + 2.0;      // + a D^nu, ex2
+        else if (S.mode == MODE_GEN12) per_d = 2.0 * 9 + 2.0;
+        else per_d = 2.0 * 10 + 2.0 + 2.0;                                          // ICE1: + shape FMA, two recurrences
+        h->stats.exec_flop_per_pair[s] = per_d * S.nd;
     }
     average_timings(h);
     if (flags[0] & 1)

@@ -867,7 +867,7 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
 // ------------------------------------------------------------------------------------------
 // One block.  bin_start = exclusive scan of the counts; tile_start = exclusive scan of
 // ceil(count/TILE); chunk_start = exclusive scan of ceil(tiles/CHUNK) (the work units the
-// integration kernel hands out dynamically); totals[] = {pairs, tiles, chunks, bins}
+// integration kernel hands out dynamically); totals[] = {pairs, tiles, chunks, bins, pairs of species 0..4}
 __global__ void k_scan_bins(const __grid_constant__ DevConfig cfg, const int *__restrict__ hist, int *bin_start,
                             int *tile_start, int *chunk_start, int *cursor, long long *totals)
 {
@@ -875,7 +875,9 @@ __global__ void k_scan_bins(const __grid_constant__ DevConfig cfg, const int *__
     __shared__ int s_warp[3][32];
     const int tid = threadIdx.x, nthr = blockDim.x;
     __shared__ int s_bins;
+    __shared__ int s_species[RADOP_NSPECIES_MAX];
     if (tid == 0) { s_tot[0] = s_tot[1] = s_tot[2] = 0; s_bins = 0; }
+    if (tid < RADOP_NSPECIES_MAX) s_species[tid] = 0;
     __syncthreads();
     for (int base = 0; base < cfg.total_bins; base += nthr) {
         int b = base + tid;
@@ -917,7 +919,12 @@ __global__ void k_scan_bins(const __grid_constant__ DevConfig cfg, const int *__
             cursor[b] = bs;
             tile_start[b] = s_tot[1] + off1 + v1 - tiles;
             chunk_start[b] = s_tot[2] + off2 + v2 - chunks;
-            if (cnt) atomicAdd(&s_bins, 1);
+            if (cnt) {
+                atomicAdd(&s_bins, 1);
+                int sp = 0;
+                while (sp + 1 < cfg.n_species && b >= cfg.sp[sp + 1].bin_base) ++sp;
+                atomicAdd(&s_species[sp], cnt);
+            }
         }
         __syncthreads();
         if (tid == nthr - 1) {
@@ -935,6 +942,7 @@ __global__ void k_scan_bins(const __grid_constant__ DevConfig cfg, const int *__
         totals[1] = s_tot[1];
         totals[2] = s_tot[2];
         totals[3] = s_bins;
+        for (int sp = 0; sp < RADOP_NSPECIES_MAX; ++sp) totals[4 + sp] = s_species[sp];
     }
 }
 

@@ -209,6 +209,9 @@ typedef struct {
                                      over the executes since radop_enable_timing(h, 1)     */
     int32_t n_timed;              /* executes in that mean                                  */
     float ms_spectrum;            /* Doppler-spectrum kernels (scheme 3), included in ms_total */
+    int64_t pairs_by_species[RADOP_NSPECIES_MAX];   /* active pairs per species (params order)   */
+    double exec_flop_per_pair[RADOP_NSPECIES_MAX];  /* FP32 operations the integration kernel
+                                     executes per pair of that species (2 per FMA lane)        */
 } RadopStats;
 int radop_get_stats(RadopHandle *h, RadopStats *s);
 int radop_enable_timing(RadopHandle *h, int on);
