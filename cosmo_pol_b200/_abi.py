@@ -10,13 +10,13 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libradop.so')
 
-RADOP_ABI_VERSION = 2
+RADOP_ABI_VERSION = 3
 NSPECIES_MAX = 5
 NVAR_MAX = 16
 N_OUT = 10
 OUT_NAMES = ['ZH', 'ZDR', 'ZV', 'KDP', 'DELTA_HV', 'PHIDP', 'RHOHV', 'ATT_H', 'ATT_V', 'RVEL']
 VAR_IDS = {'U': 0, 'V': 1, 'W': 2, 'T': 3, 'RHO': 4, 'QR_v': 5, 'QS_v': 6, 'QG_v': 7, 'QI_v': 8, 'QH_v': 9,
-           'QNR_v': 10, 'QNS_v': 11, 'QNG_v': 12, 'QNI_v': 13, 'QNH_v': 14}
+           'QNR_v': 10, 'QNS_v': 11, 'QNG_v': 12, 'QNI_v': 13, 'QNH_v': 14, 'EDR': 15}
 VAR_NAMES = {v: k for k, v in VAR_IDS.items()}
 SPECIES_IDS = {'R': 0, 'S': 1, 'G': 2, 'H': 3, 'I': 4}
 
@@ -45,7 +45,9 @@ class RadopParams(C.Structure):
                 ('sensitivity_mode', C.c_int32), ('sensitivity', C.c_double * 3),
                 ('output_model_vars', C.c_int32), ('keep_debug', C.c_int32), ('n_species', C.c_int32),
                 ('reserved', C.c_int32), ('species', RadopSpecies * NSPECIES_MAX),
-                ('n_vel', C.c_int32), ('reserved2', C.c_int32), ('vel_min', C.c_double), ('vel_res', C.c_double)]
+                ('n_vel', C.c_int32), ('reserved2', C.c_int32), ('vel_min', C.c_double), ('vel_res', C.c_double),
+                ('spectrum_turbulence', C.c_int32), ('spectrum_motion', C.c_int32),
+                ('antenna_speed', C.c_double), ('beamwidth_deg', C.c_double)]
 
 
 class RadopScan(C.Structure):
@@ -228,9 +230,11 @@ class Engine(object):
         p.doppler_scheme = int(config['doppler']['scheme'])
         if p.doppler_scheme == 3:
             d = config['doppler']
-            if d.get('turbulence_correction', 0) or d.get('motion_correction', 0):
-                raise ValueError('spectrum broadening (turbulence_correction / motion_correction, '
-                                 'doppler_scatter.py:727-801) is not implemented in the GPU path')
+            # broadening of the sub-beam spectra (doppler_scatter.py:357-367, 727-801)
+            p.spectrum_turbulence = 1 if d.get('turbulence_correction', 0) else 0
+            p.spectrum_motion = 1 if d.get('motion_correction', 0) else 0
+            p.antenna_speed = float(r.get('antenna_speed', 0.2))
+            p.beamwidth_deg = float(r['3dB_beamwidth'])
             # constants.VARRAY = np.arange(-NVEL, NVEL + VRES, VRES), global_constants.py:168-171
             p.n_vel = len(constants.VARRAY)
             p.vel_min, p.vel_res = float(-constants.NVEL), float(constants.VRES)

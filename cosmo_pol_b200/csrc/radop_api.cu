@@ -80,7 +80,7 @@ struct RadopHandle_ {
     // work buffers
     DevBuf geo, mask, active, wind, sinth, vsum, nsum, key, p0, p1, vals, lat, lon, hist, flags;
     DevBuf bin_start, tile_start, cost_start, cursor, totals, rec, sz_out, ice_vn, dop_vn, ice_tot, comb, out, model_out;
-    DevBuf d3_uh, d3_w, d3_rho, d3_st, attw, spec_acc, spec_out;
+    DevBuf d3_uh, d3_w, d3_rho, d3_st, attw, spec_acc, spec_out, d3_std, sub_acc, brd_flag;
     size_t k4_smem = 0;
     DevBuf dbg_cell, dbg_level, dbg_status, dbg_e, dbg_t, dbg_rot;
     DevConfig cfg;
@@ -157,7 +157,7 @@ int radop_destroy(RadopHandle *h)
     DevBuf *bufs[] = {&h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
                       &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
                       &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
-                      &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_st, &h->attw, &h->spec_acc, &h->spec_out, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
+                      &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_st, &h->attw, &h->spec_acc, &h->spec_out, &h->d3_std, &h->sub_acc, &h->brd_flag, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
                       &h->dbg_status, &h->dbg_e, &h->dbg_t, &h->dbg_rot};
     for (DevBuf *b : bufs) b->release();
     for (auto &l : h->lut) { l.table.release(); l.aux.release(); }
@@ -182,6 +182,9 @@ int radop_set_params(RadopHandle *h, const RadopParams *p)
         return h->fail(RADOP_ERR_UNSUPPORTED, "doppler scheme must be 1, 2 or 3");
     if (p->doppler_scheme == 3 && (p->n_vel < 2 || p->n_vel > 4096 || !(p->vel_res > 0.0)))
         return h->fail(RADOP_ERR_ARG, "doppler scheme 3 needs 2 <= n_vel <= 4096 and vel_res > 0");
+    if ((p->spectrum_turbulence || p->spectrum_motion) && p->doppler_scheme == 3 &&
+        !(p->beamwidth_deg > 0.0 && p->radial_resolution_m > 0.0))
+        return h->fail(RADOP_ERR_ARG, "spectrum broadening needs beamwidth_deg > 0 and radial_resolution_m > 0");
     if (p->sensitivity_mode < 0 || p->sensitivity_mode > 2)
         return h->fail(RADOP_ERR_UNSUPPORTED, "sensitivity must be [ZH] or [ZH, range]");
     for (int s = 0; s < p->n_species; ++s) {
@@ -238,7 +241,7 @@ int radop_upload_field(RadopHandle *h, int var_id, const float *data)
 {
     if (!h || !data) return RADOP_ERR_ARG;
     if (!h->have_grid) return h->fail(RADOP_ERR_STATE, "upload the grid before the fields");
-    if (var_id < 0 || var_id >= RADOP_NVAR_MAX - 1) return h->fail(RADOP_ERR_ARG, "unknown variable id");
+    if (var_id < 0 || var_id >= RADOP_NVAR_MAX) return h->fail(RADOP_ERR_ARG, "unknown variable id");
     CU(h, cudaSetDevice(h->device));
     size_t n = (size_t)h->nz * h->ny * h->nx;
     CU(h, cudaMemcpyAsync(h->stage.p, data, n * 4, cudaMemcpyHostToDevice, h->stream));
@@ -419,6 +422,22 @@ static int prepare(RadopHandle *h)
     c.sens0 = (float)p.sensitivity[0]; c.sens1 = (float)p.sensitivity[1];
     c.n_vel = p.n_vel; c.vel_min = p.vel_min; c.vel_res = p.vel_res;
     c.inv_vel_res = p.vel_res > 0 ? 1.0 / p.vel_res : 0.0;
+    c.brd_mode = 0;
+    if (p.doppler_scheme == 3) c.brd_mode = (p.spectrum_turbulence ? 1 : 0) | (p.spectrum_motion ? 2 : 0);
+    if (c.brd_mode) {
+        // spectral_width_turb / spectral_width_motion, doppler_scatter.py:727-777
+        const double A = 1.6;                              // global_constants.py: turbulence constant
+        const double bw = p.beamwidth_deg * 0.017453292519943295;
+        c.brd_res = p.radial_resolution_m;
+        c.brd_sigma_r = 0.35 * p.radial_resolution_m;
+        c.brd_sigma_theta = bw / (4.0 * sqrt(log(2.0)));
+        c.brd_turb_far = c.brd_sigma_theta * pow(A, 1.5) / 0.72;
+        c.brd_turb_near = c.brd_sigma_r * pow(1.35 * A, 1.5);
+        c.brd_motion_num = (float)(p.wavelength_mm / 100.0 * p.antenna_speed);
+        c.brd_motion_den = 2.0 * 3.141592653589793 * bw;
+        if ((c.brd_mode & 1) && !(h->var_mask & (1u << RADOP_VAR_EDR)))
+            return h->fail(RADOP_ERR_STATE, "turbulence broadening needs the EDR variable (RADOP_VAR_EDR)");
+    }
     c.ice_numeric = -1;
     uint32_t need = (1u << RADOP_VAR_U) | (1u << RADOP_VAR_V) | (1u << RADOP_VAR_W) | (1u << RADOP_VAR_T);
     int bins = 0, nd_max = 0;
@@ -525,7 +544,12 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     const long long per_ray = (long long)c.n_sub * ng;
     int n_chunks = 1;
     // without host copies to overlap, chunks only bound the work memory (8x larger chunks)
-    const long long target = out ? h->chunk_sbg : 8 * h->chunk_sbg;
+    long long target = out ? h->chunk_sbg : 8 * h->chunk_sbg;
+    if (c.brd_mode) {
+        // the sub-beam spectra of a chunk are kept in float64: at most ~4 GB of them
+        const long long cap = std::max<long long>(per_ray, (4LL << 30) / ((long long)c.n_vel * 8));
+        target = target > 0 ? std::min(target, cap) : cap;
+    }
     if (!c.keep_debug && target > 0)
         n_chunks = (int)std::min<long long>(n_rays, std::max<long long>(1, (h->n_sbg + target / 2) / target));
     const int rays_per_chunk = (n_rays + n_chunks - 1) / n_chunks;
@@ -566,6 +590,11 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         CU(h, h->attw.reserve((size_t)n * 4));
         CU(h, h->spec_acc.reserve(c_rg * c.n_vel * 8));
         CU(h, h->spec_out.reserve(n_rg * c.n_vel * 4));
+        if (c.brd_mode) {
+            CU(h, h->d3_std.reserve((size_t)n * 8));
+            CU(h, h->sub_acc.reserve((size_t)n * c.n_vel * 8));
+            CU(h, h->brd_flag.reserve((size_t)rays_per_chunk * c.n_sub));
+        }
     }
     CU(h, h->ice_tot.reserve((size_t)rays_per_chunk * c.n_sub * 3 * 4));
     CU(h, h->comb.reserve(c_rg * 8 * 4));
@@ -586,6 +615,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         CU(h, cudaFuncSetAttribute(k_scatter_pairs, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_spectrum, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_beam_attenuation, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(h, cudaFuncSetAttribute(k_spectrum_broaden, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_done[h->device & 63] = true;
     }
     int occ = 1;
@@ -595,6 +625,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     int occ1 = 1;
     CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, k_interp_psd, 128, hist_smem));
     const size_t smem_a = (size_t)4 * 2 * ng * 4;
+    const size_t smem_b = (size_t)4 * ((size_t)BRD_WMAX * 8 + (size_t)((std::max(c.n_vel, 1) + 1) & ~1) * 8);
     int occ4 = 1;
     if (c.doppler_scheme == 3) {
         if (smem_a > 200 * 1024) return h->fail(RADOP_ERR_ARG, "too many gates per ray for the spectrum attenuation scan");
@@ -649,6 +680,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         if (c.doppler_scheme == 3) {
             o.d3_uh = h->d3_uh.as<double>(); o.d3_w = h->d3_w.as<float>(); o.d3_rho = h->d3_rho.as<float>();
             o.d3_st = h->d3_st.as<float2>();
+            if (c.brd_mode) o.d3_std = h->d3_std.as<double>();
         }
         if (c.keep_debug) {
             o.dbg_cell = h->dbg_cell.as<int>(); o.dbg_level = h->dbg_level.as<int>(); o.dbg_status = h->dbg_status.as<int>();
@@ -712,10 +744,19 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             a4.hist = h->hist.as<int>(); a4.bin_start = h->bin_start.as<int>(); a4.chunk_start = h->cost_start.as<int>();
             a4.totals = totals; a4.counter = h->flags.as<int>() + 2; a4.rec = h->rec.as<PairRec>();
             CU(h, cudaMemsetAsync(h->spec_acc.p, 0, cc_rg * c.n_vel * 8, st));
+            a4.d3_std = nullptr; a4.sub_acc = nullptr; a4.brd_flag = nullptr;
+            if (c.brd_mode) {
+                a4.d3_std = h->d3_std.as<double>(); a4.sub_acc = h->sub_acc.as<double>(); a4.brd_flag = h->brd_flag.as<uint8_t>();
+                CU(h, cudaMemsetAsync(h->sub_acc.p, 0, (size_t)nc * c.n_vel * 8, st));
+            }
             k_beam_attenuation<<<(nr * c.n_sub + 3) / 4, 128, smem_a, st>>>(c, a4);
             CU(h, cudaGetLastError()); ++launches;
             k_spectrum<<<std::max(1, occ4) * h->n_sm, 128, h->k4_smem, st>>>(c, a4);
             CU(h, cudaGetLastError()); ++launches;
+            if (c.brd_mode) {
+                k_spectrum_broaden<<<(unsigned)((nc + 3) / 4), 128, smem_b, st>>>(c, a4, nc);
+                CU(h, cudaGetLastError()); ++launches;
+            }
             k_spectrum_finish<<<(unsigned)((cc_rg * 32 + 127) / 128), 128, 0, st>>>(c, a4);
             CU(h, cudaGetLastError()); ++launches;
         }

@@ -576,6 +576,11 @@ __device__ __forceinline__ bool interp_columns(const DevConfig &cfg, const CellG
         } else {
             float a = __ldg(reinterpret_cast<const float *>(f1) + 8), b = __ldg(reinterpret_cast<const float *>(f2) + 8);
             accum(8, a, b);
+            if (cfg.var_mask & (1u << RADOP_VAR_EDR)) {
+                a = __ldg(reinterpret_cast<const float *>(f1) + RADOP_VAR_EDR);
+                b = __ldg(reinterpret_cast<const float *>(f2) + RADOP_VAR_EDR);
+                accum(RADOP_VAR_EDR, a, b);
+            }
         }
     }
     return rare;
@@ -603,6 +608,7 @@ struct K1Out {
     double *d3_uh;
     float *d3_w, *d3_rho;
     float2 *d3_st;         // float32 (sin, tan) of the folded elevation
+    double *d3_std;        // spectral width added by turbulence / antenna motion (or null)
     uint16_t *key;         // [species][sbg]
     float *p0, *p1;        // [species][sbg]
     float *vals;           // [sbg][NVP] interpolated variables (model output / debug) or null
@@ -833,6 +839,27 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                     double sn, cs;
                     sincos((double)__fmul_rn(ef, 0.017453292519943295f), &sn, &cs);
                     o.d3_st[sbg] = make_float2((float)sn, (float)(sn / cs));
+                }
+                if (o.d3_std) {
+                    double sd = 0.0;
+                    if (cfg.brd_mode & 1) {      // spectral_width_turb, doppler_scatter.py:727-758
+                        const double r = 0.5 * cfg.brd_res + (double)g * cfg.brd_res;
+                        const double edr = (double)val[RADOP_VAR_EDR];
+                        if (cfg.brd_sigma_r < 0.1 * r * cfg.brd_sigma_theta)
+                            sd += pow(r * edr * cfg.brd_turb_far, 1.0 / 3.0);
+                        else {
+                            const double x = r * cfg.brd_sigma_theta / cfg.brd_sigma_r;
+                            const double den = 11.0 / 15.0 + 4.0 / 15.0 * x * x;
+                            sd += pow((edr * cfg.brd_turb_near) / (1.0 / (den * sqrt(den))), 1.0 / 3.0);
+                        }
+                    }
+                    if (cfg.brd_mode & 2) {      // spectral_width_motion, :760-777 (float32 cosine)
+                        float ef = e_g;
+                        if (ef > 90.f) ef = __fsub_rn(180.f, ef);
+                        if (ef < 0.f) ef = -ef;
+                        sd += (double)__fmul_rn(cfg.brd_motion_num, cosf(__fmul_rn(ef, 0.017453292519943295f))) / cfg.brd_motion_den;
+                    }
+                    o.d3_std[sbg] = sd;
                 }
             }
             o.active[sbg] = active;
@@ -1645,6 +1672,10 @@ struct K4Args {
     const float *ray_nyquist;
     float *attw;          // [sbg] quadrature weight x attenuation factor of the sub-beam at the gate
     double *spec_acc;     // [ray][gate][n_vel] float64 accumulator (atomics)
+    // broadening (doppler_scatter.py:357-367): spectra are kept per sub-beam until they are filtered
+    const double *d3_std; // [sbg] added spectral width, or null
+    double *sub_acc;      // [sbg][n_vel] un-attenuated, un-weighted sub-beam spectra, or null
+    uint8_t *brd_flag;    // [ray][sub-beam] np.sum(add_specwidth) > 0
     float *spec_out;      // [ray][gate][n_vel]
     float *out;           // [N_OUT+1][ray][gate]
     // work list of the integration kernel (pairs sorted by LUT bin)
@@ -1700,6 +1731,15 @@ k_beam_attenuation(const __grid_constant__ DevConfig cfg, K4Args A)
         }
     }
     for (int g = lane; g < ng; g += 32) A.attw[base + g] = w * exp10f(-0.1f * total[g]);
+    if (A.d3_std) {
+        // the sub-beam is broadened if np.sum(add_specwidth) > 0: a NaN gate (EDR outside the model
+        // domain) switches the broadening of the whole sub-beam off (doppler_scatter.py:366)
+        double sum = 0.0;
+        for (int g = lane; g < ng; g += 32) sum += A.d3_std[base + g];
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+        if (lane == 0) A.brd_flag[rq] = (sum > 0.0) ? 1 : 0;
+    }
 }
 
 // Spectrum of every active (sub-beam gate, species) pair, one warp per pair.  The work list
@@ -1897,8 +1937,9 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                 }
                 __syncwarp();
                 // ---- 3. velocity bins -----------------------------------------------------------
-                const double scale = 6.283185307179586 * (double)n0 * (double)zfac3 * (double)A.attw[sbg] * (double)spec_scale;
-                double *dst = A.spec_acc + rg * nvel;
+                const double scale = 6.283185307179586 * (double)n0 * (double)zfac3 * (double)spec_scale *
+                                     (A.sub_acc ? 1.0 : (double)A.attw[sbg]);
+                double *dst = A.sub_acc ? A.sub_acc + (size_t)sbg * nvel : A.spec_acc + rg * nvel;
                 for (int j = j_a + lane; j < j_b; j += 32) {
                     const float Dj = s_D[j];
                     if (isnan(Dj)) continue;
@@ -1929,6 +1970,104 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                 __syncwarp();
             }
         }
+    }
+}
+
+// Broadening of the sub-beam spectra (doppler_scatter.py:357-367, 779-801), one warp per sub-beam
+// gate: the float32 spectrum of the sub-beam is filtered along the velocity axis with
+// scipy.ndimage.gaussian_filter's defaults (sigma = std / v_res; skipped when sigma <= 1e-15 or NaN;
+// radius int(4 sigma + 0.5); weights exp(-k^2 / (2 sigma^2)) normalised to 1; mode 'reflect';
+// float64 accumulation, float32 result), rescaled to its original power (rows without power become
+// 0 / 0 = NaN, as in the reference), then attenuated, weighted and added to the ray spectrum.
+#define BRD_WMAX 1024
+extern __shared__ __align__(16) unsigned char s_k4b[];
+__global__ void __launch_bounds__(128)
+k_spectrum_broaden(const __grid_constant__ DevConfig cfg, K4Args A, long long n_sbg)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const long long sbg = (long long)blockIdx.x * (blockDim.x >> 5) + wid;
+    if (sbg >= n_sbg) return;
+    const int nvel = cfg.n_vel, ng = cfg.n_gates, nvp = (nvel + 1) & ~1;
+    unsigned char *wb = s_k4b + (size_t)wid * ((size_t)BRD_WMAX * 8 + (size_t)nvp * 8);
+    double *wt = reinterpret_cast<double *>(wb);
+    float *row = reinterpret_cast<float *>(wb + (size_t)BRD_WMAX * 8), *flt = row + nvp;
+    const long long rq = sbg / ng;
+    const int g = (int)(sbg - rq * ng);
+    const size_t rg = (size_t)(rq / cfg.n_sub) * ng + g;
+    const double *src = A.sub_acc + (size_t)sbg * nvel;
+    double *dst = A.spec_acc + rg * nvel;
+    float osum = 0.f;
+    bool any = false;
+    for (int j = lane; j < nvel; j += 32) {
+        const float x = (float)src[j];      // get_doppler_spectrum returns float32
+        row[j] = x;
+        osum += x;
+        any = any || (x != 0.f);
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) osum += __shfl_xor_sync(0xffffffffu, osum, d);
+    any = __any_sync(0xffffffffu, any);
+    const bool brd = A.brd_flag[rq] != 0;
+    const double attw = (double)A.attw[sbg];
+    if (!brd) {
+        if (any)
+            for (int j = lane; j < nvel; j += 32)
+                if (row[j] != 0.f) atomicAdd(dst + j, (double)row[j] * attw);
+        return;
+    }
+    __syncwarp();
+    const double sigma = A.d3_std[sbg] / cfg.vel_res;
+    const float *res = row;
+    if (any && sigma > 1e-15) {
+        const double t = 4.0 * sigma + 0.5;
+        const int lw = t < 1e9 ? (int)t : 1000000000;
+        const double c = -0.5 / (sigma * sigma);
+        const bool tab = lw < BRD_WMAX;
+        double wsum = 0.0;
+        if (tab) {
+            for (int k = lane; k <= lw; k += 32) {
+                const double w = exp(c * (double)k * (double)k);
+                wt[k] = w;
+                wsum += k ? 2.0 * w : w;
+            }
+        } else {
+            // weights beyond 39 sigma underflow to 0: the sum is complete long before lw
+            for (int k = lane; k <= lw && (double)k <= 40.0 * sigma + 64.0; k += 32) {
+                const double w = exp(c * (double)k * (double)k);
+                wsum += k ? 2.0 * w : w;
+            }
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+        __syncwarp();
+
+        for (int j = lane; j < nvel; j += 32) {
+            double acc = (double)row[j];        // weight 1 before the normalisation
+            int ia = j, ib = j;                 // reflected indices of j - k and j + k, walked incrementally
+            int da = -1, db = 1;
+            for (int k = 1; k <= lw; ++k) {
+                ia += da; if (ia < 0) { ia = 0; da = 1; } else if (ia >= nvel) { ia = nvel - 1; da = -1; }
+                ib += db; if (ib >= nvel) { ib = nvel - 1; db = -1; } else if (ib < 0) { ib = 0; db = 1; }
+                double w;
+                if (tab) w = wt[k];
+                else {
+                    if ((double)k > 40.0 * sigma + 64.0) break;
+                    w = exp(c * (double)k * (double)k);
+                }
+                acc += w * ((double)row[ia] + (double)row[ib]);
+            }
+            flt[j] = (float)(acc / wsum);
+        }
+        res = flt;
+        __syncwarp();
+    }
+    float csum = 0.f;
+    for (int j = lane; j < nvel; j += 32) csum += res[j];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) csum += __shfl_xor_sync(0xffffffffu, csum, d);
+    for (int j = lane; j < nvel; j += 32) {
+        const float o = __fmul_rn(__fdiv_rn(res[j], csum), osum);   // spectrum / convolved_power * original_power
+        if (o != 0.f) atomicAdd(dst + j, (double)o * attw);          // NaN != 0: NaN rows propagate
     }
 }
 

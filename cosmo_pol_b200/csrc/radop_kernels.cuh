@@ -71,6 +71,12 @@ struct DevConfig {
     // Doppler spectrum (scheme 3): VARRAY[j] = vel_min + j vel_res, j < n_vel (global_constants.py:168-171)
     int n_vel;
     double vel_min, vel_res, inv_vel_res;
+    // broadening of the sub-beam spectra (doppler_scatter.py:727-801): bit 0 turbulence, bit 1 antenna motion
+    int brd_mode;
+    float brd_motion_num;       // float32(wavelength / 100 * antenna_speed)
+    double brd_motion_den;      // 2 pi deg2rad(beamwidth)
+    double brd_res;             // radial resolution (RANGE_RADAR[g] = res / 2 + g res)
+    double brd_sigma_r, brd_sigma_theta, brd_turb_far, brd_turb_near;
     SpeciesDev sp[RADOP_NSPECIES_MAX];
 };
 

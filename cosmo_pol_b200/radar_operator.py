@@ -224,6 +224,8 @@ class RadarOperator(object):
             self._engine_flags = flags
             self._dirty['params'] = False
             self._dirty['lut'] = True       # tables are premultiplied with the species constants
+        if c['doppler']['scheme'] == 3 and c['doppler']['turbulence_correction'] and 'EDR' not in self.dic_vars:
+            raise KeyError('EDR')        # subrad.values['EDR'], doppler_scatter.py:364
         if self._dirty['model']:
             eng.upload_model(self.dic_vars)
             self._dirty['model'] = False

@@ -58,7 +58,7 @@ def _smooth_noise(rng, shape, sigma):
 
 
 def make_model(nz=60, ny=400, nx=400, res=0.02, radar=ALBIS, scheme='1mom', seed=1234,
-               south_pole=SOUTH_POLE, top=22000.0):
+               south_pole=SOUTH_POLE, top=22000.0, with_edr=False):
     """Returns dict name -> ModelVariable (all float32, C-contiguous)."""
     rng = np.random.default_rng(seed)
     rlat0, rlon0 = _wgs_to_rot(radar[0], radar[1], south_pole[0], south_pole[1])
@@ -117,6 +117,12 @@ def make_model(nz=60, ny=400, nx=400, res=0.02, radar=ALBIS, scheme='1mom', seed
             xbar = np.exp(np.log(lo) + (np.log(hi) - np.log(lo)) * u)
             data['QN' + h + '_v'] = (data['Q' + h + '_v'].astype(np.float64) / xbar).astype(np.float32)
         names += BASE_VARIABLES_2MOM
+    if with_edr:
+        # eddy dissipation rate [m2 s-3] (radar_operator.py:253-254), drawn last so that the other
+        # variables do not depend on the flag
+        edr = 10.0 ** (-3.0 + 0.8 * np.clip(_smooth_noise(rng, shape, sig), -2.0, 2.0))
+        data['EDR'] = edr.astype(np.float32)
+        names.append('EDR')
     attrs = {'z-levels': z, 'proj_info': proj, 'resolution': [res, res], 'time': '2026-01-01 00:00:00'}
     return {n: ModelVariable(n, np.ascontiguousarray(data[n]), attrs) for n in names}
 

@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define RADOP_ABI_VERSION 2
+#define RADOP_ABI_VERSION 3
 
 /* ---- status codes ------------------------------------------------------- */
 enum {
@@ -54,6 +54,7 @@ enum {
     RADOP_VAR_U = 0, RADOP_VAR_V, RADOP_VAR_W, RADOP_VAR_T, RADOP_VAR_RHO,
     RADOP_VAR_QR, RADOP_VAR_QS, RADOP_VAR_QG, RADOP_VAR_QI,          /* 9 one-moment vars */
     RADOP_VAR_QH, RADOP_VAR_QNR, RADOP_VAR_QNS, RADOP_VAR_QNG, RADOP_VAR_QNI, RADOP_VAR_QNH,
+    RADOP_VAR_EDR,               /* eddy dissipation rate, radar_operator.py:253-254 (turbulence broadening) */
     RADOP_NVAR_MAX = 16
 };
 
@@ -107,6 +108,11 @@ typedef struct {
     int32_t n_vel;
     int32_t reserved2;
     double vel_min, vel_res;
+    /* Doppler scheme 3, broadening of the sub-beam spectra (doppler_scatter.py:357-367, 727-801) */
+    int32_t spectrum_turbulence;  /* CONFIG['doppler']['turbulence_correction'] (needs RADOP_VAR_EDR) */
+    int32_t spectrum_motion;      /* CONFIG['doppler']['motion_correction']                      */
+    double antenna_speed;         /* CONFIG['radar']['antenna_speed']                            */
+    double beamwidth_deg;         /* CONFIG['radar']['3dB_beamwidth']                            */
 } RadopParams;
 
 /*

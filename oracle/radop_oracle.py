@@ -856,6 +856,68 @@ def get_doppler_spectrum(sub, hyd, luts, order, cfg, consts):
 
 
 # --------------------------------------------------------------------------- #
+# a16: spectrum broadening (doppler_scatter.py:357-367, 727-801)
+# --------------------------------------------------------------------------- #
+TURB_A = 1.6          # global_constants.py: turbulence constant A (Doviak & Zrnic p. 409)
+
+
+def spectral_width_turb(ranges, EDR, cfg):
+    """doppler_scatter.py:727-758 (python-3 division: 3/2 = 1.5)."""
+    sigma_r = 0.35 * cfg['radar']['radial_resolution']
+    sigma_theta = np.deg2rad(cfg['radar']['3dB_beamwidth']) / (4. * np.sqrt(np.log(2)))
+    std_turb = np.zeros((len(EDR),))
+    with np.errstate(invalid='ignore'):
+        idx_r = sigma_r < 0.1 * ranges * sigma_theta
+        std_turb[idx_r] = ((ranges[idx_r] * EDR[idx_r] * sigma_theta * TURB_A ** (3 / 2.)) / 0.72) ** (1 / 3.)
+        idx_r = sigma_r >= 0.1 * ranges * sigma_theta
+        std_turb[idx_r] = (((EDR[idx_r] * sigma_r * (1.35 * TURB_A) ** (3 / 2)) /
+                            (11. / 15. + 4. / 15. * (ranges[idx_r] * sigma_theta / sigma_r) ** 2)
+                            ** (-3 / 2.)) ** (1 / 3.))
+    return std_turb
+
+
+def spectral_width_motion(elevations, cfg, consts):
+    """doppler_scatter.py:760-777 (the wavelength in mm divided by 100, sic)."""
+    wavelength = consts['WAVELENGTH'] / 100.
+    bandwidth_3dB = cfg['radar']['3dB_beamwidth']
+    ang_vel = cfg['radar']['antenna_speed']
+    return ((wavelength * ang_vel * np.cos(np.deg2rad(elevations))) /
+            (2 * np.pi * np.deg2rad(bandwidth_3dB)))
+
+
+def gaussian_filter1d(x, sigma, truncate=4.0):
+    """scipy.ndimage.gaussian_filter of a 1-D array with the defaults the reference uses
+    (scipy 1.18.1 here; _filters.py: gaussian_filter -> gaussian_filter1d -> correlate1d):
+    axes with sigma <= 1e-15 (or NaN) are skipped, radius int(4 sigma + 0.5), weights
+    exp(-x^2 / (2 sigma^2)) normalised to 1, mode 'reflect' (d c b a | a b c d | d c b a),
+    float64 accumulation, result in the dtype of the input."""
+    sd = float(sigma)
+    if not sd > 1e-15:
+        return np.array(x, copy=True)
+    lw = int(truncate * sd + 0.5)
+    k = np.arange(-lw, lw + 1)
+    w = np.exp(-0.5 / (sd * sd) * k ** 2)
+    w = w / w.sum()
+    n = len(x)
+    idx = np.mod(np.arange(n)[:, None] + k[None, :], 2 * n)
+    idx = np.where(idx >= n, 2 * n - 1 - idx, idx)
+    return (np.asarray(x, dtype=np.float64)[idx] @ w).astype(np.asarray(x).dtype)
+
+
+def broaden_spectrum(spectrum, std, consts):
+    """doppler_scatter.py:779-801: rows with no power become NaN (0 / 0)."""
+    v = consts['VARRAY']
+    v_res = v[2] - v[1]
+    original_power = np.sum(spectrum, 1)
+    for i, t in enumerate(std):
+        spectrum[i, :] = gaussian_filter1d(spectrum[i, :], t / v_res)
+    convolved_power = np.sum(spectrum, 1)
+    with np.errstate(invalid='ignore', divide='ignore'):
+        spectrum = spectrum / convolved_power[:, None] * original_power[:, None]
+    return spectrum
+
+
+# --------------------------------------------------------------------------- #
 # a7-a15: get_radar_observables (doppler_scatter.py:49-489)
 # --------------------------------------------------------------------------- #
 def get_radar_observables(subs, luts, cfg, accum='ref', debug=False):
@@ -953,6 +1015,13 @@ def get_radar_observables(subs, luts, cfg, accum='ref', debug=False):
             rvel_avg = _nansum2(rvel_avg, pw * sub['quad_weight'])
         elif doppler_scheme == 3:
             spec = get_doppler_spectrum(sub, hyd, luts, list(hydrom_types), cfg, consts)
+            add_specwidth = np.zeros(len(spec))
+            if cfg['doppler'].get('turbulence_correction', 0):
+                add_specwidth += spectral_width_turb(consts['RANGE_RADAR'], sub['values']['EDR'], cfg)
+            if cfg['doppler'].get('motion_correction', 0):
+                add_specwidth += spectral_width_motion(sub['elev'], cfg, consts)
+            if np.sum(add_specwidth) > 0:          # False when a gate of the sub-beam is NaN (sic)
+                spec = broaden_spectrum(spec, add_specwidth, consts)
             if att_corr:
                 ahc = nan_cumsum(ah_per_beam)
                 sum_power = np.nansum(spec, axis=1)

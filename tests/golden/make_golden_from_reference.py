@@ -181,6 +181,10 @@ def import_reference():
 def set_config(R, config):
     R['cfg'].CONFIG = config
     sys.modules['cosmo_pol.config'].CONFIG = config
+    # doppler_scatter.py:26 binds CONFIG at import time (None), and spectral_width_turb / _motion
+    # (:741-742, 771-772) read that stale module global: as shipped, the spectrum-broadening options
+    # raise TypeError.  The goldens of those options rebind the global to the live configuration.
+    R['scatter'].CONFIG = config
     R['constants'].update()
 
 
@@ -313,6 +317,17 @@ CASES = {
     'c1mom_dop3': ('1mom', 5.6, dict(radar={'range': 20000, 'radial_resolution': 1000, 'FFT_length': 64},
                                      doppler={'scheme': 3}, integration={'nv_GH': 1, 'nh_GH': 3}),
                    [(45.0, 3.5)], {}),
+    # spectrum broadening (doppler_scatter.py:357-367, 727-801): antenna motion alone, and turbulence +
+    # motion with an EDR field.  Ray 2 of the second case leaves the model top, so its upper sub-beams hold
+    # NaN EDR gates and are not broadened (np.sum(NaN) > 0 is False)
+    'c1mom_dop3_mot': ('1mom', 5.6, dict(radar={'range': 20000, 'radial_resolution': 1000, 'FFT_length': 64},
+                                         doppler={'scheme': 3, 'motion_correction': 1},
+                                         integration={'nv_GH': 3, 'nh_GH': 1}),
+                       [(45.0, 3.5)], {}),
+    'c1mom_dop3_turb': ('1mom', 5.6, dict(radar={'range': 20000, 'radial_resolution': 1000, 'FFT_length': 64},
+                                          doppler={'scheme': 3, 'motion_correction': 1, 'turbulence_correction': 1},
+                                          integration={'nv_GH': 3, 'nh_GH': 1}),
+                        [(45.0, 3.5), (200.0, 60.0)], {'with_edr': True, 'top': 15000.0}),
 }
 MODEL_KW = dict(nz=24, ny=64, nx=64, res=0.04)
 

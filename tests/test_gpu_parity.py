@@ -247,6 +247,10 @@ def _spectrum_close(a, b, zh, what):
     underflow float32) are only required to be weak on the GPU as well."""
     a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
     assert a.shape == b.shape, (what, a.shape, b.shape)
+    # rows the reference turns into NaN (broadened sub-beam without power, doppler_scatter.py:799)
+    nan_rows = np.isnan(b).all(axis=-1)
+    assert np.isnan(a[nan_rows]).all(), what + ': NaN rows of the reference'
+    b = np.nan_to_num(b, nan=0.0)
     a = np.nan_to_num(a, nan=0.0)        # get_PPI censors empty bins to NaN (doppler_scatter.py:843-849)
     tot = b.sum(axis=-1)
     zh = np.nan_to_num(np.asarray(zh, dtype=np.float64))
@@ -306,6 +310,65 @@ def test_doppler_spectrum_against_reference_golden():
     assert np.max(np.abs(a[ok] - b[ok])) < 0.05
 
 
+@pytest.mark.parametrize('scheme,freq,turb', [('1mom', 5.6, 0), ('1mom', 5.6, 1), ('2mom', 9.41, 1)])
+def test_doppler_spectrum_broadening_against_oracle(scheme, freq, turb):
+    """Doppler scheme 3 with broadened sub-beam spectra (antenna motion, turbulence from the EDR field:
+    doppler_scatter.py:357-367, 727-801).  The 40 deg rays leave the model top: with the turbulence term
+    their sub-beams hold NaN widths and stay un-broadened, as in the reference."""
+    conf = copy.deepcopy(CONF_1MOM)
+    conf['doppler'] = {'scheme': 3, 'motion_correction': 1, 'turbulence_correction': turb}
+    conf['radar'].update({'FFT_length': 64, 'sensitivity': [-300, 10000], 'antenna_speed': 0.35})
+    op, model, luts = make_operator(conf, scheme, freq, with_edr=bool(turb), top=15000.0)
+    az = np.array([5., 95., 185., 275.])
+    els = [1.0, 8.5, 40.0]
+    rays_az, rays_el = np.tile(az, len(els)), np.repeat(els, len(az))
+    out = op.simulate_rays(rays_az, rays_el)
+    pm, pl = plain(model, luts)
+    ref = O.simulate_scan(pm, pl, oracle_cfg(op), rays_az, rays_el, accum='f64', sensitivity_cut=True)
+    assert_observables_close(out, ref, what='dop3 broadened ' + scheme)
+    strong = _spectrum_close(out['DSPECTRUM'], ref['DSPECTRUM'], ref['ZH'], 'dop3 broadened ' + scheme)
+    a, b = out['RVEL'], ref['RVEL']
+    assert np.all(np.isnan(a[np.isnan(b)])) and np.all(np.isfinite(a[strong]))
+    ok = np.isfinite(b) & strong
+    assert ok.sum() > 50
+    assert np.quantile(np.abs(a[ok] - b[ok]), 0.99) < 1e-3 and np.max(np.abs(a[ok] - b[ok])) < 0.05
+    # the broadening must actually have happened: wider spectra than without it
+    conf0 = copy.deepcopy(conf)
+    conf0['doppler'] = {'scheme': 3}
+    op0, _, _ = make_operator(conf0, scheme, freq, with_edr=bool(turb), top=15000.0)
+    plainout = op0.simulate_rays(rays_az, rays_el)
+    nb = lambda x: (np.nan_to_num(x) > 0).sum(axis=-1)
+    assert np.sum(nb(out['DSPECTRUM'])[strong]) > 1.5 * np.sum(nb(plainout['DSPECTRUM'])[strong])
+    if turb:
+        from cosmo_pol_b200 import RadarOperator
+        bad = RadarOperator(op.config, output_variables='only_radar', device=0)
+        bad.set_lut(luts)
+        bad.load_model({k: v for k, v in model.items() if k != 'EDR'})
+        with pytest.raises(KeyError):
+            bad.simulate_rays(rays_az[:1], rays_el[:1])
+
+
+@pytest.mark.parametrize('name', ['c1mom_dop3_mot', 'c1mom_dop3_turb'])
+def test_doppler_spectrum_broadening_against_reference_golden(name):
+    from cosmo_pol_b200 import RadarOperator
+    g, cfg, kw = load_golden_case(name)
+    model, luts = synthetic_inputs('1mom', 5.6, **kw)
+    conf = copy.deepcopy(cfg)
+    conf['radar']['sensitivity'] = [-300, 10000]
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    rays = g['rays']
+    out = op.simulate_rays(rays[:, 0], rays[:, 1])
+    ref = {k[4:]: g[k] for k in g.files if k.startswith('obs_')}
+    assert_observables_close(out, ref, sz_scale=5e-4 * np.abs(ref['KDP']), what=name)
+    strong = _spectrum_close(out['DSPECTRUM'], ref['DSPECTRUM'], ref['ZH'], name)
+    a, b = out['RVEL'], ref['RVEL']
+    assert np.all(np.isnan(a[np.isnan(b)])) and np.all(np.isfinite(a[strong]))
+    ok = np.isfinite(b) & strong
+    assert np.max(np.abs(a[ok] - b[ok])) < 0.05
+
+
 def test_edge_cases_and_errors():
     from cosmo_pol_b200 import RadarOperator
     from cosmo_pol_b200._abi import RadopError
@@ -335,11 +398,11 @@ def test_edge_cases_and_errors():
     pm, pl = plain(model, luts)
     ref = O.simulate_scan(pm, pl, oracle_cfg(op), [5.], [2.], accum='f64', sensitivity_cut=True)
     assert_observables_close({k: v[0] for k, v in r1.fields.items()}, ref, what='1x1')
-    conf['doppler'] = {'scheme': 3, 'motion_correction': 1}
+    conf['doppler'] = {'scheme': 3, 'turbulence_correction': 1}      # no EDR in the model
     op = RadarOperator(conf, output_variables='only_radar', device=0)
     op.set_lut(luts)
     op.load_model(model)
-    with pytest.raises(ValueError):
+    with pytest.raises(KeyError):
         op.get_PPI([2.0], azimuths=[5.])
     with pytest.raises(ValueError):
         RadarOperator(conf).load_model({'T': model['T']})
@@ -405,3 +468,52 @@ def test_scan_level_properties():
     assert relerr(y['ZDR'], x['ZDR']) < 1e-5, relerr(y['ZDR'], x['ZDR'])
     st = op._engine.stats()
     assert st['n_active_pairs'] > 0 and st['launches'] >= 6
+
+
+def test_full_size_volume_properties():
+    """BASELINE.json configuration 3 at its full size (7200 rays x 500 gates x 9 sub-beams, the
+    workload bench.py times): determinism, shard consistency (two half volumes = the whole volume,
+    the multi-GPU decomposition), chunk invariance, and oracle parity on rays drawn from the
+    volume (rays are independent, so the oracle only has to simulate the sample)."""
+    import bench
+    from cosmo_pol_b200 import RadarOperator
+    model, luts = bench.build_inputs()
+    conf = bench.volume_config()
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    ray_az, ray_el = bench.volume_rays()
+    assert len(ray_az) == 7200
+    keys = ('ZH', 'ZV', 'ZDR', 'KDP', 'PHIDP', 'RHOHV', 'ATT_H', 'ATT_V', 'RVEL', 'DELTA_HV', 'mask', 'lat', 'lon')
+    a = {k: v.copy() for k, v in op.simulate_rays(ray_az, ray_el).items()}
+    assert a['ZH'].shape == (7200, 500)
+    st = op._engine.stats()
+    assert st['n_subbeam_gates'] == 7200 * 500 * 9
+    assert st['n_active_pairs'] == sum(st['pairs_by_species'])
+    b = op.simulate_rays(ray_az, ray_el)
+    for k in keys:
+        assert np.array_equal(a[k], b[k], equal_nan=True), 'non deterministic ' + k
+    half = 3600
+    d0 = {k: v.copy() for k, v in op.simulate_rays(ray_az[:half], ray_el[:half]).items()}
+    d1 = op.simulate_rays(ray_az[half:], ray_el[half:])
+    for k in keys:
+        assert np.array_equal(np.concatenate([d0[k], d1[k]]), a[k], equal_nan=True), 'sharding changes ' + k
+    op._engine.set_chunk(0)
+    c = op.simulate_rays(ray_az, ray_el)
+    for k in keys:
+        assert np.array_equal(c[k], a[k], equal_nan=True), 'chunking changes ' + k
+    op._engine.set_chunk(8000000)
+    # a finite, plausible volume: some precipitation, nothing absurd
+    zh = a['ZH'][np.isfinite(a['ZH'])]
+    assert zh.size > 100000 and zh.min() > 0 and 10 * np.log10(zh.max()) < 90
+    # oracle on a sample of rays of the volume
+    pick = np.array([17, 361 + 90, 5 * 360 + 201, 12 * 360 + 7, 19 * 360 + 333])
+    pm, pl = plain(model, luts)
+    cfg = oracle_cfg(op)
+    ref = O.simulate_scan(pm, pl, cfg, ray_az[pick], ray_el[pick], accum='f64', sensitivity_cut=True)
+    got = {k: a[k][pick] for k in a}
+    assert_observables_close(got, ref, what='cfg3 sample')
+    ok = np.isfinite(ref['RVEL'])
+    assert np.array_equal(np.isnan(got['RVEL']), ~ok)
+    assert np.max(np.abs(got['RVEL'][ok] - ref['RVEL'][ok])) < 2e-3
+    op.close()

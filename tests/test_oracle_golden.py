@@ -11,7 +11,8 @@ import radop_oracle as O
 from conftest import GOLDEN, load_golden_case, plain, synthetic_inputs
 
 CASES = {'c1mom': ('1mom', 5.6), 'c2mom': ('2mom', 9.41), 'c1mom_thr': ('1mom', 5.6), 'c1mom_nyq': ('1mom', 5.6),
-         'c1mom_dop2': ('1mom', 5.6), 'c1mom_dop3': ('1mom', 5.6)}
+         'c1mom_dop2': ('1mom', 5.6), 'c1mom_dop3': ('1mom', 5.6), 'c1mom_dop3_mot': ('1mom', 5.6),
+         'c1mom_dop3_turb': ('1mom', 5.6)}
 
 
 def test_constants_match_reference():
@@ -117,3 +118,18 @@ def test_path_matches_reference(name):
             O.cut_at_sensitivity(vals, cfg)
             for k in vals:
                 assert np.array_equal(vals[k], g['cut_' + k][i], equal_nan=True), (name, k)
+
+
+def test_gaussian_filter_restates_scipy():
+    """The oracle's numpy restatement of scipy.ndimage.gaussian_filter (the one third-party call
+    of the spectrum broadening, doppler_scatter.py:796) against scipy itself, including radii
+    beyond the array (multiple reflections), sigma = 0 and NaN (axis skipped)."""
+    ndi = pytest.importorskip('scipy.ndimage')
+    rng = np.random.default_rng(3)
+    for n in (65, 129):
+        for sigma in (0.0, float('nan'), 1e-16, 0.12, 0.9, 3.3, 17.0, 40.0, 150.0):
+            x = (rng.random(n) ** 8).astype(np.float32)
+            a = O.gaussian_filter1d(x, sigma)
+            b = ndi.gaussian_filter(x, sigma)
+            assert a.dtype == b.dtype
+            assert np.allclose(a, b, rtol=2e-6, atol=1e-12), (n, sigma, np.max(np.abs(a - b)))
