@@ -753,7 +753,8 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                 if (interp_columns<false>(cfg, c, h_g, z_t, fields, val)) interp_columns<true>(cfg, c, h_g, z_t, fields, val);
                 if (!cfg.two_moment) {
 #pragma unroll
-                    for (int j = 9; j < 16; ++j) val[j] = 0.f;
+                    for (int j = 9; j < RADOP_VAR_EDR; ++j) val[j] = 0.f;
+                    if (!(cfg.var_mask & (1u << RADOP_VAR_EDR))) val[RADOP_VAR_EDR] = 0.f;
                 }
 
                 // --- incidence elevation folded to [0, 90] (doppler_scatter.py:173-176) ---------
@@ -1963,6 +1964,28 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                         const double hi = s_base[cb] + vb, lo = (ka >= 0) ? s_base[ca] + va : 0.0;
                         diff = hi - lo;
                         if (fabs(diff) < 2e-15 * fabs(hi)) diff = 0.0;      // rounding of the bases
+                    }
+                    if (A.sub_acc && !(diff > 1e-6 * (s_base[cb] + vb))) {
+                        // Broadening turns a sub-beam spectrum without power into NaN (0 / 0,
+                        // doppler_scatter.py:799), so "tiny" and "zero" are not the same thing here:
+                        // where the prefix difference has lost the value (far PSD tail), the samples
+                        // of the bin are summed directly, as get_refl does (doppler_c.c:23-30)
+                        float acc = 0.f;
+                        const float lam = rec.p0;
+                        const float ea = -LOG2E * lam;
+                        const float a1 = -20.78f * LOG2E * lam, a2 = -3.290f * LOG2E * lam;
+                        const float c2 = (S.mode == MODE_ICE1) ? 17.46f * exp2f(0.6357f * log2f(lam)) : 0.f;
+                        for (int k = ia; k < ib; ++k) {
+                            const int ad = (k % cpl) * 32 + k / cpl;
+                            float shape;
+                            if (S.mode == MODE_ICE1) {
+                                const float Dk = __ldg(S.aux + k);
+                                shape = fmaf(s_auxp[ad], c2 * exp2f(a2 * Dk), 490.6f * exp2f(a1 * Dk));
+                            } else if (S.mode == MODE_GEO8) shape = exp2f(ea * __ldg(S.aux + k));
+                            else shape = exp2f(ea * s_auxp[ad]);      // exp2f keeps subnormals (ex2.approx.ftz does not)
+                            acc = fmaf(s_col0[ad], shape, acc);
+                        }
+                        diff = (double)acc;
                     }
                     const double val = diff * scale;
                     if (val != 0.0) atomicAdd(dst + j, val);
