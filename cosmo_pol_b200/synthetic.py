@@ -150,6 +150,69 @@ def diameter_limits(hydrom, scheme):
     return getattr(c, 'D_MIN_' + hydrom), getattr(c, 'D_MAX_' + hydrom)
 
 
+W_CONTENTS = np.linspace(1E-3, 0.999, 100)     # compute_lut_sz.py:63
+
+
+def make_melting_lut(hydrom, frequency=5.6, scheme='1mom', seed=4321, n_e=None, n_d=NUM_DIAMETERS):
+    """Synthetic table of a melting species ('mS', 'mG') in the layout of sz_lut_melting
+    (compute_lut_sz.py:299-369): axes e, wc (100 wet fractions), d = [n_wc, n_d] diameters between
+    wet-fraction dependent limits (hydrometeors.py:333-340), 12 columns.  The scattering blends the
+    solid species into rain with the wet fraction (wet particles scatter like water well before
+    they are liquid)."""
+    solid = 'S' if hydrom == 'mS' else 'G'
+    sw, sd = _SPECIES['R'], _SPECIES[solid]
+    rng = np.random.default_rng(seed + sum(ord(ch) for ch in hydrom))
+    elev = ELEVATIONS if n_e is None else ELEVATIONS[:n_e]
+    wc = W_CONTENTS
+    rmin, rmax = diameter_limits('R', scheme)
+    smin, smax = diameter_limits(solid, scheme)
+    D = np.stack([np.linspace(w * rmin + (1 - w) * smin, w * rmax + (1 - w) * smax, n_d).astype('float32') for w in wc])
+    lam = 299792458. / (frequency * 1e9) * 1000.
+    Dd = D.astype(np.float64)[None, :, :]
+    e = np.deg2rad(elev.astype(np.float64))[:, None, None]
+    w = wc[None, :, None]
+    blend = w ** 0.4
+    mix = lambda a, b: (1 - blend) * a + blend * b
+    kfac = mix(np.sqrt(sd['k2']), np.sqrt(sw['k2']))
+    xsz = np.pi * Dd / lam
+    amp = np.pi ** 2 * kfac * Dd ** 3 / (2 * lam ** 2) * (1.0 - 0.18 * xsz ** 2 / (1.0 + xsz ** 2))
+    oblc = mix(sd['obl'], 1.6 * sw['obl'])
+    cant = mix(sd['cant'], sw['cant'])
+    obl = oblc * Dd / (1.0 + 0.08 * Dd) * np.exp(-2 * np.deg2rad(cant) ** 2) * np.cos(e) ** 2
+    wig = 1.0 + 0.01 * np.sin(0.7 * Dd + 3.0 * w)
+    shh = amp * (1.0 + obl) * wig
+    svv = amp * (1.0 - obl) / wig
+    dphi = 0.04 * xsz ** 2 * np.cos(e) ** 2 * (1 + 0.2 * w)
+    rho0 = 0.9985 - 0.004 * obl / (oblc + 1e-12) - 0.002 * xsz ** 2 / (1 + xsz ** 2) - 0.01 * w * (1 - w)
+    shape = (len(elev), len(wc), n_d)
+    tab = np.zeros(shape + (12,), dtype=np.float64)
+    hh2 = np.broadcast_to(shh ** 2, shape)
+    vv2 = np.broadcast_to(svv ** 2, shape)
+    co = np.broadcast_to(shh * svv * rho0, shape)
+    tab[..., 0] = 0.5 * (hh2 + vv2)
+    tab[..., 1] = 0.5 * (vv2 - hh2)
+    tab[..., 2] = tab[..., 1]
+    tab[..., 3] = tab[..., 0] * (1.0 + 1e-3)
+    tab[..., 4] = -co * np.cos(dphi)
+    tab[..., 5] = 0.5 * co * np.sin(dphi)
+    tab[..., 6] = -0.5 * co * np.sin(dphi)
+    tab[..., 7] = tab[..., 4]
+    fwd = np.pi ** 2 * kfac * Dd ** 3 / (2 * lam ** 2)
+    loss = mix(sd['absorb'], 2.0 * sw['absorb']) * fwd + (2. / 3.) * (2 * np.pi / lam) * fwd ** 2
+    tab[..., 8] = np.broadcast_to(fwd * (1.0 - 0.8 * obl), shape)
+    tab[..., 9] = np.broadcast_to(loss * (1.0 - 0.8 * obl), shape)
+    tab[..., 10] = np.broadcast_to(fwd * (1.0 + 0.8 * obl), shape)
+    tab[..., 11] = np.broadcast_to(loss * (1.0 + 0.8 * obl), shape)
+    tab *= 1.0 + 0.01 * rng.standard_normal((len(elev), len(wc), 1, 12))
+    lut = Lookup_table()
+    lut.add_axis('e', elev)
+    lut.add_axis('wc', wc)
+    lut.add_axis('d', D)
+    lut.add_axis('sz', np.arange(12))
+    lut.set_value_table(tab)
+    return lut
+
+
 def make_lut(hydrom, frequency=5.6, scheme='1mom', seed=4321, n_e=None, n_t=None, n_d=NUM_DIAMETERS):
     """Synthetic scattering table for one species; same axes/layout the reference
     generator writes (compute_lut_sz.py:428-433).  ``n_e``/``n_t`` truncate the
@@ -217,8 +280,13 @@ def species_for(scheme, with_ice=True):
     return h
 
 
-def make_all_luts(frequency=5.6, scheme='1mom', with_ice=True, seed=4321, n_e=None, n_t=None):
-    return {h: make_lut(h, frequency, scheme, seed, n_e, n_t) for h in species_for(scheme, with_ice)}
+def make_all_luts(frequency=5.6, scheme='1mom', with_ice=True, seed=4321, n_e=None, n_t=None, with_melting=False,
+                  n_e_melting=None):
+    luts = {h: make_lut(h, frequency, scheme, seed, n_e, n_t) for h in species_for(scheme, with_ice)}
+    if with_melting:
+        for h in ('mS', 'mG'):
+            luts[h] = make_melting_lut(h, frequency, scheme, seed, n_e_melting if n_e_melting else n_e)
+    return luts
 
 
 def lut_as_plain(lut):

@@ -404,10 +404,11 @@ def melting(sub):
         v['QS_v'][mwm] = 0
         v['QG_v'][mwm] = 0
         v['QR_v'][mwm] = 0
-        v['fwet_mS'] = np.zeros(n)
-        v['fwet_mS'][mask_ml] = (QRm * QSm / QSG) / v['QmS_v'][mask_ml]
-        v['fwet_mG'] = np.zeros(n)
-        v['fwet_mG'][mask_ml] = (QRm * QGm / QSG) / v['QmG_v'][mask_ml]
+        with np.errstate(invalid='ignore', divide='ignore'):      # 0 / 0 where only one of QS, QG is present
+            v['fwet_mS'] = np.zeros(n)
+            v['fwet_mS'][mask_ml] = (QRm * QSm / QSG) / v['QmS_v'][mask_ml]
+            v['fwet_mG'] = np.zeros(n)
+            v['fwet_mG'][mask_ml] = (QRm * QGm / QSG) / v['QmG_v'][mask_ml]
     sub['has_melting'] = has
     sub['mask_ml'] = mask_ml
     return sub
@@ -698,6 +699,90 @@ class Hydro(object):
 
 
 # --------------------------------------------------------------------------- #
+# a6 / N1: melting snow and graupel (hydrometeors.py:303-500, 1393-1481)
+# --------------------------------------------------------------------------- #
+D_LIMITS_1MOM = {'R': (0.1, 8.), 'S': (0.2, 20.), 'G': (0.2, 15.), 'I': (0.05, 2.)}   # constants_1mom.py:52-91
+
+
+def vlinspace(a, b, N):
+    """utilities.py:158-174."""
+    a, b = np.asanyarray(a), np.asanyarray(b)
+    return a[..., None] + (b - a)[..., None] / (N - 1) * np.arange(N)
+
+
+class MeltHydro(object):
+    """_MeltingHydrometeor with its two subclasses, one-moment scheme (the two-moment call
+    set_psd(QN, QM) of doppler_scatter.py:209-211 raises ValueError in the reference).
+    The PSD follows from the flux of the equivalent rain (get_N, :372-390); the solid
+    counterpart only enters through its mass and fall-speed power laws."""
+
+    def __init__(self, kind, scheme):
+        if scheme != '1mom':
+            raise ValueError('Invalid parameters, cannot set psd')
+        self.kind = kind
+        self.scheme = scheme
+        self.rain = Hydro('R', scheme)
+        self.solid = Hydro('S' if kind == 'mS' else 'G', scheme)
+        self.rain.d_min, self.rain.d_max = D_LIMITS_1MOM['R']
+        self.solid.d_min, self.solid.d_max = D_LIMITS_1MOM[self.solid.kind]
+        self.nbins_D = 1024
+        self.prop_factor = None
+        self.d_min = self.d_max = None
+
+    def set_fwet(self, fw):
+        self.f_wet = fw
+        self.d_max = fw * self.rain.d_max + (1 - fw) * self.solid.d_max
+        self.d_min = fw * self.rain.d_min + (1 - fw) * self.solid.d_min
+
+    def set_psd(self, *args):
+        self.prop_factor = None
+        if self.kind == 'mS':
+            T, q, fw = np.array(args[0]), np.array(args[1]), np.array(args[2])
+            self.solid.set_psd(T, q)
+        else:
+            q, fw = np.array(args[0]), np.array(args[1])
+            self.solid.set_psd(q)
+        self.rain.set_psd(q)
+        self.set_fwet(fw)
+        with np.errstate(divide='ignore', invalid='ignore'):
+            self.prop_factor = q / self.integrate_M()
+
+    def get_M(self, D):
+        fw2 = self.f_wet ** 2
+        return fw2[:, None] * (self.rain.a * D ** self.rain.b) + (1 - fw2)[:, None] * (self.solid.a * D ** self.solid.b)
+
+    def _D_r(self, d):
+        rho_m = self.get_M(d) / (np.pi / 6 * d ** 3)
+        return (rho_m / RHO_W) ** (1 / 3.) * d
+
+    def get_V(self, D):
+        V_rain = self.rain.alpha * self._D_r(D) ** self.rain.beta
+        V_dry = self.solid.alpha * D ** self.solid.beta
+        phi = 0.246 * self.f_wet + (1 - 0.246) * self.f_wet ** 7
+        return phi[:, None] * V_rain + (1 - phi)[:, None] * V_dry
+
+    def get_N(self, D):
+        Dr = self._D_r(D)
+        dDr = (self._D_r(D + 0.01) - Dr) / 0.01
+        lam = self.rain.lambda_
+        Nr = self.rain.N0 * Dr ** self.rain.mu * np.exp(-lam[:, None] * Dr ** self.rain.nu)
+        if self.prop_factor is not None:
+            Nr = self.prop_factor[:, None] * Nr
+        return Nr * (self.rain.alpha * Dr ** self.rain.beta) / self.get_V(D) * dDr
+
+    def integrate_M(self):
+        D = vlinspace(self.d_min, self.d_max, self.nbins_D)
+        dD = D[:, 1] - D[:, 0]
+        return np.sum(self.get_N(D) * self.get_M(D), axis=1) * dD
+
+    def integrate_V(self):
+        D = vlinspace(self.d_min, self.d_max, self.nbins_D)
+        dD = D[:, 1] - D[:, 0]
+        N = self.get_N(D)
+        return np.sum(N * self.get_V(D), axis=1) * dD, np.sum(N, axis=1) * dD
+
+
+# --------------------------------------------------------------------------- #
 # a10: lookup (lut.py:309-344)
 # --------------------------------------------------------------------------- #
 def lut_index(x, lo, step, dim):
@@ -712,7 +797,7 @@ def lut_index(x, lo, step, dim):
 
 def lookup_line(lut, e, t):
     """lut: dict(value_table [ne,nt,nd,12] f64, axes_limits, axes_step, axes).
-    Axis 0 is 'e', axis 1 is 't'."""
+    Axis 0 is 'e', axis 1 is 't' (or 'wc' for the melting species)."""
     v = lut['value_table']
     ie = lut_index(e, lut['axes_limits'][0][0], lut['axes_step'][0], v.shape[0])
     it = lut_index(t, lut['axes_limits'][1][0], lut['axes_step'][1], v.shape[1])
@@ -940,6 +1025,12 @@ def get_radar_observables(subs, luts, cfg, accum='ref', debug=False):
     hydrom_types = species_list(cfg)
     hyd = {}
     for h in hydrom_types:
+        if h in ('mS', 'mG'):
+            # the limits taken from the table (doppler_scatter.py:117-123) are overwritten by the
+            # f_wet setter at every set_psd (hydrometeors.py:333-340)
+            hyd[h] = MeltHydro(h, scheme)
+            hyd[h].nbins_D = luts[h]['value_table'].shape[-2]
+            continue
         hyd[h] = Hydro(h, scheme)
         d_axis = luts[h]['axes'][2]
         hyd[h].nbins_D = luts[h]['value_table'].shape[-2]
@@ -959,6 +1050,11 @@ def get_radar_observables(subs, luts, cfg, accum='ref', debug=False):
         if doppler_scheme == 3:
             ah_per_beam = np.zeros((n_gates,), dtype='float32') + np.nan
         for j, h in enumerate(hydrom_types):
+            wet = h in ('mS', 'mG')
+            if wet and not sub.get('has_melting', False):
+                continue                                    # doppler_scatter.py:162-165
+            if wet and doppler_scheme == 3:
+                raise NotImplementedError('Doppler spectrum of melting species')
             elev_lut = sub['elev']                          # alias, folded in place (Q3)
             elev_lut[elev_lut > 90] = 180 - elev_lut[elev_lut > 90]
             elev_lut[elev_lut < 0] = -elev_lut[elev_lut < 0]
@@ -969,19 +1065,30 @@ def get_radar_observables(subs, luts, cfg, accum='ref', debug=False):
             if not np.any(valid):
                 continue
             if scheme == '1mom':
-                if h in ('S', 'I'):
+                if h == 'mG':
+                    fwet = sub['values']['fwet_' + h]
+                    hyd[h].set_psd(QM[valid], fwet[valid])
+                elif h == 'mS':
+                    fwet = sub['values']['fwet_' + h]
+                    hyd[h].set_psd(T[valid], QM[valid], fwet[valid])
+                elif h in ('S', 'I'):
                     hyd[h].set_psd(T[valid], QM[valid])
                 else:
                     hyd[h].set_psd(QM[valid])
             else:
                 QN = sub['values']['QN' + h + '_v']
                 hyd[h].set_psd(QN[valid], QM[valid])
-            list_D = luts[h]['axes'][2]
-            dD = list_D[1] - list_D[0]
+            if wet:
+                # per-gate diameter grids between the wet-fraction dependent limits (:216-221)
+                list_D = vlinspace(hyd[h].d_min, hyd[h].d_max, hyd[h].nbins_D)
+                dD = (list_D[:, 1] - list_D[:, 0])[:, None]
+            else:
+                list_D = luts[h]['axes'][2]
+                dD = list_D[1] - list_D[0]
             N = hyd[h].get_N(list_D)
             if len(N.shape) == 1:
                 N = np.reshape(N, [len(N), 1])
-            sz, ie, it = lookup_line(luts[h], elev_lut[valid], T[valid])
+            sz, ie, it = lookup_line(luts[h], elev_lut[valid], fwet[valid] if wet else T[valid])
             if debug:
                 dbg['e_idx'][(i, h)] = ie
                 dbg['t_idx'][(i, h)] = it

@@ -35,10 +35,13 @@ def has_gpu():
 _CACHE = {}
 
 
-def synthetic_inputs(scheme='1mom', freq=5.6, **model_kw):
+MELTING_N_E = 8      # elevation bins of the synthetic melting tables, as in make_golden_from_reference.py
+
+
+def synthetic_inputs(scheme='1mom', freq=5.6, with_melting=False, **model_kw):
     """Seeded synthetic model + lookup tables (cached per session)."""
     from cosmo_pol_b200 import synthetic
-    key = (scheme, freq, tuple(sorted(model_kw.items())))
+    key = (scheme, freq, with_melting, tuple(sorted(model_kw.items())))
     if key not in _CACHE:
         kw = dict(nz=24, ny=64, nx=64, res=0.04)
         kw.update(model_kw)
@@ -46,7 +49,14 @@ def synthetic_inputs(scheme='1mom', freq=5.6, **model_kw):
         lkey = ('lut', scheme, freq)
         if lkey not in _CACHE:
             _CACHE[lkey] = synthetic.make_all_luts(freq, scheme, with_ice=True)
-        _CACHE[key] = (model, _CACHE[lkey])
+        luts = _CACHE[lkey]
+        if with_melting:
+            mkey = ('lut_melting', scheme, freq)
+            if mkey not in _CACHE:
+                _CACHE[mkey] = {h: synthetic.make_melting_lut(h, freq, scheme, n_e=MELTING_N_E) for h in ('mS', 'mG')}
+            luts = dict(luts)
+            luts.update(_CACHE[mkey])
+        _CACHE[key] = (model, luts)
     return _CACHE[key]
 
 

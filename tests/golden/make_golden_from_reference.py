@@ -202,7 +202,12 @@ def ref_lut(R, lut):
     L.axes = lut.axes
     L.axes_names = dict(lut.axes_names)
     L.axes_limits = np.asarray(lut.axes_limits)      # what np.save/np.load of the list gives
-    L.axes_step = np.asarray(lut.axes_step)
+    try:
+        L.axes_step = np.asarray(lut.axes_step)
+    except ValueError:                                # melting tables: the 'd' step is a vector (object array)
+        L.axes_step = np.empty(len(lut.axes_step), dtype=object)
+        for i, v in enumerate(lut.axes_step):
+            L.axes_step[i] = v
     return L
 
 
@@ -328,8 +333,17 @@ CASES = {
                                           doppler={'scheme': 3, 'motion_correction': 1, 'turbulence_correction': 1},
                                           integration={'nv_GH': 3, 'nh_GH': 1}),
                         [(45.0, 3.5), (200.0, 60.0)], {'with_edr': True, 'top': 15000.0}),
+    # melting scheme (melting.py:19-90, hydrometeors.py:303-500, 1393-1481): wet snow / wet graupel
+    # with per-gate diameter grids and the wet-fraction table axis; Doppler schemes 1 and 2
+    'c1mom_melt': ('1mom', 5.6, dict(radar={'range': 30000, 'radial_resolution': 500},
+                                     microphysics={'with_melting': 1}, integration={'nv_GH': 3, 'nh_GH': 1}),
+                   [(220.0, 3.5), (170.0, 3.5)], {}),
+    'c1mom_melt_dop2': ('1mom', 5.6, dict(radar={'range': 30000, 'radial_resolution': 500}, doppler={'scheme': 2},
+                                          microphysics={'with_melting': 1}, integration={'nv_GH': 1, 'nh_GH': 3}),
+                        [(220.0, 3.5)], {}),
 }
 MODEL_KW = dict(nz=24, ny=64, nx=64, res=0.04)
+MELTING_N_E = 8          # elevation bins of the synthetic melting tables (0..14 deg): 78 MB per species
 
 
 def golden_path(R, name):
@@ -337,7 +351,8 @@ def golden_path(R, name):
     kw = dict(MODEL_KW)
     kw.update(mkw)
     model = synthetic.make_model(scheme=scheme, **kw)
-    luts = synthetic.make_all_luts(freq, scheme, with_ice=True)
+    melt = bool(over.get('microphysics', {}).get('with_melting', 0))
+    luts = synthetic.make_all_luts(freq, scheme, with_ice=True, with_melting=melt, n_e_melting=MELTING_N_E)
     over = {k: dict(v) for k, v in over.items()}
     over.setdefault('radar', {})['frequency'] = freq
     over.setdefault('microphysics', {})['scheme'] = scheme

@@ -12,7 +12,7 @@ from conftest import GOLDEN, load_golden_case, plain, synthetic_inputs
 
 CASES = {'c1mom': ('1mom', 5.6), 'c2mom': ('2mom', 9.41), 'c1mom_thr': ('1mom', 5.6), 'c1mom_nyq': ('1mom', 5.6),
          'c1mom_dop2': ('1mom', 5.6), 'c1mom_dop3': ('1mom', 5.6), 'c1mom_dop3_mot': ('1mom', 5.6),
-         'c1mom_dop3_turb': ('1mom', 5.6)}
+         'c1mom_dop3_turb': ('1mom', 5.6), 'c1mom_melt': ('1mom', 5.6), 'c1mom_melt_dop2': ('1mom', 5.6)}
 
 
 def test_constants_match_reference():
@@ -84,7 +84,7 @@ def test_lookup_line_matches_reference():
 def test_path_matches_reference(name):
     scheme, freq = CASES[name]
     g, cfg, kw = load_golden_case(name)
-    model, luts = synthetic_inputs(scheme, freq, **kw)
+    model, luts = synthetic_inputs(scheme, freq, with_melting=bool(cfg['microphysics'].get('with_melting', 0)), **kw)
     # the seeded generator must still produce the inputs the goldens were made from
     assert float(np.sum(model['T'].data.astype(np.float64))) == float(g['fp_T'])
     assert float(np.sum(model['QR_v'].data.astype(np.float64))) == float(g['fp_QR'])
