@@ -10,15 +10,15 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libradop.so')
 
-RADOP_ABI_VERSION = 3
-NSPECIES_MAX = 5
+RADOP_ABI_VERSION = 4
+NSPECIES_MAX = 7
 NVAR_MAX = 16
 N_OUT = 10
 OUT_NAMES = ['ZH', 'ZDR', 'ZV', 'KDP', 'DELTA_HV', 'PHIDP', 'RHOHV', 'ATT_H', 'ATT_V', 'RVEL']
 VAR_IDS = {'U': 0, 'V': 1, 'W': 2, 'T': 3, 'RHO': 4, 'QR_v': 5, 'QS_v': 6, 'QG_v': 7, 'QI_v': 8, 'QH_v': 9,
            'QNR_v': 10, 'QNS_v': 11, 'QNG_v': 12, 'QNI_v': 13, 'QNH_v': 14, 'EDR': 15}
 VAR_NAMES = {v: k for k, v in VAR_IDS.items()}
-SPECIES_IDS = {'R': 0, 'S': 1, 'G': 2, 'H': 3, 'I': 4}
+SPECIES_IDS = {'R': 0, 'S': 1, 'G': 2, 'H': 3, 'I': 4, 'mS': 5, 'mG': 6}
 
 EXPORTS = ['radop_abi_version', 'radop_create', 'radop_destroy', 'radop_last_error', 'radop_set_params',
            'radop_upload_grid', 'radop_upload_field', 'radop_upload_lut', 'radop_simulate', 'radop_stage_scan',
@@ -34,7 +34,8 @@ class RadopSpecies(C.Structure):
     _fields_ = [('species', C.c_int32), ('psd', C.c_int32), ('numeric_vn', C.c_int32), ('reserved', C.c_int32),
                 ('a', C.c_double), ('b', C.c_double), ('alpha', C.c_double), ('beta', C.c_double),
                 ('mu', C.c_double), ('nu', C.c_double), ('N0', C.c_double), ('lambda_factor', C.c_double),
-                ('vel_factor', C.c_double), ('ntot_factor', C.c_double), ('x_min', C.c_double), ('x_max', C.c_double)]
+                ('vel_factor', C.c_double), ('ntot_factor', C.c_double), ('x_min', C.c_double), ('x_max', C.c_double),
+                ('melt', C.c_double * 8)]
 
 
 class RadopParams(C.Structure):
@@ -47,7 +48,8 @@ class RadopParams(C.Structure):
                 ('reserved', C.c_int32), ('species', RadopSpecies * NSPECIES_MAX),
                 ('n_vel', C.c_int32), ('reserved2', C.c_int32), ('vel_min', C.c_double), ('vel_res', C.c_double),
                 ('spectrum_turbulence', C.c_int32), ('spectrum_motion', C.c_int32),
-                ('antenna_speed', C.c_double), ('beamwidth_deg', C.c_double)]
+                ('antenna_speed', C.c_double), ('beamwidth_deg', C.c_double),
+                ('with_melting', C.c_int32), ('reserved3', C.c_int32)]
 
 
 class RadopScan(C.Structure):
@@ -228,6 +230,7 @@ class Engine(object):
         p.two_moment = 1 if config['microphysics']['scheme'] == '2mom' else 0
         p.with_attenuation = int(config['microphysics']['with_attenuation'])
         p.doppler_scheme = int(config['doppler']['scheme'])
+        p.with_melting = 1 if config['microphysics'].get('with_melting', 0) else 0
         if p.doppler_scheme == 3:
             d = config['doppler']
             # broadening of the sub-beam spectra (doppler_scatter.py:357-367, 727-801)
@@ -254,7 +257,11 @@ class Engine(object):
         p.n_species = len(hydrometeors)
         for i, hy in enumerate(hydrometeors):
             for k, v in hy.abi_fields().items():
-                setattr(p.species[i], k, v)
+                if k == 'melt':
+                    for j, x in enumerate(v):
+                        p.species[i].melt[j] = x
+                else:
+                    setattr(p.species[i], k, v)
         self._check(self.lib.radop_set_params(self.h, C.byref(p)))
         self.params = p
         self.species_order = [hy.kind for hy in hydrometeors]
@@ -291,10 +298,14 @@ class Engine(object):
                 continue
             vt = np.ascontiguousarray(lut.value_table, dtype=np.float64)
             names = lut.axes_names
-            ie, it, idd = names['e'], names['t'], names['d']
+            second = 'wc' if h in ('mS', 'mG') else 't'       # wet fraction axis of the melting species
+            ie, it, idd = names['e'], names[second], names['d']
             if (ie, it, idd) != (0, 1, 2) or vt.ndim != 4 or vt.shape[3] != 12:
-                raise ValueError('lookup table of {} must have axes (e, t, d, sz[12])'.format(h))
-            d_axis = np.ascontiguousarray(lut.axes[idd], dtype=np.float32)
+                raise ValueError('lookup table of {} must have axes (e, {}, d, sz[12])'.format(h, second))
+            d_axis = np.asarray(lut.axes[idd], dtype=np.float32)
+            if d_axis.ndim == 2:                               # [n_wc, nd]: per-gate grids on the device
+                d_axis = d_axis[0]
+            d_axis = np.ascontiguousarray(d_axis)
             self._check(self.lib.radop_upload_lut(
                 self.h, SPECIES_IDS[h], _ptr(vt), vt.shape[0], vt.shape[1], vt.shape[2],
                 C.c_float(np.float32(lut.axes_limits[ie][0])), C.c_float(np.float32(lut.axes_step[ie])),

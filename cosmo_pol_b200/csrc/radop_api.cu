@@ -118,6 +118,9 @@ static int species_vars(int sp, int *qm, int *qn)
     case RADOP_SP_G: *qm = RADOP_VAR_QG; *qn = RADOP_VAR_QNG; return 0;
     case RADOP_SP_H: *qm = RADOP_VAR_QH; *qn = RADOP_VAR_QNH; return 0;
     case RADOP_SP_I: *qm = RADOP_VAR_QI; *qn = RADOP_VAR_QNI; return 0;
+    // melting species are made from QR, QS and QG after the interpolation (melting.py:19-90)
+    case RADOP_SP_MS: *qm = RADOP_VAR_QS; *qn = RADOP_VAR_QNS; return 0;
+    case RADOP_SP_MG: *qm = RADOP_VAR_QG; *qn = RADOP_VAR_QNG; return 0;
     }
     return -1;
 }
@@ -190,7 +193,15 @@ int radop_set_params(RadopHandle *h, const RadopParams *p)
     for (int s = 0; s < p->n_species; ++s) {
         int qm, qn;
         if (species_vars(p->species[s].species, &qm, &qn)) return h->fail(RADOP_ERR_ARG, "unknown species id");
-        if (p->species[s].psd < 0 || p->species[s].psd > RADOP_PSD_2MOM) return h->fail(RADOP_ERR_ARG, "unknown psd family");
+        if (p->species[s].psd < 0 || p->species[s].psd > RADOP_PSD_MELTING) return h->fail(RADOP_ERR_ARG, "unknown psd family");
+        const bool wet_species = p->species[s].species == RADOP_SP_MS || p->species[s].species == RADOP_SP_MG;
+        if (wet_species != (p->species[s].psd == RADOP_PSD_MELTING))
+            return h->fail(RADOP_ERR_ARG, "melting species and RADOP_PSD_MELTING go together");
+        if (wet_species && (!p->with_melting || p->two_moment))
+            return h->fail(RADOP_ERR_UNSUPPORTED, "melting species need with_melting and the one-moment scheme "
+                                                  "(the reference's two-moment call raises ValueError)");
+        if (wet_species && p->doppler_scheme == 3)
+            return h->fail(RADOP_ERR_UNSUPPORTED, "Doppler spectrum (scheme 3) of melting species is not implemented");
     }
     h->p = *p;
     h->have_params = true;
@@ -270,7 +281,9 @@ int radop_upload_lut(RadopHandle *h, int species, const double *value_table, int
     double d0 = d_axis[0], dD = ((double)d_axis[nd - 1] - d0) / (nd - 1), dev = 0;
     for (int k = 0; k < nd; ++k) dev = std::max(dev, fabs((double)d_axis[k] - (d0 + k * dD)));
     bool uniform = dev <= 4e-7 * std::max(1.0, fabs((double)d_axis[nd - 1])) + 1e-12;
-    if (S->psd == RADOP_PSD_1MOM_ICE) {
+    if (S->psd == RADOP_PSD_MELTING) {
+        L.mode = MODE_MELT; L.ncol = 8; L.cost = 1;
+    } else if (S->psd == RADOP_PSD_1MOM_ICE) {
         if (!uniform || (nd % RADOP_HBLOCK) != 0)
             return h->fail(RADOP_ERR_LUT, "1-mom ice needs a uniform diameter axis with a multiple of 32 bins");
         L.mode = MODE_ICE1; L.ncol = 12; L.cost = 15;
@@ -422,6 +435,7 @@ static int prepare(RadopHandle *h)
     c.sens0 = (float)p.sensitivity[0]; c.sens1 = (float)p.sensitivity[1];
     c.n_vel = p.n_vel; c.vel_min = p.vel_min; c.vel_res = p.vel_res;
     c.inv_vel_res = p.vel_res > 0 ? 1.0 / p.vel_res : 0.0;
+    c.with_melting = p.with_melting ? 1 : 0;
     c.brd_mode = 0;
     if (p.doppler_scheme == 3) c.brd_mode = (p.spectrum_turbulence ? 1 : 0) | (p.spectrum_motion ? 2 : 0);
     if (c.brd_mode) {
@@ -459,6 +473,8 @@ static int prepare(RadopHandle *h)
         species_vars(S.species, &d.qm_var, &d.qn_var);
         need |= (1u << d.qm_var);
         if (S.psd == RADOP_PSD_2MOM) need |= (1u << d.qn_var);
+        if (S.psd == RADOP_PSD_MELTING) need |= (1u << RADOP_VAR_QR) | (1u << RADOP_VAR_QS) | (1u << RADOP_VAR_QG);
+        memcpy(d.melt, S.melt, sizeof d.melt);
         d.dD_geo = L.dD_geo; d.dD_ref = L.dD_ref; d.dD_d = L.dD_d;
         d.d_min = L.d_min; d.d_max = L.d_max; d.spec_step = L.spec_step;
         d.inv_beta = 1.0 / S.beta; d.inv_alpha = 1.0 / S.alpha;
@@ -581,7 +597,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     CU(h, h->rec.reserve((size_t)n * nsp * sizeof(PairRec)));
     CU(h, h->sz_out.reserve((size_t)n * nsp * 8 * 4));
     CU(h, h->ice_vn.reserve((size_t)n * 8));
-    if (c.doppler_scheme == 2) CU(h, h->dop_vn.reserve((size_t)n * nsp * 8));
+    if (c.doppler_scheme == 2 || c.with_melting) CU(h, h->dop_vn.reserve((size_t)n * nsp * 8));
     if (c.doppler_scheme == 3) {
         CU(h, h->d3_uh.reserve((size_t)n * 8));
         CU(h, h->d3_w.reserve((size_t)n * 4));
@@ -711,6 +727,13 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         a2.counter = h->flags.as<int>() + 1;
         a2.rec = h->rec.as<PairRec>(); a2.sz_out = h->sz_out.as<float>(); a2.ice_vn = h->ice_vn.as<float2>(); a2.dop_vn = h->dop_vn.as<float2>();
         k_integrate<<<h->k2_blocks, RADOP_TILE_THREADS, h->k2_smem, st>>>(c, a2);
+        if (c.with_melting) {
+            K2mArgs am;
+            am.rec = h->rec.as<PairRec>(); am.key = h->key.as<uint16_t>(); am.bin_start = h->bin_start.as<int>();
+            am.sz_out = h->sz_out.as<float>(); am.dop_vn = h->dop_vn.as<float2>(); am.n_sbg = nc;
+            k_integrate_melting<<<h->n_sm * 8, 128, 0, st>>>(c, am);
+            CU(h, cudaGetLastError()); ++launches;
+        }
         CU(h, cudaGetLastError()); ++launches;
         if (ev) CU(h, cudaEventRecord(ev[3], st));
 
@@ -840,6 +863,7 @@ static int finish(RadopHandle *h)
         if (S.mode == MODE_GEO8) per_d = 2.0 * (RADOP_NC + extra);
         else if (S.mode == MODE_GEN8) per_d = 2.0 * (RADOP_NC + extra) + 2.0;      // + a D^nu, ex2
         else if (S.mode == MODE_GEN12) per_d = 2.0 * 9 + 2.0;
+        else if (S.mode == MODE_MELT) per_d = 0;                                    // float64 kernel, not counted
         else per_d = 2.0 * 10 + 2.0 + 2.0;                                          // ICE1: + shape FMA, two recurrences
         h->stats.exec_flop_per_pair[s] = per_d * S.nd;
     }

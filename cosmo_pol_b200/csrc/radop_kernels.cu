@@ -105,7 +105,7 @@ __global__ void k_pack_lut(const double *__restrict__ src, float *__restrict__ d
         int k = (int)(r % nd);
         const double *s = src + r * 12;
         double D = (double)d_axis[k];
-        double pre = (mode == MODE_ICE1) ? dD : pow(D, mu) * dD;
+        double pre = (mode == MODE_ICE1) ? dD : (mode == MODE_MELT ? 1.0 : pow(D, mu) * dD);
         float *o = dst + r * ncol;
         o[0] = (float)((s[0] - s[1] - s[2] + s[3]) * pre);
         o[1] = (float)((s[0] + s[1] + s[2] + s[3]) * pre);
@@ -655,6 +655,12 @@ __device__ __forceinline__ int lut_bin(float x, float lo, float step, float rste
     return i;
 }
 
+// one-moment slots that carry the melting re-partition (melting.py:19-90)
+#define MELT_SLOT_QMS 9
+#define MELT_SLOT_QMG 10
+#define MELT_SLOT_FWS 11
+#define MELT_SLOT_FWG 12
+
 extern __shared__ int s_hist[];
 
 // register-resident select (a dynamic index would push the value array to local memory)
@@ -756,6 +762,23 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                     for (int j = 9; j < RADOP_VAR_EDR; ++j) val[j] = 0.f;
                     if (!(cfg.var_mask & (1u << RADOP_VAR_EDR))) val[RADOP_VAR_EDR] = 0.f;
                 }
+                if (cfg.with_melting) {
+                    // melting.py:19-90 (float32 like the interpolated profiles): where rain coexists
+                    // with snow or graupel the rain mass is shared out to wet snow / wet graupel in
+                    // proportion to their dry masses, and the three original species are emptied.
+                    // Slots 9..12 (unused by the one-moment scheme) carry QmS, QmG, fwet_mS, fwet_mG.
+                    const float QR = val[RADOP_VAR_QR], QS = val[RADOP_VAR_QS], QG = val[RADOP_VAR_QG];
+                    const float QSG = __fadd_rn(QS, QG);
+                    if (QR > 0.f && QSG > 0.f) {
+                        const float qms = __fadd_rn(QS, __fmul_rn(QR, __fdiv_rn(QS, QSG)));
+                        const float qmg = __fadd_rn(QG, __fmul_rn(QR, __fdiv_rn(QG, QSG)));
+                        val[MELT_SLOT_QMS] = qms;
+                        val[MELT_SLOT_QMG] = qmg;
+                        val[MELT_SLOT_FWS] = __fdiv_rn(__fdiv_rn(__fmul_rn(QR, QS), QSG), qms);
+                        val[MELT_SLOT_FWG] = __fdiv_rn(__fdiv_rn(__fmul_rn(QR, QG), QSG), qmg);
+                        if (qms > 0.f || qmg > 0.f) { val[RADOP_VAR_QR] = 0.f; val[RADOP_VAR_QS] = 0.f; val[RADOP_VAR_QG] = 0.f; }
+                    }
+                }
 
                 // --- incidence elevation folded to [0, 90] (doppler_scatter.py:173-176) ---------
                 float e = e_g;
@@ -768,9 +791,24 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
 #pragma unroll 1
                 for (int s = 0; s < cfg.n_species; ++s) {
                     const SpeciesDev &S = cfg.sp[s];
-                    const float QMf = pick_mass(val, S.qm_var);
+                    const bool wet = S.psd == RADOP_PSD_MELTING;
+                    const float QMf = wet ? (S.species == RADOP_SP_MS ? val[MELT_SLOT_QMS] : val[MELT_SLOT_QMG])
+                                          : pick_mass(val, S.qm_var);
                     if (!(QMf > 0.f)) continue;
                     active |= (uint8_t)(1u << s);
+                    if (wet) {
+                        // PSD and integrals per gate in k_integrate_melting; here only the table bin:
+                        // lookup_line(e=..., wc=fwet), float64 arithmetic for the float64 fwet profile
+                        const float fw = S.species == RADOP_SP_MS ? val[MELT_SLOT_FWS] : val[MELT_SLOT_FWG];
+                        const int ie = lut_bin(e, S.e_min, S.e_step, S.e_rstep, S.ne);
+                        const double fb = floor(((double)fw - (double)S.t_min) / (double)S.t_step);
+                        const int it = fb < 0.0 ? 0 : (fb >= (double)S.nt ? S.nt - 1 : (int)fb);
+                        keys[s] = (uint32_t)(S.bin_base + ie * S.nt + it);
+                        o.p0[(size_t)s * n_sbg + sbg] = fw;
+                        o.p1[(size_t)s * n_sbg + sbg] = QMf;
+                        if (o.dbg_e) { o.dbg_e[sbg * cfg.n_species + s] = ie; o.dbg_t[sbg * cfg.n_species + s] = it; }
+                        continue;
+                    }
                     const double lQM = log((double)QMf);
                     double loglam, logn0 = 0.0, n0 = S.N0, ntot_2m = 0.0;
                     bool n0_from_log = false, n0_negative = false;
@@ -1306,6 +1344,7 @@ k_integrate(const __grid_constant__ DevConfig cfg, K2Args A)
         int s = 0;
         while (s + 1 < nsp && b >= cfg.sp[s + 1].bin_base) ++s;
         const SpeciesDev &S = cfg.sp[s];
+        if (S.mode == MODE_MELT) continue;      // melting species: k_integrate_melting
         const int cnt = A.hist[b];
         const int tiles = (cnt + RADOP_TILE - 1) / RADOP_TILE;
         const int j0 = (unit - A.chunk_start[b]) * RADOP_CHUNK, j1 = min(tiles, j0 + RADOP_CHUNK);
@@ -1455,6 +1494,117 @@ __global__ void k_ice_totals(const __grid_constant__ DevConfig cfg, const uint8_
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// K2m: melting snow / melting graupel (hydrometeors.py:303-500, 1393-1481; doppler_scatter.py:195-268).
+// One warp per active (sub-beam gate, melting species) pair, lanes over the diameters.  The PSD has
+// no closed form along the diameter axis: every gate has its own diameter grid (limits blended
+// with the wet fraction), and
+//     N(D) = prop * N_rain(D_r) V_rain(D_r) / V(D) dD_r/dD,   D_r = (m(D) / (pi/6 rho_w))^(1/3),
+//     m(D) = fw^2 m_rain(D) + (1 - fw^2) m_dry(D),            V = phi V_rain(D_r) + (1 - phi) V_dry(D),
+// with dD_r/dD the reference's forward difference (h = 0.01 mm) and prop = Q / sum(N m dD) so that the
+// mass is conserved.  Everything is float64 as in the reference (the pairs of a melting layer are few).
+struct K2mArgs {
+    const PairRec *rec;
+    const uint16_t *key;     // [species][n_sbg]
+    const int *bin_start;
+    float *sz_out;
+    float2 *dop_vn;
+    long long n_sbg;
+};
+
+__device__ __forceinline__ double pow_small(double x, double b)
+{
+    if (b == 3.0) return x * x * x;
+    if (b == 2.0) return x * x;
+    if (b == 1.0) return x;
+    if (b == 0.5) return sqrt(x);
+    if (b == 0.0) return 1.0;
+    return pow(x, b);
+}
+
+__global__ void __launch_bounds__(128)
+k_integrate_melting(const __grid_constant__ DevConfig cfg, K2mArgs A)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const int n_warps = (int)(((long long)gridDim.x * blockDim.x) >> 5);
+    const int nsp = cfg.n_species;
+    for (int s = 0; s < nsp; ++s) {
+        const SpeciesDev &S = cfg.sp[s];
+        if (S.mode != MODE_MELT) continue;
+        const int first = A.bin_start[S.bin_base], last = A.bin_start[S.bin_base + S.ne * S.nt];
+        const int nd = S.nd;
+        const double ar = S.melt[0], br = S.melt[1], alr = S.melt[2], ber = S.melt[3];
+        const double as = S.a, bs = S.b, als = S.alpha, bes = S.beta;
+        const double inv_vol = 1.0 / (3.141592653589793 / 6.0 * (1000. / (1000. * 1000. * 1000.)));   // 1 / (pi/6 rho_w)
+        for (int i = first + warp; i < last; i += n_warps) {
+            const PairRec rec = A.rec[i];
+            const uint32_t sbg = rec.sbg;
+            const double fw = (double)rec.p0, q = (double)rec.p1;
+            const int b = (int)A.key[(size_t)s * A.n_sbg + sbg] - S.bin_base;
+            const float4 *tab = reinterpret_cast<const float4 *>(S.table + (size_t)b * nd * 8);
+            // wet-fraction dependent diameter limits (f_wet setter, hydrometeors.py:333-340), vlinspace
+            const double dmax = fw * S.melt[5] + (1.0 - fw) * S.melt[7];
+            const double dmin = fw * S.melt[4] + (1.0 - fw) * S.melt[6];
+            const double step = (dmax - dmin) / (double)(nd - 1);
+            const double dD = (dmin + step) - dmin;
+            const double fw2 = fw * fw;
+            const double phi = 0.246 * fw + (1.0 - 0.246) * fw * fw * fw * fw * fw * fw * fw;
+            // equivalent rain with the mass of the melting species (Rain.set_psd, hydrometeors.py:761-772)
+            const double lam = pow(S.lambda_factor / q, 1.0 / (4.0 + S.mu));
+            double acc[7] = {0., 0., 0., 0., 0., 0., 0.};
+            double sm = 0.0, sv = 0.0, sn = 0.0, edge = 0.0, edge_v = 0.0;
+            for (int k = lane; k < nd; k += 32) {
+                const double D = dmin + step * (double)k;
+                const double D2 = D + 0.01;
+                const double m = fw2 * (ar * pow_small(D, br)) + (1.0 - fw2) * (as * pow_small(D, bs));
+                const double m2 = fw2 * (ar * pow_small(D2, br)) + (1.0 - fw2) * (as * pow_small(D2, bs));
+                const double Dr = cbrt(m * inv_vol), Dr2 = cbrt(m2 * inv_vol);
+                const double dDr = (Dr2 - Dr) / 0.01;
+                const double Vr = alr * pow_small(Dr, ber);
+                const double V = phi * Vr + (1.0 - phi) * (als * pow_small(D, bes));
+                const double Nr = S.N0 * pow_small(Dr, S.mu) * exp(-lam * pow_small(Dr, S.nu));
+                const double N = Nr * Vr / V * dDr;
+                const float4 t0 = __ldg(tab + 2 * k), t1 = __ldg(tab + 2 * k + 1);
+                acc[0] += (double)t0.x * N; acc[1] += (double)t0.y * N; acc[2] += (double)t0.z * N; acc[3] += (double)t0.w * N;
+                acc[4] += (double)t1.x * N; acc[5] += (double)t1.y * N; acc[6] += (double)t1.z * N;
+                sm += N * m;
+                if (cfg.doppler_scheme == 2) {
+                    const double nb = N * (double)t0.x;       // N rcs / (2 pi)
+                    sn += nb; sv += nb * V;
+                    if (k == 0 || k == nd - 1) { edge += nb; edge_v += nb * V; }
+                } else { sn += N; sv += N * V; }
+            }
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) {
+#pragma unroll
+                for (int c = 0; c < 7; ++c) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], d);
+                sm += __shfl_xor_sync(0xffffffffu, sm, d);
+                sv += __shfl_xor_sync(0xffffffffu, sv, d);
+                sn += __shfl_xor_sync(0xffffffffu, sn, d);
+                edge += __shfl_xor_sync(0xffffffffu, edge, d);
+                edge_v += __shfl_xor_sync(0xffffffffu, edge_v, d);
+            }
+            if (lane == 0) {
+                const double prop = q / (sm * dD);             // prop_factor = q / integrate_M()
+                const double f = prop * dD * (double)rec.w;
+                float4 *dst = reinterpret_cast<float4 *>(A.sz_out + ((size_t)sbg * nsp + s) * 8);
+                dst[0] = make_float4((float)(acc[0] * f), (float)(acc[1] * f), (float)(acc[2] * f), (float)(acc[3] * f));
+                dst[1] = make_float4((float)(acc[4] * f), (float)(acc[5] * f), (float)(acc[6] * f), 0.f);
+                if (A.dop_vn) {
+                    float2 vn;
+                    if (cfg.doppler_scheme == 2) {            // np.trapz with dx = 1 (doppler_scatter.py:286-296)
+                        const double c = 6.283185307179586 * prop;
+                        vn = make_float2((float)(c * (sv - 0.5 * edge_v)), (float)(c * (sn - 0.5 * edge)));
+                    } else                                      // integrate_V, hydrometeors.py:441-460
+                        vn = make_float2((float)(sv * prop * dD), (float)(sn * prop * dD));
+                    A.dop_vn[(size_t)sbg * nsp + s] = vn;
+                }
+            }
+        }
+    }
+}
+
 struct K3Args {
     const int8_t *mask;
     const uint8_t *active;
@@ -1511,6 +1661,13 @@ k_reduce_subbeams(const __grid_constant__ DevConfig cfg, K3Args A)
                 if (cfg.ice_numeric >= 0 && (act & (1u << cfg.ice_numeric))) {
                     const float *t = A.ice_tot + 3 * ((size_t)ray * cfg.n_sub + q);
                     if (__float_as_int(t[2]) == g) { vs += t[0]; ns += t[1]; }
+                }
+                if (cfg.with_melting) {       // numeric moments of the melting species (hydrometeors.py:441-460)
+                    for (int s = 0; s < nsp; ++s) {
+                        if (cfg.sp[s].psd != RADOP_PSD_MELTING || !(act & (1u << s))) continue;
+                        const float2 x = __ldg(A.dop_vn + sbg * nsp + s);
+                        vs += x.x; ns += x.y;
+                    }
                 }
             } else {
                 vs = 0.f; ns = 0.f;

@@ -17,7 +17,8 @@
 enum { MODE_GEO8 = 0,       // nu == 1 on a uniform D grid: blocked Horner, 8 columns
        MODE_GEN8 = 1,       // general nu: one ex2 per diameter, 8 columns
        MODE_ICE1 = 2,       // 1-mom ice (Field 2005 double exponential), 12 columns
-       MODE_GEN12 = 3 };    // general nu with numeric fall-speed integrals, 12 columns
+       MODE_GEN12 = 3,      // general nu with numeric fall-speed integrals, 12 columns
+       MODE_MELT = 4 };     // melting species: raw combined columns, PSD evaluated per gate (k_integrate_melting)
 
 struct SpeciesDev {
     int species, psd, mode, ncol;
@@ -47,6 +48,7 @@ struct SpeciesDev {
     double c_n, e_n;            // n-moment  = c_n * N0 * lambda^e_n
     double c_q, e_q;            // 2-mom N0  = c_q * QN * lambda^e_q * exp(-c_ka); lambda *= exp(-c_kb)
     double c_ka, c_kb;
+    double melt[8];             // RadopSpecies.melt (melting species)
 };
 
 struct DevConfig {
@@ -72,6 +74,7 @@ struct DevConfig {
     int n_vel;
     double vel_min, vel_res, inv_vel_res;
     // broadening of the sub-beam spectra (doppler_scatter.py:727-801): bit 0 turbulence, bit 1 antenna motion
+    int with_melting;
     int brd_mode;
     float brd_motion_num;       // float32(wavelength / 100 * antenna_speed)
     double brd_motion_den;      // 2 pi deg2rad(beamwidth)

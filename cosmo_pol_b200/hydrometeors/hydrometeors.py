@@ -16,17 +16,16 @@ import numpy as np
 from ..constants import constants_1mom, constants_2mom
 from ..constants import global_constants as constants
 
-_PSD_1MOM_FIXED, _PSD_1MOM_SNOW, _PSD_1MOM_ICE, _PSD_2MOM = 0, 1, 2, 3
-_SPECIES_ID = {'R': 0, 'S': 1, 'G': 2, 'H': 3, 'I': 4}
+_PSD_1MOM_FIXED, _PSD_1MOM_SNOW, _PSD_1MOM_ICE, _PSD_2MOM, _PSD_MELTING = 0, 1, 2, 3, 4
+_SPECIES_ID = {'R': 0, 'S': 1, 'G': 2, 'H': 3, 'I': 4, 'mS': 5, 'mG': 6}
 _CANTING = {'R': 10., 'S': 20., 'G': 40., 'H': 40., 'I': 5.}
 
 
 def create_hydrometeor(hydrom_type, scheme='1mom', sedi=False):
     """Factory with the reference's signature (hydrometeors.py:39-74)."""
-    cls = {'R': Rain, 'S': Snow, 'G': Graupel, 'H': Hail, 'I': IceParticle}.get(hydrom_type)
+    cls = {'R': Rain, 'S': Snow, 'G': Graupel, 'H': Hail, 'I': IceParticle,
+           'mS': MeltingSnow, 'mG': MeltingGraupel}.get(hydrom_type)
     if cls is None:
-        if hydrom_type in ('mS', 'mG'):
-            raise NotImplementedError('melting hydrometeors are not part of this build (SURVEY.md 8f N1)')
         raise ValueError('Invalid hydrometeor type, must be R, S, G, H, I, mS or mG')
     return cls(scheme)
 
@@ -198,3 +197,102 @@ class IceParticle(_Hydrometeor):
         N = self.get_N(D)
         dD = D[1] - D[0]
         return np.sum(N * self.get_V(D), axis=1) * dD, np.sum(N, axis=1) * dD
+
+
+class _MeltingHydrometeor(object):
+    """Wet snow / wet graupel between their dry counterpart and the equivalent rain
+    (hydrometeors.py:303-500): mass quadratic in the wet fraction, fall speed after
+    Frick et al. (2013), PSD from the flux of the equivalent rain, scaled so that the mass is
+    conserved.  One-moment scheme (the reference's two-moment call raises ValueError).
+    On the GPU path the class describes the species (``abi_fields``); the per-gate
+    evaluation is k_integrate_melting in csrc/radop_kernels.cu."""
+    kind = None
+    solid_cls = None
+
+    def __init__(self, scheme='1mom'):
+        if scheme != '1mom':
+            raise ValueError('Invalid parameters, cannot set psd')
+        self.scheme = scheme
+        self.nbins_D = 1024
+        self.equivalent_rain = Rain(scheme)
+        self.equivalent_solid = self.solid_cls(scheme)
+        self.prop_factor = None
+        self.canting_angle_std = self.equivalent_solid.canting_angle_std
+        self._f_wet = None
+
+    @property
+    def f_wet(self):
+        return self._f_wet
+
+    @f_wet.setter
+    def f_wet(self, fw):
+        r, d = self.equivalent_rain, self.equivalent_solid
+        self._f_wet = fw
+        self.d_max = fw * r.d_max + (1 - fw) * d.d_max
+        self.d_min = fw * r.d_min + (1 - fw) * d.d_min
+
+    def abi_fields(self):
+        r, d = self.equivalent_rain, self.equivalent_solid
+        return dict(species=_SPECIES_ID[self.kind], psd=_PSD_MELTING, numeric_vn=0,
+                    a=float(d.a), b=float(d.b), alpha=float(d.alpha), beta=float(d.beta),
+                    mu=float(r.mu), nu=float(r.nu), N0=float(r.N0), lambda_factor=float(r.lambda_factor),
+                    vel_factor=0.0, ntot_factor=0.0, x_min=0.0, x_max=0.0,
+                    melt=[float(r.a), float(r.b), float(r.alpha), float(r.beta),
+                          float(r.d_min), float(r.d_max), float(d.d_min), float(d.d_max)])
+
+    def set_psd(self, *args):
+        """(T, QM, f_wet) for melting snow, (QM, f_wet) for melting graupel."""
+        q = np.atleast_1d(np.asarray(args[-2], dtype=np.float64))
+        fw = np.atleast_1d(np.asarray(args[-1], dtype=np.float64))
+        self.prop_factor = None
+        self.equivalent_rain.set_psd(q)
+        self.f_wet = fw
+        with np.errstate(divide='ignore', invalid='ignore'):
+            self.prop_factor = q / self.integrate_M()
+
+    def _grid(self):
+        from ..utilities import vlinspace
+        D = vlinspace(self.d_min, self.d_max, self.nbins_D)
+        return D, D[:, 1] - D[:, 0]
+
+    def get_M(self, D):
+        fw2 = self.f_wet[:, None] ** 2
+        return fw2 * self.equivalent_rain.get_M(D) + (1 - fw2) * self.equivalent_solid.get_M(D)
+
+    def _equivalent_diameter(self, D):
+        return (self.get_M(D) / (np.pi / 6 * constants.RHO_W)) ** (1 / 3.)
+
+    def get_V(self, D):
+        fw = self.f_wet[:, None]
+        phi = 0.246 * fw + (1 - 0.246) * fw ** 7
+        return (phi * self.equivalent_rain.get_V(self._equivalent_diameter(D)) +
+                (1 - phi) * self.equivalent_solid.get_V(D))
+
+    def get_N(self, D):
+        D = np.asarray(D, dtype=np.float64)
+        r = self.equivalent_rain
+        Dr = self._equivalent_diameter(D)
+        slope = (self._equivalent_diameter(D + 0.01) - Dr) / 0.01
+        n_rain = r.N0 * Dr ** r.mu * np.exp(-np.atleast_1d(r.lambda_)[:, None] * Dr ** r.nu)
+        if self.prop_factor is not None:
+            n_rain = self.prop_factor[:, None] * n_rain
+        return n_rain * r.get_V(Dr) / self.get_V(D) * slope
+
+    def integrate_M(self):
+        D, dD = self._grid()
+        return np.sum(self.get_N(D) * self.get_M(D), axis=1) * dD
+
+    def integrate_V(self):
+        D, dD = self._grid()
+        N = self.get_N(D)
+        return np.sum(N * self.get_V(D), axis=1) * dD, np.sum(N, axis=1) * dD
+
+
+class MeltingSnow(_MeltingHydrometeor):
+    kind = 'mS'
+    solid_cls = Snow
+
+
+class MeltingGraupel(_MeltingHydrometeor):
+    kind = 'mG'
+    solid_cls = Graupel

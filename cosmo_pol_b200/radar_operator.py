@@ -148,7 +148,12 @@ class RadarOperator(object):
         c = self.__config
         h = ['R', 'S', 'G']
         if c['microphysics']['with_melting']:
-            raise NotImplementedError('the melting scheme is not part of this build (SURVEY.md 8f N1)')
+            if c['microphysics']['scheme'] == '2mom':
+                # MeltingSnow / MeltingGraupel.set_psd(QN, QM), hydrometeors.py:1413-1415, 1458-1460
+                raise ValueError('Invalid parameters, cannot set psd')
+            if c['doppler']['scheme'] == 3:
+                raise NotImplementedError('Doppler scheme 3 (spectrum) with the melting scheme is not part of this build')
+            h.extend(['mS', 'mG'])
         if c['microphysics']['scheme'] == '2mom':
             h.append('H')
         if c['microphysics']['with_ice_crystals']:

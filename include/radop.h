@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define RADOP_ABI_VERSION 3
+#define RADOP_ABI_VERSION 4
 
 /* ---- status codes ------------------------------------------------------- */
 enum {
@@ -59,14 +59,18 @@ enum {
 };
 
 /* ---- hydrometeor species (order of doppler_scatter.py:99-106) ------------- */
-enum { RADOP_SP_R = 0, RADOP_SP_S, RADOP_SP_G, RADOP_SP_H, RADOP_SP_I, RADOP_NSPECIES_MAX = 5 };
+enum { RADOP_SP_R = 0, RADOP_SP_S, RADOP_SP_G, RADOP_SP_H, RADOP_SP_I,
+       RADOP_SP_MS, RADOP_SP_MG,          /* melting snow / graupel (with_melting, melting.py:19-90) */
+       RADOP_NSPECIES_MAX = 7 };
 
 /* PSD families (cosmo_pol/hydrometeors/hydrometeors.py) */
 enum {
     RADOP_PSD_1MOM_FIXED_N0 = 0, /* Rain :761-772, Graupel :1039-1049                     */
     RADOP_PSD_1MOM_SNOW = 1,     /* Snow :894-907 (N0 from temperature)                   */
     RADOP_PSD_1MOM_ICE = 2,      /* IceParticle :1320-1339 (Field et al. 2005 moments)    */
-    RADOP_PSD_2MOM = 3           /* _Hydrometeor.set_psd :224-255, IceParticle :1341-1365 */
+    RADOP_PSD_2MOM = 3,          /* _Hydrometeor.set_psd :224-255, IceParticle :1341-1365 */
+    RADOP_PSD_MELTING = 4        /* _MeltingHydrometeor :303-500, MeltingSnow / MeltingGraupel :1393-1481
+                                    (one-moment scheme; PSD from the flux of the equivalent rain)  */
 };
 
 /* One species: constants of cosmo_pol/constants/constants_{1,2}mom.py */
@@ -82,6 +86,11 @@ typedef struct {
     double N0;              /* fixed intercept (1-mom rain / graupel)                     */
     double lambda_factor, vel_factor, ntot_factor;
     double x_min, x_max;    /* 2-mom mean-mass limits                                     */
+    /* RADOP_PSD_MELTING: a, b, alpha, beta above are those of the dry counterpart (snow / graupel);
+       mu, nu, N0, lambda_factor those of the equivalent rain; and
+       melt[0..3] = rain a, b, alpha, beta; melt[4..5] = rain D_MIN, D_MAX; melt[6..7] = dry D_MIN, D_MAX
+       (constants_1mom.py; the wet-fraction dependent limits of hydrometeors.py:333-340)              */
+    double melt[8];
 } RadopSpecies;
 
 /* Scalars the hot path reads from cfg.CONFIG / global_constants */
@@ -113,6 +122,9 @@ typedef struct {
     int32_t spectrum_motion;      /* CONFIG['doppler']['motion_correction']                      */
     double antenna_speed;         /* CONFIG['radar']['antenna_speed']                            */
     double beamwidth_deg;         /* CONFIG['radar']['3dB_beamwidth']                            */
+    int32_t with_melting;         /* CONFIG['microphysics']['with_melting']: re-partition QR, QS, QG into
+                                     the melting species after the interpolation (melting.py:19-90) */
+    int32_t reserved3;
 } RadopParams;
 
 /*
@@ -180,7 +192,9 @@ int radop_upload_grid(RadopHandle *h, int nz, int ny, int nx, const float *zleve
 int radop_upload_field(RadopHandle *h, int var_id, const float *data);
 
 /* One scattering table (lut.Lookup_table): value_table [ne][nt][nd][12] float64,
- * axis minimum and step as float32 (axes_limits / axes_step), diameters [nd] float32. */
+ * axis minimum and step as float32 (axes_limits / axes_step), diameters [nd] float32.
+ * Melting species: the second axis is the wet fraction 'wc' (t_min, t_step = its minimum and
+ * step); their diameters depend on the gate, d_axis is only used for its length. */
 int radop_upload_lut(RadopHandle *h, int species, const double *value_table,
                      int ne, int nt, int nd, float e_min, float e_step,
                      float t_min, float t_step, const float *d_axis);

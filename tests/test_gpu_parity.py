@@ -18,7 +18,8 @@ CONF_1MOM = {'radar': {'coords': [47.28436, 8.51201, 891.], 'type': 'ground', 'f
 
 def make_operator(conf, scheme='1mom', freq=5.6, output_variables='only_radar', **model_kw):
     from cosmo_pol_b200 import RadarOperator
-    model, luts = synthetic_inputs(scheme, freq, **model_kw)
+    melt = bool(conf.get('microphysics', {}).get('with_melting', 0))
+    model, luts = synthetic_inputs(scheme, freq, with_melting=melt, **model_kw)
     conf = copy.deepcopy(conf)
     conf['radar']['frequency'] = freq
     op = RadarOperator(conf, output_variables=output_variables, device=0)
@@ -367,6 +368,70 @@ def test_doppler_spectrum_broadening_against_reference_golden(name):
     assert np.all(np.isnan(a[np.isnan(b)])) and np.all(np.isfinite(a[strong]))
     ok = np.isfinite(b) & strong
     assert np.max(np.abs(a[ok] - b[ok])) < 0.05
+
+
+@pytest.mark.parametrize('doppler', [1, 2])
+def test_melting_scheme_against_oracle(doppler):
+    """Melting scheme: re-partition of QR, QS, QG (melting.py:19-90), wet snow
+    and wet graupel with per-gate diameter grids, wet-fraction table axis, numeric fall-speed moments
+    (hydrometeors.py:303-500, 1393-1481; doppler_scatter.py:162-165, 195-201, 216-221, 236-248)."""
+    conf = copy.deepcopy(CONF_1MOM)
+    conf['radar'].update({'range': 30000, 'radial_resolution': 500})
+    conf['microphysics'] = {'with_melting': 1}
+    conf['doppler'] = {'scheme': doppler}
+    op, model, luts = make_operator(conf, '1mom', 5.6)
+    az = np.array([150., 170., 180., 220.])
+    els = [1.0, 3.5, 6.0]
+    rays_az, rays_el = np.tile(az, len(els)), np.repeat(els, len(az))
+    eng = op._prepare_engine(keep_debug=True)
+    out = op.simulate_rays(rays_az, rays_el)
+    pm, pl = plain(model, luts)
+    ref = O.simulate_scan(pm, pl, oracle_cfg(op), rays_az, rays_el, accum='f64', sensitivity_cut=True, debug=True)
+    st = op._engine.stats()
+    order = op._engine.species_order
+    assert order == ['R', 'S', 'G', 'mS', 'mG', 'I']
+    n_wet = st['pairs_by_species'][order.index('mS')], st['pairs_by_species'][order.index('mG')]
+    assert n_wet[0] > 20 and n_wet[1] > 200, n_wet
+    assert_observables_close(out, ref, what='melting dop{}'.format(doppler))
+    a, b = out['RVEL'], ref['RVEL']
+    assert np.array_equal(np.isnan(a), np.isnan(b))
+    ok = np.isfinite(b)
+    assert np.max(np.abs(a[ok] - b[ok])) < 2e-3
+    # the melting layer must matter: without the scheme the reflectivities differ
+    conf0 = copy.deepcopy(conf)
+    conf0['microphysics'] = {'with_melting': 0}
+    op0, _, _ = make_operator(conf0, '1mom', 5.6)
+    dry = op0.simulate_rays(rays_az, rays_el)
+    both = np.isfinite(dry['ZH']) & np.isfinite(out['ZH'])
+    assert np.max(np.abs(10 * np.log10(dry['ZH'][both] / out['ZH'][both]))) > 1.0
+
+
+@pytest.mark.parametrize('name', ['c1mom_melt', 'c1mom_melt_dop2'])
+def test_melting_scheme_against_reference_golden(name):
+    from cosmo_pol_b200 import RadarOperator
+    g, cfg, kw = load_golden_case(name)
+    model, luts = synthetic_inputs('1mom', 5.6, with_melting=True, **kw)
+    conf = copy.deepcopy(cfg)
+    conf['radar']['sensitivity'] = [-300, 10000]
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    rays = g['rays']
+    out = op.simulate_rays(rays[:, 0], rays[:, 1])
+    ref = {k[4:]: g[k] for k in g.files if k.startswith('obs_')}
+    assert_observables_close(out, ref, sz_scale=5e-4 * np.abs(ref['KDP']), what=name)
+    a, b = out['RVEL'], ref['RVEL']
+    assert np.array_equal(np.isnan(a), np.isnan(b))
+    ok = np.isfinite(b)
+    assert np.max(np.abs(a[ok] - b[ok])) < 2e-3
+    # unsupported combinations fail loudly
+    bad = copy.deepcopy(conf)
+    bad['doppler'] = {'scheme': 3}
+    op3 = RadarOperator(bad, output_variables='only_radar', device=0)
+    op3.set_lut(luts)
+    op3.load_model(model)
+    with pytest.raises(NotImplementedError):
+        op3.simulate_rays(rays[:1, 0], rays[:1, 1])
 
 
 def test_edge_cases_and_errors():
