@@ -685,7 +685,7 @@ __device__ __forceinline__ float pick_number(const float (&v)[RADOP_NVP], int va
 
 // Persistent blocks: each block walks chunks of 128 consecutive sub-beam gates and keeps
 // one shared-memory histogram of the LUT bins for its whole life (flushed once).
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 8)
 k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *__restrict__ geo,
              const float *__restrict__ z_t, const float *__restrict__ fields, K1Out o, long long n_sbg)
 {

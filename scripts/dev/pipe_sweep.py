@@ -1,4 +1,6 @@
-"""Sweep of the chunk-pipelining parameters on configuration 3 (device step time)."""
+"""Sweep of the chunk-pipelining parameters on configuration 3 (device step time).
+Needs the experimental radop_set_pipeline build described in profiles/r01d_pipeline_experiment.md
+(not in the tree: the experiment was negative)."""
 import os, sys, json
 import numpy as np
 ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), '..', '..'))
