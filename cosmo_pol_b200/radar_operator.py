@@ -176,6 +176,9 @@ class RadarOperator(object):
         two = all(v in dic_vars for v in BASE_VARIABLES_2MOM)
         scheme = '2mom' if two else '1mom'
         print('Using {}-moment scheme'.format(2 if two else 1))
+        dic_vars = dict(dic_vars)
+        if 'N' in dic_vars:          # refractivity for the ODE refraction scheme (radar_operator.py:294-296)
+            self.N = dic_vars.pop('N')
         self.dic_vars = dic_vars
         self._dirty['model'] = True
         changed = scheme != self.current_microphys_scheme
@@ -253,10 +256,13 @@ class RadarOperator(object):
         ts = np.empty((len(uniq), nv, ng), np.float32)
         th = np.empty_like(ts)
         te = np.empty_like(ts)
+        if c['refraction']['scheme'] == 2 and not hasattr(self.N, 'data'):
+            raise ValueError('refraction scheme 2 (Zeng and Blahak 2014) needs the refractivity N among the model variables')
         for i, el in enumerate(uniq):
             for j, pt in enumerate(fan.pts_ver):
                 ts[i, j], th[i, j], te[i, j] = compute_trajectory_radial(rr, pt + el, c['radar']['coords'],
-                                                                          c['refraction']['scheme'], self.N)
+                                                                          c['refraction']['scheme'], self.N,
+                                                                          c['radar']['type'])
         nyq = None
         f = c['radar']['nyquist_velocity']
         if f is not None:

@@ -58,7 +58,7 @@ def _smooth_noise(rng, shape, sigma):
 
 
 def make_model(nz=60, ny=400, nx=400, res=0.02, radar=ALBIS, scheme='1mom', seed=1234,
-               south_pole=SOUTH_POLE, top=22000.0, with_edr=False):
+               south_pole=SOUTH_POLE, top=22000.0, with_edr=False, with_refractivity=False):
     """Returns dict name -> ModelVariable (all float32, C-contiguous)."""
     rng = np.random.default_rng(seed)
     rlat0, rlon0 = _wgs_to_rot(radar[0], radar[1], south_pole[0], south_pole[1])
@@ -123,6 +123,12 @@ def make_model(nz=60, ny=400, nx=400, res=0.02, radar=ALBIS, scheme='1mom', seed
         edr = 10.0 ** (-3.0 + 0.8 * np.clip(_smooth_noise(rng, shape, sig), -2.0, 2.0))
         data['EDR'] = edr.astype(np.float32)
         names.append('EDR')
+    if with_refractivity:
+        # atmospheric refractivity N = (n - 1) 1e6 (radar_operator.py:239, 294-296): exponential reference
+        # atmosphere with a seeded ducting-like perturbation near 1.5 km; drawn after everything else
+        nn = 315.0 * np.exp(-zz / 7350.0) * (1.0 + 0.02 * np.exp(-((zz - 1500.0) / 400.0) ** 2))
+        data['N'] = (nn + 0.3 * _smooth_noise(rng, shape, sig)).astype(np.float32)
+        names.append('N')
     attrs = {'z-levels': z, 'proj_info': proj, 'resolution': [res, res], 'time': '2026-01-01 00:00:00'}
     return {n: ModelVariable(n, np.ascontiguousarray(data[n]), attrs) for n in names}
 
@@ -298,7 +304,8 @@ def lut_as_plain(lut):
 def model_as_plain(dic_vars):
     """Plain-dict view of a model dictionary (what the CPU oracle consumes)."""
     first = next(iter(dic_vars.values()))
-    return {'vars': {k: v.data for k, v in dic_vars.items()},
+    extra = {'refractivity': dic_vars['N'].data} if 'N' in dic_vars else {}
+    return {'vars': {k: v.data for k, v in dic_vars.items() if k != 'N'}, **extra,
             'z_levels': first.attributes['z-levels'],
             'proj': first.attributes['proj_info'],
             'resolution': first.attributes['resolution']}

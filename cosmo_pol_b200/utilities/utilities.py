@@ -106,3 +106,17 @@ def combine_subradials(list_of_subradials):
             print('Beams are not defined on the same set of coordinates, aborting')
             return
     return x
+
+
+def WGS_to_COSMO(coords, south_pole):
+    """Geographic (lat, lon) [deg] -> rotated-pole (rlat, rlon) [deg] for the rotated SOUTH pole
+    (lat, lon): rotation about z by the pole longitude, then about y by 90 deg + pole latitude
+    (the transform pycosmo.WGS_to_COSMO provides to the reference, interpolation.py:566-568;
+    on the device the same rotation is in k_interp_psd)."""
+    lat, lon = np.deg2rad(np.asarray(coords[0], dtype=np.float64)), np.deg2rad(np.asarray(coords[1], dtype=np.float64))
+    th, ph = np.deg2rad(90. + south_pole[0]), np.deg2rad(south_pole[1])
+    x, y, z = np.cos(lon) * np.cos(lat), np.sin(lon) * np.cos(lat), np.sin(lat)
+    xn = np.cos(th) * np.cos(ph) * x + np.cos(th) * np.sin(ph) * y + np.sin(th) * z
+    yn = -np.sin(ph) * x + np.cos(ph) * y
+    zn = -np.sin(th) * np.cos(ph) * x - np.sin(th) * np.sin(ph) * y + np.cos(th) * z
+    return np.rad2deg(np.arcsin(zn)), np.rad2deg(np.arctan2(yn, xn))

@@ -277,6 +277,59 @@ def ref_4_3(range_vec, elevation_angle, coords_radar):
     return s, h, e
 
 
+def ref_ode(range_vec, elevation_angle, coords_radar, N, radar_type='ground'):
+    """atm_refraction.py:56-148 (Zeng and Blahak 2014): beam height and elevation from the second-order
+    ODE through the refractive-index profile of the model column at the radar.  N: dict(data [nz,ny,nx]
+    refractivity, z_levels, proj, resolution).  Third-party arithmetic of the reference on this path:
+    scipy.integrate.odeint (LSODA) and scipy.interpolate.interp1d (scipy 1.18.1 in this image), called
+    here exactly as the reference calls them.  Quirks kept: the latitude index of the radar is used for
+    both horizontal axes (:113-117); the profile stays float32; the arc distance of the first gate is 0."""
+    from scipy.integrate import odeint
+    from scipy.interpolate import interp1d
+    proj = N['proj']
+    rot = wgs_to_rotated(coords_radar[0], coords_radar[1], proj['Latitude_of_southern_pole'],
+                         proj['Longitude_of_southern_pole'])[0]
+    llc = (float(proj['Lo1']), float(proj['La1']))
+    res = N['resolution']
+    pos = [(rot[0] - llc[1]) / res[1], (rot[1] - llc[0]) / res[0]]
+    i = int(np.round(pos[0]))
+    n_prof = 1 + (N['data'][:, i, i]) * 1E-6
+    h = N['z_levels'][:, i, i]
+    RE = earth_radius(coords_radar[0])
+    if radar_type == 'ground':
+        h = h[::-1]
+        n_prof = n_prof[::-1]
+
+    def piecewise(x, y):
+        f = interp1d(x, y)
+        xs, ys = f.x, f.y
+
+        def at(v):
+            if v < xs[0]:
+                return ys[0] + (v - xs[0]) * (ys[1] - ys[0]) / (xs[1] - xs[0])
+            if v > xs[-1]:
+                return ys[-1] + (v - xs[-1]) * (ys[-1] - ys[-2]) / (xs[-1] - xs[-2])
+            return f(v)
+        return at
+
+    n_of_h = piecewise(h, n_prof)
+    dn_of_h = piecewise(h[0:-1], np.diff(n_prof) / np.diff(h))
+
+    def rhs(z, r):
+        hh, u = z
+        k = (1. / n_of_h(hh)) * dn_of_h(hh) + 1. / (RE + hh)
+        return [u, float(np.squeeze(-u ** 2 * k + k))]
+
+    Z = odeint(rhs, [coords_radar[2], np.sin(np.deg2rad(elevation_angle))], range_vec)
+    hh = Z[:, 0]
+    e = np.arcsin(Z[:, 1])
+    s = np.zeros(hh.shape)
+    dR = range_vec[1] - range_vec[0]
+    for k in range(1, len(s)):
+        s[k] = s[k - 1] + RE * np.arcsin((np.cos(e[k - 1]) * dR) / (RE + hh[k]))
+    return s.astype('float32'), hh.astype('float32'), np.rad2deg(e.astype('float32'))
+
+
 # --------------------------------------------------------------------------- #
 # a3: geolocation (third-party arithmetic restated)
 # --------------------------------------------------------------------------- #
@@ -415,14 +468,21 @@ def melting(sub):
 
 
 def get_interpolated_radial(model, azimuth, elevation, cfg, debug=False):
-    """interpolation.py:91-438 for integration scheme 1, refraction scheme 1.
+    """interpolation.py:91-438 for integration scheme 1, refraction schemes 1 and 2 (the refractivity field is
+    model['refractivity'], kept apart from the interpolated variables like the reference's self.N).
     A sub-radial is a dict with the attributes of the reference's Radial
     (radial.py:16-54)."""
     names = list(model['vars'].keys())
     pts_hor, pts_ver, weights, keep = gauss_hermite_subbeams(cfg)
     rranges = derived_constants(cfg)['RANGE_RADAR']
     radar_pos = cfg['radar']['coords']
-    list_refraction = [ref_4_3(rranges, pt + elevation, radar_pos) for pt in pts_ver]
+    if cfg['refraction']['scheme'] == 2:
+        N = {'data': model['refractivity'], 'z_levels': model['z_levels'], 'proj': model['proj'],
+             'resolution': model['resolution']}
+        list_refraction = [ref_ode(rranges, pt + elevation, radar_pos, N, cfg['radar'].get('type', 'ground'))
+                           for pt in pts_ver]
+    else:
+        list_refraction = [ref_4_3(rranges, pt + elevation, radar_pos) for pt in pts_ver]
     subs = []
     for i in range(len(pts_hor)):
         for j in range(len(pts_ver)):

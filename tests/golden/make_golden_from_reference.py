@@ -106,8 +106,9 @@ pycosmo = types.ModuleType('pycosmo')
 
 
 def _wgs_to_cosmo(coords, sp):
-    lats, lons = coords
-    return O.wgs_to_rotated(lats, lons, sp[0], sp[1])
+    lats, lons = coords[0], coords[1]      # _ref_ODE passes [lat, lon, alt] (atm_refraction.py:100-103)
+    r = O.wgs_to_rotated(lats, lons, sp[0], sp[1])
+    return r[0] if np.ndim(lats) == 0 else r          # scalar position -> (rlat, rlon)
 
 
 pycosmo.WGS_to_COSMO = _wgs_to_cosmo
@@ -212,6 +213,9 @@ def ref_lut(R, lut):
 
 
 # --------------------------------------------------------------------------------------------
+MODEL_KW = dict(nz=24, ny=64, nx=64, res=0.04)
+
+
 def golden_constants(R):
     out = {}
     for tag, mod in (('1mom', R['c1']), ('2mom', R['c2'])):
@@ -247,6 +251,20 @@ def golden_units(R):
     g['traj_s'] = np.stack([t[0] for t in tr])
     g['traj_h'] = np.stack([t[1] for t in tr])
     g['traj_e'] = np.stack([t[2] for t in tr])
+    # ODE refraction (Zeng and Blahak 2014, atm_refraction.py:56-148) through a synthetic refractivity field
+    mN = synthetic.make_model(scheme='1mom', with_refractivity=True, **MODEL_KW)['N']
+    els2 = np.array([-0.2, 0.4, 1.0, 5.5, 20.0, 40.0])
+    rr2 = np.arange(150., 60000., 300.)
+    g['ode_elev'] = els2
+    g['ode_range'] = rr2
+    # numpy >= 1.24 refuses the ragged [scalar, array(1)] list _deriv_z returns (atm_refraction.py:75-77);
+    # same arithmetic, elements squeezed to floats
+    _orig_deriv = R['atm']._deriv_z
+    R['atm']._deriv_z = lambda z, r, n_h, dn_dh, RE: [float(np.squeeze(v)) for v in _orig_deriv(z, r, n_h, dn_dh, RE)]
+    tr = [R['atm'].compute_trajectory_radial(rr2, e, cfgd['radar']['coords'], 2, mN) for e in els2]
+    g['ode_s'] = np.stack([t[0] for t in tr])
+    g['ode_h'] = np.stack([t[1] for t in tr])
+    g['ode_e'] = np.stack([t[2] for t in tr])
     g['earth_radius_in'] = np.array([0., 8.51201, 47.3, 90.])
     g['earth_radius'] = np.array([R['utilities'].get_earth_radius(x) for x in g['earth_radius_in']])
     # aliasing, nansum
@@ -342,7 +360,6 @@ CASES = {
                                           microphysics={'with_melting': 1}, integration={'nv_GH': 1, 'nh_GH': 3}),
                         [(220.0, 3.5)], {}),
 }
-MODEL_KW = dict(nz=24, ny=64, nx=64, res=0.04)
 MELTING_N_E = 8          # elevation bins of the synthetic melting tables (0..14 deg): 78 MB per species
 
 

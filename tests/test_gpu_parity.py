@@ -434,6 +434,36 @@ def test_melting_scheme_against_reference_golden(name):
         op3.simulate_rays(rays[:1, 0], rays[:1, 1])
 
 
+def test_ode_refraction_scheme_against_oracle():
+    """Refraction scheme 2 (atm_refraction.py:56-148): the trajectories come from the host-side
+    ODE through the model's refractivity, the kernels are unchanged.  Bit-exact interpolation decisions."""
+    conf = copy.deepcopy(CONF_1MOM)
+    conf['refraction'] = {'scheme': 2}
+    op, model, luts = make_operator(conf, '1mom', 5.6, output_variables='all', with_refractivity=True)
+    az = np.array([20., 140., 260.])
+    els = [0.4, 3.5, 12.0]
+    res = op.get_PPI(els, azimuths=az)
+    pm, pl = plain(model, luts)
+    rays_az, rays_el = np.tile(az, len(els)), np.repeat(els, len(az))
+    ref = O.simulate_scan(pm, pl, oracle_cfg(op), rays_az, rays_el, accum='f64', output_variables='all',
+                          sensitivity_cut=True)
+    got = {k: v.reshape(-1, v.shape[-1]) for k, v in res.fields.items()}
+    assert_observables_close(got, ref, what='ODE refraction')
+    assert np.array_equal(res.heights.reshape(ref['heights'].shape), ref['heights'])
+    assert np.array_equal(res.dist.reshape(ref['dist'].shape), ref['dist'])
+    for name in ('T', 'QR_v'):
+        assert np.allclose(got[name], ref[name], rtol=2e-5, atol=1e-9), name
+    # and it is not the 4/3 model
+    conf1 = copy.deepcopy(CONF_1MOM)
+    op1, _, _ = make_operator(conf1, '1mom', 5.6, with_refractivity=True)
+    r1 = op1.get_PPI(els, azimuths=az)
+    assert np.max(np.abs(r1.heights - res.heights)) > 1.0
+    # without a refractivity field the scheme is refused
+    op2, _, _ = make_operator(conf, '1mom', 5.6)
+    with pytest.raises(ValueError):
+        op2.get_PPI([1.0], azimuths=[5.])
+
+
 def test_edge_cases_and_errors():
     from cosmo_pol_b200 import RadarOperator
     from cosmo_pol_b200._abi import RadopError

@@ -92,8 +92,53 @@ def test_refraction_matches_reference_bitwise():
         s, h, e = compute_trajectory_radial(g['derived_range'], el, coords, 1)
         assert s.dtype == np.float32 and np.array_equal(s, g['traj_s'][i])
         assert np.array_equal(h, g['traj_h'][i]) and np.array_equal(e, g['traj_e'][i])
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(AttributeError):      # scheme 2 without a refractivity field (N = 0), as in the reference
         compute_trajectory_radial(g['derived_range'], 1.0, coords, 2)
+
+
+def test_ode_refraction_matches_reference_bitwise():
+    """Refraction scheme 2 (Zeng and Blahak 2014, atm_refraction.py:56-148) through the synthetic
+    refractivity field: host implementation and oracle against vectors produced by the reference."""
+    import radop_oracle as O
+    from cosmo_pol_b200 import synthetic
+    from cosmo_pol_b200.interpolation.atm_refraction import compute_trajectory_radial
+    g = np.load(os.path.join(GOLDEN, 'ref_units.npz'), allow_pickle=True)
+    model = synthetic.make_model(scheme='1mom', with_refractivity=True, nz=24, ny=64, nx=64, res=0.04)
+    pm = synthetic.model_as_plain(model)
+    N = {'data': pm['refractivity'], 'z_levels': pm['z_levels'], 'proj': pm['proj'], 'resolution': pm['resolution']}
+    coords = list(synthetic.ALBIS)
+    for i, el in enumerate(g['ode_elev']):
+        for s, h, e in (compute_trajectory_radial(g['ode_range'], el, coords, 2, model['N']),
+                        O.ref_ode(g['ode_range'], el, coords, N)):
+            assert s.dtype == np.float32 and s[0] == 0
+            assert np.array_equal(s, g['ode_s'][i]) and np.array_equal(h, g['ode_h'][i]) and np.array_equal(e, g['ode_e'][i])
+
+
+def test_melting_hydrometeor_classes_match_oracle():
+    """Host mirror of MeltingSnow / MeltingGraupel (hydrometeors.py:303-500, 1393-1481) against the
+    oracle's restatement, which the reference goldens pin (test_oracle_golden.py, c1mom_melt*)."""
+    import radop_oracle as O
+    from cosmo_pol_b200.hydrometeors import create_hydrometeor
+    rng = np.random.default_rng(11)
+    # float32 values in float64 arrays, as melting() leaves them in the sub-radial (melting.py:62-80)
+    q = rng.uniform(1e-5, 2e-3, 7).astype(np.float32).astype(np.float64)
+    fw = rng.uniform(0.02, 0.97, 7).astype(np.float32).astype(np.float64)
+    T = rng.uniform(268, 276, 7).astype(np.float32)
+    for kind in ('mS', 'mG'):
+        a, b = create_hydrometeor(kind, '1mom'), O.MeltHydro(kind, '1mom')
+        args = (T, q, fw) if kind == 'mS' else (q, fw)
+        a.set_psd(*args)
+        b.set_psd(*args)
+        assert np.allclose(a.d_min, b.d_min, rtol=1e-7) and np.allclose(a.d_max, b.d_max, rtol=1e-7)
+        D = O.vlinspace(b.d_min, b.d_max, 1024)
+        assert np.allclose(a.get_N(D), b.get_N(D), rtol=1e-9)
+        assert np.allclose(a.get_V(D), b.get_V(D), rtol=1e-12)
+        for x, y in zip(a.integrate_V(), b.integrate_V()):
+            assert np.allclose(x, y, rtol=1e-9)
+        # the PSD carries the prescribed mass
+        assert np.allclose(a.integrate_M(), q, rtol=1e-6)
+        f = a.abi_fields()
+        assert f['psd'] == 4 and len(f['melt']) == 8
 
 
 @pytest.mark.parametrize('scheme,kinds', [('1mom', 'RSGI'), ('2mom', 'RSGHI')])
