@@ -55,8 +55,13 @@ class SimulatedScan(object):
         return {'elevations': self.elevations, 'azimuths': self.azimuths, 'ranges': self.ranges,
                 'pos_time': self.pos_time, 'data': self.data}
 
+    def to_volume(self):
+        """The scan in the field layout of the reference's PyartRadop (no Py-ART needed)."""
+        from .radar import RadopVolume
+        return RadopVolume(self.scan_type, self)
+
     def to_pyart(self):
-        raise NotImplementedError('the Py-ART adapter (PyartRadop) is outside the hot path (SURVEY.md 8f N2)')
+        return self.to_volume().to_pyart()
 
 
 class RadarOperator(object):

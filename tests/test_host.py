@@ -199,3 +199,55 @@ def test_product_never_imports_oracle():
             if f.endswith('.py'):
                 src = open(os.path.join(dirpath, f)).read()
                 assert 'radop_oracle' not in src and 'oracle/' not in src.replace('oracle/_ref', ''), f
+
+
+def test_output_adapter_matches_per_radial_assembly():
+    """RadopVolume against the reference's own assembly order, restated here from
+    pyart_wrapper.py:205-327 over the list (sweeps) of lists (rays) of Radial objects."""
+    from cosmo_pol_b200.radar_operator import SimulatedScan
+    rng = np.random.default_rng(5)
+    ns, nr, ng, nv = 3, 4, 6, 5
+    fields = {k: rng.uniform(0.1, 50, (ns, nr, ng)).astype(np.float32) for k in ('ZH', 'ZV', 'ZDR', 'KDP', 'RVEL')}
+    fields['ZH'][0, 1, 2] = 0.0                      # exact zero -> NaN before the dB conversion
+    fields['KDP'][1, 0, 3] = np.nan
+    fields['DSPECTRUM'] = rng.uniform(0, 1, (ns, nr, ng, nv)).astype(np.float32)
+    lats, lons = rng.uniform(46, 48, (ns, nr, ng)), rng.uniform(7, 9, (ns, nr, ng))
+    mask = np.zeros((ns, nr, ng), np.float32)
+    els, azs, ranges = np.array([1.0, 5.0, 9.0]), np.array([0., 90., 180., 270.]), np.arange(ng) * 300. + 150.
+    pos = {'latitude': 47.28, 'longitude': 8.51, 'altitude': 891., 'time': '2026-01-01 00:00:00'}
+    scan = SimulatedScan('ppi', els, azs, ranges, pos, fields, mask, lats, lons, lats * 0, lats * 0)
+    vol = scan.to_volume()
+    # the reference's loop
+    data = scan.data
+    exp, start, stop, el_all, az_all, i0 = {}, [], [], [], [], 0
+    for i in range(ns):
+        sweep = {}
+        for k in fields:
+            a = np.array([it.values[k] for it in data[i]])
+            if k in ('ZDR', 'ZV', 'ZH', 'DSpectrum'):
+                a[a == 0] = float('nan')
+                with np.errstate(invalid='ignore'):
+                    a = 10 * np.log10(a)
+            sweep[k] = a
+        sweep['Latitude'] = np.array([it.lats_profile for it in data[i]])
+        sweep['Longitude'] = np.array([it.lons_profile for it in data[i]])
+        start.append(i0); stop.append(i0 + nr - 1); i0 += nr
+        el_all.extend([els[i]] * nr); az_all.extend(list(azs))
+        for k, a in sweep.items():
+            exp[k] = a if k not in exp else np.vstack([exp[k], a])
+    for k, a in exp.items():
+        got = vol.fields[k]['data']
+        assert got.shape == a.shape, k
+        assert np.array_equal(np.ma.getmaskarray(got), np.isnan(a)), k
+        assert np.allclose(np.ma.filled(got, 0), np.nan_to_num(a), rtol=1e-6), k
+    assert np.array_equal(vol.sweep_start_ray_index['data'], start) and np.array_equal(vol.sweep_end_ray_index['data'], stop)
+    assert np.array_equal(vol.elevation['data'], el_all) and np.array_equal(vol.azimuth['data'], az_all)
+    assert np.array_equal(vol.fields['rangearray']['data'], np.tile(ranges, (ns * nr, 1)))
+    assert vol.get_field(1, 'ZH').shape == (nr, ng) and vol.nrays == ns * nr and vol.ngates == ng
+    assert np.array_equal(vol.fixed_angle['data'], els)
+    rhi = SimulatedScan('rhi', np.array([0., 1., 2., 3.]), np.array([10., 20., 30.]), ranges, pos, fields, mask, lats, lons,
+                        lats * 0, lats * 0).to_volume()
+    assert np.array_equal(rhi.azimuth['data'], np.repeat([10., 20., 30.], nr))
+    assert np.array_equal(rhi.elevation['data'], np.tile([0., 1., 2., 3.], ns))
+    with pytest.raises(ImportError):
+        vol.to_pyart()
