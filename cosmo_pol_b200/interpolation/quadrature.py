@@ -3,7 +3,8 @@
 
 Scheme 1 of cosmo_pol/interpolation/interpolation.py:148-166 (Gauss-Hermite nodes scaled by
 sigma = bw/(2 sqrt(2 ln 2)), weights multiplied by |cos(pts_ver)| and normalised) followed by
-the cumulative weight threshold of interpolation.py:343-354."""
+the cumulative weight threshold of interpolation.py:343-354; scheme 2 (multi-Gaussian antenna pattern,
+irregular points, interpolation.py:194-228)."""
 import numpy as np
 from numpy.polynomial.hermite import hermgauss
 
@@ -24,11 +25,64 @@ class SubbeamFan(object):
         self.center = int(self.n_sub / 2)
 
 
+    @classmethod
+    def irregular(cls, daz, dele, weight):
+        """Fan of unrelated points (integration scheme 2): every sub-beam has its own elevation offset and
+        therefore its own trajectory row (interpolation.py:440-494)."""
+        fan = cls.__new__(cls)
+        n = len(daz)
+        fan.pts_hor = np.asarray(daz, dtype=np.float64)
+        fan.pts_ver = np.asarray(dele, dtype=np.float64)
+        fan.weights = np.asarray(weight, dtype=np.float64)
+        fan.i_hor = np.arange(n, dtype=np.int32)
+        fan.j_ver = np.arange(n, dtype=np.int32)
+        fan.daz, fan.dele, fan.weight = fan.pts_hor, fan.pts_ver, fan.weights
+        fan.n_sub = n
+        fan.center = int(n / 2)
+        return fan
+
+
+def _threshold(weights, fraction):
+    """Smallest weight kept so that the kept ones hold `fraction` of the total (interpolation.py:343-352)."""
+    srt = np.sort(np.asarray(weights).ravel())[::-1]
+    cum = np.cumsum(srt / np.sum(srt))
+    cum[-1] = 1.
+    return srt[np.where(cum >= fraction)[0][0]]
+
+
+def multi_gaussian_fan(config):
+    """Integration scheme 2 (interpolation.py:194-228): an antenna pattern given as a sum of Gaussians
+    (``antenna_params`` rows: amplitude [dB], mean [deg], sigma [deg]) sampled with Gauss-Hermite nodes
+    along the radius and Gauss-Legendre nodes around the beam axis; weight = polar area element times the
+    cosine of the elevation offset.  Offsets are relative to the ray direction."""
+    from numpy.polynomial.legendre import leggauss
+    integ = config['integration']
+    ap = np.atleast_2d(np.asarray(integ['antenna_params'], dtype=np.float64))
+    xa, wa = leggauss(int(integ['na_GL']))
+    xr, wr = hermgauss(int(integ['nr_GH']))
+    amp, mean, sig = 10 ** (0.1 * ap[:, 0]), ap[:, 1], ap[:, 2]
+    # index order of the reference's triple loop: radial node, Gaussian, angular node
+    r = (mean[None, :, None] + np.sqrt(2) * sig[None, :, None] * xr[:, None, None]) * np.ones((1, 1, len(xa)))
+    theta = (np.pi * xa + np.pi)[None, None, :] * np.ones_like(r)
+    w = (np.pi * wa[None, None, :] * wr[:, None, None] * amp[None, :, None] * np.sqrt(2) * sig[None, :, None] * np.abs(r))
+    w = w * np.cos(r * np.sin(theta))
+    r, theta, w = r.ravel(), theta.ravel(), w.ravel()
+    total = 0.0
+    for x in w:                      # the reference accumulates the normalisation sequentially (:216)
+        total += x
+    w = w / total
+    keep = w >= _threshold(w, integ['weight_threshold'])
+    return SubbeamFan.irregular((r * np.cos(theta))[keep], (r * np.sin(theta))[keep], w[keep])
+
+
 def subbeam_fan(config):
     bw = config['radar']['3dB_beamwidth']
+    if config['integration']['scheme'] == 2:
+        return multi_gaussian_fan(config)
     nh, nv = int(config['integration']['nh_GH']), int(config['integration']['nv_GH'])
     if config['integration']['scheme'] != 1:
-        raise NotImplementedError('only integration scheme 1 (Gauss-Hermite) is part of this build (SURVEY.md 8f N3)')
+        raise NotImplementedError('integration schemes 1 (Gauss-Hermite) and 2 (multi-Gaussian antenna) are part of this '
+                                  'build; 3-6 and \'ml\' need antenna diagram files / per-gate weights (SURVEY.md 8f N3)')
     sigma = bw / (2 * np.sqrt(2 * np.log(2)))
     xh, wh = hermgauss(nh)
     xv, wv = hermgauss(nv)

@@ -250,6 +250,38 @@ def gauss_hermite_subbeams(cfg):
     return pts_hor, pts_ver, weights, keep
 
 
+def multi_gaussian_points(cfg, azimuth, elevation):
+    """Integration scheme 2 (interpolation.py:194-228): Gauss-Hermite in the radial and Gauss-Legendre in
+    the angular direction around the beam axis for an antenna pattern given as a sum of Gaussians
+    (antenna_params rows: amplitude [dB], mean, sigma [deg]).  An irregular list of (azimuth, elevation)
+    points; every point has its own refracted trajectory (:440-494)."""
+    from numpy.polynomial.legendre import leggauss
+    nr_GH = int(cfg['integration']['nr_GH'])
+    na_GL = int(cfg['integration']['na_GL'])
+    ap = np.asarray(cfg['integration']['antenna_params'], dtype=np.float64)
+    pts_ang, w_ang = leggauss(na_GL)
+    pts_rad, w_rad = hermgauss(nr_GH)
+    a_dB, mu, sigma = ap[:, 0], ap[:, 1], ap[:, 2]
+    list_pts, weights, sum_weights = [], [], 0
+    for i in range(nr_GH):
+        for j in range(len(sigma)):
+            for k in range(na_GL):
+                r = mu[j] + np.sqrt(2) * sigma[j] * pts_rad[i]
+                theta = np.pi * pts_ang[k] + np.pi
+                weight = (np.pi * w_ang[k] * w_rad[i] * 10 ** (0.1 * a_dB[j]) * np.sqrt(2) * sigma[j] * abs(r))
+                weight *= np.cos(r * np.sin(theta))
+                weights.append(weight)
+                sum_weights += weight
+                list_pts.append([r * np.cos(theta) + azimuth, r * np.sin(theta) + elevation])
+    weights = np.array(weights)
+    weights /= sum_weights
+    w_sort = np.sort(weights.ravel())[::-1]
+    w_cum = np.cumsum(w_sort / np.sum(w_sort))
+    w_cum[-1] = 1.
+    threshold = w_sort[np.where(w_cum >= cfg['integration']['weight_threshold'])[0][0]]
+    return list_pts, weights, weights >= threshold
+
+
 # --------------------------------------------------------------------------- #
 # a2: trajectory (atm_refraction.py:181-220, utilities.py:126-139)
 # --------------------------------------------------------------------------- #
@@ -467,15 +499,53 @@ def melting(sub):
     return sub
 
 
+def _trajectory(cfg, model, rranges, elevation, radar_pos):
+    if cfg['refraction']['scheme'] == 2:
+        N = {'data': model['refractivity'], 'z_levels': model['z_levels'], 'proj': model['proj'],
+             'resolution': model['resolution']}
+        return ref_ode(rranges, elevation, radar_pos, N, cfg['radar'].get('type', 'ground'))
+    return ref_4_3(rranges, elevation, radar_pos)
+
+
+def _irregular_radial(model, names, azimuth, elevation, cfg, rranges, radar_pos, debug):
+    """interpolation.py:440-494: one trajectory per quadrature point."""
+    list_pts, weights, keep = multi_gaussian_points(cfg, azimuth, elevation)
+    subs = []
+    for i, pt in enumerate(list_pts):
+        if not keep[i]:
+            continue
+        s, h, e = _trajectory(cfg, model, rranges, pt[1], radar_pos)
+        r = trilin_interp_radial(model, names, pt[0], s, h, cfg, debug=debug)
+        values = {}
+        for k, bi in enumerate(r[2]):
+            if k == 0:
+                mask = np.zeros(len(bi))
+                mask[bi == -9999] = 1
+                mask[np.isnan(bi)] = -1
+            bi[mask != 0] = np.nan
+            values[names[k]] = bi
+        sub = {'values': values, 'mask': mask, 'lats': r[0], 'lons': r[1], 'dist': s, 'heights': h, 'elev': e,
+               'quad_pt': list(pt), 'quad_weight': weights[i], 'has_melting': False, 'ij': (i, i)}
+        if debug:
+            sub['coords'] = r[3]
+            sub['dbg'] = r[4]
+        if cfg['microphysics']['with_melting']:
+            sub = melting(sub)
+        subs.append(sub)
+    return subs
+
+
 def get_interpolated_radial(model, azimuth, elevation, cfg, debug=False):
     """interpolation.py:91-438 for integration scheme 1, refraction schemes 1 and 2 (the refractivity field is
     model['refractivity'], kept apart from the interpolated variables like the reference's self.N).
     A sub-radial is a dict with the attributes of the reference's Radial
     (radial.py:16-54)."""
     names = list(model['vars'].keys())
-    pts_hor, pts_ver, weights, keep = gauss_hermite_subbeams(cfg)
     rranges = derived_constants(cfg)['RANGE_RADAR']
     radar_pos = cfg['radar']['coords']
+    if cfg['integration']['scheme'] == 2:
+        return _irregular_radial(model, names, azimuth, elevation, cfg, rranges, radar_pos, debug)
+    pts_hor, pts_ver, weights, keep = gauss_hermite_subbeams(cfg)
     if cfg['refraction']['scheme'] == 2:
         N = {'data': model['refractivity'], 'z_levels': model['z_levels'], 'proj': model['proj'],
              'resolution': model['resolution']}

@@ -359,6 +359,12 @@ CASES = {
     'c1mom_melt_dop2': ('1mom', 5.6, dict(radar={'range': 30000, 'radial_resolution': 500}, doppler={'scheme': 2},
                                           microphysics={'with_melting': 1}, integration={'nv_GH': 1, 'nh_GH': 3}),
                         [(220.0, 3.5)], {}),
+    # integration scheme 2 (interpolation.py:194-228, 440-494): irregular (azimuth, elevation) points of a
+    # two-Gaussian antenna pattern (main lobe + first side-lobe ring), one trajectory per point
+    'c1mom_quad2': ('1mom', 5.6, dict(radar={'range': 30000, 'radial_resolution': 1000},
+                                      integration={'scheme': 2, 'nr_GH': 3, 'na_GL': 5, 'weight_threshold': 0.999,
+                                                   'antenna_params': [[0.0, 0.0, 0.4247], [-24.0, 1.6, 0.3]]}),
+                    [(45.0, 3.5), (250.5, 8.5)], {}),
 }
 MELTING_N_E = 8          # elevation bins of the synthetic melting tables (0..14 deg): 78 MB per species
 
@@ -377,12 +383,15 @@ def golden_path(R, name):
     nyq = cfgd['radar'].get('nyquist_velocity')
     if nyq is not None:
         cfgd['radar']['nyquist_velocity'] = (lambda e, a, _v=nyq: _v)
+    if 'antenna_params' in cfgd['integration']:      # interpolation.py:200-204 slices it as an array
+        cfgd['integration']['antenna_params'] = np.asarray(cfgd['integration']['antenna_params'], dtype=float)
     set_config(R, cfgd)
     ref_luts = {h: ref_lut(R, l) for h, l in luts.items()}
     out = {'rays': np.array(rays)}
     per_ray = []
     for az, el in rays:
-        subs = R['interp'].get_interpolated_radial(model, az, el)
+        # the worker passes N = self.N, 0 unless a refractivity field was loaded (radar_operator.py:76, 210, 417)
+        subs = R['interp'].get_interpolated_radial(model, az, el, 0)
         sub_vals = {k: np.stack([np.array(s.values[k], copy=True) for s in subs]) for k in subs[0].values.keys()}
         sub_mask = np.stack([s.mask for s in subs])
         sub_w = np.array([s.quad_weight for s in subs])
@@ -408,7 +417,7 @@ def golden_path(R, name):
         per_ray.append(rec)
     for k in per_ray[0].keys():
         out[k] = np.stack([r[k] for r in per_ray])
-    out['config_json'] = np.array(json.dumps({s: {k: (v if not callable(v) else 'callable') for k, v in d.items()}
+    out['config_json'] = np.array(json.dumps({s: {k: (v.tolist() if isinstance(v, np.ndarray) else v if not callable(v) else 'callable') for k, v in d.items()}
                                               for s, d in cfgd.items()}, default=float))
     out['nyquist'] = np.array(-1.0 if nyq is None else float(nyq))
     out['model_kw_json'] = np.array(json.dumps(kw))

@@ -464,6 +464,35 @@ def test_ode_refraction_scheme_against_oracle():
         op2.get_PPI([1.0], azimuths=[5.])
 
 
+def test_integration_scheme2_irregular_points():
+    """Integration scheme 2 (interpolation.py:194-228, 440-494): an irregular list of
+    (azimuth, elevation) sub-beams, each with its own trajectory row, through the unchanged kernels; against the
+    reference golden and the oracle, integer decisions bit-exact."""
+    from cosmo_pol_b200 import RadarOperator
+    g, cfg, kw = load_golden_case('c1mom_quad2')
+    model, luts = synthetic_inputs('1mom', 5.6, **kw)
+    conf = copy.deepcopy(cfg)
+    conf['radar']['sensitivity'] = [-300, 10000]
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    rays = g['rays']
+    eng = op._prepare_engine(keep_debug=True)
+    out = op.simulate_rays(rays[:, 0], rays[:, 1], keep_debug=True)
+    ref = {k[4:]: g[k] for k in g.files if k.startswith('obs_')}
+    assert_observables_close(out, ref, sz_scale=5e-4 * np.abs(ref['KDP']), what='quad2 golden')
+    assert np.array_equal(out['mask'], g['mask'].astype(np.float32))
+    n_sub = g['sub_w'].shape[1]
+    assert op._engine.stats()['n_subbeam_gates'] == len(rays) * n_sub * out['ZH'].shape[1]
+    dbg = op._engine.debug_indices(op._last_scan)
+    names = dbg['var_names']
+    for k in ('T', 'QR_v', 'U'):
+        assert np.array_equal(dbg['values'][..., names.index(k)], g['sub_' + k].astype(np.float32), equal_nan=True), k
+    pm, pl = plain(model, luts)
+    oref = O.simulate_scan(pm, pl, oracle_cfg(op), rays[:, 0], rays[:, 1], accum='f64', sensitivity_cut=True)
+    assert_observables_close(out, oref, what='quad2 oracle')
+
+
 def test_edge_cases_and_errors():
     from cosmo_pol_b200 import RadarOperator
     from cosmo_pol_b200._abi import RadopError
