@@ -2012,7 +2012,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                             // clip to the axis ends whatever the power law gives (margin 1e-9 >> rounding)
                             if (wh >= S.wh_hi) D = S.d_max;
                             else if (wh <= S.wh_lo) D = S.d_min;
-                            else D = (float)pow(wh * S.inv_alpha, S.inv_beta);
+                            else D = (float)exp2(S.inv_beta * log2(wh * S.inv_alpha));   // pow(): same to 1e-15
                             for (int t = s; t < nsp; ++t) {
                                 if (!(act & (1u << t))) continue;
                                 if (D >= cfg.sp[t].d_max) D = cfg.sp[t].d_max;
@@ -2023,9 +2023,10 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     }
                 }
                 // ---- 2. prefix sums of N(D_k) rcs(D_k) dD over this lane's samples ------------
-                double loc[SPEC_SUB];
+                // local running sums in float32: they are stored as float32 anyway, and a chain is 8 samples long
+                float loc[SPEC_SUB];
 #pragma unroll
-                for (int u = 0; u < SPEC_SUB; ++u) loc[u] = 0.0;
+                for (int u = 0; u < SPEC_SUB; ++u) loc[u] = 0.f;
                 float n0 = rec.p1;
                 const float *Dax = S.aux + lane * cpl;          // diameters of this lane's samples
                 if (S.mode == MODE_ICE1) {
@@ -2046,8 +2047,8 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                             const int ad = (u * sub + ii) * 32 + lane;
                             const float phi = fmaf(s_auxp[ad], E2[u], E1[u]);
                             mass = fmaf(s_colm[ad], phi, mass);
-                            loc[u] += (double)(s_col0[ad] * phi);
-                            s_C[ad] = (float)loc[u];
+                            loc[u] = fmaf(s_col0[ad], phi, loc[u]);
+                            s_C[ad] = loc[u];
                             E1[u] *= r1; E2[u] *= r2;
                         }
                     }
@@ -2064,8 +2065,8 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
 #pragma unroll
                         for (int u = 0; u < SPEC_SUB; ++u) {
                             const int ad = (u * sub + ii) * 32 + lane;
-                            loc[u] += (double)(s_col0[ad] * E[u]);
-                            s_C[ad] = (float)loc[u];
+                            loc[u] = fmaf(s_col0[ad], E[u], loc[u]);
+                            s_C[ad] = loc[u];
                             E[u] *= r;
                         }
                     }
@@ -2075,13 +2076,13 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
 #pragma unroll
                         for (int u = 0; u < SPEC_SUB; ++u) {
                             const int ad = (u * sub + ii) * 32 + lane;
-                            loc[u] += (double)(s_col0[ad] * ex2f_approx(a * s_auxp[ad]));
-                            s_C[ad] = (float)loc[u];
+                            loc[u] = fmaf(s_col0[ad], ex2f_approx(a * s_auxp[ad]), loc[u]);
+                            s_C[ad] = loc[u];
                         }
                     }
                 }
                 {   // exclusive scan of the lane totals, then the bases of the four chains
-                    const double tot = (loc[0] + loc[1]) + (loc[2] + loc[3]);
+                    const double tot = ((double)loc[0] + (double)loc[1]) + ((double)loc[2] + (double)loc[3]);
                     double x = tot;
 #pragma unroll
                     for (int d = 1; d < 32; d <<= 1) {
@@ -2091,7 +2092,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     const double prev = __shfl_up_sync(0xffffffffu, x, 1);
                     double bs = lane ? prev : 0.0;
 #pragma unroll
-                    for (int u = 0; u < SPEC_SUB; ++u) { s_base[lane * SPEC_SUB + u] = bs; bs += loc[u]; }
+                    for (int u = 0; u < SPEC_SUB; ++u) { s_base[lane * SPEC_SUB + u] = bs; bs += (double)loc[u]; }
                 }
                 __syncwarp();
                 // ---- 3. velocity bins -----------------------------------------------------------
