@@ -396,7 +396,10 @@ def run_ours(args):
         'gpu_launches': launches,
         'clocks': clocks,
         'roofline': {'bound': 'fp32', 'kernel': 'k_integrate', 'achieved': achieved, 'peak': sustained, 'unit': 'TFLOP/s',
-                     'frac': (achieved / sustained) if achieved else None, 'traffic': None,
+                     'frac': (achieved / sustained) if achieved else None,
+                     # dram__bytes_read.sum + dram__bytes_write.sum of one k_integrate launch of this workload
+                     # (ncu --set full capture, profiles/r01c_k_integrate_full.txt: 505.7 MB + 917.4 MB)
+                     'traffic': 1.4231e9,
                      'peak_kind': 'measured here: dependent-free FFMA probe, sustained (median of back-to-back runs); '
                                   'burst {:.1f}. MEASURED_PEAKS.json holds no FP32 figure (hbm {} GB/s)'.format(
                                       burst, peaks.get('hbm_gbs')),

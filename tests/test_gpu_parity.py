@@ -641,3 +641,48 @@ def test_full_size_volume_properties():
     assert np.array_equal(np.isnan(got['RVEL']), ~ok)
     assert np.max(np.abs(got['RVEL'][ok] - ref['RVEL'][ok])) < 2e-3
     op.close()
+
+
+def test_full_size_rhi_dense_quadrature():
+    """BASELINE.json configuration 4 at its full size: RHI 0..90 deg, 29 x 29 Gauss-Hermite sub-beams
+    (841 per ray, 3.8e7 sub-beam gates), attenuation on -- the sub-beam reduction and the along-ray scans
+    under load.  Determinism, shard consistency, chunk invariance, and oracle parity on one ray."""
+    import bench
+    from cosmo_pol_b200 import RadarOperator
+    model, luts = bench.build_inputs()
+    conf = bench.volume_config()
+    conf['integration'].update({'nh_GH': 29, 'nv_GH': 29})
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    ray_az, ray_el = np.full(91, 0.0), np.arange(91.)
+    keys = ('ZH', 'ZV', 'ZDR', 'KDP', 'PHIDP', 'RHOHV', 'ATT_H', 'ATT_V', 'RVEL', 'DELTA_HV', 'mask', 'lat', 'lon')
+    a = {k: v.copy() for k, v in op.simulate_rays(ray_az, ray_el).items()}
+    st = op._engine.stats()
+    assert st['n_subbeam_gates'] == 91 * 841 * 500
+    b = op.simulate_rays(ray_az, ray_el)
+    for k in keys:
+        assert np.array_equal(a[k], b[k], equal_nan=True), 'non deterministic ' + k
+    d0 = {k: v.copy() for k, v in op.simulate_rays(ray_az[:40], ray_el[:40]).items()}
+    d1 = op.simulate_rays(ray_az[40:], ray_el[40:])
+    for k in keys:
+        assert np.array_equal(np.concatenate([d0[k], d1[k]]), a[k], equal_nan=True), 'sharding changes ' + k
+    op._engine.set_chunk(3000000)
+    c = op.simulate_rays(ray_az, ray_el)
+    for k in keys:
+        assert np.array_equal(c[k], a[k], equal_nan=True), 'chunking changes ' + k
+    op._engine.set_chunk(8000000)
+    # PHIDP is an inclusive cumulative sum of 2 KDP dr + DELTA_HV (doppler_scatter.py:406-409)
+    kdp = np.nan_to_num(a['KDP'].astype(np.float64))
+    phi = np.cumsum(2 * kdp, axis=1) * 0.3 + a['DELTA_HV']
+    ok = np.isfinite(a['PHIDP'])
+    assert np.max(np.abs(phi[ok] - a['PHIDP'][ok]) / (np.abs(a['PHIDP'][ok]) + 1e-2)) < 1e-3
+    pick = np.array([12])
+    pm, pl = plain(model, luts)
+    ref = O.simulate_scan(pm, pl, oracle_cfg(op), ray_az[pick], ray_el[pick], accum='f64', sensitivity_cut=True)
+    got = {k: a[k][pick] for k in a}
+    assert_observables_close(got, ref, what='cfg4 ray')
+    ok = np.isfinite(ref['RVEL'])
+    assert np.array_equal(np.isnan(got['RVEL']), ~ok)
+    assert np.max(np.abs(got['RVEL'][ok] - ref['RVEL'][ok])) < 2e-3
+    op.close()
