@@ -268,6 +268,9 @@ def run_ours(args):
         raise SystemExit('bench.py needs a CUDA GPU: the hot path has no CPU fallback (use --impl reference for the CPU arm)')
     torch.cuda.set_device(local)
     if world > 1:
+        # the gather runs beside persistent kernels that fill every SM: a few NCCL CTAs are enough to move
+        # 158 MB per peer within a step and leave the SMs to the kernels
+        os.environ.setdefault('NCCL_MAX_CTAS', '8')
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     quiet = open(os.devnull, 'w')
     stdout, sys.stdout = sys.stdout, quiet            # the host layer prints like the reference does

@@ -696,8 +696,18 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
     const int ng = cfg.n_gates;
     const float qnan = __int_as_float(0x7fc00000);
 
-    for (long long base = (long long)blockIdx.x * blockDim.x; base < n_sbg; base += (long long)gridDim.x * blockDim.x) {
-        const long long sbg = base + tid;
+    // Work is handed out per warp in pieces of 128 consecutive sub-beam gates from a global counter
+    // (o.flags[3]): warps that start late (an NCCL kernel holding the SM, a slow neighbour) simply
+    // take fewer pieces, and the kernel ends when the last piece does.
+    const long long n_pieces = (n_sbg + 127) / 128;
+    for (;;) {
+      long long piece = 0;
+      if (lane == 0) piece = (long long)atomicAdd(o.flags + 3, 1);
+      piece = __shfl_sync(0xffffffffu, piece, 0);
+      if (piece >= n_pieces) break;
+#pragma unroll 1
+      for (int part = 0; part < 4; ++part) {
+        const long long sbg = piece * 128 + part * 32 + (long long)lane;
         uint32_t keys[RADOP_NSPECIES_MAX];
 #pragma unroll
         for (int s = 0; s < RADOP_NSPECIES_MAX; ++s) keys[s] = RADOP_KEY_NONE;
@@ -920,6 +930,7 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
             const unsigned peers = __match_any_sync(0xffffffffu, key);
             if (key != RADOP_KEY_NONE && lane == (unsigned)(__ffs(peers) - 1)) atomicAdd(&s_hist[key], __popc(peers));
         }
+      }
     }
     __syncthreads();
     for (int b = tid; b < cfg.total_bins; b += blockDim.x) {
