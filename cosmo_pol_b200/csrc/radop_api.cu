@@ -568,8 +568,26 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     }
     if (!c.keep_debug && target > 0)
         n_chunks = (int)std::min<long long>(n_rays, std::max<long long>(1, (h->n_sbg + target / 2) / target));
-    const int rays_per_chunk = (n_rays + n_chunks - 1) / n_chunks;
-    n_chunks = (n_rays + rays_per_chunk - 1) / rays_per_chunk;
+    // Chunk boundaries.  With host copies to overlap (radop_simulate) the chunks shrink linearly towards
+    // the end: the copy of the last chunk is the only one nothing can hide, so it should be short.
+    std::vector<int> chunk_r0(1, 0);
+    {
+        const int even = (n_rays + n_chunks - 1) / n_chunks;
+        if (out && n_chunks >= 3) {
+            const double unit = (double)n_rays / ((double)n_chunks * n_chunks);     // sum of (2 (n - i) - 1) = n^2
+            int r = 0;
+            for (int i = 0; i < n_chunks - 1 && r < n_rays; ++i) {
+                r = std::min(n_rays, r + std::max(1, (int)(unit * (2 * (n_chunks - i) - 1) + 0.5)));
+                if (r < n_rays) chunk_r0.push_back(r);
+            }
+        } else {
+            for (int r = even; r < n_rays; r += even) chunk_r0.push_back(r);
+        }
+        n_chunks = (int)chunk_r0.size();
+        chunk_r0.push_back(n_rays);
+    }
+    int rays_per_chunk = 1;            // rays of the largest chunk: the work memory is sized for it
+    for (int i = 0; i < n_chunks; ++i) rays_per_chunk = std::max(rays_per_chunk, chunk_r0[i + 1] - chunk_r0[i]);
     const long long n = (long long)rays_per_chunk * per_ray;          // sub-beam gates of the largest chunk
     const size_t c_rg = (size_t)rays_per_chunk * ng;
     if (n * nsp >= 0x7fffffffLL || n >= 0xfffffff0LL)
@@ -662,7 +680,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     c.out_stride = (long long)n_rg;
 
     for (int ch = 0; ch < n_chunks; ++ch) {
-        const int r0 = ch * rays_per_chunk, nr = std::min(rays_per_chunk, n_rays - r0);
+        const int r0 = chunk_r0[ch], nr = chunk_r0[ch + 1] - r0;
         c.n_rays = nr;
         const long long nc = (long long)nr * per_ray;
         const size_t cc_rg = (size_t)nr * ng, off_rg = (size_t)r0 * ng;
