@@ -71,6 +71,7 @@ struct RadopHandle_ {
     bool have_scan = false, executed = false;
     int n_rays = 0, n_sub = 0, n_traj = 0, n_vert = 0, center_sub = 0;
     bool have_nyquist = false;
+    size_t overlap_min_bytes = (size_t)32 << 20;   // radop_simulate chunks the scan only above this output size
     long long n_sbg = 0;
     void *pinned = nullptr;
     size_t pinned_cap = 0;
@@ -560,7 +561,19 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     const long long per_ray = (long long)c.n_sub * ng;
     int n_chunks = 1;
     // without host copies to overlap, chunks only bound the work memory (8x larger chunks)
-    long long target = out ? h->chunk_sbg : 8 * h->chunk_sbg;
+    // bytes radop_simulate copies back: chunking only pays when there is a copy worth hiding (every chunk
+    // costs a pass over the bin table and partial tiles; a dense-quadrature RHI returns 2 MB for 2e7 gates)
+    size_t d2h_bytes = 0;
+    if (out) {
+        for (int v = 0; v < RADOP_N_OUT; ++v) if (out->obs[v]) d2h_bytes += n_rg * 4;
+        if (out->mask) d2h_bytes += n_rg * 4;
+        if (out->lat) d2h_bytes += n_rg * 8;
+        if (out->lon) d2h_bytes += n_rg * 8;
+        if (out->dspectrum) d2h_bytes += n_rg * (size_t)c.n_vel * 4;
+        for (int v = 0; v < RADOP_NVAR_MAX; ++v) if (out->model[v]) d2h_bytes += n_rg * 4;
+    }
+    const bool overlap_copies = out && d2h_bytes >= h->overlap_min_bytes;
+    long long target = overlap_copies ? h->chunk_sbg : 8 * h->chunk_sbg;
     if (c.brd_mode) {
         // the sub-beam spectra of a chunk are kept in float64: at most ~4 GB of them
         const long long cap = std::max<long long>(per_ray, (4LL << 30) / ((long long)c.n_vel * 8));
@@ -573,7 +586,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     std::vector<int> chunk_r0(1, 0);
     {
         const int even = (n_rays + n_chunks - 1) / n_chunks;
-        if (out && n_chunks >= 3) {
+        if (overlap_copies && n_chunks >= 3) {
             const double unit = (double)n_rays / ((double)n_chunks * n_chunks);     // sum of (2 (n - i) - 1) = n^2
             int r = 0;
             for (int i = 0; i < n_chunks - 1 && r < n_rays; ++i) {
@@ -920,6 +933,13 @@ int radop_set_chunk(RadopHandle *h, int64_t subbeam_gates_per_chunk)
 {
     if (!h) return RADOP_ERR_ARG;
     h->chunk_sbg = subbeam_gates_per_chunk;
+    return RADOP_OK;
+}
+
+int radop_set_overlap_threshold(RadopHandle *h, int64_t min_output_bytes)
+{
+    if (!h || min_output_bytes < 0) return RADOP_ERR_ARG;
+    h->overlap_min_bytes = (size_t)min_output_bytes;
     return RADOP_OK;
 }
 

@@ -211,6 +211,10 @@ int radop_synchronize(RadopHandle *h);
  * chunk): work memory is sized for one chunk and, in radop_simulate, the device -> host copies
  * of a chunk overlap the kernels of the next one.  Results do not depend on the chunking. */
 int radop_set_chunk(RadopHandle *h, int64_t subbeam_gates_per_chunk);
+/* radop_simulate splits the scan into chunks only when the requested outputs are at least this large
+ * (default 32 MiB): every chunk costs a pass over the bin table and partial tiles, which only pays when
+ * there is a device -> host copy to hide.  0 = always chunk (used by the chunk-invariance tests). */
+int radop_set_overlap_threshold(RadopHandle *h, int64_t min_output_bytes);
 
 /* Device-resident results of the last radop_execute (for NCCL gathers): pointer to
  * float32 [RADOP_N_OUT + 1][n_rays][n_gates] (observables then mask). */

@@ -560,6 +560,7 @@ def test_scan_level_properties():
     for k in keys:
         assert np.array_equal(np.concatenate([d0[k], d1[k]]), a[k], equal_nan=True), 'sharding changes ' + k
     # chunked execution (work memory per chunk, copies overlapped with the next chunk): same bits
+    op._engine.set_overlap_threshold(0)       # chunk however small the outputs are
     for chunk in (0, 100000, 37 * 9 * 160):
         op._engine.set_chunk(chunk)
         f = op.simulate_rays(ray_az, ray_el)
@@ -670,6 +671,7 @@ def test_full_size_rhi_dense_quadrature():
     d1 = op.simulate_rays(ray_az[40:], ray_el[40:])
     for k in keys:
         assert np.array_equal(np.concatenate([d0[k], d1[k]]), a[k], equal_nan=True), 'sharding changes ' + k
+    op._engine.set_overlap_threshold(0)
     op._engine.set_chunk(3000000)
     c = op.simulate_rays(ray_az, ray_el)
     for k in keys:
