@@ -686,3 +686,39 @@ def test_full_size_rhi_dense_quadrature():
     assert np.array_equal(np.isnan(got['RVEL']), ~ok)
     assert np.max(np.abs(got['RVEL'][ok] - ref['RVEL'][ok])) < 2e-3
     op.close()
+
+
+@pytest.mark.parametrize('scheme,freq', [('1mom', 5.6), ('2mom', 9.41)])
+def test_full_size_ppi(scheme, freq):
+    """BASELINE.json configurations 1 and 2 at their full size (PPI at 1 deg, 360 rays x 500 gates x 3x3
+    sub-beams; C-band one-moment, X-band two-moment with hail): determinism, ray-order invariance and
+    oracle parity on rays drawn from the sweep."""
+    import bench
+    from cosmo_pol_b200 import RadarOperator
+    model, luts = bench.build_inputs(scheme, freq)
+    conf = bench.volume_config()
+    conf['radar']['frequency'] = freq
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    ray_az, ray_el = np.arange(360.), np.full(360, 1.0)
+    keys = ('ZH', 'ZV', 'ZDR', 'KDP', 'PHIDP', 'RHOHV', 'ATT_H', 'ATT_V', 'RVEL', 'DELTA_HV', 'mask', 'lat', 'lon')
+    a = {k: v.copy() for k, v in op.simulate_rays(ray_az, ray_el).items()}
+    st = op._engine.stats()
+    assert st['n_subbeam_gates'] == 360 * 9 * 500
+    assert op._engine.species_order == (['R', 'S', 'G', 'I'] if scheme == '1mom' else ['R', 'S', 'G', 'H', 'I'])
+    b = op.simulate_rays(ray_az, ray_el)
+    perm = np.random.default_rng(9).permutation(360)
+    c = op.simulate_rays(ray_az[perm], ray_el[perm])
+    for k in keys:
+        assert np.array_equal(a[k], b[k], equal_nan=True), 'non deterministic ' + k
+        assert np.array_equal(c[k], a[k][perm], equal_nan=True), 'ray order matters for ' + k
+    pick = np.array([3, 121, 288])
+    pm, pl = plain(model, luts)
+    ref = O.simulate_scan(pm, pl, oracle_cfg(op), ray_az[pick], ray_el[pick], accum='f64', sensitivity_cut=True)
+    got = {k: a[k][pick] for k in a}
+    assert_observables_close(got, ref, what='full-size PPI ' + scheme)
+    ok = np.isfinite(ref['RVEL'])
+    assert np.array_equal(np.isnan(got['RVEL']), ~ok)
+    assert np.max(np.abs(got['RVEL'][ok] - ref['RVEL'][ok])) < 2e-3
+    op.close()
