@@ -620,6 +620,19 @@ struct K1Out {
     double *dbg_rot;
 };
 
+// Logarithm and exponential of the one-moment PSD parameter algebra in float32 accuracy: the parameters end
+// up as float32 (lambda, N0) and only have to be good to ~1e-6 (0.01 dB = 2.3e-3), so the double-precision
+// library calls (~60 instructions each) are replaced by the single-precision ones.  The two-moment scheme
+// keeps the double calls: its KDP has gates where species cancel to 1e-3 of their size.  exp splits its
+// argument into a float32 part and the tiny remainder, so the result carries expf's 1 ulp, not the
+// rounding of a large argument.
+__device__ __forceinline__ double log_sp(float x) { return (double)logf(x); }
+__device__ __forceinline__ double exp_sp(double x)
+{
+    const float hi = (float)x;
+    return (double)expf(hi) * (1.0 + (x - (double)hi));
+}
+
 // log of the second moment of Field et al. (2005), hydrometeors.py:1277-1299 with n = 3:
 // log Q2 = (log QM' - ln10 * A(T)) / B(T)
 __device__ __forceinline__ double ice_log_mom2(double T, double logQM)
@@ -819,7 +832,7 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                         if (o.dbg_e) { o.dbg_e[sbg * cfg.n_species + s] = ie; o.dbg_t[sbg * cfg.n_species + s] = it; }
                         continue;
                     }
-                    const double lQM = log((double)QMf);
+                    const double lQM = (S.psd == RADOP_PSD_2MOM) ? log((double)QMf) : log_sp(QMf);
                     double loglam, logn0 = 0.0, n0 = S.N0, ntot_2m = 0.0;
                     bool n0_from_log = false, n0_negative = false;
                     float p0, p1;
@@ -847,8 +860,9 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                         n0_negative = (S.c_q * QN) < 0.0;
                         loglam = ll0 - S.c_kb;
                     }
-                    const double lam = exp(loglam);
-                    if (n0_from_log) n0 = n0_negative ? -exp(logn0) : exp(logn0);
+                    const bool two = S.psd == RADOP_PSD_2MOM;     // N0 spans 20 orders of magnitude there: full double
+                    const double lam = two ? exp(loglam) : exp_sp(loglam);
+                    if (n0_from_log) n0 = two ? (n0_negative ? -exp(logn0) : exp(logn0)) : exp_sp(logn0);
                     if (S.psd == RADOP_PSD_1MOM_ICE) { p0 = (float)lam; p1 = QMf; }     // lambda / 1000, QM
                     else { p0 = (float)lam; p1 = (float)n0; }
                     const int ie = lut_bin(e, S.e_min, S.e_step, S.e_rstep, S.ne);
@@ -859,8 +873,8 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                     if (o.dbg_e) { o.dbg_e[sbg * cfg.n_species + s] = ie; o.dbg_t[sbg * cfg.n_species + s] = it; }
                     if (cfg.doppler_scheme == 1 && !S.numeric_vn) {
                         // _Hydrometeor.integrate_V, hydrometeors.py:178-199
-                        const double v = S.c_v * n0 * exp(S.e_v * loglam);
-                        const double n = (S.psd == RADOP_PSD_2MOM) ? ntot_2m : S.c_n * n0 * exp(S.e_n * loglam);
+                        const double v = S.c_v * n0 * (two ? exp(S.e_v * loglam) : exp_sp(S.e_v * loglam));
+                        const double n = (S.psd == RADOP_PSD_2MOM) ? ntot_2m : S.c_n * n0 * exp_sp(S.e_n * loglam);
                         vsum += (float)v;
                         nsum += (float)n;
                     }
