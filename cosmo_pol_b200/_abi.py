@@ -24,7 +24,8 @@ EXPORTS = ['radop_abi_version', 'radop_create', 'radop_destroy', 'radop_last_err
            'radop_upload_grid', 'radop_upload_field', 'radop_upload_lut', 'radop_simulate', 'radop_stage_scan',
            'radop_execute', 'radop_fetch', 'radop_synchronize', 'radop_device_outputs', 'radop_get_stream',
            'radop_get_stats', 'radop_enable_timing', 'radop_debug_indices', 'radop_measure_fp32_peak',
-           'radop_get_all_radar_pts', 'radop_selftest_division', 'radop_set_chunk', 'radop_set_overlap_threshold']
+           'radop_get_all_radar_pts', 'radop_selftest_division', 'radop_set_chunk', 'radop_set_overlap_threshold',
+           'radop_set_geodesy', 'radop_get_geodesy']
 
 (RADOP_OK, RADOP_ERR_CUDA, RADOP_ERR_ARG, RADOP_ERR_OUT_OF_DOMAIN, RADOP_ERR_LUT, RADOP_ERR_STATE,
  RADOP_ERR_UNSUPPORTED) = range(7)
@@ -115,6 +116,8 @@ def load_library():
     lib.radop_measure_fp32_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
     lib.radop_set_chunk.argtypes = [C.c_void_p, C.c_int64]
     lib.radop_set_overlap_threshold.argtypes = [C.c_void_p, C.c_int64]
+    lib.radop_set_geodesy.argtypes = [C.c_void_p, C.c_int]
+    lib.radop_get_geodesy.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
     lib.radop_selftest_division.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.radop_get_all_radar_pts.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -407,6 +410,15 @@ class Engine(object):
 
     def set_chunk(self, subbeam_gates_per_chunk):
         self._check(self.lib.radop_set_chunk(self.h, C.c_int64(int(subbeam_gates_per_chunk))))
+
+    def set_geodesy(self, mode):
+        """0: per sub-beam polynomials (default; per-gate solution when they do not converge), 1: per gate."""
+        self._check(self.lib.radop_set_geodesy(self.h, C.c_int(int(mode))))
+
+    def geodesy_used_polynomials(self):
+        v = C.c_int(0)
+        self._check(self.lib.radop_get_geodesy(self.h, C.byref(v)))
+        return bool(v.value)
 
     def set_overlap_threshold(self, min_output_bytes):
         """simulate() chunks the scan only when the outputs are at least this large (0: always)."""

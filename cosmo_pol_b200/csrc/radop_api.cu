@@ -79,6 +79,10 @@ struct RadopHandle_ {
     ScanDev scan;
     const float *d_nyquist = nullptr;
     // work buffers
+    DevBuf geo_poly;
+    int geodesy_mode = 0;        // 0: per sub-beam polynomials (per-gate solution when they do not converge), 1: per gate
+    bool geo_poly_ok = false, geo_poly_launched = false, geo_poly_used = false;
+    double geo_mid = 0.0, geo_half = 1.0;
     DevBuf geo, mask, active, wind, sinth, vsum, nsum, key, p0, p1, vals, lat, lon, hist, flags;
     DevBuf bin_start, tile_start, cost_start, cursor, totals, rec, sz_out, ice_vn, dop_vn, ice_tot, comb, out, model_out;
     DevBuf d3_uh, d3_w, d3_rho, d3_st, attw, spec_acc, spec_out, d3_std, sub_acc, brd_flag;
@@ -158,7 +162,7 @@ int radop_destroy(RadopHandle *h)
     if (!h) return RADOP_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    DevBuf *bufs[] = {&h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
+    DevBuf *bufs[] = {&h->geo_poly, &h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
                       &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
                       &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
                       &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_st, &h->attw, &h->spec_acc, &h->spec_out, &h->d3_std, &h->sub_acc, &h->brd_flag, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
@@ -387,6 +391,19 @@ int radop_stage_scan(RadopHandle *h, const RadopScan *sc)
     memcpy(P + o_jv, sc->sub_jv, (size_t)sc->n_sub * 4);
     memcpy(P + o_w, sc->sub_weight, (size_t)sc->n_sub * 8);
     memcpy(P + o_s, sc->traj_s, ntr * 4);
+    {   // ground-distance range of the scan: interval of the geodesy polynomials (k_sub_geopoly)
+        float lo = sc->traj_s[0], hi = sc->traj_s[0];
+        bool finite = true;
+        for (size_t i = 0; i < ntr; ++i) {
+            const float v = sc->traj_s[i];
+            if (!(v - v == 0.f)) finite = false;
+            lo = std::min(lo, v); hi = std::max(hi, v);
+        }
+        h->geo_mid = 0.5 * ((double)lo + (double)hi);
+        h->geo_half = std::max(0.5 * ((double)hi - (double)lo), 1.0);
+        // 0.05 rad of arc (~320 km): beyond that the truncated series is not trusted a priori
+        h->geo_poly_ok = finite && (h->geo_half * 2.0 <= 0.05 * 6.371e6) && std::fabs(h->geo_mid) <= 0.05 * 6.371e6;
+    }
     memcpy(P + o_h, sc->traj_h, ntr * 4);
     memcpy(P + o_e, sc->traj_e, ntr * 4);
     if (have_trig) { memcpy(P + o_sin, sc->traj_sin, ntr * 4); memcpy(P + o_tan, sc->traj_tan, ntr * 4); }
@@ -606,6 +623,8 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     if (n * nsp >= 0x7fffffffLL || n >= 0xfffffff0LL)
         return h->fail(RADOP_ERR_ARG, "chunk too large (rays x sub-beams x gates x species >= 2^31): lower the chunk size");
     CU(h, h->geo.reserve((size_t)rays_per_chunk * c.n_sub * sizeof(SubGeo)));
+    if (h->geodesy_mode == 0 && h->geo_poly_ok) CU(h, h->geo_poly.reserve((size_t)rays_per_chunk * c.n_sub * sizeof(SubPoly)));
+    c.geo_mid = h->geo_mid; c.geo_rhalf = 1.0 / h->geo_half;
     CU(h, h->mask.reserve(n));
     CU(h, h->active.reserve(n));
     CU(h, h->wind.reserve(n * 4));
@@ -658,7 +677,8 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     static bool attr_done[64] = {false};
     if (!attr_done[h->device & 63]) {
         CU(h, cudaFuncSetAttribute(k_integrate, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        CU(h, cudaFuncSetAttribute(k_interp_psd, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(h, cudaFuncSetAttribute(k_interp_psd<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(h, cudaFuncSetAttribute(k_interp_psd<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_scatter_pairs, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_spectrum, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_beam_attenuation, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -670,7 +690,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     h->k2_blocks = std::max(1, occ) * h->n_sm;
     const size_t hist_smem = (size_t)c.total_bins * 4;
     int occ1 = 1;
-    CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, k_interp_psd, 128, hist_smem));
+    CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, k_interp_psd<true>, 128, hist_smem));
     const size_t smem_a = (size_t)4 * 2 * ng * 4;
     const size_t smem_b = (size_t)4 * ((size_t)BRD_WMAX * 8 + (size_t)((std::max(c.n_vel, 1) + 1) & ~1) * 8);
     int occ4 = 1;
@@ -735,11 +755,24 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         }
         {
             const int n_rq = nr * c.n_sub;
-            k_sub_geometry<<<(n_rq + 127) / 128, 128, 0, st>>>(nr, c.n_sub, c.radar_lat, scan.ray_az, scan.sub_daz, h->geo.as<SubGeo>());
-            CU(h, cudaGetLastError()); ++launches;
             const long long want = (nc + 127) / 128;
             const unsigned grid1 = (unsigned)std::min<long long>(want, (long long)std::max(1, occ1) * h->n_sm);
-            k_interp_psd<<<grid1, 128, hist_smem, st>>>(c, scan, h->geo.as<SubGeo>(), h->z_t.as<float>(), h->fields.as<float>(), o, nc);
+            const float *zt = h->z_t.as<float>(), *fl = h->fields.as<float>();
+            const bool poly = h->geodesy_mode == 0 && h->geo_poly_ok;
+            h->geo_poly_launched = poly;
+            k_sub_geometry<<<(n_rq + 127) / 128, 128, 0, st>>>(nr, c.n_sub, c.radar_lat, scan.ray_az, scan.sub_daz, h->geo.as<SubGeo>());
+            CU(h, cudaGetLastError()); ++launches;
+            if (poly) {
+                // per sub-beam polynomials of the rotated-pole coordinates; a sub-beam whose series does not
+                // converge raises flag bit 2 and the per-gate instance does the work instead (both are launched,
+                // the one that is not wanted returns at once)
+                k_sub_geopoly<<<(n_rq + 7) / 8, 128, 0, st>>>(c, nr, h->geo_mid, h->geo_half, scan.ray_az, scan.sub_daz,
+                                                               h->geo_poly.as<SubPoly>(), h->flags.as<int>());
+                CU(h, cudaGetLastError()); ++launches;
+                k_interp_psd<true><<<grid1, 128, hist_smem, st>>>(c, scan, h->geo_poly.p, zt, fl, o, nc, 1);
+                CU(h, cudaGetLastError()); ++launches;
+            }
+            k_interp_psd<false><<<grid1, 128, hist_smem, st>>>(c, scan, h->geo.p, zt, fl, o, nc, poly ? 1 : 0);
             CU(h, cudaGetLastError()); ++launches;
         }
         if (ev) CU(h, cudaEventRecord(ev[1], st));
@@ -899,6 +932,7 @@ static int finish(RadopHandle *h)
         h->stats.exec_flop_per_pair[s] = per_d * S.nd;
     }
     average_timings(h);
+    h->geo_poly_used = h->geo_poly_launched && !(flags[0] & 4);
     if (flags[0] & 1)
         return h->fail(RADOP_ERR_OUT_OF_DOMAIN, "radar domain is not entirely contained in the model domain");
     return RADOP_OK;
@@ -940,6 +974,20 @@ int radop_set_overlap_threshold(RadopHandle *h, int64_t min_output_bytes)
 {
     if (!h || min_output_bytes < 0) return RADOP_ERR_ARG;
     h->overlap_min_bytes = (size_t)min_output_bytes;
+    return RADOP_OK;
+}
+
+int radop_set_geodesy(RadopHandle *h, int mode)
+{
+    if (!h || (mode != 0 && mode != 1)) return RADOP_ERR_ARG;
+    h->geodesy_mode = mode;
+    return RADOP_OK;
+}
+
+int radop_get_geodesy(RadopHandle *h, int *used_polynomials)
+{
+    if (!h || !used_polynomials) return RADOP_ERR_ARG;
+    *used_polynomials = h->geo_poly_used ? 1 : 0;
     return RADOP_OK;
 }
 

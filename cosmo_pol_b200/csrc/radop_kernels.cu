@@ -299,6 +299,111 @@ __device__ __forceinline__ void rotate_pole(const double *__restrict__ R, double
 }
 
 // ------------------------------------------------------------------------------------------
+// Geodesy by polynomial: along one sub-beam the azimuth is fixed and the rotated-pole coordinates
+// are analytic functions of the ground distance s alone.  The arc a radar ray covers is a few
+// hundredths of a radian, so their Chebyshev series on [s_min, s_max] of the scan converges
+// geometrically (each coefficient ~ 0.01 x the previous one): the Vincenty solution + rotation is
+// evaluated at GEO_NP Chebyshev nodes per (ray, sub-beam) instead of at every gate, the series is
+// truncated after GEO_NC terms (the dropped ones are checked to be below 1e-13 degrees, else flag
+// bit 2 and the scan is refused) and converted to the power basis, and a gate costs one Horner
+// evaluation per coordinate.  The difference to the per-gate solution is ~1e-14 degrees, the
+// rounding level of the per-gate solution itself (tests/test_gpu_parity.py::test_geodesy_polynomial).
+// ------------------------------------------------------------------------------------------
+#define GEO_NP 16
+#define GEO_NC 12
+struct __align__(16) SubPoly {
+    double sinA1, cosA1;
+    double c[4][GEO_NC];     // rlat, rlon, lat, lon (degrees) as polynomials in x = (s - geo_mid) * geo_rhalf
+};
+
+__device__ __forceinline__ double poly_eval(const double2 *__restrict__ c, double x)
+{   // coefficients in ascending order, GEO_NC / 2 double2
+    double2 t = __ldg(c + GEO_NC / 2 - 1);
+    double r = fma(t.y, x, t.x);
+#pragma unroll
+    for (int k = GEO_NC / 2 - 2; k >= 0; --k) {
+        t = __ldg(c + k);
+        r = fma(r, x, t.y);
+        r = fma(r, x, t.x);
+    }
+    return r;
+}
+
+// block = 128 threads = 8 sub-beams x 16 nodes
+__global__ void __launch_bounds__(128)
+k_sub_geopoly(const __grid_constant__ DevConfig cfg, int n_rays, double s_mid, double s_half,
+              const double *__restrict__ ray_az, const double *__restrict__ sub_daz, SubPoly *__restrict__ out, int *flags)
+{
+    const int n_sub = cfg.n_sub;
+    const double lat0_deg = cfg.radar_lat, lon0_deg = cfg.radar_lon, cl0 = cfg.cos_lon0, sl0 = cfg.sin_lon0;
+    const double *rot = cfg.rot;
+    __shared__ double s_f[8][4][GEO_NP];
+    __shared__ double s_a[8][4][GEO_NP];
+    const int sub_l = threadIdx.x >> 4, j = threadIdx.x & 15;
+    const int i = blockIdx.x * 8 + sub_l;
+    const bool ok = i < n_rays * n_sub;
+    const double f = WGS84_F, a = WGS84_A, b = (1.0 - f) * a;
+    SubGeo k;
+    if (ok) {
+        double az = ray_az[i / n_sub] + sub_daz[i % n_sub];
+        double phi1 = lat0_deg * DEG2RAD, alpha1 = az * DEG2RAD;
+        sincos(alpha1, &k.sinA1, &k.cosA1);
+        double tanU1 = (1.0 - f) * tan(phi1);
+        k.cosU1 = 1.0 / sqrt(1.0 + tanU1 * tanU1);
+        k.sinU1 = tanU1 * k.cosU1;
+        double sigma1 = atan2(tanU1, k.cosA1);
+        sincos(2.0 * sigma1, &k.s2s1, &k.c2s1);
+        k.sinAlpha = k.cosU1 * k.sinA1;
+        double cosSqAlpha = 1.0 - k.sinAlpha * k.sinAlpha;
+        double uSq = cosSqAlpha * (a * a - b * b) / (b * b);
+        double A = 1.0 + uSq / 16384.0 * (4096.0 + uSq * (-768.0 + uSq * (320.0 - 175.0 * uSq)));
+        k.B = uSq / 1024.0 * (256.0 + uSq * (-128.0 + uSq * (74.0 - 47.0 * uSq)));
+        k.C = f / 16.0 * cosSqAlpha * (4.0 + f * (4.0 - 3.0 * cosSqAlpha));
+        k.inv_bA = 1.0 / (b * A);
+        const double xj = cospi(((double)j + 0.5) / GEO_NP);
+        double gx, gy, gz, lon, lat, rlat, rlon;
+        geod_forward(k, s_mid + s_half * xj, cl0, sl0, lon0_deg, true, gx, gy, gz, lon, lat);
+        rotate_pole(rot, gx, gy, gz, rlat, rlon);
+        s_f[sub_l][0][j] = rlat; s_f[sub_l][1][j] = rlon; s_f[sub_l][2][j] = lat; s_f[sub_l][3][j] = lon;
+    }
+    __syncthreads();
+    if (ok) {
+        bool bad = false;
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+            double acc = 0.0;
+            for (int n = 0; n < GEO_NP; ++n) acc += s_f[sub_l][v][n] * cospi((double)j * ((double)n + 0.5) / GEO_NP);
+            acc *= (j == 0 ? 1.0 : 2.0) / GEO_NP;
+            s_a[sub_l][v][j] = acc;
+            if (j >= GEO_NC && fabs(acc) > 1e-13) bad = true;
+        }
+        if (bad) atomicOr(flags, 4);
+    }
+    __syncthreads();
+    if (ok && j < 4) {
+        // Chebyshev -> power basis: T_{n+1} = 2 x T_n - T_{n-1}
+        double m[GEO_NC], t0[GEO_NC], t1[GEO_NC];
+#pragma unroll
+        for (int n = 0; n < GEO_NC; ++n) { m[n] = 0.0; t0[n] = 0.0; t1[n] = 0.0; }
+        t0[0] = 1.0; t1[1] = 1.0;
+        m[0] = s_a[sub_l][j][0];
+        m[1] = s_a[sub_l][j][1];
+#pragma unroll
+        for (int n = 2; n < GEO_NC; ++n) {
+            double t2[GEO_NC];
+#pragma unroll
+            for (int d = 0; d < GEO_NC; ++d) t2[d] = (d ? 2.0 * t1[d - 1] : 0.0) - t0[d];
+            const double an = s_a[sub_l][j][n];
+#pragma unroll
+            for (int d = 0; d < GEO_NC; ++d) { m[d] = fma(an, t2[d], m[d]); t0[d] = t1[d]; t1[d] = t2[d]; }
+        }
+#pragma unroll
+        for (int d = 0; d < GEO_NC; ++d) out[i].c[j][d] = m[d];
+        if (j == 0) { out[i].sinA1 = k.sinA1; out[i].cosA1 = k.cosA1; }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // trilinear interpolation: bit-exact restatement of interpolation_c.c:42-103, 108-164
 // on the transposed layout z_t[col][level]
 // ------------------------------------------------------------------------------------------
@@ -698,9 +803,15 @@ __device__ __forceinline__ float pick_number(const float (&v)[RADOP_NVP], int va
 
 // Persistent blocks: each block walks chunks of 128 consecutive sub-beam gates and keeps
 // one shared-memory histogram of the LUT bins for its whole life (flushed once).
+// GEO_POLY: rotated-pole (and, for the central sub-beam, geographic) coordinates from the per-sub-beam
+// polynomials of k_sub_geopoly instead of a Vincenty solution per gate.
+// (A phase-synchronous variant -- large blocks whose warps meet at a barrier after geodesy / cell search /
+// interpolation / species so that they share the instruction cache -- was measured and is not kept:
+// 3.97 ms at 256 / 512 threads and 4.24 ms at 1024 against 3.94 ms, profiles/r01f_k1_experiments.md.)
+template <bool GEO_POLY>
 __global__ void __launch_bounds__(128, 8)
-k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *__restrict__ geo,
-             const float *__restrict__ z_t, const float *__restrict__ fields, K1Out o, long long n_sbg)
+k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const void *__restrict__ geo_v,
+             const float *__restrict__ z_t, const float *__restrict__ fields, K1Out o, long long n_sbg, int by_flag)
 {
     const int tid = threadIdx.x;
     for (int b = tid; b < cfg.total_bins; b += blockDim.x) s_hist[b] = 0;
@@ -708,6 +819,9 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
     const unsigned lane = tid & 31;
     const int ng = cfg.n_gates;
     const float qnan = __int_as_float(0x7fc00000);
+    // both instances are launched; flag bit 2 (a polynomial of k_sub_geopoly did not converge) selects
+    // the one that does the work
+    if (by_flag && GEO_POLY != !(*(volatile int *)o.flags & 4)) return;
 
     // Work is handed out per warp in pieces of 128 consecutive sub-beam gates from a global counter
     // (o.flags[3]): warps that start late (an NCCL kernel holding the SM, a slow neighbour) simply
@@ -724,28 +838,50 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
         uint32_t keys[RADOP_NSPECIES_MAX];
 #pragma unroll
         for (int s = 0; s < RADOP_NSPECIES_MAX; ++s) keys[s] = RADOP_KEY_NONE;
+        const bool in_range = sbg < n_sbg;
+        int g = 0;
+        size_t trow = 0;
+        float h_g = 0.f, e_g = 0.f, pos0 = 0.f, pos1 = 0.f;
+        double sinA1 = 0.0, cosA1 = 0.0, rlat = 0.0, rlon = 0.0;
+        CellGeom c;
+        c.status = 1;
 
-        if (sbg < n_sbg) {
+        if (in_range) {
             // n_sbg < 2^32 (checked by the host): 32-bit index arithmetic
             const unsigned rq = (unsigned)sbg / (unsigned)ng;
-            const int g = (int)((unsigned)sbg - rq * (unsigned)ng);
+            g = (int)((unsigned)sbg - rq * (unsigned)ng);
             const int ray = (int)(rq / (unsigned)cfg.n_sub);
             const int q = (int)(rq - (unsigned)ray * (unsigned)cfg.n_sub);
-            const size_t trow = ((size_t)scan.ray_traj[ray] * cfg.n_vert + scan.sub_jv[q]) * ng + g;
-            const float s_g = __ldg(scan.traj_s + trow), h_g = __ldg(scan.traj_h + trow), e_g = __ldg(scan.traj_e + trow);
+            trow = ((size_t)scan.ray_traj[ray] * cfg.n_vert + scan.sub_jv[q]) * ng + g;
+            const float s_g = __ldg(scan.traj_s + trow);
+            h_g = __ldg(scan.traj_h + trow); e_g = __ldg(scan.traj_e + trow);
 
             // --- geolocation ------------------------------------------------------------------
-            SubGeo kc;
-            {
-                const double2 *gp = reinterpret_cast<const double2 *>(geo + rq);
+            const bool center = (q == cfg.center_sub) && o.lat;
+            double lon = 0.0, lat = 0.0;
+            if (GEO_POLY) {
+                const SubPoly *sp = reinterpret_cast<const SubPoly *>(geo_v) + rq;
+                const double2 *cp = reinterpret_cast<const double2 *>(sp);
+                const double2 t0 = __ldg(cp);
+                sinA1 = t0.x; cosA1 = t0.y;
+                const double x = ((double)s_g - cfg.geo_mid) * cfg.geo_rhalf;
+                rlat = poly_eval(cp + 1, x);
+                rlon = poly_eval(cp + 1 + GEO_NC / 2, x);
+                if (center) {
+                    lat = poly_eval(cp + 1 + GEO_NC, x);
+                    lon = poly_eval(cp + 1 + 3 * GEO_NC / 2, x);
+                }
+            } else {
+                SubGeo kc;
+                const double2 *gp = reinterpret_cast<const double2 *>(reinterpret_cast<const SubGeo *>(geo_v) + rq);
                 double2 t0 = __ldg(gp), t1 = __ldg(gp + 1), t2 = __ldg(gp + 2), t3 = __ldg(gp + 3), t4 = __ldg(gp + 4);
                 kc.sinA1 = t0.x; kc.cosA1 = t0.y; kc.sinU1 = t1.x; kc.cosU1 = t1.y; kc.s2s1 = t2.x; kc.c2s1 = t2.y;
                 kc.sinAlpha = t3.x; kc.B = t3.y; kc.C = t4.x; kc.inv_bA = t4.y;
+                sinA1 = kc.sinA1; cosA1 = kc.cosA1;
+                double gx, gy, gz;
+                geod_forward(kc, (double)s_g, cfg.cos_lon0, cfg.sin_lon0, cfg.radar_lon, center, gx, gy, gz, lon, lat);
+                rotate_pole(cfg.rot, gx, gy, gz, rlat, rlon);
             }
-            const bool center = (q == cfg.center_sub) && o.lat;
-            double gx, gy, gz, lon = 0.0, lat = 0.0, rlat, rlon;
-            geod_forward(kc, (double)s_g, cfg.cos_lon0, cfg.sin_lon0, cfg.radar_lon, center, gx, gy, gz, lon, lat);
-            rotate_pole(cfg.rot, gx, gy, gz, rlat, rlon);
             if (center) {
                 o.lat[(size_t)ray * ng + g] = lat;
                 o.lon[(size_t)ray * ng + g] = lon;
@@ -756,9 +892,10 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                 atomicOr(o.flags, 1);
             // SWIG typemap casts the coordinates to float32 (interpolation_c.i:16)
             const float crlat = (float)rlat, crlon = (float)rlon;
-            const float pos0 = div_const(__fsub_rn(crlat, cfg.llc[1]), cfg.res[1], cfg.rres[1]);
-            const float pos1 = div_const(__fsub_rn(crlon, cfg.llc[0]), cfg.res[0], cfg.rres[0]);
-            CellGeom c;
+            pos0 = div_const(__fsub_rn(crlat, cfg.llc[1]), cfg.res[1], cfg.rres[1]);
+            pos1 = div_const(__fsub_rn(crlon, cfg.llc[0]), cfg.res[0], cfg.rres[0]);
+        }
+        if (in_range) {
             locate_cell(z_t, cfg.nz, cfg.ny, cfg.nx, pos0, pos1, h_g, cfg.z_strict != 0, c);
             o.mask[sbg] = (int8_t)c.status;
             if (o.dbg_cell) {
@@ -770,16 +907,22 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                 o.dbg_rot[2 * sbg + 1] = rlon;
                 for (int s = 0; s < cfg.n_species; ++s) { o.dbg_e[sbg * cfg.n_species + s] = -1; o.dbg_t[sbg * cfg.n_species + s] = -1; }
             }
+        }
 
-            float val[RADOP_NVP];
+        float val[RADOP_NVP];
+        const bool live = in_range && c.status == 0;
+        if (live) {
+            // --- interpolate every variable with the same 8 corner weights ----------------
+            // fast pass: shared-reciprocal quotients without a branch; a rare flag (zero /
+            // tiny / non-finite quotient, odd level spacing) sends the gate through the
+            // same code with IEEE divisions
+            if (interp_columns<false>(cfg, c, h_g, z_t, fields, val)) interp_columns<true>(cfg, c, h_g, z_t, fields, val);
+        }
+
+        if (in_range) {
             uint8_t active = 0;
             float wind = qnan, sinth = 0.f, vsum = 0.f, nsum = 0.f;
-            if (c.status == 0) {
-                // --- interpolate every variable with the same 8 corner weights ----------------
-                // fast pass: shared-reciprocal quotients without a branch; a rare flag (zero /
-                // tiny / non-finite quotient, odd level spacing) sends the gate through the
-                // same code with IEEE divisions
-                if (interp_columns<false>(cfg, c, h_g, z_t, fields, val)) interp_columns<true>(cfg, c, h_g, z_t, fields, val);
+            if (live) {
                 if (!cfg.two_moment) {
 #pragma unroll
                     for (int j = 9; j < RADOP_VAR_EDR; ++j) val[j] = 0.f;
@@ -883,7 +1026,7 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                 const float theta = e * 0.017453292519943295f;
                 float st, ct;
                 sincosf(theta, &st, &ct);
-                wind = (float)(((double)val[RADOP_VAR_U] * kc.sinA1 + (double)val[RADOP_VAR_V] * kc.cosA1) * (double)ct +
+                wind = (float)(((double)val[RADOP_VAR_U] * sinA1 + (double)val[RADOP_VAR_V] * cosA1) * (double)ct +
                                (double)val[RADOP_VAR_W] * (double)st);
                 sinth = st;
             } else {
@@ -891,7 +1034,7 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const SubGeo *
                 for (int j = 0; j < RADOP_NVP; ++j) val[j] = qnan;
             }
             if (o.d3_uh) {
-                o.d3_uh[sbg] = (double)val[RADOP_VAR_U] * kc.sinA1 + (double)val[RADOP_VAR_V] * kc.cosA1;
+                o.d3_uh[sbg] = (double)val[RADOP_VAR_U] * sinA1 + (double)val[RADOP_VAR_V] * cosA1;
                 o.d3_w[sbg] = val[RADOP_VAR_W];
                 o.d3_rho[sbg] = val[RADOP_VAR_RHO];
                 if (scan.traj_sin) o.d3_st[sbg] = make_float2(__ldg(scan.traj_sin + trow), __ldg(scan.traj_tan + trow));

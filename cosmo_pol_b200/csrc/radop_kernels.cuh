@@ -57,6 +57,7 @@ struct DevConfig {
     long long out_stride;       // rays x gates of the whole scan: stride between output variables
     double radar_lat, radar_lon;
     double cos_lon0, sin_lon0;  // of the radar longitude
+    double geo_mid, geo_rhalf;  // polynomial geodesy: x = (s - geo_mid) * geo_rhalf in [-1, 1] over the scan's ground distances
     // model grid
     int nz, ny, nx;
     float llc[2], urc[2], res[2];

@@ -218,6 +218,15 @@ int radop_set_overlap_threshold(RadopHandle *h, int64_t min_output_bytes);
 
 /* Device-resident results of the last radop_execute (for NCCL gathers): pointer to
  * float32 [RADOP_N_OUT + 1][n_rays][n_gates] (observables then mask). */
+/* Geolocation of the gates (stands in for pyproj.Geod.fwd + pycosmo.WGS_to_COSMO,
+ * interpolation.py:526-568).  mode 0 (default): the rotated-pole coordinates of a sub-beam are
+ * polynomials in the ground distance, fitted per (ray, sub-beam) to the Vincenty solution at 16
+ * Chebyshev nodes; scans longer than 0.05 rad of arc or with a non-converging series use the
+ * per-gate solution automatically.  mode 1: per-gate solution always.
+ * radop_get_geodesy: *used_polynomials = 1 if the last execute ran on the polynomials. */
+int radop_set_geodesy(RadopHandle *h, int mode);
+int radop_get_geodesy(RadopHandle *h, int *used_polynomials);
+
 int radop_device_outputs(RadopHandle *h, void **dev_ptr, int64_t *n_rays, int64_t *n_gates);
 /* cudaStream_t of the handle (as void*), to record events on. */
 int radop_get_stream(RadopHandle *h, void **stream);

@@ -143,6 +143,46 @@ def test_indices_and_interpolated_values_bit_exact(scheme, freq):
     assert n_bad_coords == 0
 
 
+def test_geodesy_polynomial():
+    """The per sub-beam polynomials of the rotated-pole coordinates (default) against the per-gate
+    Vincenty solution + rotation: float64 coordinates to 1e-12 degrees, their float32 casts (what the
+    interpolation consumes) identical, hence every index, mask and observable identical; scans too long
+    for the truncated series take the per-gate solution by themselves."""
+    conf = copy.deepcopy(CONF_1MOM)
+    conf['radar']['range'] = 150000
+    conf['radar']['radial_resolution'] = 300
+    op, model, luts = make_operator(conf, ny=100, nx=100)
+    az = np.arange(0., 360., 7.5)
+    el = np.resize(np.array([-0.2, 1.0, 5.5, 20.0, 40.0, 89.0]), az.size)
+    eng = op._prepare_engine(keep_debug=True)
+    scan = op.build_scan(az, el)
+    res = {}
+    for mode in (0, 1):
+        eng.set_geodesy(mode)
+        out = eng.simulate(scan)
+        assert eng.geodesy_used_polynomials() == (mode == 0)
+        res[mode] = (copy.deepcopy(out), eng.debug_indices(scan))
+    eng.set_geodesy(0)
+    (o0, d0), (o1, d1) = res[0], res[1]
+    assert np.max(np.abs(d0['rot'] - d1['rot'])) < 1e-12
+    n_diff32 = int(np.sum(d0['rot'].astype(np.float32) != d1['rot'].astype(np.float32)))
+    assert n_diff32 == 0, n_diff32          # ~1e-7 per gate expected: none among 1.3e6 coordinates
+    for k in ('cell', 'level', 'status', 'lut_e', 'lut_t'):
+        assert np.array_equal(d0[k], d1[k]), k
+    assert np.array_equal(d0['values'].view(np.uint32), d1['values'].view(np.uint32))
+    for k in o0:
+        if k not in ('lat', 'lon'):
+            assert np.array_equal(o0[k].view(np.uint32), o1[k].view(np.uint32)), k
+    assert np.max(np.abs(o0['lat'] - o1['lat'])) < 1e-12 and np.max(np.abs(o0['lon'] - o1['lon'])) < 1e-12
+    # 400 km of range on a grid that holds it: 0.063 rad of arc, beyond the a-priori limit of the series
+    conf['radar']['range'] = 400000
+    conf['radar']['radial_resolution'] = 2000
+    op2, _, _ = make_operator(conf, ny=220, nx=220)
+    eng2 = op2._prepare_engine()
+    eng2.simulate(op2.build_scan(np.array([45., 200.]), np.array([0.5, 0.5])))
+    assert not eng2.geodesy_used_polynomials()
+
+
 @pytest.mark.parametrize('scheme,freq', [('1mom', 5.6), ('2mom', 9.41)])
 def test_observables_against_oracle(scheme, freq):
     op, model, luts = make_operator(CONF_1MOM, scheme, freq, output_variables='all')
