@@ -282,6 +282,7 @@ def run_ours(args):
     op.set_lut(luts)
     op.load_model(model)
     eng = op._prepare_engine()
+    eng.set_integration(args.integration)
     t_up = time.time() - t_up
     scaling = args.scaling
     if scaling == 'weak':
@@ -448,6 +449,7 @@ def run_ours(args):
                            pairs / (sbg1 * 4), 'lut_bins_touched': int(st['n_lut_bins']), 'tiles': int(st['n_tiles']),
                            'one_time_upload_s': t_up, 'checksum': checksum},
     }
+    line['integration'] = eng.integration_info()
     if world == 1 and not args.no_cpu:
         line['cpu_baseline'] = cpu_baseline(model, luts, conf)
     else:
@@ -468,6 +470,8 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--scaling', default='weak', choices=['weak', 'strong'])
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    ap.add_argument('--integration', default='table', choices=['table', 'direct'],
+                    help='diameter integral through lambda-transformed tables (default) or by direct sums')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
     if args.impl == 'reference':

@@ -10,7 +10,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libradop.so')
 
-RADOP_ABI_VERSION = 4
+RADOP_ABI_VERSION = 5
 NSPECIES_MAX = 7
 NVAR_MAX = 16
 N_OUT = 10
@@ -25,7 +25,7 @@ EXPORTS = ['radop_abi_version', 'radop_create', 'radop_destroy', 'radop_last_err
            'radop_execute', 'radop_fetch', 'radop_synchronize', 'radop_device_outputs', 'radop_get_stream',
            'radop_get_stats', 'radop_enable_timing', 'radop_debug_indices', 'radop_measure_fp32_peak',
            'radop_get_all_radar_pts', 'radop_selftest_division', 'radop_set_chunk', 'radop_set_overlap_threshold',
-           'radop_set_geodesy', 'radop_get_geodesy']
+           'radop_set_geodesy', 'radop_get_geodesy', 'radop_set_integration', 'radop_get_integration', 'radop_debug_integration']
 
 (RADOP_OK, RADOP_ERR_CUDA, RADOP_ERR_ARG, RADOP_ERR_OUT_OF_DOMAIN, RADOP_ERR_LUT, RADOP_ERR_STATE,
  RADOP_ERR_UNSUPPORTED) = range(7)
@@ -118,6 +118,10 @@ def load_library():
     lib.radop_set_overlap_threshold.argtypes = [C.c_void_p, C.c_int64]
     lib.radop_set_geodesy.argtypes = [C.c_void_p, C.c_int]
     lib.radop_get_geodesy.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+    lib.radop_set_integration.argtypes = [C.c_void_p, C.c_int]
+    lib.radop_debug_integration.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64), C.c_void_p, C.c_int64]
+    lib.radop_get_integration.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                          C.POINTER(C.c_int64), C.POINTER(C.c_float)]
     lib.radop_selftest_division.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.radop_get_all_radar_pts.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -419,6 +423,30 @@ class Engine(object):
         v = C.c_int(0)
         self._check(self.lib.radop_get_geodesy(self.h, C.byref(v)))
         return bool(v.value)
+
+    def set_integration(self, mode):
+        """How the diameter integral (get_N x lookup_line, doppler_scatter.py:246-268) is evaluated.
+        'table' / 0 (default): lambda-transformed tables, verified piece by piece against the direct sum;
+        'direct' / 1: sums over the diameters."""
+        mode = {'table': 0, 'direct': 1}.get(mode, mode)
+        self._check(self.lib.radop_set_integration(self.h, C.c_int(int(mode))))
+
+    def integration_info(self):
+        m, n, r, d, ms = C.c_int(0), C.c_int64(0), C.c_int64(0), C.c_int64(0), C.c_float(0)
+        self._check(self.lib.radop_get_integration(self.h, C.byref(m), C.byref(n), C.byref(r), C.byref(d), C.byref(ms)))
+        why = (C.c_int64 * 4)()
+        self._check(self.lib.radop_debug_integration(self.h, C.c_int(0), why, None, C.c_int64(0)))
+        return {'mode': 'table' if m.value == 0 else 'direct', 'pieces': int(n.value), 'rejected_pieces': int(r.value),
+                'direct_pairs': int(d.value), 'build_ms': float(ms.value),
+                'direct_pairs_by_reason': dict(zip(('rejected_piece', 'below_range', 'above_range', 'not_normal'),
+                                                   [int(v) for v in why]))}
+
+    def lamtab_piece_status(self, species, n_bins):
+        """[n_bins, 176] exponent word of the first column per (bin, piece); INT32_MIN marks a rejected piece."""
+        out = np.zeros(n_bins * 176, dtype=np.int32)
+        self._check(self.lib.radop_debug_integration(self.h, C.c_int(SPECIES_IDS[species]), None,
+                                                     out.ctypes.data_as(C.c_void_p), C.c_int64(out.size)))
+        return out.reshape(n_bins, 176)
 
     def set_overlap_threshold(self, min_output_bytes):
         """simulate() chunks the scan only when the outputs are at least this large (0: always)."""

@@ -43,6 +43,9 @@ struct LutHost {
     RadopSpecies packed_for;   // constants the table was premultiplied with
     int packed_doppler = 0;    // Doppler scheme the table was laid out for
     DevBuf table, aux;
+    DevBuf lamtab;             // lambda-transformed table (k_build_lamtab), built on first use
+    bool lamtab_built = false;
+    int lt_nc = 0, lt_stride = 0;
 };
 
 }  // namespace
@@ -91,6 +94,10 @@ struct RadopHandle_ {
     DevConfig cfg;
     int k2_blocks = 0;
     size_t k2_smem = 0;
+    int integration_mode = 0;    // 0: lambda-transformed tables (k_integrate_tab), 1: direct sums over the diameters (k_integrate)
+    DevBuf lt_stat;              // [0] u64 pairs integrated directly by k_integrate_tab, [1] (int) rejected pieces
+    long long lt_pieces = 0, lt_rejected = 0, lt_fallback = 0, lt_why[4] = {0, 0, 0, 0};
+    float lt_build_ms = 0.f;
     // timing
     bool timing = false;
     std::vector<cudaEvent_t> ev;   // 6 events per timed execute since radop_enable_timing(1)
@@ -333,7 +340,53 @@ int radop_upload_lut(RadopHandle *h, int species, const double *value_table, int
     raw.release();
     dax.release();
     L.loaded = true;
+    L.lamtab_built = false;
     h->executed = false;
+    return RADOP_OK;
+}
+
+// lambda-transformed tables of every species that does not have them yet (table mode only)
+static int build_lamtabs(RadopHandle *h)
+{
+    DevConfig &c = h->cfg;
+    CU(h, h->lt_stat.reserve(64));
+    bool any = false;
+    for (int s = 0; s < c.n_species; ++s) {
+        SpeciesDev &d = c.sp[s];
+        LutHost &L = h->lut[d.species];
+        if (d.mode == MODE_MELT) continue;
+        const int nc = lt_columns(d.mode, c.doppler_scheme), stride = lt_stride(nc);
+        if (!L.lamtab_built) {
+            if (!any) {
+                h->lt_pieces = h->lt_rejected = 0;
+                for (int i = 0; i < RADOP_NSPECIES_MAX; ++i)
+                    if (h->lut[i].lamtab_built) h->lt_pieces += (long long)h->lut[i].ne * h->lut[i].nt * LT_NP;
+            }
+            cudaEvent_t e0, e1;
+            CU(h, cudaEventCreate(&e0)); CU(h, cudaEventCreate(&e1));
+            const size_t bins = (size_t)L.ne * L.nt;
+            if (bins * LT_NP > 0x7fffffffull) return h->fail(RADOP_ERR_LUT, "too many (bin, piece) combinations for the lambda tables");
+            CU(h, L.lamtab.reserve(bins * LT_NP * stride * 4));
+            CU(h, cudaMemsetAsync((char *)h->lt_stat.p + 32, 0, 4, h->stream));
+            CU(h, cudaEventRecord(e0, h->stream));
+            k_build_lamtab<<<(unsigned)(bins * LT_NP), 256, 0, h->stream>>>(d, nc, stride, L.lamtab.as<float>(),
+                                                                            (int *)((char *)h->lt_stat.p + 32));
+            CU(h, cudaGetLastError());
+            CU(h, cudaEventRecord(e1, h->stream));
+            int bad = 0;
+            CU(h, cudaMemcpyAsync(&bad, (char *)h->lt_stat.p + 32, 4, cudaMemcpyDeviceToHost, h->stream));
+            CU(h, cudaStreamSynchronize(h->stream));
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, e0, e1);
+            cudaEventDestroy(e0); cudaEventDestroy(e1);
+            h->lt_build_ms = any ? h->lt_build_ms + ms : ms;
+            h->lt_pieces += (long long)bins * LT_NP;
+            h->lt_rejected += bad;
+            L.lamtab_built = true; L.lt_nc = nc; L.lt_stride = stride;
+            any = true;
+        }
+        d.lamtab = L.lamtab.as<float>(); d.lt_nc = nc; d.lt_stride = stride;
+    }
     return RADOP_OK;
 }
 
@@ -569,6 +622,10 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     int rc = prepare(h);
     if (rc) return rc;
     CU(h, cudaSetDevice(h->device));
+    if (h->integration_mode == 0) {
+        rc = build_lamtabs(h);
+        if (rc) return rc;
+    }
     DevConfig &c = h->cfg;
     const int nsp = c.n_species, ng = c.n_gates;
     const int n_rays = h->n_rays;
@@ -710,6 +767,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     const bool timed = h->timing && h->n_timed + n_chunks <= 16384;
     if (timed) ++h->n_exec_timed;
     CU(h, cudaMemsetAsync(h->flags.p, 0, 4, st));
+    if (h->integration_mode == 0) CU(h, cudaMemsetAsync(h->lt_stat.p, 0, 32, st));
     c.out_stride = (long long)n_rg;
 
     for (int ch = 0; ch < n_chunks; ++ch) {
@@ -766,7 +824,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
                 // per sub-beam polynomials of the rotated-pole coordinates; a sub-beam whose series does not
                 // converge raises flag bit 2 and the per-gate instance does the work instead (both are launched,
                 // the one that is not wanted returns at once)
-                k_sub_geopoly<<<(n_rq + 7) / 8, 128, 0, st>>>(c, nr, h->geo_mid, h->geo_half, scan.ray_az, scan.sub_daz,
+                k_sub_geopoly<<<(n_rq + 7) / 8, 128, 0, st>>>(c, nr, scan, scan.ray_az, scan.sub_daz,
                                                                h->geo_poly.as<SubPoly>(), h->flags.as<int>());
                 CU(h, cudaGetLastError()); ++launches;
                 k_interp_psd<true><<<grid1, 128, hist_smem, st>>>(c, scan, h->geo_poly.p, zt, fl, o, nc, 1);
@@ -780,9 +838,14 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         k_scan_bins<<<1, 1024, 0, st>>>(c, h->hist.as<int>(), h->bin_start.as<int>(), h->tile_start.as<int>(),
                                          h->cost_start.as<int>(), h->cursor.as<int>(), totals);
         CU(h, cudaGetLastError()); ++launches;
-        k_scatter_pairs<<<(unsigned)((nc + 255) / 256), 256, hist_smem, st>>>(c, h->key.as<uint16_t>(), h->p0.as<float>(), h->p1.as<float>(),
-                                                                               scan.sub_weight, h->cursor.as<int>(), h->rec.as<PairRec>(), nc);
-        CU(h, cudaGetLastError()); ++launches;
+        // the sorted work list serves the direct kernel, the melting kernel and the spectrum kernel;
+        // the table kernel reads the pairs in ray order straight from K1's outputs
+        const bool table_mode = h->integration_mode == 0;
+        if (!table_mode || c.with_melting || c.doppler_scheme == 3) {
+            k_scatter_pairs<<<(unsigned)((nc + 255) / 256), 256, hist_smem, st>>>(c, h->key.as<uint16_t>(), h->p0.as<float>(), h->p1.as<float>(),
+                                                                                   scan.sub_weight, h->cursor.as<int>(), h->rec.as<PairRec>(), nc);
+            CU(h, cudaGetLastError()); ++launches;
+        }
         if (ev) CU(h, cudaEventRecord(ev[2], st));
 
         K2Args a2;
@@ -790,7 +853,19 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         a2.chunk_start = h->cost_start.as<int>(); a2.totals = totals;
         a2.counter = h->flags.as<int>() + 1;
         a2.rec = h->rec.as<PairRec>(); a2.sz_out = h->sz_out.as<float>(); a2.ice_vn = h->ice_vn.as<float2>(); a2.dop_vn = h->dop_vn.as<float2>();
-        k_integrate<<<h->k2_blocks, RADOP_TILE_THREADS, h->k2_smem, st>>>(c, a2);
+        if (table_mode) {
+            K2tArgs at;
+            at.key = h->key.as<uint16_t>(); at.p0 = h->p0.as<float>(); at.p1 = h->p1.as<float>();
+            at.sub_weight = scan.sub_weight; at.sz_out = a2.sz_out; at.ice_vn = a2.ice_vn; at.dop_vn = a2.dop_vn;
+            at.n_sbg = nc; at.n_fallback = h->lt_stat.as<unsigned long long>();
+            static const int occ_t = getenv("RADOP_K2T_OCC") ? atoi(getenv("RADOP_K2T_OCC")) : 3;
+            const unsigned gridt = (unsigned)std::min<long long>((nc + 255) / 256, (long long)h->n_sm * 8 * occ_t);
+            if (occ_t == 2) k_integrate_tab<2><<<gridt, 256, 0, st>>>(c, at);
+            else if (occ_t == 4) k_integrate_tab<4><<<gridt, 256, 0, st>>>(c, at);
+            else k_integrate_tab<3><<<gridt, 256, 0, st>>>(c, at);
+        } else {
+            k_integrate<<<h->k2_blocks, RADOP_TILE_THREADS, h->k2_smem, st>>>(c, a2);
+        }
         if (c.with_melting) {
             K2mArgs am;
             am.rec = h->rec.as<PairRec>(); am.key = h->key.as<uint16_t>(); am.bin_start = h->bin_start.as<int>();
@@ -931,6 +1006,12 @@ static int finish(RadopHandle *h)
         else per_d = 2.0 * 10 + 2.0 + 2.0;                                          // ICE1: + shape FMA, two recurrences
         h->stats.exec_flop_per_pair[s] = per_d * S.nd;
     }
+    if (h->integration_mode == 0 && h->lt_stat.p) {
+        unsigned long long nf[4] = {0, 0, 0, 0};
+        CU(h, cudaMemcpy(nf, h->lt_stat.p, 32, cudaMemcpyDeviceToHost));
+        h->lt_fallback = (long long)(nf[0] + nf[1] + nf[2] + nf[3]);
+        for (int i = 0; i < 4; ++i) h->lt_why[i] = (long long)nf[i];
+    }
     average_timings(h);
     h->geo_poly_used = h->geo_poly_launched && !(flags[0] & 4);
     if (flags[0] & 1)
@@ -981,6 +1062,43 @@ int radop_set_geodesy(RadopHandle *h, int mode)
 {
     if (!h || (mode != 0 && mode != 1)) return RADOP_ERR_ARG;
     h->geodesy_mode = mode;
+    return RADOP_OK;
+}
+
+int radop_set_integration(RadopHandle *h, int mode)
+{
+    if (!h || (mode != 0 && mode != 1)) return RADOP_ERR_ARG;
+    h->integration_mode = mode;
+    h->executed = false;
+    return RADOP_OK;
+}
+
+int radop_get_integration(RadopHandle *h, int *mode, int64_t *n_pieces, int64_t *n_rejected_pieces,
+                          int64_t *n_direct_pairs, float *build_ms)
+{
+    if (!h) return RADOP_ERR_ARG;
+    if (mode) *mode = h->integration_mode;
+    if (n_pieces) *n_pieces = h->lt_pieces;
+    if (n_rejected_pieces) *n_rejected_pieces = h->lt_rejected;
+    if (n_direct_pairs) *n_direct_pairs = h->integration_mode == 0 ? h->lt_fallback : 0;
+    if (build_ms) *build_ms = h->lt_build_ms;
+    return RADOP_OK;
+}
+
+int radop_debug_integration(RadopHandle *h, int species, int64_t why[4], int32_t *piece_status, int64_t n_status)
+{
+    if (!h) return RADOP_ERR_ARG;
+    if (why) for (int i = 0; i < 4; ++i) why[i] = h->lt_why[i];
+    if (piece_status) {
+        if (species < 0 || species >= RADOP_NSPECIES_MAX) return h->fail(RADOP_ERR_ARG, "unknown species id");
+        const LutHost &L = h->lut[species];
+        if (!L.lamtab_built) return h->fail(RADOP_ERR_STATE, "no lambda table for this species");
+        const size_t n = (size_t)L.ne * L.nt * LT_NP;
+        if ((size_t)n_status < n) return h->fail(RADOP_ERR_ARG, "piece_status too short");
+        CU(h, cudaSetDevice(h->device));
+        CU(h, cudaMemcpy2D(piece_status, 4, (const char *)L.lamtab.p + (size_t)12 * L.lt_nc * 4, (size_t)L.lt_stride * 4, 4, n,
+                           cudaMemcpyDeviceToHost));
+    }
     return RADOP_OK;
 }
 

@@ -309,11 +309,22 @@ __device__ __forceinline__ void rotate_pole(const double *__restrict__ R, double
 // evaluation per coordinate.  The difference to the per-gate solution is ~1e-14 degrees, the
 // rounding level of the per-gate solution itself (tests/test_gpu_parity.py::test_geodesy_polynomial).
 // ------------------------------------------------------------------------------------------
+struct ScanDev {
+    const double *ray_az;
+    const int *ray_traj;
+    const double *sub_daz;
+    const int *sub_jv;
+    const double *sub_weight;
+    const float *traj_s, *traj_h, *traj_e;
+    const float *traj_sin, *traj_tan;   // optional (Doppler scheme 3)
+};
+
 #define GEO_NP 16
 #define GEO_NC 12
 struct __align__(16) SubPoly {
     double sinA1, cosA1;
-    double c[4][GEO_NC];     // rlat, rlon, lat, lon (degrees) as polynomials in x = (s - geo_mid) * geo_rhalf
+    double mid, rhalf;       // x = (s - mid) * rhalf in [-1, 1] over the ground distances of THIS sub-beam's trajectory
+    double c[4][GEO_NC];     // rlat, rlon, lat, lon (degrees) as polynomials in x
 };
 
 __device__ __forceinline__ double poly_eval(const double2 *__restrict__ c, double x)
@@ -331,7 +342,7 @@ __device__ __forceinline__ double poly_eval(const double2 *__restrict__ c, doubl
 
 // block = 128 threads = 8 sub-beams x 16 nodes
 __global__ void __launch_bounds__(128)
-k_sub_geopoly(const __grid_constant__ DevConfig cfg, int n_rays, double s_mid, double s_half,
+k_sub_geopoly(const __grid_constant__ DevConfig cfg, int n_rays, ScanDev scan,
               const double *__restrict__ ray_az, const double *__restrict__ sub_daz, SubPoly *__restrict__ out, int *flags)
 {
     const int n_sub = cfg.n_sub;
@@ -344,6 +355,26 @@ k_sub_geopoly(const __grid_constant__ DevConfig cfg, int n_rays, double s_mid, d
     const bool ok = i < n_rays * n_sub;
     const double f = WGS84_F, a = WGS84_A, b = (1.0 - f) * a;
     SubGeo k;
+    // The interval is the ground-distance range of the sub-beam's own trajectory row, so that the
+    // polynomial (and with it lat / lon to the last bit) does not depend on which other rays share
+    // the scan, the shard or the chunk.
+    double s_mid = 0.0, s_half = 1.0;
+    {
+        float lo = 3.0e38f, hi = -3.0e38f;
+        if (ok) {
+            const float *row = scan.traj_s + ((size_t)scan.ray_traj[i / n_sub] * cfg.n_vert + scan.sub_jv[i % n_sub]) * cfg.n_gates;
+            for (int g = j; g < cfg.n_gates; g += GEO_NP) { const float v = __ldg(row + g); lo = fminf(lo, v); hi = fmaxf(hi, v); }
+        }
+#pragma unroll
+        for (int d = 8; d >= 1; d >>= 1) {
+            lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, d));
+            hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, d));
+        }
+        if (ok) {
+            s_mid = 0.5 * ((double)lo + (double)hi);
+            s_half = fmax(0.5 * ((double)hi - (double)lo), 1.0);
+        }
+    }
     if (ok) {
         double az = ray_az[i / n_sub] + sub_daz[i % n_sub];
         double phi1 = lat0_deg * DEG2RAD, alpha1 = az * DEG2RAD;
@@ -399,7 +430,7 @@ k_sub_geopoly(const __grid_constant__ DevConfig cfg, int n_rays, double s_mid, d
         }
 #pragma unroll
         for (int d = 0; d < GEO_NC; ++d) out[i].c[j][d] = m[d];
-        if (j == 0) { out[i].sinA1 = k.sinA1; out[i].cosA1 = k.cosA1; }
+        if (j == 0) { out[i].sinA1 = k.sinA1; out[i].cosA1 = k.cosA1; out[i].mid = s_mid; out[i].rhalf = 1.0 / s_half; }
     }
 }
 
@@ -693,16 +724,6 @@ __device__ __forceinline__ bool interp_columns(const DevConfig &cfg, const CellG
 // ------------------------------------------------------------------------------------------
 // K1: per sub-beam gate
 // ------------------------------------------------------------------------------------------
-struct ScanDev {
-    const double *ray_az;
-    const int *ray_traj;
-    const double *sub_daz;
-    const int *sub_jv;
-    const double *sub_weight;
-    const float *traj_s, *traj_h, *traj_e;
-    const float *traj_sin, *traj_tan;   // optional (Doppler scheme 3)
-};
-
 struct K1Out {
     int8_t *mask;          // [sbg]
     uint8_t *active;       // [sbg] bit per species
@@ -864,12 +885,13 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const void *__
                 const double2 *cp = reinterpret_cast<const double2 *>(sp);
                 const double2 t0 = __ldg(cp);
                 sinA1 = t0.x; cosA1 = t0.y;
-                const double x = ((double)s_g - cfg.geo_mid) * cfg.geo_rhalf;
-                rlat = poly_eval(cp + 1, x);
-                rlon = poly_eval(cp + 1 + GEO_NC / 2, x);
+                const double2 iv = __ldg(cp + 1);
+                const double x = ((double)s_g - iv.x) * iv.y;
+                rlat = poly_eval(cp + 2, x);
+                rlon = poly_eval(cp + 2 + GEO_NC / 2, x);
                 if (center) {
-                    lat = poly_eval(cp + 1 + GEO_NC, x);
-                    lon = poly_eval(cp + 1 + 3 * GEO_NC / 2, x);
+                    lat = poly_eval(cp + 2 + GEO_NC, x);
+                    lon = poly_eval(cp + 2 + 3 * GEO_NC / 2, x);
                 }
             } else {
                 SubGeo kc;
@@ -1621,6 +1643,383 @@ k_integrate(const __grid_constant__ DevConfig cfg, K2Args A)
                         }
                     }
                 }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K2t: the contraction through lambda-transformed tables
+// ------------------------------------------------------------------------------------------
+// For every species the PSD is a ONE-parameter family of shapes: N(D) = N0 * shape(lambda, D)
+// (hydrometeors.py:128-152 generalised gamma, :1231-1254 + constants_1mom.py:103-104 Field 2005).
+// The diameter integral of one (e, t) bin and one combined column,
+//     F_c(lambda) = sum_k tab[k][c] shape(lambda, D_k),
+// is therefore a function of lambda alone -- a discrete Laplace-type transform of the table
+// column -- and it is analytic in u = log2(lambda).  k_build_lamtab evaluates it in float64 at
+// Chebyshev nodes of eighth-octave pieces of u, once per table upload, in the scaled form
+//     F_c = 2^{L_c(u)} R_c(u),   L_c = log2 sum_k |tab[k][c]| shape,   R_c = F_c / 2^{L_c} in [-1, 1]
+// (envelope and signed ratio: the relative accuracy is that of the float32 sum itself, whatever
+// the signs of the column), fits degree-5 polynomials, and VERIFIES every piece at two more
+// nodes (x = 0, x = 1, extrema of T_6) against the float64 sum: a piece that misses 2e-7 is
+// marked and its pairs are integrated directly, diameter by diameter.  A pair then costs 12 NC
+// coefficients (384 B, shared by neighbouring gates: same bin, same piece) and ~100 FMA instead
+// of nd x NC.  radop_set_integration(1) selects the direct kernel (k_integrate) instead; both are
+// held to the oracle by the same tests and to each other by test_table_vs_direct.
+#define LT_U0 (-10)              // u = log2(lambda) covered: [LT_U0, LT_U0 + LT_OCT)
+#define LT_OCT 22
+#define LT_PPO 8                 // pieces per octave
+#define LT_NP (LT_OCT * LT_PPO)
+#define LT_BAD ((int)0x80000000)
+#define LT_TOL 2e-7
+
+__host__ __device__ inline int lt_columns(int mode, int doppler_scheme)
+{
+    if (mode == MODE_ICE1) return 10;
+    if (mode == MODE_GEN12) return 9;
+    return doppler_scheme == 2 ? 8 : 7;
+}
+// floats per (bin, piece): 6 x 2 NC coefficients, NC integer exponents, padded to 128 B lines
+__host__ __device__ inline int lt_stride(int nc) { return (12 * nc + ((nc + 3) & ~3) + 31) / 32 * 32; }
+
+// shape(lambda, D_k) / 2^{shift(lambda)} in float64 (the common factor keeps the sum in range)
+__device__ __forceinline__ double lt_weight(const SpeciesDev &S, double lam, double lam_p, int k, double y0)
+{
+    const int nd = S.nd;
+    if (S.mode == MODE_GEO8) return exp(-lam * (double)k * S.dD_d);
+    if (S.mode == MODE_ICE1) {
+        const double D = (double)__ldg(S.aux + k);
+        return 490.6 * exp(-lam * (20.78 * D - 3.29 * y0)) +
+               17.46 * lam_p * (double)__ldg(S.aux + 2 * nd + k) * exp(-3.29 * lam * (D - y0));
+    }
+    return exp(-lam * ((double)__ldg(S.aux + nd + k) - y0));
+}
+__device__ __forceinline__ double lt_y0(const SpeciesDev &S)
+{
+    return (double)__ldg(S.aux + ((S.mode == MODE_GEO8 || S.mode == MODE_ICE1) ? 0 : S.nd));
+}
+// log2 of the common factor
+__device__ __forceinline__ double lt_shift(const SpeciesDev &S, double lam, double y0)
+{
+    return -(S.mode == MODE_ICE1 ? 3.29 : 1.0) * lam * y0 * 1.4426950408889634;
+}
+
+// one CTA per (bin, piece); warp = node (6 Chebyshev nodes + 2 check nodes), lanes over diameters
+__global__ void __launch_bounds__(256)
+k_build_lamtab(const __grid_constant__ SpeciesDev S, int nc, int stride, float *__restrict__ out, int *__restrict__ n_bad)
+{
+    __shared__ double s_v[8][20];
+    __shared__ double s_err[20];
+    __shared__ int s_flag;
+    const int bin = blockIdx.x / LT_NP, piece = blockIdx.x % LT_NP;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) s_flag = 0;
+    __syncthreads();
+    {
+        const double x = warp < 6 ? cospi(((double)warp + 0.5) / 6.0) : (warp == 6 ? 0.0 : 1.0);
+        const double u = (double)LT_U0 + ((double)piece + 0.5 * (x + 1.0)) / (double)LT_PPO;
+        const double lam = exp2(u), lam_p = pow(lam, 0.6357), y0 = lt_y0(S);
+        double F[10], A[10];
+#pragma unroll
+        for (int c = 0; c < 10; ++c) { F[c] = 0.0; A[c] = 0.0; }
+        const float *tab = S.table + (size_t)bin * S.nd * S.ncol;
+        for (int k = lane; k < S.nd; k += 32) {
+            const double w = lt_weight(S, lam, lam_p, k, y0);
+            const float *row = tab + (size_t)k * S.ncol;
+#pragma unroll
+            for (int c = 0; c < 10; ++c)
+                if (c < nc) {
+                    const double t = (double)__ldg(row + c);
+                    F[c] = fma(w, t, F[c]);
+                    A[c] = fma(w, fabs(t), A[c]);
+                }
+        }
+#pragma unroll
+        for (int c = 0; c < 10; ++c)
+#pragma unroll
+            for (int d = 16; d >= 1; d >>= 1) {
+                F[c] += __shfl_xor_sync(0xffffffffu, F[c], d);
+                A[c] += __shfl_xor_sync(0xffffffffu, A[c], d);
+            }
+        if (lane == 0) {
+            const double sh = lt_shift(S, lam, y0);
+#pragma unroll
+            for (int c = 0; c < 10; ++c)
+                if (c < nc) {
+                    double L = 0.0, R = 0.0;
+                    if (A[c] > 0.0 && A[c] < 1e300) { L = log2(A[c]) + sh; R = F[c] / A[c]; }
+                    else if (A[c] == 0.0) atomicOr(&s_flag, 1 << 1);      // empty column (or total underflow)
+                    else atomicOr(&s_flag, 1);
+                    if (A[c] > 0.0) atomicOr(&s_flag, 1 << 2);
+                    s_v[warp][c] = L;
+                    s_v[warp][nc + c] = R;
+                }
+        }
+    }
+    __syncthreads();
+    float *dst = out + ((size_t)bin * LT_NP + piece) * stride;
+    const int f = threadIdx.x;
+    double p[6] = {0, 0, 0, 0, 0, 0};
+    if (f < 2 * nc) {
+        double a[6];
+#pragma unroll
+        for (int n = 0; n < 6; ++n) {
+            double acc = 0.0;
+#pragma unroll
+            for (int j = 0; j < 6; ++j) acc += s_v[j][f] * cospi((double)n * ((double)j + 0.5) / 6.0);
+            a[n] = acc * (n == 0 ? 1.0 : 2.0) / 6.0;
+        }
+        // Chebyshev -> power basis (degree 5)
+        p[0] = a[0] - a[2] + a[4];
+        p[1] = a[1] - 3.0 * a[3] + 5.0 * a[5];
+        p[2] = 2.0 * a[2] - 8.0 * a[4];
+        p[3] = 4.0 * a[3] - 20.0 * a[5];
+        p[4] = 8.0 * a[4];
+        p[5] = 16.0 * a[5];
+        const double e0 = fabs(p[0] - s_v[6][f]);
+        const double e1 = fabs(p[0] + p[1] + p[2] + p[3] + p[4] + p[5] - s_v[7][f]);
+        // the float32 evaluation carries ~1e-7 of the range the polynomial sweeps inside the piece anyway
+        const double range = fmax(1.0, fabs(p[1]) + fabs(p[2]) + fabs(p[3]) + fabs(p[4]) + fabs(p[5]));
+        s_err[f] = fmax(e0, e1) * (f < nc ? 0.6931471805599453 : 1.0) / range;
+    }
+    __syncthreads();
+    // a piece is unusable when a node was out of range, when a column is empty at some nodes only
+    // (underflow), or when the fit misses the tolerance at the check nodes
+    bool bad = (s_flag & 1) != 0;
+    for (int c = 0; c < nc; ++c) {
+        const double e = s_err[c] + s_err[nc + c];
+        if (!(e <= LT_TOL)) bad = true;
+    }
+    if ((s_flag & 6) == 6) {
+        // mixed empty / non-empty: fine when whole columns are empty at all 8 nodes, else underflow
+        for (int c = 0; c < nc; ++c) {
+            int zero = 0;
+            for (int j = 0; j < 8; ++j) zero += (s_v[j][c] == 0.0 && s_v[j][nc + c] == 0.0);
+            if (zero != 0 && zero != 8) bad = true;
+        }
+    }
+    if (f < 2 * nc) {
+        int L0 = 0;
+        if (f < nc) {
+            L0 = (int)rint(p[0]);
+            p[0] -= (double)L0;
+            reinterpret_cast<int *>(dst)[12 * nc + f] = (bad && f == 0) ? LT_BAD : L0;
+        }
+        // layout per piece: [column][L coefficients 0..5, R coefficients 0..5], then the nc exponent words
+        float *o = (f < nc) ? dst + f * 12 : dst + (f - nc) * 12 + 6;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) o[j] = (float)p[j];
+    }
+    if (bad && f == 0) atomicAdd(n_bad, 1);
+}
+
+// 2^e as a double, flushing what a float result could not hold anyway
+__device__ __forceinline__ double lt_pow2(int e)
+{
+    if (e < -1000) return 0.0;
+    if (e > 1000) e = 1000;
+    return __hiloint2double((e + 1023) << 20, 0);
+}
+
+// table evaluation of one pair: dv[c] = F_c(lambda); a non-zero return says why the pair needs the
+// direct sum instead (1 rejected piece, 2 below / 3 above the tabulated range, 4 not a positive normal number)
+template <int NC>
+__device__ __forceinline__ int lamtab_eval(const float *__restrict__ lt_bin, float lam, double (&dv)[NC])
+{
+    if (!(lam > 0.f) || !(lam < 3.0e38f)) return 4;
+    const int bits = __float_as_int(lam);
+    const int e = (bits >> 23) - 127;
+    if (e < -126) return 4;
+    const float m = __int_as_float((bits & 0x007fffff) | 0x3f800000);      // [1, 2)
+    const float t = (float)LT_PPO * log2f(m);                              // [0, LT_PPO)
+    int it = (int)t;
+    if (it > LT_PPO - 1) it = LT_PPO - 1;
+    const int piece = (e - LT_U0) * LT_PPO + it;
+    if (piece < 0) return 2;
+    if (piece >= LT_NP) return 3;
+    const float x = 2.f * (t - (float)it) - 1.f;
+    constexpr int stride = (12 * NC + ((NC + 3) & ~3) + 31) / 32 * 32;
+    const float4 *src = reinterpret_cast<const float4 *>(lt_bin + (size_t)piece * stride);
+    int L0[(NC + 3) & ~3];
+#pragma unroll
+    for (int i = 0; i < (NC + 3) / 4; ++i) {
+        const int4 v = __ldg(reinterpret_cast<const int4 *>(src + 3 * NC) + i);
+        L0[4 * i] = v.x; L0[4 * i + 1] = v.y; L0[4 * i + 2] = v.z; L0[4 * i + 3] = v.w;
+    }
+    if (L0[0] == LT_BAD) return 1;
+    // one column at a time: 12 coefficients (three 16 B loads), two Horner chains, one ex2
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+        const float4 a = __ldg(src + 3 * k), b = __ldg(src + 3 * k + 1), c = __ldg(src + 3 * k + 2);
+        float L = b.y, R = c.w;
+        L = fmaf(L, x, b.x); R = fmaf(R, x, c.z);
+        L = fmaf(L, x, a.w); R = fmaf(R, x, c.y);
+        L = fmaf(L, x, a.z); R = fmaf(R, x, c.x);
+        L = fmaf(L, x, a.y); R = fmaf(R, x, b.w);
+        L = fmaf(L, x, a.x); R = fmaf(R, x, b.z);
+        dv[k] = (double)(exp2f(L) * R) * lt_pow2(L0[k]);
+    }
+    return 0;
+}
+
+// the same sums diameter by diameter, by a whole warp for ONE pair (pairs outside the tabulated
+// range or on a rejected piece): lanes stride over the diameters, shuffle reduction
+template <int NC>
+__device__ __noinline__ void warp_direct(const SpeciesDev &S, int bin_local, float lam, int lane, double (&dv)[NC])
+{
+    const int nd = S.nd;
+    float acc[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) acc[c] = 0.f;
+    const float a = -LOG2E * lam;
+    const float y0 = __ldg(S.aux + ((S.mode == MODE_GEO8 || S.mode == MODE_ICE1) ? 0 : nd));
+    // everything underflows float32 (the direct kernel returns zeros there as well); NaN runs the loop
+    const bool dead = (S.mode == MODE_ICE1 ? 3.29f : 1.f) * a * y0 <= -250.f;
+    if (!dead) {
+        const float *tab = S.table + (size_t)bin_local * nd * S.ncol;
+        const float c2 = (S.mode == MODE_ICE1) ? 17.46f * exp2f(0.6357f * log2f(lam)) : 0.f;
+        for (int k = lane; k < nd; k += 32) {
+            float w;
+            if (S.mode == MODE_GEO8) w = exp2f(a * (float)((double)y0 + (double)k * S.dD_d));
+            else if (S.mode == MODE_ICE1) {
+                const float D = __ldg(S.aux + k);
+                w = 490.6f * exp2f(20.78f * a * D) + c2 * __ldg(S.aux + 2 * nd + k) * exp2f(3.29f * a * D);
+            } else w = exp2f(a * __ldg(S.aux + nd + k));
+            const float *row = tab + (size_t)k * S.ncol;
+#pragma unroll
+            for (int c = 0; c < NC; ++c) acc[c] = fmaf(w, __ldg(row + c), acc[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c)
+#pragma unroll
+            for (int d = 16; d >= 1; d >>= 1) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], d);
+    }
+#pragma unroll
+    for (int c = 0; c < NC; ++c) dv[c] = (double)acc[c];
+}
+
+struct K2tArgs {
+    const uint16_t *key;     // [species][sbg] global bin id or RADOP_KEY_NONE
+    const float *p0, *p1;    // [species][sbg]
+    const double *sub_weight;
+    float *sz_out;
+    float2 *ice_vn, *dop_vn;
+    long long n_sbg;
+    unsigned long long *n_fallback;   // [4] pairs integrated directly, by reason (lamtab_eval)
+};
+
+// One species of one warp's 32 sub-beam gates: table evaluation per lane, then the lanes whose pair
+// could not be served by the table are integrated directly one after the other by the whole warp.
+// Must be called by all 32 lanes (have = this lane holds an active pair of the species).
+template <int NC>
+__device__ __forceinline__ void pair_tab(const DevConfig &cfg, const K2tArgs &A, const SpeciesDev &S, int s, bool have,
+                                         int bin, uint32_t sbg, float p0, float p1, float w, int lane)
+{
+    const int nsp = cfg.n_species, nd = S.nd;
+    const int bl = bin - S.bin_base;
+    double dv[NC];
+    int why = 0;
+    if (have) why = lamtab_eval<NC>(S.lamtab + (size_t)bl * LT_NP * S.lt_stride, p0, dv);
+    unsigned need = __ballot_sync(0xffffffffu, why != 0);
+    if (why) atomicAdd(A.n_fallback + (why - 1), 1ull);
+    while (need) {
+        const int src = __ffs(need) - 1;
+        need &= need - 1;
+        const int bl_s = __shfl_sync(0xffffffffu, bl, src);
+        const float lam_s = __shfl_sync(0xffffffffu, p0, src);
+        double ds[NC];
+        warp_direct<NC>(S, bl_s, lam_s, lane, ds);
+        if (lane == src) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) dv[c] = ds[c];
+        }
+    }
+    if (!have) return;
+    float v7[7];
+    if (S.mode == MODE_ICE1) {
+        // N0 renormalised so that the mass integral equals QM (hydrometeors.py:1330-1339)
+        const double n0 = (double)p1 / dv[9];
+#pragma unroll
+        for (int c = 0; c < 7; ++c) v7[c] = (float)(dv[c] * n0 * (double)w);
+        store_sz(A.sz_out, nsp, s, sbg, v7, 1.f);
+        if (cfg.doppler_scheme == 2) {
+            const float *tab = S.table + (size_t)bl * nd * S.ncol;
+            const float D0 = __ldg(S.aux), DL = __ldg(S.aux + nd - 1);
+            const float c2 = 17.46f * exp2f(0.6357f * log2f(p0));
+            const float w0 = 490.6f * ex2f_approx(-20.78f * LOG2E * p0 * D0) +
+                             c2 * __ldg(S.aux + 2 * nd) * ex2f_approx(-3.290f * LOG2E * p0 * D0);
+            const float wL = 490.6f * ex2f_approx(-20.78f * LOG2E * p0 * DL) +
+                             c2 * __ldg(S.aux + 3 * nd - 1) * ex2f_approx(-3.290f * LOG2E * p0 * DL);
+            const double n_ = dv[0] - 0.5 * ((double)__ldg(tab) * w0 + (double)__ldg(tab + (size_t)(nd - 1) * S.ncol) * wL);
+            const double v_ = dv[NC > 7 ? 7 : 0] - 0.5 * ((double)__ldg(tab + 7) * w0 + (double)__ldg(tab + (size_t)(nd - 1) * S.ncol + 7) * wL);
+            const double sc = 6.283185307179586 * n0 / (double)S.dD_ref;
+            A.dop_vn[(size_t)sbg * nsp + s] = make_float2((float)(v_ * sc), (float)(n_ * sc));
+        } else {
+            A.ice_vn[sbg] = make_float2((float)(dv[NC > 7 ? 7 : 0] * n0), (float)(dv[NC > 8 ? 8 : 0] * n0));
+        }
+        return;
+    }
+    const double pre = (double)p1 * (double)w;
+#pragma unroll
+    for (int c = 0; c < 7; ++c) v7[c] = (float)(dv[c] * pre);
+    store_sz(A.sz_out, nsp, s, sbg, v7, 1.f);
+    if (S.mode == MODE_GEN12) {
+        A.ice_vn[sbg] = make_float2((float)(dv[NC > 7 ? 7 : 0] * (double)p1), (float)(dv[NC > 8 ? 8 : 0] * (double)p1));
+    } else if (NC == 8) {
+        // trapezoid end corrections of Doppler scheme 2 (doppler2_moments)
+        const float *tab = S.table + (size_t)bl * nd * S.ncol;
+        const float a = -LOG2E * p0;
+        float yF, yL;
+        if (S.mode == MODE_GEO8) { yF = __ldg(S.aux); yL = (float)((double)yF + (double)(nd - 1) * S.dD_d); }
+        else { yF = __ldg(S.aux + nd); yL = __ldg(S.aux + 2 * nd - 1); }
+        const float wF = ex2f_approx(a * yF), wL = ex2f_approx(a * yL);
+        const double n_ = dv[0] - 0.5 * ((double)__ldg(tab) * wF + (double)__ldg(tab + (size_t)(nd - 1) * S.ncol) * wL);
+        const double v_ = dv[NC > 7 ? 7 : 0] - 0.5 * ((double)__ldg(tab + 7) * wF + (double)__ldg(tab + (size_t)(nd - 1) * S.ncol + 7) * wL);
+        const double sc = 6.283185307179586 * (double)p1 / (double)S.dD_ref;
+        A.dop_vn[(size_t)sbg * nsp + s] = make_float2((float)(v_ * sc), (float)(n_ * sc));
+    }
+}
+
+// thread per sub-beam gate, in ray order: neighbouring gates share the bin and mostly the piece,
+// so the coefficient loads of a warp are broadcasts out of L1; no sort is needed.
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB)
+k_integrate_tab(const __grid_constant__ DevConfig cfg, K2tArgs A)
+{
+    const int ng = cfg.n_gates;
+    const int lane = threadIdx.x & 31;
+    // warp-uniform trip count: the direct integration of a pair is a warp-collective step
+    for (long long base = (long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < A.n_sbg;
+         base += (long long)gridDim.x * blockDim.x) {
+        const long long sbg = base + lane;
+        const bool in_range = sbg < A.n_sbg;
+        const int q = in_range ? (int)(((unsigned)sbg / (unsigned)ng) % (unsigned)cfg.n_sub) : 0;
+        const float w = (float)__ldg(A.sub_weight + q);
+        // software pipeline over the species: the key / lambda / N0 loads of the next species are in
+        // flight while the current one is evaluated
+        uint32_t k_nxt = in_range ? (uint32_t)A.key[sbg] : RADOP_KEY_NONE;
+        float p0_nxt = 1.f, p1_nxt = 0.f;
+        if (k_nxt != RADOP_KEY_NONE) { p0_nxt = A.p0[sbg]; p1_nxt = A.p1[sbg]; }
+#pragma unroll 1
+        for (int s = 0; s < cfg.n_species; ++s) {
+            const uint32_t k = k_nxt;
+            const float p0 = p0_nxt, p1 = p1_nxt;
+            if (s + 1 < cfg.n_species) {
+                const size_t o = (size_t)(s + 1) * A.n_sbg + sbg;
+                k_nxt = in_range ? (uint32_t)A.key[o] : RADOP_KEY_NONE;
+                p0_nxt = 1.f; p1_nxt = 0.f;
+                if (k_nxt != RADOP_KEY_NONE) { p0_nxt = A.p0[o]; p1_nxt = A.p1[o]; }
+            }
+            const SpeciesDev &S = cfg.sp[s];
+            if (S.mode == MODE_MELT) continue;
+            const bool have = k != RADOP_KEY_NONE;
+            if (!__any_sync(0xffffffffu, have)) continue;
+            const int bin = have ? (int)k : S.bin_base;
+            switch (S.lt_nc) {
+            case 7: pair_tab<7>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane); break;
+            case 8: pair_tab<8>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane); break;
+            case 9: pair_tab<9>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane); break;
+            default: pair_tab<10>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane); break;
             }
         }
     }

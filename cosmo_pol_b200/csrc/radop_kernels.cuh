@@ -39,6 +39,8 @@ struct SpeciesDev {
     double dD_d;                // dD_geo in float64
     const float *table;         // [ne][nt][nd][ncol] combined + premultiplied columns
     const float *aux;           // [3][nd]: D, D^nu, D^0.6357
+    const float *lamtab;        // [ne*nt][LT_NP][lt_stride] lambda-transformed table (k_build_lamtab) or null
+    int lt_nc, lt_stride;       // columns tabulated, floats per (bin, piece)
     double a, b, alpha, beta, mu, nu, N0, lambda_factor, vel_factor, ntot_factor, x_min, x_max;
     // log-domain constants of the PSD parameters (filled by the host, radop_api.cu prepare()):
     //   log(lambda) = c_inv * (c_l0 [+ log N0(T)] - log QM)          1-mom rain / graupel / snow

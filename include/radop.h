@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define RADOP_ABI_VERSION 4
+#define RADOP_ABI_VERSION 5
 
 /* ---- status codes ------------------------------------------------------- */
 enum {
@@ -225,6 +225,20 @@ int radop_set_overlap_threshold(RadopHandle *h, int64_t min_output_bytes);
  * per-gate solution automatically.  mode 1: per-gate solution always.
  * radop_get_geodesy: *used_polynomials = 1 if the last execute ran on the polynomials. */
 int radop_set_geodesy(RadopHandle *h, int mode);
+/* How the PSD x scattering-table contraction (hydrometeors.py:128-152 get_N, doppler_scatter.py:246-268
+ * einsum over the diameters) is evaluated.  mode 0 (default): through lambda-transformed tables -- the sum
+ * over the diameters of one (e, t) bin is a function of the PSD slope alone; it is tabulated in float64 when a
+ * table is first used, every piece verified against the direct sum, and evaluated per pair (k_integrate_tab).
+ * mode 1: directly, diameter by diameter (k_integrate).  radop_get_integration reports the pieces tabulated,
+ * the pieces rejected by the verification and the pairs of the last execute that were summed directly
+ * inside mode 0 (outside the tabulated range or on a rejected piece).  Any output pointer may be NULL. */
+int radop_set_integration(RadopHandle *h, int mode);
+int radop_get_integration(RadopHandle *h, int *mode, int64_t *n_pieces, int64_t *n_rejected_pieces,
+                          int64_t *n_direct_pairs, float *build_ms);
+/* Diagnostics of mode 0: why[] = direct pairs of the last execute by reason (rejected piece, slope below the
+ * tabulated range, above it, not a positive normal number); piece_status[bin * 176 + piece] of one species'
+ * table = exponent word of the first column, INT32_MIN for a rejected piece (n_status >= ne * nt * 176). */
+int radop_debug_integration(RadopHandle *h, int species, int64_t why[4], int32_t *piece_status, int64_t n_status);
 int radop_get_geodesy(RadopHandle *h, int *used_polynomials);
 
 int radop_device_outputs(RadopHandle *h, void **dev_ptr, int64_t *n_rays, int64_t *n_gates);

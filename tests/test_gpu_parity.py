@@ -280,6 +280,56 @@ def test_doppler_scheme2_against_oracle(scheme, freq):
     assert np.nanmax(np.abs(out1['RVEL'] - a)) > 0.05
 
 
+@pytest.mark.parametrize('scheme,freq,doppler', [('1mom', 5.6, 1), ('1mom', 5.6, 2), ('2mom', 9.41, 1), ('2mom', 9.41, 2)])
+def test_table_vs_direct_integration(scheme, freq, doppler):
+    """The diameter integral through the lambda-transformed tables (radop_set_integration 0, the default:
+    k_build_lamtab + k_integrate_tab) against the direct sums over the diameters (mode 1: k_integrate).
+    Both restate hydrometeors.py:128-152 x doppler_scatter.py:246-268; they must agree far inside the
+    north-star tolerances, and the direct mode must meet the oracle like the default does."""
+    conf = copy.deepcopy(CONF_1MOM)
+    conf['doppler'] = {'scheme': doppler}
+    op, model, luts = make_operator(conf, scheme, freq)
+    az = np.arange(2., 360., 24.)
+    els = [0.5, 4.0, 12.0, 40.0, 88.0]
+    rays_az, rays_el = np.tile(az, len(els)), np.repeat(els, len(az))
+    tab = op.simulate_rays(rays_az, rays_el)
+    info = op._engine.integration_info()
+    assert info['mode'] == 'table' and info['pieces'] > 0
+    # the verification at build time rejects (almost) nothing on smooth tables, and only pairs with an
+    # extreme slope (no signal left) take the per-pair direct sum
+    assert info['rejected_pieces'] <= 0.02 * info['pieces'], info
+    st = op._engine.stats()
+    assert info['direct_pairs'] <= 0.02 * st['n_active_pairs'], (info, st['n_active_pairs'])
+    op._engine.set_integration('direct')
+    dirc = op.simulate_rays(rays_az, rays_el)
+    assert op._engine.integration_info()['mode'] == 'direct'
+    op._engine.set_integration('table')
+    for k in ('ZH', 'ZV', 'KDP', 'ATT_H', 'ATT_V', 'ZDR', 'RHOHV', 'DELTA_HV', 'PHIDP', 'RVEL'):
+        a, b = tab[k].astype(np.float64), dirc[k].astype(np.float64)
+        assert np.array_equal(np.isnan(a), np.isnan(b)), k
+        ok = np.isfinite(b)
+        assert ok.sum() > 500, k
+        if k == 'RVEL':
+            # folded into the Nyquist interval: a gate sitting on the fold may land on either side
+            assert np.quantile(np.abs(a[ok] - b[ok]), 0.999) < 1e-3, k
+        elif k in ('RHOHV',):
+            err = np.max(np.abs(a[ok] - b[ok]))
+            assert err < 2e-5, (k, err)
+        elif k in ('ZDR', 'DELTA_HV', 'PHIDP'):
+            err = np.max(np.abs(a[ok] - b[ok]) / (np.abs(b[ok]) + 1e-2))
+            assert err < 1e-4, (k, err)
+        else:
+            # both modes carry float32 rounding relative to sum |table| N(D); KDP is a difference of columns
+            tol = 2e-4 if k == 'KDP' else 2e-5
+            scale = np.abs(b[ok]) + (np.nanmax(np.abs(b[ok])) * 1e-6 if k == 'KDP' else 0)
+            err = np.max(np.abs(a[ok] - b[ok]) / scale)
+            assert err < tol, (k, err)
+    pm, pl = plain(model, luts)
+    ref = O.simulate_scan(pm, pl, oracle_cfg(op), rays_az, rays_el, accum='f64', sensitivity_cut=True)
+    assert_observables_close(dirc, ref, what='direct ' + scheme)
+    assert_observables_close(tab, ref, what='table ' + scheme)
+
+
 def _spectrum_close(a, b, zh, what):
     """DSPECTRUM against the oracle: bin by bin to 1e-4 of the gate's strongest bin, cumulative
     power along the velocity axis (robust against a diameter sample sitting exactly on a
