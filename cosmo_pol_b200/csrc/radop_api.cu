@@ -852,17 +852,19 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         a2.hist = h->hist.as<int>(); a2.bin_start = h->bin_start.as<int>(); a2.tile_start = h->tile_start.as<int>();
         a2.chunk_start = h->cost_start.as<int>(); a2.totals = totals;
         a2.counter = h->flags.as<int>() + 1;
-        a2.rec = h->rec.as<PairRec>(); a2.sz_out = h->sz_out.as<float>(); a2.ice_vn = h->ice_vn.as<float2>(); a2.dop_vn = h->dop_vn.as<float2>();
+        a2.rec = h->rec.as<PairRec>(); a2.n_sbg = nc; a2.sz_out = h->sz_out.as<float>(); a2.ice_vn = h->ice_vn.as<float2>(); a2.dop_vn = h->dop_vn.as<float2>();
         if (table_mode) {
             K2tArgs at;
             at.key = h->key.as<uint16_t>(); at.p0 = h->p0.as<float>(); at.p1 = h->p1.as<float>();
             at.sub_weight = scan.sub_weight; at.sz_out = a2.sz_out; at.ice_vn = a2.ice_vn; at.dop_vn = a2.dop_vn;
             at.n_sbg = nc; at.n_fallback = h->lt_stat.as<unsigned long long>();
-            static const int occ_t = getenv("RADOP_K2T_OCC") ? atoi(getenv("RADOP_K2T_OCC")) : 3;
+            static const int occ_t = getenv("RADOP_K2T_OCC") ? atoi(getenv("RADOP_K2T_OCC")) : 4;
             const unsigned gridt = (unsigned)std::min<long long>((nc + 255) / 256, (long long)h->n_sm * 8 * occ_t);
-            if (occ_t == 2) k_integrate_tab<2><<<gridt, 256, 0, st>>>(c, at);
-            else if (occ_t == 4) k_integrate_tab<4><<<gridt, 256, 0, st>>>(c, at);
-            else k_integrate_tab<3><<<gridt, 256, 0, st>>>(c, at);
+            const size_t smem_t = 0;
+            if (occ_t == 2) k_integrate_tab<2><<<gridt, 256, smem_t, st>>>(c, at);
+            else if (occ_t == 3) k_integrate_tab<3><<<gridt, 256, smem_t, st>>>(c, at);
+            else if (occ_t == 6) k_integrate_tab<6><<<gridt, 256, smem_t, st>>>(c, at);
+            else k_integrate_tab<4><<<gridt, 256, smem_t, st>>>(c, at);
         } else {
             k_integrate<<<h->k2_blocks, RADOP_TILE_THREADS, h->k2_smem, st>>>(c, a2);
         }

@@ -1384,18 +1384,26 @@ struct K2Args {
     const long long *totals;
     int *counter;       // dynamic work-unit counter (zeroed before the launch)
     const PairRec *rec;
-    float *sz_out;      // [sbg][n_species][8]
+    float *sz_out;      // [n_species][sbg][8] (sz_plane)
+    long long n_sbg;
     float2 *ice_vn;     // [sbg] numeric fall-speed moments of the ice species
     float2 *dop_vn;     // [sbg][n_species] rcs-weighted fall-speed moments (Doppler scheme 2)
 };
 
 extern __shared__ __align__(128) unsigned char s_k2[];
 
-__device__ __forceinline__ void store_sz(float *sz_out, int nsp, int s, uint32_t sbg, const float (&v)[7], float pre)
+// sz_out is stored per species, [species][sub-beam gate][8] (32 B rows: columns 0-3 | 4-6, pad): consecutive
+// lanes of the table kernel, of the sub-beam reduction and of the beam attenuation touch consecutive rows,
+// 1 KB per warp and request, instead of one 128 B line each as with the species interleaved
+__device__ __forceinline__ size_t sz_plane(long long n_sbg, int s, int half, size_t sbg)
 {
-    float4 *dst = reinterpret_cast<float4 *>(sz_out + ((size_t)sbg * nsp + s) * 8);
-    dst[0] = make_float4(v[0] * pre, v[1] * pre, v[2] * pre, v[3] * pre);
-    dst[1] = make_float4(v[4] * pre, v[5] * pre, v[6] * pre, 0.f);
+    return ((size_t)s * (size_t)n_sbg + sbg) * 2 + half;
+}
+__device__ __forceinline__ void store_sz(float *sz_out, long long n_sbg, int s, uint32_t sbg, const float (&v)[7], float pre)
+{
+    float4 *dst = reinterpret_cast<float4 *>(sz_out);
+    dst[sz_plane(n_sbg, s, 0, sbg)] = make_float4(v[0] * pre, v[1] * pre, v[2] * pre, v[3] * pre);
+    dst[sz_plane(n_sbg, s, 1, sbg)] = make_float4(v[4] * pre, v[5] * pre, v[6] * pre, 0.f);
 }
 
 #define RADOP_NO_PAIR 0xFFFFFFFFu
@@ -1453,7 +1461,7 @@ __device__ __forceinline__ void tile_geo(const K2Args &A, const SpeciesDev &S, i
         const float a = -LOG2E * rec.p0;
         const float e0 = ex2f_approx(a * D0);
         const float v7[7] = {v[0], v[1], v[2], v[3], v[4], v[5], v[6]};
-        store_sz(A.sz_out, nsp, s, rec.sbg, v7, rec.p1 * rec.w * e0);
+        store_sz(A.sz_out, A.n_sbg, s, rec.sbg, v7, rec.p1 * rec.w * e0);
         if (NC == 8) {
             const float w_last = ex2f_approx(a * (float)((double)(nd - 1) * S.dD_d));
             A.dop_vn[(size_t)rec.sbg * nsp + s] =
@@ -1486,7 +1494,7 @@ __device__ __forceinline__ void tile_gen(const K2Args &A, const SpeciesDev &S, i
 #pragma unroll
         for (int c = 0; c < NC; ++c) v[c] = (g & 1) ? acc[g / 2][c].y : acc[g / 2][c].x;
         const float v7[7] = {v[0], v[1], v[2], v[3], v[4], v[5], v[6]};
-        store_sz(A.sz_out, nsp, s, rec.sbg, v7, rec.p1 * rec.w);
+        store_sz(A.sz_out, A.n_sbg, s, rec.sbg, v7, rec.p1 * rec.w);
         if (NC == 8) {
             const float ag = -LOG2E * rec.p0;
             A.dop_vn[(size_t)rec.sbg * nsp + s] =
@@ -1598,7 +1606,7 @@ k_integrate(const __grid_constant__ DevConfig cfg, K2Args A)
                             for (int c = 0; c < 9; ++c) v[c] = (g & 1) ? acc[g / 2][c].y : acc[g / 2][c].x;
                             const float n0 = rec.p1;
                             const float v7[7] = {v[0], v[1], v[2], v[3], v[4], v[5], v[6]};
-                            store_sz(A.sz_out, nsp, s, rec.sbg, v7, n0 * rec.w);
+                            store_sz(A.sz_out, A.n_sbg, s, rec.sbg, v7, n0 * rec.w);
                             A.ice_vn[rec.sbg] = make_float2(v[7] * n0, v[8] * n0);
                         }
                     } else {   // MODE_ICE1
@@ -1624,7 +1632,7 @@ k_integrate(const __grid_constant__ DevConfig cfg, K2Args A)
                             // N0 renormalised so that the mass integral equals QM (hydrometeors.py:1330-1339)
                             const float n0 = rec.p1 / v[9];
                             const float v7[7] = {v[0], v[1], v[2], v[3], v[4], v[5], v[6]};
-                            store_sz(A.sz_out, nsp, s, rec.sbg, v7, n0 * rec.w);
+                            store_sz(A.sz_out, A.n_sbg, s, rec.sbg, v7, n0 * rec.w);
                             if (cfg.doppler_scheme == 2) {
                                 // shape function at the two end diameters (trapezoid correction)
                                 const float D0 = __ldg(S.aux), DL = __ldg(S.aux + nd - 1);
@@ -1679,8 +1687,8 @@ __host__ __device__ inline int lt_columns(int mode, int doppler_scheme)
     if (mode == MODE_GEN12) return 9;
     return doppler_scheme == 2 ? 8 : 7;
 }
-// floats per (bin, piece): 6 x 2 NC coefficients, NC integer exponents, padded to 128 B lines
-__host__ __device__ inline int lt_stride(int nc) { return (12 * nc + ((nc + 3) & ~3) + 31) / 32 * 32; }
+// floats per (bin, piece): 6 x 2 NC coefficients, NC integer exponents, one mask word, padded to 128 B lines
+__host__ __device__ inline int lt_stride(int nc) { return (12 * nc + ((nc + 1 + 3) & ~3) + 31) / 32 * 32; }
 
 // shape(lambda, D_k) / 2^{shift(lambda)} in float64 (the common factor keeps the sum in range)
 __device__ __forceinline__ double lt_weight(const SpeciesDev &S, double lam, double lam_p, int k, double y0)
@@ -1798,74 +1806,128 @@ k_build_lamtab(const __grid_constant__ SpeciesDev S, int nc, int stride, float *
             if (zero != 0 && zero != 8) bad = true;
         }
     }
+    // layout per piece: [column][L coefficients 0..5] | [column][R coefficients 0..5] | nc exponent words |
+    // mask word: bit c = R_c is the constant +1 or -1 (a column of one sign), bit 16 + c = its sign is minus
     if (f < 2 * nc) {
-        int L0 = 0;
         if (f < nc) {
-            L0 = (int)rint(p[0]);
+            const int L0 = (int)rint(p[0]);
             p[0] -= (double)L0;
             reinterpret_cast<int *>(dst)[12 * nc + f] = (bad && f == 0) ? LT_BAD : L0;
         }
-        // layout per piece: [column][L coefficients 0..5, R coefficients 0..5], then the nc exponent words
-        float *o = (f < nc) ? dst + f * 12 : dst + (f - nc) * 12 + 6;
+        float *o = (f < nc) ? dst + f * 6 : dst + 6 * nc + (f - nc) * 6;
 #pragma unroll
         for (int j = 0; j < 6; ++j) o[j] = (float)p[j];
+    }
+    if (f == 0) {
+        unsigned mask = 0;
+        for (int c = 0; c < nc; ++c) {
+            bool plus = true, minus = true;
+            for (int j = 0; j < 8; ++j) {
+                if (fabs(s_v[j][nc + c] - 1.0) > 1e-12) plus = false;
+                if (fabs(s_v[j][nc + c] + 1.0) > 1e-12) minus = false;
+            }
+            if (plus) mask |= 1u << c;
+            if (minus) mask |= (1u << c) | (1u << (16 + c));
+        }
+        reinterpret_cast<unsigned *>(dst)[13 * nc] = mask;
     }
     if (bad && f == 0) atomicAdd(n_bad, 1);
 }
 
-// 2^e as a double, flushing what a float result could not hold anyway
-__device__ __forceinline__ double lt_pow2(int e)
+// v * 2^e in float32 for any integer e (two exact power-of-two factors; what float32 cannot hold
+// flushes to zero / infinity as a float32 sum would)
+__device__ __forceinline__ float lt_scale(float v, int e)
 {
-    if (e < -1000) return 0.0;
-    if (e > 1000) e = 1000;
-    return __hiloint2double((e + 1023) << 20, 0);
+    e = max(-252, min(252, e));
+    const int e1 = e / 2, e2 = e - e1;
+    return (v * __int_as_float((e1 + 127) << 23)) * __int_as_float((e2 + 127) << 23);
 }
 
-// table evaluation of one pair: dv[c] = F_c(lambda); a non-zero return says why the pair needs the
-// direct sum instead (1 rejected piece, 2 below / 3 above the tabulated range, 4 not a positive normal number)
-template <int NC>
-__device__ __forceinline__ int lamtab_eval(const float *__restrict__ lt_bin, float lam, double (&dv)[NC])
+// which piece of the table serves lambda, and where inside it; a non-zero return says why the pair needs
+// the direct sum instead (2 below / 3 above the tabulated range, 4 not a positive normal number; 1 = rejected
+// piece, found when the piece is read)
+__device__ __forceinline__ int lt_locate(float lam, int &piece, float &x)
 {
+    piece = 0; x = 0.f;
     if (!(lam > 0.f) || !(lam < 3.0e38f)) return 4;
     const int bits = __float_as_int(lam);
     const int e = (bits >> 23) - 127;
     if (e < -126) return 4;
-    const float m = __int_as_float((bits & 0x007fffff) | 0x3f800000);      // [1, 2)
-    const float t = (float)LT_PPO * log2f(m);                              // [0, LT_PPO)
-    int it = (int)t;
-    if (it > LT_PPO - 1) it = LT_PPO - 1;
-    const int piece = (e - LT_U0) * LT_PPO + it;
-    if (piece < 0) return 2;
-    if (piece >= LT_NP) return 3;
-    const float x = 2.f * (t - (float)it) - 1.f;
-    constexpr int stride = (12 * NC + ((NC + 3) & ~3) + 31) / 32 * 32;
-    const float4 *src = reinterpret_cast<const float4 *>(lt_bin + (size_t)piece * stride);
-    int L0[(NC + 3) & ~3];
+    const float mant = __int_as_float((bits & 0x007fffff) | 0x3f800000);   // [1, 2)
+    const float t = (float)LT_PPO * __log2f(mant);                         // [0, LT_PPO)
+    const int it = max(0, min(LT_PPO - 1, (int)t));
+    const int pc = (e - LT_U0) * LT_PPO + it;
+    if (pc < 0) return 2;
+    if (pc >= LT_NP) return 3;
+    piece = pc;
+    x = 2.f * (t - (float)it) - 1.f;
+    return 0;
+}
+
+// F_c(lambda) = m[c] * 2^ex[c] from the coefficients of one piece.  The envelope polynomials L_c are
+// read two columns at a time (12 floats = three 16 B loads); the ratio polynomial R_c is read only for the
+// columns that change sign along the diameter axis -- for a column of one sign it is the constant +-1 and
+// the piece's mask word says so (in the shipped table families every column but s10 - s8 is of one sign,
+// so a pair reads ~1.5 NC + 3 chunks instead of 3 NC + 3; the kernel is bound by the L1 wavefronts of
+// exactly these loads, ncu: l1tex__data_pipe_lsu_wavefronts 84 %).
+template <int NC>
+__device__ __forceinline__ void lt_horner(const float *__restrict__ base, float x, float (&m)[NC], int (&ex)[NC])
+{
+    const float4 *src = reinterpret_cast<const float4 *>(base);
+    int L0[((NC + 1) + 3) & ~3];
 #pragma unroll
-    for (int i = 0; i < (NC + 3) / 4; ++i) {
-        const int4 v = __ldg(reinterpret_cast<const int4 *>(src + 3 * NC) + i);
-        L0[4 * i] = v.x; L0[4 * i + 1] = v.y; L0[4 * i + 2] = v.z; L0[4 * i + 3] = v.w;
+    for (int i = 0; i < (NC + 1 + 3) / 4; ++i) {
+        const float4 v = __ldg(src + 3 * NC + i);
+        L0[4 * i] = __float_as_int(v.x); L0[4 * i + 1] = __float_as_int(v.y);
+        L0[4 * i + 2] = __float_as_int(v.z); L0[4 * i + 3] = __float_as_int(v.w);
     }
-    if (L0[0] == LT_BAD) return 1;
-    // one column at a time: 12 coefficients (three 16 B loads), two Horner chains, one ex2
+    const unsigned mask = (unsigned)L0[NC];
+    float Lv[NC];
+#pragma unroll
+    for (int k2 = 0; k2 < NC / 2; ++k2) {
+        const float4 a = __ldg(src + 3 * k2), b = __ldg(src + 3 * k2 + 1), c = __ldg(src + 3 * k2 + 2);
+        float L = b.y, M = c.w;
+        L = fmaf(L, x, b.x); M = fmaf(M, x, c.z);
+        L = fmaf(L, x, a.w); M = fmaf(M, x, c.y);
+        L = fmaf(L, x, a.z); M = fmaf(M, x, c.x);
+        L = fmaf(L, x, a.y); M = fmaf(M, x, b.w);
+        L = fmaf(L, x, a.x); M = fmaf(M, x, b.z);
+        Lv[2 * k2] = L; Lv[2 * k2 + 1] = M;
+    }
+    if (NC & 1) {
+        const float4 a = __ldg(src + 3 * (NC / 2)), b = __ldg(src + 3 * (NC / 2) + 1);
+        float L = b.y;
+        L = fmaf(L, x, b.x);
+        L = fmaf(L, x, a.w);
+        L = fmaf(L, x, a.z);
+        L = fmaf(L, x, a.y);
+        L = fmaf(L, x, a.x);
+        Lv[NC - 1] = L;
+    }
 #pragma unroll
     for (int k = 0; k < NC; ++k) {
-        const float4 a = __ldg(src + 3 * k), b = __ldg(src + 3 * k + 1), c = __ldg(src + 3 * k + 2);
-        float L = b.y, R = c.w;
-        L = fmaf(L, x, b.x); R = fmaf(R, x, c.z);
-        L = fmaf(L, x, a.w); R = fmaf(R, x, c.y);
-        L = fmaf(L, x, a.z); R = fmaf(R, x, c.x);
-        L = fmaf(L, x, a.y); R = fmaf(R, x, b.w);
-        L = fmaf(L, x, a.x); R = fmaf(R, x, b.z);
-        dv[k] = (double)(exp2f(L) * R) * lt_pow2(L0[k]);
+        float R;
+        if (mask & (1u << k)) {
+            R = (mask & (1u << (16 + k))) ? -1.f : 1.f;
+        } else {
+            const float2 *r = reinterpret_cast<const float2 *>(base + 6 * NC + 6 * k);
+            const float2 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
+            R = r2.y;
+            R = fmaf(R, x, r2.x);
+            R = fmaf(R, x, r1.y);
+            R = fmaf(R, x, r1.x);
+            R = fmaf(R, x, r0.y);
+            R = fmaf(R, x, r0.x);
+        }
+        m[k] = ex2f_approx(Lv[k]) * R;
+        ex[k] = L0[k];
     }
-    return 0;
 }
 
 // the same sums diameter by diameter, by a whole warp for ONE pair (pairs outside the tabulated
 // range or on a rejected piece): lanes stride over the diameters, shuffle reduction
 template <int NC>
-__device__ __noinline__ void warp_direct(const SpeciesDev &S, int bin_local, float lam, int lane, double (&dv)[NC])
+__device__ __noinline__ void warp_direct(const SpeciesDev &S, int bin_local, float lam, int lane, float (&dv)[NC])
 {
     const int nd = S.nd;
     float acc[NC];
@@ -1895,7 +1957,7 @@ __device__ __noinline__ void warp_direct(const SpeciesDev &S, int bin_local, flo
             for (int d = 16; d >= 1; d >>= 1) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], d);
     }
 #pragma unroll
-    for (int c = 0; c < NC; ++c) dv[c] = (double)acc[c];
+    for (int c = 0; c < NC; ++c) dv[c] = acc[c];
 }
 
 struct K2tArgs {
@@ -1908,18 +1970,28 @@ struct K2tArgs {
     unsigned long long *n_fallback;   // [4] pairs integrated directly, by reason (lamtab_eval)
 };
 
-// One species of one warp's 32 sub-beam gates: table evaluation per lane, then the lanes whose pair
-// could not be served by the table are integrated directly one after the other by the whole warp.
+// One species of one warp's 32 sub-beam gates: table evaluation per lane (the coefficient loads of lanes
+// that share a piece are broadcasts), then the lanes whose pair the table cannot serve are integrated
+// directly one after the other by the whole warp.  Staging the pieces of a warp in shared memory first
+// (one coalesced fetch per distinct piece) was measured and is slower: 2.6 ms against 2.0 ms at cfg 3.
 // Must be called by all 32 lanes (have = this lane holds an active pair of the species).
 template <int NC>
 __device__ __forceinline__ void pair_tab(const DevConfig &cfg, const K2tArgs &A, const SpeciesDev &S, int s, bool have,
                                          int bin, uint32_t sbg, float p0, float p1, float w, int lane)
 {
+    constexpr int STR = (12 * NC + ((NC + 1 + 3) & ~3) + 31) / 32 * 32;      // lt_stride(NC)
     const int nsp = cfg.n_species, nd = S.nd;
     const int bl = bin - S.bin_base;
-    double dv[NC];
+    float m[NC];
+    int ex[NC];
+    int piece;
+    float x;
     int why = 0;
-    if (have) why = lamtab_eval<NC>(S.lamtab + (size_t)bl * LT_NP * S.lt_stride, p0, dv);
+    if (have) why = lt_locate(p0, piece, x);
+    const int id = (have && !why) ? bl * LT_NP + piece : -1;
+    // out-of-range lanes read piece 0 of their bin (valid memory), the result is discarded
+    lt_horner<NC>(S.lamtab + (size_t)(id >= 0 ? id : bl * LT_NP) * STR, x, m, ex);
+    if (id >= 0 && ex[0] == LT_BAD) why = 1;
     unsigned need = __ballot_sync(0xffffffffu, why != 0);
     if (why) atomicAdd(A.n_fallback + (why - 1), 1ull);
     while (need) {
@@ -1927,21 +1999,23 @@ __device__ __forceinline__ void pair_tab(const DevConfig &cfg, const K2tArgs &A,
         need &= need - 1;
         const int bl_s = __shfl_sync(0xffffffffu, bl, src);
         const float lam_s = __shfl_sync(0xffffffffu, p0, src);
-        double ds[NC];
+        float ds[NC];
         warp_direct<NC>(S, bl_s, lam_s, lane, ds);
         if (lane == src) {
 #pragma unroll
-            for (int c = 0; c < NC; ++c) dv[c] = ds[c];
+            for (int c = 0; c < NC; ++c) { m[c] = ds[c]; ex[c] = 0; }
         }
     }
     if (!have) return;
     float v7[7];
     if (S.mode == MODE_ICE1) {
-        // N0 renormalised so that the mass integral equals QM (hydrometeors.py:1330-1339)
-        const double n0 = (double)p1 / dv[9];
+        // N0 renormalised so that the mass integral equals QM (hydrometeors.py:1330-1339): n0 = p1 / F_9
+        constexpr int C9 = NC > 9 ? 9 : 0, C8 = NC > 8 ? 8 : 0, C7 = NC > 7 ? 7 : 0;
+        const float inv9 = 1.f / m[C9];
+        const int e9 = ex[C9];
 #pragma unroll
-        for (int c = 0; c < 7; ++c) v7[c] = (float)(dv[c] * n0 * (double)w);
-        store_sz(A.sz_out, nsp, s, sbg, v7, 1.f);
+        for (int c = 0; c < 7; ++c) v7[c] = lt_scale(m[c] * inv9 * p1 * w, ex[c] - e9);
+        store_sz(A.sz_out, A.n_sbg, s, sbg, v7, 1.f);
         if (cfg.doppler_scheme == 2) {
             const float *tab = S.table + (size_t)bl * nd * S.ncol;
             const float D0 = __ldg(S.aux), DL = __ldg(S.aux + nd - 1);
@@ -1950,70 +2024,82 @@ __device__ __forceinline__ void pair_tab(const DevConfig &cfg, const K2tArgs &A,
                              c2 * __ldg(S.aux + 2 * nd) * ex2f_approx(-3.290f * LOG2E * p0 * D0);
             const float wL = 490.6f * ex2f_approx(-20.78f * LOG2E * p0 * DL) +
                              c2 * __ldg(S.aux + 3 * nd - 1) * ex2f_approx(-3.290f * LOG2E * p0 * DL);
-            const double n_ = dv[0] - 0.5 * ((double)__ldg(tab) * w0 + (double)__ldg(tab + (size_t)(nd - 1) * S.ncol) * wL);
-            const double v_ = dv[NC > 7 ? 7 : 0] - 0.5 * ((double)__ldg(tab + 7) * w0 + (double)__ldg(tab + (size_t)(nd - 1) * S.ncol + 7) * wL);
-            const double sc = 6.283185307179586 * n0 / (double)S.dD_ref;
-            A.dop_vn[(size_t)sbg * nsp + s] = make_float2((float)(v_ * sc), (float)(n_ * sc));
+            const float f0 = lt_scale(m[0], ex[0]), f7 = lt_scale(m[C7], ex[C7]);
+            const float n0 = p1 / lt_scale(m[C9], e9);
+            const float n_ = f0 - 0.5f * (__ldg(tab) * w0 + __ldg(tab + (size_t)(nd - 1) * S.ncol) * wL);
+            const float v_ = f7 - 0.5f * (__ldg(tab + 7) * w0 + __ldg(tab + (size_t)(nd - 1) * S.ncol + 7) * wL);
+            const float sc = 6.283185307179586f * n0 / S.dD_ref;
+            A.dop_vn[(size_t)sbg * nsp + s] = make_float2(v_ * sc, n_ * sc);
         } else {
-            A.ice_vn[sbg] = make_float2((float)(dv[NC > 7 ? 7 : 0] * n0), (float)(dv[NC > 8 ? 8 : 0] * n0));
+            A.ice_vn[sbg] = make_float2(lt_scale(m[C7] * inv9 * p1, ex[C7] - e9), lt_scale(m[C8] * inv9 * p1, ex[C8] - e9));
         }
         return;
     }
-    const double pre = (double)p1 * (double)w;
+    const float pre = p1 * w;
 #pragma unroll
-    for (int c = 0; c < 7; ++c) v7[c] = (float)(dv[c] * pre);
-    store_sz(A.sz_out, nsp, s, sbg, v7, 1.f);
+    for (int c = 0; c < 7; ++c) v7[c] = lt_scale(m[c] * pre, ex[c]);
+    store_sz(A.sz_out, A.n_sbg, s, sbg, v7, 1.f);
     if (S.mode == MODE_GEN12) {
-        A.ice_vn[sbg] = make_float2((float)(dv[NC > 7 ? 7 : 0] * (double)p1), (float)(dv[NC > 8 ? 8 : 0] * (double)p1));
+        constexpr int C8 = NC > 8 ? 8 : 0, C7 = NC > 7 ? 7 : 0;
+        A.ice_vn[sbg] = make_float2(lt_scale(m[C7] * p1, ex[C7]), lt_scale(m[C8] * p1, ex[C8]));
     } else if (NC == 8) {
         // trapezoid end corrections of Doppler scheme 2 (doppler2_moments)
+        constexpr int C7 = NC > 7 ? 7 : 0;
         const float *tab = S.table + (size_t)bl * nd * S.ncol;
         const float a = -LOG2E * p0;
         float yF, yL;
         if (S.mode == MODE_GEO8) { yF = __ldg(S.aux); yL = (float)((double)yF + (double)(nd - 1) * S.dD_d); }
         else { yF = __ldg(S.aux + nd); yL = __ldg(S.aux + 2 * nd - 1); }
         const float wF = ex2f_approx(a * yF), wL = ex2f_approx(a * yL);
-        const double n_ = dv[0] - 0.5 * ((double)__ldg(tab) * wF + (double)__ldg(tab + (size_t)(nd - 1) * S.ncol) * wL);
-        const double v_ = dv[NC > 7 ? 7 : 0] - 0.5 * ((double)__ldg(tab + 7) * wF + (double)__ldg(tab + (size_t)(nd - 1) * S.ncol + 7) * wL);
-        const double sc = 6.283185307179586 * (double)p1 / (double)S.dD_ref;
-        A.dop_vn[(size_t)sbg * nsp + s] = make_float2((float)(v_ * sc), (float)(n_ * sc));
+        const float f0 = lt_scale(m[0], ex[0]), f7 = lt_scale(m[C7], ex[C7]);
+        const float n_ = f0 - 0.5f * (__ldg(tab) * wF + __ldg(tab + (size_t)(nd - 1) * S.ncol) * wL);
+        const float v_ = f7 - 0.5f * (__ldg(tab + 7) * wF + __ldg(tab + (size_t)(nd - 1) * S.ncol + 7) * wL);
+        const float sc = 6.283185307179586f * p1 / S.dD_ref;
+        A.dop_vn[(size_t)sbg * nsp + s] = make_float2(v_ * sc, n_ * sc);
     }
 }
 
-// thread per sub-beam gate, in ray order: neighbouring gates share the bin and mostly the piece,
-// so the coefficient loads of a warp are broadcasts out of L1; no sort is needed.
+// Thread per sub-beam gate, in ray order (neighbouring gates share the bin and mostly the piece, so the
+// coefficient loads of a warp are broadcasts out of L1; no sort is needed).  Every iteration first issues
+// the key loads of all species, then the lambda / N0 loads of the active ones, then evaluates the species
+// one after the other.
 template <int MINB>
 __global__ void __launch_bounds__(256, MINB)
 k_integrate_tab(const __grid_constant__ DevConfig cfg, K2tArgs A)
 {
     const int ng = cfg.n_gates;
     const int lane = threadIdx.x & 31;
-    // warp-uniform trip count: the direct integration of a pair is a warp-collective step
+    // warp-uniform trip count: staging and the direct integration of a pair are warp-collective steps
     for (long long base = (long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < A.n_sbg;
          base += (long long)gridDim.x * blockDim.x) {
         const long long sbg = base + lane;
         const bool in_range = sbg < A.n_sbg;
+        unsigned long long kp[2] = {~0ull, ~0ull};          // 16-bit keys of up to 8 species
+        float P0[RADOP_NSPECIES_MAX], P1[RADOP_NSPECIES_MAX];
+#pragma unroll
+        for (int s = 0; s < RADOP_NSPECIES_MAX; ++s)
+            if (in_range && s < cfg.n_species) {
+                const unsigned long long k = (unsigned long long)__ldg(A.key + (size_t)s * A.n_sbg + sbg);
+                kp[s >> 2] = (kp[s >> 2] & ~(0xffffull << (16 * (s & 3)))) | (k << (16 * (s & 3)));
+            }
+#pragma unroll
+        for (int s = 0; s < RADOP_NSPECIES_MAX; ++s) {
+            P0[s] = 1.f; P1[s] = 0.f;
+            if (((kp[s >> 2] >> (16 * (s & 3))) & 0xffffull) != RADOP_KEY_NONE) {
+                P0[s] = __ldg(A.p0 + (size_t)s * A.n_sbg + sbg);
+                P1[s] = __ldg(A.p1 + (size_t)s * A.n_sbg + sbg);
+            }
+        }
         const int q = in_range ? (int)(((unsigned)sbg / (unsigned)ng) % (unsigned)cfg.n_sub) : 0;
         const float w = (float)__ldg(A.sub_weight + q);
-        // software pipeline over the species: the key / lambda / N0 loads of the next species are in
-        // flight while the current one is evaluated
-        uint32_t k_nxt = in_range ? (uint32_t)A.key[sbg] : RADOP_KEY_NONE;
-        float p0_nxt = 1.f, p1_nxt = 0.f;
-        if (k_nxt != RADOP_KEY_NONE) { p0_nxt = A.p0[sbg]; p1_nxt = A.p1[sbg]; }
 #pragma unroll 1
         for (int s = 0; s < cfg.n_species; ++s) {
-            const uint32_t k = k_nxt;
-            const float p0 = p0_nxt, p1 = p1_nxt;
-            if (s + 1 < cfg.n_species) {
-                const size_t o = (size_t)(s + 1) * A.n_sbg + sbg;
-                k_nxt = in_range ? (uint32_t)A.key[o] : RADOP_KEY_NONE;
-                p0_nxt = 1.f; p1_nxt = 0.f;
-                if (k_nxt != RADOP_KEY_NONE) { p0_nxt = A.p0[o]; p1_nxt = A.p1[o]; }
-            }
             const SpeciesDev &S = cfg.sp[s];
             if (S.mode == MODE_MELT) continue;
+            const uint32_t k = (uint32_t)((kp[s >> 2] >> (16 * (s & 3))) & 0xffffull);
             const bool have = k != RADOP_KEY_NONE;
             if (!__any_sync(0xffffffffu, have)) continue;
+            const float p0 = P0[s], p1 = P1[s];
             const int bin = have ? (int)k : S.bin_base;
             switch (S.lt_nc) {
             case 7: pair_tab<7>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane); break;
@@ -2155,9 +2241,9 @@ k_integrate_melting(const __grid_constant__ DevConfig cfg, K2mArgs A)
             if (lane == 0) {
                 const double prop = q / (sm * dD);             // prop_factor = q / integrate_M()
                 const double f = prop * dD * (double)rec.w;
-                float4 *dst = reinterpret_cast<float4 *>(A.sz_out + ((size_t)sbg * nsp + s) * 8);
-                dst[0] = make_float4((float)(acc[0] * f), (float)(acc[1] * f), (float)(acc[2] * f), (float)(acc[3] * f));
-                dst[1] = make_float4((float)(acc[4] * f), (float)(acc[5] * f), (float)(acc[6] * f), 0.f);
+                float4 *dst = reinterpret_cast<float4 *>(A.sz_out);
+                dst[sz_plane(A.n_sbg, s, 0, sbg)] = make_float4((float)(acc[0] * f), (float)(acc[1] * f), (float)(acc[2] * f), (float)(acc[3] * f));
+                dst[sz_plane(A.n_sbg, s, 1, sbg)] = make_float4((float)(acc[4] * f), (float)(acc[5] * f), (float)(acc[6] * f), 0.f);
                 if (A.dop_vn) {
                     float2 vn;
                     if (cfg.doppler_scheme == 2) {            // np.trapz with dx = 1 (doppler_scatter.py:286-296)
@@ -2198,6 +2284,7 @@ k_reduce_subbeams(const __grid_constant__ DevConfig cfg, K3Args A)
     const int g = (int)(idx % cfg.n_gates);
     const int ray = (int)(idx / cfg.n_gates);
     const int nsp = cfg.n_species;
+    const long long n_sbg_all = (long long)cfg.n_rays * cfg.n_sub * cfg.n_gates;
     float comb[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float rsum = 0.f, wsum = 0.f, msum = 0.f;
     float mv[RADOP_NVP];
@@ -2216,8 +2303,8 @@ k_reduce_subbeams(const __grid_constant__ DevConfig cfg, K3Args A)
         uint8_t act = A.active[sbg];
         for (int s = 0; s < nsp; ++s) {
             if (!(act & (1u << s))) continue;
-            const float4 *row = reinterpret_cast<const float4 *>(A.sz_out + (sbg * nsp + s) * 8);
-            float4 r0 = __ldg(row), r1 = __ldg(row + 1);
+            const float4 *pl = reinterpret_cast<const float4 *>(A.sz_out);
+            float4 r0 = __ldg(pl + sz_plane(n_sbg_all, s, 0, sbg)), r1 = __ldg(pl + sz_plane(n_sbg_all, s, 1, sbg));
             comb[0] += r0.x; comb[1] += r0.y; comb[2] += r0.z; comb[3] += r0.w;
             comb[4] += r1.x; comb[5] += r1.y; comb[6] += r1.z;
         }
@@ -2436,7 +2523,7 @@ k_beam_attenuation(const __grid_constant__ DevConfig cfg, K4Args A)
             for (int g0 = 0; g0 < ng; g0 += 32) {
                 const int g = g0 + lane;
                 const bool valid = g < ng && (A.active[base + g] & (1u << s));
-                float x = valid ? fac * (A.sz_out[((base + g) * nsp + s) * 8 + 6] / w) : 0.f;
+                float x = valid ? fac * (A.sz_out[sz_plane((long long)cfg.n_rays * cfg.n_sub * ng, s, 1, base + g) * 4 + 2] / w) : 0.f;
                 const unsigned bal = __ballot_sync(0xffffffffu, valid);
                 const int pos = cnt + __popc(bal & ((1u << lane) - 1u));
 #pragma unroll
