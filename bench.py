@@ -45,6 +45,8 @@ VOLUME_ELEVATIONS = [-0.2, 0.4, 1.0, 1.6, 2.5, 3.5, 4.5, 5.5, 6.5, 7.5, 8.5, 9.5
 FLOP_PER_PAIR = 28672          # 2*1024*12 contraction + 4*1024 PSD evaluation
 METRIC = 'sub-beam gates/sec for a 20-elevation volume scan'
 UNIT = 'sub-beam gates/s'
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_interp_psd launch at cfg 3 (ncu --set full, profiles/)
+K1_TRAFFIC = 1.3431e9
 
 
 def volume_config():
@@ -72,8 +74,10 @@ def workload_config(world, scaling):
                            'stream (step k gathered beside the kernels of step k+1, all gathers inside the timed region)'.format(world)
                            if world > 1 else 'single GPU',
             'scaling_mode': scaling,
-            'l2': 'no explicit flush: one step streams ~6 GB of per-gate work buffers plus a 614 MB field '
-                  'array, far larger than the 126 MB L2'}
+            'l2': 'no explicit flush: one step streams ~3 GB of per-gate work buffers (K1 outputs, sz_out) plus a 614 MB '
+                  'field array, far larger than the 126 MB L2',
+            'integration': 'diameter integral through lambda-transformed tables built at table upload (radop_set_integration 0, '
+                           'the library default); --integration direct times the per-diameter sums instead'}
 
 
 class ClockSampler(object):
@@ -398,21 +402,86 @@ def run_ours(args):
             dist.destroy_process_group()
         return 0
 
+    # ---- the direct integration kernel, timed beside the run (not part of `value`): same scan, mode 1 -----
+    direct = None
+    if world == 1 and args.integration == 'table':
+        eng.set_integration('direct')
+        for _ in range(3):
+            eng.execute()
+        eng.synchronize()
+        eng.enable_timing(True)
+        for _ in range(5):
+            eng.execute()
+        eng.synchronize()
+        direct = eng.stats()
+        eng.enable_timing(False)
+        eng.set_integration('table')
+        eng.execute()
+        eng.synchronize()
+
     burst, sustained = fp32_peaks(eng)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
     except Exception:
         pass
+    hbm_peak = float(peaks.get('hbm_gbs', 6650.0))
+    hbm_kind = ('MEASURED_PEAKS.json hbm_gbs (driver-measured copy bandwidth)' if 'hbm_gbs' in peaks else
+                'fallback of B200_PROFILING.md (MEASURED_PEAKS.json absent)')
     pairs = float(st['n_active_pairs'])
     flops = FLOP_PER_PAIR * pairs
-    achieved = flops / (st['ms_integrate'] * 1e-3) / 1e12 if st['ms_integrate'] > 0 else None
-    # what the kernel really executes (7 combined columns, Horner recurrence): FP32 lane operations
-    exec_flops = float(sum(n * f for n, f in zip(st['pairs_by_species'], st['exec_flop_per_pair'])))
-    executed = exec_flops / (st['ms_integrate'] * 1e-3) / 1e12 if st['ms_integrate'] > 0 else None
     sbg1 = float(scan.n_subbeam_gates)
     nvar = 9
-    alg_bytes = sbg1 * (nvar * 32 + 32) + scan.n_rays * scan.n_gates * 52 + st['n_lut_bins'] * 49152
+    # bytes per sub-beam gate n_var * 32 + 32 (8 corners x n_var x 4 B + trajectory / outputs)
+    k1_bytes = sbg1 * (nvar * 32 + 32)
+    alg_bytes = k1_bytes + scan.n_rays * scan.n_gates * 52 + st['n_lut_bins'] * 49152
+    table_mode = args.integration == 'table'
+    k1_ms = st['ms_interp']
+    dstats = direct if direct is not None else (st if not table_mode else None)
+    dsec = None
+    if dstats is not None and dstats['ms_integrate'] > 0:
+        exec_flops = float(sum(n * f for n, f in zip(dstats['pairs_by_species'], dstats['exec_flop_per_pair'])))
+        dsec = {'kernel': 'k_integrate', 'kernel_ms': dstats['ms_integrate'], 'step_ms': dstats['ms_total'],
+                'bound': 'fp32', 'peak_tflops': sustained,
+                'peak_kind': 'measured here: dependent-free FFMA probe, sustained (median of back-to-back runs); '
+                             'burst {:.1f}'.format(burst),
+                'algorithmic_tflops': flops / (dstats['ms_integrate'] * 1e-3) / 1e12,
+                'executed_tflops': exec_flops / (dstats['ms_integrate'] * 1e-3) / 1e12,
+                'executed_frac': exec_flops / (dstats['ms_integrate'] * 1e-3) / 1e12 / sustained,
+                'executed_flop_per_launch': exec_flops, 'algorithmic_flop_per_launch': flops,
+                'flop_per_active_pair': FLOP_PER_PAIR, 'fp32_floor_ms': flops / (sustained * 1e12) * 1e3,
+                'note': 'radop_set_integration(1): sums over the 1024 diameters per pair (7 combined columns, Horner '
+                        'recurrence); timed in 5 extra steps after the timed region'}
+    if table_mode:
+        roof = {'bound': 'hbm', 'kernel': 'k_interp_psd', 'achieved': k1_bytes / (k1_ms * 1e-3) / 1e9 if k1_ms > 0 else None,
+                'peak': hbm_peak, 'unit': 'GB/s',
+                'frac': (k1_bytes / (k1_ms * 1e-3) / 1e9 / hbm_peak) if k1_ms > 0 else None,
+                # dram__bytes_read.sum + dram__bytes_write.sum of one k_interp_psd launch of this workload
+                # (ncu --set full capture, profiles/r01f_k_interp_psd_full.txt: 165.3 MB read + 1177.7 MB written)
+                'traffic': K1_TRAFFIC, 'peak_kind': hbm_kind, 'kernel_ms': k1_ms,
+                'algorithmic_bytes_per_launch': k1_bytes, 'bytes_per_sub_beam_gate': nvar * 32 + 32,
+                'note': 'dominant kernel of the step since the diameter integral runs through the lambda-transformed '
+                        'tables (k_integrate_tab). achieved = ALGORITHMIC bytes (SURVEY.md 8d: 320 B per sub-beam gate) / '
+                        'launch time; the DRAM traffic is 8x smaller because neighbouring sub-beams and gates share model '
+                        'cells in L2, so the kernel sits at its instruction-issue limit (float64 geodesy polynomials, '
+                        'bit-exact float32 interpolation arithmetic; ncu: profiles/), not at the HBM roofline.',
+                'hbm_floor_ms': alg_bytes / (hbm_peak * 1e9) * 1e3,
+                'algorithmic_fp32_floor_ms': flops / (sustained * 1e12) * 1e3,
+                'step_vs_algorithmic_fp32_floor': (flops / (sustained * 1e12) * 1e3) / (ms / args.steps),
+                'integrate_tab': {'kernel': 'k_integrate_tab', 'kernel_ms': st['ms_integrate'],
+                                  'pairs_per_s': pairs / (st['ms_integrate'] * 1e-3) if st['ms_integrate'] > 0 else None,
+                                  'algorithmic_tflops_equivalent': flops / (st['ms_integrate'] * 1e-3) / 1e12
+                                  if st['ms_integrate'] > 0 else None,
+                                  'bound': 'L1 wavefronts of the coefficient loads (ncu l1tex__data_pipe_lsu_wavefronts)'},
+                'direct_integration': dsec,
+                'pairs_by_species': dict(zip(eng.species_order, st['pairs_by_species'])),
+                'active_pairs_per_launch': pairs}
+    else:
+        roof = dict(dsec or {})
+        roof.update({'bound': 'fp32', 'kernel': 'k_integrate', 'achieved': dsec and dsec['algorithmic_tflops'],
+                     'peak': sustained, 'unit': 'TFLOP/s', 'frac': dsec and dsec['algorithmic_tflops'] / sustained,
+                     'traffic': 1.4231e9, 'pairs_by_species': dict(zip(eng.species_order, st['pairs_by_species'])),
+                     'hbm_floor_ms': alg_bytes / (hbm_peak * 1e9) * 1e3})
     line = {
         'metric': METRIC, 'value': total_sbg / (ms * 1e-3 / args.steps), 'unit': UNIT, 'n_gpus': world,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True,
@@ -423,26 +492,7 @@ def run_ours(args):
                 'call': 'radop_simulate (C-ABI, host buffers) per rank'},
         'gpu_launches': launches,
         'clocks': clocks,
-        'roofline': {'bound': 'fp32', 'kernel': 'k_integrate', 'achieved': achieved, 'peak': sustained, 'unit': 'TFLOP/s',
-                     'frac': (achieved / sustained) if achieved else None,
-                     # dram__bytes_read.sum + dram__bytes_write.sum of one k_integrate launch of this workload
-                     # (ncu --set full capture, profiles/r01c_k_integrate_full.txt: 505.7 MB + 917.4 MB)
-                     'traffic': 1.4231e9,
-                     'peak_kind': 'measured here: dependent-free FFMA probe, sustained (median of back-to-back runs); '
-                                  'burst {:.1f}. MEASURED_PEAKS.json holds no FP32 figure (hbm {} GB/s)'.format(
-                                      burst, peaks.get('hbm_gbs')),
-                     'note': 'achieved counts the ALGORITHMIC 28672 flop per active pair (SURVEY.md 8d: 12-column '
-                             'contraction + per-diameter PSD evaluation); the kernel executes fewer (7 linear '
-                             'combinations of the 12 columns, geometric recurrence instead of exp per diameter), so '
-                             'frac can exceed 1. executed_* is the FP32 work actually issued against the same peak.',
-                     'executed_tflops': executed, 'executed_frac': (executed / sustained) if executed else None,
-                     'executed_flop_per_launch': exec_flops,
-                     'pairs_by_species': dict(zip(eng.species_order, st['pairs_by_species'])),
-                     'step_frac_of_fp32_floor': (flops / (sustained * 1e12) * 1e3) / (ms / args.steps),
-                     'algorithmic_flop_per_launch': flops, 'flop_per_active_pair': FLOP_PER_PAIR,
-                     'active_pairs_per_launch': pairs, 'kernel_ms': st['ms_integrate'],
-                     'hbm_floor_ms': alg_bytes / (peaks.get('hbm_gbs', 6650.0) * 1e9) * 1e3,
-                     'fp32_floor_ms': flops / (sustained * 1e12) * 1e3},
+        'roofline': roof,
         'stages_ms': {'interp_psd': st['ms_interp'], 'bin_sort': st['ms_sort'], 'integrate': st['ms_integrate'],
                       'reduce_epilogue': st['ms_reduce'], 'total': st['ms_total'], 'n_timed': st['n_timed']},
         'workload_stats': {'sub_beam_gates_per_gpu': sbg1, 'active_pairs_per_gpu': pairs, 'active_pair_fraction':

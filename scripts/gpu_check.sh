@@ -19,7 +19,13 @@ if [[ $what == all || $what == ncu ]]; then
       --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
   echo "ncu list rc=$?"
   timeout 600 $CMD > gpurun_out/plain2.log 2>&1 &&
-  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k_integrate -s 3 -c 1 \
-      -f -o gpurun_out/prof_integrate $CMD > gpurun_out/ncu_full.log 2>&1
+  timeout 1200 ncu --set full --clock-control none --import-source on -k "regex:k_interp_psd<1>" -s 3 -c 1 \
+      -f -o gpurun_out/prof_k1 $CMD > gpurun_out/ncu_full.log 2>&1
   echo "ncu full rc=$?"
+fi
+if [[ $what == all || $what == ncu ]]; then
+  timeout 600 $CMD > gpurun_out/plain3.log 2>&1 &&
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k_integrate_tab -s 3 -c 1 \
+      -f -o gpurun_out/prof_k2t $CMD > gpurun_out/ncu_full2.log 2>&1
+  echo "ncu full (k_integrate_tab) rc=$?"
 fi
