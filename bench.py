@@ -278,6 +278,9 @@ def run_ours(args):
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     quiet = open(os.devnull, 'w')
     stdout, sys.stdout = sys.stdout, quiet            # the host layer prints like the reference does
+    sys.__stdout__.flush()
+    fd_out = os.dup(1)                                # native libraries (NCCL's version banner) write to fd 1:
+    os.dup2(2, 1)                                     # keep stdout for the ONE JSON line
 
     conf = volume_config()
     model, luts = build_inputs()
@@ -397,6 +400,8 @@ def run_ours(args):
     else:
         total_sbg, total_pairs = float(scan.n_subbeam_gates), float(st['n_active_pairs'])
     sys.stdout = stdout
+    os.dup2(fd_out, 1)
+    os.close(fd_out)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

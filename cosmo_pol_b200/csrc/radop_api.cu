@@ -627,6 +627,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         if (rc) return rc;
     }
     DevConfig &c = h->cfg;
+    c.sum_species = (h->integration_mode == 0 && !c.with_melting && c.doppler_scheme != 3) ? 1 : 0;
     const int nsp = c.n_species, ng = c.n_gates;
     const int n_rays = h->n_rays;
     const size_t n_rg = (size_t)n_rays * ng;

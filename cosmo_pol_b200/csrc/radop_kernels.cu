@@ -1977,7 +1977,7 @@ struct K2tArgs {
 // Must be called by all 32 lanes (have = this lane holds an active pair of the species).
 template <int NC>
 __device__ __forceinline__ void pair_tab(const DevConfig &cfg, const K2tArgs &A, const SpeciesDev &S, int s, bool have,
-                                         int bin, uint32_t sbg, float p0, float p1, float w, int lane)
+                                         int bin, uint32_t sbg, float p0, float p1, float w, int lane, float (&acc)[7])
 {
     constexpr int STR = (12 * NC + ((NC + 1 + 3) & ~3) + 31) / 32 * 32;      // lt_stride(NC)
     const int nsp = cfg.n_species, nd = S.nd;
@@ -2015,7 +2015,10 @@ __device__ __forceinline__ void pair_tab(const DevConfig &cfg, const K2tArgs &A,
         const int e9 = ex[C9];
 #pragma unroll
         for (int c = 0; c < 7; ++c) v7[c] = lt_scale(m[c] * inv9 * p1 * w, ex[c] - e9);
-        store_sz(A.sz_out, A.n_sbg, s, sbg, v7, 1.f);
+        if (cfg.sum_species) {
+#pragma unroll
+            for (int c = 0; c < 7; ++c) acc[c] += v7[c];
+        } else store_sz(A.sz_out, A.n_sbg, s, sbg, v7, 1.f);
         if (cfg.doppler_scheme == 2) {
             const float *tab = S.table + (size_t)bl * nd * S.ncol;
             const float D0 = __ldg(S.aux), DL = __ldg(S.aux + nd - 1);
@@ -2038,7 +2041,10 @@ __device__ __forceinline__ void pair_tab(const DevConfig &cfg, const K2tArgs &A,
     const float pre = p1 * w;
 #pragma unroll
     for (int c = 0; c < 7; ++c) v7[c] = lt_scale(m[c] * pre, ex[c]);
-    store_sz(A.sz_out, A.n_sbg, s, sbg, v7, 1.f);
+    if (cfg.sum_species) {
+#pragma unroll
+        for (int c = 0; c < 7; ++c) acc[c] += v7[c];
+    } else store_sz(A.sz_out, A.n_sbg, s, sbg, v7, 1.f);
     if (S.mode == MODE_GEN12) {
         constexpr int C8 = NC > 8 ? 8 : 0, C7 = NC > 7 ? 7 : 0;
         A.ice_vn[sbg] = make_float2(lt_scale(m[C7] * p1, ex[C7]), lt_scale(m[C8] * p1, ex[C8]));
@@ -2092,6 +2098,9 @@ k_integrate_tab(const __grid_constant__ DevConfig cfg, K2tArgs A)
         }
         const int q = in_range ? (int)(((unsigned)sbg / (unsigned)ng) % (unsigned)cfg.n_sub) : 0;
         const float w = (float)__ldg(A.sub_weight + q);
+        // sum over the species in the reference's order (doppler_scatter.py:148-158), kept in registers
+        float acc[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        bool any = false;
 #pragma unroll 1
         for (int s = 0; s < cfg.n_species; ++s) {
             const SpeciesDev &S = cfg.sp[s];
@@ -2099,15 +2108,17 @@ k_integrate_tab(const __grid_constant__ DevConfig cfg, K2tArgs A)
             const uint32_t k = (uint32_t)((kp[s >> 2] >> (16 * (s & 3))) & 0xffffull);
             const bool have = k != RADOP_KEY_NONE;
             if (!__any_sync(0xffffffffu, have)) continue;
+            any |= have;
             const float p0 = P0[s], p1 = P1[s];
             const int bin = have ? (int)k : S.bin_base;
             switch (S.lt_nc) {
-            case 7: pair_tab<7>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane); break;
-            case 8: pair_tab<8>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane); break;
-            case 9: pair_tab<9>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane); break;
-            default: pair_tab<10>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane); break;
+            case 7: pair_tab<7>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane, acc); break;
+            case 8: pair_tab<8>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane, acc); break;
+            case 9: pair_tab<9>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane, acc); break;
+            default: pair_tab<10>(cfg, A, S, s, have, bin, (uint32_t)sbg, p0, p1, w, lane, acc); break;
             }
         }
+        if (cfg.sum_species && any) store_sz(A.sz_out, A.n_sbg, 0, (uint32_t)sbg, acc, 1.f);
     }
 }
 
@@ -2301,8 +2312,8 @@ k_reduce_subbeams(const __grid_constant__ DevConfig cfg, K3Args A)
         if (m != 0) continue;
         float w = (float)A.sub_weight[q];
         uint8_t act = A.active[sbg];
-        for (int s = 0; s < nsp; ++s) {
-            if (!(act & (1u << s))) continue;
+        for (int s = 0; s < (cfg.sum_species ? (act ? 1 : 0) : nsp); ++s) {
+            if (!cfg.sum_species && !(act & (1u << s))) continue;
             const float4 *pl = reinterpret_cast<const float4 *>(A.sz_out);
             float4 r0 = __ldg(pl + sz_plane(n_sbg_all, s, 0, sbg)), r1 = __ldg(pl + sz_plane(n_sbg_all, s, 1, sbg));
             comb[0] += r0.x; comb[1] += r0.y; comb[2] += r0.z; comb[3] += r0.w;

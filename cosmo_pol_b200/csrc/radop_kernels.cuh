@@ -78,6 +78,8 @@ struct DevConfig {
     double vel_min, vel_res, inv_vel_res;
     // broadening of the sub-beam spectra (doppler_scatter.py:727-801): bit 0 turbulence, bit 1 antenna motion
     int with_melting;
+    int sum_species;            // sz_out holds ONE row per sub-beam gate, already summed over the species (table mode
+                                // without melting species and without Doppler spectra, whose kernels need the rows per species)
     int brd_mode;
     float brd_motion_num;       // float32(wavelength / 100 * antenna_speed)
     double brd_motion_den;      // 2 pi deg2rad(beamwidth)

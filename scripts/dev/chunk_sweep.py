@@ -13,7 +13,7 @@ op.set_lut(luts); op.load_model(model)
 eng = op._prepare_engine()
 az, el = bench.volume_rays()
 scan = op.build_scan(az, el)
-for chunk in (16000000, 8000000, 5400000, 4000000, 2700000, 2000000, 1000000):
+for chunk in (16000000, 8000000, 5400000, 4000000, 2700000, 2000000, 1350000, 1000000):
     eng.set_chunk(chunk)
     for _ in range(3):
         eng.simulate(scan)
