@@ -19,7 +19,7 @@ if [[ $what == all || $what == ncu ]]; then
       --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
   echo "ncu list rc=$?"
   timeout 600 $CMD > gpurun_out/plain2.log 2>&1 &&
-  timeout 1200 ncu --set full --clock-control none --import-source on -k "regex:k_interp_psd<1>" -s 3 -c 1 \
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k_interp_psd -s 4 -c 1 \
       -f -o gpurun_out/prof_k1 $CMD > gpurun_out/ncu_full.log 2>&1
   echo "ncu full rc=$?"
 fi
