@@ -859,13 +859,10 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             at.key = h->key.as<uint16_t>(); at.p0 = h->p0.as<float>(); at.p1 = h->p1.as<float>();
             at.sub_weight = scan.sub_weight; at.sz_out = a2.sz_out; at.ice_vn = a2.ice_vn; at.dop_vn = a2.dop_vn;
             at.n_sbg = nc; at.n_fallback = h->lt_stat.as<unsigned long long>();
-            static const int occ_t = getenv("RADOP_K2T_OCC") ? atoi(getenv("RADOP_K2T_OCC")) : 4;
-            const unsigned gridt = (unsigned)std::min<long long>((nc + 255) / 256, (long long)h->n_sm * 8 * occ_t);
-            const size_t smem_t = 0;
-            if (occ_t == 2) k_integrate_tab<2><<<gridt, 256, smem_t, st>>>(c, at);
-            else if (occ_t == 3) k_integrate_tab<3><<<gridt, 256, smem_t, st>>>(c, at);
-            else if (occ_t == 6) k_integrate_tab<6><<<gridt, 256, smem_t, st>>>(c, at);
-            else k_integrate_tab<4><<<gridt, 256, smem_t, st>>>(c, at);
+            // 4 CTAs of 256 per SM (64 registers), 8 waves of CTAs; measured against 2, 3 and 6 CTAs per SM and
+            // against 4 ... all-at-once waves (profiles/README.md)
+            const unsigned gridt = (unsigned)std::min<long long>((nc + 255) / 256, (long long)h->n_sm * 32);
+            k_integrate_tab<4><<<gridt, 256, 0, st>>>(c, at);
         } else {
             k_integrate<<<h->k2_blocks, RADOP_TILE_THREADS, h->k2_smem, st>>>(c, a2);
         }
