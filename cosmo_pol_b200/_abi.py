@@ -25,7 +25,7 @@ EXPORTS = ['radop_abi_version', 'radop_create', 'radop_destroy', 'radop_last_err
            'radop_execute', 'radop_fetch', 'radop_synchronize', 'radop_device_outputs', 'radop_get_stream',
            'radop_get_stats', 'radop_enable_timing', 'radop_debug_indices', 'radop_measure_fp32_peak',
            'radop_get_all_radar_pts', 'radop_selftest_division', 'radop_set_chunk', 'radop_set_overlap_threshold',
-           'radop_set_geodesy', 'radop_get_geodesy', 'radop_set_integration', 'radop_get_integration', 'radop_debug_integration']
+           'radop_set_geodesy', 'radop_get_geodesy', 'radop_set_integration', 'radop_get_integration', 'radop_debug_integration', 'radop_set_search']
 
 (RADOP_OK, RADOP_ERR_CUDA, RADOP_ERR_ARG, RADOP_ERR_OUT_OF_DOMAIN, RADOP_ERR_LUT, RADOP_ERR_STATE,
  RADOP_ERR_UNSUPPORTED) = range(7)
@@ -119,6 +119,7 @@ def load_library():
     lib.radop_set_geodesy.argtypes = [C.c_void_p, C.c_int]
     lib.radop_get_geodesy.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
     lib.radop_set_integration.argtypes = [C.c_void_p, C.c_int]
+    lib.radop_set_search.argtypes = [C.c_void_p, C.c_int]
     lib.radop_debug_integration.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64), C.c_void_p, C.c_int64]
     lib.radop_get_integration.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int64), C.POINTER(C.c_int64),
                                           C.POINTER(C.c_int64), C.POINTER(C.c_float)]
@@ -423,6 +424,10 @@ class Engine(object):
         v = C.c_int(0)
         self._check(self.lib.radop_get_geodesy(self.h, C.byref(v)))
         return bool(v.value)
+
+    def set_search(self, mode):
+        """Level search of the interpolation: 0 guessed window with bisection as the fallback (default), 1 bisection."""
+        self._check(self.lib.radop_set_search(self.h, C.c_int(int(mode))))
 
     def set_integration(self, mode):
         """How the diameter integral (get_N x lookup_line, doppler_scatter.py:246-268) is evaluated.

@@ -68,7 +68,8 @@ struct RadopHandle_ {
     double rot[9];
     uint32_t var_mask = 0;
     int z_strict = 0;
-    DevBuf z_t, fields, stage;
+    DevBuf z_t, fields, stage, lev_guess;
+    int search_mode = 0;         // 0: guessed window + bisection when it misses, 1: bisection always
     LutHost lut[RADOP_NSPECIES_MAX];   // indexed by RADOP_SP_*
     // scan
     bool have_scan = false, executed = false;
@@ -169,7 +170,7 @@ int radop_destroy(RadopHandle *h)
     if (!h) return RADOP_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    DevBuf *bufs[] = {&h->geo_poly, &h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
+    DevBuf *bufs[] = {&h->lev_guess, &h->geo_poly, &h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
                       &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
                       &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
                       &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_st, &h->attw, &h->spec_acc, &h->spec_out, &h->d3_std, &h->sub_acc, &h->brd_flag, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
@@ -244,6 +245,19 @@ int radop_upload_grid(RadopHandle *h, int nz, int ny, int nx, const float *zleve
         CU(h, cudaMemcpyAsync(&bad, h->flags.p, 4, cudaMemcpyDeviceToHost, h->stream));
         CU(h, cudaStreamSynchronize(h->stream));
         h->z_strict = bad ? 0 : 1;
+    }
+    {   // level against normalised height for the column in the middle of the grid (first guess of the search)
+        std::vector<uint8_t> g(RADOP_NGUESS, 0);
+        const size_t cidx = (size_t)(ny / 2) * nx + nx / 2, plane = (size_t)ny * nx;
+        const double top = zlevels[cidx], bot = zlevels[(size_t)(nz - 1) * plane + cidx];
+        int i = 0;
+        for (int t = RADOP_NGUESS - 1; t >= 0; --t) {        // heights descending, levels ascending
+            const double hh = bot + (top - bot) * ((double)t + 0.5) / RADOP_NGUESS;
+            while (i + 1 <= nz - 2 && (double)zlevels[(size_t)(i + 1) * plane + cidx] >= hh) ++i;
+            g[t] = (uint8_t)std::min(i, 255);
+        }
+        CU(h, h->lev_guess.reserve(RADOP_NGUESS));
+        CU(h, cudaMemcpy(h->lev_guess.p, g.data(), RADOP_NGUESS, cudaMemcpyHostToDevice));
     }
     CU(h, cudaStreamSynchronize(h->stream));
     h->nz = nz; h->ny = ny; h->nx = nx;
@@ -499,6 +513,7 @@ static int prepare(RadopHandle *h)
     memcpy(c.rot, h->rot, sizeof c.rot);
     c.var_mask = h->var_mask;
     c.z_strict = h->z_strict;
+    c.lev_guess = (h->search_mode == 0 && h->nz >= 8 && h->nz <= 256) ? h->lev_guess.as<uint8_t>() : nullptr;
     c.n_species = p.n_species;
     c.two_moment = p.two_moment; c.doppler_scheme = p.doppler_scheme; c.with_attenuation = p.with_attenuation;
     c.sensitivity_mode = p.sensitivity_mode; c.output_model_vars = p.output_model_vars; c.keep_debug = p.keep_debug;
@@ -1062,6 +1077,14 @@ int radop_set_geodesy(RadopHandle *h, int mode)
 {
     if (!h || (mode != 0 && mode != 1)) return RADOP_ERR_ARG;
     h->geodesy_mode = mode;
+    return RADOP_OK;
+}
+
+int radop_set_search(RadopHandle *h, int mode)
+{
+    if (!h || (mode != 0 && mode != 1)) return RADOP_ERR_ARG;
+    h->search_mode = mode;
+    h->executed = false;
     return RADOP_OK;
 }
 

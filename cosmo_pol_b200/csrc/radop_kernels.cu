@@ -531,8 +531,10 @@ struct CellGeom {
 // binary search (interpolation_c.c:108-135) then returns the largest index i <= nz-2 with
 // col[i] >= h (an exact match is always probed, the last level never is), which the four
 // neighbour columns find together in ceil(log2(nz-1)) rounds of independent loads.
+#define RADOP_NGUESS 1024
 __device__ __forceinline__ void locate_cell(const float *__restrict__ z_t, int nz, int ny, int nx, float pos0,
-                                            float pos1, float h, bool strict, CellGeom &c)
+                                            float pos1, float h, bool strict, CellGeom &c,
+                                            const uint8_t *__restrict__ guess = nullptr)
 {
     c.iy = (int)floorf(pos0);
     c.ix = (int)floorf(pos1);
@@ -561,15 +563,44 @@ __device__ __forceinline__ void locate_cell(const float *__restrict__ z_t, int n
         if (h > top0 || h > top1 || h > top2 || h > top3) { c.status = 1; return; }
         const float bot[4] = {t0, t1, t2, t3};
         int idx[4] = {0, 0, 0, 0};
-        int step = 1;
-        while (2 * step <= nz - 2) step *= 2;
-        for (; step > 0; step >>= 1) {
-            float v[4];
+        unsigned todo = 0xfu;          // columns that still need the bisection
+        if (guess) {
+            // One round trip instead of six: the level is guessed from the height normalised by the column's
+            // own top and bottom (table of a reference column, radop_upload_grid: exact for sigma-like levels,
+            // close for hybrid ones), four consecutive levels around the guess are read, and the answer --
+            // the largest i <= nz - 2 with col[i] >= h, unique in a strictly descending column -- is taken
+            // from them when they bracket h.  A column whose window misses takes the bisection below, so the
+            // result is the reference's in every case.
+            const float top[4] = {top0, top1, top2, top3};
+            int a[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) v[k] = __ldg(col[k] + min(idx[k] + step, nz - 2));
+            for (int k = 0; k < 4; ++k) {
+                const float eta = __fdividef(h - bot[k], top[k] - bot[k]);
+                const int t = min(max((int)(eta * (float)RADOP_NGUESS), 0), RADOP_NGUESS - 1);
+                a[k] = min(max((int)__ldg(guess + t) - 1, 0), nz - 4);
+            }
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                if (idx[k] + step <= nz - 2 && v[k] >= h) idx[k] += step;
+            for (int k = 0; k < 4; ++k) {
+                const float *w = col[k] + a[k];
+                const int cnt = (__ldg(w) >= h) + (__ldg(w + 1) >= h) + (__ldg(w + 2) >= h) + (__ldg(w + 3) >= h);
+                const bool ok = (cnt >= 1 || a[k] == 0) && (cnt <= 3 || a[k] + 3 >= nz - 2);
+                if (ok) {
+                    idx[k] = min(a[k] + max(cnt, 1) - 1, nz - 2);
+                    todo &= ~(1u << k);
+                }
+            }
+        }
+        if (todo) {
+            int step = 1;
+            while (2 * step <= nz - 2) step *= 2;
+            for (; step > 0; step >>= 1) {
+                float v[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) v[k] = (todo & (1u << k)) ? __ldg(col[k] + min(idx[k] + step, nz - 2)) : 0.f;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if ((todo & (1u << k)) && idx[k] + step <= nz - 2 && v[k] >= h) idx[k] += step;
+            }
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
@@ -918,7 +949,7 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const void *__
             pos1 = div_const(__fsub_rn(crlon, cfg.llc[0]), cfg.res[0], cfg.rres[0]);
         }
         if (in_range) {
-            locate_cell(z_t, cfg.nz, cfg.ny, cfg.nx, pos0, pos1, h_g, cfg.z_strict != 0, c);
+            locate_cell(z_t, cfg.nz, cfg.ny, cfg.nx, pos0, pos1, h_g, cfg.z_strict != 0, c, cfg.lev_guess);
             o.mask[sbg] = (int8_t)c.status;
             if (o.dbg_cell) {
                 o.dbg_cell[2 * sbg] = c.iy;

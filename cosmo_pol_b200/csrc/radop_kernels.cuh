@@ -70,6 +70,7 @@ struct DevConfig {
     int n_species, total_bins;
     int two_moment, doppler_scheme, with_attenuation, sensitivity_mode;
     int z_strict;               // every z-level column is strictly descending (fast column search)
+    const uint8_t *lev_guess;   // [1024] level of a reference column against the normalised height, or null
     int output_model_vars, keep_debug, ice_numeric;   // ice_numeric: species index with numeric v,n or -1
     float wavelength, k_squared, radial_res;
     float sens0, sens1;

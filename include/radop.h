@@ -225,6 +225,11 @@ int radop_set_overlap_threshold(RadopHandle *h, int64_t min_output_bytes);
  * per-gate solution automatically.  mode 1: per-gate solution always.
  * radop_get_geodesy: *used_polynomials = 1 if the last execute ran on the polynomials. */
 int radop_set_geodesy(RadopHandle *h, int mode);
+/* Level search in strictly descending z-level columns (interpolation_c.c:108-135 binary_search): mode 0 (default)
+ * guesses the level from the height normalised by the column's own top and bottom (table of the grid's middle column,
+ * made by radop_upload_grid), reads four consecutive levels around the guess and takes the reference's answer from them
+ * when they bracket the height, else bisects; mode 1 bisects always.  The indices are the same in both modes. */
+int radop_set_search(RadopHandle *h, int mode);
 /* How the PSD x scattering-table contraction (hydrometeors.py:128-152 get_N, doppler_scatter.py:246-268
  * einsum over the diameters) is evaluated.  mode 0 (default): through lambda-transformed tables -- the sum
  * over the diameters of one (e, t) bin is a function of the PSD slope alone; it is tabulated in float64 when a

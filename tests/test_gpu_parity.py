@@ -100,6 +100,52 @@ def test_non_monotone_columns_take_reference_search():
                 assert np.array_equal(a[ok].view(np.uint32), b[ok].view(np.uint32)), (r, q, name)
 
 
+def test_guessed_level_search_equals_bisection_on_hybrid_levels():
+    """radop_set_search: the level guessed from the normalised height (exact for the sigma-like synthetic levels)
+    misses on hybrid levels whose terrain influence decays with height; those columns bisect.  Levels, status and
+    interpolated values must equal the reference's (interpolation_c.c:108-135) in both modes, bit for bit."""
+    op, model, luts = make_operator(CONF_1MOM)
+    z = model['T'].attributes['z-levels'].astype(np.float64)
+    nz = z.shape[0]
+    topo, top = z[-1], z[0]
+    k = np.arange(nz, dtype=np.float64)
+    frac = ((nz - 1 - k) / (nz - 1)) ** 1.8
+    decay = np.exp(-4.0 * frac)[:, None, None]                 # terrain influence fading out aloft (SLEVE-like)
+    zh = (400.0 + (top[None] - 400.0) * frac[:, None, None] + (topo[None] - 400.0) * decay * (1 - frac[:, None, None]))
+    zh[-1] = topo
+    zh = zh.astype(np.float32)
+    assert np.all(np.diff(zh, axis=0) < 0)                      # still strictly descending
+    attrs = dict(model['T'].attributes)
+    attrs['z-levels'] = zh
+    hyb = {kk: type(v)(kk, v.data, attrs) for kk, v in model.items()}
+    op.load_model(hyb)
+    az, el = np.array([33.0, 214.0, 120.0]), np.array([0.5, 6.0, 25.0])
+    pm, pl = plain(hyb, luts)
+    cfg = oracle_cfg(op)
+    results = []
+    for mode in (0, 1):
+        eng = op._prepare_engine(keep_debug=True)
+        eng.set_search(mode)
+        scan = op.build_scan(az, el)
+        out = eng.simulate(scan)
+        dbg = eng.debug_indices(scan)
+        results.append((np.array(out['ZH'], copy=True), dbg['level'].copy(), dbg['values'].copy()))
+        for r in range(len(az)):
+            ref = O.simulate_ray(pm, pl, cfg, az[r], el[r], accum='f64', debug=True)
+            for q, sub in enumerate(ref['subs']):
+                _, cell, level, status = sub['dbg']
+                assert np.array_equal(dbg['level'][r, q], level), (mode, r, q)
+                assert np.array_equal(dbg['status'][r, q], status), (mode, r, q)
+                for i, name in enumerate(dbg['var_names']):
+                    a, b = dbg['values'][r, q, :, i], sub['values'][name]
+                    ok = np.isfinite(b) & np.isfinite(a)
+                    assert np.array_equal(a[ok].view(np.uint32), b[ok].view(np.uint32)), (mode, r, q, name)
+    eng.set_search(0)
+    assert np.array_equal(results[0][1], results[1][1])
+    assert np.array_equal(results[0][0], results[1][0], equal_nan=True)
+    assert np.array_equal(results[0][2], results[1][2], equal_nan=True)
+
+
 @pytest.mark.parametrize('scheme,freq', [('1mom', 5.6), ('2mom', 9.41)])
 def test_indices_and_interpolated_values_bit_exact(scheme, freq):
     """Grid cell, level and LUT-bin indices bit-exact; interpolated variables bit-exact."""
