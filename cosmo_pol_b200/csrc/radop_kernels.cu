@@ -691,27 +691,31 @@ __device__ __forceinline__ bool interp_columns(const DevConfig &cfg, const CellG
 {
     // slots 0..8 are the 1-moment variables: two float4 + one scalar per level;
     // the 2-moment scheme reads all four float4
-    const int ys[4] = {c.y0, c.y0, c.y1, c.y1};
-    const int xs[4] = {c.x0, c.x1, c.x0, c.x1};
-    const int order[4] = {0, 2, 1, 3};      // accumulation order of the reference
+    // The four neighbour columns run through ONE copy of the body (a rolled loop: the kernel is limited by
+    // instruction fetch, and four specialised copies of ~140 instructions each do not fit beside the rest of the
+    // gate's code path), in the accumulation order of the reference: columns 0, 2, 1, 3.  -0 is the additive
+    // identity of IEEE addition (x + -0 = x for every x, zeros included), so the running sums start from it
+    // and every column is added the same way.
     bool rare = false;
 #pragma unroll
+    for (int j = 0; j < RADOP_NVP; ++j) val[j] = -0.f;
+#pragma unroll 1
     for (int oi = 0; oi < 4; ++oi) {
-        const int k = order[oi];
-        const size_t colidx = (size_t)ys[k] * cfg.nx + xs[k];
-        const float *zc = z_t + colidx * cfg.nz + c.level[k];
+        const int k = (oi == 1) ? 2 : (oi == 2 ? 1 : oi);
+        const int yk = (k & 2) ? c.y1 : c.y0, xk = (k & 1) ? c.x1 : c.x0;
+        const int lvl = (k == 0) ? c.level[0] : (k == 1 ? c.level[1] : (k == 2 ? c.level[2] : c.level[3]));
+        const size_t colidx = (size_t)yk * cfg.nx + xk;
+        const float *zc = z_t + colidx * cfg.nz + lvl;
         const float c1 = __ldg(zc), c2 = __ldg(zc + 1);
         const float den = __fsub_rn(c1, c2), dh = __fsub_rn(h_g, c2);
         const float rden = EXACT ? 0.f : __frcp_rn(den);
         if (!EXACT) rare = rare || !div_den_safe(den);
-        const float4 *f1 = reinterpret_cast<const float4 *>(fields + (colidx * cfg.nz + c.level[k]) * RADOP_NVP);
+        const float4 *f1 = reinterpret_cast<const float4 *>(fields + (colidx * cfg.nz + lvl) * RADOP_NVP);
         const float4 *f2 = f1 + RADOP_NVP / 4;
-        float w0, w1;      // term = (w0 * v) * w1 in the reference's association
-        bool v_mid;        // col 1, 2: (w0 * v) * w1 ; col 0, 3: (w0 * w1) * v
-        if (k == 0) { w0 = __fmul_rn(c.dx, c.dy); w1 = 0.f; v_mid = false; }
-        else if (k == 2) { w0 = c.x; w1 = c.dy; v_mid = true; }
-        else if (k == 1) { w0 = c.dx; w1 = c.y; v_mid = true; }
-        else { w0 = __fmul_rn(c.x, c.y); w1 = 0.f; v_mid = false; }
+        // term = (w0 * v) * w1 in the reference's association: col 1, 2: (w0 * v) * w1 ; col 0, 3: (w0 * w1) * v
+        const bool v_mid = (k == 1) || (k == 2);
+        const float w0 = (k == 0) ? __fmul_rn(c.dx, c.dy) : (k == 2 ? c.x : (k == 1 ? c.dx : __fmul_rn(c.x, c.y)));
+        const float w1 = (k == 2) ? c.dy : c.y;
         auto accum = [&](int j, float a, float b) {
             const float n = __fsub_rn(b, a);
             float q;
@@ -724,8 +728,9 @@ __device__ __forceinline__ bool interp_columns(const DevConfig &cfg, const CellG
                 rare = rare || !(aq <= 1e30f) || (aq < 1e-30f && n != 0.f);
             }
             float vv = __fsub_rn(b, __fmul_rn(q, dh));
-            float term = v_mid ? __fmul_rn(__fmul_rn(w0, vv), w1) : __fmul_rn(w0, vv);
-            val[j] = (oi == 0) ? term : __fadd_rn(val[j], term);
+            const float t0 = __fmul_rn(w0, vv);
+            const float term = v_mid ? __fmul_rn(t0, w1) : t0;
+            val[j] = __fadd_rn(val[j], term);
         };
 #pragma unroll
         for (int v4 = 0; v4 < 2; ++v4) {
