@@ -46,7 +46,7 @@ FLOP_PER_PAIR = 28672          # 2*1024*12 contraction + 4*1024 PS
 METRIC = 'sub-beam gates/sec for a 20-elevation volume scan'
 UNIT = 'sub-beam gates/s'
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_interp_psd launch at cfg 3 (ncu --set full, profiles/)
-K1_TRAFFIC = 1.2615e9
+K1_TRAFFIC = 1.3000e9
 
 
 def volume_config():
@@ -462,7 +462,7 @@ def run_ours(args):
                 'peak': hbm_peak, 'unit': 'GB/s',
                 'frac': (k1_bytes / (k1_ms * 1e-3) / 1e9 / hbm_peak) if k1_ms > 0 else None,
                 # dram__bytes_read.sum + dram__bytes_write.sum of one k_interp_psd launch of this workload
-                # (ncu --set full capture, profiles/r01g_k_interp_psd_full.txt: 163.3 MB read + 1098.2 MB written)
+                # (ncu --set full capture, profiles/r01h_k_interp_psd_full.txt: 162.8 MB read + 1137.2 MB written)
                 'traffic': K1_TRAFFIC, 'peak_kind': hbm_kind, 'kernel_ms': k1_ms,
                 'algorithmic_bytes_per_launch': k1_bytes, 'bytes_per_sub_beam_gate': nvar * 32 + 32,
                 'note': 'dominant kernel of the step since the diameter integral runs through the lambda-transformed '
