@@ -271,6 +271,9 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit('bench.py needs a CUDA GPU: the hot path has no CPU fallback (use --impl reference for the CPU arm)')
     torch.cuda.set_device(local)
+    sys.__stdout__.flush()
+    fd_out = os.dup(1)                                # native libraries (NCCL's version banner) write to fd 1:
+    os.dup2(2, 1)                                     # keep stdout for the ONE JSON line
     if world > 1:
         # the gather runs beside persistent kernels that fill every SM: a few NCCL CTAs are enough to move
         # 158 MB per peer within a step and leave the SMs to the kernels
@@ -278,9 +281,6 @@ def run_ours(args):
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     quiet = open(os.devnull, 'w')
     stdout, sys.stdout = sys.stdout, quiet            # the host layer prints like the reference does
-    sys.__stdout__.flush()
-    fd_out = os.dup(1)                                # native libraries (NCCL's version banner) write to fd 1:
-    os.dup2(2, 1)                                     # keep stdout for the ONE JSON line
 
     conf = volume_config()
     model, luts = build_inputs()
