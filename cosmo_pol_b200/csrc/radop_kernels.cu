@@ -6,9 +6,13 @@
 //                          variables (bit-exact restatement of interpolation_c.c), PSD
 //                          parameters, LUT bin keys, analytic Doppler moments, histogram
 //  K1b k_scan_bins / k_scatter_pairs    counting sort of the active pairs by LUT bin
-//  K2  k_integrate         PSD x scattering-table contraction over 1024 diameters
-//                          (the FLOP carrier): LUT slice staged in shared memory by TMA
-//                          bulk copy, register-tiled blocked-Horner evaluation
+//  K2t k_build_lamtab / k_integrate_tab   (default) the PSD x scattering-table contraction
+//                          through lambda-transformed tables: the sum over the diameters of
+//                          one bin is a function of the PSD slope alone, tabulated piecewise
+//                          in float64 at table upload and evaluated per pair in ray order
+//  K2  k_integrate         (radop_set_integration(1)) the same contraction summed over the
+//                          1024 diameters: LUT slice staged in shared memory by TMA bulk
+//                          copy, register-tiled blocked-Horner evaluation (FFMA2)
 //  K3  k_ice_totals / k_reduce_subbeams / k_ray_epilogue
 //                          quadrature + species sums, polarimetric observables,
 //                          PHIDP / attenuation prefix scans with warp shuffles
@@ -1709,7 +1713,8 @@ k_integrate(const __grid_constant__ DevConfig cfg, K2Args A)
 // marked and its pairs are integrated directly, diameter by diameter.  A pair then costs 12 NC
 // coefficients (384 B, shared by neighbouring gates: same bin, same piece) and ~100 FMA instead
 // of nd x NC.  radop_set_integration(1) selects the direct kernel (k_integrate) instead; both are
-// held to the oracle by the same tests and to each other by test_table_vs_direct.
+// held to the oracle by the same tests and to each other by test_table_vs_direct_integration;
+// tests/test_lamtab_math.py restates the construction in numpy against the oracle on the CPU.
 #define LT_U0 (-10)              // u = log2(lambda) covered: [LT_U0, LT_U0 + LT_OCT)
 #define LT_OCT 22
 #define LT_PPO 8                 // pieces per octave
@@ -2003,7 +2008,7 @@ struct K2tArgs {
     float *sz_out;
     float2 *ice_vn, *dop_vn;
     long long n_sbg;
-    unsigned long long *n_fallback;   // [4] pairs integrated directly, by reason (lamtab_eval)
+    unsigned long long *n_fallback;   // [4] pairs integrated directly, by reason (lt_locate; rejected piece)
 };
 
 // One species of one warp's 32 sub-beam gates: table evaluation per lane (the coefficient loads of lanes
