@@ -16,10 +16,16 @@ fields and scattering tables (no data files exist offline).
           engine's stream around exactly K steps; max over ranks.
   e2e   : the same through the reference-facing C-ABI call radop_simulate() with HOST
           buffers: ray list + trajectories copied H2D, every observable copied D2H, each step.
-  N > 1 : weak scaling.  Rank r simulates its own volume (the azimuths of rank r are offset
-          by r/N of the azimuth step, i.e. the N-rank job is one volume with N x denser
-          azimuth sampling, sharded by ray); fields and tables are replicated; the only
-          exchange is the gather of the observables to rank 0 over NCCL (inside the step).
+  N > 1 : STRONG scaling (default): the ONE 7200-ray volume is cut into N contiguous blocks of
+          rays, 7200 / N per rank, as the reference splits its ray list over pool workers
+          (cosmo_pol/radar_operator.py:402-435); fields and tables are replicated; the only
+          exchange is the gather of the observables to rank 0 over NCCL (parallel.RayGather,
+          the same object RadarOperator uses under torchrun), inside the timed step.
+          `value` = device-resident result on rank 0; `e2e` = host-resident result on rank 0
+          through RadarOperator.simulate_rays (ray list H2D on every rank, kernels, status
+          agreement, NCCL gather, D2H on rank 0).  A few weak-scaling steps (every rank a full
+          volume, azimuths offset by r/N of the azimuth step) are timed afterwards and
+          reported under "weak" (--scaling weak makes them the headline instead).
 
 --impl reference times the CPU restatement of the reference's algorithm (oracle/, a "port":
 the reference package itself needs pycosmo / pyproj / pyart and Python 2 idioms and cannot
@@ -67,11 +73,14 @@ def volume_rays(rank=0, world=1, n_az=360):
 
 
 def workload_config(world, scaling):
-    return {'workload': 'cfg3: 20-elevation C-band (5.6 GHz) volume scan, 1-mom R/S/G/I, 360 az x 500 gates x 3x3 GH '
-                        'sub-beams per GPU, synthetic COSMO grid 60x400x400 @0.02deg',
-            'rays_per_gpu': 7200, 'gates': 500, 'sub_beams': 9, 'species': 'R,S,G,I',
-            'parallelism': 'rays sharded over {} GPU(s), fields+tables replicated, NCCL gather of observables on a side '
-                           'stream (step k gathered beside the kernels of step k+1, all gathers inside the timed region)'.format(world)
+    rays = 7200 if scaling == 'weak' else 7200 // world
+    return {'workload': 'cfg3: 20-elevation C-band (5.6 GHz) volume scan (20 x 360 = 7200 rays), 1-mom R/S/G/I, 500 gates x '
+                        '3x3 GH sub-beams, synthetic COSMO grid 60x400x400 @0.02deg'
+                        + ('' if scaling == 'strong' else '; one such volume PER GPU'),
+            'rays_per_gpu': rays, 'rays_total': rays * world, 'gates': 500, 'sub_beams': 9, 'species': 'R,S,G,I',
+            'parallelism': 'rays sharded contiguously over {} GPU(s), fields+tables replicated, NCCL gather of the observables '
+                           'to rank 0 on a side stream (step k gathered beside the kernels of step k+1, all gathers inside '
+                           'the timed region; cosmo_pol_b200.parallel.RayGather)'.format(world)
                            if world > 1 else 'single GPU',
             'scaling_mode': scaling,
             'l2': 'no explicit flush: one step streams ~3 GB of per-gate work buffers (K1 outputs, sz_out) plus a 614 MB '
@@ -235,8 +244,8 @@ def run_reference(args):
               'gates, numpy oracle port of the reference algorithm, {} worker processes'.format(n, sbg, arm.cores))
     line = {'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * t / args.steps,
-            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64/f32 (numpy, reference dtypes)',
-            'data': 'synthetic', 'config': workload_config(1, 'weak'),
+            'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64/f32 (numpy, reference dtypes)',
+            'data': 'synthetic', 'config': workload_config(1, 'strong'),
             'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': arm.cores, 'kind': 'port', 'sample': sample},
             'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
@@ -247,6 +256,43 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------
+def e2e_breakdown(op, eng, az, el, rank, world, local):
+    """Wall-clock stages of one sharded product call (the stages of RadarOperator._simulate_sharded, timed one
+    after the other with a device synchronisation between them): where the end-to-end time goes at N > 1."""
+    import torch
+    import torch.distributed as dist
+    from cosmo_pol_b200 import parallel
+    from cosmo_pol_b200._abi import OUT_NAMES, BUF_OBS
+    lo, hi = parallel.shard_bounds(len(az), rank, world)
+    t = {}
+    dist.barrier()
+    c = time.perf_counter()
+    scan = op.build_scan(az[lo:hi], el[lo:hi])
+    eng.stage(scan)
+    eng.synchronize()
+    t['stage_h2d'] = time.perf_counter() - c
+    c = time.perf_counter()
+    eng.execute()
+    eng.finish()
+    t['kernels_and_flags'] = time.perf_counter() - c
+    c = time.perf_counter()
+    parallel.agree_status(0, local)
+    t['status_allreduce'] = time.perf_counter() - c
+    c = time.perf_counter()
+    g = op._gather or parallel.RayGather('root', depth=1)
+    ptr, _ = eng.device_buffer(BUF_OBS)
+    stream = torch.cuda.ExternalStream(eng.stream_ptr(), device=torch.device('cuda', local))
+    pend = g.launch(parallel.device_tensor(ptr, (len(OUT_NAMES) + 1, hi - lo, scan.n_gates), local), len(az), stream)
+    g.wait(pend)
+    torch.cuda.synchronize()
+    t['nccl_gather'] = time.perf_counter() - c
+    c = time.perf_counter()
+    g.to_host(pend, key=BUF_OBS)
+    t['d2h_rank0'] = time.perf_counter() - c
+    tt = torch.tensor([t[k] for k in sorted(t)], dtype=torch.float64, device='cuda:{}'.format(local))
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    return {k: 1e3 * float(v) for k, v in zip(sorted(t), tt)}
+
 def fp32_peaks(eng, seconds=1.5):
     """Measured FP32 FMA throughput (dependent-free FFMA chains, radop_measure_fp32_peak):
     burst = best of the first calls, sustained = median of back-to-back calls over `seconds`."""
@@ -270,81 +316,30 @@ def run_ours(args):
     local = int(os.environ.get('LOCAL_RANK', 0))
     if not torch.cuda.is_available():
         raise SystemExit('bench.py needs a CUDA GPU: the hot path has no CPU fallback (use --impl reference for the CPU arm)')
-    torch.cuda.set_device(local)
     sys.__stdout__.flush()
     fd_out = os.dup(1)                                # native libraries (NCCL's version banner) write to fd 1:
     os.dup2(2, 1)                                     # keep stdout for the ONE JSON line
-    if world > 1:
-        # the gather runs beside persistent kernels that fill every SM: a few NCCL CTAs are enough to move
-        # 158 MB per peer within a step and leave the SMs to the kernels
-        os.environ.setdefault('NCCL_MAX_CTAS', '8')
-        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    # one process per GPU: CPU affinity local to the GPU, NCCL limited to a few CTAs (parallel.init_distributed)
+    parallel.init_distributed(local)
     quiet = open(os.devnull, 'w')
     stdout, sys.stdout = sys.stdout, quiet            # the host layer prints like the reference does
+    dev = torch.device('cuda', local)
 
     conf = volume_config()
     model, luts = build_inputs()
     t_up = time.time()
-    op = RadarOperator(conf, output_variables='only_radar', device=local)
+    op = RadarOperator(conf, output_variables='only_radar', device=local, gather='root')
     op.set_lut(luts)
     op.load_model(model)
     eng = op._prepare_engine()
     eng.set_integration(args.integration)
     t_up = time.time() - t_up
-    scaling = args.scaling
-    if scaling == 'weak':
-        az, el = volume_rays(rank, world)
-    else:
-        az, el = volume_rays()
-        lo, hi = parallel.shard_bounds(len(az), rank, world)
-        az, el = az[lo:hi], el[lo:hi]
-    scan = op.build_scan(az, el)
-    eng.stage(scan)
-    stream = torch.cuda.ExternalStream(eng.stream_ptr(), device=torch.device('cuda', local))
+    scaling = args.scaling if world > 1 else 'strong'
+    az_full, el_full = volume_rays()
+    n_full = len(az_full)
+    stream = torch.cuda.ExternalStream(eng.stream_ptr(), device=dev)
     n_out = len(OUT_NAMES) + 1
-    gather_list = None
-
-    # N > 1: the observables of a step are gathered on rank 0 (NCCL) from a staging copy on a side stream,
-    # so that the gather of step k runs beside the kernels of step k + 1; every gather is inside the timed
-    # region (the engine stream joins the side stream before the closing event).
-    comm = torch.cuda.Stream(device=torch.device('cuda', local)) if world > 1 else None
-    staged = {'buf': None, 'free': None}
-
-    def step():
-        eng.execute()
-        if world > 1:
-            ptr, nr, ng = eng.device_outputs()
-            t = parallel.device_tensor(ptr, (n_out, nr, ng), local)
-            with torch.cuda.stream(stream):
-                if staged['buf'] is None:
-                    staged['buf'] = torch.empty_like(t)
-                if staged['free'] is not None:
-                    stream.wait_event(staged['free'])          # the previous gather has read the staging copy
-                staged['buf'].copy_(t, non_blocking=True)
-                ready = torch.cuda.Event()
-                ready.record(stream)
-            comm.wait_event(ready)
-            with torch.cuda.stream(comm):
-                dist.gather(staged['buf'], gather_list if rank == 0 else None, dst=0)
-                staged['free'] = torch.cuda.Event()
-                staged['free'].record(comm)
-
-    def join_comm():
-        if world > 1:
-            stream.wait_stream(comm)
-
-    if world > 1:
-        eng.execute()
-        eng.synchronize()
-        ptr, nr, ng = eng.device_outputs()
-        if rank == 0:
-            lens = [scan.n_rays] * world
-            if scaling == 'strong':
-                lens = [parallel.shard_bounds(7200, r, world)[1] - parallel.shard_bounds(7200, r, world)[0] for r in range(world)]
-            if len(set(lens)) != 1:
-                raise SystemExit('strong scaling needs 7200 divisible by the number of GPUs')
-            gather_list = [torch.empty((n_out, nr, ng), dtype=torch.float32, device='cuda:{}'.format(local))
-                           for _ in range(world)]
+    gather = parallel.RayGather('root', depth=2)
 
     def barrier():
         if world > 1:
@@ -352,53 +347,128 @@ def run_ours(args):
         torch.cuda.synchronize()
         eng.synchronize()
 
-    for _ in range(args.warmup):
-        step()
-    join_comm()
-    barrier()
+    def device_run(scan, n_total, steps, warmup, timing):
+        """K device-timed steps of radop_execute on the staged scan, every step followed by the gather of its
+        observables to rank 0 (N > 1); returns (ms for `steps` steps, stats)."""
+        eng.stage(scan)
+        last = [None]
+
+        def step():
+            eng.execute()
+            if world > 1:
+                ptr, nr, ng = eng.device_outputs()
+                last[0] = gather.launch(parallel.device_tensor(ptr, (n_out, nr, ng), local), n_total, stream)
+
+        def join():
+            if last[0] is not None:
+                gather.wait(last[0], stream)       # the engine stream joins the side stream before the closing event
+
+        for _ in range(warmup):
+            step()
+        join()
+        barrier()
+        if timing:
+            eng.enable_timing(True)
+            barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            step()
+        join()
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        st = eng.stats() if timing else None
+        if timing:
+            eng.enable_timing(False)
+        return ms, st
+
+    def reduce_max(*vals):
+        if world == 1:
+            return [float(v) for v in vals]
+        tt = torch.tensor(vals, dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return [float(x) for x in tt]
+
+    def reduce_sum(*vals):
+        if world == 1:
+            return [float(v) for v in vals]
+        tt = torch.tensor(vals, dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.SUM)
+        return [float(x) for x in tt]
+
+    # ---- headline: device-timed steps -------------------------------------------------------
+    if scaling == 'weak':
+        az, el = volume_rays(rank, world)
+        n_total = n_full * world
+    else:
+        if n_full % world:
+            raise SystemExit('the 7200-ray volume does not divide by {} ranks'.format(world))
+        lo, hi = parallel.shard_bounds(n_full, rank, world)
+        az, el = az_full[lo:hi], el_full[lo:hi]
+        n_total = n_full
+    scan = op.build_scan(az, el)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
         time.sleep(0.25)
-    eng.enable_timing(True)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.time()
-    e0.record(stream)
-    for _ in range(args.steps):
-        step()
-    join_comm()
-    e1.record(stream)
-    barrier()
+    ms, st = device_run(scan, n_total, args.steps, args.warmup, True)
     t1 = time.time()
-    ms = e0.elapsed_time(e1)
-    st = eng.stats()
-    eng.enable_timing(False)
     clocks = sampler.stop(t0, t1) if rank == 0 else None
     launches = int(st['launches']) * args.steps
+    (ms,) = reduce_max(ms)
+    total_sbg, total_pairs = reduce_sum(scan.n_subbeam_gates, st['n_active_pairs'])
 
-    # ---- end to end through the C-ABI with host buffers -------------------------------------
+    # ---- the other scaling mode, a few steps (secondary record) ------------------------------
+    other = None
+    if world > 1:
+        k2 = max(3, min(args.steps, 5))
+        if scaling == 'strong':
+            az2, el2 = volume_rays(rank, world)
+            n2 = n_full * world
+        else:
+            lo, hi = parallel.shard_bounds(n_full, rank, world)
+            az2, el2 = az_full[lo:hi], el_full[lo:hi]
+            n2 = n_full
+        scan2 = op.build_scan(az2, el2)
+        ms2, _ = device_run(scan2, n2, k2, 3, False)
+        (ms2,) = reduce_max(ms2)
+        (sbg2,) = reduce_sum(scan2.n_subbeam_gates)
+        other = {'scaling': 'weak' if scaling == 'strong' else 'strong', 'value': sbg2 / (ms2 * 1e-3 / k2), 'unit': UNIT,
+                 'ms_per_step': ms2 / k2, 'steps': k2, 'rays_per_gpu': scan2.n_rays}
+        eng.stage(scan)
+
+    # ---- end to end: host buffers in, host buffers out --------------------------------------
+    # N = 1: the reference-facing C-ABI call radop_simulate.  N > 1: the product path a user of get_PPI under
+    # torchrun runs (RadarOperator.simulate_rays: shard, H2D, kernels, status agreement, NCCL gather, D2H on rank 0).
+    def e2e_call():
+        if world == 1:
+            return eng.simulate(scan, want_latlon=True)
+        return op.simulate_rays(az_full, el_full, copy=False)
+
     for _ in range(2):
-        arrays = eng.simulate(scan, want_latlon=True)
+        arrays = e2e_call()
     barrier()
     te = time.perf_counter()
     for _ in range(args.steps):
-        arrays = eng.simulate(scan, want_latlon=True)
+        arrays = e2e_call()
     barrier()
     te = time.perf_counter() - te
-    h2d = scan.bytes_in()
-    d2h = int(sum(a.nbytes for a in arrays.values()))
-    checksum = float(np.nansum(arrays['ZH'][::97]))
-
-    if world > 1:
-        tt = torch.tensor([ms, te], dtype=torch.float64, device='cuda:{}'.format(local))
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms, te = float(tt[0]), float(tt[1])
-        cnt = torch.tensor([scan.n_subbeam_gates, st['n_active_pairs']], dtype=torch.float64, device='cuda:{}'.format(local))
-        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-        total_sbg, total_pairs = float(cnt[0]), float(cnt[1])
+    (te,) = reduce_max(te)
+    if world == 1:
+        h2d = scan.bytes_in()
+        d2h = int(eng.last_d2h_bytes)
+        d2h_first = int(sum(a.nbytes for a in arrays.values()))
     else:
-        total_sbg, total_pairs = float(scan.n_subbeam_gates), float(st['n_active_pairs'])
+        h2d = scan.bytes_in()                       # per rank: its block of the ray list + the trajectories
+        d2h = int(sum(arrays[k].nbytes for k in OUT_NAMES + ['mask'])) if rank == 0 else 0
+        d2h_first = d2h + (int(arrays['lat'].nbytes + arrays['lon'].nbytes) if rank == 0 else 0)
+    checksum = float(np.nansum(arrays['ZH'][::97])) if arrays is not None else 0.0
+    st_e2e = None
+    if world > 1:
+        # itemised cost of the product call on rank 0 (wall clock, one extra call): where e2e goes beyond the kernels
+        st_e2e = e2e_breakdown(op, eng, az_full, el_full, rank, world, local)
     sys.stdout = stdout
     os.dup2(fd_out, 1)
     os.close(fd_out)
@@ -409,7 +479,7 @@ def run_ours(args):
 
     # ---- the direct integration kernel, timed beside the run (not part of `value`): same scan, mode 1 -----
     direct = None
-    if world == 1 and args.integration == 'table':
+    if world == 1 and args.integration == 'table' and not args.no_direct:
         eng.set_integration('direct')
         for _ in range(3):
             eng.execute()
@@ -492,9 +562,16 @@ def run_ours(args):
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms / args.steps, 'higher_is_better': True,
         'scaling': scaling, 'vs_baseline': None, 'dtype': 'f32 (f64 geodesy and PSD parameters)', 'data': 'synthetic',
         'config': workload_config(world, scaling),
-        'e2e': {'value': total_sbg / (te / args.steps), 'unit': UNIT, 'h2d_bytes_per_step': h2d,
+        'e2e': {'value': (n_full * 9 * 500.0) / (te / args.steps), 'unit': UNIT, 'h2d_bytes_per_step': h2d,
                 'd2h_bytes_per_step': d2h, 'ms_per_step': 1e3 * te / args.steps,
-                'call': 'radop_simulate (C-ABI, host buffers) per rank'},
+                'd2h_bytes_first_call': d2h_first,
+                'latlon': 'gate positions (float64 lat/lon, 58 MB per volume) depend on the scan geometry only: copied by the '
+                          'first call on a ray list (d2h_bytes_first_call), kept in the pinned buffers afterwards',
+                'call': 'radop_simulate (C-ABI, host buffers)' if world == 1 else
+                        'RadarOperator.simulate_rays on the ONE 7200-ray volume, sharded over the ranks, result on rank 0 '
+                        '(h2d per rank, d2h on rank 0)',
+                'breakdown_ms': st_e2e},
+        'other_scaling': other,
         'gpu_launches': launches,
         'clocks': clocks,
         'roofline': roof,
@@ -523,7 +600,9 @@ def main():
     ap.add_argument('--steps', type=int, default=10)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--scaling', default='weak', choices=['weak', 'strong'])
+    ap.add_argument('--scaling', default='strong', choices=['weak', 'strong'],
+                    help='N > 1: strong = ONE 7200-ray volume sharded by ray (default); weak = one volume per GPU')
+    ap.add_argument('--no-direct', action='store_true', help='skip the extra steps that time the direct integration kernel')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     ap.add_argument('--integration', default='table', choices=['table', 'direct'],
                     help='diameter integral through lambda-transformed tables (default) or by direct sums')

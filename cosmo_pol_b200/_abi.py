@@ -10,7 +10,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libradop.so')
 
-RADOP_ABI_VERSION = 5
+RADOP_ABI_VERSION = 6
 NSPECIES_MAX = 7
 NVAR_MAX = 16
 N_OUT = 10
@@ -25,7 +25,10 @@ EXPORTS = ['radop_abi_version', 'radop_create', 'radop_destroy', 'radop_last_err
            'radop_execute', 'radop_fetch', 'radop_synchronize', 'radop_device_outputs', 'radop_get_stream',
            'radop_get_stats', 'radop_enable_timing', 'radop_debug_indices', 'radop_measure_fp32_peak',
            'radop_get_all_radar_pts', 'radop_selftest_division', 'radop_set_chunk', 'radop_set_overlap_threshold',
-           'radop_set_geodesy', 'radop_get_geodesy', 'radop_set_integration', 'radop_get_integration', 'radop_debug_integration', 'radop_set_search']
+           'radop_set_geodesy', 'radop_get_geodesy', 'radop_set_integration', 'radop_get_integration', 'radop_debug_integration',
+           'radop_set_search', 'radop_sizeof', 'radop_device_buffer', 'radop_get_refl']
+
+BUF_OBS, BUF_LAT, BUF_LON, BUF_MODEL, BUF_DSPECTRUM = range(5)
 
 (RADOP_OK, RADOP_ERR_CUDA, RADOP_ERR_ARG, RADOP_ERR_OUT_OF_DOMAIN, RADOP_ERR_LUT, RADOP_ERR_STATE,
  RADOP_ERR_UNSUPPORTED) = range(7)
@@ -72,6 +75,10 @@ class RadopStats(C.Structure):
                 ('ms_integrate', C.c_float), ('ms_reduce', C.c_float), ('ms_total', C.c_float),
                 ('n_timed', C.c_int32), ('ms_spectrum', C.c_float),
                 ('pairs_by_species', C.c_int64 * NSPECIES_MAX), ('exec_flop_per_pair', C.c_double * NSPECIES_MAX)]
+
+
+# order of RADOP_SIZEOF_* in include/radop.h
+ABI_STRUCTS = (RadopParams, RadopSpecies, RadopScan, RadopOut, RadopStats)
 
 
 class RadopError(RuntimeError):
@@ -126,8 +133,17 @@ def load_library():
     lib.radop_selftest_division.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.radop_get_all_radar_pts.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.radop_sizeof.argtypes = [C.c_int]
+    lib.radop_device_buffer.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+    lib.radop_get_refl.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 8
     if lib.radop_abi_version() != RADOP_ABI_VERSION:
         raise RadopError('libradop.so ABI version mismatch')
+    # the struct layouts of this binding against the ones the library was compiled with (radop_sizeof):
+    # a short RadopParams would make radop_set_params read past the caller's struct
+    for which, st in enumerate(ABI_STRUCTS):
+        if lib.radop_sizeof(which) != C.sizeof(st):
+            raise RadopError('libradop.so: sizeof({}) is {} in the library and {} in this binding'.format(
+                st.__name__, lib.radop_sizeof(which), C.sizeof(st)))
     _lib = lib
     return lib
 
@@ -162,6 +178,17 @@ class Scan(object):
         self.n_rays = len(self.ray_az)
         self.n_sub = fan.n_sub
         self.n_traj, self.n_vert, self.n_gates = self.traj_s.shape
+        self._geom_key = None
+
+    def geometry_key(self):
+        """Digest of everything the gate positions depend on (ray list, fan, trajectories)."""
+        if self._geom_key is None:
+            import hashlib
+            hsh = hashlib.blake2b(digest_size=16)
+            for a in (self.ray_az, self.ray_traj, self.sub_daz, self.sub_jv, self.traj_s):
+                hsh.update(a.tobytes())
+            self._geom_key = hsh.hexdigest()
+        return self._geom_key
 
     def as_struct(self):
         s = RadopScan()
@@ -198,6 +225,8 @@ class Engine(object):
         self.uploaded_vars = []
         self._pinned = {}
         self._keep = []
+        self._latlon_key = None      # geometry the pinned lat / lon buffers currently hold
+        self.cache_latlon = True
 
     def close(self):
         if getattr(self, 'h', None):
@@ -369,11 +398,26 @@ class Engine(object):
             out.dspectrum = a.ctypes.data
         return out, arrays
 
+    def _geometry_key(self, scan):
+        p = self.params
+        return (scan.geometry_key(), p.radar_lat, p.radar_lon, p.n_gates, scan.n_rays)
+
     def simulate(self, scan, want_latlon=True, want_model=False):
-        """The reference-facing call: host in -> host out."""
+        """The reference-facing call: host in -> host out.  The gate positions (lat, lon: 16 of the 60 bytes
+        per ray gate) depend on the scan geometry only; when the pinned buffers already hold the positions of
+        this very ray list, fan and trajectories, they are neither recomputed nor copied again."""
         out, arrays = self.make_out(scan, want_latlon, want_model)
+        key = self._geometry_key(scan) if want_latlon else None
+        reuse = want_latlon and self.cache_latlon and key == self._latlon_key
+        if reuse:
+            out.lat = None
+            out.lon = None
         s = scan.as_struct()
+        self._latlon_key = None if (want_latlon and not reuse) else self._latlon_key
         self._check(self.lib.radop_simulate(self.h, C.byref(s), C.byref(out)))
+        if want_latlon:
+            self._latlon_key = key
+        self.last_d2h_bytes = int(sum(a.nbytes for k, a in arrays.items() if not (reuse and k in ('lat', 'lon'))))
         return arrays
 
     def stage(self, scan):
@@ -388,8 +432,21 @@ class Engine(object):
 
     def fetch(self, scan, want_latlon=True, want_model=False):
         out, arrays = self.make_out(scan, want_latlon, want_model)
+        self._latlon_key = None
         self._check(self.lib.radop_fetch(self.h, C.byref(out)))
+        if want_latlon:
+            self._latlon_key = self._geometry_key(scan)
         return arrays
+
+    def finish(self):
+        """Drain the stream and raise what the run flagged (IndexError when a gate left the model domain)."""
+        self._check(self.lib.radop_fetch(self.h, None))
+
+    def device_buffer(self, which):
+        """(device pointer, bytes) of a device-resident result of the last execute (BUF_*)."""
+        p, n = C.c_void_p(), C.c_int64()
+        self._check(self.lib.radop_device_buffer(self.h, C.c_int(which), C.byref(p), C.byref(n)))
+        return p.value, n.value
 
     def enable_timing(self, on=True):
         self._check(self.lib.radop_enable_timing(self.h, 1 if on else 0))
@@ -481,6 +538,18 @@ class Engine(object):
             d[k] = d[k].reshape(shp + d[k].shape[1:])
         d['var_names'] = list(self.uploaded_vars)
         return d
+
+    def get_refl(self, Da, Db, rcs, D, N, step_D, Dmin):
+        """Compatibility shim with the data contract of the SWIG function get_refl
+        (doppler_scatter.py:715-716, doppler_c.c:11-32): returns refl [len(Da)]."""
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float32)
+        Da, Db, rcs, D, N, step_D, Dmin = f(Da), f(Db), f(rcs), f(D), f(N), f(step_D), f(Dmin)
+        n, nh = Da.shape
+        nd = rcs.shape[0]
+        out = np.zeros(n, dtype=np.float32)
+        self._check(self.lib.radop_get_refl(self.h, n, nh, nd, _ptr(Da), _ptr(Db), _ptr(rcs), _ptr(D), _ptr(N),
+                                            _ptr(step_D), _ptr(Dmin), _ptr(out)))
+        return out
 
     def get_all_radar_pts(self, coords, heights_gates, model_data, model_heights, llc, res):
         """Compatibility shim with the data contract of the SWIG function

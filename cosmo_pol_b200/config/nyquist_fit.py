@@ -13,9 +13,19 @@ def nyquist_interpolator(nyquist_file):
     def interpolator(elevation, azimuth):
         closest_el = elev[np.argmin(np.abs(elev - elevation))]
         idx_el = np.where(elev == closest_el)[0]
-        # the reference picks the azimuth row through an argmin over (az - azimuth) without
-        # abs(); every shipped table has a single azimuth (0) per elevation, so it is row 0
-        return float(nyq[idx_el[0]])
+        az_at_el = azim[idx_el]
+        # The reference selects the azimuth row with pandas label lookups that take the azimuth VALUES of the
+        # elevation's rows as row labels of the whole table, and an argmin over (az - azimuth) without abs()
+        # (nyquist_fit.py:22-28).  Restated as is: with one azimuth (0) per elevation -- every shipped table --
+        # it is that elevation's row; a table whose azimuth values are not valid row labels raises KeyError
+        # there and here.
+        rows = az_at_el.astype(int)
+        if np.any(rows != az_at_el) or np.any(rows < 0) or np.any(rows >= len(azim)):
+            raise KeyError('azimuth values {} are not row labels of the Nyquist table'.format(list(az_at_el)))
+        sub = azim[rows]
+        closest_az = azim[int(np.argmin(sub - azimuth))]
+        j = np.where(closest_az == sub)[0][0]
+        return float(nyq[idx_el[j]])
 
     interpolator.table = (elev, azim, nyq)
     return interpolator

@@ -73,6 +73,7 @@ struct RadopHandle_ {
     LutHost lut[RADOP_NSPECIES_MAX];   // indexed by RADOP_SP_*
     // scan
     bool have_scan = false, executed = false;
+    bool latlon_valid = false;   // the last run computed the central sub-beam positions
     int n_rays = 0, n_sub = 0, n_traj = 0, n_vert = 0, center_sub = 0;
     bool have_nyquist = false;
     size_t overlap_min_bytes = (size_t)32 << 20;   // radop_simulate chunks the scan only above this output size
@@ -142,6 +143,18 @@ extern "C" {
 
 int radop_abi_version(void) { return RADOP_ABI_VERSION; }
 
+int radop_sizeof(int which)
+{
+    switch (which) {
+    case RADOP_SIZEOF_PARAMS: return (int)sizeof(RadopParams);
+    case RADOP_SIZEOF_SPECIES: return (int)sizeof(RadopSpecies);
+    case RADOP_SIZEOF_SCAN: return (int)sizeof(RadopScan);
+    case RADOP_SIZEOF_OUT: return (int)sizeof(RadopOut);
+    case RADOP_SIZEOF_STATS: return (int)sizeof(RadopStats);
+    }
+    return -1;
+}
+
 int radop_create(int device, RadopHandle **out)
 {
     if (!out) return RADOP_ERR_ARG;
@@ -170,13 +183,14 @@ int radop_destroy(RadopHandle *h)
     if (!h) return RADOP_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    DevBuf *bufs[] = {&h->lev_guess, &h->geo_poly, &h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
+    cudaStreamSynchronize(h->copy_stream);
+    DevBuf *bufs[] = {&h->lt_stat, &h->lev_guess, &h->geo_poly, &h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
                       &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
                       &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
                       &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_st, &h->attw, &h->spec_acc, &h->spec_out, &h->d3_std, &h->sub_acc, &h->brd_flag, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
                       &h->dbg_status, &h->dbg_e, &h->dbg_t, &h->dbg_rot};
     for (DevBuf *b : bufs) b->release();
-    for (auto &l : h->lut) { l.table.release(); l.aux.release(); }
+    for (auto &l : h->lut) { l.table.release(); l.aux.release(); l.lamtab.release(); }
     if (h->pinned) cudaFreeHost(h->pinned);
     for (auto &e : h->ev) cudaEventDestroy(e);
     for (auto &e : h->chunk_done) cudaEventDestroy(e);
@@ -613,6 +627,7 @@ static int copy_outputs(RadopHandle *h, const RadopOut *out, int r0, int nr, cud
     for (int v = 0; v < RADOP_N_OUT; ++v)
         if (out->obs[v]) CU(h, cudaMemcpyAsync(out->obs[v] + off, h->out.as<float>() + (size_t)v * n_rg + off, cnt * 4, cudaMemcpyDeviceToHost, st));
     if (out->mask) CU(h, cudaMemcpyAsync(out->mask + off, h->out.as<float>() + (size_t)RADOP_N_OUT * n_rg + off, cnt * 4, cudaMemcpyDeviceToHost, st));
+    if ((out->lat || out->lon) && !h->latlon_valid) return h->fail(RADOP_ERR_STATE, "lat / lon were not computed by the last run");
     if (out->lat) CU(h, cudaMemcpyAsync(out->lat + off, h->lat.as<double>() + off, cnt * 8, cudaMemcpyDeviceToHost, st));
     if (out->lon) CU(h, cudaMemcpyAsync(out->lon + off, h->lon.as<double>() + off, cnt * 8, cudaMemcpyDeviceToHost, st));
     if (out->dspectrum) {
@@ -816,7 +831,12 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         o.wind = h->wind.as<float>(); o.sinth = h->sinth.as<float>(); o.vsum = h->vsum.as<float>(); o.nsum = h->nsum.as<float>();
         o.key = h->key.as<uint16_t>(); o.p0 = h->p0.as<float>(); o.p1 = h->p1.as<float>();
         o.vals = want_vals ? h->vals.as<float>() : nullptr;
-        o.lat = h->lat.as<double>() + off_rg; o.lon = h->lon.as<double>() + off_rg;
+        // the positions depend on the scan geometry only: a caller that kept them from an earlier call on the
+        // same ray list (radop_simulate with lat = lon = NULL) does not pay for them again
+        const bool want_latlon = !out || out->lat || out->lon;
+        o.lat = want_latlon ? h->lat.as<double>() + off_rg : nullptr;
+        o.lon = want_latlon ? h->lon.as<double>() + off_rg : nullptr;
+        h->latlon_valid = want_latlon;
         o.hist = h->hist.as<int>(); o.flags = h->flags.as<int>();
         if (c.doppler_scheme == 3) {
             o.d3_uh = h->d3_uh.as<double>(); o.d3_w = h->d3_w.as<float>(); o.d3_rho = h->d3_rho.as<float>();
@@ -1053,7 +1073,14 @@ int radop_simulate(RadopHandle *h, const RadopScan *scan, const RadopOut *out)
     int rc = radop_stage_scan(h, scan);
     if (rc) return rc;
     rc = run_scan(h, out);          // copies of a chunk overlap the kernels of the next one
-    if (rc) return rc;
+    if (rc) {
+        // copies into the caller's buffers may already be queued: drain them before the error reaches the caller
+        const std::string msg = h->err;
+        cudaStreamSynchronize(h->stream);
+        cudaStreamSynchronize(h->copy_stream);
+        h->err = msg;
+        return rc;
+    }
     CU(h, cudaStreamSynchronize(h->stream));
     CU(h, cudaStreamSynchronize(h->copy_stream));
     return finish(h);
@@ -1139,6 +1166,32 @@ int radop_device_outputs(RadopHandle *h, void **dev_ptr, int64_t *n_rays, int64_
     *dev_ptr = h->out.p;
     if (n_rays) *n_rays = h->cfg.n_rays;
     if (n_gates) *n_gates = h->cfg.n_gates;
+    return RADOP_OK;
+}
+
+int radop_device_buffer(RadopHandle *h, int which, void **dev_ptr, int64_t *bytes)
+{
+    if (!h || !dev_ptr) return RADOP_ERR_ARG;
+    if (!h->executed) return h->fail(RADOP_ERR_STATE, "nothing executed");
+    const size_t n_rg = (size_t)h->n_rays * h->cfg.n_gates;
+    void *p = nullptr;
+    size_t n = 0;
+    switch (which) {
+    case RADOP_BUF_OBS: p = h->out.p; n = n_rg * (RADOP_N_OUT + 1) * 4; break;
+    case RADOP_BUF_LAT:
+    case RADOP_BUF_LON:
+        if (!h->latlon_valid) return h->fail(RADOP_ERR_STATE, "lat / lon were not computed by the last run");
+        p = which == RADOP_BUF_LAT ? h->lat.p : h->lon.p; n = n_rg * 8; break;
+    case RADOP_BUF_MODEL:
+        if (!h->cfg.output_model_vars) return h->fail(RADOP_ERR_STATE, "model variables were not integrated (output_model_vars = 0)");
+        p = h->model_out.p; n = n_rg * RADOP_NVP * 4; break;
+    case RADOP_BUF_DSPECTRUM:
+        if (h->cfg.doppler_scheme != 3) return h->fail(RADOP_ERR_STATE, "no Doppler spectrum (scheme 3) in this configuration");
+        p = h->spec_out.p; n = n_rg * (size_t)h->cfg.n_vel * 4; break;
+    default: return h->fail(RADOP_ERR_ARG, "unknown buffer id");
+    }
+    *dev_ptr = p;
+    if (bytes) *bytes = (int64_t)n;
     return RADOP_OK;
 }
 
@@ -1273,6 +1326,33 @@ int radop_get_all_radar_pts(RadopHandle *h, int n, const float *coords, const fl
     CU(h, cudaMemcpyAsync(output, dout.p, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
     dc.release(); dh.release(); dd.release(); dz.release(); dout.release();
+    return RADOP_OK;
+}
+
+int radop_get_refl(RadopHandle *h, int len, int nhydro, int nd, const float *Da, const float *Db, const float *rcs,
+                   const float *D, const float *N, const float *step_D, const float *Dmin, float *refl)
+{
+    (void)D;      // the reference passes the diameters and never reads them (doppler_c.c:11-32)
+    if (!h || !Da || !Db || !rcs || !N || !step_D || !Dmin || !refl || len <= 0 || nhydro <= 0 || nd <= 0)
+        return RADOP_ERR_ARG;
+    CU(h, cudaSetDevice(h->device));
+    DevBuf blob, dout;
+    const size_t n_ab = (size_t)len * nhydro, n_tab = (size_t)nd * nhydro;
+    CU(h, blob.reserve((2 * n_ab + 2 * n_tab + 2 * (size_t)nhydro) * 4));
+    CU(h, dout.reserve((size_t)len * 4));
+    float *dDa = blob.as<float>(), *dDb = dDa + n_ab, *drcs = dDb + n_ab, *dN = drcs + n_tab, *dstep = dN + n_tab,
+          *dmin = dstep + nhydro;
+    CU(h, cudaMemcpyAsync(dDa, Da, n_ab * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(dDb, Db, n_ab * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(drcs, rcs, n_tab * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(dN, N, n_tab * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(dstep, step_D, (size_t)nhydro * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(dmin, Dmin, (size_t)nhydro * 4, cudaMemcpyHostToDevice, h->stream));
+    k_refl_compat<<<(len + 127) / 128, 128, 0, h->stream>>>(len, nhydro, nd, dDa, dDb, drcs, dN, dstep, dmin, dout.as<float>());
+    CU(h, cudaGetLastError());
+    CU(h, cudaMemcpyAsync(refl, dout.p, (size_t)len * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    blob.release(); dout.release();
     return RADOP_OK;
 }
 

@@ -684,6 +684,28 @@ __global__ void k_interp_compat(int n, const float *__restrict__ coords, const f
                        __fmul_rn(__fmul_rn(x, y), vv[3]));
 }
 
+// compatibility kernel: same data contract and float32 order of operations as get_refl (doppler_c.c:11-32);
+// thread = velocity bin, species and diameters in sequence
+__global__ void k_refl_compat(int len, int nhydro, int nd, const float *__restrict__ Da, const float *__restrict__ Db,
+                              const float *__restrict__ rcs, const float *__restrict__ N, const float *__restrict__ step_D,
+                              const float *__restrict__ Dmin, float *__restrict__ refl)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= len) return;
+    float r = 0.f;
+    for (int j = 0; j < nhydro; ++j) {
+        const float st = step_D[j], d0 = Dmin[j];
+        // (int) of a float quotient, truncation toward zero as in C
+        int ka = (int)__fdiv_rn(__fsub_rn(Da[i * nhydro + j], d0), st);
+        int kb = (int)__fdiv_rn(__fsub_rn(Db[i * nhydro + j], d0), st);
+        ka = max(ka, 0); kb = min(kb, nd);           // memory safety (undefined behaviour in the reference)
+        float sum = 0.f;
+        for (int k = ka; k < kb; ++k) sum = __fadd_rn(sum, __fmul_rn(N[k * nhydro + j], rcs[k * nhydro + j]));
+        r = __fadd_rn(r, __fmul_rn(sum, st));
+    }
+    refl[i] = r;
+}
+
 // All variables of one gate from the 8 surrounding grid points, in the reference's order of
 // operations (interpolation_c.c:84-103, 138-164).  EXACT = false: quotients from the reciprocal
 // shared by the variables of a column, no branch; returns true when some quotient needs the

@@ -1,10 +1,15 @@
 # -*- coding: utf-8 -*-
 """Ray sharding over the GPUs of one box.
 
-The reference farms rays out to a multiprocess.Pool (cosmo_pol/radar_operator.py:402-435).
-Here rays are independent units sharded contiguously over the ranks of a torch.distributed
-job (one process per GPU); fields and lookup tables are replicated; the only exchange is one
-all-gather of the per-ray outputs at the end (NCCL over NVLink on GPUs, gloo in CPU tests)."""
+The reference farms rays out to a multiprocess.Pool (cosmo_pol/radar_operator.py:402-435: ONE
+ray list, ``pool.map`` over it).  Here the same ray list is cut into contiguous blocks, one per
+rank of a torch.distributed job (one process per GPU); fields and lookup tables are replicated;
+the only exchange is the gather of the per-ray outputs (NCCL over NVLink on GPUs, gloo in the CPU
+tests).  ``RayGather`` is the one implementation of that exchange: ``RadarOperator`` uses it under
+``torchrun`` and ``bench.py`` times it, so the scaling that is measured is the scaling a user gets.
+"""
+import os
+
 import numpy as np
 
 
@@ -25,31 +30,88 @@ def shard_bounds(n_items, rank, world):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
-def all_gather_rays(local, n_total, group=None):
-    """local: torch tensor [C, n_local, G] (any device); returns [C, n_total, G] holding every
-    rank's block in rank order.  Uneven blocks are padded to the largest one."""
+# ---------------------------------------------------------------------------------------------
+# process set-up
+# ---------------------------------------------------------------------------------------------
+def bind_cpu_to_gpu(device, local_rank=None, local_world=None):
+    """Pin this process to the host cores that are local to its GPU (NVML's CPU affinity of the
+    device), sharing them out between the ranks of the box: pinned host buffers are then allocated,
+    and the device -> host copies issued, from the GPU's own NUMA node.  Returns the core list or
+    None when NVML / sched_setaffinity are not available (nothing is changed then)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        hdl = pynvml.nvmlDeviceGetHandleByIndex(int(device))
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(hdl, (n_cpu + 63) // 64)
+        cores = [64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1]
+        allowed = sorted(set(cores) & set(os.sched_getaffinity(0)))
+        if not allowed:
+            return None
+        if local_rank is not None and local_world and local_world > 1:
+            # ranks whose GPUs share a NUMA node split its cores so that their copy threads do not collide
+            same = []
+            for d in range(local_world):
+                try:
+                    w = pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(d), (n_cpu + 63) // 64)
+                    if list(w) == list(words):
+                        same.append(d)
+                except Exception:
+                    pass
+            if local_rank in same and len(allowed) >= len(same):
+                per = len(allowed) // len(same)
+                k = same.index(local_rank)
+                allowed = allowed[k * per:(k + 1) * per]
+        os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:
+        return None
+
+
+def init_distributed(local_rank=None, backend=None, max_ctas=8, bind_cpu=True):
+    """Join the torch.distributed job described by the torchrun environment (RANK, WORLD_SIZE,
+    LOCAL_RANK, MASTER_*).  NCCL is limited to a few CTAs: the gather of one step runs beside the
+    persistent kernels of the next one, which fill every SM, and ~20 MB per peer need no more.
+    Returns (rank, world, local_rank)."""
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    if local_rank is None:
+        local_rank = int(os.environ.get('LOCAL_RANK', 0))
+    use_cuda = torch.cuda.is_available()
+    if backend is None:
+        backend = 'nccl' if use_cuda else 'gloo'
+    if use_cuda:
+        torch.cuda.set_device(local_rank)
+        if bind_cpu:
+            bind_cpu_to_gpu(local_rank, local_rank, int(os.environ.get('LOCAL_WORLD_SIZE', world)))
+    if world > 1 and not dist.is_initialized():
+        if backend == 'nccl':
+            os.environ.setdefault('NCCL_MAX_CTAS', str(int(max_ctas)))
+            dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
+        else:
+            dist.init_process_group(backend)
+    return rank, world, local_rank
+
+
+def agree_status(code, device=None):
+    """MAX over the ranks of an integer status, so that every rank raises (or not) together and none
+    is left waiting inside a collective."""
     import torch
     import torch.distributed as dist
     rank, world = dist_info()
     if world == 1:
-        return local
-    n_max = (n_total + world - 1) // world
-    C, n_local, G = local.shape
-    send = local
-    if n_local != n_max:
-        send = torch.zeros((C, n_max, G), dtype=local.dtype, device=local.device)
-        send[:, :n_local] = local
-    send = send.contiguous()
-    recv = torch.empty((world * C, n_max, G), dtype=local.dtype, device=local.device)
-    dist.all_gather_into_tensor(recv, send, group=group)      # concatenated along dim 0
-    recv = recv.view(world, C, n_max, G)
-    parts = []
-    for r in range(world):
-        lo, hi = shard_bounds(n_total, r, world)
-        parts.append(recv[r, :, :hi - lo])
-    return torch.cat(parts, dim=1)
+        return int(code)
+    dev = 'cpu' if (device is None or dist.get_backend() == 'gloo') else 'cuda:{}'.format(device)
+    t = torch.tensor([int(code)], dtype=torch.int32, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return int(t.item())
 
 
+# ---------------------------------------------------------------------------------------------
+# the gather
+# ---------------------------------------------------------------------------------------------
 class DeviceArray(object):
     """__cuda_array_interface__ view of a raw device pointer (to hand libradop's device-
     resident outputs to torch.distributed without a host round trip)."""
@@ -59,6 +121,160 @@ class DeviceArray(object):
                                          'data': (int(ptr), False), 'version': 3, 'strides': None}
 
 
-def device_tensor(ptr, shape, device):
+def device_tensor(ptr, shape, device, typestr='<f4'):
     import torch
-    return torch.as_tensor(DeviceArray(ptr, shape), device='cuda:{}'.format(device))
+    return torch.as_tensor(DeviceArray(ptr, shape, typestr), device='cuda:{}'.format(device))
+
+
+class _Pending(object):
+    __slots__ = ('recv', 'n_total', 'C', 'G', 'done', 'dtype')
+
+
+class RayGather(object):
+    """Gather of per-ray blocks ``[C, n_local, G]`` (rank order = ray order) into the full ray list.
+
+    ``mode='all'``: every rank receives everything (all_gather); ``mode='root'``: only rank 0 does
+    (gather).  On CUDA tensors the exchange is asynchronous: ``launch`` takes a staging copy of the
+    local block on the producer's stream (so the producer may overwrite its buffer at once), the
+    collective runs on a private side stream, and ``wait`` makes a consumer stream (or the host)
+    wait for it -- the gather of step k runs beside the kernels of step k + 1.  Buffers are kept
+    between calls.  CPU tensors (gloo) take the same code path synchronously."""
+
+    def __init__(self, mode='all', depth=2):
+        assert mode in ('all', 'root')
+        self.mode = mode
+        self.depth = max(1, int(depth))
+        self._slots = {}
+        self._turn = 0
+        self._comm = None
+        self._host = {}
+
+    def _comm_stream(self, device):
+        import torch
+        if self._comm is None:
+            self._comm = torch.cuda.Stream(device=device)
+        return self._comm
+
+    def _slot(self, key, C, n_max, G, dtype, device, world, want_recv):
+        import torch
+        slots = self._slots.setdefault(key, [None] * self.depth)
+        i = self._turn % self.depth
+        self._turn += 1
+        s = slots[i]
+        if s is None:
+            s = {'send': torch.zeros((C, n_max, G), dtype=dtype, device=device), 'recv': None, 'free': None}
+            slots[i] = s
+        if want_recv and s['recv'] is None:
+            s['recv'] = torch.empty((world, C, n_max, G), dtype=dtype, device=device)
+        return s
+
+    def launch(self, local, n_total, producer_stream=None):
+        """local: tensor [C, n_local, G] of this rank's rays (n_local may be 0).  Returns a handle."""
+        import torch
+        import torch.distributed as dist
+        rank, world = dist_info()
+        C, n_local, G = local.shape
+        lo, hi = shard_bounds(n_total, rank, world)
+        assert n_local == hi - lo, 'block does not match the shard bounds'
+        n_max = (n_total + world - 1) // world
+        p = _Pending()
+        p.n_total, p.C, p.G, p.dtype, p.done = n_total, C, G, local.dtype, None
+        if world == 1:
+            p.recv = local.reshape(1, C, n_local, G)
+            return p
+        want_recv = self.mode == 'all' or rank == 0
+        s = self._slot((C, n_max, G, local.dtype, str(local.device)), C, n_max, G, local.dtype, local.device, world, want_recv)
+        cuda = local.is_cuda
+        if cuda:
+            prod = producer_stream if producer_stream is not None else torch.cuda.current_stream(local.device)
+            comm = self._comm_stream(local.device)
+            with torch.cuda.stream(prod):
+                if s['free'] is not None:
+                    prod.wait_event(s['free'])          # the previous user of this slot has been sent
+                if n_local:
+                    s['send'][:, :n_local].copy_(local, non_blocking=True)
+                ready = torch.cuda.Event()
+                ready.record(prod)
+            comm.wait_event(ready)
+            with torch.cuda.stream(comm):
+                self._collective(dist, s, rank, world)
+                s['free'] = torch.cuda.Event()
+                s['free'].record(comm)
+            p.done = s['free']
+        else:
+            if n_local:
+                s['send'][:, :n_local].copy_(local)
+            self._collective(dist, s, rank, world)
+        p.recv = s['recv']
+        return p
+
+    def _collective(self, dist, s, rank, world):
+        if self.mode == 'all':
+            dist.all_gather_into_tensor(s['recv'].view(world * s['send'].shape[0], *s['send'].shape[1:]), s['send'])
+        else:
+            dist.gather(s['send'], list(s['recv'].unbind(0)) if rank == 0 else None, dst=0)
+
+    def wait(self, pending, consumer_stream=None):
+        """Make consumer_stream (None: the host) wait for the collective of this handle."""
+        if pending.done is None:
+            return
+        if consumer_stream is None:
+            pending.done.synchronize()
+        else:
+            consumer_stream.wait_event(pending.done)
+
+    def blocks(self, pending):
+        """Per-rank views [C, n_r, G] in rank (= ray) order, or None on a rank that received nothing."""
+        if pending.recv is None:
+            return None
+        rank, world = dist_info()
+        out = []
+        for r in range(pending.recv.shape[0]):
+            lo, hi = shard_bounds(pending.n_total, r, world) if world > 1 else (0, pending.recv.shape[2])
+            out.append(pending.recv[r, :, :hi - lo])
+        return out
+
+    def to_host(self, pending, out=None, key=None):
+        """Assembled [C, n_total, G] on the host (torch tensor; pinned when the blocks are on a GPU).  The
+        copies are contiguous per (rank, channel); returns None where nothing was received.  Without `out`
+        the result lives in a pinned buffer owned by this object (one per `key` and shape) that the next
+        call with the same key overwrites."""
+        import torch
+        blocks = self.blocks(pending)
+        if blocks is None:
+            return None
+        self.wait(pending)
+        C, G, n_total = pending.C, pending.G, pending.n_total
+        cuda = blocks[0].is_cuda
+        if out is None:
+            hk = (key, C, n_total, G, pending.dtype)
+            out = self._host.get(hk)
+            if out is None:
+                if len(self._host) > 16:
+                    self._host.clear()
+                out = torch.empty((C, n_total, G), dtype=pending.dtype, pin_memory=cuda)
+                self._host[hk] = out
+        row = 0
+        for b in blocks:
+            n = b.shape[1]
+            if n:
+                for c in range(C):
+                    out[c, row:row + n].copy_(b[c], non_blocking=cuda)
+            row += n
+        if cuda:
+            torch.cuda.current_stream(blocks[0].device).synchronize()
+        return out
+
+
+def all_gather_rays(local, n_total, group=None):
+    """local: torch tensor [C, n_local, G] (any device); returns [C, n_total, G] holding every
+    rank's block in rank order (synchronous convenience wrapper around RayGather)."""
+    import torch
+    rank, world = dist_info()
+    if world == 1:
+        return local
+    g = RayGather('all', depth=1)
+    p = g.launch(local.contiguous(), n_total)
+    if local.is_cuda:
+        g.wait(p, torch.cuda.current_stream(local.device))
+    return torch.cat(g.blocks(p), dim=1)

@@ -65,7 +65,9 @@ class SimulatedScan(object):
 
 
 class RadarOperator(object):
-    def __init__(self, options_file=None, output_variables='all', device=None, lut_folder=None):
+    def __init__(self, options_file=None, output_variables='all', device=None, lut_folder=None, gather='all'):
+        """gather: under torch.distributed the rays of a scan are sharded over the ranks; 'all' hands the
+        assembled scan to every rank, 'root' to rank 0 only (the other ranks' get_PPI / get_RHI return None)."""
         print('Reading options defined in options file')
         cfg.init(options_file)
         self.current_microphys_scheme = '1mom'
@@ -79,6 +81,10 @@ class RadarOperator(object):
         self._engine = None
         self._dirty = {'params': True, 'model': True, 'lut': True}
         self._engine_flags = None
+        self.gather_mode = gather
+        self._gather = None
+        self._traj_cache = {}
+        self._scan_cache = {}
         self.config = cfg.CONFIG
         if output_variables in ('all', 'only_model', 'only_radar'):
             self.output_variables = output_variables
@@ -112,6 +118,8 @@ class RadarOperator(object):
         cfg.CONFIG = checked
         constants.update()
         self._dirty['params'] = True
+        self._traj_cache = {}
+        self._scan_cache = {}
         if reload_lut:
             self.set_lut()
 
@@ -184,6 +192,8 @@ class RadarOperator(object):
         dic_vars = dict(dic_vars)
         if 'N' in dic_vars:          # refractivity for the ODE refraction scheme (radar_operator.py:294-296)
             self.N = dic_vars.pop('N')
+        self._traj_cache = {}
+        self._scan_cache = {}
         self.dic_vars = dic_vars
         self._dirty['model'] = True
         changed = scheme != self.current_microphys_scheme
@@ -247,14 +257,41 @@ class RadarOperator(object):
             self._dirty['lut'] = False
         return eng
 
+    def _trajectory(self, elevation):
+        """(s, h, e) of one beam elevation; depends on the elevation, the radar and the refraction scheme only
+        (atm_refraction.py:181-220), so it is kept between scans (the reference's own ``list_refraction`` reuse
+        hook, interpolation.py:104-111, is never used by its callers)."""
+        key = float(elevation)
+        t = self._traj_cache.get(key)
+        if t is None:
+            c = self.__config
+            t = compute_trajectory_radial(constants.RANGE_RADAR, elevation, c['radar']['coords'],
+                                          c['refraction']['scheme'], self.N, c['radar']['type'])
+            if len(self._traj_cache) > 65536:
+                self._traj_cache = {}
+            self._traj_cache[key] = t
+        return t
+
     def build_scan(self, ray_az, ray_el):
         """Host-side scan description: quadrature fan, one trajectory group per distinct
         elevation (the refraction depends on the elevation only, atm_refraction.py:181-220),
-        Nyquist velocity of the central sub-beam (doppler_scatter.py:432-437)."""
+        Nyquist velocity of the central sub-beam (doppler_scatter.py:432-437).  The last few scan
+        descriptions are kept: a repeated get_PPI / get_RHI on the same ray list does no host work."""
         c = self.__config
+        ray_az = np.ascontiguousarray(ray_az, dtype=np.float64)
+        ray_el = np.ascontiguousarray(ray_el, dtype=np.float64)
+        f = c['radar']['nyquist_velocity']
+        ckey = None
+        if not callable(f):
+            import hashlib
+            hsh = hashlib.blake2b(digest_size=16)
+            hsh.update(ray_az.tobytes())
+            hsh.update(ray_el.tobytes())
+            ckey = hsh.hexdigest()
+            hit = self._scan_cache.get(ckey)
+            if hit is not None:
+                return hit
         fan = subbeam_fan(c)
-        ray_az = np.asarray(ray_az, dtype=np.float64)
-        ray_el = np.asarray(ray_el, dtype=np.float64)
         uniq, inv = np.unique(ray_el, return_inverse=True)
         rr = constants.RANGE_RADAR
         ng, nv = len(rr), len(fan.pts_ver)
@@ -265,77 +302,133 @@ class RadarOperator(object):
             raise ValueError('refraction scheme 2 (Zeng and Blahak 2014) needs the refractivity N among the model variables')
         for i, el in enumerate(uniq):
             for j, pt in enumerate(fan.pts_ver):
-                ts[i, j], th[i, j], te[i, j] = compute_trajectory_radial(rr, pt + el, c['radar']['coords'],
-                                                                          c['refraction']['scheme'], self.N,
-                                                                          c['radar']['type'])
+                ts[i, j], th[i, j], te[i, j] = self._trajectory(pt + el)
         nyq = None
-        f = c['radar']['nyquist_velocity']
         if f is not None:
-            el0 = ray_el + fan.dele[fan.center]
-            az0 = ray_az + fan.daz[fan.center]
-            cache = {}
             nyq = np.empty(len(ray_az), np.float32)
-            for i, (e0, a0) in enumerate(zip(el0, az0)):
-                key = (e0, a0) if callable(f) else None
-                if callable(f):
-                    if e0 not in cache:
-                        cache[e0] = f(e0, a0)
-                    nyq[i] = cache[e0]
-                else:
-                    nyq[i] = float(f)
-        return Scan(ray_az, ray_el, inv.astype(np.int32), nyq, fan, ts, th, te)
+            if callable(f):
+                # nyquist_velocity(elev_0, az_0) of the central sub-beam, per ray (doppler_scatter.py:431-437)
+                el0 = ray_el + fan.dele[fan.center]
+                az0 = ray_az + fan.daz[fan.center]
+                cache = {}
+                for i, key in enumerate(zip(el0, az0)):
+                    if key not in cache:
+                        cache[key] = f(key[0], key[1])
+                    nyq[i] = cache[key]
+            else:
+                nyq[:] = float(f)
+        scan = Scan(ray_az, ray_el, inv.astype(np.int32), nyq, fan, ts, th, te)
+        if ckey is not None:
+            if len(self._scan_cache) >= 4:
+                self._scan_cache.pop(next(iter(self._scan_cache)))
+            self._scan_cache[ckey] = scan
+        return scan
 
-    def simulate_rays(self, ray_az, ray_el, keep_debug=False, distributed=True):
+    def simulate_rays(self, ray_az, ray_el, keep_debug=False, distributed=True, copy=True):
         """Batched hot path over an arbitrary ray list; returns dict name -> [n_rays, n_gates].
-        With torch.distributed initialised (and distributed=True) the rays are sharded over the
-        ranks and every rank receives the full result."""
+        With torch.distributed initialised (and distributed=True) the ONE ray list is cut into contiguous
+        blocks, one per rank, as the reference splits it over its pool workers (radar_operator.py:402-435),
+        and the result is gathered over NCCL (``gather='all'``: on every rank, ``'root'``: on rank 0, None
+        elsewhere).  copy=False returns views of the pinned host buffers the operator owns (valid until its next
+        call) instead of fresh arrays."""
         eng = self._prepare_engine(keep_debug=keep_debug)
         ray_az = np.asarray(ray_az, dtype=np.float64)
         ray_el = np.asarray(ray_el, dtype=np.float64)
-        n_total = len(ray_az)
         rank, world = parallel.dist_info() if distributed else (0, 1)
         want_model = self.output_variables in ('all', 'only_model')
         if world == 1:
             scan = self.build_scan(ray_az, ray_el)
             self._last_scan = scan
             arrays = eng.simulate(scan, want_latlon=True, want_model=want_model)
-            out = {k: np.array(v, copy=True) for k, v in arrays.items()}
+            out = {k: (np.array(v, copy=True) if copy else v) for k, v in arrays.items()}
             out['dist'] = scan.traj_s[scan.ray_traj, scan.fan.j_ver[scan.fan.center]]
             out['heights'] = scan.traj_h[scan.ray_traj, scan.fan.j_ver[scan.fan.center]]
             return out
-        return self._simulate_sharded(eng, ray_az, ray_el, rank, world, want_model)
+        return self._simulate_sharded(eng, ray_az, ray_el, rank, world, want_model, copy)
 
-    def _simulate_sharded(self, eng, ray_az, ray_el, rank, world, want_model):
+    def _simulate_sharded(self, eng, ray_az, ray_el, rank, world, want_model, copy=True):
+        """Rank r simulates rays [lo_r, hi_r) of the list; observables, positions, model variables and
+        spectra travel device -> device through parallel.RayGather (no host bounce), the receiving ranks copy
+        the assembled result to pinned host memory.  A rank without rays (more ranks than rays) takes part
+        in the collectives with an empty block; the ranks agree on an error status BEFORE the first data
+        collective, so a shard that leaves the model domain raises IndexError on every rank instead of
+        leaving its peers waiting."""
         import torch
+        from ._abi import BUF_OBS, BUF_LAT, BUF_LON, BUF_MODEL, BUF_DSPECTRUM
         n_total = len(ray_az)
         lo, hi = parallel.shard_bounds(n_total, rank, world)
-        scan = self.build_scan(ray_az[lo:hi], ray_el[lo:hi])
-        self._last_scan = scan
-        eng.stage(scan)
-        eng.execute()
-        eng.synchronize()
-        ptr, nr, ng = eng.device_outputs()
-        local = parallel.device_tensor(ptr, (len(OUT_NAMES) + 1, nr, ng), eng.device)
-        full = parallel.all_gather_rays(local, n_total)
-        host = full.cpu().numpy()
-        out = {name: host[i] for i, name in enumerate(OUT_NAMES)}
-        out['mask'] = host[len(OUT_NAMES)]
-        # geometry of every ray is cheap host arithmetic: recompute instead of gathering
-        arrays = eng.fetch(scan, want_latlon=True, want_model=want_model)
-        lat = torch.from_numpy(np.array(arrays['lat'], copy=True)[None]).cuda(eng.device)
-        lon = torch.from_numpy(np.array(arrays['lon'], copy=True)[None]).cuda(eng.device)
-        out['lat'] = parallel.all_gather_rays(lat, n_total)[0].cpu().numpy()
-        out['lon'] = parallel.all_gather_rays(lon, n_total)[0].cpu().numpy()
-        if 'DSPECTRUM' in arrays:
-            sp = np.array(arrays['DSPECTRUM'], copy=True)          # [n_local, n_gates, n_vel]
-            loc = torch.from_numpy(np.ascontiguousarray(sp.transpose(2, 0, 1))).cuda(eng.device)
-            out['DSPECTRUM'] = np.ascontiguousarray(parallel.all_gather_rays(loc, n_total).cpu().numpy().transpose(1, 2, 0))
+        n_loc = hi - lo
+        ng = len(constants.RANGE_RADAR)
+        code, err, scan = 0, None, None
+        try:
+            if n_loc:
+                scan = self.build_scan(ray_az[lo:hi], ray_el[lo:hi])
+                self._last_scan = scan
+                eng.stage(scan)
+                eng.execute()
+                eng.finish()                   # drains the stream, raises what the kernels flagged
+        except IndexError as e:
+            code, err = 3, e
+        except ValueError as e:
+            code, err = 2, e
+        except Exception as e:                 # noqa: BLE001 -- every rank must reach agree_status
+            code, err = 1, e
+        worst = parallel.agree_status(code, eng.device)
+        if worst:
+            if err is not None and code == worst:
+                raise err
+            exc = {3: IndexError, 2: ValueError}.get(worst, RuntimeError)
+            raise exc('another rank failed on its shard of the scan (status {})'.format(worst))
+        if self._gather is None or self._gather.mode != self.gather_mode:
+            self._gather = parallel.RayGather(self.gather_mode, depth=1)
+        G = self._gather
+        dev = eng.device
+        stream = torch.cuda.ExternalStream(eng.stream_ptr(), device=torch.device('cuda', dev))
+
+        def local_block(which, C, width, typestr='<f4', dtype=torch.float32):
+            if not n_loc:
+                return torch.empty((C, 0, width), dtype=dtype, device='cuda:{}'.format(dev))
+            ptr, _ = eng.device_buffer(which)
+            return parallel.device_tensor(ptr, (C, n_loc, width), dev, typestr)
+
+        def gathered(which, C, width, typestr='<f4', dtype=torch.float32):
+            pend = G.launch(local_block(which, C, width, typestr, dtype), n_total, stream)
+            host = G.to_host(pend, key=which)
+            if host is None:
+                return None
+            return np.array(host.numpy(), copy=True) if copy else host.numpy()
+
+        receives = self.gather_mode == 'all' or rank == 0
+        out = {}
+        obs = gathered(BUF_OBS, len(OUT_NAMES) + 1, ng)
+        if receives:
+            for i, name in enumerate(OUT_NAMES):
+                out[name] = obs[i]
+            out['mask'] = obs[len(OUT_NAMES)]
+        # positions depend on the ray list only: gathered once per geometry
+        gkey = (self.build_scan(ray_az, ray_el).geometry_key(), world, self.gather_mode)
+        if getattr(self, '_latlon_sharded', (None,))[0] == gkey:
+            lat, lon = self._latlon_sharded[1:]
+        else:
+            lat = gathered(BUF_LAT, 1, ng, '<f8', torch.float64)
+            lon = gathered(BUF_LON, 1, ng, '<f8', torch.float64)
+            if lat is not None and not copy:
+                lat, lon = lat.copy(), lon.copy()
+            self._latlon_sharded = (gkey, lat, lon)
+        if receives:
+            out['lat'], out['lon'] = lat[0], lon[0]
+        if self.__config['doppler']['scheme'] == 3 and self.output_variables in ('all', 'only_radar'):
+            n_vel = len(constants.VARRAY)
+            sp = gathered(BUF_DSPECTRUM, 1, ng * n_vel)
+            if receives:
+                out['DSPECTRUM'] = sp[0].reshape(n_total, ng, n_vel)
         if want_model:
-            names = list(eng.uploaded_vars)
-            loc = torch.from_numpy(np.stack([arrays[n] for n in names])).cuda(eng.device)
-            g = parallel.all_gather_rays(loc, n_total).cpu().numpy()
-            for i, n in enumerate(names):
-                out[n] = g[i]
+            mv = gathered(BUF_MODEL, len(VAR_IDS), ng)
+            if receives:
+                for n in eng.uploaded_vars:
+                    out[n] = mv[VAR_IDS[n]]
+        if not receives:
+            return None
         full_scan = self.build_scan(ray_az, ray_el)
         out['dist'] = full_scan.traj_s[full_scan.ray_traj, full_scan.fan.j_ver[full_scan.fan.center]]
         out['heights'] = full_scan.traj_h[full_scan.ray_traj, full_scan.fan.j_ver[full_scan.fan.center]]
@@ -372,6 +465,8 @@ class RadarOperator(object):
         el = np.repeat(np.asarray(elevations, dtype=np.float64), len(azimuths))
         az = np.tile(azimuths, len(elevations))
         out = self.simulate_rays(az, el)
+        if out is None:                   # gather='root' on a rank other than 0
+            return None
         return self._assemble('ppi', out, len(elevations), len(azimuths), elevations, azimuths)
 
     def get_RHI(self, azimuths, elevations=None, elev_step=None, elev_start=0, elev_stop=90):
@@ -386,11 +481,15 @@ class RadarOperator(object):
         az = np.repeat(np.asarray(azimuths, dtype=np.float64), len(elevations))
         el = np.tile(elevations, len(azimuths))
         out = self.simulate_rays(az, el)
+        if out is None:
+            return None
         return self._assemble('rhi', out, len(azimuths), len(elevations), elevations, azimuths)
 
     def get_VPROF(self):
         """Vertical profile: one ray at 90 degrees elevation (radar_operator.py:311-354)."""
         out = self.simulate_rays([0.], [90.])
+        if out is None:
+            return None
         return self._assemble('vprof', out, 1, 1, [90.], [0.])
 
     # ------------------------------------------------------------------- single-ray helpers
@@ -416,10 +515,8 @@ class RadarOperator(object):
             e = scan.traj_e[0, j].copy()
             sub = Radial(vals, st, None, None, scan.traj_s[0, j], scan.traj_h[0, j], e,
                          [azimuth + fan.daz[q], elevation + fan.dele[q]], fan.weight[q])
-            sub._ray_result = result
-            sub._ray_model = model
             subs.append(sub)
-        return subs
+        return _interp_mod.seal_subradials(subs, result, model, self.lut_sz)
 
 
 # --------------------------------------------------------------------------------- model I/O

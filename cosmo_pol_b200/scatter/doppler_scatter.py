@@ -13,12 +13,13 @@ def get_radar_observables(list_subradials, lut_sz=None):
 
     The sub-radials must come from ``get_interpolated_radial`` of this package: that call
     already ran the fused GPU path for the ray (interpolation and scattering are one batched
-    launch sequence here), so this returns the ray's integrated Radial."""
-    res = getattr(list_subradials[0], '_ray_result', None) if len(list_subradials) else None
-    if res is None:
-        raise ValueError('get_radar_observables needs the sub-radials returned by '
-                         'cosmo_pol_b200.interpolation.get_interpolated_radial (GPU path, no CPU fallback)')
-    return res
+    launch sequence here), so this returns the ray's integrated Radial -- after checking that the
+    list is complete, in order and unmodified, and that ``lut_sz`` is the operator's own dictionary;
+    a caller that edited a sub-radial (the reference would recompute from the edit) gets a ValueError,
+    never the unedited answer."""
+    from ..interpolation.interpolation import check_sealed
+    result, _ = check_sealed(list_subradials, 'get_radar_observables', lut_sz)
+    return result
 
 
 def get_pol_from_sz(sz, KW=None):

@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define RADOP_ABI_VERSION 5
+#define RADOP_ABI_VERSION 6
 
 /* ---- status codes ------------------------------------------------------- */
 enum {
@@ -178,6 +178,10 @@ int radop_create(int device, RadopHandle **out);
 int radop_destroy(RadopHandle *h);
 const char *radop_last_error(const RadopHandle *h);
 int radop_abi_version(void);
+/* sizeof() of the ABI structs as this library was compiled: a binding checks its own layout against it
+ * before the first radop_set_params (which = RADOP_SIZEOF_*; unknown -> -1). */
+enum { RADOP_SIZEOF_PARAMS = 0, RADOP_SIZEOF_SPECIES, RADOP_SIZEOF_SCAN, RADOP_SIZEOF_OUT, RADOP_SIZEOF_STATS };
+int radop_sizeof(int which);
 
 /* ---- configuration and one-time uploads ----------------------------------- */
 int radop_set_params(RadopHandle *h, const RadopParams *p);
@@ -247,6 +251,15 @@ int radop_debug_integration(RadopHandle *h, int species, int64_t why[4], int32_t
 int radop_get_geodesy(RadopHandle *h, int *used_polynomials);
 
 int radop_device_outputs(RadopHandle *h, void **dev_ptr, int64_t *n_rays, int64_t *n_gates);
+/* Any device-resident result of the last radop_execute, for gathers that must not bounce through the host
+ * (one rank per GPU, cosmo_pol_b200/parallel.py): which = RADOP_BUF_*; *dev_ptr / *bytes describe
+ *   RADOP_BUF_OBS        float32 [RADOP_N_OUT + 1][n_rays][n_gates]   (same as radop_device_outputs)
+ *   RADOP_BUF_LAT / LON  float64 [n_rays][n_gates]                    central sub-beam positions
+ *   RADOP_BUF_MODEL      float32 [RADOP_NVAR_MAX][n_rays][n_gates]    integrate_radials (output_model_vars)
+ *   RADOP_BUF_DSPECTRUM  float32 [n_rays][n_gates][n_vel]             Doppler scheme 3
+ * A buffer the configuration does not produce gives RADOP_ERR_STATE. */
+enum { RADOP_BUF_OBS = 0, RADOP_BUF_LAT, RADOP_BUF_LON, RADOP_BUF_MODEL, RADOP_BUF_DSPECTRUM };
+int radop_device_buffer(RadopHandle *h, int which, void **dev_ptr, int64_t *bytes);
 /* cudaStream_t of the handle (as void*), to record events on. */
 int radop_get_stream(RadopHandle *h, void **stream);
 
@@ -289,6 +302,14 @@ int radop_get_all_radar_pts(RadopHandle *h, int n, const float *coords_rad_pts,
                             const float *radar_heights, const float *model_data,
                             const float *model_heights, int nz, int ny, int nx,
                             const float *llc_cosmo, const float *res_cosmo, float *output);
+/* doppler_c.c:11  get_refl(refl[len], Da[len][nhydro], Db[len][nhydro], rcs[nd][nhydro], D[nd][nhydro],
+ *                          N[nd][nhydro], step_D[nhydro], Dmin[nhydro]):
+ * refl[i] = sum_j step_D[j] * sum_{k = int((Da - Dmin)/step) .. int((Db - Dmin)/step) - 1} N[k][j] rcs[k][j]
+ * in the reference's float32 order of operations (bit-exact against the gcc build for in-range indices;
+ * indices outside [0, nd] -- undefined behaviour in the reference -- are clamped). */
+int radop_get_refl(RadopHandle *h, int len, int nhydro, int nd, const float *Da, const float *Db,
+                   const float *rcs, const float *D, const float *N, const float *step_D,
+                   const float *Dmin, float *refl);
 
 #ifdef __cplusplus
 }

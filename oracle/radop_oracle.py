@@ -582,6 +582,74 @@ def get_interpolated_radial(model, azimuth, elevation, cfg, debug=False):
     return subs
 
 
+def sweep_indices(model, luts, cfg, azimuths, elevation, geod=None):
+    """The integer decisions of every sub-beam gate of one sweep (all `azimuths` at one `elevation`), vectorised
+    over the rays: what get_interpolated_radial (interpolation.py:381-438, 498-597; interpolation_c.c:42-103) and
+    lookup_line (lut.py:336-342) decide for integration scheme 1, refraction scheme 1, without the melting scheme.
+    Same arithmetic as get_interpolated_radial / get_radar_observables above, element for element (numpy's
+    elementwise kernels do not depend on the array shape), so that a whole 7200-ray volume can be checked in
+    minutes.  Returns dict of arrays [n_rays, n_sub, n_gates(, ...)]: cell [.., 2], level [.., 4], status,
+    lut_e / lut_t [.., n_species] (-1 where the species is inactive), rot [.., 2] float64 rotated coordinates.
+    geod: alternative direct-geodesic function (lon0, lat0, azimuth, dist) -> (lon, lat), default geod_fwd."""
+    geod = geod_fwd if geod is None else geod
+    names = list(model['vars'].keys())
+    rranges = derived_constants(cfg)['RANGE_RADAR']
+    radar_pos = cfg['radar']['coords']
+    pts_hor, pts_ver, weights, keep = gauss_hermite_subbeams(cfg)
+    refr = [ref_4_3(rranges, pt + elevation, radar_pos) for pt in pts_ver]
+    species = species_list(cfg)
+    proj = model['proj']
+    llc = np.asarray((float(proj['Lo1']), float(proj['La1']))).astype('float32')
+    urc = np.asarray((float(proj['Lo2']), float(proj['La2']))).astype('float32')
+    res = model['resolution']
+    azimuths = np.asarray(azimuths, dtype=np.float64)
+    nr, ng = len(azimuths), len(rranges)
+    subs = [(i, j) for i in range(len(pts_hor)) for j in range(len(pts_ver)) if keep[i, j]]
+    out = {'cell': np.zeros((nr, len(subs), ng, 2), np.int32), 'level': np.zeros((nr, len(subs), ng, 4), np.int32),
+           'status': np.zeros((nr, len(subs), ng), np.int32), 'rot': np.zeros((nr, len(subs), ng, 2), np.float64),
+           'lut_e': np.full((nr, len(subs), ng, len(species)), -1, np.int32),
+           'lut_t': np.full((nr, len(subs), ng, len(species)), -1, np.int32)}
+    for q, (i, j) in enumerate(subs):
+        s, h, e = refr[j]
+        lons, lats = geod(radar_pos[1], radar_pos[0], (pts_hor[i] + azimuths)[:, None], np.asarray(s, np.float64)[None, :])
+        coords = wgs_to_rotated(lats.ravel(), lons.ravel(), proj['Latitude_of_southern_pole'],
+                                proj['Longitude_of_southern_pole'])
+        if (np.any(coords[:, 1] < llc[0]) or np.any(coords[:, 0] < llc[1]) or
+                np.any(coords[:, 1] > urc[0]) or np.any(coords[:, 0] > urc[1])):
+            raise OutOfDomain('radar domain is not entirely contained in the model domain')
+        hh = np.tile(h, nr)
+        first, cell, level, status = interp_port(coords, hh, model['vars'][names[0]], model['z_levels'], llc, res, debug=True)
+        mask = np.zeros(len(first))
+        mask[first == -9999] = 1
+        mask[np.isnan(first)] = -1
+        out['cell'][:, q] = cell.reshape(nr, ng, 2)
+        out['level'][:, q] = level.reshape(nr, ng, 4)
+        out['status'][:, q] = status.reshape(nr, ng)
+        out['rot'][:, q] = coords.reshape(nr, ng, 2)
+        ef = np.array(e, copy=True)
+        ef[ef > 90] = 180 - ef[ef > 90]
+        ef[ef < 0] = -ef[ef < 0]
+        ef = np.tile(ef, nr)
+        T = interp_gates(coords, hh, model['vars']['T'], model['z_levels'], llc, res)
+        T[mask != 0] = np.nan
+        for k, hname in enumerate(species):
+            QM = interp_gates(coords, hh, model['vars']['Q' + hname + '_v'], model['z_levels'], llc, res)
+            QM[mask != 0] = np.nan
+            with np.errstate(invalid='ignore'):
+                valid = QM > 0
+            lut = luts[hname]
+            v = lut['value_table']
+            ie = lut_index(ef[valid], lut['axes_limits'][0][0], lut['axes_step'][0], v.shape[0])
+            it = lut_index(T[valid], lut['axes_limits'][1][0], lut['axes_step'][1], v.shape[1])
+            le = np.full(nr * ng, -1, np.int32)
+            lt = np.full(nr * ng, -1, np.int32)
+            le[valid] = ie
+            lt[valid] = it
+            out['lut_e'][:, q, :, k] = le.reshape(nr, ng)
+            out['lut_t'][:, q, :, k] = lt.reshape(nr, ng)
+    return out
+
+
 def _nansum2(x, y):
     """utilities.nansum_arr (utilities.py:231-261) for equal shapes or y shorter
     (zero padded at the end)."""

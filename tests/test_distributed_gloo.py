@@ -57,3 +57,52 @@ def test_all_gather_rays_gloo_world2(n_total):
     assert sorted(r[0] for r in res) == [0, 1]
     assert all(r[1] for r in res)
     assert all(r[2][1] == 2 for r in res)
+
+
+def _worker_gather(rank, world, port, n_total, mode, q):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from cosmo_pol_b200 import parallel
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        lo, hi = parallel.shard_bounds(n_total, rank, world)
+        full = torch.arange(2 * n_total * 3, dtype=torch.float64).reshape(2, n_total, 3)
+        g = parallel.RayGather(mode, depth=2)
+        ok = True
+        for rep in range(3):                                   # slots are reused
+            pend = g.launch((full[:, lo:hi] + rep).contiguous(), n_total)
+            host = g.to_host(pend, key='x')
+            if mode == 'all' or rank == 0:
+                ok = ok and host is not None and bool(torch.equal(host, full + rep))
+            else:
+                ok = ok and host is None
+        # every rank learns the worst status (here: rank 1 reports 3)
+        worst = parallel.agree_status(3 if rank == 1 else 0)
+        q.put((rank, ok, worst))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('n_total,mode', [(1, 'all'), (1, 'root'), (7, 'root'), (8, 'all')])
+def test_ray_gather_gloo_world2(n_total, mode):
+    """RayGather as RadarOperator._simulate_sharded uses it: empty shards (1 ray, 2 ranks), uneven blocks,
+    both modes, repeated launches, and the status agreement that precedes the data collectives."""
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_gather, args=(r, 2, port, n_total, mode, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(r[0] for r in res) == [0, 1]
+    assert all(r[1] for r in res)
+    assert all(r[2] == 3 for r in res)

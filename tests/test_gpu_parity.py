@@ -59,6 +59,34 @@ def test_interp_shim_bit_exact_against_reference_c():
     eng.close()
 
 
+def test_refl_shim_bit_exact_against_reference_c():
+    """radop_get_refl (compat shim with the data contract of doppler_c.c:11 get_refl) == the reference's C compiled
+    unmodified (oracle/_ref/libdoppler_ref.so, or the C port of it where that is absent), bit for bit: the
+    float32 bin-index arithmetic (int((D - Dmin) / step)) and the sequential float32 sums."""
+    from cosmo_pol_b200._abi import Engine
+    rng = np.random.default_rng(5)
+    nd, nh, nb = 1024, 4, 129
+    d_min = np.array([0.2, 0.2, 0.5, 0.05], np.float32)
+    d_max = np.array([8.0, 20.0, 15.0, 2.0], np.float32)
+    D = np.stack([np.linspace(a, b, nd, dtype=np.float32) for a, b in zip(d_min, d_max)], axis=1)
+    step = (D[1] - D[0]).astype(np.float32)
+    N = (10 ** rng.uniform(-6, 4, (nd, nh))).astype(np.float32)
+    rcs = (10 ** rng.uniform(-9, 1, (nd, nh))).astype(np.float32)
+    # edges inside the diameter range, some exactly on grid points, some empty / reversed intervals
+    lo = rng.uniform(0, 1, (nb, nh)).astype(np.float32)
+    hi = np.clip(lo + rng.uniform(-0.05, 0.4, (nb, nh)), 0, 1).astype(np.float32)
+    Da = (d_min + lo * (d_max - d_min)).astype(np.float32)
+    Db = (d_min + hi * (d_max - d_min)).astype(np.float32)
+    Da[::7] = D[rng.integers(0, nd, (len(Da[::7]), nh)), np.arange(nh)]
+    Db[::11] = D[-1]
+    eng = Engine(0)
+    got = eng.get_refl(Da, Db, rcs, D, N, step, d_min)
+    ref = O.spectrum_bins(Da, Db, rcs, D, N, step, d_min)
+    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))
+    assert (ref > 0).sum() > 100
+    eng.close()
+
+
 def test_shared_reciprocal_division_is_ieee():
     """The interpolation kernel divides by a reciprocal shared by all variables of a column
     (Markstein correction); it must equal the IEEE float32 division bit for bit."""
@@ -675,6 +703,37 @@ def test_edge_cases_and_errors():
         RadarOperator(conf).load_model({'T': model['T']})
 
 
+def test_single_ray_helpers_refuse_edited_subradials():
+    """get_interpolated_radial / get_radar_observables / integrate_radials keep the reference's names
+    (interpolation.py:91, doppler_scatter.py:49, interpolation.py:36) over ONE fused GPU pass per ray; the second
+    call must not hand back a stale result when the caller edited a sub-radial, dropped one or passes other tables."""
+    from cosmo_pol_b200 import RadarOperator
+    from cosmo_pol_b200.interpolation import get_interpolated_radial, integrate_radials
+    from cosmo_pol_b200.scatter.doppler_scatter import get_radar_observables
+    model, luts = synthetic_inputs()
+    op = RadarOperator(copy.deepcopy(CONF_1MOM), output_variables='all', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    subs = get_interpolated_radial(op.dic_vars, 40., 3.0)
+    assert len(subs) == 9
+    ray = get_radar_observables(subs, op.lut_sz)
+    scan = op.get_PPI([3.0], azimuths=[40.])
+    assert np.array_equal(ray.values['ZH'], scan.fields['ZH'][0, 0], equal_nan=True)
+    assert np.array_equal(integrate_radials(subs).values['T'], scan.fields['T'][0, 0], equal_nan=True)
+    with pytest.raises(ValueError):
+        get_radar_observables(subs[:-1], op.lut_sz)             # incomplete list
+    with pytest.raises(ValueError):
+        get_radar_observables(subs[::-1], op.lut_sz)            # other order
+    with pytest.raises(ValueError):
+        get_radar_observables(subs, dict(op.lut_sz))            # other table dictionary
+    subs[4].values['QR_v'][10] *= 2.0
+    with pytest.raises(ValueError):
+        get_radar_observables(subs, op.lut_sz)                  # edited profile
+    with pytest.raises(ValueError):
+        integrate_radials(subs)
+    op.close()
+
+
 def test_scan_level_properties():
     """Size-independent properties on a larger scan: determinism, ray-permutation invariance,
     azimuth periodicity, shard consistency, linearity in the scattering table."""
@@ -736,6 +795,80 @@ def test_scan_level_properties():
     assert relerr(y['ZDR'], x['ZDR']) < 1e-5, relerr(y['ZDR'], x['ZDR'])
     st = op._engine.stats()
     assert st['n_active_pairs'] > 0 and st['launches'] >= 6
+
+
+_SWEEP = {}
+
+
+def _sweep_oracle(el):
+    return O.sweep_indices(_SWEEP['model'], _SWEEP['luts'], _SWEEP['cfg'], _SWEEP['az'], el)
+
+
+def test_full_volume_every_index_bit_exact():
+    """The bit-exact index contract at the size the benchmark is quoted on: grid cell, the four column levels, the
+    status and the (e, t) lookup bin of every species for ALL 3.24e7 sub-beam gates of configuration 3 (20 elevations
+    x 360 azimuths x 9 sub-beams x 500 gates) against the oracle's interpolation half (the reference's arithmetic,
+    vectorised over the rays of a sweep: O.sweep_indices -- itself held to the per-ray oracle here on one sweep).
+    The float32 casts of the rotated coordinates, which decide the cells, must be identical as well."""
+    import multiprocessing as mp
+    import bench
+    from cosmo_pol_b200 import RadarOperator, synthetic
+    conf = bench.volume_config()
+    model, luts = bench.build_inputs()
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    cfg = oracle_cfg(op)
+    pm, pl = plain(model, luts)
+    az = np.arange(360, dtype=np.float64)
+    els = bench.VOLUME_ELEVATIONS
+    _SWEEP.update(model=pm, luts=pl, cfg=cfg, az=az)
+    # the vectorised sweep oracle against the per-ray oracle (3 rays of one sweep)
+    chk = O.sweep_indices(pm, pl, cfg, az[[0, 77, 359]], 8.5)
+    species = O.species_list(cfg)
+    for i, a in enumerate((0., 77., 359.)):
+        ref = O.simulate_ray(pm, pl, cfg, a, 8.5, accum='f64', debug=True)
+        for q, sub in enumerate(ref['subs']):
+            _, cell, level, status = sub['dbg']
+            assert np.array_equal(chk['cell'][i, q], cell) and np.array_equal(chk['level'][i, q], level)
+            assert np.array_equal(chk['status'][i, q], status)
+            assert np.array_equal(chk['rot'][i, q], sub['coords'])
+            for j, h in enumerate(species):
+                e_ref = np.full(len(status), -1)
+                t_ref = np.full(len(status), -1)
+                if (q, h) in ref['dbg']['valid']:
+                    v = ref['dbg']['valid'][(q, h)]
+                    e_ref[v] = ref['dbg']['e_idx'][(q, h)]
+                    t_ref[v] = ref['dbg']['t_idx'][(q, h)]
+                assert np.array_equal(chk['lut_e'][i, q, :, j], e_ref) and np.array_equal(chk['lut_t'][i, q, :, j], t_ref)
+    try:
+        n_proc = max(1, min(len(els), len(__import__('os').sched_getaffinity(0))))
+    except Exception:
+        n_proc = 4
+    pool = mp.get_context('fork').Pool(n_proc)
+    try:
+        pending = [pool.apply_async(_sweep_oracle, (el,)) for el in els]
+        eng = op._prepare_engine(keep_debug=True)
+        n_checked, n_active, n_cast = 0, 0, 0
+        for el, job in zip(els, pending):
+            scan = op.build_scan(az, np.full(len(az), el))
+            eng.simulate(scan)
+            dbg = eng.debug_indices(scan)
+            ref = job.get(timeout=1800)
+            for k in ('cell', 'level', 'status', 'lut_e', 'lut_t'):
+                assert np.array_equal(dbg[k], ref[k]), 'elevation {}: {} differs at {} sub-beam gates'.format(
+                    el, k, int(np.sum(np.any((dbg[k] != ref[k]).reshape(dbg['status'].shape + (-1,)), axis=-1))))
+            n_cast += int(np.sum(dbg['rot'].astype(np.float32) != ref['rot'].astype(np.float32)))
+            assert np.max(np.abs(dbg['rot'] - ref['rot'])) < 1e-10
+            n_checked += dbg['status'].size
+            n_active += int(np.sum(dbg['lut_e'] >= 0))
+    finally:
+        pool.terminate()
+        pool.join()
+    assert n_checked == 20 * 360 * 9 * 500
+    assert n_cast == 0, n_cast
+    assert n_active > 2e7
+    op.close()
 
 
 def test_full_size_volume_properties():

@@ -3,6 +3,7 @@ format, quadrature, refraction, hydrometeor classes, constants, the C-ABI export
 import ctypes
 import json
 import os
+import sys
 import re
 
 import numpy as np
@@ -182,6 +183,24 @@ def test_abi_library_exports_every_declared_symbol():
         sizes = [int(x) for x in subprocess.check_output([os.path.join(d, 't')]).split()]
     assert sizes == [ctypes.sizeof(_abi.RadopSpecies), ctypes.sizeof(_abi.RadopParams), ctypes.sizeof(_abi.RadopScan),
                      ctypes.sizeof(_abi.RadopOut), ctypes.sizeof(_abi.RadopStats)]
+
+
+def test_integration_stub_matches_library():
+    """The reference-side ctypes stub documented in INTEGRATION.md is generated from include/radop.h; execute it
+    against the built library: its own assertions compare every struct size with radop_sizeof()."""
+    import subprocess
+    from cosmo_pol_b200 import _abi
+    doc = open(os.path.join(ROOT, 'INTEGRATION.md')).read()
+    gen = subprocess.check_output([sys.executable, os.path.join(ROOT, 'scripts', 'gen_integration_stub.py'), '--print'],
+                                  universal_newlines=True)
+    assert gen in doc, 'INTEGRATION.md stub is stale: run python scripts/gen_integration_stub.py'
+    ns = {}
+    exec(gen.replace("C.CDLL('libradop.so')", 'C.CDLL({!r})'.format(_abi.LIB_PATH)), ns)
+    for name in ('RadopParams', 'RadopSpecies', 'RadopScan', 'RadopOut', 'RadopStats'):
+        assert ctypes.sizeof(ns[name]) == ctypes.sizeof(getattr(_abi, name)), name
+    assert ns['lib'].radop_sizeof(99) == -1
+    with pytest.raises(IndexError):
+        ns['check'](None, 3)
 
 
 def test_no_cpu_fallback_without_gpu():
