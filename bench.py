@@ -16,8 +16,8 @@ fields and scattering tables (no data files exist offline).
           engine's stream around exactly K steps; max over ranks.
   e2e   : the same through the reference-facing C-ABI call radop_simulate() with HOST
           buffers: ray list + trajectories copied H2D, every observable copied D2H, each step.
-  N > 1 : STRONG scaling (default): the ONE 7200-ray volume is cut into N contiguous blocks of
-          rays, 7200 / N per rank, as the reference splits its ray list over pool workers
+  N > 1 : STRONG scaling (default): the ONE 7200-ray volume is dealt out to the N ranks in blocks
+          of 4 rays (parallel.shard_indices), 7200 / N per rank, as the reference splits its ray list over pool workers
           (cosmo_pol/radar_operator.py:402-435); fields and tables are replicated; the only
           exchange is the gather of the observables to rank 0 over NCCL (parallel.RayGather,
           the same object RadarOperator uses under torchrun), inside the timed step.
@@ -78,7 +78,7 @@ def workload_config(world, scaling):
                         '3x3 GH sub-beams, synthetic COSMO grid 60x400x400 @0.02deg'
                         + ('' if scaling == 'strong' else '; one such volume PER GPU'),
             'rays_per_gpu': rays, 'rays_total': rays * world, 'gates': 500, 'sub_beams': 9, 'species': 'R,S,G,I',
-            'parallelism': 'rays sharded contiguously over {} GPU(s), fields+tables replicated, NCCL gather of the observables '
+            'parallelism': 'rays dealt block-cyclically (4 rays) to {} GPU(s), fields+tables replicated, NCCL gather of the observables '
                            'to rank 0 on a side stream (step k gathered beside the kernels of step k+1, all gathers inside '
                            'the timed region; cosmo_pol_b200.parallel.RayGather)'.format(world)
                            if world > 1 else 'single GPU',
@@ -263,11 +263,11 @@ def e2e_breakdown(op, eng, az, el, rank, world, local):
     import torch.distributed as dist
     from cosmo_pol_b200 import parallel
     from cosmo_pol_b200._abi import OUT_NAMES, BUF_OBS
-    lo, hi = parallel.shard_bounds(len(az), rank, world)
+    mine = parallel.shard_indices(len(az), rank, world)
     t = {}
     dist.barrier()
     c = time.perf_counter()
-    scan = op.build_scan(az[lo:hi], el[lo:hi])
+    scan = op.build_scan(az[mine], el[mine])
     eng.stage(scan)
     eng.synchronize()
     t['stage_h2d'] = time.perf_counter() - c
@@ -282,7 +282,7 @@ def e2e_breakdown(op, eng, az, el, rank, world, local):
     g = op._gather or parallel.RayGather('root', depth=1)
     ptr, _ = eng.device_buffer(BUF_OBS)
     stream = torch.cuda.ExternalStream(eng.stream_ptr(), device=torch.device('cuda', local))
-    pend = g.launch(parallel.device_tensor(ptr, (len(OUT_NAMES) + 1, hi - lo, scan.n_gates), local), len(az), stream)
+    pend = g.launch(parallel.device_tensor(ptr, (len(OUT_NAMES) + 1, len(mine), scan.n_gates), local), len(az), stream)
     g.wait(pend)
     torch.cuda.synchronize()
     t['nccl_gather'] = time.perf_counter() - c
@@ -333,6 +333,9 @@ def run_ours(args):
     op.load_model(model)
     eng = op._prepare_engine()
     eng.set_integration(args.integration)
+    eng.set_pipeline(args.pipeline)
+    if os.environ.get('RADOP_FUSED_WARPS'):
+        eng.set_tuning('fused_warps', int(os.environ['RADOP_FUSED_WARPS']))
     t_up = time.time() - t_up
     scaling = args.scaling if world > 1 else 'strong'
     az_full, el_full = volume_rays()
@@ -404,8 +407,8 @@ def run_ours(args):
     else:
         if n_full % world:
             raise SystemExit('the 7200-ray volume does not divide by {} ranks'.format(world))
-        lo, hi = parallel.shard_bounds(n_full, rank, world)
-        az, el = az_full[lo:hi], el_full[lo:hi]
+        mine = parallel.shard_indices(n_full, rank, world)
+        az, el = az_full[mine], el_full[mine]
         n_total = n_full
     scan = op.build_scan(az, el)
     sampler = ClockSampler(local)
@@ -428,8 +431,8 @@ def run_ours(args):
             az2, el2 = volume_rays(rank, world)
             n2 = n_full * world
         else:
-            lo, hi = parallel.shard_bounds(n_full, rank, world)
-            az2, el2 = az_full[lo:hi], el_full[lo:hi]
+            mine = parallel.shard_indices(n_full, rank, world)
+            az2, el2 = az_full[mine], el_full[mine]
             n2 = n_full
         scan2 = op.build_scan(az2, el2)
         ms2, _ = device_run(scan2, n2, k2, 3, False)
@@ -604,6 +607,8 @@ def main():
                     help='N > 1: strong = ONE 7200-ray volume sharded by ray (default); weak = one volume per GPU')
     ap.add_argument('--no-direct', action='store_true', help='skip the extra steps that time the direct integration kernel')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    ap.add_argument('--pipeline', default='fused', choices=['fused', 'staged'],
+                    help='fused: k_gate_fused (default where the configuration allows it); staged: k_interp_psd -> k_integrate_tab -> k_reduce_subbeams')
     ap.add_argument('--integration', default='table', choices=['table', 'direct'],
                     help='diameter integral through lambda-transformed tables (default) or by direct sums')
     args = ap.parse_args()

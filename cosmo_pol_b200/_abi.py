@@ -26,7 +26,7 @@ EXPORTS = ['radop_abi_version', 'radop_create', 'radop_destroy', 'radop_last_err
            'radop_get_stats', 'radop_enable_timing', 'radop_debug_indices', 'radop_measure_fp32_peak',
            'radop_get_all_radar_pts', 'radop_selftest_division', 'radop_set_chunk', 'radop_set_overlap_threshold',
            'radop_set_geodesy', 'radop_get_geodesy', 'radop_set_integration', 'radop_get_integration', 'radop_debug_integration',
-           'radop_set_search', 'radop_sizeof', 'radop_device_buffer', 'radop_get_refl']
+           'radop_set_search', 'radop_sizeof', 'radop_device_buffer', 'radop_get_refl', 'radop_set_pipeline', 'radop_get_pipeline', 'radop_set_tuning']
 
 BUF_OBS, BUF_LAT, BUF_LON, BUF_MODEL, BUF_DSPECTRUM = range(5)
 
@@ -133,6 +133,9 @@ def load_library():
     lib.radop_selftest_division.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.radop_get_all_radar_pts.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.radop_set_pipeline.argtypes = [C.c_void_p, C.c_int]
+    lib.radop_get_pipeline.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+    lib.radop_set_tuning.argtypes = [C.c_void_p, C.c_int, C.c_int64]
     lib.radop_sizeof.argtypes = [C.c_int]
     lib.radop_device_buffer.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
     lib.radop_get_refl.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 8
@@ -485,6 +488,20 @@ class Engine(object):
     def set_search(self, mode):
         """Level search of the interpolation: 0 guessed window with bisection as the fallback (default), 1 bisection."""
         self._check(self.lib.radop_set_search(self.h, C.c_int(int(mode))))
+
+    def set_pipeline(self, mode):
+        """'fused' / 0 (default): k_gate_fused whenever the configuration allows it; 'staged' / 1: the staged pipeline
+        (k_interp_psd -> k_integrate_tab / k_integrate -> k_reduce_subbeams) always."""
+        mode = {'fused': 0, 'staged': 1}.get(mode, mode)
+        self._check(self.lib.radop_set_pipeline(self.h, C.c_int(int(mode))))
+
+    def set_tuning(self, key, value):
+        self._check(self.lib.radop_set_tuning(self.h, C.c_int({'fused_warps': 0}.get(key, key)), C.c_int64(int(value))))
+
+    def used_fused(self):
+        v = C.c_int(0)
+        self._check(self.lib.radop_get_pipeline(self.h, C.byref(v)))
+        return bool(v.value)
 
     def set_integration(self, mode):
         """How the diameter integral (get_N x lookup_line, doppler_scatter.py:246-268) is evaluated.

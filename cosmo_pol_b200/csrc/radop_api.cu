@@ -97,6 +97,12 @@ struct RadopHandle_ {
     int k2_blocks = 0;
     size_t k2_smem = 0;
     int integration_mode = 0;    // 0: lambda-transformed tables (k_integrate_tab), 1: direct sums over the diameters (k_integrate)
+    int pipeline_mode = 0;       // 0: fused kernel when the configuration allows it, 1: staged pipeline always
+    int fused_warps = 0;         // warps per CTA of the fused kernel (0: chosen from the sub-beam count)
+    bool last_fused = false;
+    bool geo_ready = false;      // geo_poly holds the polynomials of the staged scan (whole ray list)
+    bool geo_poly_conv = false;  // ... and every series converged
+    DevBuf traj_sc, traj_ie, f_wsum, f_ice, f_cnt;
     DevBuf lt_stat;              // [0] u64 pairs integrated directly by k_integrate_tab, [1] (int) rejected pieces
     long long lt_pieces = 0, lt_rejected = 0, lt_fallback = 0, lt_why[4] = {0, 0, 0, 0};
     float lt_build_ms = 0.f;
@@ -184,7 +190,7 @@ int radop_destroy(RadopHandle *h)
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     cudaStreamSynchronize(h->copy_stream);
-    DevBuf *bufs[] = {&h->lt_stat, &h->lev_guess, &h->geo_poly, &h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
+    DevBuf *bufs[] = {&h->lt_stat, &h->traj_sc, &h->traj_ie, &h->f_wsum, &h->f_ice, &h->f_cnt, &h->lev_guess, &h->geo_poly, &h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
                       &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
                       &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
                       &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_st, &h->attw, &h->spec_acc, &h->spec_out, &h->d3_std, &h->sub_acc, &h->brd_flag, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
@@ -233,6 +239,7 @@ int radop_set_params(RadopHandle *h, const RadopParams *p)
     h->p = *p;
     h->have_params = true;
     h->executed = false;
+    h->geo_ready = false;
     return RADOP_OK;
 }
 
@@ -285,6 +292,7 @@ int radop_upload_grid(RadopHandle *h, int nz, int ny, int nx, const float *zleve
     h->var_mask = 0;
     h->have_grid = true;
     h->executed = false;
+    h->geo_ready = false;
     return RADOP_OK;
 }
 
@@ -506,6 +514,36 @@ int radop_stage_scan(RadopHandle *h, const RadopScan *sc)
     h->n_sbg = (long long)sc->n_rays * sc->n_sub * ng;
     h->have_scan = true;
     h->executed = false;
+    h->geo_ready = false;
+    return RADOP_OK;
+}
+
+static int prepare(RadopHandle *h);
+
+// Per sub-beam polynomials of the rotated-pole coordinates for the WHOLE staged ray list.  They depend on the
+// scan geometry, the radar position and the grid's pole only, so they are made once per staged scan (first
+// run after radop_stage_scan / radop_set_params / radop_upload_grid) and reused by every execute; the host
+// learns here whether every series converged (else the per-gate solution runs).
+static int ensure_geometry(RadopHandle *h)
+{
+    if (h->geo_ready) return RADOP_OK;
+    h->geo_poly_conv = false;
+    if (h->geodesy_mode == 0 && h->geo_poly_ok) {
+        const int n_rq = h->n_rays * h->n_sub;
+        CU(h, h->geo_poly.reserve((size_t)n_rq * sizeof(SubPoly)));
+        CU(h, h->flags.reserve(16));
+        CU(h, cudaMemsetAsync(h->flags.p, 0, 16, h->stream));
+        DevConfig c = h->cfg;
+        c.n_rays = h->n_rays;
+        k_sub_geopoly<<<(n_rq + 7) / 8, 128, 0, h->stream>>>(c, h->n_rays, h->scan, h->scan.ray_az, h->scan.sub_daz,
+                                                             h->geo_poly.as<SubPoly>(), h->flags.as<int>());
+        CU(h, cudaGetLastError());
+        int flag = 0;
+        CU(h, cudaMemcpyAsync(&flag, h->flags.p, 4, cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));
+        h->geo_poly_conv = !(flag & 4);
+    }
+    h->geo_ready = true;
     return RADOP_OK;
 }
 
@@ -660,6 +698,14 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     c.sum_species = (h->integration_mode == 0 && !c.with_melting && c.doppler_scheme != 3) ? 1 : 0;
     const int nsp = c.n_species, ng = c.n_gates;
     const int n_rays = h->n_rays;
+    rc = ensure_geometry(h);
+    if (rc) return rc;
+    const bool poly = h->geodesy_mode == 0 && h->geo_poly_ok && h->geo_poly_conv;
+    h->geo_poly_launched = poly;
+    bool fused = h->pipeline_mode == 0 && h->integration_mode == 0 && !c.with_melting && c.doppler_scheme != 3 &&
+                 !c.keep_debug && !c.output_model_vars && poly;
+    for (int s = 0; s < nsp; ++s) fused = fused && c.sp[s].ne <= 255 && c.sp[s].mode != MODE_MELT;
+    h->last_fused = fused;
     const size_t n_rg = (size_t)n_rays * ng;
     const bool want_vals = c.output_model_vars || c.keep_debug;
     // ---- chunking --------------------------------------------------------------------------
@@ -710,9 +756,17 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     const size_t c_rg = (size_t)rays_per_chunk * ng;
     if (n * nsp >= 0x7fffffffLL || n >= 0xfffffff0LL)
         return h->fail(RADOP_ERR_ARG, "chunk too large (rays x sub-beams x gates x species >= 2^31): lower the chunk size");
-    CU(h, h->geo.reserve((size_t)rays_per_chunk * c.n_sub * sizeof(SubGeo)));
-    if (h->geodesy_mode == 0 && h->geo_poly_ok) CU(h, h->geo_poly.reserve((size_t)rays_per_chunk * c.n_sub * sizeof(SubPoly)));
     c.geo_mid = h->geo_mid; c.geo_rhalf = 1.0 / h->geo_half;
+    const int n_spans = (ng + 31) / 32;
+    const long long traj_n = (long long)h->n_traj * h->n_vert * ng;
+    if (fused) {
+        CU(h, h->traj_sc.reserve((size_t)traj_n * 8));
+        CU(h, h->traj_ie.reserve((size_t)traj_n * nsp));
+        CU(h, h->f_wsum.reserve(c_rg * 4));
+        CU(h, h->f_cnt.reserve(RADOP_NSPECIES_MAX * 8));
+        if (c.ice_numeric >= 0 && c.doppler_scheme == 1) CU(h, h->f_ice.reserve((size_t)rays_per_chunk * c.n_sub * n_spans * 32));
+    } else {
+    if (!poly) CU(h, h->geo.reserve((size_t)rays_per_chunk * c.n_sub * sizeof(SubGeo)));
     CU(h, h->mask.reserve(n));
     CU(h, h->active.reserve(n));
     CU(h, h->wind.reserve(n * 4));
@@ -723,6 +777,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     CU(h, h->p0.reserve((size_t)n * nsp * 4));
     CU(h, h->p1.reserve((size_t)n * nsp * 4));
     if (want_vals) CU(h, h->vals.reserve((size_t)n * RADOP_NVP * 4));
+    }
     CU(h, h->lat.reserve(n_rg * 8));
     CU(h, h->lon.reserve(n_rg * 8));
     CU(h, h->hist.reserve((size_t)c.total_bins * 4));
@@ -732,10 +787,13 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     CU(h, h->cost_start.reserve((size_t)(c.total_bins + 1) * 8));
     CU(h, h->cursor.reserve((size_t)c.total_bins * 4));
     CU(h, h->totals.reserve((size_t)n_chunks * RADOP_TOTALS * 8));
-    CU(h, h->rec.reserve((size_t)n * nsp * sizeof(PairRec)));
-    CU(h, h->sz_out.reserve((size_t)n * nsp * 8 * 4));
-    CU(h, h->ice_vn.reserve((size_t)n * 8));
-    if (c.doppler_scheme == 2 || c.with_melting) CU(h, h->dop_vn.reserve((size_t)n * nsp * 8));
+    if (!fused) {
+        if (h->integration_mode != 0 || c.with_melting || c.doppler_scheme == 3) CU(h, h->rec.reserve((size_t)n * nsp * sizeof(PairRec)));
+        CU(h, h->sz_out.reserve((size_t)n * (c.sum_species ? 1 : nsp) * 8 * 4));
+        CU(h, h->ice_vn.reserve((size_t)n * 8));
+        if (c.doppler_scheme == 2 || c.with_melting) CU(h, h->dop_vn.reserve((size_t)n * nsp * 8));
+        CU(h, h->ice_tot.reserve((size_t)rays_per_chunk * c.n_sub * 3 * 4));
+    }
     if (c.doppler_scheme == 3) {
         CU(h, h->d3_uh.reserve((size_t)n * 8));
         CU(h, h->d3_w.reserve((size_t)n * 4));
@@ -750,7 +808,6 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             CU(h, h->brd_flag.reserve((size_t)rays_per_chunk * c.n_sub));
         }
     }
-    CU(h, h->ice_tot.reserve((size_t)rays_per_chunk * c.n_sub * 3 * 4));
     CU(h, h->comb.reserve(c_rg * 8 * 4));
     CU(h, h->out.reserve(n_rg * (RADOP_N_OUT + 1) * 4));
     if (c.output_model_vars) CU(h, h->model_out.reserve(n_rg * RADOP_NVP * 4));
@@ -765,6 +822,8 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     static bool attr_done[64] = {false};
     if (!attr_done[h->device & 63]) {
         CU(h, cudaFuncSetAttribute(k_integrate, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(h, cudaFuncSetAttribute(k_gate_fused<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
+        CU(h, cudaFuncSetAttribute(k_gate_fused<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
         CU(h, cudaFuncSetAttribute(k_interp_psd<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_interp_psd<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_scatter_pairs, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -847,27 +906,94 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             o.dbg_cell = h->dbg_cell.as<int>(); o.dbg_level = h->dbg_level.as<int>(); o.dbg_status = h->dbg_status.as<int>();
             o.dbg_e = h->dbg_e.as<int>(); o.dbg_t = h->dbg_t.as<int>(); o.dbg_rot = h->dbg_rot.as<double>();
         }
+        if (fused) {
+            // ---- fused pipeline: one kernel from the ray list to the per ray-gate sums -------------------
+            FusedArgs fa;
+            memset(&fa, 0, sizeof fa);
+            fa.poly = h->geo_poly.as<SubPoly>() + (size_t)r0 * c.n_sub;
+            fa.traj_sc = h->traj_sc.as<float2>(); fa.traj_ie = h->traj_ie.as<uint8_t>(); fa.traj_n = traj_n;
+            fa.comb = h->comb.as<float>(); fa.wsum = h->f_wsum.as<float>();
+            fa.mask_out = h->out.as<float>() + (size_t)RADOP_N_OUT * n_rg + off_rg;
+            fa.lat = o.lat; fa.lon = o.lon;
+            const bool ice = c.ice_numeric >= 0 && c.doppler_scheme == 1;
+            fa.ice_part = ice ? h->f_ice.as<float4>() : nullptr;
+            fa.flags = h->flags.as<int>();
+            fa.n_fallback = h->lt_stat.as<unsigned long long>();
+            fa.n_pairs = h->f_cnt.as<unsigned long long>();
+            fa.n_spans = n_spans;
+            const double log2e = 1.4426950408889634;
+            for (int s = 0; s < nsp; ++s) {
+                const SpeciesDev &d = c.sp[s];
+                FusedSpecies &f = fa.fs[s];
+                f.u0 = d.c_l0 * log2e; f.uk = d.c_inv;
+                f.na = log2e * (8.939515416590824 + 0.107 * 273.15); f.nb = -0.107 * log2e;
+                f.n0 = (float)d.N0;
+                f.cv = (float)d.c_v; f.cn = (float)d.c_n; f.ev = (float)d.e_v; f.en = (float)d.e_n;
+            }
+            if (ch == 0) {
+                CU(h, cudaMemsetAsync(h->f_cnt.p, 0, RADOP_NSPECIES_MAX * 8, st));
+                k_traj_tables<<<(unsigned)((traj_n + 255) / 256), 256, 0, st>>>(c, h->scan.traj_e, traj_n, h->traj_sc.as<float2>(),
+                                                                               h->traj_ie.as<uint8_t>());
+                CU(h, cudaGetLastError()); ++launches;
+            }
+            // warps per CTA = sub-beams of a ray (at most 12), else the count between 6 and 12 that leaves the fewest idle
+            int W = h->fused_warps > 0 ? std::min(std::min(h->fused_warps, c.n_sub), FUSED_MAX_WARPS) : 0;
+            if (W == 0) {
+                // the warp count (at most 10) that leaves the fewest warps idle in the last round over the sub-beams
+                // (9 sub-beams: 3 warps x 3 rounds; 841: 10 x 85 with 9 idle slots ...), the larger CTA winning ties
+                int waste = 1 << 30;
+                for (int w = 3; w <= std::min(c.n_sub, FUSED_MAX_WARPS); ++w) {
+                    const int ws = (c.n_sub + w - 1) / w * w - c.n_sub;
+                    if (ws * 64 / c.n_sub <= waste) { waste = ws * 64 / c.n_sub; W = w; }
+                }
+                if (W == 0) W = std::max(1, std::min(c.n_sub, FUSED_MAX_WARPS));
+                if (c.n_sub == 9) W = 3;
+            }
+            const size_t smemf = (size_t)W * FUSED_NPART * 32 * 4;
+            int occf = 1;
+            if (c.two_moment) CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, k_gate_fused<true>, 32 * W, smemf));
+            else CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, k_gate_fused<false>, 32 * W, smemf));
+            const long long pieces = (long long)nr * n_spans;
+            const unsigned gridf = (unsigned)std::min<long long>(pieces, (long long)std::max(1, occf) * h->n_sm);
+            if (c.two_moment) k_gate_fused<true><<<gridf, 32 * W, smemf, st>>>(c, scan, h->z_t.as<float>(), h->fields.as<float>(), fa);
+            else k_gate_fused<false><<<gridf, 32 * W, smemf, st>>>(c, scan, h->z_t.as<float>(), h->fields.as<float>(), fa);
+            CU(h, cudaGetLastError()); ++launches;
+            if (ev) { CU(h, cudaEventRecord(ev[1], st)); CU(h, cudaEventRecord(ev[2], st)); CU(h, cudaEventRecord(ev[3], st)); }
+            if (ice) {
+                k_ice_fixup<<<(nr + 127) / 128, 128, 0, st>>>(c, h->f_ice.as<float4>(), n_spans, h->comb.as<float>(), h->f_wsum.as<float>());
+                CU(h, cudaGetLastError()); ++launches;
+            }
+            K3Args a3;
+            memset(&a3, 0, sizeof a3);
+            a3.sub_weight = scan.sub_weight; a3.ray_nyquist = nyq;
+            a3.comb = h->comb.as<float>(); a3.wsum = h->f_wsum.as<float>(); a3.out = h->out.as<float>() + off_rg;
+            k_ray_epilogue<<<(nr * 32 + 127) / 128, 128, 0, st>>>(c, a3);
+            CU(h, cudaGetLastError()); ++launches;
+            if (ev) { CU(h, cudaEventRecord(ev[4], st)); CU(h, cudaEventRecord(ev[5], st)); }
+            if (out) {
+                CU(h, cudaEventRecord(h->chunk_done[ch], st));
+                CU(h, cudaStreamWaitEvent(h->copy_stream, h->chunk_done[ch], 0));
+                rc = copy_outputs(h, out, r0, nr, h->copy_stream);
+                if (rc) return rc;
+            }
+            continue;
+        }
         {
             const int n_rq = nr * c.n_sub;
             const long long want = (nc + 127) / 128;
             const unsigned grid1 = (unsigned)std::min<long long>(want, (long long)std::max(1, occ1) * h->n_sm);
             const float *zt = h->z_t.as<float>(), *fl = h->fields.as<float>();
-            const bool poly = h->geodesy_mode == 0 && h->geo_poly_ok;
-            h->geo_poly_launched = poly;
-            k_sub_geometry<<<(n_rq + 127) / 128, 128, 0, st>>>(nr, c.n_sub, c.radar_lat, scan.ray_az, scan.sub_daz, h->geo.as<SubGeo>());
-            CU(h, cudaGetLastError()); ++launches;
             if (poly) {
-                // per sub-beam polynomials of the rotated-pole coordinates; a sub-beam whose series does not
-                // converge raises flag bit 2 and the per-gate instance does the work instead (both are launched,
-                // the one that is not wanted returns at once)
-                k_sub_geopoly<<<(n_rq + 7) / 8, 128, 0, st>>>(c, nr, scan, scan.ray_az, scan.sub_daz,
-                                                               h->geo_poly.as<SubPoly>(), h->flags.as<int>());
+                // per sub-beam polynomials of the rotated-pole coordinates, made once per staged scan (ensure_geometry)
+                k_interp_psd<true><<<grid1, 128, hist_smem, st>>>(c, scan, (const void *)(h->geo_poly.as<SubPoly>() + (size_t)r0 * c.n_sub),
+                                                                  zt, fl, o, nc, 0);
                 CU(h, cudaGetLastError()); ++launches;
-                k_interp_psd<true><<<grid1, 128, hist_smem, st>>>(c, scan, h->geo_poly.p, zt, fl, o, nc, 1);
+            } else {
+                k_sub_geometry<<<(n_rq + 127) / 128, 128, 0, st>>>(nr, c.n_sub, c.radar_lat, scan.ray_az, scan.sub_daz, h->geo.as<SubGeo>());
+                CU(h, cudaGetLastError()); ++launches;
+                k_interp_psd<false><<<grid1, 128, hist_smem, st>>>(c, scan, h->geo.p, zt, fl, o, nc, 0);
                 CU(h, cudaGetLastError()); ++launches;
             }
-            k_interp_psd<false><<<grid1, 128, hist_smem, st>>>(c, scan, h->geo.p, zt, fl, o, nc, poly ? 1 : 0);
-            CU(h, cudaGetLastError()); ++launches;
         }
         if (ev) CU(h, cudaEventRecord(ev[1], st));
 
@@ -922,7 +1048,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         a3.sz_out = h->sz_out.as<float>(); a3.ice_tot = h->ice_tot.as<float>(); a3.dop_vn = h->dop_vn.as<float2>();
         a3.vals = want_vals ? h->vals.as<float>() : nullptr;
         a3.sub_weight = scan.sub_weight; a3.ray_nyquist = nyq;
-        a3.comb = h->comb.as<float>(); a3.out = h->out.as<float>() + off_rg;
+        a3.comb = h->comb.as<float>(); a3.wsum = nullptr; a3.out = h->out.as<float>() + off_rg;
         a3.model_out = c.output_model_vars ? h->model_out.as<float>() + off_rg : nullptr;
         k_reduce_subbeams<<<(unsigned)((cc_rg + 127) / 128), 128, 0, st>>>(c, a3);
         CU(h, cudaGetLastError()); ++launches;
@@ -1021,7 +1147,15 @@ static int finish(RadopHandle *h)
     CU(h, cudaMemcpy(flags, h->flags.p, sizeof flags, cudaMemcpyDeviceToHost));
     h->stats.n_active_pairs = h->stats.n_tiles = h->stats.n_lut_bins = 0;
     for (int s = 0; s < RADOP_NSPECIES_MAX; ++s) h->stats.pairs_by_species[s] = 0;
-    for (int ch = 0; ch < std::max(1, h->n_chunks); ++ch) {
+    if (h->last_fused) {
+        unsigned long long cnt[RADOP_NSPECIES_MAX];
+        CU(h, cudaMemcpy(cnt, h->f_cnt.p, sizeof cnt, cudaMemcpyDeviceToHost));
+        for (int s = 0; s < RADOP_NSPECIES_MAX; ++s) {
+            h->stats.pairs_by_species[s] = (long long)cnt[s];
+            h->stats.n_active_pairs += (long long)cnt[s];
+        }
+    }
+    for (int ch = 0; !h->last_fused && ch < std::max(1, h->n_chunks); ++ch) {
         const long long *t = tot.data() + (size_t)RADOP_TOTALS * ch;
         h->stats.n_active_pairs += t[0];
         h->stats.n_tiles += t[1];
@@ -1112,6 +1246,33 @@ int radop_set_search(RadopHandle *h, int mode)
     if (!h || (mode != 0 && mode != 1)) return RADOP_ERR_ARG;
     h->search_mode = mode;
     h->executed = false;
+    return RADOP_OK;
+}
+
+int radop_set_pipeline(RadopHandle *h, int mode)
+{
+    if (!h || (mode != 0 && mode != 1)) return RADOP_ERR_ARG;
+    h->pipeline_mode = mode;
+    h->executed = false;
+    return RADOP_OK;
+}
+
+int radop_set_tuning(RadopHandle *h, int key, int64_t value)
+{
+    if (!h) return RADOP_ERR_ARG;
+    switch (key) {
+    case RADOP_TUNE_FUSED_WARPS:
+        if (value < 0 || value > FUSED_MAX_WARPS) return h->fail(RADOP_ERR_ARG, "fused warps per CTA: 0 (automatic) ... 10");
+        h->fused_warps = (int)value;
+        return RADOP_OK;
+    }
+    return h->fail(RADOP_ERR_ARG, "unknown tuning key");
+}
+
+int radop_get_pipeline(RadopHandle *h, int *used_fused)
+{
+    if (!h || !used_fused) return RADOP_ERR_ARG;
+    *used_fused = h->last_fused ? 1 : 0;
     return RADOP_OK;
 }
 

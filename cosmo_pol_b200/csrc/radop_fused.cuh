@@ -1,0 +1,513 @@
+// radop_fused.cuh -- K1f k_gate_fused: the whole per-gate hot path of the default configuration in ONE kernel.
+//
+// Included by radop_kernels.cu after the interpolation helpers (locate_cell, div_const, lut_bin) and the
+// lambda-table helpers (lt_horner, lt_scale, warp_direct).
+//
+// What it fuses (reference files as in the kernel file header): geolocation from the per sub-beam polynomials,
+// the bit-exact trilinear interpolation of interpolation_c.c:42-103, the PSD parameters of every species
+// (hydrometeors.py:224-255, 761-772, 894-907, 1039-1049, 1320-1373), the floor bins of lookup_line (lut.py:336-342),
+// the PSD x scattering-table contraction through the lambda-transformed tables (doppler_scatter.py:246-268),
+// the sum over the species (:148-158, 400-401), the analytic / rcs-weighted fall-speed moments and the wind
+// projection (:276-333), and the quadrature sum over the sub-beams of a ray (:259-268, 313-333, 472-477).
+// The older pipeline -- k_interp_psd, k_integrate_tab, k_reduce_subbeams -- wrote keys, slopes, intercepts and one
+// 32-byte row of sums per sub-beam gate to HBM and read them back twice (~3 GB per volume); here nothing per
+// sub-beam gate leaves the SM.  Melting species, Doppler spectra, the direct integration, model-variable outputs
+// and the debug index dump keep the older pipeline (they need the per sub-beam-gate arrays).
+//
+// Mapping: a work piece is (ray, span of 32 consecutive gates); lanes = gates.  The CTA has W warps; warp w
+// takes the sub-beams q = w, w + W, ... of the piece (W = number of sub-beams when there are at most 12), so the
+// sub-beams of one gate span run side by side on one SM and find each other's model cells in L1.  Every warp
+// adds its sub-beams' sums into a shared-memory row; warp 0 adds the rows in warp order (a fixed order: results
+// do not depend on scheduling, chunking or sharding) and writes one 36-byte record per ray gate.
+// Pieces are handed out from a global counter, so CTAs that start late (an NCCL kernel on their SM) take fewer.
+#pragma once
+
+#define FUSED_MAX_WARPS 10
+#define FUSED_NPART 10        // b c p q kd s9 s11 | sum rv w | sum w | sum mask
+
+// constants of one species in the form the fused kernel wants them (filled by the host, prepare_fused())
+struct FusedSpecies {
+    double u0, uk;            // u = log2(lambda) = uk * (u0 [+ log2 N0(T)] - log2 QM)   (one-moment families)
+    double na, nb;            // snow: log2 N0 = na + nb * T
+    float n0;                 // fixed intercept
+    float cv, cn;             // analytic moments: v = cv n0 2^(ev u), n = cn n0 2^(en u)
+    float ev, en;
+};
+
+struct FusedArgs {
+    const SubPoly *poly;            // [ray][sub] of the rays of this launch
+    const float2 *traj_sc;          // [trajectory row][gate] (sin, cos) of the folded incidence elevation
+    const uint8_t *traj_ie;         // [species][trajectory row][gate] elevation bin of the species' table
+    long long traj_n;               // trajectory rows x gates
+    float *comb;                    // [ray][gate][8]: b c p q kd s9 s11 | sum of rv * w
+    float *wsum;                    // [ray][gate] sum of the weights behind comb[7]
+    float *mask_out;                // [ray][gate] averaged mask
+    double *lat, *lon;              // [ray][gate] central sub-beam, or null
+    float4 *ice_part;               // [ray][sub][span][2] partial numeric fall-speed moments, or null
+    int *flags;                     // [0] bit 0: a gate left the model domain; [3] work counter
+    unsigned long long *n_fallback; // [4] pairs summed directly, by reason
+    unsigned long long *n_pairs;    // [RADOP_NSPECIES_MAX] active pairs per species
+    int n_spans;                    // ceil(n_gates / 32)
+    FusedSpecies fs[RADOP_NSPECIES_MAX];
+};
+
+// (sin, cos) of the folded elevation and the elevation bins of every species' table for every trajectory row:
+// they depend on the scan geometry only (doppler_scatter.py:173-176; lut.py:336-341).
+__global__ void k_traj_tables(const __grid_constant__ DevConfig cfg, const float *__restrict__ traj_e, long long n,
+                              float2 *__restrict__ sc, uint8_t *__restrict__ ie)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float e = __ldg(traj_e + i);
+    if (e > 90.f) e = __fsub_rn(180.f, e);
+    if (e < 0.f) e = -e;
+    float st, ct;
+    sincosf(e * 0.017453292519943295f, &st, &ct);
+    sc[i] = make_float2(st, ct);
+    for (int s = 0; s < cfg.n_species; ++s) {
+        const SpeciesDev &S = cfg.sp[s];
+        ie[(size_t)s * n + i] = (uint8_t)lut_bin(e, S.e_min, S.e_step, S.e_rstep, S.ne);
+    }
+}
+
+// the interpolation of interp_columns for the variables the radar observables need (RHO and EDR are read by
+// the Doppler spectrum and the model outputs only)
+template <bool EXACT, bool TWO_MOM>
+__device__ __forceinline__ bool interp_fused(const DevConfig &cfg, const CellGeom &c, float h_g,
+                                             const float *__restrict__ z_t, const float *__restrict__ fields,
+                                             float (&val)[TWO_MOM ? 15 : 9])
+{
+    constexpr int NV = TWO_MOM ? 15 : 9;
+    bool rare = false;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) val[j] = -0.f;
+#pragma unroll 1
+    for (int oi = 0; oi < 4; ++oi) {
+        const int k = (oi == 1) ? 2 : (oi == 2 ? 1 : oi);        // accumulation order of the reference: 0, 2, 1, 3
+        const int yk = (k & 2) ? c.y1 : c.y0, xk = (k & 1) ? c.x1 : c.x0;
+        const int lvl = (k == 0) ? c.level[0] : (k == 1 ? c.level[1] : (k == 2 ? c.level[2] : c.level[3]));
+        const size_t cell = ((size_t)yk * cfg.nx + xk) * cfg.nz + lvl;
+        const float c1 = __ldg(z_t + cell), c2 = __ldg(z_t + cell + 1);
+        const float den = __fsub_rn(c1, c2), dh = __fsub_rn(h_g, c2);
+        const float rden = EXACT ? 0.f : __frcp_rn(den);
+        if (!EXACT) rare = rare || !div_den_safe(den);
+        const float4 *f1 = reinterpret_cast<const float4 *>(fields + cell * RADOP_NVP);
+        const float4 *f2 = f1 + RADOP_NVP / 4;
+        const bool v_mid = (k == 1) || (k == 2);
+        const float w0 = (k == 0) ? __fmul_rn(c.dx, c.dy) : (k == 2 ? c.x : (k == 1 ? c.dx : __fmul_rn(c.x, c.y)));
+        const float w1 = (k == 2) ? c.dy : c.y;
+        auto accum = [&](int j, float a, float b) {
+            const float n = __fsub_rn(b, a);
+            float q;
+            if (EXACT) q = __fdiv_rn(n, den);
+            else {
+                const float q0 = __fmul_rn(n, rden);
+                const float r = __fmaf_rn(-den, q0, n);
+                q = __fmaf_rn(r, rden, q0);
+                const float aq = fabsf(q);
+                rare = rare || !(aq <= 1e30f) || (aq < 1e-30f && n != 0.f);
+            }
+            const float vv = __fsub_rn(b, __fmul_rn(q, dh));
+            const float t0 = __fmul_rn(w0, vv);
+            val[j] = __fadd_rn(val[j], v_mid ? __fmul_rn(t0, w1) : t0);
+        };
+        {
+            const float4 a = __ldg(f1), b = __ldg(f2);
+            accum(0, a.x, b.x); accum(1, a.y, b.y); accum(2, a.z, b.z); accum(3, a.w, b.w);
+        }
+        {
+            const float4 a = __ldg(f1 + 1), b = __ldg(f2 + 1);       // RHO (slot 4) is not needed
+            accum(5, a.y, b.y); accum(6, a.z, b.z); accum(7, a.w, b.w);
+        }
+        if (TWO_MOM) {
+            const float4 a = __ldg(f1 + 2), b = __ldg(f2 + 2), a3 = __ldg(f1 + 3), b3 = __ldg(f2 + 3);
+            accum(8, a.x, b.x); accum(9, a.y, b.y); accum(10, a.z, b.z); accum(11, a.w, b.w);
+            accum(12, a3.x, b3.x); accum(13, a3.y, b3.y); accum(14, a3.z, b3.z);
+        } else {
+            accum(8, __ldg(reinterpret_cast<const float *>(f1) + 8), __ldg(reinterpret_cast<const float *>(f2) + 8));
+        }
+    }
+    return rare;
+}
+
+template <int NV>
+__device__ __forceinline__ float pick_var(const float (&v)[NV], int var)
+{   // register-resident select (a dynamic index would push the array to local memory)
+    float r = v[RADOP_VAR_QR];
+    if (var == RADOP_VAR_QS) r = v[RADOP_VAR_QS];
+    if (var == RADOP_VAR_QG) r = v[RADOP_VAR_QG];
+    if (var == RADOP_VAR_QI) r = v[RADOP_VAR_QI];
+    if (NV > 9) {
+        if (var == RADOP_VAR_QH) r = v[NV > 9 ? RADOP_VAR_QH : 0];
+        if (var == RADOP_VAR_QNR) r = v[NV > 9 ? RADOP_VAR_QNR : 0];
+        if (var == RADOP_VAR_QNS) r = v[NV > 9 ? RADOP_VAR_QNS : 0];
+        if (var == RADOP_VAR_QNG) r = v[NV > 9 ? RADOP_VAR_QNG : 0];
+        if (var == RADOP_VAR_QNI) r = v[NV > 9 ? RADOP_VAR_QNI : 0];
+        if (var == RADOP_VAR_QNH) r = v[NV > 9 ? RADOP_VAR_QNH : 0];
+    }
+    return r;
+}
+
+// One species of one warp's 32 gates, from the PSD slope in the log domain (u = log2 lambda) to the seven
+// weighted column sums: the arithmetic of pair_tab without the trip through global memory.  vn: numeric
+// fall-speed moments (ice, Doppler scheme 1) or the rcs-weighted ones of scheme 2.  All 32 lanes must call.
+template <int NC>
+__device__ __forceinline__ void species_tab(const DevConfig &cfg, const FusedArgs &A, const SpeciesDev &S, bool have,
+                                            int bl, double u, float p1, float w, int lane, float (&acc)[7], float2 &vn)
+{
+    constexpr int STR = (12 * NC + ((NC + 1 + 3) & ~3) + 31) / 32 * 32;      // lt_stride(NC)
+    const int nd = S.nd;
+    float m[NC];
+    int ex[NC];
+    int piece = 0, why = 0;
+    float x = 0.f;
+    if (have) {
+        // piece and position inside it straight from u (what lt_locate derives from the float32 slope)
+        const double t = (u - (double)LT_U0) * (double)LT_PPO;
+        if (!(fabs(t) < 1e9)) why = 4;
+        else if (t < 0.0) why = 2;
+        else if (t >= (double)LT_NP) why = 3;
+        else {
+            piece = (int)t;
+            x = (float)(2.0 * (t - (double)piece) - 1.0);
+        }
+    }
+    const int id = (have && !why) ? bl * LT_NP + piece : -1;
+    lt_horner<NC>(S.lamtab + (size_t)(id >= 0 ? id : bl * LT_NP) * STR, x, m, ex);
+    if (id >= 0 && ex[0] == LT_BAD) why = 1;
+    unsigned need = __ballot_sync(0xffffffffu, why != 0);
+    if (why) atomicAdd(A.n_fallback + (why - 1), 1ull);
+    const float lam = need ? exp2f((float)u) : 0.f;
+    while (need) {
+        const int src = __ffs(need) - 1;
+        need &= need - 1;
+        const int bl_s = __shfl_sync(0xffffffffu, bl, src);
+        const float lam_s = __shfl_sync(0xffffffffu, lam, src);
+        float ds[NC];
+        warp_direct<NC>(S, bl_s, lam_s, lane, ds);
+        if (lane == src) {
+#pragma unroll
+            for (int c = 0; c < NC; ++c) { m[c] = ds[c]; ex[c] = 0; }
+        }
+    }
+    if (!have) return;
+    if (S.mode == MODE_ICE1) {
+        // N0 renormalised so that the mass integral equals QM (hydrometeors.py:1330-1339): n0 = p1 / F_9
+        constexpr int C9 = NC > 9 ? 9 : 0, C8 = NC > 8 ? 8 : 0, C7 = NC > 7 ? 7 : 0;
+        const float inv9 = 1.f / m[C9];
+        const int e9 = ex[C9];
+#pragma unroll
+        for (int c = 0; c < 7; ++c) acc[c] += lt_scale(m[c] * inv9 * p1 * w, ex[c] - e9);
+        if (cfg.doppler_scheme == 2) {
+            const float lam1 = exp2f((float)u);
+            const float *tab = S.table + (size_t)bl * nd * S.ncol;
+            const float D0 = __ldg(S.aux), DL = __ldg(S.aux + nd - 1);
+            const float c2 = 17.46f * exp2f(0.6357f * log2f(lam1));
+            const float w0 = 490.6f * ex2f_approx(-20.78f * LOG2E * lam1 * D0) +
+                             c2 * __ldg(S.aux + 2 * nd) * ex2f_approx(-3.290f * LOG2E * lam1 * D0);
+            const float wL = 490.6f * ex2f_approx(-20.78f * LOG2E * lam1 * DL) +
+                             c2 * __ldg(S.aux + 3 * nd - 1) * ex2f_approx(-3.290f * LOG2E * lam1 * DL);
+            const float f0 = lt_scale(m[0], ex[0]), f7 = lt_scale(m[C7], ex[C7]);
+            const float n0 = p1 / lt_scale(m[C9], e9);
+            const float n_ = f0 - 0.5f * (__ldg(tab) * w0 + __ldg(tab + (size_t)(nd - 1) * S.ncol) * wL);
+            const float v_ = f7 - 0.5f * (__ldg(tab + 7) * w0 + __ldg(tab + (size_t)(nd - 1) * S.ncol + 7) * wL);
+            const float sc = 6.283185307179586f * n0 / S.dD_ref;
+            vn = make_float2(v_ * sc, n_ * sc);
+        } else {
+            vn = make_float2(lt_scale(m[C7] * inv9 * p1, ex[C7] - e9), lt_scale(m[C8] * inv9 * p1, ex[C8] - e9));
+        }
+        return;
+    }
+    const float pre = p1 * w;
+#pragma unroll
+    for (int c = 0; c < 7; ++c) acc[c] += lt_scale(m[c] * pre, ex[c]);
+    if (S.mode == MODE_GEN12) {
+        constexpr int C8 = NC > 8 ? 8 : 0, C7 = NC > 7 ? 7 : 0;
+        vn = make_float2(lt_scale(m[C7] * p1, ex[C7]), lt_scale(m[C8] * p1, ex[C8]));
+    } else if (NC == 8) {
+        // trapezoid end corrections of Doppler scheme 2 (doppler2_moments)
+        constexpr int C7 = NC > 7 ? 7 : 0;
+        const float *tab = S.table + (size_t)bl * nd * S.ncol;
+        const float a = -LOG2E * exp2f((float)u);
+        float yF, yL;
+        if (S.mode == MODE_GEO8) { yF = __ldg(S.aux); yL = (float)((double)yF + (double)(nd - 1) * S.dD_d); }
+        else { yF = __ldg(S.aux + nd); yL = __ldg(S.aux + 2 * nd - 1); }
+        const float wF = ex2f_approx(a * yF), wL = ex2f_approx(a * yL);
+        const float f0 = lt_scale(m[0], ex[0]), f7 = lt_scale(m[C7], ex[C7]);
+        const float n_ = f0 - 0.5f * (__ldg(tab) * wF + __ldg(tab + (size_t)(nd - 1) * S.ncol) * wL);
+        const float v_ = f7 - 0.5f * (__ldg(tab + 7) * wF + __ldg(tab + (size_t)(nd - 1) * S.ncol + 7) * wL);
+        const float sc = 6.283185307179586f * p1 / S.dD_ref;
+        vn = make_float2(v_ * sc, n_ * sc);
+    }
+}
+
+// log2 of a positive float32 as a float64: exponent + log2 of the mantissa (MUFU.LG2 on [1, 2): absolute error 2^-22)
+__device__ __forceinline__ double log2_split(float x)
+{
+    int bits = __float_as_int(x);
+    int e = (bits >> 23) - 127;
+    if (e == -127) {                       // subnormal: renormalise
+        x *= 16777216.f;
+        bits = __float_as_int(x);
+        e = (bits >> 23) - 127 - 24;
+    }
+    const float mant = __int_as_float((bits & 0x007fffff) | 0x3f800000);
+    return (double)e + (double)__log2f(mant);
+}
+
+// 2^t for a float64 t with the integer part applied exactly
+__device__ __forceinline__ float exp2_split(double t)
+{
+    const double ip = rint(t);
+    return lt_scale(ex2f_approx((float)(t - ip)), (int)fmax(-300.0, fmin(300.0, ip)));
+}
+
+template <bool TWO_MOM>
+__global__ void __launch_bounds__(32 * FUSED_MAX_WARPS, 3)
+k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const float *__restrict__ z_t,
+             const float *__restrict__ fields, const __grid_constant__ FusedArgs A)
+{
+    constexpr int NV = TWO_MOM ? 15 : 9;
+    extern __shared__ float s_part_raw[];                  // [W][FUSED_NPART][32]
+    float (*s_part)[FUSED_NPART][32] = reinterpret_cast<float (*)[FUSED_NPART][32]>(s_part_raw);
+    __shared__ int s_piece;
+    __shared__ unsigned s_pairs[RADOP_NSPECIES_MAX];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, W = blockDim.x >> 5;
+    const int ng = cfg.n_gates, n_sub = cfg.n_sub, n_spans = A.n_spans;
+    const int n_pieces = cfg.n_rays * n_spans;
+    const float qnan = __int_as_float(0x7fc00000);
+    if (threadIdx.x < RADOP_NSPECIES_MAX) s_pairs[threadIdx.x] = 0u;
+
+    for (;;) {
+        if (threadIdx.x == 0) s_piece = atomicAdd(A.flags + 3, 1);
+        __syncthreads();
+        const int piece = s_piece;
+        if (piece >= n_pieces) break;
+        const int ray = piece / n_spans, span = piece - ray * n_spans;
+        const int g = span * 32 + lane;
+        const bool in_range = g < ng;
+
+#pragma unroll 1
+        for (int q = warp; q < n_sub; q += W) {
+            const int rq = ray * n_sub + q;
+            const size_t trow = ((size_t)__ldg(scan.ray_traj + ray) * cfg.n_vert + __ldg(scan.sub_jv + q)) * ng + (in_range ? g : 0);
+            const float wq = (float)__ldg(scan.sub_weight + q);
+            const double2 *cp = reinterpret_cast<const double2 *>(A.poly + rq);
+            const double2 az = __ldg(cp);                        // sin, cos of the sub-beam azimuth
+            float h_g = 0.f, pos0 = 0.f, pos1 = 0.f;
+            CellGeom c;
+            c.status = 1;
+            if (in_range) {
+                const float s_g = __ldg(scan.traj_s + trow);
+                h_g = __ldg(scan.traj_h + trow);
+                // --- geolocation: rotated-pole coordinates from the sub-beam's polynomials ---------------
+                const double2 iv = __ldg(cp + 1);
+                const double x = ((double)s_g - iv.x) * iv.y;
+                const double rlat = poly_eval(cp + 2, x), rlon = poly_eval(cp + 2 + GEO_NC / 2, x);
+                if (q == cfg.center_sub && A.lat) {
+                    A.lat[(size_t)ray * ng + g] = poly_eval(cp + 2 + GEO_NC, x);
+                    A.lon[(size_t)ray * ng + g] = poly_eval(cp + 2 + 3 * GEO_NC / 2, x);
+                }
+                // domain check on float64 coordinates against float32 corners (interpolation.py:572-575)
+                if (rlon < (double)cfg.llc[0] || rlat < (double)cfg.llc[1] || rlon > (double)cfg.urc[0] ||
+                    rlat > (double)cfg.urc[1])
+                    atomicOr(A.flags, 1);
+                // SWIG typemap casts the coordinates to float32 (interpolation_c.i:16)
+                pos0 = div_const(__fsub_rn((float)rlat, cfg.llc[1]), cfg.res[1], cfg.rres[1]);
+                pos1 = div_const(__fsub_rn((float)rlon, cfg.llc[0]), cfg.res[0], cfg.rres[0]);
+                locate_cell(z_t, cfg.nz, cfg.ny, cfg.nx, pos0, pos1, h_g, cfg.z_strict != 0, c, cfg.lev_guess);
+            }
+            const float mask_q = in_range ? (float)c.status : 0.f;
+            const bool live = in_range && c.status == 0;
+            float val[NV];
+            if (live) {
+                if (interp_fused<false, TWO_MOM>(cfg, c, h_g, z_t, fields, val))
+                    interp_fused<true, TWO_MOM>(cfg, c, h_g, z_t, fields, val);
+            } else {
+#pragma unroll
+                for (int j = 0; j < NV; ++j) val[j] = 0.f;
+            }
+            const float T = val[RADOP_VAR_T];
+            // --- wind along the sub-beam (proj_vel, doppler_scatter.py:30-47; theta is the folded elevation) ---
+            float wind = qnan, sinth = 0.f;
+            if (live) {
+                const float2 sc = __ldg(A.traj_sc + trow);
+                wind = (float)(((double)val[RADOP_VAR_U] * az.x + (double)val[RADOP_VAR_V] * az.y) * (double)sc.y +
+                               (double)val[RADOP_VAR_W] * (double)sc.x);
+                sinth = sc.x;
+            }
+            // --- species: PSD slope in the log domain, table bin, table evaluation, sums over the species ---
+            float acc[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            float vs = 0.f, ns = 0.f;
+            bool ice_here = false;
+            float2 ice_vn = make_float2(0.f, 0.f);
+#pragma unroll 1
+            for (int s = 0; s < cfg.n_species; ++s) {
+                const SpeciesDev &S = cfg.sp[s];
+                const FusedSpecies &F = A.fs[s];
+                const float QMf = pick_var<NV>(val, S.qm_var);
+                const bool have = live && QMf > 0.f;
+                const unsigned who = __ballot_sync(0xffffffffu, have);
+                if (!who) continue;
+                if (lane == 0) atomicAdd(&s_pairs[s], (unsigned)__popc(who));
+                double u = 0.0;
+                float p1 = 0.f, n0 = 0.f;
+                int bl = 0;
+                if (have) {
+                    if (S.psd == RADOP_PSD_2MOM) {
+                        // _Hydrometeor.set_psd, hydrometeors.py:224-255 (float64 as in k_interp_psd: N0 spans 20 orders
+                        // of magnitude and the two-moment KDP has gates where species cancel to 1e-3 of their size)
+                        const double QN = (double)pick_var<NV>(val, S.qn_var);
+                        const double xm = fmin(fmax((double)QMf / (QN + 2.220446049250313e-16), S.x_min), S.x_max);
+                        const double ll0 = S.c_inv * log(S.lambda_factor * xm);
+                        const double logn0 = log(fabs(S.c_q * QN)) + S.e_q * ll0 - S.c_ka;
+                        const double dn0 = (S.c_q * QN) < 0.0 ? -exp(logn0) : exp(logn0);
+                        const double loglam = ll0 - S.c_kb;
+                        u = loglam * 1.4426950408889634;
+                        n0 = (float)dn0;
+                        p1 = n0;
+                        if (cfg.doppler_scheme == 1 && !S.numeric_vn) {
+                            vs += (float)(S.c_v * dn0 * exp(S.e_v * loglam));
+                            ns += (float)QN;
+                        }
+                    } else {
+                        const double lq = log2_split(QMf);
+                        if (S.psd == RADOP_PSD_1MOM_FIXED_N0) {
+                            // lambda = (lambda_factor / QM)^(1/(4+mu)), hydrometeors.py:761-772, 1039-1049
+                            u = F.uk * (F.u0 - lq);
+                            n0 = F.n0;
+                            p1 = n0;
+                        } else if (S.psd == RADOP_PSD_1MOM_SNOW) {
+                            // N0 = 13.5 * 5.65e5 * exp(-0.107 (T - 273.15)) / 1000, hydrometeors.py:894-907
+                            const double l2n0 = fma(F.nb, (double)T, F.na);
+                            u = F.uk * (F.u0 + l2n0 - lq);
+                            n0 = exp2_split(l2n0);
+                            p1 = n0;
+                        } else {
+                            // 1-mom ice: lambda = (Q2 / QM)^(1/(b-2)) with the Field et al. (2005) second moment,
+                            // hydrometeors.py:1277-1299, 1320-1339; log2 Q2 = (log2 QM' - log2(10) A(T)) / B(T)
+                            const double Tc = (double)T - 273.15;
+                            const double a = (5.065339 - 3.032362 * 3.0 + 0.312550 * 9.0 - 0.015952 * 27.0) +
+                                             Tc * ((-0.062659 + 0.029469 * 3.0 + 0.003199 * 9.0) + Tc * (-0.000285 + 0.000204 * 3.0));
+                            const double b = (0.476221 + 0.165977 * 3.0 + 0.060366 * 9.0 - 0.003577 * 27.0) +
+                                             Tc * ((-0.015896 + 0.007468 * 3.0 + 0.000594 * 9.0) + Tc * (-0.000141 + 0.000079 * 3.0));
+                            double rb = (double)(1.f / (float)b);
+                            rb = rb * (2.0 - b * rb);
+                            rb = rb * (2.0 - b * rb);
+                            const double l2q2 = (lq - F.u0 - 3.321928094887362 * a) * rb;
+                            u = F.uk * (l2q2 - lq) - 9.965784284662087;          // lambda / 1000
+                            p1 = QMf;
+                        }
+                        if (cfg.doppler_scheme == 1 && !S.numeric_vn) {
+                            // _Hydrometeor.integrate_V, hydrometeors.py:178-199
+                            const float fu = (float)u;
+                            vs += F.cv * n0 * ex2f_approx(F.ev * fu);
+                            ns += F.cn * n0 * ex2f_approx(F.en * fu);
+                        }
+                    }
+                    const int ie = (int)__ldg(A.traj_ie + (size_t)s * A.traj_n + trow);
+                    const int it = lut_bin(T, S.t_min, S.t_step, S.t_rstep, S.nt);
+                    bl = ie * S.nt + it;
+                }
+                float2 vn = make_float2(0.f, 0.f);
+                switch (S.lt_nc) {
+                case 7: species_tab<7>(cfg, A, S, have, bl, u, p1, wq, lane, acc, vn); break;
+                case 8: species_tab<8>(cfg, A, S, have, bl, u, p1, wq, lane, acc, vn); break;
+                case 9: species_tab<9>(cfg, A, S, have, bl, u, p1, wq, lane, acc, vn); break;
+                default: species_tab<10>(cfg, A, S, have, bl, u, p1, wq, lane, acc, vn); break;
+                }
+                if (have) {
+                    if (cfg.doppler_scheme == 2) { vs += vn.x; ns += vn.y; }
+                    else if (s == cfg.ice_numeric) { ice_here = true; ice_vn = vn; }
+                }
+            }
+            // --- radial velocity of the sub-beam (doppler_scatter.py:313-333) and this warp's running sums ---
+            {
+                float rvw = 0.f, ww = 0.f;
+                if (live) {
+                    const float rv = wind - (vs / ns) * sinth;     // 0/0 -> NaN where no hydrometeor (Q7)
+                    if (!isnan(rv)) { rvw = rv * wq; ww = wq; }
+                }
+                float (*row)[32] = s_part[warp];
+                if (q == warp) {
+#pragma unroll
+                    for (int cc = 0; cc < 7; ++cc) row[cc][lane] = acc[cc];
+                    row[7][lane] = rvw; row[8][lane] = ww; row[9][lane] = mask_q;
+                } else {
+#pragma unroll
+                    for (int cc = 0; cc < 7; ++cc) row[cc][lane] += acc[cc];
+                    row[7][lane] += rvw; row[8][lane] += ww; row[9][lane] += mask_q;
+                }
+            }
+            // --- numeric fall-speed moments (IceParticle.integrate_V sums over ALL gates of a sub-beam and the
+            //     total lands on its first gate with ice, hydrometeors.py:1256-1275): partial sums of this span ---
+            if (A.ice_part) {
+                const unsigned icy = __ballot_sync(0xffffffffu, ice_here);
+                float v = ice_vn.x, n = ice_vn.y;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) {
+                    v += __shfl_xor_sync(0xffffffffu, v, d);
+                    n += __shfl_xor_sync(0xffffffffu, n, d);
+                }
+                const int first = icy ? __ffs(icy) - 1 : 0;
+                const float w_f = __shfl_sync(0xffffffffu, wind, first), s_f = __shfl_sync(0xffffffffu, sinth, first);
+                const float vs_f = __shfl_sync(0xffffffffu, vs, first), ns_f = __shfl_sync(0xffffffffu, ns, first);
+                if (lane == 0) {
+                    float4 *dst = A.ice_part + ((size_t)rq * n_spans + span) * 2;
+                    dst[0] = make_float4(v, n, __int_as_float(icy ? span * 32 + first : -1), w_f);
+                    dst[1] = make_float4(s_f, vs_f, ns_f, wq);
+                }
+            }
+        }
+        __syncthreads();
+        if (warp == 0 && in_range) {
+            float t[FUSED_NPART];
+#pragma unroll
+            for (int i = 0; i < FUSED_NPART; ++i) t[i] = s_part[0][i][lane];
+            const int nw = min(W, n_sub);
+            for (int w = 1; w < nw; ++w)
+#pragma unroll
+                for (int i = 0; i < FUSED_NPART; ++i) t[i] += s_part[w][i][lane];
+            const size_t rg = (size_t)ray * ng + g;
+            float4 *dst = reinterpret_cast<float4 *>(A.comb + rg * 8);
+            dst[0] = make_float4(t[0], t[1], t[2], t[3]);
+            dst[1] = make_float4(t[4], t[5], t[6], t[7]);
+            A.wsum[rg] = t[8];
+            float mk = t[9] / (float)n_sub;
+            if (mk > -1.f && mk <= 0.f) mk = 0.f;
+            A.mask_out[rg] = mk;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < cfg.n_species && s_pairs[threadIdx.x]) atomicAdd(A.n_pairs + threadIdx.x, (unsigned long long)s_pairs[threadIdx.x]);
+}
+
+// The total of the numeric fall-speed moments of a sub-beam lands on its first gate with ice (see above): one
+// thread per ray adds the spans' partial sums in order and replaces that gate's contribution to the velocity sums.
+__global__ void k_ice_fixup(const __grid_constant__ DevConfig cfg, const float4 *__restrict__ ice_part, int n_spans,
+                            float *__restrict__ comb, float *__restrict__ wsum)
+{
+    const int ray = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ray >= cfg.n_rays) return;
+    for (int q = 0; q < cfg.n_sub; ++q) {
+        const float4 *p = ice_part + ((size_t)ray * cfg.n_sub + q) * n_spans * 2;
+        float V = 0.f, N = 0.f;
+        int first = -1;
+        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+        for (int sp = 0; sp < n_spans; ++sp) {
+            const float4 x = __ldg(p + 2 * sp);
+            V += x.x; N += x.y;
+            if (first < 0 && __float_as_int(x.z) >= 0) { first = __float_as_int(x.z); a0 = x; a1 = __ldg(p + 2 * sp + 1); }
+        }
+        if (first < 0) continue;
+        const float wind = a0.w, sinth = a1.x, vs = a1.y, ns = a1.z, w = a1.w;
+        const float rv_old = wind - (vs / ns) * sinth;
+        const float rv_new = wind - ((vs + V) / (ns + N)) * sinth;
+        const size_t rg = (size_t)ray * cfg.n_gates + first;
+        float r = comb[rg * 8 + 7], ws = wsum[rg];
+        if (!isnan(rv_old)) { r -= rv_old * w; ws -= w; }
+        if (!isnan(rv_new)) { r += rv_new * w; ws += w; }
+        comb[rg * 8 + 7] = r;
+        wsum[rg] = ws;
+    }
+}

@@ -2185,6 +2185,8 @@ k_integrate_tab(const __grid_constant__ DevConfig cfg, K2tArgs A)
     }
 }
 
+#include "radop_fused.cuh"
+
 // ------------------------------------------------------------------------------------------
 // K3: quadrature / species sums and the per-ray epilogue
 // ------------------------------------------------------------------------------------------
@@ -2343,6 +2345,7 @@ struct K3Args {
     const double *sub_weight;
     const float *ray_nyquist;
     float *comb;        // [ray][gate][8]: b c p q kd s9 s11 rvel
+    const float *wsum;  // fused pipeline: comb[7] holds sum(rv w) and this the sum of the weights; else null
     float *out;         // [N_OUT+1][ray][gate]
     float *model_out;   // [NVP][ray][gate]
 };
@@ -2480,6 +2483,7 @@ k_ray_epilogue(const __grid_constant__ DevConfig cfg, K3Args A)
             const float4 *src = reinterpret_cast<const float4 *>(A.comb + ((size_t)ray * ng + g) * 8);
             float4 a = src[0], b = src[1];
             c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b.x; c[5] = b.y; c[6] = b.z; c[7] = b.w;
+            if (A.wsum) c[7] = c[7] / A.wsum[(size_t)ray * ng + g];
         } else {
 #pragma unroll
             for (int i = 0; i < 8; ++i) c[i] = 0.f;

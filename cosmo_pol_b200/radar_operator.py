@@ -326,8 +326,8 @@ class RadarOperator(object):
 
     def simulate_rays(self, ray_az, ray_el, keep_debug=False, distributed=True, copy=True):
         """Batched hot path over an arbitrary ray list; returns dict name -> [n_rays, n_gates].
-        With torch.distributed initialised (and distributed=True) the ONE ray list is cut into contiguous
-        blocks, one per rank, as the reference splits it over its pool workers (radar_operator.py:402-435),
+        With torch.distributed initialised (and distributed=True) the ONE ray list is dealt out to the ranks in
+        small blocks (parallel.shard_indices), as the reference splits it over its pool workers (radar_operator.py:402-435),
         and the result is gathered over NCCL (``gather='all'``: on every rank, ``'root'``: on rank 0, None
         elsewhere).  copy=False returns views of the pinned host buffers the operator owns (valid until its next
         call) instead of fresh arrays."""
@@ -347,7 +347,7 @@ class RadarOperator(object):
         return self._simulate_sharded(eng, ray_az, ray_el, rank, world, want_model, copy)
 
     def _simulate_sharded(self, eng, ray_az, ray_el, rank, world, want_model, copy=True):
-        """Rank r simulates rays [lo_r, hi_r) of the list; observables, positions, model variables and
+        """Rank r simulates the rays parallel.shard_indices(n, r, world) of the list; observables, positions, model variables and
         spectra travel device -> device through parallel.RayGather (no host bounce), the receiving ranks copy
         the assembled result to pinned host memory.  A rank without rays (more ranks than rays) takes part
         in the collectives with an empty block; the ranks agree on an error status BEFORE the first data
@@ -356,13 +356,13 @@ class RadarOperator(object):
         import torch
         from ._abi import BUF_OBS, BUF_LAT, BUF_LON, BUF_MODEL, BUF_DSPECTRUM
         n_total = len(ray_az)
-        lo, hi = parallel.shard_bounds(n_total, rank, world)
-        n_loc = hi - lo
+        mine = parallel.shard_indices(n_total, rank, world)
+        n_loc = len(mine)
         ng = len(constants.RANGE_RADAR)
         code, err, scan = 0, None, None
         try:
             if n_loc:
-                scan = self.build_scan(ray_az[lo:hi], ray_el[lo:hi])
+                scan = self.build_scan(ray_az[mine], ray_el[mine])
                 self._last_scan = scan
                 eng.stage(scan)
                 eng.execute()

@@ -249,6 +249,18 @@ int radop_get_integration(RadopHandle *h, int *mode, int64_t *n_pieces, int64_t 
  * table = exponent word of the first column, INT32_MIN for a rejected piece (n_status >= ne * nt * 176). */
 int radop_debug_integration(RadopHandle *h, int species, int64_t why[4], int32_t *piece_status, int64_t n_status);
 int radop_get_geodesy(RadopHandle *h, int *used_polynomials);
+/* Launch sequence of the hot path.  mode 0 (default): the fused kernel k_gate_fused (geolocation, interpolation,
+ * PSD parameters, table contraction, species and sub-beam sums in one pass, nothing per sub-beam gate written to
+ * HBM) whenever the configuration allows it -- table integration, no melting species, Doppler scheme 1 or 2, no
+ * model-variable outputs, no debug dump, polynomial geodesy -- else the staged pipeline (k_interp_psd ->
+ * k_integrate_tab / k_integrate -> k_reduce_subbeams).  mode 1: the staged pipeline always.  Both are held to the
+ * oracle and to each other by the GPU tests.  radop_get_pipeline: *used_fused = 1 if the last run was fused. */
+int radop_set_pipeline(RadopHandle *h, int mode);
+/* Launch-shape knobs (results do not depend on them): RADOP_TUNE_FUSED_WARPS = warps per CTA of the fused kernel,
+ * 0 = chosen from the number of sub-beams. */
+enum { RADOP_TUNE_FUSED_WARPS = 0 };
+int radop_set_tuning(RadopHandle *h, int key, int64_t value);
+int radop_get_pipeline(RadopHandle *h, int *used_fused);
 
 int radop_device_outputs(RadopHandle *h, void **dev_ptr, int64_t *n_rays, int64_t *n_gates);
 /* Any device-resident result of the last radop_execute, for gathers that must not bounce through the host

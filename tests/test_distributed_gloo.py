@@ -10,6 +10,21 @@ import pytest
 from conftest import ROOT
 
 
+def test_shard_indices_partition_the_ray_list():
+    from cosmo_pol_b200.parallel import shard_indices, shard_counts
+    for n in (0, 1, 7, 52, 360, 7200, 7201):
+        for world in (1, 2, 3, 8):
+            parts = [shard_indices(n, r, world) for r in range(world)]
+            assert sorted(np.concatenate(parts).tolist()) == list(range(n))
+            assert [len(p) for p in parts] == list(shard_counts(n, world))
+            assert all(np.all(np.diff(p) > 0) for p in parts)
+    # every rank sees every elevation of a 20 x 360 volume, equal ray counts at 2, 4, 8 ranks
+    for world in (2, 4, 8):
+        parts = [shard_indices(7200, r, world) for r in range(world)]
+        assert all(len(p) == 7200 // world for p in parts)
+        assert all(len(np.unique(p // 360)) == 20 for p in parts)
+
+
 def test_shard_bounds_cover_everything():
     from cosmo_pol_b200.parallel import shard_bounds
     for n in (0, 1, 7, 360, 7200, 7201):
@@ -30,16 +45,16 @@ def _worker(rank, world, port, n_total, q):
     os.environ['MASTER_PORT'] = str(port)
     dist.init_process_group('gloo', rank=rank, world_size=world)
     try:
-        lo, hi = parallel.shard_bounds(n_total, rank, world)
+        mine = torch.from_numpy(parallel.shard_indices(n_total, rank, world))
         full = torch.arange(3 * n_total * 5, dtype=torch.float32).reshape(3, n_total, 5)
-        local = full[:, lo:hi].contiguous()
+        local = full[:, mine].contiguous()
         got = parallel.all_gather_rays(local, n_total)
         q.put((rank, bool(torch.equal(got, full)), parallel.dist_info()))
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize('n_total', [7, 10])
+@pytest.mark.parametrize('n_total', [7, 10, 41])
 def test_all_gather_rays_gloo_world2(n_total):
     import torch.multiprocessing as mp
     s = socket.socket()
@@ -68,12 +83,12 @@ def _worker_gather(rank, world, port, n_total, mode, q):
     os.environ['MASTER_PORT'] = str(port)
     dist.init_process_group('gloo', rank=rank, world_size=world)
     try:
-        lo, hi = parallel.shard_bounds(n_total, rank, world)
+        mine = torch.from_numpy(parallel.shard_indices(n_total, rank, world))
         full = torch.arange(2 * n_total * 3, dtype=torch.float64).reshape(2, n_total, 3)
         g = parallel.RayGather(mode, depth=2)
         ok = True
         for rep in range(3):                                   # slots are reused
-            pend = g.launch((full[:, lo:hi] + rep).contiguous(), n_total)
+            pend = g.launch((full[:, mine] + rep).contiguous(), n_total)
             host = g.to_host(pend, key='x')
             if mode == 'all' or rank == 0:
                 ok = ok and host is not None and bool(torch.equal(host, full + rep))
@@ -86,7 +101,7 @@ def _worker_gather(rank, world, port, n_total, mode, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize('n_total,mode', [(1, 'all'), (1, 'root'), (7, 'root'), (8, 'all')])
+@pytest.mark.parametrize('n_total,mode', [(1, 'all'), (1, 'root'), (7, 'root'), (8, 'all'), (37, 'root')])
 def test_ray_gather_gloo_world2(n_total, mode):
     """RayGather as RadarOperator._simulate_sharded uses it: empty shards (1 ray, 2 ranks), uneven blocks,
     both modes, repeated launches, and the status agreement that precedes the data collectives."""
