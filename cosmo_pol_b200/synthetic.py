@@ -51,16 +51,34 @@ def _wgs_to_rot(lat, lon, sp_lat, sp_lon):
     return np.rad2deg(np.arcsin(zn)), np.rad2deg(np.arctan2(yn, xn))
 
 
-def _smooth_noise(rng, shape, sigma):
-    f = gaussian_filter(rng.standard_normal(shape).astype(np.float32), sigma, mode='wrap')
+def _smooth_noise(rng, shape, sigma, coarsen=1):
+    """Gaussian-filtered white noise with unit variance.  coarsen > 1 draws it on a horizontally coarser grid and
+    interpolates linearly (for COSMO-1 sized domains, where filtering 7e7 points per variable takes minutes)."""
+    if coarsen > 1:
+        small = (shape[0], -(-shape[1] // coarsen) + 1, -(-shape[2] // coarsen) + 1)
+        g = gaussian_filter(rng.standard_normal(small).astype(np.float32), (sigma[0], sigma[1] / coarsen, sigma[2] / coarsen),
+                            mode='wrap')
+        yy = np.arange(shape[1], dtype=np.float32) / coarsen
+        xx = np.arange(shape[2], dtype=np.float32) / coarsen
+        y0, x0 = yy.astype(int), xx.astype(int)
+        fy, fx = (yy - y0)[None, :, None], (xx - x0)[None, None, :]
+        f = ((1 - fy) * (1 - fx) * g[:, y0][:, :, x0] + (1 - fy) * fx * g[:, y0][:, :, x0 + 1] +
+             fy * (1 - fx) * g[:, y0 + 1][:, :, x0] + fy * fx * g[:, y0 + 1][:, :, x0 + 1]).astype(np.float32)
+    else:
+        f = gaussian_filter(rng.standard_normal(shape).astype(np.float32), sigma, mode='wrap')
     f /= (np.std(f) + 1e-12)
     return f
 
 
 def make_model(nz=60, ny=400, nx=400, res=0.02, radar=ALBIS, scheme='1mom', seed=1234,
-               south_pole=SOUTH_POLE, top=22000.0, with_edr=False, with_refractivity=False):
-    """Returns dict name -> ModelVariable (all float32, C-contiguous)."""
+               south_pole=SOUTH_POLE, top=22000.0, with_edr=False, with_refractivity=False, coarsen=1):
+    """Returns dict name -> ModelVariable (all float32, C-contiguous).  coarsen: see _smooth_noise (1 = the generator
+    every seeded fixture was made with)."""
     rng = np.random.default_rng(seed)
+    _plain_noise = _smooth_noise
+
+    def _smooth_noise_c(r, shp, sg):
+        return _plain_noise(r, shp, sg, coarsen)
     rlat0, rlon0 = _wgs_to_rot(radar[0], radar[1], south_pole[0], south_pole[1])
     Lo1 = float(np.round(rlon0 - res * (nx - 1) / 2., 4))
     La1 = float(np.round(rlat0 - res * (ny - 1) / 2., 4))
@@ -86,12 +104,12 @@ def make_model(nz=60, ny=400, nx=400, res=0.02, radar=ALBIS, scheme='1mom', seed
     T = 288.15 - 0.0065 * zz + 0.5 * rng.standard_normal(shape)
     T = np.clip(T, 200., 314.).astype(np.float32)
     RHO = (1.225 * np.exp(-zz / 8500.)).astype(np.float32)
-    U = (15. * _smooth_noise(rng, shape, sig)).astype(np.float32)
-    V = (15. * _smooth_noise(rng, shape, sig)).astype(np.float32)
-    W = (2. * _smooth_noise(rng, shape, sig)).astype(np.float32)
+    U = (15. * _smooth_noise_c(rng, shape, sig)).astype(np.float32)
+    V = (15. * _smooth_noise_c(rng, shape, sig)).astype(np.float32)
+    W = (2. * _smooth_noise_c(rng, shape, sig)).astype(np.float32)
 
     def blobs(peak, cond, thr=0.3):
-        f = _smooth_noise(rng, shape, sig)
+        f = _smooth_noise_c(rng, shape, sig)
         f = np.maximum(f - thr, 0.0)
         f = f / (f.max() + 1e-12) * peak
         f[~cond] = 0.0
@@ -113,21 +131,21 @@ def make_model(nz=60, ny=400, nx=400, res=0.02, radar=ALBIS, scheme='1mom', seed
                'I': (constants_2mom.X_MIN_I, constants_2mom.X_MAX_I)}
         for h in ('H', 'R', 'S', 'G', 'I'):
             lo, hi = lim[h]
-            u = 0.5 + 0.25 * np.clip(_smooth_noise(rng, shape, sig), -1.8, 1.8)
+            u = 0.5 + 0.25 * np.clip(_smooth_noise_c(rng, shape, sig), -1.8, 1.8)
             xbar = np.exp(np.log(lo) + (np.log(hi) - np.log(lo)) * u)
             data['QN' + h + '_v'] = (data['Q' + h + '_v'].astype(np.float64) / xbar).astype(np.float32)
         names += BASE_VARIABLES_2MOM
     if with_edr:
         # eddy dissipation rate [m2 s-3] (radar_operator.py:253-254), drawn last so that the other
         # variables do not depend on the flag
-        edr = 10.0 ** (-3.0 + 0.8 * np.clip(_smooth_noise(rng, shape, sig), -2.0, 2.0))
+        edr = 10.0 ** (-3.0 + 0.8 * np.clip(_smooth_noise_c(rng, shape, sig), -2.0, 2.0))
         data['EDR'] = edr.astype(np.float32)
         names.append('EDR')
     if with_refractivity:
         # atmospheric refractivity N = (n - 1) 1e6 (radar_operator.py:239, 294-296): exponential reference
         # atmosphere with a seeded ducting-like perturbation near 1.5 km; drawn after everything else
         nn = 315.0 * np.exp(-zz / 7350.0) * (1.0 + 0.02 * np.exp(-((zz - 1500.0) / 400.0) ** 2))
-        data['N'] = (nn + 0.3 * _smooth_noise(rng, shape, sig)).astype(np.float32)
+        data['N'] = (nn + 0.3 * _smooth_noise_c(rng, shape, sig)).astype(np.float32)
         names.append('N')
     attrs = {'z-levels': z, 'proj_info': proj, 'resolution': [res, res], 'time': '2026-01-01 00:00:00'}
     return {n: ModelVariable(n, np.ascontiguousarray(data[n]), attrs) for n in names}
@@ -219,10 +237,18 @@ def make_melting_lut(hydrom, frequency=5.6, scheme='1mom', seed=4321, n_e=None, 
     return lut
 
 
-def make_lut(hydrom, frequency=5.6, scheme='1mom', seed=4321, n_e=None, n_t=None, n_d=NUM_DIAMETERS):
+def make_lut(hydrom, frequency=5.6, scheme='1mom', seed=4321, n_e=None, n_t=None, n_d=NUM_DIAMETERS, family='smooth'):
     """Synthetic scattering table for one species; same axes/layout the reference
     generator writes (compute_lut_sz.py:428-433).  ``n_e``/``n_t`` truncate the
-    e / t axes (tests use small tables)."""
+    e / t axes (tests use small tables).
+
+    family='smooth': Rayleigh-Gans-like columns with a 1 % ripple (every column but s10 - s8 of one sign).
+    family='mie': the same magnitudes with what real T-matrix columns of large particles show at C / X band
+    (compute_lut_sz.py:265-297 tabulates them up to size parameters of several units for graupel and hail):
+    resonance ripple along the diameter axis with a period of about one unit of the size parameter x = pi D / lambda
+    (i.e. lambda / pi in D) and an amplitude that grows with x, and SIGN CHANGES of the differential quantities
+    -- Z12 = Z21, Z34 = -Z43, Re and Im of S_hh - S_vv -- once x exceeds ~1.  It exists to stress the
+    lambda-transformed tables (sign-changing columns are the hard case of their envelope / ratio representation)."""
     sp = _SPECIES[hydrom]
     rng = np.random.default_rng(seed + sum(ord(ch) for ch in hydrom))
     elev = ELEVATIONS if n_e is None else ELEVATIONS[:n_e]
@@ -242,9 +268,21 @@ def make_lut(hydrom, frequency=5.6, scheme='1mom', seed=4321, n_e=None, n_t=None
     # oblateness seen by the beam: grows with D, vanishes at vertical incidence
     obl = sp['obl'] * Dd / (1.0 + 0.08 * Dd) * np.exp(-2 * np.deg2rad(sp['cant']) ** 2) * np.cos(e) ** 2
     wig = 1.0 + 0.01 * np.sin(0.7 * Dd + 0.05 * (t - 250.))
+    dphi = 0.04 * xsz ** 2 * np.cos(e) ** 2 * (1 + 0.002 * (t - 273.15))     # backscatter phase difference
+    if family == 'mie':
+        # resonances: one ripple per unit of the size parameter (period lambda / pi in D; 1.5 ripples per unit for the
+        # liquid species), amplitude saturating at 45 %; the differential terms oscillate through zero with a
+        # slightly different frequency and a phase that drifts with elevation and temperature
+        kres = 2.0 * np.pi * (1.5 if sp['liq'] else 1.0)
+        grow = xsz ** 2 / (1.0 + xsz ** 2)
+        amp = amp * (1.0 + 0.45 * grow * np.sin(kres * xsz + 0.3 + 0.002 * (t - 250.)))
+        flip = np.cos(0.8 * kres * np.maximum(xsz - 0.6, 0.0) + 0.4 * np.cos(e) + 0.003 * (t - 250.))
+        obl = obl * flip                                                     # Z12 / Z21, S_hh - S_vv change sign
+        dphi = dphi * np.cos(0.6 * kres * xsz + 0.2)                         # Z34 / Z43 change sign
+    elif family != 'smooth':
+        raise ValueError('unknown table family {!r}'.format(family))
     shh = amp * (1.0 + obl) * wig
     svv = amp * (1.0 - obl) / wig
-    dphi = 0.04 * xsz ** 2 * np.cos(e) ** 2 * (1 + 0.002 * (t - 273.15))     # backscatter phase difference
     rho0 = 0.9985 - 0.004 * obl / (sp['obl'] + 1e-12) - 0.002 * xsz ** 2 / (1 + xsz ** 2)
     shape = (len(elev), len(temp), n_d)
     tab = np.zeros(shape + (12,), dtype=np.float64)
@@ -287,8 +325,8 @@ def species_for(scheme, with_ice=True):
 
 
 def make_all_luts(frequency=5.6, scheme='1mom', with_ice=True, seed=4321, n_e=None, n_t=None, with_melting=False,
-                  n_e_melting=None):
-    luts = {h: make_lut(h, frequency, scheme, seed, n_e, n_t) for h in species_for(scheme, with_ice)}
+                  n_e_melting=None, family='smooth'):
+    luts = {h: make_lut(h, frequency, scheme, seed, n_e, n_t, family=family) for h in species_for(scheme, with_ice)}
     if with_melting:
         for h in ('mS', 'mG'):
             luts[h] = make_melting_lut(h, frequency, scheme, seed, n_e_melting if n_e_melting else n_e)

@@ -417,6 +417,78 @@ def geod_fwd(lon0, lat0, azimuth, dist):
     return lon2, lat2
 
 
+def geod_fwd_karney(lon0, lat0, azimuth, dist):
+    """Direct geodesic on WGS84 by the algorithm pyproj.Geod.fwd runs (PROJ's geodesic.c = GeographicLib):
+    C. F. F. Karney, "Algorithms for geodesics", J. Geodesy 87 (2013), sections 2-4, series truncated at order 6
+    in the expansion parameter epsilon (eqs. 17, 18, 21, 24, 25).  The reference calls it at
+    interpolation.py:526-536; pyproj is absent here and its version is unpinned (setup.py:53), so this is a
+    restatement of the PUBLISHED algorithm, not of PROJ's source, used to measure how far the Vincenty stand-in
+    (geod_fwd) is from it.  All float64, vectorised with numpy broadcasting.  Returns lon, lat [deg]."""
+    a, f = WGS84_A, WGS84_F
+    b = (1 - f) * a
+    n = f / (2 - f)
+    ep2 = f * (2 - f) / ((1 - f) ** 2)                  # second eccentricity squared
+    dist = np.asarray(dist, dtype=np.float64)
+    phi1 = np.deg2rad(np.float64(lat0))
+    alp1 = np.deg2rad(np.asarray(azimuth, dtype=np.float64))
+    salp1, calp1 = np.sin(alp1), np.cos(alp1)
+    # reduced latitude
+    sbet1, cbet1 = (1 - f) * np.sin(phi1), np.cos(phi1)
+    nrm = np.hypot(sbet1, cbet1)
+    sbet1, cbet1 = sbet1 / nrm, cbet1 / nrm
+    # azimuth at the equator crossing (eq. 10), arc length and longitude on the auxiliary sphere at point 1 (11, 12)
+    salp0 = salp1 * cbet1
+    calp0 = np.hypot(calp1, salp1 * sbet1)
+    ssig1, csig1 = sbet1, calp1 * cbet1
+    somg1, comg1 = salp0 * sbet1, calp1 * cbet1
+    nrm = np.hypot(ssig1, csig1)
+    ssig1, csig1 = ssig1 / nrm, csig1 / nrm
+    sig1 = np.arctan2(ssig1, csig1)
+    k2 = ep2 * calp0 ** 2
+    eps = k2 / (2 * (1 + np.sqrt(1 + k2)) + k2)         # eq. 16
+    e2_ = eps * eps
+    A1 = (1 + e2_ * (1. / 4 + e2_ * (1. / 64 + e2_ / 256))) / (1 - eps)          # eq. 17
+    C1 = [eps * (-1. / 2 + e2_ * (3. / 16 - e2_ / 32)),                           # eq. 18
+          e2_ * (-1. / 16 + e2_ * (1. / 32 - e2_ * 9. / 2048)),
+          eps * e2_ * (-1. / 48 + e2_ * 3. / 256),
+          e2_ * e2_ * (-5. / 512 + e2_ * 3. / 512),
+          eps * e2_ * e2_ * (-7. / 1280),
+          e2_ * e2_ * e2_ * (-7. / 2048)]
+    C1p = [eps * (1. / 2 + e2_ * (-9. / 32 + e2_ * 205. / 1536)),                 # eq. 21 (reverted series)
+           e2_ * (5. / 16 + e2_ * (-37. / 96 + e2_ * 1335. / 4096)),
+           eps * e2_ * (29. / 96 - e2_ * 75. / 128),
+           e2_ * e2_ * (539. / 1536 - e2_ * 2391. / 2560),
+           eps * e2_ * e2_ * (3467. / 7680),
+           e2_ * e2_ * e2_ * (38081. / 61440)]
+    A3 = 1 - eps * ((1 - n) / 2 + eps * ((1. / 4 + n / 8 - 3 * n * n / 8) + eps * ((1. / 16 + 3 * n / 16 + n * n / 16) +
+               eps * ((3. / 64 + n / 32) + eps * 3. / 128))))                     # eq. 24
+    C3 = [eps * ((1 - n) / 4 + eps * ((1 - n * n) / 8 + eps * ((3. / 64 + 3 * n / 64 - n * n / 64) +
+                 eps * ((5. / 128 + n / 64) + eps * 3. / 128)))),                 # eq. 25
+          e2_ * ((1. / 16 - 3 * n / 32 + n * n / 32) + eps * ((3. / 64 - n / 32 - 3 * n * n / 64) +
+                 eps * ((3. / 128 + n / 128) + eps * 5. / 256))),
+          eps * e2_ * ((5. / 192 - 3 * n / 64 + 5 * n * n / 192) + eps * ((3. / 128 - 5 * n / 192) + eps * 7. / 512)),
+          e2_ * e2_ * ((7. / 512 - 7 * n / 256) + eps * 7. / 512),
+          eps * e2_ * e2_ * (21. / 2560)]
+
+    def fourier(coef, sig):
+        return sum(c * np.sin(2 * (l + 1) * sig) for l, c in enumerate(coef))
+
+    B11 = fourier(C1, sig1)
+    tau1 = sig1 + B11                                   # I1(sigma1) / A1
+    tau2 = tau1 + dist / (b * A1)                       # eq. 7: s / b = I1(sigma)
+    sig2 = tau2 + fourier(C1p, tau2)                    # eq. 20
+    ssig2, csig2 = np.sin(sig2), np.cos(sig2)
+    sbet2 = calp0 * ssig2
+    cbet2 = np.hypot(salp0, calp0 * csig2)
+    somg2, comg2 = salp0 * ssig2, csig2
+    # longitude difference on the auxiliary sphere, then eq. 8 with I3 (eq. 23)
+    omg12 = np.arctan2(somg2 * comg1 - comg2 * somg1, comg2 * comg1 + somg2 * somg1)
+    lam12 = omg12 - f * salp0 * A3 * ((sig2 - sig1) + (fourier(C3, sig2) - fourier(C3, sig1)))
+    lat2 = np.rad2deg(np.arctan2(sbet2, (1 - f) * cbet2))
+    lon2 = np.float64(lon0) + np.rad2deg(lam12)
+    return lon2, lat2
+
+
 def wgs_to_rotated(lat, lon, sp_lat, sp_lon):
     """Geographic -> rotated-pole coordinates given the rotated SOUTH pole
     (stand-in for pycosmo.WGS_to_COSMO, interpolation.py:566-568).  Rotation about

@@ -34,7 +34,7 @@ CONFIGS = {
     'cfg1': dict(conf=base_conf(), scheme='1mom', rays='ppi', what='PPI 1.0 deg, C-band, 1-mom, 360 x 500 x 3x3'),
     'cfg2': dict(conf=base_conf(freq=9.41), scheme='2mom', rays='ppi', what='PPI 1.0 deg, X-band, 2-mom R/S/G/H/I, 360 x 500 x 3x3'),
     'cfg4': dict(conf=base_conf(nh=29, nv=29), scheme='1mom', rays='rhi', what='RHI 0..90 deg, 29x29 Gauss-Hermite, attenuation on, 91 x 500 x 841'),
-    'cfg5': dict(conf=base_conf(doppler=3), scheme='1mom', rays='volume', model=dict(nz=80, ny=774, nx=1158, res=0.01),
+    'cfg5': dict(conf=base_conf(doppler=3), scheme='1mom', rays='volume', model=dict(nz=80, ny=774, nx=1158, res=0.01, coarsen=3),
                  what='20-elevation volume, Doppler spectrum (scheme 3, FFT 128), COSMO-1 sized grid 80x774x1158'),
     'cfg5s': dict(conf=base_conf(doppler=3), scheme='1mom', rays='volume',
                   what='20-elevation volume, Doppler spectrum (scheme 3, FFT 128), standard 60x400x400 grid'),

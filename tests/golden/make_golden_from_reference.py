@@ -61,6 +61,14 @@ PATCHES = {
         ('    list_variables = dic_variables.values()\n    keys = dic_variables.keys()\n',
          '    list_variables = list(dic_variables.values())\n    keys = list(dic_variables.keys())\n'),
     ],
+    # only exercised by golden_lut_file: dict.has_key is python 2; np.save of the ragged list of axes made an
+    # object array by itself up to numpy 1.23 and raises since; see also the third patch
+    'cosmo_pol/lookup/lut.py': [
+        ('if self.axes_names.has_key(name):', 'if name in self.axes_names:'),
+        ("np.save(tmp_dir + 'axes',lut.axes)", "np.save(tmp_dir + 'axes', np.array(lut.axes, dtype=object))"),
+        # ndarray.all() of a 0-d object array returned the object (the dict) up to numpy 1.x
+        ('            data = data.all()\n', '            data = data.item()\n'),
+    ],
 }
 
 
@@ -321,6 +329,28 @@ def golden_units(R):
     np.savez_compressed(os.path.join(HERE, 'ref_units.npz'), **g)
 
 
+def golden_lut_file(R):
+    """A lookup-table file written by the reference's OWN save_lut (lut.py:78-124) from a table assembled with its own
+    Lookup_table.add_axis / set_value_table, read back with its own load_lut: tests/golden/ref_saved_by_reference.lut
+    (committed, 10 KB) is what cosmo_pol_b200.lookup.load_lut must be able to read."""
+    lut = synthetic.make_lut('S', 5.6, '1mom', n_e=3, n_t=4, n_d=8)
+    L = R['lut'].Lookup_table()
+    for name in ('e', 't', 'd', 'sz'):
+        L.add_axis(name, lut.axes[lut.axes_names[name]])
+    L.set_value_table(lut.value_table)
+    path = os.path.join(HERE, 'ref_saved_by_reference.lut')
+    R['lut'].save_lut(L, path)
+    back = R['lut'].load_lut(path)
+    e = np.array([-0.5, 1.0, 3.9, 9.0], dtype='float32')
+    t = np.array([199.0, 202.5, 205.9, 300.0], dtype='float32')
+    np.savez_compressed(os.path.join(HERE, 'ref_lut_file.npz'), value_table=np.asarray(back.value_table),
+                        axes_limits=np.asarray(back.axes_limits, dtype=np.float64),
+                        axes_step=np.asarray(back.axes_step, dtype=np.float64),
+                        axis_d=np.asarray(back.axes[back.axes_names['d']], dtype=np.float64),
+                        names=np.array(json.dumps(back.axes_names)), e=e, t=t, line=back.lookup_line(e=e, t=t))
+    print('lutfile done:', os.path.getsize(path), 'bytes')
+
+
 CASES = {
     # name: (scheme, freq, config overrides, rays [(az, el)], model kwargs)
     'c1mom': ('1mom', 5.6, dict(radar={'range': 45000, 'radial_resolution': 900}, integration={'nv_GH': 3, 'nh_GH': 3}),
@@ -433,6 +463,8 @@ if __name__ == '__main__':
     R = import_reference()
     golden_constants(R)
     golden_units(R)
+    golden_lut_file(R)
     which = sys.argv[1:] or list(CASES.keys())
     for name in which:
-        golden_path(R, name)
+        if name != 'lutfile':
+            golden_path(R, name)

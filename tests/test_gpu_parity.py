@@ -930,6 +930,56 @@ def test_full_volume_every_index_bit_exact():
     op.close()
 
 
+def test_cfg5_doppler_spectra_on_cosmo1_sized_domain():
+    """Configuration 5 at its stated size: the 20-elevation volume with Doppler spectra (scheme 3, FFT 128 -> 129
+    velocity bins, 1.86 GB of DSPECTRUM) on an 80 x 774 x 1158 grid at 0.01 deg (the COSMO-1 domain the reference
+    names, radar_operator.py:684): 4.6 GB of interleaved fields on the device.  A ray sample is held to the oracle
+    (observables, spectra bin by bin, velocities); the whole volume to what does not depend on the size: RVEL is the
+    power-weighted mean velocity of the returned spectrum at every one of the 3.6e6 ray gates
+    (doppler_scatter.py:422-429), censored gates are NaN in both, and a second run returns the same bits."""
+    import bench
+    from cosmo_pol_b200 import RadarOperator, synthetic
+    from cosmo_pol_b200.constants import global_constants as constants
+    conf = bench.volume_config()
+    conf['doppler'] = {'scheme': 3}
+    conf['radar']['FFT_length'] = 128
+    conf['radar']['sensitivity'] = [-300, 10000]
+    model = synthetic.make_model(nz=80, ny=774, nx=1158, res=0.01, coarsen=3)
+    luts = synthetic.make_all_luts(5.6, '1mom', with_ice=True)
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    az, el = bench.volume_rays()
+    out = op.simulate_rays(az, el, copy=False)
+    sp = out['DSPECTRUM']
+    assert sp.shape == (7200, 500, 129) and len(constants.VARRAY) == 129
+    v = np.asarray(constants.VARRAY, dtype=np.float64)
+    with np.errstate(invalid='ignore', divide='ignore'):
+        tot = np.nansum(sp, axis=2, dtype=np.float64)
+        mean_v = np.nansum(sp * v[None, None, :], axis=2, dtype=np.float64) / tot
+    rv = out['RVEL'].astype(np.float64)
+    has = tot > 0
+    assert has.sum() > 1e6
+    assert np.all(np.isnan(rv[~has]))
+    assert np.max(np.abs(rv[has] - mean_v[has])) < 2e-3
+    zh = out['ZH']
+    assert np.array_equal(np.isnan(zh), ~has) or np.sum(np.isnan(zh) != ~has) < 1e-3 * has.size
+    chk = (float(np.nansum(zh[::11])), float(np.nansum(sp[::53])))
+    # ray sample against the oracle (two low rays through rain / snow, one at 20 deg)
+    raz, rel = np.array([25., 200., 311.]), np.array([1.0, 4.5, 20.0])
+    idx = [int(np.where((az == a) & (el == e))[0][0]) for a, e in zip(raz, rel)]
+    pm, pl = plain(model, luts)
+    ref = O.simulate_scan(pm, pl, oracle_cfg(op), raz, rel, accum='f64', sensitivity_cut=True)
+    got = {k: np.asarray(out[k])[idx] for k in ('ZH', 'ZV', 'ZDR', 'KDP', 'RHOHV', 'ATT_H', 'ATT_V', 'PHIDP', 'DELTA_HV', 'RVEL', 'DSPECTRUM')}
+    assert_observables_close(got, ref, what='cfg5')
+    strong = _spectrum_close(got['DSPECTRUM'], ref['DSPECTRUM'], ref['ZH'], 'cfg5')
+    ok = np.isfinite(ref['RVEL']) & strong
+    assert ok.sum() > 100 and np.max(np.abs(got['RVEL'][ok] - ref['RVEL'][ok])) < 0.05
+    again = op.simulate_rays(az, el, copy=False)
+    assert chk == (float(np.nansum(again['ZH'][::11])), float(np.nansum(again['DSPECTRUM'][::53])))
+    op.close()
+
+
 def test_full_size_volume_properties():
     """BASELINE.json configuration 3 at its full size (7200 rays x 500 gates x 9 sub-beams, the
     workload bench.py times): determinism, shard consistency (two half volumes = the whole volume,

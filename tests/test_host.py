@@ -64,6 +64,21 @@ def test_lut_file_roundtrip_and_floor_lookup(tmp_path):
         load_all_lut('1mom', ['G'], 5.6, 'tmatrix_masc', folder=str(tmp_path))
 
 
+def test_reads_a_table_file_written_by_the_reference():
+    """tests/golden/ref_saved_by_reference.lut was written by the reference's own save_lut (cosmo_pol/lookup/lut.py:78-124)
+    from a table assembled with its own Lookup_table (make_golden_from_reference.py golden_lut_file); the loader of this
+    package must read it into the same arrays and answer lookup_line like the reference's load_lut + lookup_line."""
+    from cosmo_pol_b200.lookup import load_lut
+    g = np.load(os.path.join(GOLDEN, 'ref_lut_file.npz'))
+    lut = load_lut(os.path.join(GOLDEN, 'ref_saved_by_reference.lut'))
+    assert dict(lut.axes_names) == json.loads(str(g['names']))
+    assert np.array_equal(np.asarray(lut.value_table), g['value_table'])
+    assert np.array_equal(np.asarray(lut.axes_limits, dtype=np.float64), g['axes_limits'])
+    assert np.array_equal(np.asarray(lut.axes_step, dtype=np.float64), g['axes_step'])
+    assert np.array_equal(np.asarray(lut.axes[lut.axes_names['d']], dtype=np.float64), g['axis_d'])
+    assert np.array_equal(lut.lookup_line(e=g['e'], t=g['t']), g['line'])
+
+
 def test_quadrature_fan():
     from cosmo_pol_b200.interpolation.quadrature import subbeam_fan
     import radop_oracle as O
