@@ -233,8 +233,6 @@ int radop_set_params(RadopHandle *h, const RadopParams *p)
         if (wet_species && (!p->with_melting || p->two_moment))
             return h->fail(RADOP_ERR_UNSUPPORTED, "melting species need with_melting and the one-moment scheme "
                                                   "(the reference's two-moment call raises ValueError)");
-        if (wet_species && p->doppler_scheme == 3)
-            return h->fail(RADOP_ERR_UNSUPPORTED, "Doppler spectrum (scheme 3) of melting species is not implemented");
     }
     h->p = *p;
     h->have_params = true;
@@ -939,15 +937,17 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             // warps per CTA = sub-beams of a ray (at most 12), else the count between 6 and 12 that leaves the fewest idle
             int W = h->fused_warps > 0 ? std::min(std::min(h->fused_warps, c.n_sub), FUSED_MAX_WARPS) : 0;
             if (W == 0) {
-                // the warp count (at most 10) that leaves the fewest warps idle in the last round over the sub-beams
-                // (9 sub-beams: 3 warps x 3 rounds; 841: 10 x 85 with 9 idle slots ...), the larger CTA winning ties
-                int waste = 1 << 30;
-                for (int w = 3; w <= std::min(c.n_sub, FUSED_MAX_WARPS); ++w) {
-                    const int ws = (c.n_sub + w - 1) / w * w - c.n_sub;
-                    if (ws * 64 / c.n_sub <= waste) { waste = ws * 64 / c.n_sub; W = w; }
+                // one warp per sub-beam up to 10 sub-beams (3 x 3 quadrature: 9 warps, measured 4.08 ms against 4.46 ms
+                // with 3 warps x 3 rounds); beyond, the count between 5 and 10 that leaves the fewest warps idle in the last
+                // round over the sub-beams (841: 10 x 85 with 9 idle slots), the larger CTA winning ties
+                W = std::min(c.n_sub, FUSED_MAX_WARPS);
+                if (c.n_sub > FUSED_MAX_WARPS) {
+                    int waste = 1 << 30;
+                    for (int w = 5; w <= FUSED_MAX_WARPS; ++w) {
+                        const int ws = (c.n_sub + w - 1) / w * w - c.n_sub;
+                        if (ws * 64 / c.n_sub <= waste) { waste = ws * 64 / c.n_sub; W = w; }
+                    }
                 }
-                if (W == 0) W = std::max(1, std::min(c.n_sub, FUSED_MAX_WARPS));
-                if (c.n_sub == 9) W = 3;
             }
             const size_t smemf = (size_t)W * FUSED_NPART * 32 * 4;
             int occf = 1;
@@ -1185,6 +1185,12 @@ static int finish(RadopHandle *h)
     h->geo_poly_used = h->geo_poly_launched && !(flags[0] & 4);
     if (flags[0] & 1)
         return h->fail(RADOP_ERR_OUT_OF_DOMAIN, "radar domain is not entirely contained in the model domain");
+    if (flags[0] & 8)
+        // get_doppler_spectrum fills D[:, j] = np.linspace(d_min, d_max, nbins_D) with the per-gate limits of a
+        // melting species, arrays of shape (1,): the assignment raises ValueError (doppler_scatter.py:686-692)
+        return h->fail(RADOP_ERR_UNSUPPORTED, "could not broadcast input array from shape (1024,1) into shape (1024,): the Doppler "
+                                              "spectrum (scheme 3) of a gate that holds melting snow / graupel -- the reference "
+                                              "raises this ValueError in get_doppler_spectrum (doppler_scatter.py:686-692)");
     return RADOP_OK;
 }
 

@@ -1047,6 +1047,9 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const void *__
                     if (!(QMf > 0.f)) continue;
                     active |= (uint8_t)(1u << s);
                     if (wet) {
+                        // the reference cannot form the Doppler spectrum of a gate with a melting species
+                        // (ValueError in get_doppler_spectrum, doppler_scatter.py:686-692): report it
+                        if (cfg.doppler_scheme == 3) atomicOr(o.flags, 8);
                         // PSD and integrals per gate in k_integrate_melting; here only the table bin:
                         // lookup_line(e=..., wc=fwet), float64 arithmetic for the float64 fwet profile
                         const float fw = S.species == RADOP_SP_MS ? val[MELT_SLOT_FWS] : val[MELT_SLOT_FWG];

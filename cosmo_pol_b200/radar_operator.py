@@ -164,8 +164,6 @@ class RadarOperator(object):
             if c['microphysics']['scheme'] == '2mom':
                 # MeltingSnow / MeltingGraupel.set_psd(QN, QM), hydrometeors.py:1413-1415, 1458-1460
                 raise ValueError('Invalid parameters, cannot set psd')
-            if c['doppler']['scheme'] == 3:
-                raise NotImplementedError('Doppler scheme 3 (spectrum) with the melting scheme is not part of this build')
             h.extend(['mS', 'mG'])
         if c['microphysics']['scheme'] == '2mom':
             h.append('H')
