@@ -8,7 +8,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libradop.so')
+# RADOP_LIB: another build of the same sources (launch-shape experiments, scripts/build_variants.sh)
+LIB_PATH = os.environ.get('RADOP_LIB') or os.path.join(_HERE, 'libradop.so')
 
 RADOP_ABI_VERSION = 6
 NSPECIES_MAX = 7
@@ -18,6 +19,8 @@ OUT_NAMES = ['ZH', 'ZDR', 'ZV', 'KDP', 'DELTA_HV', 'PHIDP', 'RHOHV', 'ATT_H', 'A
 VAR_IDS = {'U': 0, 'V': 1, 'W': 2, 'T': 3, 'RHO': 4, 'QR_v': 5, 'QS_v': 6, 'QG_v': 7, 'QI_v': 8, 'QH_v': 9,
            'QNR_v': 10, 'QNS_v': 11, 'QNG_v': 12, 'QNI_v': 13, 'QNH_v': 14, 'EDR': 15}
 VAR_NAMES = {v: k for k, v in VAR_IDS.items()}
+# one-moment slots that carry the melting re-partition when with_melting is set (melting.py:74-90)
+MELT_VAR_SLOTS = {'QmS_v': 9, 'QmG_v': 10, 'fwet_mS': 11, 'fwet_mG': 12}
 SPECIES_IDS = {'R': 0, 'S': 1, 'G': 2, 'H': 3, 'I': 4, 'mS': 5, 'mG': 6}
 
 EXPORTS = ['radop_abi_version', 'radop_create', 'radop_destroy', 'radop_last_error', 'radop_set_params',
@@ -391,10 +394,10 @@ class Engine(object):
                 arrays[k] = a
                 setattr(out, k, a.ctypes.data)
         if want_model:
-            for name in self.uploaded_vars:
+            for name, slot in self.model_output_slots().items():
                 a = self._host_buffer(('model', name), shape, np.float32)
                 arrays[name] = a
-                out.model[VAR_IDS[name]] = a.ctypes.data
+                out.model[slot] = a.ctypes.data
         if self.params is not None and self.params.doppler_scheme == 3:
             a = self._host_buffer('dspectrum', shape + (self.n_vel,), np.float32)
             arrays['DSPECTRUM'] = a
@@ -404,6 +407,14 @@ class Engine(object):
     def _geometry_key(self, scan):
         p = self.params
         return (scan.geometry_key(), p.radar_lat, p.radar_lon, p.n_gates, scan.n_rays)
+
+    def model_output_slots(self):
+        """name -> slot of every variable integrate_radials returns (interpolation.py:36-89): the uploaded model
+        variables and, with the melting scheme, the re-partitioned masses and wet fractions."""
+        slots = {n: VAR_IDS[n] for n in self.uploaded_vars}
+        if self.params is not None and self.params.with_melting:
+            slots.update(MELT_VAR_SLOTS)
+        return slots
 
     def simulate(self, scan, want_latlon=True, want_model=False):
         """The reference-facing call: host in -> host out.  The gate positions (lat, lon: 16 of the 60 bytes

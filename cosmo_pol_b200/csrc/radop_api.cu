@@ -68,6 +68,10 @@ struct RadopHandle_ {
     double rot[9];
     uint32_t var_mask = 0;
     int z_strict = 0;
+    // bounds of the vertical differences (k_level_diff_bounds): z-level spacings and, per variable, |f[l+1] - f[l]|
+    float z_dmin = 0.f, z_dmax = 0.f;
+    bool z_dpos = false;
+    float var_nmax[RADOP_NVAR_MAX], var_nmin[RADOP_NVAR_MAX];
     DevBuf z_t, fields, stage, lev_guess;
     int search_mode = 0;         // 0: guessed window + bisection when it misses, 1: bisection always
     LutHost lut[RADOP_NSPECIES_MAX];   // indexed by RADOP_SP_*
@@ -265,6 +269,17 @@ int radop_upload_grid(RadopHandle *h, int nz, int ny, int nx, const float *zleve
         CU(h, cudaStreamSynchronize(h->stream));
         h->z_strict = bad ? 0 : 1;
     }
+    {   // spacings of vertically adjacent levels: the divisors of the vertical interpolation
+        unsigned init[4] = {0u, 0xffffffffu, 0u, 0u}, got[4];
+        CU(h, cudaMemcpyAsync(h->flags.p, init, 16, cudaMemcpyHostToDevice, h->stream));
+        k_level_diff_bounds<<<h->n_sm * 8, 256, 0, h->stream>>>(h->stage.as<float>(), nz, (size_t)ny * nx, 1, (unsigned *)h->flags.p);
+        CU(h, cudaGetLastError());
+        CU(h, cudaMemcpyAsync(got, h->flags.p, 16, cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));
+        memcpy(&h->z_dmax, &got[0], 4);
+        memcpy(&h->z_dmin, &got[1], 4);
+        h->z_dpos = got[2] == 0u && got[1] != 0xffffffffu;
+    }
     {   // level against normalised height for the column in the middle of the grid (first guess of the search)
         std::vector<uint8_t> g(RADOP_NGUESS, 0);
         const size_t cidx = (size_t)(ny / 2) * nx + nx / 2, plane = (size_t)ny * nx;
@@ -304,6 +319,18 @@ int radop_upload_field(RadopHandle *h, int var_id, const float *data)
     CU(h, cudaMemcpyAsync(h->stage.p, data, n * 4, cudaMemcpyHostToDevice, h->stream));
     k_pack_field<<<h->n_sm * 8, 256, 0, h->stream>>>(h->stage.as<float>(), h->fields.as<float>(), h->nz, h->ny, h->nx, var_id);
     CU(h, cudaGetLastError());
+    {   // vertical differences of the variable: the numerators of the vertical interpolation
+        unsigned init[4] = {0u, 0xffffffffu, 0u, 0u}, got[4];
+        CU(h, h->flags.reserve(16));
+        CU(h, cudaMemcpyAsync(h->flags.p, init, 16, cudaMemcpyHostToDevice, h->stream));
+        k_level_diff_bounds<<<h->n_sm * 8, 256, 0, h->stream>>>(h->stage.as<float>(), h->nz, (size_t)h->ny * h->nx, 0, (unsigned *)h->flags.p);
+        CU(h, cudaGetLastError());
+        CU(h, cudaMemcpyAsync(got, h->flags.p, 16, cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));
+        memcpy(&h->var_nmax[var_id], &got[0], 4);
+        if (got[1] == 0xffffffffu) h->var_nmin[var_id] = 1.0f;        // a constant field: every numerator is zero
+        else memcpy(&h->var_nmin[var_id], &got[1], 4);
+    }
     CU(h, cudaStreamSynchronize(h->stream));
     h->var_mask |= (1u << var_id);
     h->executed = false;
@@ -563,6 +590,17 @@ static int prepare(RadopHandle *h)
     memcpy(c.rot, h->rot, sizeof c.rot);
     c.var_mask = h->var_mask;
     c.z_strict = h->z_strict;
+    {   // Is every quotient n / den of the vertical interpolation inside the range where the shared reciprocal gives
+        // the IEEE quotient (div_den_safe, div_shared_rcp: 0.125 <= den <= 1e15, 1e-30 <= |q| <= 1e30 or n == 0)?
+        // den runs over the spacings of adjacent levels, n over the vertical differences of each uploaded variable.
+        bool ok = h->z_dpos && h->z_dmin >= 0.125f && h->z_dmax <= 1e15f;
+        for (int v = 0; ok && v < RADOP_NVAR_MAX; ++v)
+            if (h->var_mask & (1u << v)) {
+                const double nmax = h->var_nmax[v], nmin = h->var_nmin[v];
+                ok = std::isfinite(h->var_nmax[v]) && nmax / (double)h->z_dmin <= 1e29 && nmin / (double)h->z_dmax >= 1e-29;
+            }
+        c.div_exact = ok ? 1 : 0;
+    }
     c.lev_guess = (h->search_mode == 0 && h->nz >= 8 && h->nz <= 256) ? h->lev_guess.as<uint8_t>() : nullptr;
     c.n_species = p.n_species;
     c.two_moment = p.two_moment; c.doppler_scheme = p.doppler_scheme; c.with_attenuation = p.with_attenuation;
@@ -673,7 +711,8 @@ static int copy_outputs(RadopHandle *h, const RadopOut *out, int r0, int nr, cud
     }
     for (int v = 0; v < RADOP_NVAR_MAX; ++v)
         if (out->model[v]) {
-            if (!h->cfg.output_model_vars || !(h->var_mask & (1u << v))) return h->fail(RADOP_ERR_ARG, "model output requested but not computed");
+            if (!h->cfg.output_model_vars || !((h->var_mask | (h->cfg.with_melting ? 0x1E00u : 0u)) & (1u << v)))
+                return h->fail(RADOP_ERR_ARG, "model output requested but not computed");
             CU(h, cudaMemcpyAsync(out->model[v] + off, h->model_out.as<float>() + (size_t)v * n_rg + off, cnt * 4, cudaMemcpyDeviceToHost, st));
         }
     return RADOP_OK;
@@ -820,8 +859,10 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     static bool attr_done[64] = {false};
     if (!attr_done[h->device & 63]) {
         CU(h, cudaFuncSetAttribute(k_integrate, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        CU(h, cudaFuncSetAttribute(k_gate_fused<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
-        CU(h, cudaFuncSetAttribute(k_gate_fused<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
+        CU(h, cudaFuncSetAttribute(k_gate_fused<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
+        CU(h, cudaFuncSetAttribute(k_gate_fused<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
+        CU(h, cudaFuncSetAttribute(k_gate_fused<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
+        CU(h, cudaFuncSetAttribute(k_gate_fused<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
         CU(h, cudaFuncSetAttribute(k_interp_psd<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_interp_psd<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_scatter_pairs, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -950,13 +991,15 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
                 }
             }
             const size_t smemf = (size_t)W * FUSED_NPART * 32 * 4;
+            typedef void (*FusedKernel)(const DevConfig, const ScanDev, const float *, const float *, const FusedArgs);
+            const bool dop2 = c.doppler_scheme == 2;
+            FusedKernel fk = c.two_moment ? (dop2 ? (FusedKernel)k_gate_fused<true, true> : (FusedKernel)k_gate_fused<true, false>)
+                                          : (dop2 ? (FusedKernel)k_gate_fused<false, true> : (FusedKernel)k_gate_fused<false, false>);
             int occf = 1;
-            if (c.two_moment) CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, k_gate_fused<true>, 32 * W, smemf));
-            else CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, k_gate_fused<false>, 32 * W, smemf));
+            CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, fk, 32 * W, smemf));
             const long long pieces = (long long)nr * n_spans;
             const unsigned gridf = (unsigned)std::min<long long>(pieces, (long long)std::max(1, occf) * h->n_sm);
-            if (c.two_moment) k_gate_fused<true><<<gridf, 32 * W, smemf, st>>>(c, scan, h->z_t.as<float>(), h->fields.as<float>(), fa);
-            else k_gate_fused<false><<<gridf, 32 * W, smemf, st>>>(c, scan, h->z_t.as<float>(), h->fields.as<float>(), fa);
+            fk<<<gridf, 32 * W, smemf, st>>>(c, scan, h->z_t.as<float>(), h->fields.as<float>(), fa);
             CU(h, cudaGetLastError()); ++launches;
             if (ev) { CU(h, cudaEventRecord(ev[1], st)); CU(h, cudaEventRecord(ev[2], st)); CU(h, cudaEventRecord(ev[3], st)); }
             if (ice) {

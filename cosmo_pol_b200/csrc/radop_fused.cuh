@@ -22,7 +22,15 @@
 // Pieces are handed out from a global counter, so CTAs that start late (an NCCL kernel on their SM) take fewer.
 #pragma once
 
-#define FUSED_MAX_WARPS 10
+#ifndef FUSED_MAX_WARPS
+#define FUSED_MAX_WARPS 10    // warps per CTA (a build-time experiment knob together with FUSED_MIN_CTAS: registers per thread)
+#endif
+#ifndef FUSED_MIN_CTAS
+#define FUSED_MIN_CTAS 3
+#endif
+#ifndef FUSED_UNROLL_COLS
+#define FUSED_UNROLL_COLS 0   // 1: the four neighbour columns of the interpolation as straight-line code
+#endif
 #define FUSED_NPART 10        // b c p q kd s9 s11 | sum rv w | sum w | sum mask
 
 // constants of one species in the form the fused kernel wants them (filled by the host, prepare_fused())
@@ -72,7 +80,10 @@ __global__ void k_traj_tables(const __grid_constant__ DevConfig cfg, const float
 
 // the interpolation of interp_columns for the variables the radar observables need (RHO and EDR are read by
 // the Doppler spectrum and the model outputs only)
-template <bool EXACT, bool TWO_MOM>
+// MODE 0: shared-reciprocal quotients with per-quotient range checks (returns true when the gate must be redone with
+// IEEE divisions), 1: IEEE divisions, 2: shared-reciprocal quotients WITHOUT checks -- only when the upload-time bounds
+// (DevConfig.div_exact) guarantee that no quotient of this grid and these fields can leave the exact range.
+template <int MODE, bool TWO_MOM>
 __device__ __forceinline__ bool interp_fused(const DevConfig &cfg, const CellGeom &c, float h_g,
                                              const float *__restrict__ z_t, const float *__restrict__ fields,
                                              float (&val)[TWO_MOM ? 15 : 9])
@@ -81,7 +92,11 @@ __device__ __forceinline__ bool interp_fused(const DevConfig &cfg, const CellGeo
     bool rare = false;
 #pragma unroll
     for (int j = 0; j < NV; ++j) val[j] = -0.f;
+#if FUSED_UNROLL_COLS
+#pragma unroll
+#else
 #pragma unroll 1
+#endif
     for (int oi = 0; oi < 4; ++oi) {
         const int k = (oi == 1) ? 2 : (oi == 2 ? 1 : oi);        // accumulation order of the reference: 0, 2, 1, 3
         const int yk = (k & 2) ? c.y1 : c.y0, xk = (k & 1) ? c.x1 : c.x0;
@@ -89,8 +104,8 @@ __device__ __forceinline__ bool interp_fused(const DevConfig &cfg, const CellGeo
         const size_t cell = ((size_t)yk * cfg.nx + xk) * cfg.nz + lvl;
         const float c1 = __ldg(z_t + cell), c2 = __ldg(z_t + cell + 1);
         const float den = __fsub_rn(c1, c2), dh = __fsub_rn(h_g, c2);
-        const float rden = EXACT ? 0.f : __frcp_rn(den);
-        if (!EXACT) rare = rare || !div_den_safe(den);
+        const float rden = MODE == 1 ? 0.f : __frcp_rn(den);
+        if (MODE == 0) rare = rare || !div_den_safe(den);
         const float4 *f1 = reinterpret_cast<const float4 *>(fields + cell * RADOP_NVP);
         const float4 *f2 = f1 + RADOP_NVP / 4;
         const bool v_mid = (k == 1) || (k == 2);
@@ -99,13 +114,15 @@ __device__ __forceinline__ bool interp_fused(const DevConfig &cfg, const CellGeo
         auto accum = [&](int j, float a, float b) {
             const float n = __fsub_rn(b, a);
             float q;
-            if (EXACT) q = __fdiv_rn(n, den);
+            if (MODE == 1) q = __fdiv_rn(n, den);
             else {
                 const float q0 = __fmul_rn(n, rden);
                 const float r = __fmaf_rn(-den, q0, n);
                 q = __fmaf_rn(r, rden, q0);
-                const float aq = fabsf(q);
-                rare = rare || !(aq <= 1e30f) || (aq < 1e-30f && n != 0.f);
+                if (MODE == 0) {
+                    const float aq = fabsf(q);
+                    rare = rare || !(aq <= 1e30f) || (aq < 1e-30f && n != 0.f);
+                }
             }
             const float vv = __fsub_rn(b, __fmul_rn(q, dh));
             const float t0 = __fmul_rn(w0, vv);
@@ -148,17 +165,102 @@ __device__ __forceinline__ float pick_var(const float (&v)[NV], int var)
     return r;
 }
 
-// One species of one warp's 32 gates, from the PSD slope in the log domain (u = log2 lambda) to the seven
-// weighted column sums: the arithmetic of pair_tab without the trip through global memory.  vn: numeric
-// fall-speed moments (ice, Doppler scheme 1) or the rcs-weighted ones of scheme 2.  All 32 lanes must call.
-template <int NC>
+// One column of one piece of a lambda-transformed table (layout of k_build_lamtab): mantissa 2^{L(x)} R(x) of
+// F_k(lambda); the integer part of the exponent stays in the piece's exponent word.  The sign-mask test is hoisted
+// to the warp: a column whose ratio polynomial is the constant +-1 on the pieces of ALL 32 lanes (every column but
+// s10 - s8 in the smooth table family) costs no divergent branch.
+template <int NC, int K>
+__device__ __forceinline__ float lt_col(const float *__restrict__ base, float x, unsigned mask, unsigned all_const)
+{
+    const float2 *l = reinterpret_cast<const float2 *>(base + 6 * K);
+    const float2 l0 = __ldg(l), l1 = __ldg(l + 1), l2 = __ldg(l + 2);
+    float L = l2.y;
+    L = fmaf(L, x, l2.x);
+    L = fmaf(L, x, l1.y);
+    L = fmaf(L, x, l1.x);
+    L = fmaf(L, x, l0.y);
+    L = fmaf(L, x, l0.x);
+    // sign bit of the constant ratio moved onto the value: -1 where bit 16 + K of the mask word is set
+    float R = __int_as_float(0x3f800000 | ((mask << (15 - K)) & 0x80000000u));
+    if (!(all_const & (1u << K))) {               // warp-uniform
+        if (!(mask & (1u << K))) {
+            const float2 *r = reinterpret_cast<const float2 *>(base + 6 * NC + 6 * K);
+            const float2 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
+            R = r2.y;
+            R = fmaf(R, x, r2.x);
+            R = fmaf(R, x, r1.y);
+            R = fmaf(R, x, r1.x);
+            R = fmaf(R, x, r0.y);
+            R = fmaf(R, x, r0.x);
+        }
+    }
+    return ex2f_approx(L) * R;
+}
+
+// v * 2^e: one exact multiplication for the exponents the tables really hold (|e| <= 126), else the two-factor form
+__device__ __forceinline__ float scale2(float v, int e)
+{
+    if ((unsigned)(e + 126) > 252u) return lt_scale(v, e);
+    return v * __int_as_float((e << 23) + 0x3f800000);
+}
+
+// A pair the table cannot serve (slope outside the tabulated range, rejected piece): the sums over the diameters by the
+// whole warp (warp_direct), then the arithmetic of the table path with zero exponents.  out[0..6] columns, out[7..8]
+// the fall-speed moments.  Cold: a few hundred pairs of 2.7e7.
+template <int NC, bool DOP2>
+__device__ __noinline__ void pair_direct(const DevConfig &cfg, const SpeciesDev &S, int bl, float lam, float p1, float w,
+                                         int lane, float (&out)[9])
+{
+    float m[NC];
+    warp_direct<NC>(S, bl, lam, lane, m);
+    const int nd = S.nd;
+    out[7] = 0.f; out[8] = 0.f;
+    constexpr int C9 = NC > 9 ? 9 : 0, C8 = NC > 8 ? 8 : 0, C7 = NC > 7 ? 7 : 0;
+    if (S.mode == MODE_ICE1) {
+        const float inv9 = 1.f / m[C9];
+#pragma unroll
+        for (int c = 0; c < 7; ++c) out[c] = m[c] * inv9 * p1 * w;
+        if (!DOP2) { out[7] = m[C7] * inv9 * p1; out[8] = m[C8] * inv9 * p1; }
+        else {
+            const float *tab = S.table + (size_t)bl * nd * S.ncol;
+            const float D0 = __ldg(S.aux), DL = __ldg(S.aux + nd - 1);
+            const float c2 = 17.46f * exp2f(0.6357f * log2f(lam));
+            const float w0 = 490.6f * ex2f_approx(-20.78f * LOG2E * lam * D0) + c2 * __ldg(S.aux + 2 * nd) * ex2f_approx(-3.290f * LOG2E * lam * D0);
+            const float wL = 490.6f * ex2f_approx(-20.78f * LOG2E * lam * DL) + c2 * __ldg(S.aux + 3 * nd - 1) * ex2f_approx(-3.290f * LOG2E * lam * DL);
+            const float n_ = m[0] - 0.5f * (__ldg(tab) * w0 + __ldg(tab + (size_t)(nd - 1) * S.ncol) * wL);
+            const float v_ = m[C7] - 0.5f * (__ldg(tab + 7) * w0 + __ldg(tab + (size_t)(nd - 1) * S.ncol + 7) * wL);
+            const float sc = 6.283185307179586f * (p1 / m[C9]) / S.dD_ref;
+            out[7] = v_ * sc; out[8] = n_ * sc;
+        }
+        return;
+    }
+#pragma unroll
+    for (int c = 0; c < 7; ++c) out[c] = m[c] * (p1 * w);
+    if (S.mode == MODE_GEN12) { out[7] = m[C7] * p1; out[8] = m[C8] * p1; }
+    else if (DOP2) {
+        const float *tab = S.table + (size_t)bl * nd * S.ncol;
+        const float a = -LOG2E * lam;
+        float yF, yL;
+        if (S.mode == MODE_GEO8) { yF = __ldg(S.aux); yL = (float)((double)yF + (double)(nd - 1) * S.dD_d); }
+        else { yF = __ldg(S.aux + nd); yL = __ldg(S.aux + 2 * nd - 1); }
+        const float wF = ex2f_approx(a * yF), wL = ex2f_approx(a * yL);
+        const float n_ = m[0] - 0.5f * (__ldg(tab) * wF + __ldg(tab + (size_t)(nd - 1) * S.ncol) * wL);
+        const float v_ = m[C7] - 0.5f * (__ldg(tab + 7) * wF + __ldg(tab + (size_t)(nd - 1) * S.ncol + 7) * wL);
+        const float sc = 6.283185307179586f * p1 / S.dD_ref;
+        out[7] = v_ * sc; out[8] = n_ * sc;
+    }
+}
+
+// One species of one warp's 32 gates, from the PSD slope in the log domain (u = log2 lambda) to the seven weighted
+// column sums: the arithmetic of pair_tab without the trip through global memory, one column at a time so that no
+// array of mantissas and exponents has to stay in registers.  vn: numeric fall-speed moments (ice, Doppler scheme 1)
+// or the rcs-weighted ones of scheme 2.  All 32 lanes must call.
+template <int NC, bool DOP2>
 __device__ __forceinline__ void species_tab(const DevConfig &cfg, const FusedArgs &A, const SpeciesDev &S, bool have,
                                             int bl, double u, float p1, float w, int lane, float (&acc)[7], float2 &vn)
 {
     constexpr int STR = (12 * NC + ((NC + 1 + 3) & ~3) + 31) / 32 * 32;      // lt_stride(NC)
-    const int nd = S.nd;
-    float m[NC];
-    int ex[NC];
+    constexpr int C9 = NC > 9 ? 9 : 0, C8 = NC > 8 ? 8 : 0, C7 = NC > 7 ? 7 : 0;
     int piece = 0, why = 0;
     float x = 0.f;
     if (have) {
@@ -172,73 +274,98 @@ __device__ __forceinline__ void species_tab(const DevConfig &cfg, const FusedArg
             x = (float)(2.0 * (t - (double)piece) - 1.0);
         }
     }
-    const int id = (have && !why) ? bl * LT_NP + piece : -1;
-    lt_horner<NC>(S.lamtab + (size_t)(id >= 0 ? id : bl * LT_NP) * STR, x, m, ex);
-    if (id >= 0 && ex[0] == LT_BAD) why = 1;
-    unsigned need = __ballot_sync(0xffffffffu, why != 0);
-    if (why) atomicAdd(A.n_fallback + (why - 1), 1ull);
-    const float lam = need ? exp2f((float)u) : 0.f;
-    while (need) {
-        const int src = __ffs(need) - 1;
-        need &= need - 1;
-        const int bl_s = __shfl_sync(0xffffffffu, bl, src);
-        const float lam_s = __shfl_sync(0xffffffffu, lam, src);
-        float ds[NC];
-        warp_direct<NC>(S, bl_s, lam_s, lane, ds);
-        if (lane == src) {
+    // lanes without a servable pair read piece 0 of their bin (valid memory); their result is discarded
+    const float *base = S.lamtab + (size_t)(bl * LT_NP + piece) * STR;
+    const int *ew = reinterpret_cast<const int *>(base) + 12 * NC;        // NC exponent words, then the mask word
+    if (have && !why && __ldg(ew) == LT_BAD) why = 1;
+    const unsigned need = __ballot_sync(0xffffffffu, why != 0);
+    const bool tab = have && !why;
+    if (need) {
+        if (why) atomicAdd(A.n_fallback + (why - 1), 1ull);
+        const float lam = exp2f((float)u);
+        unsigned todo = need;
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            float out[9];
+            pair_direct<NC, DOP2>(cfg, S, __shfl_sync(0xffffffffu, bl, src), __shfl_sync(0xffffffffu, lam, src),
+                                  __shfl_sync(0xffffffffu, p1, src), w, lane, out);
+            if (lane == src) {
 #pragma unroll
-            for (int c = 0; c < NC; ++c) { m[c] = ds[c]; ex[c] = 0; }
+                for (int c = 0; c < 7; ++c) acc[c] += out[c];
+                vn = make_float2(out[7], out[8]);
+            }
         }
     }
-    if (!have) return;
+    const unsigned mask = (unsigned)__ldg(ew + NC);
+    const unsigned all_const = __reduce_and_sync(0xffffffffu, tab ? mask : 0xffffffffu);
+    if (!__any_sync(0xffffffffu, tab)) return;
+    float pre;
+    int e_off = 0;
     if (S.mode == MODE_ICE1) {
         // N0 renormalised so that the mass integral equals QM (hydrometeors.py:1330-1339): n0 = p1 / F_9
-        constexpr int C9 = NC > 9 ? 9 : 0, C8 = NC > 8 ? 8 : 0, C7 = NC > 7 ? 7 : 0;
-        const float inv9 = 1.f / m[C9];
-        const int e9 = ex[C9];
-#pragma unroll
-        for (int c = 0; c < 7; ++c) acc[c] += lt_scale(m[c] * inv9 * p1 * w, ex[c] - e9);
-        if (cfg.doppler_scheme == 2) {
-            const float lam1 = exp2f((float)u);
-            const float *tab = S.table + (size_t)bl * nd * S.ncol;
-            const float D0 = __ldg(S.aux), DL = __ldg(S.aux + nd - 1);
-            const float c2 = 17.46f * exp2f(0.6357f * log2f(lam1));
-            const float w0 = 490.6f * ex2f_approx(-20.78f * LOG2E * lam1 * D0) +
-                             c2 * __ldg(S.aux + 2 * nd) * ex2f_approx(-3.290f * LOG2E * lam1 * D0);
-            const float wL = 490.6f * ex2f_approx(-20.78f * LOG2E * lam1 * DL) +
-                             c2 * __ldg(S.aux + 3 * nd - 1) * ex2f_approx(-3.290f * LOG2E * lam1 * DL);
-            const float f0 = lt_scale(m[0], ex[0]), f7 = lt_scale(m[C7], ex[C7]);
-            const float n0 = p1 / lt_scale(m[C9], e9);
-            const float n_ = f0 - 0.5f * (__ldg(tab) * w0 + __ldg(tab + (size_t)(nd - 1) * S.ncol) * wL);
-            const float v_ = f7 - 0.5f * (__ldg(tab + 7) * w0 + __ldg(tab + (size_t)(nd - 1) * S.ncol + 7) * wL);
-            const float sc = 6.283185307179586f * n0 / S.dD_ref;
-            vn = make_float2(v_ * sc, n_ * sc);
-        } else {
-            vn = make_float2(lt_scale(m[C7] * inv9 * p1, ex[C7] - e9), lt_scale(m[C8] * inv9 * p1, ex[C8] - e9));
+        const float inv9 = 1.f / lt_col<NC, C9>(base, x, mask, all_const);
+        e_off = __ldg(ew + C9);
+        pre = inv9 * p1;
+        if (tab) {
+            if (!DOP2) {
+                vn = make_float2(scale2(lt_col<NC, C7>(base, x, mask, all_const) * pre, __ldg(ew + C7) - e_off),
+                                 scale2(lt_col<NC, C8>(base, x, mask, all_const) * pre, __ldg(ew + C8) - e_off));
+            } else {
+                const int nd = S.nd;
+                const float lam1 = exp2f((float)u);
+                const float *tb = S.table + (size_t)bl * nd * S.ncol;
+                const float D0 = __ldg(S.aux), DL = __ldg(S.aux + nd - 1);
+                const float c2 = 17.46f * exp2f(0.6357f * log2f(lam1));
+                const float w0 = 490.6f * ex2f_approx(-20.78f * LOG2E * lam1 * D0) +
+                                 c2 * __ldg(S.aux + 2 * nd) * ex2f_approx(-3.290f * LOG2E * lam1 * D0);
+                const float wL = 490.6f * ex2f_approx(-20.78f * LOG2E * lam1 * DL) +
+                                 c2 * __ldg(S.aux + 3 * nd - 1) * ex2f_approx(-3.290f * LOG2E * lam1 * DL);
+                const float f0 = lt_scale(lt_col<NC, 0>(base, x, mask, all_const), __ldg(ew));
+                const float f7 = lt_scale(lt_col<NC, C7>(base, x, mask, all_const), __ldg(ew + C7));
+                const float n0 = pre / lt_scale(1.f, e_off);
+                const float n_ = f0 - 0.5f * (__ldg(tb) * w0 + __ldg(tb + (size_t)(nd - 1) * S.ncol) * wL);
+                const float v_ = f7 - 0.5f * (__ldg(tb + 7) * w0 + __ldg(tb + (size_t)(nd - 1) * S.ncol + 7) * wL);
+                const float sc = 6.283185307179586f * n0 / S.dD_ref;
+                vn = make_float2(v_ * sc, n_ * sc);
+            }
         }
-        return;
+        pre *= w;
+    } else {
+        pre = p1 * w;
+        if (S.mode == MODE_GEN12) {
+            if (tab) vn = make_float2(scale2(lt_col<NC, C7>(base, x, mask, all_const) * p1, __ldg(ew + C7)),
+                                      scale2(lt_col<NC, C8>(base, x, mask, all_const) * p1, __ldg(ew + C8)));
+        } else if (DOP2 && NC == 8) {
+            // trapezoid end corrections of Doppler scheme 2 (doppler2_moments)
+            if (tab) {
+                const int nd = S.nd;
+                const float *tb = S.table + (size_t)bl * nd * S.ncol;
+                const float a = -LOG2E * exp2f((float)u);
+                float yF, yL;
+                if (S.mode == MODE_GEO8) { yF = __ldg(S.aux); yL = (float)((double)yF + (double)(nd - 1) * S.dD_d); }
+                else { yF = __ldg(S.aux + nd); yL = __ldg(S.aux + 2 * nd - 1); }
+                const float wF = ex2f_approx(a * yF), wL = ex2f_approx(a * yL);
+                const float f0 = lt_scale(lt_col<NC, 0>(base, x, mask, all_const), __ldg(ew));
+                const float f7 = lt_scale(lt_col<NC, C7>(base, x, mask, all_const), __ldg(ew + C7));
+                const float n_ = f0 - 0.5f * (__ldg(tb) * wF + __ldg(tb + (size_t)(nd - 1) * S.ncol) * wL);
+                const float v_ = f7 - 0.5f * (__ldg(tb + 7) * wF + __ldg(tb + (size_t)(nd - 1) * S.ncol + 7) * wL);
+                const float sc = 6.283185307179586f * p1 / S.dD_ref;
+                vn = make_float2(v_ * sc, n_ * sc);
+            }
+        }
     }
-    const float pre = p1 * w;
-#pragma unroll
-    for (int c = 0; c < 7; ++c) acc[c] += lt_scale(m[c] * pre, ex[c]);
-    if (S.mode == MODE_GEN12) {
-        constexpr int C8 = NC > 8 ? 8 : 0, C7 = NC > 7 ? 7 : 0;
-        vn = make_float2(lt_scale(m[C7] * p1, ex[C7]), lt_scale(m[C8] * p1, ex[C8]));
-    } else if (NC == 8) {
-        // trapezoid end corrections of Doppler scheme 2 (doppler2_moments)
-        constexpr int C7 = NC > 7 ? 7 : 0;
-        const float *tab = S.table + (size_t)bl * nd * S.ncol;
-        const float a = -LOG2E * exp2f((float)u);
-        float yF, yL;
-        if (S.mode == MODE_GEO8) { yF = __ldg(S.aux); yL = (float)((double)yF + (double)(nd - 1) * S.dD_d); }
-        else { yF = __ldg(S.aux + nd); yL = __ldg(S.aux + 2 * nd - 1); }
-        const float wF = ex2f_approx(a * yF), wL = ex2f_approx(a * yL);
-        const float f0 = lt_scale(m[0], ex[0]), f7 = lt_scale(m[C7], ex[C7]);
-        const float n_ = f0 - 0.5f * (__ldg(tab) * wF + __ldg(tab + (size_t)(nd - 1) * S.ncol) * wL);
-        const float v_ = f7 - 0.5f * (__ldg(tab + 7) * wF + __ldg(tab + (size_t)(nd - 1) * S.ncol + 7) * wL);
-        const float sc = 6.283185307179586f * p1 / S.dD_ref;
-        vn = make_float2(v_ * sc, n_ * sc);
-    }
+    if (!tab) pre = 0.f;          // lanes without a table pair add exact zeros
+    // the seven columns of get_pol_from_sz, one at a time
+    const int4 e03 = __ldg(reinterpret_cast<const int4 *>(ew));
+    const int4 e47 = __ldg(reinterpret_cast<const int4 *>(ew) + 1);
+    acc[0] += tab ? scale2(lt_col<NC, 0>(base, x, mask, all_const) * pre, e03.x - e_off) : 0.f;
+    acc[1] += tab ? scale2(lt_col<NC, 1>(base, x, mask, all_const) * pre, e03.y - e_off) : 0.f;
+    acc[2] += tab ? scale2(lt_col<NC, 2>(base, x, mask, all_const) * pre, e03.z - e_off) : 0.f;
+    acc[3] += tab ? scale2(lt_col<NC, 3>(base, x, mask, all_const) * pre, e03.w - e_off) : 0.f;
+    acc[4] += tab ? scale2(lt_col<NC, 4>(base, x, mask, all_const) * pre, e47.x - e_off) : 0.f;
+    acc[5] += tab ? scale2(lt_col<NC, 5>(base, x, mask, all_const) * pre, e47.y - e_off) : 0.f;
+    acc[6] += tab ? scale2(lt_col<NC, 6>(base, x, mask, all_const) * pre, e47.z - e_off) : 0.f;
 }
 
 // log2 of a positive float32 as a float64: exponent + log2 of the mantissa (MUFU.LG2 on [1, 2): absolute error 2^-22)
@@ -262,15 +389,15 @@ __device__ __forceinline__ float exp2_split(double t)
     return lt_scale(ex2f_approx((float)(t - ip)), (int)fmax(-300.0, fmin(300.0, ip)));
 }
 
-template <bool TWO_MOM>
-__global__ void __launch_bounds__(32 * FUSED_MAX_WARPS, 3)
+template <bool TWO_MOM, bool DOP2>
+__global__ void __launch_bounds__(32 * FUSED_MAX_WARPS, FUSED_MIN_CTAS)
 k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const float *__restrict__ z_t,
              const float *__restrict__ fields, const __grid_constant__ FusedArgs A)
 {
     constexpr int NV = TWO_MOM ? 15 : 9;
     extern __shared__ float s_part_raw[];                  // [W][FUSED_NPART][32]
     float (*s_part)[FUSED_NPART][32] = reinterpret_cast<float (*)[FUSED_NPART][32]>(s_part_raw);
-    __shared__ int s_piece;
+    __shared__ int s_piece[2];
     __shared__ unsigned s_pairs[RADOP_NSPECIES_MAX];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, W = blockDim.x >> 5;
     const int ng = cfg.n_gates, n_sub = cfg.n_sub, n_spans = A.n_spans;
@@ -279,11 +406,15 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
     if (threadIdx.x < RADOP_NSPECIES_MAX) s_pairs[threadIdx.x] = 0u;
 
     for (;;) {
-        if (threadIdx.x == 0) s_piece = atomicAdd(A.flags + 3, 1);
+        if (threadIdx.x == 0) {
+            const int pc = atomicAdd(A.flags + 3, 1);
+            const int r = pc / n_spans;
+            s_piece[0] = pc < n_pieces ? r : -1;
+            s_piece[1] = pc - r * n_spans;
+        }
         __syncthreads();
-        const int piece = s_piece;
-        if (piece >= n_pieces) break;
-        const int ray = piece / n_spans, span = piece - ray * n_spans;
+        const int ray = s_piece[0], span = s_piece[1];
+        if (ray < 0) break;
         const int g = span * 32 + lane;
         const bool in_range = g < ng;
 
@@ -321,8 +452,9 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
             const bool live = in_range && c.status == 0;
             float val[NV];
             if (live) {
-                if (interp_fused<false, TWO_MOM>(cfg, c, h_g, z_t, fields, val))
-                    interp_fused<true, TWO_MOM>(cfg, c, h_g, z_t, fields, val);
+                if (cfg.div_exact) interp_fused<2, TWO_MOM>(cfg, c, h_g, z_t, fields, val);
+                else if (interp_fused<0, TWO_MOM>(cfg, c, h_g, z_t, fields, val))
+                    interp_fused<1, TWO_MOM>(cfg, c, h_g, z_t, fields, val);
             } else {
 #pragma unroll
                 for (int j = 0; j < NV; ++j) val[j] = 0.f;
@@ -332,8 +464,9 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
             float wind = qnan, sinth = 0.f;
             if (live) {
                 const float2 sc = __ldg(A.traj_sc + trow);
-                wind = (float)(((double)val[RADOP_VAR_U] * az.x + (double)val[RADOP_VAR_V] * az.y) * (double)sc.y +
-                               (double)val[RADOP_VAR_W] * (double)sc.x);
+                // float32 products of float32 winds: the rounding (1e-7 of 50 m/s) is far below the spread of the
+                // float32 sums over the sub-beams that follow
+                wind = fmaf(fmaf(val[RADOP_VAR_U], (float)az.x, val[RADOP_VAR_V] * (float)az.y), sc.y, val[RADOP_VAR_W] * sc.x);
                 sinth = sc.x;
             }
             // --- species: PSD slope in the log domain, table bin, table evaluation, sums over the species ---
@@ -366,7 +499,7 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
                         u = loglam * 1.4426950408889634;
                         n0 = (float)dn0;
                         p1 = n0;
-                        if (cfg.doppler_scheme == 1 && !S.numeric_vn) {
+                        if (!DOP2 && !S.numeric_vn) {
                             vs += (float)(S.c_v * dn0 * exp(S.e_v * loglam));
                             ns += (float)QN;
                         }
@@ -398,7 +531,7 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
                             u = F.uk * (l2q2 - lq) - 9.965784284662087;          // lambda / 1000
                             p1 = QMf;
                         }
-                        if (cfg.doppler_scheme == 1 && !S.numeric_vn) {
+                        if (!DOP2 && !S.numeric_vn) {
                             // _Hydrometeor.integrate_V, hydrometeors.py:178-199
                             const float fu = (float)u;
                             vs += F.cv * n0 * ex2f_approx(F.ev * fu);
@@ -410,14 +543,13 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
                     bl = ie * S.nt + it;
                 }
                 float2 vn = make_float2(0.f, 0.f);
-                switch (S.lt_nc) {
-                case 7: species_tab<7>(cfg, A, S, have, bl, u, p1, wq, lane, acc, vn); break;
-                case 8: species_tab<8>(cfg, A, S, have, bl, u, p1, wq, lane, acc, vn); break;
-                case 9: species_tab<9>(cfg, A, S, have, bl, u, p1, wq, lane, acc, vn); break;
-                default: species_tab<10>(cfg, A, S, have, bl, u, p1, wq, lane, acc, vn); break;
-                }
+                // columns tabulated (lt_columns): 7 (8 with the rcs-weighted fall speed of Doppler scheme 2), 10 for 1-mom
+                // ice, 9 for a species with numeric fall-speed moments in scheme 1
+                constexpr int NC_A = DOP2 ? 8 : 7, NC_B = (TWO_MOM && !DOP2) ? 9 : 10;
+                if (S.lt_nc == NC_A) species_tab<NC_A, DOP2>(cfg, A, S, have, bl, u, p1, wq, lane, acc, vn);
+                else species_tab<NC_B, DOP2>(cfg, A, S, have, bl, u, p1, wq, lane, acc, vn);
                 if (have) {
-                    if (cfg.doppler_scheme == 2) { vs += vn.x; ns += vn.y; }
+                    if (DOP2) { vs += vn.x; ns += vn.y; }
                     else if (s == cfg.ice_numeric) { ice_here = true; ice_vn = vn; }
                 }
             }

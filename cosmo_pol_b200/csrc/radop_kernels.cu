@@ -90,6 +90,38 @@ __global__ void k_pack_field(const float *__restrict__ src, float *__restrict__ 
     }
 }
 
+// Bounds of the vertical differences of one array [nz][ny][nx] (float32 a[l+1] - a[l], the numerators / divisors of the
+// reference's vertical interpolation, interpolation_c.c:84-91, which always pairs vertically adjacent levels):
+// out[0] = largest |difference| as a bit pattern (NaN / inf compare above every finite value), out[1] = smallest
+// non-zero one, out[2] = 1 if some difference is <= 0 (only meaningful for the z-levels, where the kernel
+// subtracts the other way round).  From these the host decides, once per upload, whether EVERY quotient the
+// interpolation can ever form takes the shared-reciprocal path exactly (div_shared_rcp), so that the per-gate
+// kernels need no per-quotient range checks.
+__global__ void k_level_diff_bounds(const float *__restrict__ src, int nz, size_t plane, int descending, unsigned *out)
+{
+    unsigned hi = 0u, lo = 0xffffffffu, bad = 0u;
+    const size_t n = (size_t)(nz - 1) * plane;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float a = src[i], b = src[i + plane];
+        const float d = descending ? __fsub_rn(a, b) : __fsub_rn(b, a);
+        const unsigned u = __float_as_uint(d) & 0x7fffffffu;
+        hi = max(hi, u);
+        if (u) lo = min(lo, u);
+        if (descending && !(d > 0.f)) bad = 1u;
+    }
+#pragma unroll
+    for (int k = 16; k > 0; k >>= 1) {
+        hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, k));
+        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, k));
+        bad |= __shfl_xor_sync(0xffffffffu, bad, k);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMax(out, hi);
+        atomicMin(out + 1, lo);
+        if (bad) atomicOr(out + 2, 1u);
+    }
+}
+
 // LUT value_table [ne][nt][nd][12] float64 -> combined float32 [ne][nt][nd][ncol]
 // columns: 0: b = s0-s1-s2+s3   1: c = s0+s1+s2+s3   2: p = s4+s7   3: q = s6-s5
 //          4: kd = s10-s8       5: s9                6: s11         7: spare
@@ -2437,7 +2469,9 @@ k_reduce_subbeams(const __grid_constant__ DevConfig cfg, K3Args A)
     if (A.model_out) {
 #pragma unroll
         for (int v = 0; v < RADOP_NVP; ++v)
-            if (cfg.var_mask & (1u << v)) A.model_out[(size_t)v * cfg.out_stride + idx] = mv[v];
+            // with the melting scheme the one-moment slots 9..12 carry QmS_v, QmG_v, fwet_mS, fwet_mG (melting.py:74-90),
+            // which integrate_radials averages like every other entry of the sub-radials' value dictionary
+            if ((cfg.var_mask | (cfg.with_melting ? 0x1E00u : 0u)) & (1u << v)) A.model_out[(size_t)v * cfg.out_stride + idx] = mv[v];
     }
 }
 

@@ -70,6 +70,8 @@ struct DevConfig {
     int n_species, total_bins;
     int two_moment, doppler_scheme, with_attenuation, sensitivity_mode;
     int z_strict;               // every z-level column is strictly descending (fast column search)
+    int div_exact;              // 1: every quotient of the vertical interpolation of this grid and these fields takes the
+                                // shared-reciprocal path exactly (bounds taken at upload, k_level_diff_bounds): no range checks
     const uint8_t *lev_guess;   // [1024] level of a reference column against the normalised height, or null
     int output_model_vars, keep_debug, ice_numeric;   // ice_numeric: species index with numeric v,n or -1
     float wavelength, k_squared, radial_res;

@@ -14,7 +14,7 @@ import os
 import numpy as np
 
 from . import parallel
-from ._abi import Engine, Scan, OUT_NAMES, VAR_IDS
+from ._abi import Engine, Scan, OUT_NAMES, VAR_IDS, MELT_VAR_SLOTS
 from .config import cfg
 from .constants import global_constants as constants
 from .hydrometeors import create_hydrometeor
@@ -423,8 +423,8 @@ class RadarOperator(object):
         if want_model:
             mv = gathered(BUF_MODEL, len(VAR_IDS), ng)
             if receives:
-                for n in eng.uploaded_vars:
-                    out[n] = mv[VAR_IDS[n]]
+                for n, slot in eng.model_output_slots().items():
+                    out[n] = mv[slot]
         if not receives:
             return None
         full_scan = self.build_scan(ray_az, ray_el)
@@ -437,7 +437,7 @@ class RadarOperator(object):
         if self.output_variables in ('all', 'only_radar'):
             names += OUT_NAMES
         if self.output_variables in ('all', 'only_model'):
-            names += [n for n in VAR_IDS if n in out]
+            names += [n for n in list(VAR_IDS) + list(MELT_VAR_SLOTS) if n in out]
         shp = (n_sweeps, n_per, -1)
         fields = {n: out[n].reshape(shp) for n in names}
         if 'DSPECTRUM' in out and self.output_variables in ('all', 'only_radar'):
@@ -504,7 +504,7 @@ class RadarOperator(object):
                         np.array(arrays['lat'][0]), np.array(arrays['lon'][0]), dist_c, h_c)
         model = None
         if self.output_variables in ('all', 'only_model'):
-            model = Radial({n: np.array(arrays[n][0]) for n in eng.uploaded_vars}, np.array(arrays['mask'][0]),
+            model = Radial({n: np.array(arrays[n][0]) for n in eng.model_output_slots()}, np.array(arrays['mask'][0]),
                            np.array(arrays['lat'][0]), np.array(arrays['lon'][0]), dist_c, h_c)
         for q in range(fan.n_sub):
             vals = {n: dbg['values'][0, q, :, i] for i, n in enumerate(dbg['var_names'])}

@@ -167,7 +167,8 @@ typedef struct {
     float *obs[RADOP_N_OUT];
     float *mask;                      /* averaged sub-beam mask, doppler_scatter.py:472-477 */
     double *lat, *lon;                /* central sub-beam gate positions (WGS84)           */
-    float *model[RADOP_NVAR_MAX];     /* integrate_radials of each uploaded variable       */
+    float *model[RADOP_NVAR_MAX];     /* integrate_radials of each uploaded variable; with with_melting (one-moment
+                                         scheme) the slots 9..12 hold QmS_v, QmG_v, fwet_mS, fwet_mG (melting.py:74-90) */
     float *dspectrum;                 /* [n_rays][n_gates][n_vel] DSPECTRUM (Doppler scheme 3) */
 } RadopOut;
 
