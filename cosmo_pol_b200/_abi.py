@@ -16,7 +16,7 @@ NSPECIES_MAX = 7
 NVAR_MAX = 16
 N_OUT = 10
 OUT_NAMES = ['ZH', 'ZDR', 'ZV', 'KDP', 'DELTA_HV', 'PHIDP', 'RHOHV', 'ATT_H', 'ATT_V', 'RVEL']
-VAR_IDS = {'U': 0, 'V': 1, 'W': 2, 'T': 3, 'RHO': 4, 'QR_v': 5, 'QS_v': 6, 'QG_v': 7, 'QI_v': 8, 'QH_v': 9,
+VAR_IDS = {'U': 0, 'V': 1, 'W': 2, 'T': 3, 'QR_v': 4, 'QS_v': 5, 'QG_v': 6, 'QI_v': 7, 'RHO': 8, 'QH_v': 9,
            'QNR_v': 10, 'QNS_v': 11, 'QNG_v': 12, 'QNI_v': 13, 'QNH_v': 14, 'EDR': 15}
 VAR_NAMES = {v: k for k, v in VAR_IDS.items()}
 # one-moment slots that carry the melting re-partition when with_melting is set (melting.py:74-90)

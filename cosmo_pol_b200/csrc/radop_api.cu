@@ -990,7 +990,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
                     }
                 }
             }
-            const size_t smemf = (size_t)W * FUSED_NPART * 32 * 4;
+            const size_t smemf = (size_t)(FUSED_NOBARRIER ? 2 : 1) * W * FUSED_NPART * 32 * 4;
             typedef void (*FusedKernel)(const DevConfig, const ScanDev, const float *, const float *, const FusedArgs);
             const bool dop2 = c.doppler_scheme == 2;
             FusedKernel fk = c.two_moment ? (dop2 ? (FusedKernel)k_gate_fused<true, true> : (FusedKernel)k_gate_fused<true, false>)

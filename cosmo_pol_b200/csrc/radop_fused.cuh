@@ -28,6 +28,9 @@
 #ifndef FUSED_MIN_CTAS
 #define FUSED_MIN_CTAS 3
 #endif
+#ifndef FUSED_NOBARRIER
+#define FUSED_NOBARRIER 1     // 1: the warps of a CTA hand their rows over through shared-memory flags (no CTA-wide barrier)
+#endif
 #ifndef FUSED_UNROLL_COLS
 #define FUSED_UNROLL_COLS 0   // 1: the four neighbour columns of the interpolation as straight-line code
 #endif
@@ -79,16 +82,16 @@ __global__ void k_traj_tables(const __grid_constant__ DevConfig cfg, const float
 }
 
 // the interpolation of interp_columns for the variables the radar observables need (RHO and EDR are read by
-// the Doppler spectrum and the model outputs only)
+// the Doppler spectrum and the model outputs only): slots 0..7 = U V W T QR QS QG QI, two 16-byte loads per level
 // MODE 0: shared-reciprocal quotients with per-quotient range checks (returns true when the gate must be redone with
 // IEEE divisions), 1: IEEE divisions, 2: shared-reciprocal quotients WITHOUT checks -- only when the upload-time bounds
 // (DevConfig.div_exact) guarantee that no quotient of this grid and these fields can leave the exact range.
 template <int MODE, bool TWO_MOM>
 __device__ __forceinline__ bool interp_fused(const DevConfig &cfg, const CellGeom &c, float h_g,
                                              const float *__restrict__ z_t, const float *__restrict__ fields,
-                                             float (&val)[TWO_MOM ? 15 : 9])
+                                             float (&val)[TWO_MOM ? 15 : 8])
 {
-    constexpr int NV = TWO_MOM ? 15 : 9;
+    constexpr int NV = TWO_MOM ? 15 : 8;
     bool rare = false;
 #pragma unroll
     for (int j = 0; j < NV; ++j) val[j] = -0.f;
@@ -133,15 +136,13 @@ __device__ __forceinline__ bool interp_fused(const DevConfig &cfg, const CellGeo
             accum(0, a.x, b.x); accum(1, a.y, b.y); accum(2, a.z, b.z); accum(3, a.w, b.w);
         }
         {
-            const float4 a = __ldg(f1 + 1), b = __ldg(f2 + 1);       // RHO (slot 4) is not needed
-            accum(5, a.y, b.y); accum(6, a.z, b.z); accum(7, a.w, b.w);
+            const float4 a = __ldg(f1 + 1), b = __ldg(f2 + 1);
+            accum(4, a.x, b.x); accum(5, a.y, b.y); accum(6, a.z, b.z); accum(7, a.w, b.w);
         }
-        if (TWO_MOM) {
+        if (TWO_MOM) {               // slot 8 (RHO) and slot 15 (EDR) are not needed
             const float4 a = __ldg(f1 + 2), b = __ldg(f2 + 2), a3 = __ldg(f1 + 3), b3 = __ldg(f2 + 3);
-            accum(8, a.x, b.x); accum(9, a.y, b.y); accum(10, a.z, b.z); accum(11, a.w, b.w);
+            accum(9, a.y, b.y); accum(10, a.z, b.z); accum(11, a.w, b.w);
             accum(12, a3.x, b3.x); accum(13, a3.y, b3.y); accum(14, a3.z, b3.z);
-        } else {
-            accum(8, __ldg(reinterpret_cast<const float *>(f1) + 8), __ldg(reinterpret_cast<const float *>(f2) + 8));
         }
     }
     return rare;
@@ -154,13 +155,13 @@ __device__ __forceinline__ float pick_var(const float (&v)[NV], int var)
     if (var == RADOP_VAR_QS) r = v[RADOP_VAR_QS];
     if (var == RADOP_VAR_QG) r = v[RADOP_VAR_QG];
     if (var == RADOP_VAR_QI) r = v[RADOP_VAR_QI];
-    if (NV > 9) {
-        if (var == RADOP_VAR_QH) r = v[NV > 9 ? RADOP_VAR_QH : 0];
-        if (var == RADOP_VAR_QNR) r = v[NV > 9 ? RADOP_VAR_QNR : 0];
-        if (var == RADOP_VAR_QNS) r = v[NV > 9 ? RADOP_VAR_QNS : 0];
-        if (var == RADOP_VAR_QNG) r = v[NV > 9 ? RADOP_VAR_QNG : 0];
-        if (var == RADOP_VAR_QNI) r = v[NV > 9 ? RADOP_VAR_QNI : 0];
-        if (var == RADOP_VAR_QNH) r = v[NV > 9 ? RADOP_VAR_QNH : 0];
+    if (NV > 8) {
+        if (var == RADOP_VAR_QH) r = v[NV > 8 ? RADOP_VAR_QH : 0];
+        if (var == RADOP_VAR_QNR) r = v[NV > 8 ? RADOP_VAR_QNR : 0];
+        if (var == RADOP_VAR_QNS) r = v[NV > 8 ? RADOP_VAR_QNS : 0];
+        if (var == RADOP_VAR_QNG) r = v[NV > 8 ? RADOP_VAR_QNG : 0];
+        if (var == RADOP_VAR_QNI) r = v[NV > 8 ? RADOP_VAR_QNI : 0];
+        if (var == RADOP_VAR_QNH) r = v[NV > 8 ? RADOP_VAR_QNH : 0];
     }
     return r;
 }
@@ -394,18 +395,54 @@ __global__ void __launch_bounds__(32 * FUSED_MAX_WARPS, FUSED_MIN_CTAS)
 k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const float *__restrict__ z_t,
              const float *__restrict__ fields, const __grid_constant__ FusedArgs A)
 {
-    constexpr int NV = TWO_MOM ? 15 : 9;
-    extern __shared__ float s_part_raw[];                  // [W][FUSED_NPART][32]
-    float (*s_part)[FUSED_NPART][32] = reinterpret_cast<float (*)[FUSED_NPART][32]>(s_part_raw);
+    constexpr int NV = TWO_MOM ? 15 : 8;
+    extern __shared__ float s_part_raw[];                  // [2][W][FUSED_NPART][32] (one buffer with the CTA barrier)
     __shared__ int s_piece[2];
+#if FUSED_NOBARRIER
+    // Hand-over of the rows without a CTA-wide barrier.  The k-th piece of this CTA uses row buffer k & 1.
+    //   s_pid[k & 3] / s_seq[k & 3]: id of the k-th piece, published by warp 0 one piece ahead (a ring of four: the
+    //   slowest warp is at most two pieces behind warp 0);
+    //   s_cnt[b]: rows written into buffer b so far (all pieces); s_red[b]: last k whose buffer b has been reduced.
+    // A warp may run one piece ahead of the reduction; the reducing warp rotates with k.
+    __shared__ volatile int s_pid[4], s_seq[4], s_cnt[2], s_red[2];
+#endif
     __shared__ unsigned s_pairs[RADOP_NSPECIES_MAX];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, W = blockDim.x >> 5;
     const int ng = cfg.n_gates, n_sub = cfg.n_sub, n_spans = A.n_spans;
     const int n_pieces = cfg.n_rays * n_spans;
     const float qnan = __int_as_float(0x7fc00000);
     if (threadIdx.x < RADOP_NSPECIES_MAX) s_pairs[threadIdx.x] = 0u;
+#if FUSED_NOBARRIER
+    const int n_work = min(W, n_sub);                      // warps that own sub-beams
+    if (threadIdx.x == 0) {
+        s_pid[0] = atomicAdd(A.flags + 3, 1);
+        s_seq[0] = 0; s_seq[1] = -1; s_seq[2] = -1; s_seq[3] = -1;
+        s_cnt[0] = 0; s_cnt[1] = 0;
+        s_red[0] = -2; s_red[1] = -1;
+    }
+    __syncthreads();
+    (void)s_piece;
+#endif
 
-    for (;;) {
+    for (int k = 0;; ++k) {
+#if FUSED_NOBARRIER
+        const int buf = k & 1;
+        float (*s_part)[FUSED_NPART][32] = reinterpret_cast<float (*)[FUSED_NPART][32]>(s_part_raw) + (size_t)buf * W;
+        if (lane == 0) while (s_seq[k & 3] != k) __nanosleep(20);
+        __syncwarp();
+        const int pc = s_pid[k & 3];
+        if (pc >= n_pieces) break;
+        if (threadIdx.x == 0) {                 // the next piece, one ahead (that slot was last read for piece k - 3)
+            const int nxt = atomicAdd(A.flags + 3, 1);
+            s_pid[(k + 1) & 3] = nxt;
+            __threadfence_block();
+            s_seq[(k + 1) & 3] = k + 1;
+        }
+        const int ray = pc / n_spans, span = pc - ray * n_spans;
+        if (lane == 0) while (s_red[buf] != k - 2) __nanosleep(20);     // buffer free: piece k - 2 has been reduced
+        __syncwarp();
+#else
+        float (*s_part)[FUSED_NPART][32] = reinterpret_cast<float (*)[FUSED_NPART][32]>(s_part_raw);
         if (threadIdx.x == 0) {
             const int pc = atomicAdd(A.flags + 3, 1);
             const int r = pc / n_spans;
@@ -415,6 +452,7 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
         __syncthreads();
         const int ray = s_piece[0], span = s_piece[1];
         if (ray < 0) break;
+#endif
         const int g = span * 32 + lane;
         const bool in_range = g < ng;
 
@@ -591,8 +629,23 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
                 }
             }
         }
+#if FUSED_NOBARRIER
+        const int reducer = k % n_work;
+        if (warp < n_work) {
+            __threadfence_block();
+            __syncwarp();
+            if (lane == 0) atomicAdd((int *)&s_cnt[buf], 1);
+        }
+        if (warp == reducer) {
+            if (lane == 0) while (s_cnt[buf] != n_work * (k / 2 + 1)) __nanosleep(20);
+            __syncwarp();
+            __threadfence_block();
+        }
+        if (warp == reducer && in_range) {
+#else
         __syncthreads();
         if (warp == 0 && in_range) {
+#endif
             float t[FUSED_NPART];
 #pragma unroll
             for (int i = 0; i < FUSED_NPART; ++i) t[i] = s_part[0][i][lane];
@@ -609,6 +662,13 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
             if (mk > -1.f && mk <= 0.f) mk = 0.f;
             A.mask_out[rg] = mk;
         }
+#if FUSED_NOBARRIER
+        if (warp == reducer) {
+            __syncwarp();
+            __threadfence_block();
+            if (lane == 0) s_red[buf] = k;
+        }
+#endif
     }
     __syncthreads();
     if (threadIdx.x < cfg.n_species && s_pairs[threadIdx.x]) atomicAdd(A.n_pairs + threadIdx.x, (unsigned long long)s_pairs[threadIdx.x]);

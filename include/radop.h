@@ -51,8 +51,10 @@ enum {
 
 /* ---- model variables (cosmo_pol/radar_operator.py:35-36) ------------------ */
 enum {
-    RADOP_VAR_U = 0, RADOP_VAR_V, RADOP_VAR_W, RADOP_VAR_T, RADOP_VAR_RHO,
-    RADOP_VAR_QR, RADOP_VAR_QS, RADOP_VAR_QG, RADOP_VAR_QI,          /* 9 one-moment vars */
+    /* ids = slots of the interleaved field layout: the eight variables the radar observables of the one-moment
+       scheme need come first, so that one (cell, level) of them is two 16-byte loads */
+    RADOP_VAR_U = 0, RADOP_VAR_V, RADOP_VAR_W, RADOP_VAR_T,
+    RADOP_VAR_QR, RADOP_VAR_QS, RADOP_VAR_QG, RADOP_VAR_QI, RADOP_VAR_RHO,          /* 9 one-moment vars */
     RADOP_VAR_QH, RADOP_VAR_QNR, RADOP_VAR_QNS, RADOP_VAR_QNG, RADOP_VAR_QNI, RADOP_VAR_QNH,
     RADOP_VAR_EDR,               /* eddy dissipation rate, radar_operator.py:253-254 (turbulence broadening) */
     RADOP_NVAR_MAX = 16
