@@ -64,7 +64,7 @@ class RadopScan(C.Structure):
                 ('ray_az', C.c_void_p), ('ray_traj', C.c_void_p), ('ray_nyquist', C.c_void_p),
                 ('sub_daz', C.c_void_p), ('sub_jv', C.c_void_p), ('sub_weight', C.c_void_p),
                 ('traj_s', C.c_void_p), ('traj_h', C.c_void_p), ('traj_e', C.c_void_p),
-                ('traj_sin', C.c_void_p), ('traj_tan', C.c_void_p)]
+                ('traj_sin', C.c_void_p), ('traj_tan', C.c_void_p), ('sub_ml_only', C.c_void_p)]
 
 
 class RadopOut(C.Structure):
@@ -170,6 +170,8 @@ class Scan(object):
         self.sub_daz = np.ascontiguousarray(fan.daz, dtype=np.float64)
         self.sub_jv = np.ascontiguousarray(fan.j_ver, dtype=np.int32)
         self.sub_weight = np.ascontiguousarray(fan.weight, dtype=np.float64)
+        ml = np.ascontiguousarray(getattr(fan, 'ml_only', np.zeros(fan.n_sub)), dtype=np.int32)
+        self.sub_ml_only = ml if ml.any() else None
         self.traj_s = np.ascontiguousarray(traj_s, dtype=np.float32)
         self.traj_h = np.ascontiguousarray(traj_h, dtype=np.float32)
         self.traj_e = np.ascontiguousarray(traj_e, dtype=np.float32)
@@ -203,6 +205,7 @@ class Scan(object):
         s.sub_daz, s.sub_jv, s.sub_weight = _ptr(self.sub_daz), _ptr(self.sub_jv), _ptr(self.sub_weight)
         s.traj_s, s.traj_h, s.traj_e = _ptr(self.traj_s), _ptr(self.traj_h), _ptr(self.traj_e)
         s.traj_sin, s.traj_tan = _ptr(self.traj_sin), _ptr(self.traj_tan)
+        s.sub_ml_only = _ptr(self.sub_ml_only)
         return s
 
     @property

@@ -107,6 +107,7 @@ struct RadopHandle_ {
     bool geo_ready = false;      // geo_poly holds the polynomials of the staged scan (whole ray list)
     bool geo_poly_conv = false;  // ... and every series converged
     DevBuf traj_sc, traj_ie, f_wsum, f_ice, f_cnt;
+    DevBuf ml_wraw, ml_wsz;      // integration scheme 'ml': per-gate weights of a chunk
     DevBuf lt_stat;              // [0] u64 pairs integrated directly by k_integrate_tab, [1] (int) rejected pieces
     long long lt_pieces = 0, lt_rejected = 0, lt_fallback = 0, lt_why[4] = {0, 0, 0, 0};
     float lt_build_ms = 0.f;
@@ -194,7 +195,7 @@ int radop_destroy(RadopHandle *h)
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     cudaStreamSynchronize(h->copy_stream);
-    DevBuf *bufs[] = {&h->lt_stat, &h->traj_sc, &h->traj_ie, &h->f_wsum, &h->f_ice, &h->f_cnt, &h->lev_guess, &h->geo_poly, &h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
+    DevBuf *bufs[] = {&h->lt_stat, &h->ml_wraw, &h->ml_wsz, &h->traj_sc, &h->traj_ie, &h->f_wsum, &h->f_ice, &h->f_cnt, &h->lev_guess, &h->geo_poly, &h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
                       &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
                       &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
                       &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_st, &h->attw, &h->spec_acc, &h->spec_out, &h->d3_std, &h->sub_acc, &h->brd_flag, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
@@ -480,13 +481,14 @@ int radop_stage_scan(RadopHandle *h, const RadopScan *sc)
     const int ng = h->p.n_gates;
     const size_t ntr = (size_t)sc->n_traj * sc->n_vert * ng;
     // one pinned blob, one H2D copy
-    size_t off = 0, o_az, o_tr, o_ny, o_daz, o_jv, o_w, o_s, o_h, o_e, o_sin, o_tan;
+    size_t off = 0, o_az, o_tr, o_ny, o_daz, o_jv, o_w, o_s, o_h, o_e, o_sin, o_tan, o_ml;
     o_az = off; off = align_up(off + (size_t)sc->n_rays * 8, 256);
     o_tr = off; off = align_up(off + (size_t)sc->n_rays * 4, 256);
     o_ny = off; off = align_up(off + (size_t)sc->n_rays * 4, 256);
     o_daz = off; off = align_up(off + (size_t)sc->n_sub * 8, 256);
     o_jv = off; off = align_up(off + (size_t)sc->n_sub * 4, 256);
     o_w = off; off = align_up(off + (size_t)sc->n_sub * 8, 256);
+    o_ml = off; off = align_up(off + (size_t)sc->n_sub * 4, 256);
     o_s = off; off = align_up(off + ntr * 4, 256);
     o_h = off; off = align_up(off + ntr * 4, 256);
     o_e = off; off = align_up(off + ntr * 4, 256);
@@ -504,6 +506,7 @@ int radop_stage_scan(RadopHandle *h, const RadopScan *sc)
     memcpy(P + o_daz, sc->sub_daz, (size_t)sc->n_sub * 8);
     memcpy(P + o_jv, sc->sub_jv, (size_t)sc->n_sub * 4);
     memcpy(P + o_w, sc->sub_weight, (size_t)sc->n_sub * 8);
+    if (sc->sub_ml_only) memcpy(P + o_ml, sc->sub_ml_only, (size_t)sc->n_sub * 4);
     memcpy(P + o_s, sc->traj_s, ntr * 4);
     {   // ground-distance range of the scan: interval of the geodesy polynomials (k_sub_geopoly)
         float lo = sc->traj_s[0], hi = sc->traj_s[0];
@@ -529,6 +532,7 @@ int radop_stage_scan(RadopHandle *h, const RadopScan *sc)
     h->scan.sub_daz = (const double *)(D + o_daz);
     h->scan.sub_jv = (const int *)(D + o_jv);
     h->scan.sub_weight = (const double *)(D + o_w);
+    h->scan.sub_ml = sc->sub_ml_only ? (const int *)(D + o_ml) : nullptr;
     h->scan.traj_s = (const float *)(D + o_s);
     h->scan.traj_h = (const float *)(D + o_h);
     h->scan.traj_e = (const float *)(D + o_e);
@@ -735,6 +739,11 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     c.sum_species = (h->integration_mode == 0 && !c.with_melting && c.doppler_scheme != 3) ? 1 : 0;
     const int nsp = c.n_species, ng = c.n_gates;
     const int n_rays = h->n_rays;
+    const bool ml = h->scan.sub_ml != nullptr;
+    if (ml && !c.with_melting)
+        // the reference reads subradial.mask_ml, which only melting() sets (interpolation.py:429; AttributeError there)
+        return h->fail(RADOP_ERR_ARG, "integration scheme 'ml' needs the melting scheme (with_melting = 1)");
+    if (ml && c.doppler_scheme == 3) return h->fail(RADOP_ERR_UNSUPPORTED, "integration scheme 'ml' with Doppler scheme 3 is not implemented");
     rc = ensure_geometry(h);
     if (rc) return rc;
     const bool poly = h->geodesy_mode == 0 && h->geo_poly_ok && h->geo_poly_conv;
@@ -814,6 +823,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     CU(h, h->p0.reserve((size_t)n * nsp * 4));
     CU(h, h->p1.reserve((size_t)n * nsp * 4));
     if (want_vals) CU(h, h->vals.reserve((size_t)n * RADOP_NVP * 4));
+    if (ml) { CU(h, h->ml_wraw.reserve((size_t)n * 4)); CU(h, h->ml_wsz.reserve((size_t)n * 4)); }
     }
     CU(h, h->lat.reserve(n_rg * 8));
     CU(h, h->lon.reserve(n_rg * 8));
@@ -866,7 +876,8 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         CU(h, cudaFuncSetAttribute(k_interp_psd<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_interp_psd<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_scatter_pairs, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        CU(h, cudaFuncSetAttribute(k_spectrum, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(h, cudaFuncSetAttribute(k_spectrum<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CU(h, cudaFuncSetAttribute(k_spectrum<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_beam_attenuation, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_spectrum_broaden, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_done[h->device & 63] = true;
@@ -883,7 +894,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     if (c.doppler_scheme == 3) {
         if (smem_a > 200 * 1024) return h->fail(RADOP_ERR_ARG, "too many gates per ray for the spectrum attenuation scan");
         if (h->k4_smem > 200 * 1024) return h->fail(RADOP_ERR_ARG, "velocity array / diameter axis too long for the spectrum kernel");
-        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, k_spectrum, 128, h->k4_smem));
+        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, k_spectrum<true>, 128, h->k4_smem));
     }
     while ((int)h->chunk_done.size() < n_chunks) {
         cudaEvent_t e;
@@ -1038,6 +1049,19 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
                 CU(h, cudaGetLastError()); ++launches;
             }
         }
+        const float *wraw = nullptr, *wsz = nullptr;
+        if (ml) {
+            MlKernel mk;
+            double sum = 0.0;
+            for (int k = -8; k <= 8; ++k) sum += exp(-0.5 * k * k / 4.0);
+            for (int k = 0; k <= 8; ++k) mk.gk[k] = exp(-0.5 * k * k / 4.0) / sum;
+            k_ml_weights<<<(nr * c.n_sub * 32 + 127) / 128, 128, 0, st>>>(c, scan, mk, h->active.as<uint8_t>(), h->key.as<uint16_t>(),
+                                                                       h->hist.as<int>(), h->ml_wraw.as<float>(), nc);
+            CU(h, cudaGetLastError()); ++launches;
+            k_ml_total<<<(unsigned)((cc_rg + 127) / 128), 128, 0, st>>>(c, h->ml_wraw.as<float>(), h->ml_wsz.as<float>());
+            CU(h, cudaGetLastError()); ++launches;
+            wraw = h->ml_wraw.as<float>(); wsz = h->ml_wsz.as<float>();
+        }
         if (ev) CU(h, cudaEventRecord(ev[1], st));
 
         k_scan_bins<<<1, 1024, 0, st>>>(c, h->hist.as<int>(), h->bin_start.as<int>(), h->tile_start.as<int>(),
@@ -1048,7 +1072,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         const bool table_mode = h->integration_mode == 0;
         if (!table_mode || c.with_melting || c.doppler_scheme == 3) {
             k_scatter_pairs<<<(unsigned)((nc + 255) / 256), 256, hist_smem, st>>>(c, h->key.as<uint16_t>(), h->p0.as<float>(), h->p1.as<float>(),
-                                                                                   scan.sub_weight, h->cursor.as<int>(), h->rec.as<PairRec>(), nc);
+                                                                                   scan.sub_weight, h->cursor.as<int>(), h->rec.as<PairRec>(), nc, wsz);
             CU(h, cudaGetLastError()); ++launches;
         }
         if (ev) CU(h, cudaEventRecord(ev[2], st));
@@ -1061,7 +1085,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         if (table_mode) {
             K2tArgs at;
             at.key = h->key.as<uint16_t>(); at.p0 = h->p0.as<float>(); at.p1 = h->p1.as<float>();
-            at.sub_weight = scan.sub_weight; at.sz_out = a2.sz_out; at.ice_vn = a2.ice_vn; at.dop_vn = a2.dop_vn;
+            at.sub_weight = scan.sub_weight; at.wsz = wsz; at.sz_out = a2.sz_out; at.ice_vn = a2.ice_vn; at.dop_vn = a2.dop_vn;
             at.n_sbg = nc; at.n_fallback = h->lt_stat.as<unsigned long long>();
             // 4 CTAs of 256 per SM (64 registers), 8 waves of CTAs; measured against 2, 3 and 6 CTAs per SM and
             // against 4 ... all-at-once waves (profiles/README.md)
@@ -1092,6 +1116,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         a3.vals = want_vals ? h->vals.as<float>() : nullptr;
         a3.sub_weight = scan.sub_weight; a3.ray_nyquist = nyq;
         a3.comb = h->comb.as<float>(); a3.wsum = nullptr; a3.out = h->out.as<float>() + off_rg;
+        a3.wraw = wraw; a3.wsz = wsz;
         a3.model_out = c.output_model_vars ? h->model_out.as<float>() + off_rg : nullptr;
         k_reduce_subbeams<<<(unsigned)((cc_rg + 127) / 128), 128, 0, st>>>(c, a3);
         CU(h, cudaGetLastError()); ++launches;
@@ -1117,7 +1142,10 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             }
             k_beam_attenuation<<<(nr * c.n_sub + 3) / 4, 128, smem_a, st>>>(c, a4);
             CU(h, cudaGetLastError()); ++launches;
-            k_spectrum<<<std::max(1, occ4) * h->n_sm, 128, h->k4_smem, st>>>(c, a4);
+            bool nd1024 = true;
+            for (int s = 0; s < nsp; ++s) nd1024 = nd1024 && c.sp[s].nd == 1024;
+            if (nd1024) k_spectrum<true><<<std::max(1, occ4) * h->n_sm, 128, h->k4_smem, st>>>(c, a4);
+            else k_spectrum<false><<<std::max(1, occ4) * h->n_sm, 128, h->k4_smem, st>>>(c, a4);
             CU(h, cudaGetLastError()); ++launches;
             if (c.brd_mode) {
                 k_spectrum_broaden<<<(unsigned)((nc + 3) / 4), 128, smem_b, st>>>(c, a4, nc);

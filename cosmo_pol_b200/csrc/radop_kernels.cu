@@ -353,6 +353,7 @@ struct ScanDev {
     const double *sub_weight;
     const float *traj_s, *traj_h, *traj_e;
     const float *traj_sin, *traj_tan;   // optional (Doppler scheme 3)
+    const int *sub_ml;                  // optional (integration scheme 'ml'): 1 = weight only near the melting-layer edges
 };
 
 #define GEO_NP 16
@@ -1052,6 +1053,7 @@ k_interp_psd(const __grid_constant__ DevConfig cfg, ScanDev scan, const void *__
                     const float QR = val[RADOP_VAR_QR], QS = val[RADOP_VAR_QS], QG = val[RADOP_VAR_QG];
                     const float QSG = __fadd_rn(QS, QG);
                     if (QR > 0.f && QSG > 0.f) {
+                        if (scan.sub_ml) active |= 0x80;      // mask_ml of melting.py:45 (read and cleared by k_ml_weights)
                         const float qms = __fadd_rn(QS, __fmul_rn(QR, __fdiv_rn(QS, QSG)));
                         const float qmg = __fadd_rn(QG, __fmul_rn(QR, __fdiv_rn(QG, QSG)));
                         val[MELT_SLOT_QMS] = qms;
@@ -1305,7 +1307,7 @@ __global__ void k_scan_bins(const __grid_constant__ DevConfig cfg, const int *__
 __global__ void __launch_bounds__(256)
 k_scatter_pairs(const __grid_constant__ DevConfig cfg, const uint16_t *__restrict__ key, const float *__restrict__ p0,
                 const float *__restrict__ p1, const double *__restrict__ sub_weight, int *cursor,
-                PairRec *__restrict__ rec, long long n_sbg)
+                PairRec *__restrict__ rec, long long n_sbg, const float *__restrict__ wsz)
 {
     const int tid = threadIdx.x;
     for (int b = tid; b < cfg.total_bins; b += blockDim.x) s_hist[b] = 0;
@@ -1333,7 +1335,7 @@ k_scatter_pairs(const __grid_constant__ DevConfig cfg, const uint16_t *__restric
     __syncthreads();
     if (in_range) {
         int q = (int)((sbg / cfg.n_gates) % cfg.n_sub);
-        float w = (float)sub_weight[q];
+        float w = wsz ? wsz[sbg] : (float)sub_weight[q];
         for (int s = 0; s < cfg.n_species; ++s) {
             if (keys[s] == RADOP_KEY_NONE) continue;
             PairRec r;
@@ -2062,6 +2064,7 @@ struct K2tArgs {
     const uint16_t *key;     // [species][sbg] global bin id or RADOP_KEY_NONE
     const float *p0, *p1;    // [species][sbg]
     const double *sub_weight;
+    const float *wsz;        // integration scheme 'ml': normalised per-gate weights [sbg], else null
     float *sz_out;
     float2 *ice_vn, *dop_vn;
     long long n_sbg;
@@ -2195,7 +2198,7 @@ k_integrate_tab(const __grid_constant__ DevConfig cfg, K2tArgs A)
             }
         }
         const int q = in_range ? (int)(((unsigned)sbg / (unsigned)ng) % (unsigned)cfg.n_sub) : 0;
-        const float w = (float)__ldg(A.sub_weight + q);
+        const float w = (A.wsz && in_range) ? __ldg(A.wsz + sbg) : (float)__ldg(A.sub_weight + q);
         // sum over the species in the reference's order (doppler_scatter.py:148-158), kept in registers
         float acc[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         bool any = false;
@@ -2369,6 +2372,75 @@ k_integrate_melting(const __grid_constant__ DevConfig cfg, K2mArgs A)
     }
 }
 
+// Integration scheme 'ml' (interpolation.py:423-436; doppler_scatter.py:127-129, 186-189, 259-262): per-gate quadrature
+// weights.  One warp per (ray, sub-beam).  A sub-beam flagged sub_ml keeps its weight only around the first and the last
+// gate of its own melting layer (mask_ml = QR > 0 and QS + QG > 0, melting.py:45: bit 7 of `active`, set by k_interp_psd):
+// weight x scipy.ndimage.gaussian_filter(spikes at the two gates, sigma = 2) -- radius int(4 sigma + 0.5) = 8, normalised
+// weights, mode 'reflect'; gk = the nine one-sided filter weights in float64.  Pairs of gates whose weight is zero are
+// not evaluated by the reference (valid_data = QM > 0 and weight > 0): their keys are withdrawn from the bin histogram.
+struct MlKernel { double gk[9]; };
+__global__ void __launch_bounds__(128)
+k_ml_weights(const __grid_constant__ DevConfig cfg, ScanDev scan, MlKernel K, uint8_t *__restrict__ active,
+             uint16_t *__restrict__ key, int *__restrict__ hist, float *__restrict__ wraw, long long n_sbg)
+{
+    const int rq = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (rq >= cfg.n_rays * cfg.n_sub) return;
+    const int ng = cfg.n_gates, q = rq % cfg.n_sub;
+    const size_t base = (size_t)rq * ng;
+    const double w = scan.sub_weight[q];
+    const bool ml_only = scan.sub_ml && scan.sub_ml[q];
+    int first = 0x7fffffff, last = -1;
+    if (ml_only) {
+        for (int g = lane; g < ng; g += 32)
+            if (active[base + g] & 0x80) { first = min(first, g); last = max(last, g); }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            first = min(first, __shfl_xor_sync(0xffffffffu, first, d));
+            last = max(last, __shfl_xor_sync(0xffffffffu, last, d));
+        }
+    }
+    for (int g = lane; g < ng; g += 32) {
+        double W = w;
+        if (ml_only) {
+            double G = 0.0;
+            if (last >= 0) {
+                for (int m = g - 8; m <= g + 8; ++m) {
+                    const int r = m < 0 ? -m - 1 : (m >= ng ? 2 * ng - m - 1 : m);      // mode 'reflect'
+                    if (r == first || r == last) G += K.gk[abs(g - m)];
+                }
+            }
+            W = w * G;
+        }
+        const float Wf = (float)W;
+        wraw[base + g] = Wf;
+        uint8_t act = active[base + g] & 0x7f;
+        if (!(Wf > 0.f) && act) {
+            for (int s = 0; s < cfg.n_species; ++s) {
+                const size_t ki = (size_t)s * n_sbg + base + g;
+                const uint16_t k = key[ki];
+                if (k != RADOP_KEY_NONE) { atomicSub(hist + k, 1); key[ki] = RADOP_KEY_NONE; }
+            }
+            act = 0;
+        }
+        active[base + g] = act;
+    }
+}
+
+// total weight of a ray gate over the sub-beams (np.sum(all_weights, axis = 0), doppler_scatter.py:128-129) and the
+// normalised weights the scattering sums use (:260-261); thread per ray gate, fixed order
+__global__ void k_ml_total(const __grid_constant__ DevConfig cfg, const float *__restrict__ wraw, float *__restrict__ wsz)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)cfg.n_rays * cfg.n_gates) return;
+    const int g = (int)(idx % cfg.n_gates), ray = (int)(idx / cfg.n_gates);
+    double tot = 0.0;
+    for (int q = 0; q < cfg.n_sub; ++q) tot += (double)wraw[((size_t)ray * cfg.n_sub + q) * cfg.n_gates + g];
+    for (int q = 0; q < cfg.n_sub; ++q) {
+        const size_t sbg = ((size_t)ray * cfg.n_sub + q) * cfg.n_gates + g;
+        wsz[sbg] = (float)((double)wraw[sbg] / tot);
+    }
+}
+
 struct K3Args {
     const int8_t *mask;
     const uint8_t *active;
@@ -2381,6 +2453,7 @@ struct K3Args {
     const float *ray_nyquist;
     float *comb;        // [ray][gate][8]: b c p q kd s9 s11 rvel
     const float *wsum;  // fused pipeline: comb[7] holds sum(rv w) and this the sum of the weights; else null
+    const float *wraw, *wsz;   // integration scheme 'ml': per-gate weights [sbg] (raw, and normalised by their sum over the sub-beams)
     float *out;         // [N_OUT+1][ray][gate]
     float *model_out;   // [NVP][ray][gate]
 };
@@ -2411,7 +2484,7 @@ k_reduce_subbeams(const __grid_constant__ DevConfig cfg, K3Args A)
         int m = A.mask[sbg];
         msum += (float)m;
         if (m != 0) continue;
-        float w = (float)A.sub_weight[q];
+        float w = A.wraw ? A.wraw[sbg] : (float)A.sub_weight[q];
         uint8_t act = A.active[sbg];
         for (int s = 0; s < (cfg.sum_species ? (act ? 1 : 0) : nsp); ++s) {
             if (!cfg.sum_species && !(act & (1u << s))) continue;
@@ -2452,7 +2525,7 @@ k_reduce_subbeams(const __grid_constant__ DevConfig cfg, K3Args A)
 #pragma unroll
             for (int v4 = 0; v4 < 4; ++v4) {
                 float4 x = __ldg(vp + v4);
-                float wn = w / sumw_all;
+                float wn = A.wsz ? A.wsz[sbg] : w / sumw_all;
                 if (!isnan(x.x)) mv[4 * v4] += x.x * wn;
                 if (!isnan(x.y)) mv[4 * v4 + 1] += x.y * wn;
                 if (!isnan(x.z)) mv[4 * v4 + 2] += x.z * wn;
@@ -2685,6 +2758,9 @@ extern __shared__ __align__(16) unsigned char s_k4[];
 // running sums of one lane's samples [k0, k0 + cpl): four independent chains of cpl / 4
 // consecutive samples each (latency of the float64 adds), local prefix stored in float32
 #define SPEC_SUB 4
+// ND1024: every table has 1024 diameters (compute_lut_sz.py:69, the only size the reference generates): the index
+// arithmetic of the chains (k / cpl, k % cpl, k / sub) becomes shifts and masks instead of integer divisions
+template <bool ND1024>
 __global__ void __launch_bounds__(128)
 k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
 {
@@ -2725,8 +2801,8 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
         int s = 0;
         while (s + 1 < nsp && b >= cfg.sp[s + 1].bin_base) ++s;
         const SpeciesDev &S = cfg.sp[s];
-        const int nd = S.nd, cpl = nd >> 5;          // samples per lane (nd is a multiple of 32)
-        const int sub = cpl / SPEC_SUB;              // samples per chain (nd is a multiple of 128 here)
+        const int nd = ND1024 ? 1024 : S.nd, cpl = ND1024 ? 32 : nd >> 5;   // samples per lane (nd is a multiple of 32)
+        const int sub = ND1024 ? 32 / SPEC_SUB : cpl / SPEC_SUB;            // samples per chain (nd is a multiple of 128 here)
         const int cnt = A.hist[b];
         const int tiles = (cnt + RADOP_TILE - 1) / RADOP_TILE;
         const int j0 = (unit - A.chunk_start[b]) * RADOP_CHUNK, j1 = min(tiles, j0 + RADOP_CHUNK);

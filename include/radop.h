@@ -155,6 +155,10 @@ typedef struct {
      * (get_diameter_from_rad_vel, doppler_scatter.py:571-575), same shape as traj_e         */
     const float *traj_sin;
     const float *traj_tan;
+    /* Integration scheme 'ml' (interpolation.py:168-193, 423-436), optional (NULL: every sub-beam keeps its weight at
+     * every gate): sub_ml_only[q] = 1 for a sub-beam whose weight only counts near the first and the last
+     * melting-layer gate of the sub-beam (Gaussian-smoothed spikes, sigma = 2 gates); needs with_melting. */
+    const int32_t *sub_ml_only;   /* [n_sub] */
 } RadopScan;
 
 /* radar observables, linear units (doppler_scatter.py:446-460) */

@@ -617,7 +617,8 @@ def get_interpolated_radial(model, azimuth, elevation, cfg, debug=False):
     radar_pos = cfg['radar']['coords']
     if cfg['integration']['scheme'] == 2:
         return _irregular_radial(model, names, azimuth, elevation, cfg, rranges, radar_pos, debug)
-    pts_hor, pts_ver, weights, keep = gauss_hermite_subbeams(cfg)
+    ml = cfg['integration']['scheme'] == 'ml'
+    pts_hor, pts_ver, weights, keep = melting_layer_subbeams(cfg) if ml else gauss_hermite_subbeams(cfg)
     if cfg['refraction']['scheme'] == 2:
         N = {'data': model['refractivity'], 'z_levels': model['z_levels'], 'proj': model['proj'],
              'resolution': model['resolution']}
@@ -650,6 +651,20 @@ def get_interpolated_radial(model, azimuth, elevation, cfg, debug=False):
                 sub['dbg'] = r[4]
             if cfg['microphysics']['with_melting']:
                 sub = melting(sub)
+            if ml:
+                # interpolation.py:423-436 (sub['mask_ml'] only exists with the melting scheme: KeyError here,
+                # AttributeError in the reference)
+                if j > int(cfg['integration']['nv_GH']):
+                    smoothing = np.zeros(len(lats))
+                    idx_ml = np.where(sub['mask_ml'])[0]
+                    if len(idx_ml):
+                        smoothing[idx_ml[0]] = 1
+                        smoothing[idx_ml[-1]] = 1
+                        from scipy.ndimage import gaussian_filter
+                        smoothing = gaussian_filter(smoothing, 2)
+                    sub['quad_weight'] = sub['quad_weight'] * smoothing
+                else:
+                    sub['quad_weight'] = sub['quad_weight'] * np.ones(len(lats))
             subs.append(sub)
     return subs
 
@@ -720,6 +735,35 @@ def sweep_indices(model, luts, cfg, azimuths, elevation, geod=None):
             out['lut_e'][:, q, :, k] = le.reshape(nr, ng)
             out['lut_t'][:, q, :, k] = lt.reshape(nr, ng)
     return out
+
+
+def melting_layer_subbeams(cfg):
+    """Integration scheme 'ml' (interpolation.py:168-193): ten times the vertical Gauss-Hermite points (made odd),
+    sorted by decreasing weight; threshold as for scheme 1 (:343-352)."""
+    bw = cfg['radar']['3dB_beamwidth']
+    nh = int(cfg['integration']['nh_GH'])
+    nv = int(cfg['integration']['nv_GH'])
+    nv_ml = 10 * nv
+    if not nv_ml % 2:
+        nv_ml += 1
+    sigma = bw / (2 * np.sqrt(2 * np.log(2)))
+    pts_hor, w_hor = hermgauss(nh)
+    pts_hor = pts_hor * sigma
+    pts_ver, w_ver = hermgauss(nv_ml)
+    pts_ver = pts_ver * sigma
+    idx_sort = np.argsort(w_ver)[::-1]
+    w_ver = w_ver[idx_sort]
+    pts_ver = pts_ver[idx_sort]
+    weights = np.outer(w_hor * sigma, w_ver * sigma)
+    weights *= np.abs(np.cos(np.deg2rad(pts_ver)))
+    weights /= np.sum(weights.ravel())
+    beam_broadening = nh > 1 or nv > 1
+    w_sort = np.sort(np.array(weights).ravel())[::-1]
+    w_cum = np.cumsum(w_sort / np.sum(w_sort))
+    w_cum[-1] = 1.
+    threshold = w_sort[np.where(w_cum >= cfg['integration']['weight_threshold'])[0][0]]
+    keep = np.logical_or(weights >= threshold, not beam_broadening)
+    return pts_hor, pts_ver, weights, keep
 
 
 def _nansum2(x, y):
@@ -1313,6 +1357,8 @@ def get_radar_observables(subs, luts, cfg, accum='ref', debug=False):
     if doppler_scheme == 3:
         doppler_spectrum = np.zeros((n_gates, len(consts['VARRAY'])))
     dbg = {'e_idx': {}, 't_idx': {}, 'valid': {}}
+    if cfg['integration']['scheme'] == 'ml':            # doppler_scatter.py:127-129
+        total_weight_at_gates = np.sum(np.array([b['quad_weight'] for b in subs]), axis=0)
 
     for i, sub in enumerate(subs):
         v_integ = np.zeros(n_gates,)
@@ -1332,6 +1378,8 @@ def get_radar_observables(subs, luts, cfg, accum='ref', debug=False):
             QM = sub['values']['Q' + h + '_v']
             with np.errstate(invalid='ignore'):
                 valid = QM > 0
+            if not np.isscalar(sub['quad_weight']):          # doppler_scatter.py:186-189
+                valid = np.logical_and(valid, sub['quad_weight'] > 0)
             if not np.any(valid):
                 continue
             if scheme == '1mom':
@@ -1364,7 +1412,11 @@ def get_radar_observables(subs, luts, cfg, accum='ref', debug=False):
                 dbg['t_idx'][(i, h)] = it
                 dbg['valid'][(i, h)] = valid.copy()
             sz_psd_integ = np.einsum('ijk,ij->ik', sz, N) * dD
-            sz_integ[valid, j, :] = _nansum2(sz_integ[valid, j, :], sz_psd_integ * sub['quad_weight'])
+            if not np.isscalar(sub['quad_weight']):          # doppler_scatter.py:259-265
+                wts = sub['quad_weight'][valid] / total_weight_at_gates[valid]
+                sz_integ[valid, j, :] = _nansum2(sz_integ[valid, j, :], wts[:, None] * sz_psd_integ)
+            else:
+                sz_integ[valid, j, :] = _nansum2(sz_integ[valid, j, :], sz_psd_integ * sub['quad_weight'])
             if doppler_scheme == 1:
                 vh, n = hyd[h].integrate_V()
                 v_integ[valid] = _nansum2(v_integ[valid], vh)

@@ -389,6 +389,11 @@ CASES = {
     'c1mom_melt_dop2': ('1mom', 5.6, dict(radar={'range': 30000, 'radial_resolution': 500}, doppler={'scheme': 2},
                                           microphysics={'with_melting': 1}, integration={'nv_GH': 1, 'nh_GH': 3}),
                         [(220.0, 3.5)], {}),
+    # integration scheme 'ml' (interpolation.py:168-193, 423-436; doppler_scatter.py:127-129, 186-189, 259-262): ten
+    # times the vertical points, the extra ones weighted only around the edges of the melting layer of their sub-beam
+    'c1mom_ml': ('1mom', 5.6, dict(radar={'range': 30000, 'radial_resolution': 500},
+                                   microphysics={'with_melting': 1}, integration={'scheme': 'ml', 'nv_GH': 1, 'nh_GH': 3}),
+                 [(220.0, 3.5), (170.0, 3.5)], {}),
     # integration scheme 2 (interpolation.py:194-228, 440-494): irregular (azimuth, elevation) points of a
     # two-Gaussian antenna pattern (main lobe + first side-lobe ring), one trajectory per point
     'c1mom_quad2': ('1mom', 5.6, dict(radar={'range': 30000, 'radial_resolution': 1000},

@@ -633,6 +633,54 @@ def test_melting_scheme_against_reference_golden(name):
     assert np.isfinite(with_opt['ZH']).sum() > 5
 
 
+def test_melting_layer_integration_scheme():
+    """Integration scheme 'ml' (interpolation.py:168-193, 423-436; doppler_scatter.py:127-129, 186-189, 259-262): 33
+    sub-beams of which 27 only count around the melting-layer edges of their own sub-beam (per-gate quadrature weights:
+    k_ml_weights / k_ml_total).  Against the golden produced by the reference itself and against the float64 oracle,
+    table and direct integration; without the melting scheme the reference fails, so does this path."""
+    from cosmo_pol_b200 import RadarOperator
+    g, cfg, kw = load_golden_case('c1mom_ml')
+    model, luts = synthetic_inputs('1mom', 5.6, with_melting=True, **kw)
+    conf = copy.deepcopy(cfg)
+    conf['radar']['sensitivity'] = [-300, 10000]
+    op = RadarOperator(conf, output_variables='all', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    rays = g['rays']
+    ref = {k[4:]: g[k] for k in g.files if k.startswith('obs_')}
+    pm, pl = plain(model, luts)
+    ref64 = O.simulate_scan(pm, pl, oracle_cfg(op), rays[:, 0], rays[:, 1], accum='f64', sensitivity_cut=True)
+    for mode in ('table', 'direct'):
+        op._prepare_engine().set_integration(mode)
+        out = op.simulate_rays(rays[:, 0], rays[:, 1])
+        assert op._last_scan.n_sub == 33 and int(op._last_scan.sub_ml_only.sum()) == 27
+        assert_observables_close(out, ref, sz_scale=5e-4 * np.abs(ref['KDP']), what='ml golden ' + mode)
+        assert_observables_close(out, ref64, sz_scale=(5e-4 * np.abs(ref64['KDP'])) if mode == 'direct' else None, what='ml oracle ' + mode)
+        assert np.array_equal(out['mask'], g['mask'].astype(np.float32))
+        a, b = out['RVEL'], ref['RVEL']
+        assert np.array_equal(np.isnan(a), np.isnan(b))
+        ok = np.isfinite(b)
+        assert ok.sum() > 50 and np.max(np.abs(a[ok] - b[ok])) < 2e-3
+        for k in [f for f in g.files if f.startswith('int_')]:
+            assert np.allclose(out[k[4:]], g[k], rtol=2e-5, atol=1e-9), k
+    # the per-gate weights matter: the plain Gauss-Hermite scheme with the same base points gives other reflectivities
+    conf1 = copy.deepcopy(conf)
+    conf1['integration']['scheme'] = 1
+    op1 = RadarOperator(conf1, output_variables='only_radar', device=0)
+    op1.set_lut(luts)
+    op1.load_model(model)
+    plain_gh = op1.simulate_rays(rays[:, 0], rays[:, 1])
+    both = np.isfinite(plain_gh['ZH']) & np.isfinite(ref['ZH'])
+    assert np.max(np.abs(10 * np.log10(plain_gh['ZH'][both] / ref['ZH'][both]))) > 0.05
+    conf0 = copy.deepcopy(conf)
+    conf0['microphysics']['with_melting'] = 0
+    op0 = RadarOperator(conf0, output_variables='only_radar', device=0)
+    op0.set_lut({h: l for h, l in luts.items() if h not in ('mS', 'mG')})
+    op0.load_model(model)
+    with pytest.raises(ValueError):
+        op0.simulate_rays(rays[:1, 0], rays[:1, 1])
+
+
 def test_ode_refraction_scheme_against_oracle():
     """Refraction scheme 2 (atm_refraction.py:56-148): the trajectories come from the host-side
     ODE through the model's refractivity, the kernels are unchanged.  Bit-exact interpolation decisions."""

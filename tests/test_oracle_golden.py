@@ -13,7 +13,7 @@ from conftest import GOLDEN, load_golden_case, plain, synthetic_inputs
 CASES = {'c1mom': ('1mom', 5.6), 'c2mom': ('2mom', 9.41), 'c1mom_thr': ('1mom', 5.6), 'c1mom_nyq': ('1mom', 5.6),
          'c1mom_dop2': ('1mom', 5.6), 'c1mom_dop3': ('1mom', 5.6), 'c1mom_dop3_mot': ('1mom', 5.6),
          'c1mom_dop3_turb': ('1mom', 5.6), 'c1mom_melt': ('1mom', 5.6), 'c1mom_melt_dop2': ('1mom', 5.6),
-         'c1mom_quad2': ('1mom', 5.6)}
+         'c1mom_quad2': ('1mom', 5.6), 'c1mom_ml': ('1mom', 5.6)}
 
 
 def test_constants_match_reference():
@@ -96,7 +96,7 @@ def test_path_matches_reference(name):
         # interpolation half: bit-exact
         for q, s in enumerate(r['subs']):
             assert np.array_equal(s['mask'], g['sub_mask'][i][q])
-            assert s['quad_weight'] == g['sub_w'][i][q]
+            assert np.array_equal(np.asarray(s['quad_weight']), g['sub_w'][i][q])
             assert np.array_equal(np.asarray(s['quad_pt']), g['sub_pt'][i][q])
             assert np.array_equal(s['lats'], g['sub_lats'][i][q]) and np.array_equal(s['lons'], g['sub_lons'][i][q])
             for k, v in s['values'].items():
