@@ -23,13 +23,14 @@
 #pragma once
 
 #ifndef FUSED_MAX_WARPS
-#define FUSED_MAX_WARPS 10    // warps per CTA (a build-time experiment knob together with FUSED_MIN_CTAS: registers per thread)
+#define FUSED_MAX_WARPS 9     // warps per CTA (a build-time experiment knob together with FUSED_MIN_CTAS: registers per thread)
 #endif
 #ifndef FUSED_MIN_CTAS
-#define FUSED_MIN_CTAS 3
+#define FUSED_MIN_CTAS 4      // 9 warps x 4 CTAs -> 56 registers: the fastest of the measured shapes (profiles/r02_fused_variants.md)
 #endif
 #ifndef FUSED_NOBARRIER
-#define FUSED_NOBARRIER 1     // 1: the warps of a CTA hand their rows over through shared-memory flags (no CTA-wide barrier)
+#define FUSED_NOBARRIER 0     // 1: the warps of a CTA hand their rows over through shared-memory flags instead of a CTA-wide
+                              // barrier (measured 60 % slower: spinning warps and twice the shared memory; kept for the record)
 #endif
 #ifndef FUSED_UNROLL_COLS
 #define FUSED_UNROLL_COLS 0   // 1: the four neighbour columns of the interpolation as straight-line code

@@ -13,7 +13,11 @@ done
 timeout 2400 python -m pytest tests -m gpu -q --durations=8 > gpurun_out/gpu_tests.log 2>&1; echo "tests rc=$?"
 tail -15 gpurun_out/gpu_tests.log
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu --no-direct"
-RADOP_LIB=$PWD/cosmo_pol_b200/libradop_r56.so timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k_gate_fused -s 4 -c 1 -f -o gpurun_out/prof_fused $CMD > gpurun_out/ncu_full.log 2>&1
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k_gate_fused -s 4 -c 1 -f -o gpurun_out/prof_fused $CMD > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_spectrum$ -s 1 -c 1 -f -o gpurun_out/prof_spectrum python scripts/bench_configs.py cfg5s --steps 2 > gpurun_out/ncu_spec.log 2>&1
 echo "ncu spectrum rc=$?"
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
+echo "ncu list rc=$?"
+timeout 600 python bench.py --steps 20 --warmup 5 > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; echo "bench rc=$?"; cat gpurun_out/bench_default.json
+timeout 900 python scripts/margins.py > gpurun_out/margins.json 2> gpurun_out/margins.err; echo "margins rc=$?"
