@@ -29,9 +29,10 @@ EXPORTS = ['radop_abi_version', 'radop_create', 'radop_destroy', 'radop_last_err
            'radop_get_stats', 'radop_enable_timing', 'radop_debug_indices', 'radop_measure_fp32_peak',
            'radop_get_all_radar_pts', 'radop_selftest_division', 'radop_set_chunk', 'radop_set_overlap_threshold',
            'radop_set_geodesy', 'radop_get_geodesy', 'radop_set_integration', 'radop_get_integration', 'radop_debug_integration',
-           'radop_set_search', 'radop_sizeof', 'radop_device_buffer', 'radop_get_refl', 'radop_set_pipeline', 'radop_get_pipeline', 'radop_set_tuning']
+           'radop_set_search', 'radop_sizeof', 'radop_device_buffer', 'radop_get_refl', 'radop_get_refl_noalloc', 'radop_set_pipeline', 'radop_get_pipeline', 'radop_set_tuning']
 
 BUF_OBS, BUF_LAT, BUF_LON, BUF_MODEL, BUF_DSPECTRUM = range(5)
+NOALLOC_SCRATCH_BYTES = 4 << 20      # RADOP_NOALLOC_SCRATCH_BYTES
 
 (RADOP_OK, RADOP_ERR_CUDA, RADOP_ERR_ARG, RADOP_ERR_OUT_OF_DOMAIN, RADOP_ERR_LUT, RADOP_ERR_STATE,
  RADOP_ERR_UNSUPPORTED) = range(7)
@@ -142,6 +143,7 @@ def load_library():
     lib.radop_sizeof.argtypes = [C.c_int]
     lib.radop_device_buffer.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
     lib.radop_get_refl.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 8
+    lib.radop_get_refl_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 8
     if lib.radop_abi_version() != RADOP_ABI_VERSION:
         raise RadopError('libradop.so ABI version mismatch')
     # the struct layouts of this binding against the ones the library was compiled with (radop_sizeof):
@@ -580,6 +582,20 @@ class Engine(object):
         out = np.zeros(n, dtype=np.float32)
         self._check(self.lib.radop_get_refl(self.h, n, nh, nd, _ptr(Da), _ptr(Db), _ptr(rcs), _ptr(D), _ptr(N),
                                             _ptr(step_D), _ptr(Dmin), _ptr(out)))
+        return out
+
+    def get_refl_noalloc(self, Da, Db, rcs, D, N, step_D, Dmin, out=None):
+        """get_refl through radop_get_refl_noalloc: the device side allocates nothing (operands and result are staged in
+        a static device array of NOALLOC_SCRATCH_BYTES inside the library; larger problems raise RadopError).  Not in the
+        reference.  Pass contiguous float32 arrays and `out` to keep the host side allocation-free as well."""
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float32)
+        Da, Db, rcs, D, N, step_D, Dmin = f(Da), f(Db), f(rcs), f(D), f(N), f(step_D), f(Dmin)
+        n, nh = Da.shape
+        nd = rcs.shape[0]
+        if out is None:
+            out = np.zeros(n, dtype=np.float32)
+        self._check(self.lib.radop_get_refl_noalloc(self.h, n, nh, nd, _ptr(Da), _ptr(Db), _ptr(rcs), _ptr(D), _ptr(N),
+                                                    _ptr(step_D), _ptr(Dmin), _ptr(out)))
         return out
 
     def get_all_radar_pts(self, coords, heights_gates, model_data, model_heights, llc, res):

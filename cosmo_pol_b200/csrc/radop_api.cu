@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1595,3 +1596,64 @@ int radop_get_refl(RadopHandle *h, int len, int nhydro, int nd, const float *Da,
 }
 
 }  // extern "C"
+
+// ---- allocation-free variant of radop_get_refl ---------------------------------------------------------------------
+// The staged operands and the result of k_refl_compat live in ONE file-scope device array instead of cudaMalloc'ed
+// buffers.  Every GPU that loads the library holds these RADOP_NOALLOC_SCRATCH_BYTES until the process exits.  In host
+// code the array's name is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress, asked
+// once per device with that device current, and is what the copies and the kernel are given.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[RADOP_NOALLOC_SCRATCH_BYTES];
+static std::mutex g_noalloc_mu;
+static void *g_noalloc_ptr[64] = {nullptr};
+
+static cudaError_t noalloc_scratch_address(int device, void **ptr)
+{   // the caller has made `device` current
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    void *&slot = g_noalloc_ptr[device & 63];
+    if (device >= 64 || !slot) {
+        void *q = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&q, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        if (!q) return cudaErrorInvalidSymbol;
+        if (device >= 64) { *ptr = q; return cudaSuccess; }
+        slot = q;
+    }
+    *ptr = slot;
+    return cudaSuccess;
+}
+
+extern "C" int radop_get_refl_noalloc(RadopHandle *h, int len, int nhydro, int nd, const float *Da, const float *Db,
+                                      const float *rcs, const float *D, const float *N, const float *step_D,
+                                      const float *Dmin, float *refl)
+{
+    (void)D;
+    if (!h) return RADOP_ERR_ARG;
+    if (!Da || !Db || !rcs || !N || !step_D || !Dmin || !refl || len <= 0 || nhydro <= 0 || nd <= 0)
+        return h->fail(RADOP_ERR_ARG, "radop_get_refl_noalloc: null pointer or non-positive size");
+    const size_t n_ab = (size_t)len * nhydro, n_tab = (size_t)nd * nhydro;
+    const size_t need = (2 * n_ab + 2 * n_tab + 2 * (size_t)nhydro + (size_t)len) * 4;
+    if (need > (size_t)RADOP_NOALLOC_SCRATCH_BYTES) {
+        char msg[256];
+        snprintf(msg, sizeof msg, "radop_get_refl_noalloc: len=%d nhydro=%d nd=%d need %zu bytes of device scratch, the static "
+                 "array holds %u (use radop_get_refl)", len, nhydro, nd, need, (unsigned)RADOP_NOALLOC_SCRATCH_BYTES);
+        return h->fail(RADOP_ERR_ARG, msg);
+    }
+    CU(h, cudaSetDevice(h->device));
+    void *base = nullptr;
+    CU(h, noalloc_scratch_address(h->device, &base));
+    // nothing in the scratch has to start at zero: every word the kernel reads is overwritten by this call's copies first,
+    // and the kernel writes all `len` words of the result before they are copied back
+    float *dDa = static_cast<float *>(base), *dDb = dDa + n_ab, *drcs = dDb + n_ab, *dN = drcs + n_tab, *dstep = dN + n_tab,
+          *dmin = dstep + nhydro, *dout = dmin + nhydro;
+    CU(h, cudaMemcpyAsync(dDa, Da, n_ab * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(dDb, Db, n_ab * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(drcs, rcs, n_tab * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(dN, N, n_tab * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(dstep, step_D, (size_t)nhydro * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(dmin, Dmin, (size_t)nhydro * 4, cudaMemcpyHostToDevice, h->stream));
+    k_refl_compat<<<(len + 127) / 128, 128, 0, h->stream>>>(len, nhydro, nd, dDa, dDb, drcs, dN, dstep, dmin, dout);
+    CU(h, cudaGetLastError());
+    CU(h, cudaMemcpyAsync(refl, dout, (size_t)len * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return RADOP_OK;
+}

@@ -330,6 +330,26 @@ int radop_get_refl(RadopHandle *h, int len, int nhydro, int nd, const float *Da,
                    const float *rcs, const float *D, const float *N, const float *step_D,
                    const float *Dmin, float *refl);
 
+/* ---- allocation-free entry point -------------------------------------------------
+ * No counterpart in the reference: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid allocation).  Same contract and same bits as radop_get_refl above, but the
+ * device copies of the operands and of the result live in one file-scope
+ * `static __device__ __align__(256)` array of RADOP_NOALLOC_SCRATCH_BYTES inside libradop.so
+ * (every GPU that loads the library holds it until the process exits); the call makes no
+ * cudaMalloc / cudaFree and calls no allocating library routine.
+ * Limit: 4 * (2*len*nhydro + 2*nd*nhydro + 2*nhydro + len) <= RADOP_NOALLOC_SCRATCH_BYTES,
+ * else RADOP_ERR_ARG with the sizes in radop_last_error() (use radop_get_refl then).
+ * All calls on a GPU share the array and it keeps the previous call's contents; nothing in it
+ * has to start at zero (every word read is first overwritten by this call's copies, every
+ * result word is written by the kernel).  The call returns after its stream has drained, so
+ * calls from one thread never overlap; calls from several threads or handles on the same
+ * GPU that overlap on the device RACE on the array -- serialise them. */
+#define RADOP_NOALLOC_SCRATCH_BYTES (4u << 20)
+int radop_get_refl_noalloc(RadopHandle *h, int len, int nhydro, int nd, const float *Da, const float *Db,
+                           const float *rcs, const float *D, const float *N, const float *step_D,
+                           const float *Dmin, float *refl);
+
 #ifdef __cplusplus
 }
 #endif
