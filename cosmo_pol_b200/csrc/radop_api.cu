@@ -95,7 +95,7 @@ struct RadopHandle_ {
     double geo_mid = 0.0, geo_half = 1.0;
     DevBuf geo, mask, active, wind, sinth, vsum, nsum, key, p0, p1, vals, lat, lon, hist, flags;
     DevBuf bin_start, tile_start, cost_start, cursor, totals, rec, sz_out, ice_vn, dop_vn, ice_tot, comb, out, model_out;
-    DevBuf d3_uh, d3_w, d3_rho, d3_st, attw, spec_acc, spec_out, d3_std, sub_acc, brd_flag;
+    DevBuf d3_uh, d3_w, d3_rho, d3_st, attw, spec_pre, spec_acc, spec_out, d3_std, sub_acc, brd_flag;
     size_t k4_smem = 0;
     DevBuf dbg_cell, dbg_level, dbg_status, dbg_e, dbg_t, dbg_rot;
     DevConfig cfg;
@@ -199,7 +199,7 @@ int radop_destroy(RadopHandle *h)
     DevBuf *bufs[] = {&h->lt_stat, &h->ml_wraw, &h->ml_wsz, &h->traj_sc, &h->traj_ie, &h->f_wsum, &h->f_ice, &h->f_cnt, &h->lev_guess, &h->geo_poly, &h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
                       &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
                       &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
-                      &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_st, &h->attw, &h->spec_acc, &h->spec_out, &h->d3_std, &h->sub_acc, &h->brd_flag, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
+                      &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_st, &h->attw, &h->spec_pre, &h->spec_acc, &h->spec_out, &h->d3_std, &h->sub_acc, &h->brd_flag, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
                       &h->dbg_status, &h->dbg_e, &h->dbg_t, &h->dbg_rot};
     for (DevBuf *b : bufs) b->release();
     for (auto &l : h->lut) { l.table.release(); l.aux.release(); l.lamtab.release(); }
@@ -694,7 +694,7 @@ static int prepare(RadopHandle *h)
     c.total_bins = bins;
     h->k2_smem = smem;
     // 3 staged columns + per warp: local prefix sums (float), 4 bases per lane (double), edge diameters
-    h->k4_smem = (size_t)3 * nd_max * 4 + (size_t)4 * ((size_t)nd_max * 4 + 128 * 8 + (size_t)((std::max(p.n_vel, 1) + 1) & ~1) * 4);
+    h->k4_smem = (size_t)3 * nd_max * 4 + (size_t)SPEC_WARPS * ((size_t)nd_max * 4 + 128 * 8 + (size_t)((std::max(p.n_vel, 1) + 1) & ~1) * 4);
     return RADOP_OK;
 }
 
@@ -848,6 +848,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         CU(h, h->d3_rho.reserve((size_t)n * 4));
         CU(h, h->d3_st.reserve((size_t)n * 8));
         CU(h, h->attw.reserve((size_t)n * 4));
+        CU(h, h->spec_pre.reserve((size_t)n * sizeof(SpecPre)));
         CU(h, h->spec_acc.reserve(c_rg * c.n_vel * 8));
         CU(h, h->spec_out.reserve(n_rg * c.n_vel * 4));
         if (c.brd_mode) {
@@ -870,10 +871,6 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     static bool attr_done[64] = {false};
     if (!attr_done[h->device & 63]) {
         CU(h, cudaFuncSetAttribute(k_integrate, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        CU(h, cudaFuncSetAttribute(k_gate_fused<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
-        CU(h, cudaFuncSetAttribute(k_gate_fused<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
-        CU(h, cudaFuncSetAttribute(k_gate_fused<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
-        CU(h, cudaFuncSetAttribute(k_gate_fused<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 25));
         CU(h, cudaFuncSetAttribute(k_interp_psd<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_interp_psd<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         CU(h, cudaFuncSetAttribute(k_scatter_pairs, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -895,7 +892,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
     if (c.doppler_scheme == 3) {
         if (smem_a > 200 * 1024) return h->fail(RADOP_ERR_ARG, "too many gates per ray for the spectrum attenuation scan");
         if (h->k4_smem > 200 * 1024) return h->fail(RADOP_ERR_ARG, "velocity array / diameter axis too long for the spectrum kernel");
-        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, k_spectrum<true>, 128, h->k4_smem));
+        CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, k_spectrum<true>, 32 * SPEC_WARPS, h->k4_smem));
     }
     while ((int)h->chunk_done.size() < n_chunks) {
         cudaEvent_t e;
@@ -1002,11 +999,24 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
                     }
                 }
             }
-            const size_t smemf = (size_t)(FUSED_NOBARRIER ? 2 : 1) * W * FUSED_NPART * 32 * 4;
+            const size_t smemf = (size_t)(FUSED_DBUF ? 2 : 1) * W * FUSED_NPART * 32 * 4;
             typedef void (*FusedKernel)(const DevConfig, const ScanDev, const float *, const float *, const FusedArgs);
             const bool dop2 = c.doppler_scheme == 2;
             FusedKernel fk = c.two_moment ? (dop2 ? (FusedKernel)k_gate_fused<true, true> : (FusedKernel)k_gate_fused<true, false>)
                                           : (dop2 ? (FusedKernel)k_gate_fused<false, true> : (FusedKernel)k_gate_fused<false, false>);
+            {   // shared-memory carveout: what the CTAs that the registers allow need for their rows, the rest stays L1
+                static int carve_set[64][4] = {{0}};
+                int &cur = carve_set[h->device & 63][(c.two_moment ? 2 : 0) + (dop2 ? 1 : 0)];
+                cudaFuncAttributes fattr;
+                CU(h, cudaFuncGetAttributes(&fattr, fk));
+                const int by_regs = 65536 / std::max(1, ((fattr.numRegs + 7) / 8 * 8) * 32 * W), by_threads = 2048 / (32 * W);
+                const size_t need = (size_t)std::max(1, std::min(by_regs, by_threads)) * (smemf + fattr.sharedSizeBytes + 1024);
+                const int carve = (int)std::min<size_t>(100, (need * 100 + 228 * 1024 - 1) / (228 * 1024) + 1);
+                if (carve != cur) {
+                    CU(h, cudaFuncSetAttribute(fk, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+                    cur = carve;
+                }
+            }
             int occf = 1;
             CU(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occf, fk, 32 * W, smemf));
             const long long pieces = (long long)nr * n_spans;
@@ -1130,7 +1140,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             a4.sub_weight = scan.sub_weight;
             a4.d3_uh = h->d3_uh.as<double>(); a4.d3_w = h->d3_w.as<float>(); a4.d3_rho = h->d3_rho.as<float>();
             a4.d3_st = h->d3_st.as<float2>(); a4.ray_nyquist = nyq;
-            a4.attw = h->attw.as<float>(); a4.spec_acc = h->spec_acc.as<double>();
+            a4.attw = h->attw.as<float>(); a4.pre = h->spec_pre.as<SpecPre>(); a4.spec_acc = h->spec_acc.as<double>();
             a4.spec_out = h->spec_out.as<float>() + off_rg * c.n_vel;
             a4.out = h->out.as<float>() + off_rg;
             a4.hist = h->hist.as<int>(); a4.bin_start = h->bin_start.as<int>(); a4.chunk_start = h->cost_start.as<int>();
@@ -1145,8 +1155,8 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             CU(h, cudaGetLastError()); ++launches;
             bool nd1024 = true;
             for (int s = 0; s < nsp; ++s) nd1024 = nd1024 && c.sp[s].nd == 1024;
-            if (nd1024) k_spectrum<true><<<std::max(1, occ4) * h->n_sm, 128, h->k4_smem, st>>>(c, a4);
-            else k_spectrum<false><<<std::max(1, occ4) * h->n_sm, 128, h->k4_smem, st>>>(c, a4);
+            if (nd1024) k_spectrum<true><<<std::max(1, occ4) * h->n_sm, 32 * SPEC_WARPS, h->k4_smem, st>>>(c, a4);
+            else k_spectrum<false><<<std::max(1, occ4) * h->n_sm, 32 * SPEC_WARPS, h->k4_smem, st>>>(c, a4);
             CU(h, cudaGetLastError()); ++launches;
             if (c.brd_mode) {
                 k_spectrum_broaden<<<(unsigned)((nc + 3) / 4), 128, smem_b, st>>>(c, a4, nc);

@@ -26,14 +26,17 @@
 #define FUSED_MAX_WARPS 9     // warps per CTA (a build-time experiment knob together with FUSED_MIN_CTAS: registers per thread)
 #endif
 #ifndef FUSED_MIN_CTAS
-#define FUSED_MIN_CTAS 4      // 9 warps x 4 CTAs -> 56 registers: the fastest of the measured shapes (profiles/r02_fused_variants.md)
+#define FUSED_MIN_CTAS 3      // 9 warps x 3 CTAs -> 72 registers (4 CTAs -> 56 registers and more spills: 1.7 % slower)
 #endif
-#ifndef FUSED_NOBARRIER
-#define FUSED_NOBARRIER 0     // 1: the warps of a CTA hand their rows over through shared-memory flags instead of a CTA-wide
-                              // barrier (measured 60 % slower: spinning warps and twice the shared memory; kept for the record)
+#ifndef FUSED_DBUF
+#define FUSED_DBUF 1          // 1: two row buffers, ONE CTA barrier per piece, the reducing warp rotates (0: one buffer, two
+                              // barriers).  Measured at cfg 3 (profiles/r02_fused_variants.md): 72 registers 3.60 ms with, 3.63 ms
+                              // without; 56 registers 3.74 / 3.67 ms.  A barrier-free hand-over through shared-memory flags
+                              // was 60 % slower (spinning warps).
 #endif
 #ifndef FUSED_UNROLL_COLS
-#define FUSED_UNROLL_COLS 0   // 1: the four neighbour columns of the interpolation as straight-line code
+#define FUSED_UNROLL_COLS 1   // 1: the four neighbour columns of the interpolation as straight-line code (measured 3.68 ms
+                              // against 3.95 ms rolled at 56 registers)
 #endif
 #define FUSED_NPART 10        // b c p q kd s9 s11 | sum rv w | sum w | sum mask
 
@@ -397,62 +400,43 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
              const float *__restrict__ fields, const __grid_constant__ FusedArgs A)
 {
     constexpr int NV = TWO_MOM ? 15 : 8;
-    extern __shared__ float s_part_raw[];                  // [2][W][FUSED_NPART][32] (one buffer with the CTA barrier)
-    __shared__ int s_piece[2];
-#if FUSED_NOBARRIER
-    // Hand-over of the rows without a CTA-wide barrier.  The k-th piece of this CTA uses row buffer k & 1.
-    //   s_pid[k & 3] / s_seq[k & 3]: id of the k-th piece, published by warp 0 one piece ahead (a ring of four: the
-    //   slowest warp is at most two pieces behind warp 0);
-    //   s_cnt[b]: rows written into buffer b so far (all pieces); s_red[b]: last k whose buffer b has been reduced.
-    // A warp may run one piece ahead of the reduction; the reducing warp rotates with k.
-    __shared__ volatile int s_pid[4], s_seq[4], s_cnt[2], s_red[2];
-#endif
+    extern __shared__ float s_part_raw[];                  // [FUSED_DBUF ? 2 : 1][W][FUSED_NPART][32]
+    __shared__ int s_piece[2][2];
     __shared__ unsigned s_pairs[RADOP_NSPECIES_MAX];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, W = blockDim.x >> 5;
     const int ng = cfg.n_gates, n_sub = cfg.n_sub, n_spans = A.n_spans;
     const int n_pieces = cfg.n_rays * n_spans;
     const float qnan = __int_as_float(0x7fc00000);
     if (threadIdx.x < RADOP_NSPECIES_MAX) s_pairs[threadIdx.x] = 0u;
-#if FUSED_NOBARRIER
-    const int n_work = min(W, n_sub);                      // warps that own sub-beams
-    if (threadIdx.x == 0) {
-        s_pid[0] = atomicAdd(A.flags + 3, 1);
-        s_seq[0] = 0; s_seq[1] = -1; s_seq[2] = -1; s_seq[3] = -1;
-        s_cnt[0] = 0; s_cnt[1] = 0;
-        s_red[0] = -2; s_red[1] = -1;
-    }
+    auto fetch_piece = [&](int slot) {                     // thread 0: next piece from the global counter
+        const int pc = atomicAdd(A.flags + 3, 1);
+        const int r = pc / n_spans;
+        s_piece[slot][0] = pc < n_pieces ? r : -1;
+        s_piece[slot][1] = pc - r * n_spans;
+    };
+#if FUSED_DBUF
+    if (threadIdx.x == 0) fetch_piece(0);
     __syncthreads();
-    (void)s_piece;
 #endif
 
     for (int k = 0;; ++k) {
-#if FUSED_NOBARRIER
+#if FUSED_DBUF
+        // Piece k uses row buffer k & 1 and piece slot k & 1.  The only barrier of the iteration is the one after the rows
+        // are written; the reducing warp (k mod the working warps) adds them up while the others start piece k + 1 in the
+        // OTHER buffer, and it has finished before it reaches the next barrier -- after which buffer k & 1 is written again.
         const int buf = k & 1;
         float (*s_part)[FUSED_NPART][32] = reinterpret_cast<float (*)[FUSED_NPART][32]>(s_part_raw) + (size_t)buf * W;
-        if (lane == 0) while (s_seq[k & 3] != k) __nanosleep(20);
-        __syncwarp();
-        const int pc = s_pid[k & 3];
-        if (pc >= n_pieces) break;
-        if (threadIdx.x == 0) {                 // the next piece, one ahead (that slot was last read for piece k - 3)
-            const int nxt = atomicAdd(A.flags + 3, 1);
-            s_pid[(k + 1) & 3] = nxt;
-            __threadfence_block();
-            s_seq[(k + 1) & 3] = k + 1;
-        }
-        const int ray = pc / n_spans, span = pc - ray * n_spans;
-        if (lane == 0) while (s_red[buf] != k - 2) __nanosleep(20);     // buffer free: piece k - 2 has been reduced
-        __syncwarp();
+        const int ray = s_piece[buf][0], span = s_piece[buf][1];
+        if (ray < 0) break;
+        if (threadIdx.x == 0) fetch_piece(buf ^ 1);        // slot last read at the top of iteration k - 1, before its barrier
+        const int reducer = k % min(W, n_sub);
 #else
         float (*s_part)[FUSED_NPART][32] = reinterpret_cast<float (*)[FUSED_NPART][32]>(s_part_raw);
-        if (threadIdx.x == 0) {
-            const int pc = atomicAdd(A.flags + 3, 1);
-            const int r = pc / n_spans;
-            s_piece[0] = pc < n_pieces ? r : -1;
-            s_piece[1] = pc - r * n_spans;
-        }
+        if (threadIdx.x == 0) fetch_piece(0);
         __syncthreads();
-        const int ray = s_piece[0], span = s_piece[1];
+        const int ray = s_piece[0][0], span = s_piece[0][1];
         if (ray < 0) break;
+        const int reducer = 0;
 #endif
         const int g = span * 32 + lane;
         const bool in_range = g < ng;
@@ -630,23 +614,8 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
                 }
             }
         }
-#if FUSED_NOBARRIER
-        const int reducer = k % n_work;
-        if (warp < n_work) {
-            __threadfence_block();
-            __syncwarp();
-            if (lane == 0) atomicAdd((int *)&s_cnt[buf], 1);
-        }
-        if (warp == reducer) {
-            if (lane == 0) while (s_cnt[buf] != n_work * (k / 2 + 1)) __nanosleep(20);
-            __syncwarp();
-            __threadfence_block();
-        }
-        if (warp == reducer && in_range) {
-#else
         __syncthreads();
-        if (warp == 0 && in_range) {
-#endif
+        if (warp == reducer && in_range) {
             float t[FUSED_NPART];
 #pragma unroll
             for (int i = 0; i < FUSED_NPART; ++i) t[i] = s_part[0][i][lane];
@@ -663,13 +632,6 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
             if (mk > -1.f && mk <= 0.f) mk = 0.f;
             A.mask_out[rg] = mk;
         }
-#if FUSED_NOBARRIER
-        if (warp == reducer) {
-            __syncwarp();
-            __threadfence_block();
-            if (lane == 0) s_red[buf] = k;
-        }
-#endif
     }
     __syncthreads();
     if (threadIdx.x < cfg.n_species && s_pairs[threadIdx.x]) atomicAdd(A.n_pairs + threadIdx.x, (unsigned long long)s_pairs[threadIdx.x]);

@@ -2661,6 +2661,17 @@ k_ray_epilogue(const __grid_constant__ DevConfig cfg, K3Args A)
 // K4: Doppler spectrum (scheme 3; get_doppler_spectrum doppler_scatter.py:598-725,
 //     get_diameter_from_rad_vel :546-595, get_refl doppler_c.c:11-32, attenuation :372-383)
 // ------------------------------------------------------------------------------------------
+// Per sub-beam gate quantities of get_diameter_from_rad_vel (doppler_scatter.py:571-585) that every (gate, species)
+// pair of the gate shares; k_spectrum used to recompute them per pair on all 32 lanes (a fifth of its instructions).
+struct __align__(16) SpecPre {
+    double c0;        // W + U_h / tan(theta)
+    double inv_sin;   // 1 / sin(theta)
+    float inv_rho;    // 1 / sqrt(rho / rho_gate0) in float32, as the reference has it
+    float p;          // velocity-bin coordinate of "fall speed 0": (c0 sin(theta) - v_min) / v_res; NaN: scan all bins
+    float attw;       // quadrature weight x attenuation of the sub-beam at the gate
+    uint32_t rg;      // ray gate (ray * n_gates + gate) of the chunk
+};
+
 struct K4Args {
     const int8_t *mask;
     const uint8_t *active;
@@ -2671,6 +2682,7 @@ struct K4Args {
     const float2 *d3_st;
     const float *ray_nyquist;
     float *attw;          // [sbg] quadrature weight x attenuation factor of the sub-beam at the gate
+    struct SpecPre *pre;  // [sbg] what k_spectrum needs per sub-beam gate, prepared once (k_beam_attenuation)
     double *spec_acc;     // [ray][gate][n_vel] float64 accumulator (atomics)
     // broadening (doppler_scatter.py:357-367): spectra are kept per sub-beam until they are filtered
     const double *d3_std; // [sbg] added spectral width, or null
@@ -2730,7 +2742,25 @@ k_beam_attenuation(const __grid_constant__ DevConfig cfg, K4Args A)
             __syncwarp();
         }
     }
-    for (int g = lane; g < ng; g += 32) A.attw[base + g] = w * exp10f(-0.1f * total[g]);
+    const float nanf_ = __int_as_float(0x7fc00000);
+    const float rho0 = A.d3_rho[base];
+    const uint32_t rg0 = (uint32_t)(rq / cfg.n_sub) * (uint32_t)ng;
+    for (int g = lane; g < ng; g += 32) {
+        const float aw = w * exp10f(-0.1f * total[g]);
+        A.attw[base + g] = aw;
+        // np.sin / np.tan of the float32 angle are float32 (doppler_scatter.py:571-575)
+        const float2 st = A.d3_st[base + g];
+        const double sin_t = (double)st.x, inv_tan = 1.0 / (double)st.y;
+        const float rho_corr = sqrtf(__fdiv_rn(A.d3_rho[base + g], rho0));
+        SpecPre P;
+        P.inv_sin = 1.0 / sin_t;
+        P.inv_rho = __fdiv_rn(1.0f, rho_corr);
+        P.c0 = (double)A.d3_w[base + g] + A.d3_uh[base + g] * inv_tan;
+        P.p = (sin_t > 0.0 && P.inv_rho > 0.f && isfinite(P.c0)) ? (float)((P.c0 * sin_t - cfg.vel_min) * cfg.inv_vel_res) : nanf_;
+        P.attw = aw;
+        P.rg = rg0 + (uint32_t)g;
+        A.pre[base + g] = P;
+    }
     if (A.d3_std) {
         // the sub-beam is broadened if np.sum(add_specwidth) > 0: a NaN gate (EDR outside the model
         // domain) switches the broadening of the whole sub-beam off (doppler_scatter.py:366)
@@ -2758,10 +2788,12 @@ extern __shared__ __align__(16) unsigned char s_k4[];
 // running sums of one lane's samples [k0, k0 + cpl): four independent chains of cpl / 4
 // consecutive samples each (latency of the float64 adds), local prefix stored in float32
 #define SPEC_SUB 4
+// SPEC_WARPS warps per CTA share the three staged table columns (12 KB); each warp owns 5.6 KB (prefix sums, chain bases,
+// edge diameters).  Shared memory limits the warps per SM: 16-warp CTAs fit 32 warps where 4-warp CTAs fitted 24.
 // ND1024: every table has 1024 diameters (compute_lut_sz.py:69, the only size the reference generates): the index
 // arithmetic of the chains (k / cpl, k % cpl, k / sub) becomes shifts and masks instead of integer divisions
 template <bool ND1024>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(32 * SPEC_WARPS)
 k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
 {
     __shared__ int s_unit;
@@ -2821,32 +2853,27 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
         for (int jt = j0; jt < j1; ++jt) {
             const int first = A.bin_start[b] + jt * RADOP_TILE;
             const int n_here = min(RADOP_TILE, cnt - jt * RADOP_TILE);
-            for (int i = wid; i < n_here; i += 4) {
+            for (int i = wid; i < n_here; i += SPEC_WARPS) {
                 const PairRec rec = A.rec[first + i];
                 const uint32_t sbg = rec.sbg;
-                const unsigned rq = sbg / (unsigned)ng;
-                const int g = (int)(sbg - rq * (unsigned)ng);
-                const size_t rg = (size_t)(rq / (unsigned)cfg.n_sub) * ng + g;
                 const unsigned act = A.active[sbg];
+                const SpecPre P = A.pre[sbg];
+                const size_t rg = P.rg;
                 // ---- 1. diameters at the velocity-bin edges -----------------------------------
                 int j_a, j_b;
                 {
-                    // np.sin / np.tan of the float32 angle are float32 (doppler_scatter.py:571-575)
-                    const float2 st = A.d3_st[sbg];
-                    const double sin_t = (double)st.x, inv_sin = 1.0 / sin_t, inv_tan = 1.0 / (double)st.y;
-                    const float rho_corr = sqrtf(__fdiv_rn(A.d3_rho[sbg], A.d3_rho[sbg - g]));
-                    const float inv_rho_f = __fdiv_rn(1.0f, rho_corr);
-                    const double inv_rho = (double)inv_rho_f;
-                    const double c0 = (double)A.d3_w[sbg] + A.d3_uh[sbg] * inv_tan;
+                    const double inv_sin = P.inv_sin, inv_rho = (double)P.inv_rho, c0 = P.c0;
                     // wh_j = inv_rho (c0 - v_j / sin) falls with j: only the velocities between
                     // "faster than the largest particle" (D = d_max, empty bins) and "wh < 0"
                     // (no bin) can hold power.  Outside the normal case the whole array is done.
+                    // Bounds in float32 with a bin of slack on either side (they only have to enclose the bins with power).
                     j_a = 0; j_b = nvel - 1;
-                    if (sin_t > 0.0 && inv_rho_f > 0.f && isfinite(c0)) {
-                        const double ja = floor(((c0 - S.wh_hi * (double)rho_corr * 1.000001) * sin_t - cfg.vel_min) * cfg.inv_vel_res) - 1.0;
-                        const double jb = floor((c0 * sin_t - cfg.vel_min) * cfg.inv_vel_res) + 2.0;
-                        j_a = (int)fmin(fmax(ja, 0.0), (double)(nvel - 1));
-                        j_b = (int)fmin(fmax(jb, 0.0), (double)(nvel - 1));
+                    if (!isnan(P.p)) {
+                        // bins per unit of fall speed: rho_corr sin(theta) / v_res = 1 / (inv_rho inv_sin v_res)
+                        const float qv = __fdividef(1.000002f * (float)cfg.inv_vel_res, P.inv_rho * (float)inv_sin);
+                        const float ja = floorf(P.p - (float)S.wh_hi * qv - 0.02f) - 1.f, jb = floorf(P.p + 0.02f) + 2.f;
+                        j_a = (int)fminf(fmaxf(ja, 0.f), (float)(nvel - 1));
+                        j_b = (int)fminf(fmaxf(jb, 0.f), (float)(nvel - 1));
                     }
                     for (int j = j_a + lane; j <= j_b; j += 32) {
                         const double v = cfg.vel_min + (double)j * cfg.vel_res;
@@ -2942,7 +2969,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                 __syncwarp();
                 // ---- 3. velocity bins -----------------------------------------------------------
                 const double scale = 6.283185307179586 * (double)n0 * (double)zfac3 * (double)spec_scale *
-                                     (A.sub_acc ? 1.0 : (double)A.attw[sbg]);
+                                     (A.sub_acc ? 1.0 : (double)P.attw);
                 double *dst = A.sub_acc ? A.sub_acc + (size_t)sbg * nvel : A.spec_acc + rg * nvel;
                 for (int j = j_a + lane; j < j_b; j += 32) {
                     const float Dj = s_D[j];

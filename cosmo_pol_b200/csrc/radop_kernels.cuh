@@ -9,6 +9,9 @@
 #define RADOP_TILE_G 8          // (sub-beam gate, species) pairs per thread and tile
 #define RADOP_TILE (RADOP_TILE_THREADS * RADOP_TILE_G)
 #define RADOP_HBLOCK 32         // diameters per Horner block (re-anchoring period)
+#ifndef SPEC_WARPS
+#define SPEC_WARPS 16           // warps per CTA of the Doppler-spectrum kernel
+#endif
 #define RADOP_CHUNK 2           // tiles per dynamically scheduled work unit of the integration kernel
 #define RADOP_NC 7              // combined columns that carry data (the 8th of a row is padding)
 #define RADOP_KEY_NONE 0xFFFFu

@@ -1045,15 +1045,20 @@ def test_cfg5_doppler_spectra_on_cosmo1_sized_domain():
     strong_g = tot > 1e-25
     assert strong_g.sum() > 1e6 and np.max(np.abs(rv[strong_g] - mean_v[strong_g])) < 2e-3
     zh = out['ZH']
-    assert np.array_equal(np.isnan(zh), ~has) or np.sum(np.isnan(zh) != ~has) < 1e-3 * has.size
+    # a gate can have reflectivity and an EMPTY spectrum (every velocity bin outside the fall-speed range of its
+    # hydrometeors: 9 % of the gates here, in the oracle as on the device -- ray (0, -0.2) of the sample below is one of
+    # them), but not the reverse
+    assert np.sum(np.isnan(zh) & (tot > 1e-25)) == 0
     chk = (float(np.nansum(zh[::11])), float(np.nansum(sp[::53])))
     # ray sample against the oracle (two low rays through rain / snow, one at 20 deg)
-    raz, rel = np.array([25., 200., 311.]), np.array([1.0, 4.5, 20.0])
-    idx = [int(np.where((az == a) & (el == e))[0][0]) for a, e in zip(raz, rel)]
+    raz, rel = np.array([25., 200., 311., 0.]), np.array([1.0, 4.5, 20.0, -0.2])
+    idx = [int(np.where((az == a) & (np.abs(el - e) < 1e-9))[0][0]) for a, e in zip(raz, rel)]
     pm, pl = plain(model, luts)
     ref = O.simulate_scan(pm, pl, oracle_cfg(op), raz, rel, accum='f64', sensitivity_cut=True)
     got = {k: np.asarray(out[k])[idx] for k in ('ZH', 'ZV', 'ZDR', 'KDP', 'RHOHV', 'ATT_H', 'ATT_V', 'PHIDP', 'DELTA_HV', 'RVEL', 'DSPECTRUM')}
     assert_observables_close(got, ref, what='cfg5')
+    gt, rt = np.nansum(got['DSPECTRUM'], axis=2, dtype=np.float64), np.nansum(ref['DSPECTRUM'], axis=2, dtype=np.float64)
+    assert np.all(gt[rt == 0] == 0) and np.all(gt[rt > 1e-25] > 0) and np.sum(np.isfinite(ref['ZH']) & (rt == 0)) > 10
     strong = _spectrum_close(got['DSPECTRUM'], ref['DSPECTRUM'], ref['ZH'], 'cfg5')
     ok = np.isfinite(ref['RVEL']) & strong
     assert ok.sum() > 100 and np.max(np.abs(got['RVEL'][ok] - ref['RVEL'][ok])) < 0.05
