@@ -83,13 +83,15 @@ def workload_config(world, scaling):
                         '3x3 GH sub-beams, synthetic COSMO grid 60x400x400 @0.02deg'
                         + ('' if scaling == 'strong' else '; one such volume PER GPU'),
             'rays_per_gpu': rays, 'rays_total': rays * world, 'gates': 500, 'sub_beams': 9, 'species': 'R,S,G,I',
-            'parallelism': 'rays dealt block-cyclically (4 rays) to {} GPU(s), fields+tables replicated, NCCL gather of the observables '
-                           'to rank 0 on a side stream (step k gathered beside the kernels of step k+1, all gathers inside '
-                           'the timed region; cosmo_pol_b200.parallel.RayGather)'.format(world)
+            'parallelism': 'the ONE volume\'s rays dealt block-cyclically (4 rays) to {} GPU(s), fields+tables replicated; no device-side '
+                           'collective: every rank delivers its rays to host arrays shared by the ranks over its own PCIe link '
+                           '(cosmo_pol_b200.parallel.HostExchange, in the e2e leg); the device-timed steps are the kernels of the '
+                           'slowest rank'.format(world)
                            if world > 1 else 'single GPU',
             'scaling_mode': scaling,
-            'l2': 'no explicit flush: one step streams ~3 GB of per-gate work buffers (K1 outputs, sz_out) plus a 614 MB '
-                  'field array, far larger than the 126 MB L2',
+            'l2': 'explicit flush: 256 MB written on the launching stream before every timed step, outside the step\'s CUDA-event '
+                  'pair (the model columns under the radar footprint, ~60 MB of the 614 MB field array, would otherwise stay '
+                  'resident in the 126 MB L2 between steps)',
             'integration': 'diameter integral through lambda-transformed tables built at table upload (radop_set_integration 0, '
                            'the library default); --integration direct times the per-diameter sums instead'}
 
@@ -262,13 +264,14 @@ def run_reference(args):
 # GPU arm
 # ------------------------------------------------------------------------------------------
 def e2e_breakdown(op, eng, az, el, rank, world, local):
-    """Wall-clock stages of one sharded product call (the stages of RadarOperator._simulate_sharded, timed one
-    after the other with a device synchronisation between them): where the end-to-end time goes at N > 1."""
+    """Wall-clock stages of one sharded product call (the stages of RadarOperator._simulate_sharded_host, timed one after
+    the other, max over the ranks): where the end-to-end time goes at N > 1.  `call` is the whole radop_simulate of the
+    shard into the shared host arrays (its copies overlap its kernels chunk by chunk, so it is less than the sum)."""
     import torch
     import torch.distributed as dist
     from cosmo_pol_b200 import parallel
-    from cosmo_pol_b200._abi import OUT_NAMES, BUF_OBS
     mine = parallel.shard_indices(len(az), rank, world)
+    X = op._exchange
     t = {}
     dist.barrier()
     c = time.perf_counter()
@@ -281,19 +284,12 @@ def e2e_breakdown(op, eng, az, el, rank, world, local):
     eng.finish()
     t['kernels_and_flags'] = time.perf_counter() - c
     c = time.perf_counter()
-    parallel.agree_status(0, local)
-    t['status_allreduce'] = time.perf_counter() - c
+    eng.simulate_into(scan, X.arrays(), rank, world, parallel.RAY_BLOCK, want_latlon=False)
+    t['call_h2d_kernels_d2h'] = time.perf_counter() - c
     c = time.perf_counter()
-    g = op._gather or parallel.RayGather('root', depth=1)
-    ptr, _ = eng.device_buffer(BUF_OBS)
-    stream = torch.cuda.ExternalStream(eng.stream_ptr(), device=torch.device('cuda', local))
-    pend = g.launch(parallel.device_tensor(ptr, (len(OUT_NAMES) + 1, len(mine), scan.n_gates), local), len(az), stream)
-    g.wait(pend)
-    torch.cuda.synchronize()
-    t['nccl_gather'] = time.perf_counter() - c
-    c = time.perf_counter()
-    g.to_host(pend, key=BUF_OBS)
-    t['d2h_rank0'] = time.perf_counter() - c
+    X.barrier(0)
+    X.next_call()
+    t['host_barrier'] = time.perf_counter() - c
     tt = torch.tensor([t[k] for k in sorted(t)], dtype=torch.float64, device='cuda:{}'.format(local))
     dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     return {k: 1e3 * float(v) for k, v in zip(sorted(t), tt)}
@@ -348,6 +344,7 @@ def run_ours(args):
     stream = torch.cuda.ExternalStream(eng.stream_ptr(), device=dev)
     n_out = len(OUT_NAMES) + 1
     gather = parallel.RayGather('root', depth=2)
+    l2_flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
     def barrier():
         if world > 1:
@@ -355,15 +352,17 @@ def run_ours(args):
         torch.cuda.synchronize()
         eng.synchronize()
 
-    def device_run(scan, n_total, steps, warmup, timing):
-        """K device-timed steps of radop_execute on the staged scan, every step followed by the gather of its
-        observables to rank 0 (N > 1); returns (ms for `steps` steps, stats)."""
+    def device_run(scan, n_total, steps, warmup, timing, with_gather=False):
+        """K device-timed steps of radop_execute on the staged scan; returns (ms for `steps` steps, stats).  The product
+        path has no device-side collective (every rank delivers its rays to the host itself, see the e2e leg), so the
+        headline steps are the kernels alone; with_gather adds the NCCL gather of every step's observables to rank 0
+        (RadarOperator(gather_transport='nccl')), reported as a secondary record."""
         eng.stage(scan)
         last = [None]
 
         def step():
             eng.execute()
-            if world > 1:
+            if world > 1 and with_gather:
                 ptr, nr, ng = eng.device_outputs()
                 last[0] = gather.launch(parallel.device_tensor(ptr, (n_out, nr, ng), local), n_total, stream)
 
@@ -378,14 +377,19 @@ def run_ours(args):
         if timing:
             eng.enable_timing(True)
             barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for _ in range(steps):
-            step()
+        # every timed step starts with a cold L2: 256 MB are written on the same stream before it, outside its event pair
+        # (the 60 MB of model columns under the radar's footprint would otherwise stay L2-resident from step to step)
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        with torch.cuda.stream(stream):
+            for e0, e1 in ev:
+                if not with_gather:
+                    l2_flush.zero_()
+                e0.record(stream)
+                step()
+                e1.record(stream)
         join()
-        e1.record(stream)
         barrier()
-        ms = e0.elapsed_time(e1)
+        ms = sum(e0.elapsed_time(e1) for e0, e1 in ev) if not with_gather else ev[0][0].elapsed_time(ev[-1][1])
         st = eng.stats() if timing else None
         if timing:
             eng.enable_timing(False)
@@ -445,6 +449,12 @@ def run_ours(args):
         (sbg2,) = reduce_sum(scan2.n_subbeam_gates)
         other = {'scaling': 'weak' if scaling == 'strong' else 'strong', 'value': sbg2 / (ms2 * 1e-3 / k2), 'unit': UNIT,
                  'ms_per_step': ms2 / k2, 'steps': k2, 'rays_per_gpu': scan2.n_rays}
+        # the headline workload again with the device-side NCCL gather of every step's observables to rank 0
+        ms3, _ = device_run(scan, n_total, k2, 3, False, with_gather=True)
+        (ms3,) = reduce_max(ms3)
+        other['with_nccl_gather_to_rank0'] = {'scaling': scaling, 'value': total_sbg / (ms3 * 1e-3 / k2), 'ms_per_step': ms3 / k2,
+                                              'steps': k2, 'note': "RadarOperator(gather_transport='nccl'): 8 NCCL CTAs beside the "
+                                              'persistent kernels; not on the default product path'}
         eng.stage(scan)
 
     # ---- end to end: host buffers in, host buffers out --------------------------------------
@@ -470,8 +480,9 @@ def run_ours(args):
         d2h_first = int(sum(a.nbytes for a in arrays.values()))
     else:
         h2d = scan.bytes_in()                       # per rank: its block of the ray list + the trajectories
-        d2h = int(sum(arrays[k].nbytes for k in OUT_NAMES + ['mask'])) if rank == 0 else 0
-        d2h_first = d2h + (int(arrays['lat'].nbytes + arrays['lon'].nbytes) if rank == 0 else 0)
+        (d2h,) = reduce_sum(int(eng.last_d2h_bytes))   # all ranks together: every rank copies its own rays to the host
+        d2h = int(d2h)
+        d2h_first = d2h + n_full * 500 * 16            # + float64 lat / lon, first call on a ray list only
     checksum = float(np.nansum(arrays['ZH'][::97])) if arrays is not None else 0.0
     st_e2e = None
     if world > 1:
@@ -601,8 +612,10 @@ def run_ours(args):
                 'latlon': 'gate positions (float64 lat/lon, 58 MB per volume) depend on the scan geometry only: copied by the '
                           'first call on a ray list (d2h_bytes_first_call), kept in the pinned buffers afterwards',
                 'call': 'radop_simulate (C-ABI, host buffers)' if world == 1 else
-                        'RadarOperator.simulate_rays on the ONE 7200-ray volume, sharded over the ranks, result on rank 0 '
-                        '(h2d per rank, d2h on rank 0)',
+                        'RadarOperator.simulate_rays on the ONE 7200-ray volume, sharded over the ranks: every rank runs '
+                        'radop_simulate on its rays with output pointers into host arrays shared by the ranks '
+                        '(radop_set_output_blocks), then a barrier in shared memory; result read on rank 0 '
+                        '(h2d per rank, d2h summed over the ranks)',
                 'breakdown_ms': st_e2e},
         'other_scaling': other,
         'gpu_launches': launches,

@@ -29,7 +29,7 @@ EXPORTS = ['radop_abi_version', 'radop_create', 'radop_destroy', 'radop_last_err
            'radop_get_stats', 'radop_enable_timing', 'radop_debug_indices', 'radop_measure_fp32_peak',
            'radop_get_all_radar_pts', 'radop_selftest_division', 'radop_set_chunk', 'radop_set_overlap_threshold',
            'radop_set_geodesy', 'radop_get_geodesy', 'radop_set_integration', 'radop_get_integration', 'radop_debug_integration',
-           'radop_set_search', 'radop_sizeof', 'radop_device_buffer', 'radop_get_refl', 'radop_get_refl_noalloc', 'radop_set_pipeline', 'radop_get_pipeline', 'radop_set_tuning']
+           'radop_set_search', 'radop_sizeof', 'radop_device_buffer', 'radop_get_refl', 'radop_get_refl_noalloc', 'radop_set_output_blocks', 'radop_host_register', 'radop_host_unregister', 'radop_set_pipeline', 'radop_get_pipeline', 'radop_set_tuning']
 
 BUF_OBS, BUF_LAT, BUF_LON, BUF_MODEL, BUF_DSPECTRUM = range(5)
 NOALLOC_SCRATCH_BYTES = 4 << 20      # RADOP_NOALLOC_SCRATCH_BYTES
@@ -143,6 +143,9 @@ def load_library():
     lib.radop_sizeof.argtypes = [C.c_int]
     lib.radop_device_buffer.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
     lib.radop_get_refl.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 8
+    lib.radop_set_output_blocks.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    lib.radop_host_register.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+    lib.radop_host_unregister.argtypes = [C.c_void_p, C.c_void_p]
     lib.radop_get_refl_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 8
     if lib.radop_abi_version() != RADOP_ABI_VERSION:
         raise RadopError('libradop.so ABI version mismatch')
@@ -438,6 +441,47 @@ class Engine(object):
             self._latlon_key = key
         self.last_d2h_bytes = int(sum(a.nbytes for k, a in arrays.items() if not (reuse and k in ('lat', 'lon'))))
         return arrays
+
+    def host_register(self, array):
+        """Page-lock a host array the caller owns (the ranks' shared-memory segment); returns False where it fails."""
+        try:
+            self._check(self.lib.radop_host_register(self.h, C.c_void_p(array.ctypes.data), C.c_int64(array.nbytes)))
+            return True
+        except RadopError:
+            return False
+
+    def host_unregister(self, array):
+        self.lib.radop_host_unregister(self.h, C.c_void_p(array.ctypes.data))
+
+    def simulate_into(self, scan, arrays, rank, world, block, want_latlon=True):
+        """radop_simulate of this rank's rays straight into host arrays that hold the WHOLE scan (rows = rays of all
+        ranks, dealt in blocks of `block`; radop_set_output_blocks).  arrays: name -> [n_total_rays, ...] for the
+        observable names, 'mask', 'lat', 'lon', 'DSPECTRUM' and model variables (any subset)."""
+        out = RadopOut()
+        row0 = rank * block
+
+        def at(a):
+            return a[row0:].ctypes.data if a is not None else None
+        for i, name in enumerate(OUT_NAMES):
+            if name in arrays:
+                out.obs[i] = at(arrays[name])
+        out.mask = at(arrays.get('mask'))
+        if want_latlon:
+            out.lat, out.lon = at(arrays.get('lat')), at(arrays.get('lon'))
+        if 'DSPECTRUM' in arrays:
+            out.dspectrum = at(arrays['DSPECTRUM'])
+        for name, slot in self.model_output_slots().items():
+            if name in arrays:
+                out.model[slot] = at(arrays[name])
+        s = scan.as_struct()
+        self._check(self.lib.radop_set_output_blocks(self.h, int(block), int(block * world)))
+        try:
+            self._check(self.lib.radop_simulate(self.h, C.byref(s), C.byref(out)))
+        finally:
+            self.lib.radop_set_output_blocks(self.h, 0, 0)
+        self._latlon_key = None        # the pinned buffers of make_out do not hold this scan's positions
+        self.last_d2h_bytes = int(sum(scan.n_rays * (a.nbytes // max(1, a.shape[0])) for k, a in arrays.items()
+                                      if want_latlon or k not in ('lat', 'lon')))
 
     def stage(self, scan):
         s = scan.as_struct()

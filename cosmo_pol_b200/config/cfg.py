@@ -42,7 +42,7 @@ VALID_VALUES = {
               'nyquist_velocity': [None, str],
               'antenna_speed': Range(1E-6, 10.)},
     'refraction': {'scheme': [1, 2]},
-    'integration': {'scheme': [1, 2, 3, 4, 'ml'],
+    'integration': {'scheme': [1, 2, 3, 4, 5, 'ml'],     # cfg.py:101 lists [1, 2, 3, 4, 'ml']; 5 exists in interpolation.py:276
                     'nv_GH': range(1, 31, 2), 'nh_GH': range(1, 31, 2),
                     'n_gaussians': range(1, 13, 2),
                     'weight_threshold': Range(0.0001, 1.),
@@ -116,6 +116,17 @@ def sanity_check(config):
 
     if isinstance(config['radar']['nyquist_velocity'], str):
         config['radar']['nyquist_velocity'] = nyquist_interpolator(config['radar']['nyquist_velocity'])
+
+    # cfg.py:241-262: an antenna diagram file is fitted with a sum of Gaussians, whose parameters integration scheme 2
+    # samples (the reference tries this for every configuration, the key being always present; here only when a file is
+    # named and no parameters were given)
+    integ = config['integration']
+    if isinstance(integ.get('antenna_diagram'), str) and integ.get('antenna_params') is None:
+        from .antenna_fit import optimize_gaussians
+        import numpy as np
+        data = np.genfromtxt(integ['antenna_diagram'], delimiter=',')
+        integ['antenna_params'] = optimize_gaussians(data[:, 0], 10 * np.log10((10 ** (0.1 * data[:, 1])) ** 2),
+                                                     int(integ['n_gaussians']))
 
     if config['radar']['K_squared'] is None:
         from ..hydrometeors import dielectric

@@ -105,6 +105,7 @@ struct RadopHandle_ {
     int pipeline_mode = 0;       // 0: fused kernel when the configuration allows it, 1: staged pipeline always
     int fused_warps = 0;         // warps per CTA of the fused kernel (0: chosen from the sub-beam count)
     bool last_fused = false;
+    int out_block = 0, out_pitch = 0;   // radop_set_output_blocks: host rows of local ray i = (i / block) * pitch + i % block
     bool geo_ready = false;      // geo_poly holds the polynomials of the staged scan (whole ray list)
     bool geo_poly_conv = false;  // ... and every series converged
     DevBuf traj_sc, traj_ie, f_wsum, f_ice, f_cnt;
@@ -699,26 +700,57 @@ static int prepare(RadopHandle *h)
 }
 
 // Device -> host copies of the rays [r0, r0 + nr) of every requested output, on stream st.
+// Rows [r0, r0 + nr) of a device array [n_rays][row_bytes] to the caller's host array.  Normally the host array has the
+// same layout; with radop_set_output_blocks(block, pitch) the caller's array interleaves the rays of several handles
+// (the ranks of a multi-GPU run dealing blocks of `block` rays in turn): local ray i lands on host row
+// (i / block) * pitch + i % block, whole blocks as ONE strided copy (cudaMemcpy2DAsync: the copy engine does the striding).
+static cudaError_t copy_rows(RadopHandle *h, void *dst_, const void *src_, size_t row_bytes, int r0, int nr, cudaStream_t st)
+{
+    char *dst = static_cast<char *>(dst_);
+    const char *src = static_cast<const char *>(src_);
+    const int B = h->out_block;
+    if (B <= 0) return cudaMemcpyAsync(dst + (size_t)r0 * row_bytes, src + (size_t)r0 * row_bytes, (size_t)nr * row_bytes, cudaMemcpyDeviceToHost, st);
+    const size_t P = (size_t)h->out_pitch;
+    int r = r0;
+    const int end = r0 + nr;
+    cudaError_t e = cudaSuccess;
+    if (r % B && r < end) {               // up to the next block boundary
+        const int n = std::min(B - r % B, end - r);
+        e = cudaMemcpyAsync(dst + ((size_t)(r / B) * P + r % B) * row_bytes, src + (size_t)r * row_bytes, (size_t)n * row_bytes, cudaMemcpyDeviceToHost, st);
+        if (e != cudaSuccess) return e;
+        r += n;
+    }
+    const int full = (end - r) / B;
+    if (full > 0) {
+        e = cudaMemcpy2DAsync(dst + (size_t)(r / B) * P * row_bytes, P * row_bytes, src + (size_t)r * row_bytes, (size_t)B * row_bytes,
+                              (size_t)B * row_bytes, (size_t)full, cudaMemcpyDeviceToHost, st);
+        if (e != cudaSuccess) return e;
+        r += full * B;
+    }
+    if (r < end)
+        e = cudaMemcpyAsync(dst + (size_t)(r / B) * P * row_bytes, src + (size_t)r * row_bytes, (size_t)(end - r) * row_bytes, cudaMemcpyDeviceToHost, st);
+    return e;
+}
+
 static int copy_outputs(RadopHandle *h, const RadopOut *out, int r0, int nr, cudaStream_t st)
 {
     const int ng = h->cfg.n_gates;
-    const size_t n_rg = (size_t)h->n_rays * ng, off = (size_t)r0 * ng, cnt = (size_t)nr * ng;
+    const size_t n_rg = (size_t)h->n_rays * ng, row4 = (size_t)ng * 4, row8 = (size_t)ng * 8;
     for (int v = 0; v < RADOP_N_OUT; ++v)
-        if (out->obs[v]) CU(h, cudaMemcpyAsync(out->obs[v] + off, h->out.as<float>() + (size_t)v * n_rg + off, cnt * 4, cudaMemcpyDeviceToHost, st));
-    if (out->mask) CU(h, cudaMemcpyAsync(out->mask + off, h->out.as<float>() + (size_t)RADOP_N_OUT * n_rg + off, cnt * 4, cudaMemcpyDeviceToHost, st));
+        if (out->obs[v]) CU(h, copy_rows(h, out->obs[v], h->out.as<float>() + (size_t)v * n_rg, row4, r0, nr, st));
+    if (out->mask) CU(h, copy_rows(h, out->mask, h->out.as<float>() + (size_t)RADOP_N_OUT * n_rg, row4, r0, nr, st));
     if ((out->lat || out->lon) && !h->latlon_valid) return h->fail(RADOP_ERR_STATE, "lat / lon were not computed by the last run");
-    if (out->lat) CU(h, cudaMemcpyAsync(out->lat + off, h->lat.as<double>() + off, cnt * 8, cudaMemcpyDeviceToHost, st));
-    if (out->lon) CU(h, cudaMemcpyAsync(out->lon + off, h->lon.as<double>() + off, cnt * 8, cudaMemcpyDeviceToHost, st));
+    if (out->lat) CU(h, copy_rows(h, out->lat, h->lat.as<double>(), row8, r0, nr, st));
+    if (out->lon) CU(h, copy_rows(h, out->lon, h->lon.as<double>(), row8, r0, nr, st));
     if (out->dspectrum) {
         if (h->cfg.doppler_scheme != 3) return h->fail(RADOP_ERR_ARG, "DSPECTRUM requested but the Doppler scheme is not 3");
-        const size_t nv = (size_t)h->cfg.n_vel;
-        CU(h, cudaMemcpyAsync(out->dspectrum + off * nv, h->spec_out.as<float>() + off * nv, cnt * nv * 4, cudaMemcpyDeviceToHost, st));
+        CU(h, copy_rows(h, out->dspectrum, h->spec_out.as<float>(), row4 * (size_t)h->cfg.n_vel, r0, nr, st));
     }
     for (int v = 0; v < RADOP_NVAR_MAX; ++v)
         if (out->model[v]) {
             if (!h->cfg.output_model_vars || !((h->var_mask | (h->cfg.with_melting ? 0x1E00u : 0u)) & (1u << v)))
                 return h->fail(RADOP_ERR_ARG, "model output requested but not computed");
-            CU(h, cudaMemcpyAsync(out->model[v] + off, h->model_out.as<float>() + (size_t)v * n_rg + off, cnt * 4, cudaMemcpyDeviceToHost, st));
+            CU(h, copy_rows(h, out->model[v], h->model_out.as<float>() + (size_t)v * n_rg, row4, r0, nr, st));
         }
     return RADOP_OK;
 }
@@ -1025,7 +1057,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             CU(h, cudaGetLastError()); ++launches;
             if (ev) { CU(h, cudaEventRecord(ev[1], st)); CU(h, cudaEventRecord(ev[2], st)); CU(h, cudaEventRecord(ev[3], st)); }
             if (ice) {
-                k_ice_fixup<<<(nr + 127) / 128, 128, 0, st>>>(c, h->f_ice.as<float4>(), n_spans, h->comb.as<float>(), h->f_wsum.as<float>());
+                k_ice_fixup<<<nr, c.n_sub <= 32 ? 32 : 128, (size_t)c.n_sub * 16, st>>>(c, h->f_ice.as<float4>(), n_spans, h->comb.as<float>(), h->f_wsum.as<float>());
                 CU(h, cudaGetLastError()); ++launches;
             }
             K3Args a3;
@@ -1548,6 +1580,32 @@ int radop_selftest_division(RadopHandle *h, uint64_t n_samples, uint64_t seed, u
     CU(h, cudaStreamSynchronize(h->stream));
     cnt.release();
     *mismatches = bad;
+    return RADOP_OK;
+}
+
+int radop_set_output_blocks(RadopHandle *h, int block_rays, int block_pitch_rays)
+{
+    if (!h) return RADOP_ERR_ARG;
+    if (block_rays < 0 || (block_rays > 0 && block_pitch_rays < block_rays))
+        return h->fail(RADOP_ERR_ARG, "output blocks: block_rays >= 0 and block_pitch_rays >= block_rays");
+    h->out_block = block_rays;
+    h->out_pitch = block_rays > 0 ? block_pitch_rays : 0;
+    return RADOP_OK;
+}
+
+int radop_host_register(RadopHandle *h, void *ptr, int64_t bytes)
+{
+    if (!h || !ptr || bytes <= 0) return RADOP_ERR_ARG;
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaHostRegister(ptr, (size_t)bytes, cudaHostRegisterPortable));
+    return RADOP_OK;
+}
+
+int radop_host_unregister(RadopHandle *h, void *ptr)
+{
+    if (!h || !ptr) return RADOP_ERR_ARG;
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaHostUnregister(ptr));
     return RADOP_OK;
 }
 

@@ -2971,6 +2971,13 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                 const double scale = 6.283185307179586 * (double)n0 * (double)zfac3 * (double)spec_scale *
                                      (A.sub_acc ? 1.0 : (double)P.attw);
                 double *dst = A.sub_acc ? A.sub_acc + (size_t)sbg * nvel : A.spec_acc + rg * nvel;
+                // Second pass only for a pair whose prefix differences ALL came out as zero although it has samples inside
+                // the velocity window: its power sits in the far tail of the PSD, below the float32 resolution of the running
+                // sums, but it may be the only power of the gate -- and then decides whether RVEL is a number (the reference
+                // sums the samples of a bin directly, doppler_c.c:23-30, and keeps 1e-22 of a bin as it keeps 1e+3).
+                bool any_power = false;
+                for (int pass = 0; pass < 2; ++pass) {
+                const bool direct = A.sub_acc != nullptr || pass == 1;
                 for (int j = j_a + lane; j < j_b; j += 32) {
                     const float Dj = s_D[j];
                     if (isnan(Dj)) continue;
@@ -2995,7 +3002,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                         diff = hi - lo;
                         if (fabs(diff) < 2e-15 * fabs(hi)) diff = 0.0;      // rounding of the bases
                     }
-                    if (A.sub_acc && !(diff > 1e-6 * (s_base[cb] + vb))) {
+                    if (direct && !(diff > 1e-6 * (s_base[cb] + vb))) {
                         // Broadening turns a sub-beam spectrum without power into NaN (0 / 0,
                         // doppler_scatter.py:799), so "tiny" and "zero" are not the same thing here:
                         // where the prefix difference has lost the value (far PSD tail), the samples
@@ -3018,7 +3025,9 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                         diff = (double)acc;
                     }
                     const double val = diff * scale;
-                    if (val != 0.0) atomicAdd(dst + j, val);
+                    if (val != 0.0) { atomicAdd(dst + j, val); any_power = true; }
+                }
+                if (direct || __any_sync(0xffffffffu, any_power)) break;
                 }
                 __syncwarp();
             }

@@ -4,7 +4,8 @@
 Scheme 1 of cosmo_pol/interpolation/interpolation.py:148-166 (Gauss-Hermite nodes scaled by
 sigma = bw/(2 sqrt(2 ln 2)), weights multiplied by |cos(pts_ver)| and normalised) followed by
 the cumulative weight threshold of interpolation.py:343-354; scheme 2 (multi-Gaussian antenna pattern,
-irregular points, interpolation.py:194-228)."""
+irregular points, interpolation.py:194-228); schemes 3 and 5 on a measured antenna diagram (:232-258, 276-303);
+scheme 'ml' (:168-193)."""
 import numpy as np
 from numpy.polynomial.hermite import hermgauss
 
@@ -103,17 +104,123 @@ def melting_layer_fan(config):
     return fan
 
 
+def _regular_fan(pts_hor, pts_ver, weights, fraction, broadening):
+    """Normalised weights on a regular (horizontal x vertical) grid and the weight threshold of interpolation.py:343-354."""
+    weights = weights / np.sum(weights.ravel())
+    keep = weights >= _threshold(weights, fraction) if broadening else np.ones_like(weights, dtype=bool)
+    return SubbeamFan(np.asarray(pts_hor, dtype=np.float64), np.asarray(pts_ver, dtype=np.float64), weights, keep)
+
+
+def read_antenna_diagram(path):
+    """Two comma-separated columns: off-axis angle [deg] (symmetric about 0) and one-way power [dB]; returns the
+    angles and the two-way power in linear units (interpolation.py:236-240, 280-284)."""
+    table = np.genfromtxt(path, delimiter=',')
+    return table[:, 0], (10 ** (0.1 * table[:, 1])) ** 2
+
+
+def pattern_on_grid(angles, power, x, y):
+    """The measured cut through the antenna pattern, rotated about the beam axis and sampled at the offsets (x, y):
+    what utilities.vector_1d_to_polar / polar2cartesian (utilities.py:285-341) do -- both halves of the cut become the
+    rows theta = 0 and theta = pi of a three-row polar grid and scipy's cubic `map_coordinates` reads it at the
+    fractional (theta, radius) index of every point.  Returns [len(y), len(x)]."""
+    from scipy.interpolate import interp1d
+    from scipy.ndimage import map_coordinates
+    mid = int(np.floor(len(angles) / 2.))
+    radius = angles[mid:]
+    theta = np.array([0., np.pi, 2 * np.pi])
+    polar = np.zeros((3, len(radius)))
+    polar[0] = power[mid:]
+    polar[1] = power[:mid + 1][::-1]
+    polar[2] = polar[0]
+    gx, gy = np.meshgrid(x, y)
+    r_pt = np.sqrt(gx * gx + gy * gy).ravel()
+    t_pt = (np.arctan2(gx, gy) + np.pi).ravel()
+    i_r = interp1d(radius, np.arange(len(radius)), bounds_error=False)(r_pt)
+    i_t = interp1d(theta, np.arange(3))(t_pt)
+    i_r[r_pt > radius.max()] = len(radius) - 1
+    i_r[r_pt < radius.min()] = 0
+    return map_coordinates(polar, np.array([i_t, i_r]), order=3).reshape(gx.shape)
+
+
+def legendre_antenna_fan(config):
+    """Integration scheme 3 (interpolation.py:232-258): Gauss-Legendre nodes over the angular extent of a measured
+    antenna diagram, weighted with the two-way pattern at the nodes and the cosine of the elevation offset."""
+    from numpy.polynomial.legendre import leggauss
+    integ = config['integration']
+    nh, nv = int(integ['nh_GH']), int(integ['nv_GH'])
+    angles, power = read_antenna_diagram(integ['antenna_diagram'])
+    bounds = np.max(angles)
+    xh, wh = leggauss(nh)
+    xv, wv = leggauss(nv)
+    pts_hor, pts_ver = xh * bounds, xv * bounds
+    weights = pattern_on_grid(angles, power, pts_hor, pts_ver).T * np.outer(wh, wv)
+    weights = weights * np.abs(np.cos(np.deg2rad(pts_ver)))
+    weights = weights * (2 * bounds)
+    return _regular_fan(pts_hor, pts_ver, weights, integ['weight_threshold'], nh > 1 or nv > 1)
+
+
+def gautschi_nodes(w_func, left, right, n_points, n_samples=8192):
+    """Gauss nodes and weights for an arbitrary weight function on (left, right) -- cosmo_pol/interpolation/
+    quadrature.py:33-101: the weight is sampled at `n_samples` midpoints, the recurrence coefficients of its orthogonal
+    polynomials come from the discretised Stieltjes procedure, nodes and weights from the eigen-decomposition of the
+    Jacobi matrix (Golub-Welsch); NaN / infinite matrix entries are zeroed as the reference does."""
+    import scipy.linalg
+    step = (float(right) - left) / n_samples
+    z = np.linspace(left + 0.5 * step, right - 0.5 * step, n_samples)
+    w = step * w_func(z)
+    wz = z * w
+    cur = np.ones(z.shape)
+    cur /= np.sqrt(np.dot(cur, cur))
+    old = np.zeros(z.shape)
+    diag, off = np.empty(n_points), np.empty(n_points)
+    norm_old = 1.0
+    for j in range(n_points):
+        norm = np.dot(w * cur, cur)
+        diag[j] = np.dot(wz * cur, cur) / norm
+        off[j] = 0.0 if j == 0 else norm / norm_old
+        cur, old, norm_old = (z - diag[j]) * cur - off[j] * old, cur, norm
+    sub = np.sqrt(off[1:])
+    jacobi = np.diag(diag) + np.diag(sub, k=-1) + np.diag(sub, k=1)
+    jacobi[~np.isfinite(jacobi)] = 0.
+    nodes, vec = scipy.linalg.eigh(jacobi)
+    order = nodes.argsort()
+    return nodes[order], (vec[0, :] ** 2 * w.sum())[order]
+
+
+def gautschi_fan(config):
+    """Integration scheme 5 (interpolation.py:276-303; present in the reference's code, but its configuration check,
+    cfg.py:101, does not list it): discrete Gautschi quadrature whose weight function IS the measured two-way antenna
+    pattern (times the cosine of the offset in the vertical), so few nodes integrate the pattern exactly."""
+    from scipy.interpolate import interp1d
+    integ = config['integration']
+    nh, nv = int(integ['nh_GH']), int(integ['nv_GH'])
+    angles, power = read_antenna_diagram(integ['antenna_diagram'])
+    bounds = np.max(angles)
+    pattern = interp1d(angles, power, fill_value=0)
+    pattern_cos = interp1d(angles, power * np.cos(np.abs(np.deg2rad(angles))), fill_value=0)
+    pts_hor, wh = gautschi_nodes(pattern, -bounds, bounds, nh)
+    pts_ver, wv = gautschi_nodes(pattern_cos, -bounds, bounds, nv)
+    return _regular_fan(pts_hor, pts_ver, np.outer(wh, wv), integ['weight_threshold'], nh > 1 or nv > 1)
+
+
 def subbeam_fan(config):
     bw = config['radar']['3dB_beamwidth']
-    if config['integration']['scheme'] == 2:
+    scheme = config['integration']['scheme']
+    if scheme == 2:
         return multi_gaussian_fan(config)
     nh, nv = int(config['integration']['nh_GH']), int(config['integration']['nv_GH'])
-    if config['integration']['scheme'] == 'ml':
+    if scheme == 'ml':
         return melting_layer_fan(config)
-    if config['integration']['scheme'] != 1:
-        raise NotImplementedError("integration schemes 1 (Gauss-Hermite), 2 (multi-Gaussian antenna) and 'ml' (melting-layer "
-                                  "oversampling) are part of this build; 3 and 4 need an antenna diagram file / a pickle on the "
-                                  "authors' disk, 5 and 6 are rejected by the reference's own configuration check (cfg.py:101)")
+    if scheme in (3, 5):
+        if not config['integration'].get('antenna_diagram'):
+            raise ValueError('integration scheme {} needs integration.antenna_diagram: a comma-separated file of off-axis '
+                             'angles [deg] and one-way power [dB] (interpolation.py:236, 280)'.format(scheme))
+        return legendre_antenna_fan(config) if scheme == 3 else gautschi_fan(config)
+    if scheme != 1:
+        raise NotImplementedError("integration schemes 1 (Gauss-Hermite), 2 (multi-Gaussian antenna), 3 (Gauss-Legendre on an "
+                                  "antenna diagram), 5 (Gautschi on an antenna diagram) and 'ml' (melting-layer oversampling) "
+                                  "are part of this build; 4 reads a pickle from the authors' disk (interpolation.py:262) and 6 "
+                                  "needs the SpectralToolbox package (:307)")
     sigma = bw / (2 * np.sqrt(2 * np.log(2)))
     xh, wh = hermgauss(nh)
     xv, wv = hermgauss(nv)

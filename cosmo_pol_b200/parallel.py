@@ -313,3 +313,139 @@ def all_gather_rays(local, n_total, group=None):
     if local.is_cuda:
         g.wait(p, torch.cuda.current_stream(local.device))
     return g.result(p)
+
+
+# ---------------------------------------------------------------------------------------------
+# delivery through host memory shared by the ranks (the default of RadarOperator under torchrun)
+# ---------------------------------------------------------------------------------------------
+class HostExchange(object):
+    """Host arrays of the WHOLE scan, shared by the ranks of one box (POSIX shared memory), plus a barrier in the same
+    segment.
+
+    The reference's pool.map hands the per-ray results back to ONE host process (radar_operator.py:429-432); the
+    consumers of a scan (PyartRadop, files) live on the host.  So the ranks do not gather on the device at all: every
+    rank copies its rays device -> host straight into its rows of these arrays (Engine.simulate_into: strided copies over
+    the rank's own PCIe link, all links in parallel), then the ranks meet at `barrier`, and rank 0 (or every rank) reads the
+    assembled scan.  No collective is on the data path; torch.distributed only hands out the segment names, once per
+    array set.
+
+    Two array sets are used in turn (call k uses set k % 2): a rank that has already started call k + 1 writes the
+    other set while a slower rank still reads call k; set k % 2 is not written again before every rank has passed the
+    barrier of call k + 1.  The barrier: rank r stores (sequence number, status) in slot r of a flag array (one of
+    two, by sequence parity) and waits until all slots hold the sequence number; it returns the largest status, so a
+    failing rank makes every rank raise (see agree_status)."""
+
+    TIMEOUT_S = 600.0
+
+    def __init__(self, rank=None, world=None, register=None, unregister=None):
+        r, w = dist_info()
+        self.rank = r if rank is None else int(rank)
+        self.world = w if world is None else int(world)
+        self._register, self._unregister = register, unregister
+        self._sets = [None, None]
+        self._spec = None
+        self._segments = []
+        self._flags = None
+        self._seq = 0
+        self.calls = 0
+
+    # -- segments ---------------------------------------------------------------------------------
+    def _share(self, nbytes, pin=True):
+        """One shared segment of nbytes: created by rank 0, attached by the others (name handed out by broadcast)."""
+        from multiprocessing import shared_memory
+        import torch.distributed as dist
+        name = [None]
+        seg = None
+        if self.rank == 0:
+            seg = shared_memory.SharedMemory(create=True, size=max(8, int(nbytes)))
+            name[0] = seg.name
+        if self.world > 1:
+            dist.broadcast_object_list(name, src=0)
+        if self.rank != 0:
+            seg = shared_memory.SharedMemory(name=name[0])
+            try:        # the creator unlinks; keep the resource tracker of the attaching processes out of it
+                from multiprocessing import resource_tracker
+                resource_tracker.unregister(seg._name, 'shared_memory')
+            except Exception:
+                pass
+        buf = np.ndarray((max(8, int(nbytes)),), dtype=np.uint8, buffer=seg.buf)
+        pinned = bool(self._register(buf)) if (pin and self._register is not None) else False
+        self._segments.append((seg, buf, pinned))
+        return buf
+
+    def ensure(self, spec):
+        """spec: list of (name, row shape tuple, dtype) with a common number of rows `n_rows` given as the first
+        element of each shape.  (Re)allocates the two array sets when the spec changes (a collective call)."""
+        spec = [(n, tuple(int(x) for x in shp), np.dtype(dt).str) for n, shp, dt in spec]
+        if spec == self._spec:
+            return
+        self.close(keep_flags=True)
+        if self._flags is None:
+            self._flags = self._share(2 * self.world * 8, pin=False)[:2 * self.world * 8].view(np.int64).reshape(2, self.world)
+            if self.rank == 0:
+                self._flags[:] = 0
+            self._seq = 0
+            if self.world > 1:
+                import torch.distributed as dist
+                dist.barrier()                       # the zeroed flags are visible before anybody uses them
+        sizes = [int(np.prod(shp)) * np.dtype(dt).itemsize for _, shp, dt in spec]
+        offs = np.concatenate([[0], np.cumsum([(s + 255) // 256 * 256 for s in sizes])])
+        for k in range(2):
+            buf = self._share(int(offs[-1]))
+            self._sets[k] = {n: buf[offs[i]:offs[i] + sizes[i]].view(dt).reshape(shp) for i, (n, shp, dt) in enumerate(spec)}
+        self._spec = spec
+
+    def arrays(self):
+        """The array set of the current call (name -> array of the whole scan)."""
+        return self._sets[self.calls % 2]
+
+    def next_call(self):
+        self.calls += 1
+
+    # -- barrier ----------------------------------------------------------------------------------
+    def barrier(self, code=0):
+        """All ranks meet; returns the largest status code any rank brought."""
+        import time
+        if self.world == 1:
+            return int(code)
+        self._seq += 1
+        seq, flags = self._seq, self._flags[self._seq % 2]
+        flags[self.rank] = seq * 256 + (int(code) & 255)
+        t0, spins = time.time(), 0
+        while True:
+            v = flags.copy()
+            if np.all(v >> 8 == seq):
+                return int(np.max(v & 255))
+            spins += 1
+            if spins > 2000:
+                time.sleep(0.00005)
+                if time.time() - t0 > self.TIMEOUT_S:
+                    raise RuntimeError('HostExchange.barrier: rank(s) {} did not arrive within {} s'.format(
+                        np.where(v >> 8 != seq)[0].tolist(), self.TIMEOUT_S))
+
+    def close(self, keep_flags=False):
+        flag_ptr = self._flags.ctypes.data if (keep_flags and self._flags is not None) else None
+        keep, doomed = [], []
+        for ent in self._segments:
+            (keep if (flag_ptr is not None and ent[1].ctypes.data == flag_ptr) else doomed).append(ent)
+        self._segments = keep
+        self._sets = [None, None]
+        self._spec = None
+        if not keep_flags:
+            self._flags = None
+        for seg, buf, pinned in doomed:
+            if pinned and self._unregister is not None:
+                try:
+                    self._unregister(buf)
+                except Exception:
+                    pass
+            del buf
+            try:
+                seg.close()
+            except BufferError:
+                pass                                  # views handed out to the caller are still alive
+            if self.rank == 0:
+                try:
+                    seg.unlink()
+                except Exception:
+                    pass

@@ -65,9 +65,13 @@ class SimulatedScan(object):
 
 
 class RadarOperator(object):
-    def __init__(self, options_file=None, output_variables='all', device=None, lut_folder=None, gather='all'):
+    def __init__(self, options_file=None, output_variables='all', device=None, lut_folder=None, gather='all',
+                 gather_transport='host'):
         """gather: under torch.distributed the rays of a scan are sharded over the ranks; 'all' hands the
-        assembled scan to every rank, 'root' to rank 0 only (the other ranks' get_PPI / get_RHI return None)."""
+        assembled scan to every rank, 'root' to rank 0 only (the other ranks' get_PPI / get_RHI return None).
+        gather_transport: 'host' (default) -- every rank copies its rays device -> host into arrays shared by the
+        ranks (parallel.HostExchange: all PCIe links in parallel, no collective on the data path); 'nccl' -- the
+        shards are gathered device -> device first (parallel.RayGather), for consumers that want the scan on a GPU."""
         print('Reading options defined in options file')
         cfg.init(options_file)
         self.current_microphys_scheme = '1mom'
@@ -82,7 +86,10 @@ class RadarOperator(object):
         self._dirty = {'params': True, 'model': True, 'lut': True}
         self._engine_flags = None
         self.gather_mode = gather
+        self.gather_transport = gather_transport
         self._gather = None
+        self._exchange = None
+        self._latlon_sets = [None, None]
         self._traj_cache = {}
         self._scan_cache = {}
         self.config = cfg.CONFIG
@@ -95,6 +102,9 @@ class RadarOperator(object):
 
     # ---------------------------------------------------------------------------- config
     def close(self):
+        if self._exchange is not None:
+            self._exchange.close()
+            self._exchange = None
         if self._engine is not None:
             self._engine.close()
             self._engine = None
@@ -326,8 +336,8 @@ class RadarOperator(object):
         """Batched hot path over an arbitrary ray list; returns dict name -> [n_rays, n_gates].
         With torch.distributed initialised (and distributed=True) the ONE ray list is dealt out to the ranks in
         small blocks (parallel.shard_indices), as the reference splits it over its pool workers (radar_operator.py:402-435),
-        and the result is gathered over NCCL (``gather='all'``: on every rank, ``'root'``: on rank 0, None
-        elsewhere).  copy=False returns views of the pinned host buffers the operator owns (valid until its next
+        and the result is assembled in host arrays shared by the ranks (gather_transport='host') or gathered over NCCL
+        first ('nccl') (``gather='all'``: on every rank, ``'root'``: on rank 0, None elsewhere).  copy=False returns views of the pinned host buffers the operator owns (valid until its next
         call) instead of fresh arrays."""
         eng = self._prepare_engine(keep_debug=keep_debug)
         ray_az = np.asarray(ray_az, dtype=np.float64)
@@ -351,6 +361,8 @@ class RadarOperator(object):
         in the collectives with an empty block; the ranks agree on an error status BEFORE the first data
         collective, so a shard that leaves the model domain raises IndexError on every rank instead of
         leaving its peers waiting."""
+        if self.gather_transport == 'host':
+            return self._simulate_sharded_host(eng, ray_az, ray_el, rank, world, want_model, copy)
         import torch
         from ._abi import BUF_OBS, BUF_LAT, BUF_LON, BUF_MODEL, BUF_DSPECTRUM
         n_total = len(ray_az)
@@ -428,6 +440,64 @@ class RadarOperator(object):
         if not receives:
             return None
         full_scan = self.build_scan(ray_az, ray_el)
+        out['dist'] = full_scan.traj_s[full_scan.ray_traj, full_scan.fan.j_ver[full_scan.fan.center]]
+        out['heights'] = full_scan.traj_h[full_scan.ray_traj, full_scan.fan.j_ver[full_scan.fan.center]]
+        return out
+
+    def _simulate_sharded_host(self, eng, ray_az, ray_el, rank, world, want_model, copy=True):
+        """The default multi-GPU path: rank r simulates the rays parallel.shard_indices(n, r, world) and its
+        radop_simulate copies them device -> host straight into this rank's rows of host arrays that all ranks share
+        (parallel.HostExchange; Engine.simulate_into / radop_set_output_blocks): the device -> host copies of the ranks
+        run in parallel over their own PCIe links and there is no device-side collective.  The ranks then meet at a
+        barrier in the shared segment that also carries a status, so a shard that leaves the model domain raises
+        IndexError on every rank.  Gate positions depend on the ray list only and are written once per geometry.
+        With copy=False the returned arrays are views of the shared segment, valid until the call after the next one."""
+        n_total = len(ray_az)
+        mine = parallel.shard_indices(n_total, rank, world)
+        n_loc = len(mine)
+        ng = len(constants.RANGE_RADAR)
+        if self._exchange is None:
+            self._exchange = parallel.HostExchange(rank, world, register=eng.host_register, unregister=eng.host_unregister)
+        X = self._exchange
+        spectrum = self.__config['doppler']['scheme'] == 3 and self.output_variables in ('all', 'only_radar')
+        spec = [(n, (n_total, ng), np.float32) for n in list(OUT_NAMES) + ['mask']]
+        spec += [('lat', (n_total, ng), np.float64), ('lon', (n_total, ng), np.float64)]
+        if spectrum:
+            spec.append(('DSPECTRUM', (n_total, ng, len(constants.VARRAY)), np.float32))
+        if want_model:
+            spec += [(n, (n_total, ng), np.float32) for n in sorted(eng.model_output_slots())]
+        if [(n, tuple(s), np.dtype(d).str) for n, s, d in spec] != X._spec:
+            self._latlon_sets = [None, None]
+        X.ensure(spec)
+        arrays = X.arrays()
+        which = X.calls % 2
+        full_scan = self.build_scan(ray_az, ray_el)
+        gkey = (full_scan.geometry_key(), world)
+        want_latlon = self._latlon_sets[which] != gkey
+        code, err = 0, None
+        try:
+            if n_loc:
+                scan = self.build_scan(ray_az[mine], ray_el[mine])
+                self._last_scan = scan
+                eng.simulate_into(scan, arrays, rank, world, parallel.RAY_BLOCK, want_latlon=want_latlon)
+        except IndexError as e:
+            code, err = 3, e
+        except ValueError as e:
+            code, err = 2, e
+        except Exception as e:                 # noqa: BLE001 -- every rank must reach the barrier
+            code, err = 1, e
+        worst = X.barrier(code)
+        X.next_call()
+        if worst:
+            self._latlon_sets[which] = None
+            if err is not None and code == worst:
+                raise err
+            exc = {3: IndexError, 2: ValueError}.get(worst, RuntimeError)
+            raise exc('another rank failed on its shard of the scan (status {})'.format(worst))
+        self._latlon_sets[which] = gkey
+        if not (self.gather_mode == 'all' or rank == 0):
+            return None
+        out = {k: (np.array(a, copy=True) if copy else a) for k, a in arrays.items()}
         out['dist'] = full_scan.traj_s[full_scan.ray_traj, full_scan.fan.j_ver[full_scan.fan.center]]
         out['heights'] = full_scan.traj_h[full_scan.ray_traj, full_scan.fan.j_ver[full_scan.fan.center]]
         return out

@@ -227,6 +227,19 @@ int radop_set_chunk(RadopHandle *h, int64_t subbeam_gates_per_chunk);
  * there is a device -> host copy to hide.  0 = always chunk (used by the chunk-invariance tests). */
 int radop_set_overlap_threshold(RadopHandle *h, int64_t min_output_bytes);
 
+/* Multi-GPU delivery (stands in for the result list that pool.map returns, radar_operator.py:429-432).
+ * The ranks of one job deal blocks of `block_rays` consecutive rays of the scan in turn; every rank hands
+ * radop_simulate / radop_fetch output pointers into ONE host array shared by the ranks (each pointer at the
+ * first row of the rank: array + rank * block_rays rows) and sets block_pitch_rays = n_ranks * block_rays:
+ * local ray i then lands on row (i / block_rays) * block_pitch_rays + i % block_rays, whole blocks as one
+ * strided device -> host copy over the rank's own PCIe link.  No device-side collective is involved.
+ * block_rays = 0 (default): the caller's arrays hold this handle's rays only, contiguously. */
+int radop_set_output_blocks(RadopHandle *h, int block_rays, int block_pitch_rays);
+/* Page-lock (cudaHostRegister, portable) / release a host range the caller owns, e.g. the shared-memory
+ * segment of the ranks, so that the copies above are asynchronous DMA. */
+int radop_host_register(RadopHandle *h, void *ptr, int64_t bytes);
+int radop_host_unregister(RadopHandle *h, void *ptr);
+
 /* Device-resident results of the last radop_execute (for NCCL gathers): pointer to
  * float32 [RADOP_N_OUT + 1][n_rays][n_gates] (observables then mask). */
 /* Geolocation of the gates (stands in for pyproj.Geod.fwd + pycosmo.WGS_to_COSMO,

@@ -607,6 +607,110 @@ def _irregular_radial(model, names, azimuth, elevation, cfg, rranges, radar_pos,
     return subs
 
 
+def _threshold_keep(weights, cfg, beam_broadening):
+    # interpolation.py:343-352
+    w_sort = np.sort(np.array(weights).ravel())[::-1]
+    w_cum = np.cumsum(w_sort / np.sum(w_sort))
+    w_cum[-1] = 1.
+    threshold = w_sort[np.where(w_cum >= cfg['integration']['weight_threshold'])[0][0]]
+    return np.logical_or(weights >= threshold, not beam_broadening)
+
+
+def _polar2cartesian(r, t, grid, x, y, order=3):
+    """utilities.py:285-316"""
+    from scipy.interpolate import interp1d
+    from scipy.ndimage import map_coordinates
+    X, Y = np.meshgrid(x, y)
+    new_r = np.sqrt(X * X + Y * Y)
+    new_t = np.arctan2(X, Y) + np.pi
+    new_ir = interp1d(r, np.arange(len(r)), bounds_error=False)(new_r.ravel())
+    new_it = interp1d(t, np.arange(len(t)))(new_t.ravel())
+    new_ir[new_r.ravel() > r.max()] = len(r) - 1
+    new_ir[new_r.ravel() < r.min()] = 0
+    return map_coordinates(grid, np.array([new_it, new_ir]), order=order).reshape(new_r.shape)
+
+
+def _vector_1d_to_polar(angles, values, x, y):
+    """utilities.py:318-341"""
+    midpt = int(np.floor(len(angles) / 2.))
+    r = angles[midpt:]
+    thet = [0, np.pi, 2 * np.pi]
+    pol = np.zeros((len(thet), len(r)))
+    pol[0, :] = values[midpt:]
+    pol[1, :] = values[0:midpt + 1][::-1]
+    pol[2, :] = pol[0, :]
+    return _polar2cartesian(r, thet, pol, x, y)
+
+
+def gauss_legendre_antenna_subbeams(cfg):
+    """Integration scheme 3, interpolation.py:232-258."""
+    from numpy.polynomial.legendre import leggauss
+    nh, nv = int(cfg['integration']['nh_GH']), int(cfg['integration']['nv_GH'])
+    antenna = np.genfromtxt(cfg['integration']['antenna_diagram'], delimiter=',')
+    angles = antenna[:, 0]
+    power_sq = (10 ** (0.1 * antenna[:, 1])) ** 2
+    bounds = np.max(angles)
+    pts_hor, w_hor = leggauss(nh)
+    pts_hor = pts_hor * bounds
+    pts_ver, w_ver = leggauss(nv)
+    pts_ver = pts_ver * bounds
+    weights = _vector_1d_to_polar(angles, power_sq, pts_hor, pts_ver).T * np.outer(w_hor, w_ver)
+    weights *= np.abs(np.cos(np.deg2rad(pts_ver)))
+    weights *= 2 * bounds
+    weights /= np.sum(weights.ravel())
+    return pts_hor, pts_ver, weights, _threshold_keep(weights, cfg, nh > 1 or nv > 1)
+
+
+def _discrete_gautschi(z, w, n_iter):
+    """interpolation/quadrature.py:33-54"""
+    p = np.ones(z.shape)
+    p /= np.sqrt(np.dot(p, p))
+    p_prev = np.zeros(z.shape)
+    wz = z * w
+    a, b = np.empty(n_iter), np.empty(n_iter)
+    for j in range(n_iter):
+        p_norm = np.dot(w * p, p)
+        a[j] = np.dot(wz * p, p) / p_norm
+        b[j] = 0.0 if j == 0 else p_norm / np.dot(w * p_prev, p_prev)
+        p, p_prev = (z - a[j]) * p - b[j] * p_prev, p
+    return a, b[1:]
+
+
+def _gautschi_points_and_weights(w_func, left, right, num_points, n=8192):
+    """interpolation/quadrature.py:57-101"""
+    import scipy.linalg
+    dx = (float(right) - left) / n
+    z = np.hstack(np.linspace(left + 0.5 * dx, right - 0.5 * dx, n))
+    w = dx * w_func(z)
+    a, b = _discrete_gautschi(z, w, num_points)
+    beta = np.sqrt(b)
+    J = np.diag(a)
+    J += np.diag(beta, k=-1)
+    J += np.diag(beta, k=1)
+    J[np.isnan(J)] = 0.
+    J[np.isinf(J)] = 0.
+    points, v = scipy.linalg.eigh(J)
+    ind = points.argsort()
+    return points[ind], (v[0, :] ** 2 * w.sum())[ind]
+
+
+def gautschi_antenna_subbeams(cfg):
+    """Integration scheme 5, interpolation.py:276-303."""
+    from scipy.interpolate import interp1d
+    nh, nv = int(cfg['integration']['nh_GH']), int(cfg['integration']['nv_GH'])
+    antenna = np.genfromtxt(cfg['integration']['antenna_diagram'], delimiter=',')
+    angles = antenna[:, 0]
+    power_sq = (10 ** (0.1 * antenna[:, 1])) ** 2
+    bounds = np.max(angles)
+    fit = interp1d(angles, power_sq, fill_value=0)
+    fit_w = interp1d(angles, power_sq * np.cos(np.abs(np.deg2rad(angles))), fill_value=0)
+    pts_hor, w_hor = _gautschi_points_and_weights(fit, -bounds, bounds, nh)
+    pts_ver, w_ver = _gautschi_points_and_weights(fit_w, -bounds, bounds, nv)
+    weights = np.outer(w_hor, w_ver)
+    weights /= np.sum(weights.ravel())
+    return pts_hor, pts_ver, weights, _threshold_keep(weights, cfg, nh > 1 or nv > 1)
+
+
 def get_interpolated_radial(model, azimuth, elevation, cfg, debug=False):
     """interpolation.py:91-438 for integration scheme 1, refraction schemes 1 and 2 (the refractivity field is
     model['refractivity'], kept apart from the interpolated variables like the reference's self.N).
@@ -618,7 +722,12 @@ def get_interpolated_radial(model, azimuth, elevation, cfg, debug=False):
     if cfg['integration']['scheme'] == 2:
         return _irregular_radial(model, names, azimuth, elevation, cfg, rranges, radar_pos, debug)
     ml = cfg['integration']['scheme'] == 'ml'
-    pts_hor, pts_ver, weights, keep = melting_layer_subbeams(cfg) if ml else gauss_hermite_subbeams(cfg)
+    if cfg['integration']['scheme'] == 3:
+        pts_hor, pts_ver, weights, keep = gauss_legendre_antenna_subbeams(cfg)
+    elif cfg['integration']['scheme'] == 5:
+        pts_hor, pts_ver, weights, keep = gautschi_antenna_subbeams(cfg)
+    else:
+        pts_hor, pts_ver, weights, keep = melting_layer_subbeams(cfg) if ml else gauss_hermite_subbeams(cfg)
     if cfg['refraction']['scheme'] == 2:
         N = {'data': model['refractivity'], 'z_levels': model['z_levels'], 'proj': model['proj'],
              'resolution': model['resolution']}

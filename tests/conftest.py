@@ -65,6 +65,8 @@ def load_golden_case(name):
     cfg = json.loads(str(g['config_json']))
     nyq = float(g['nyquist'])
     cfg['radar']['nyquist_velocity'] = nyq if nyq > 0 else None
+    if cfg.get('integration', {}).get('antenna_diagram'):     # the generator recorded its own absolute path
+        cfg['integration']['antenna_diagram'] = os.path.join(GOLDEN, os.path.basename(cfg['integration']['antenna_diagram']))
     kw = json.loads(str(g['model_kw_json']))
     return g, cfg, kw
 

@@ -400,6 +400,17 @@ CASES = {
                                       integration={'scheme': 2, 'nr_GH': 3, 'na_GL': 5, 'weight_threshold': 0.999,
                                                    'antenna_params': [[0.0, 0.0, 0.4247], [-24.0, 1.6, 0.3]]}),
                     [(45.0, 3.5), (250.5, 8.5)], {}),
+    # integration schemes 3 and 5 (interpolation.py:232-258, 276-303) on the antenna diagram of tests/golden/antenna_diagram.csv
+    # (1 deg main lobe, side-lobe ring at 1.8 deg, -25 dB).  The reference's configuration check does not list scheme 5
+    # (cfg.py:101); the generator sets CONFIG directly, as for every other case.
+    'c1mom_quad3': ('1mom', 5.6, dict(radar={'range': 30000, 'radial_resolution': 1000},
+                                      integration={'scheme': 3, 'nh_GH': 9, 'nv_GH': 11, 'weight_threshold': 0.99999,
+                                                   'antenna_diagram': os.path.join(HERE, 'antenna_diagram.csv')}),
+                    [(45.0, 3.5), (250.5, 8.5)], {}),
+    'c1mom_quad5': ('1mom', 5.6, dict(radar={'range': 30000, 'radial_resolution': 1000},
+                                      integration={'scheme': 5, 'nh_GH': 3, 'nv_GH': 5, 'weight_threshold': 0.9999,
+                                                   'antenna_diagram': os.path.join(HERE, 'antenna_diagram.csv')}),
+                    [(45.0, 3.5), (250.5, 8.5)], {}),
 }
 MELTING_N_E = 8          # elevation bins of the synthetic melting tables (0..14 deg): 78 MB per species
 

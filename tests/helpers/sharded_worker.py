@@ -3,7 +3,7 @@
 Checks the product path a user of RadarOperator gets under torchrun (RadarOperator._simulate_sharded,
 the counterpart of the reference's pool.map over ONE ray list, cosmo_pol/radar_operator.py:402-435):
   * a sharded PPI equals the single-GPU PPI bit for bit (observables, mask, positions, model variables),
-    in both gather modes;
+    in both gather modes and through both transports (shared host arrays, device-side NCCL gather);
   * fewer rays than ranks (a rank with an empty shard) works;
   * a shard that leaves the model domain raises IndexError on EVERY rank (nobody hangs in a collective);
   * Doppler spectra travel through the same gather.
@@ -39,18 +39,27 @@ def main():
     az = np.arange(0., 360., 7.)                     # 52 rays: uneven blocks at world 8, even at 2
     el = [1.0, 8.0, 35.0]
     ref = op.simulate_rays(np.tile(az, 3), np.repeat(el, len(az)), distributed=False)
-    for mode in ('all', 'root'):
-        op.gather_mode = mode
-        for rep in range(2):                         # the second call runs on the cached geometry
-            got = op.get_PPI(el, azimuths=az)
-            if mode == 'root' and rank != 0:
-                assert got is None
-                continue
-            for k in list(got.fields) :
-                assert same(got.fields[k].reshape(ref[k].shape), ref[k]), (mode, rep, k)
-            assert same(got.mask.reshape(ref['mask'].shape), ref['mask'])
-            assert same(got.lats.reshape(ref['lat'].shape), ref['lat']), 'lat'
-            assert same(got.lons.reshape(ref['lon'].shape), ref['lon']), 'lon'
+    az2 = np.arange(0., 360., 6.7)                   # 54 rays: the last block of four is a partial one
+    ref2 = op.simulate_rays(az2, np.full(len(az2), 3.0), distributed=False)
+    for transport in ('host', 'nccl'):               # shared host arrays (default) and the device-side gather
+        op.gather_transport = transport
+        for mode in ('all', 'root'):
+            op.gather_mode = mode
+            for rep in range(3):                     # later calls run on the cached geometry / the other array set
+                got = op.get_PPI(el, azimuths=az)
+                if mode == 'root' and rank != 0:
+                    assert got is None
+                    continue
+                for k in list(got.fields) :
+                    assert same(got.fields[k].reshape(ref[k].shape), ref[k]), (transport, mode, rep, k)
+                assert same(got.mask.reshape(ref['mask'].shape), ref['mask'])
+                assert same(got.lats.reshape(ref['lat'].shape), ref['lat']), 'lat'
+                assert same(got.lons.reshape(ref['lon'].shape), ref['lon']), 'lon'
+        op.gather_mode = 'all'
+        got2 = op.simulate_rays(az2, np.full(len(az2), 3.0), copy=False)
+        for k in ref2:
+            assert same(np.asarray(got2[k]), np.asarray(ref2[k])), (transport, 'partial block', k)
+    op.gather_transport = 'host'
     op.gather_mode = 'all'
     # fewer rays than ranks: one ray, every rank but 0 has an empty shard
     one = op.simulate_rays([33.], [2.0], distributed=False)

@@ -121,3 +121,60 @@ def test_ray_gather_gloo_world2(n_total, mode):
     assert sorted(r[0] for r in res) == [0, 1]
     assert all(r[1] for r in res)
     assert all(r[2] == 3 for r in res)
+
+
+def _worker_exchange(rank, world, port, n_total, q):
+    """HostExchange without a GPU: the ranks fill their rows of the shared arrays as radop_set_output_blocks lays them
+    out (local ray i -> row (i / B) * world * B + rank * B + i % B), meet at the barrier, read the whole scan."""
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from cosmo_pol_b200 import parallel
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    ok = True
+    try:
+        X = parallel.HostExchange(rank, world)
+        B = parallel.RAY_BLOCK
+        mine = parallel.shard_indices(n_total, rank, world)
+        truth = np.arange(n_total * 6, dtype=np.float32).reshape(n_total, 6)
+        seen = []
+        for call in range(4):
+            X.ensure([('ZH', (n_total, 6), np.float32), ('lat', (n_total, 6), np.float64)])
+            a = X.arrays()
+            seen.append(a['ZH'].ctypes.data)
+            i = np.arange(len(mine))
+            rows = (i // B) * world * B + rank * B + i % B
+            ok = ok and np.array_equal(rows, mine)                      # the C-side row formula IS shard_indices
+            a['ZH'][rows] = truth[mine] + call
+            a['lat'][rows] = truth[mine].astype(np.float64) * 2 + call
+            worst = X.barrier(3 if (call == 2 and rank == world - 1) else 0)
+            X.next_call()
+            ok = ok and worst == (3 if call == 2 else 0)
+            ok = ok and np.array_equal(a['ZH'], truth + call) and np.array_equal(a['lat'], truth.astype(np.float64) * 2 + call)
+        ok = ok and seen[0] == seen[2] and seen[1] == seen[3] and seen[0] != seen[1]      # two array sets in turn
+        X.ensure([('ZH', (n_total + 3, 2), np.float32)])                   # a new spec re-allocates (collective)
+        ok = ok and X.arrays()['ZH'].shape == (n_total + 3, 2) and X.barrier(0) == 0
+        X.close()
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('n_total', [10, 41])
+def test_host_exchange_gloo_world2(n_total):
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_exchange, args=(r, 2, port, n_total, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(r[0] for r in res) == [0, 1]
+    assert all(r[1] for r in res), res

@@ -740,6 +740,39 @@ def test_integration_scheme2_irregular_points():
     assert_observables_close(out, oref, what='quad2 oracle')
 
 
+@pytest.mark.parametrize('name', ['c1mom_quad3', 'c1mom_quad5'])
+def test_integration_schemes_on_antenna_diagram(name):
+    """Integration schemes 3 (Gauss-Legendre nodes weighted with a measured antenna diagram, interpolation.py:232-258)
+    and 5 (discrete Gautschi quadrature of the diagram, :276-303): host-side fans on a regular grid, kernels unchanged;
+    against the reference goldens (weights and points of the fan bit for bit, interpolated values bit for bit,
+    observables within the usual tolerances) and the oracle."""
+    from cosmo_pol_b200 import RadarOperator
+    g, cfg, kw = load_golden_case(name)
+    model, luts = synthetic_inputs('1mom', 5.6, **kw)
+    conf = copy.deepcopy(cfg)
+    conf['radar']['sensitivity'] = [-300, 10000]
+    op = RadarOperator(conf, output_variables='only_radar', device=0)
+    op.set_lut(luts)
+    op.load_model(model)
+    rays = g['rays']
+    op._prepare_engine(keep_debug=True)
+    out = op.simulate_rays(rays[:, 0], rays[:, 1], keep_debug=True)
+    scan = op._last_scan
+    assert scan.n_sub == g['sub_w'].shape[1] and scan.n_sub > 9 and not scan.fan.ml_only.any()
+    assert np.array_equal(np.asarray(scan.fan.weight), g['sub_w'][0])
+    ref = {k[4:]: g[k] for k in g.files if k.startswith('obs_')}
+    assert_observables_close(out, ref, sz_scale=5e-4 * np.abs(ref['KDP']), what=name + ' golden')
+    assert np.array_equal(out['mask'], g['mask'].astype(np.float32))
+    dbg = op._engine.debug_indices(scan)
+    names = dbg['var_names']
+    for k in ('T', 'QR_v', 'U'):
+        assert np.array_equal(dbg['values'][..., names.index(k)], g['sub_' + k].astype(np.float32), equal_nan=True), k
+    pm, pl = plain(model, luts)
+    oref = O.simulate_scan(pm, pl, oracle_cfg(op), rays[:, 0], rays[:, 1], accum='f64', sensitivity_cut=True)
+    assert_observables_close(out, oref, sz_scale=5e-4 * np.abs(oref['KDP']), what=name + ' oracle')
+    op.close()
+
+
 def test_edge_cases_and_errors():
     from cosmo_pol_b200 import RadarOperator
     from cosmo_pol_b200._abi import RadopError

@@ -100,6 +100,43 @@ def test_quadrature_fan():
     assert np.array_equal(np.stack([az + fan.daz, el + fan.dele], axis=1), g['sub_pt'][0])
 
 
+def test_quadrature_fans_on_an_antenna_diagram():
+    """Integration schemes 3 and 5 (interpolation.py:232-258, 276-303) against the sub-beam lists the reference itself
+    produced (tests/golden/ref_path_c1mom_quad3/5.npz): weights and pointing angles bit for bit; and the configuration-time
+    sum-of-Gaussians fit of the diagram (config/antenna_fit.py)."""
+    from conftest import load_golden_case
+    from cosmo_pol_b200.interpolation.quadrature import subbeam_fan
+    from cosmo_pol_b200.config import antenna_fit, cfg as cfgmod
+    for name, n_min in (('c1mom_quad3', 10), ('c1mom_quad5', 10)):
+        g, cfg, kw = load_golden_case(name)
+        fan = subbeam_fan(cfg)
+        az, el = g['rays'][0]
+        assert fan.n_sub == g['sub_w'].shape[1] >= n_min
+        assert np.array_equal(fan.weight, g['sub_w'][0]) and abs(fan.weight.sum() - 1) < 1e-3
+        assert np.array_equal(np.stack([az + fan.daz, el + fan.dele], axis=1), g['sub_pt'][0])
+    cfg['integration']['antenna_diagram'] = None
+    with pytest.raises(ValueError):
+        subbeam_fan(cfg)
+    # the fit: a diagram made of two known Gaussians comes back
+    x = np.round(np.arange(-3., 3.001, 0.05), 2)
+    truth = np.array([[0., 0., 0.3], [-30., 1.5, 0.2], [-30., -1.5, 0.2]])
+    y = antenna_fit.gaussian_sum_db(x, truth)
+    got = antenna_fit.optimize_gaussians(x, y, 3)
+    start = np.array([[0., 0., 0.5], [-30., 1.5, 0.5], [-30., -1.5, 0.5]])
+    err = lambda p: np.sqrt(np.sum((antenna_fit.gaussian_sum_db(x, p) - y) ** 2))
+    assert got.shape == (3, 3) and got[0, 0] == 0 and got[0, 1] == 0 and err(got) < err(start)    # main lobe pinned
+    one = antenna_fit.optimize_gaussians(x, antenna_fit.gaussian_sum_db(x, truth[:1]), 1)
+    assert one.shape == (1, 3) and abs(one[0, 2] - 0.3) < 1e-3
+    lin = antenna_fit.antenna_diagram(x, [1.0], [0.0], [0.0])
+    assert abs(lin[60] - 1) < 1e-12 and abs(lin[np.argmin(np.abs(x - 0.5))] - 0.5) < 1e-12        # 3 dB width
+    # and through the configuration check: a named diagram yields antenna_params for scheme 2
+    c = cfgmod.sanity_check({'radar': {'coords': [46., 8., 1000.], 'range': 30000, 'radial_resolution': 1000, 'frequency': 5.6},
+                             'integration': {'scheme': 2, 'n_gaussians': 3,
+                                             'antenna_diagram': os.path.join(GOLDEN, 'antenna_diagram.csv')}})
+    assert np.asarray(c['integration']['antenna_params']).shape == (3, 3)
+    assert subbeam_fan(c).n_sub > 9
+
+
 def test_refraction_matches_reference_bitwise():
     from cosmo_pol_b200.interpolation.atm_refraction import compute_trajectory_radial
     g = np.load(os.path.join(GOLDEN, 'ref_units.npz'))

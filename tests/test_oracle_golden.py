@@ -13,7 +13,8 @@ from conftest import GOLDEN, load_golden_case, plain, synthetic_inputs
 CASES = {'c1mom': ('1mom', 5.6), 'c2mom': ('2mom', 9.41), 'c1mom_thr': ('1mom', 5.6), 'c1mom_nyq': ('1mom', 5.6),
          'c1mom_dop2': ('1mom', 5.6), 'c1mom_dop3': ('1mom', 5.6), 'c1mom_dop3_mot': ('1mom', 5.6),
          'c1mom_dop3_turb': ('1mom', 5.6), 'c1mom_melt': ('1mom', 5.6), 'c1mom_melt_dop2': ('1mom', 5.6),
-         'c1mom_quad2': ('1mom', 5.6), 'c1mom_ml': ('1mom', 5.6)}
+         'c1mom_quad2': ('1mom', 5.6), 'c1mom_ml': ('1mom', 5.6), 'c1mom_quad3': ('1mom', 5.6),
+         'c1mom_quad5': ('1mom', 5.6)}
 
 
 def test_constants_match_reference():
