@@ -465,6 +465,7 @@ def run_ours(args):
             return eng.simulate(scan, want_latlon=True)
         return op.simulate_rays(az_full, el_full, copy=False)
 
+    eng.reuse_staged = False          # the ray list and the trajectories travel host -> device in EVERY timed call
     for _ in range(2):
         arrays = e2e_call()
     barrier()
@@ -484,6 +485,17 @@ def run_ours(args):
         d2h = int(d2h)
         d2h_first = d2h + n_full * 500 * 16            # + float64 lat / lon, first call on a ray list only
     checksum = float(np.nansum(arrays['ZH'][::97])) if arrays is not None else 0.0
+    # the same call when the scan strategy repeats (one radar, successive model states): the staged scan is reused
+    eng.reuse_staged = True
+    e2e_call()
+    barrier()
+    tr = time.perf_counter()
+    for _ in range(max(3, args.steps // 4)):
+        e2e_call()
+    barrier()
+    tr = (time.perf_counter() - tr) / max(3, args.steps // 4)
+    (tr,) = reduce_max(tr)
+    eng.reuse_staged = False
     st_e2e = None
     if world > 1:
         # itemised cost of the product call on rank 0 (wall clock, one extra call): where e2e goes beyond the kernels
@@ -609,6 +621,7 @@ def run_ours(args):
         'e2e': {'value': (n_full * 9 * 500.0) / (te / args.steps), 'unit': UNIT, 'h2d_bytes_per_step': h2d,
                 'd2h_bytes_per_step': d2h, 'ms_per_step': 1e3 * te / args.steps,
                 'd2h_bytes_first_call': d2h_first,
+                'ms_per_step_repeated_scan': 1e3 * tr,
                 'latlon': 'gate positions (float64 lat/lon, 58 MB per volume) depend on the scan geometry only: copied by the '
                           'first call on a ray list (d2h_bytes_first_call), kept in the pinned buffers afterwards',
                 'call': 'radop_simulate (C-ABI, host buffers)' if world == 1 else

@@ -192,6 +192,7 @@ class Scan(object):
         self.n_sub = fan.n_sub
         self.n_traj, self.n_vert, self.n_gates = self.traj_s.shape
         self._geom_key = None
+        self._center = None
 
     def geometry_key(self):
         """Digest of everything the gate positions depend on (ray list, fan, trajectories)."""
@@ -202,6 +203,14 @@ class Scan(object):
                 hsh.update(a.tobytes())
             self._geom_key = hsh.hexdigest()
         return self._geom_key
+
+    def center_profiles(self):
+        """(ground distance, height) of the central sub-beam at every gate of every ray, [n_rays, n_gates]: geometry
+        only, made once per scan (Radial.dist_profile / heights_profile of the central sub-radial, radial.py:40-44)."""
+        if self._center is None:
+            j = self.fan.j_ver[self.fan.center]
+            self._center = (self.traj_s[self.ray_traj, j], self.traj_h[self.ray_traj, j])
+        return self._center
 
     def as_struct(self):
         s = RadopScan()
@@ -240,6 +249,9 @@ class Engine(object):
         self._pinned = {}
         self._keep = []
         self._latlon_key = None      # geometry the pinned lat / lon buffers currently hold
+        self._staged = None          # (Scan object, parameter epoch) the library currently has staged
+        self.reuse_staged = True     # False: upload the scan with every call (bench.py: inputs travel every step)
+        self._epoch = 0
         self.cache_latlon = True
 
     def close(self):
@@ -315,6 +327,7 @@ class Engine(object):
                 else:
                     setattr(p.species[i], k, v)
         self._check(self.lib.radop_set_params(self.h, C.byref(p)))
+        self._epoch += 1             # trajectories and gate count belong to the parameters: the next call stages again
         self.params = p
         self.species_order = [hy.kind for hy in hydrometeors]
 
@@ -434,13 +447,22 @@ class Engine(object):
         if reuse:
             out.lat = None
             out.lon = None
-        s = scan.as_struct()
         self._latlon_key = None if (want_latlon and not reuse) else self._latlon_key
-        self._check(self.lib.radop_simulate(self.h, C.byref(s), C.byref(out)))
+        self._check(self.lib.radop_simulate(self.h, self._scan_arg(scan), C.byref(out)))
+        self._staged = (scan, self._epoch)
         if want_latlon:
             self._latlon_key = key
         self.last_d2h_bytes = int(sum(a.nbytes for k, a in arrays.items() if not (reuse and k in ('lat', 'lon'))))
         return arrays
+
+    def _scan_arg(self, scan):
+        """The RadopScan to hand to radop_simulate: NULL when the library already has this very scan staged (the Scan
+        objects of RadarOperator.build_scan are cached per ray list, so a repeated scan strategy is staged once)."""
+        if self.reuse_staged and self._staged is not None and self._staged[0] is scan and self._staged[1] == self._epoch:
+            return None
+        self._staged = None
+        self._keep = scan.as_struct()
+        return C.byref(self._keep)
 
     def host_register(self, array):
         """Page-lock a host array the caller owns (the ranks' shared-memory segment); returns False where it fails."""
@@ -473,10 +495,10 @@ class Engine(object):
         for name, slot in self.model_output_slots().items():
             if name in arrays:
                 out.model[slot] = at(arrays[name])
-        s = scan.as_struct()
         self._check(self.lib.radop_set_output_blocks(self.h, int(block), int(block * world)))
         try:
-            self._check(self.lib.radop_simulate(self.h, C.byref(s), C.byref(out)))
+            self._check(self.lib.radop_simulate(self.h, self._scan_arg(scan), C.byref(out)))
+            self._staged = (scan, self._epoch)
         finally:
             self.lib.radop_set_output_blocks(self.h, 0, 0)
         self._latlon_key = None        # the pinned buffers of make_out do not hold this scan's positions
@@ -485,7 +507,9 @@ class Engine(object):
 
     def stage(self, scan):
         s = scan.as_struct()
+        self._staged = None
         self._check(self.lib.radop_stage_scan(self.h, C.byref(s)))
+        self._staged = (scan, self._epoch)
 
     def execute(self):
         self._check(self.lib.radop_execute(self.h))

@@ -1324,7 +1324,10 @@ int radop_fetch(RadopHandle *h, const RadopOut *out)
 int radop_simulate(RadopHandle *h, const RadopScan *scan, const RadopOut *out)
 {
     if (!h) return RADOP_ERR_ARG;
-    int rc = radop_stage_scan(h, scan);
+    int rc = RADOP_OK;
+    if (scan) rc = radop_stage_scan(h, scan);
+    else if (h->n_rays <= 0 || h->n_sbg != (long long)h->n_rays * h->n_sub * h->p.n_gates)
+        rc = h->fail(RADOP_ERR_STATE, "radop_simulate(scan = NULL) reuses the staged scan: none is staged for these parameters");
     if (rc) return rc;
     rc = run_scan(h, out);          // copies of a chunk overlap the kernels of the next one
     if (rc) {

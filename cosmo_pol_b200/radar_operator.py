@@ -349,8 +349,7 @@ class RadarOperator(object):
             self._last_scan = scan
             arrays = eng.simulate(scan, want_latlon=True, want_model=want_model)
             out = {k: (np.array(v, copy=True) if copy else v) for k, v in arrays.items()}
-            out['dist'] = scan.traj_s[scan.ray_traj, scan.fan.j_ver[scan.fan.center]]
-            out['heights'] = scan.traj_h[scan.ray_traj, scan.fan.j_ver[scan.fan.center]]
+            out['dist'], out['heights'] = scan.center_profiles()
             return out
         return self._simulate_sharded(eng, ray_az, ray_el, rank, world, want_model, copy)
 
@@ -440,8 +439,7 @@ class RadarOperator(object):
         if not receives:
             return None
         full_scan = self.build_scan(ray_az, ray_el)
-        out['dist'] = full_scan.traj_s[full_scan.ray_traj, full_scan.fan.j_ver[full_scan.fan.center]]
-        out['heights'] = full_scan.traj_h[full_scan.ray_traj, full_scan.fan.j_ver[full_scan.fan.center]]
+        out['dist'], out['heights'] = full_scan.center_profiles()
         return out
 
     def _simulate_sharded_host(self, eng, ray_az, ray_el, rank, world, want_model, copy=True):
@@ -498,8 +496,7 @@ class RadarOperator(object):
         if not (self.gather_mode == 'all' or rank == 0):
             return None
         out = {k: (np.array(a, copy=True) if copy else a) for k, a in arrays.items()}
-        out['dist'] = full_scan.traj_s[full_scan.ray_traj, full_scan.fan.j_ver[full_scan.fan.center]]
-        out['heights'] = full_scan.traj_h[full_scan.ray_traj, full_scan.fan.j_ver[full_scan.fan.center]]
+        out['dist'], out['heights'] = full_scan.center_profiles()
         return out
 
     def _assemble(self, scan_type, out, n_sweeps, n_per, elevations, azimuths):

@@ -211,7 +211,9 @@ int radop_upload_lut(RadopHandle *h, int species, const double *value_table,
                      float t_min, float t_step, const float *d_axis);
 
 /* ---- the hot path ---------------------------------------------------------- */
-/* host in -> device -> host out (the reference-facing call) */
+/* host in -> device -> host out (the reference-facing call).  scan = NULL: the scan staged by the previous call is
+ * used again (same rays, fan and trajectories: its upload and the per sub-beam geometry are skipped -- the case of
+ * one scan strategy run over successive model states). */
 int radop_simulate(RadopHandle *h, const RadopScan *scan, const RadopOut *out);
 /* the same in three steps (used to time the device part alone) */
 int radop_stage_scan(RadopHandle *h, const RadopScan *scan);   /* H2D                    */
