@@ -107,6 +107,7 @@ struct RadopHandle_ {
     bool last_fused = false;
     int out_block = 0, out_pitch = 0;   // radop_set_output_blocks: host rows of local ray i = (i / block) * pitch + i % block
     bool geo_ready = false;      // geo_poly holds the polynomials of the staged scan (whole ray list)
+    bool traj_tab_ready = false; // traj_sc / traj_ie (k_traj_tables) hold the staged trajectories for the current tables
     bool geo_poly_conv = false;  // ... and every series converged
     DevBuf traj_sc, traj_ie, f_wsum, f_ice, f_cnt;
     DevBuf ml_wraw, ml_wsz;      // integration scheme 'ml': per-gate weights of a chunk
@@ -245,6 +246,7 @@ int radop_set_params(RadopHandle *h, const RadopParams *p)
     h->have_params = true;
     h->executed = false;
     h->geo_ready = false;
+    h->traj_tab_ready = false;
     return RADOP_OK;
 }
 
@@ -309,6 +311,7 @@ int radop_upload_grid(RadopHandle *h, int nz, int ny, int nx, const float *zleve
     h->have_grid = true;
     h->executed = false;
     h->geo_ready = false;
+    h->traj_tab_ready = false;
     return RADOP_OK;
 }
 
@@ -353,6 +356,7 @@ int radop_upload_lut(RadopHandle *h, int species, const double *value_table, int
     if (!S) return h->fail(RADOP_ERR_ARG, "species is not part of the current parameters");
     CU(h, cudaSetDevice(h->device));
     LutHost &L = h->lut[species];
+    h->traj_tab_ready = false;       // elevation bins of the trajectories belong to the table's axis
     // uniformity of the diameter grid (np.linspace in compute_lut_sz.py:398)
     double d0 = d_axis[0], dD = ((double)d_axis[nd - 1] - d0) / (nd - 1), dev = 0;
     for (int k = 0; k < nd; ++k) dev = std::max(dev, fabs((double)d_axis[k] - (d0 + k * dD)));
@@ -546,6 +550,7 @@ int radop_stage_scan(RadopHandle *h, const RadopScan *sc)
     h->have_scan = true;
     h->executed = false;
     h->geo_ready = false;
+    h->traj_tab_ready = false;
     return RADOP_OK;
 }
 
@@ -695,7 +700,7 @@ static int prepare(RadopHandle *h)
     c.total_bins = bins;
     h->k2_smem = smem;
     // 3 staged columns + per warp: local prefix sums (float), 4 bases per lane (double), edge diameters
-    h->k4_smem = (size_t)3 * nd_max * 4 + (size_t)SPEC_WARPS * ((size_t)nd_max * 4 + 128 * 8 + (size_t)((std::max(p.n_vel, 1) + 1) & ~1) * 4);
+    h->k4_smem = (size_t)3 * nd_max * 4 + (size_t)SPEC_WARPS * (((((size_t)(nd_max >> 5) * 33 + 1) & ~(size_t)1)) * 4 + 128 * 8 + (size_t)((std::max(p.n_vel, 1) + 1) & ~1) * 4);
     return RADOP_OK;
 }
 
@@ -956,7 +961,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             ++h->n_timed;
         }
         if (ev) CU(h, cudaEventRecord(ev[0], st));
-        CU(h, cudaMemsetAsync(h->hist.p, 0, (size_t)c.total_bins * 4, st));
+        if (!fused) CU(h, cudaMemsetAsync(h->hist.p, 0, (size_t)c.total_bins * 4, st));
         CU(h, cudaMemsetAsync(h->flags.as<int>() + 1, 0, 12, st));
         ScanDev scan = h->scan;
         scan.ray_az += r0;
@@ -1012,9 +1017,12 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             }
             if (ch == 0) {
                 CU(h, cudaMemsetAsync(h->f_cnt.p, 0, RADOP_NSPECIES_MAX * 8, st));
-                k_traj_tables<<<(unsigned)((traj_n + 255) / 256), 256, 0, st>>>(c, h->scan.traj_e, traj_n, h->traj_sc.as<float2>(),
-                                                                               h->traj_ie.as<uint8_t>());
-                CU(h, cudaGetLastError()); ++launches;
+                if (!h->traj_tab_ready) {      // they depend on the staged trajectories and the tables' elevation axes only
+                    k_traj_tables<<<(unsigned)((traj_n + 255) / 256), 256, 0, st>>>(c, h->scan.traj_e, traj_n, h->traj_sc.as<float2>(),
+                                                                                   h->traj_ie.as<uint8_t>());
+                    CU(h, cudaGetLastError()); ++launches;
+                    h->traj_tab_ready = true;
+                }
             }
             // warps per CTA = sub-beams of a ray (at most 12), else the count between 6 and 12 that leaves the fewest idle
             int W = h->fused_warps > 0 ? std::min(std::min(h->fused_warps, c.n_sub), FUSED_MAX_WARPS) : 0;
@@ -1056,14 +1064,11 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
             fk<<<gridf, 32 * W, smemf, st>>>(c, scan, h->z_t.as<float>(), h->fields.as<float>(), fa);
             CU(h, cudaGetLastError()); ++launches;
             if (ev) { CU(h, cudaEventRecord(ev[1], st)); CU(h, cudaEventRecord(ev[2], st)); CU(h, cudaEventRecord(ev[3], st)); }
-            if (ice) {
-                k_ice_fixup<<<nr, c.n_sub <= 32 ? 32 : 128, (size_t)c.n_sub * 16, st>>>(c, h->f_ice.as<float4>(), n_spans, h->comb.as<float>(), h->f_wsum.as<float>());
-                CU(h, cudaGetLastError()); ++launches;
-            }
             K3Args a3;
             memset(&a3, 0, sizeof a3);
             a3.sub_weight = scan.sub_weight; a3.ray_nyquist = nyq;
             a3.comb = h->comb.as<float>(); a3.wsum = h->f_wsum.as<float>(); a3.out = h->out.as<float>() + off_rg;
+            a3.ice_part = ice ? h->f_ice.as<float4>() : nullptr; a3.n_spans = n_spans;
             k_ray_epilogue<<<(nr * 32 + 127) / 128, 128, 0, st>>>(c, a3);
             CU(h, cudaGetLastError()); ++launches;
             if (ev) { CU(h, cudaEventRecord(ev[4], st)); CU(h, cudaEventRecord(ev[5], st)); }
@@ -1159,6 +1164,7 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         a3.vals = want_vals ? h->vals.as<float>() : nullptr;
         a3.sub_weight = scan.sub_weight; a3.ray_nyquist = nyq;
         a3.comb = h->comb.as<float>(); a3.wsum = nullptr; a3.out = h->out.as<float>() + off_rg;
+        a3.ice_part = nullptr; a3.n_spans = 0;
         a3.wraw = wraw; a3.wsz = wsz;
         a3.model_out = c.output_model_vars ? h->model_out.as<float>() + off_rg : nullptr;
         k_reduce_subbeams<<<(unsigned)((cc_rg + 127) / 128), 128, 0, st>>>(c, a3);

@@ -595,7 +595,8 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
                 }
             }
             // --- numeric fall-speed moments (IceParticle.integrate_V sums over ALL gates of a sub-beam and the
-            //     total lands on its first gate with ice, hydrometeors.py:1256-1275): partial sums of this span ---
+            //     total lands on its first gate with ice, hydrometeors.py:1256-1275): partial sums of this span, folded into that
+            //     gate by k_ray_epilogue ---
             if (A.ice_part) {
                 const unsigned icy = __ballot_sync(0xffffffffu, ice_here);
                 float v = ice_vn.x, n = ice_vn.y;
@@ -635,46 +636,4 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
     }
     __syncthreads();
     if (threadIdx.x < cfg.n_species && s_pairs[threadIdx.x]) atomicAdd(A.n_pairs + threadIdx.x, (unsigned long long)s_pairs[threadIdx.x]);
-}
-
-// The total of the numeric fall-speed moments of a sub-beam lands on its first gate with ice (see above).  One CTA
-// per ray: its threads add the spans' partial sums of their sub-beams in span order, then thread 0 replaces the
-// contributions of those gates to the velocity sums in sub-beam order (a fixed order: several sub-beams may share
-// their first icy gate).  Dynamic shared memory: 16 bytes per sub-beam.
-__global__ void k_ice_fixup(const __grid_constant__ DevConfig cfg, const float4 *__restrict__ ice_part, int n_spans,
-                            float *__restrict__ comb, float *__restrict__ wsum)
-{
-    extern __shared__ float4 s_fix[];          // [n_sub] first gate (as int bits), rv_old, rv_new, weight
-    const int ray = blockIdx.x, n_sub = cfg.n_sub;
-    for (int q = threadIdx.x; q < n_sub; q += blockDim.x) {
-        const float4 *p = ice_part + ((size_t)ray * n_sub + q) * n_spans * 2;
-        float V = 0.f, N = 0.f;
-        int first = -1;
-        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
-        for (int sp = 0; sp < n_spans; ++sp) {
-            const float4 x = __ldg(p + 2 * sp);
-            V += x.x; N += x.y;
-            if (first < 0 && __float_as_int(x.z) >= 0) { first = __float_as_int(x.z); a0 = x; a1 = __ldg(p + 2 * sp + 1); }
-        }
-        const float wind = a0.w, sinth = a1.x, vs = a1.y, ns = a1.z, w = a1.w;
-        s_fix[q] = make_float4(__int_as_float(first), wind - (vs / ns) * sinth, wind - ((vs + V) / (ns + N)) * sinth, w);
-    }
-    __syncthreads();
-    if (threadIdx.x != 0) return;
-    int cur = -1;
-    float r = 0.f, ws = 0.f;
-    for (int q = 0; q < n_sub; ++q) {
-        const float4 f = s_fix[q];
-        const int first = __float_as_int(f.x);
-        if (first < 0) continue;
-        if (first != cur) {                    // sub-beams of a ray mostly share the gate: keep it in registers
-            if (cur >= 0) { const size_t rg = (size_t)ray * cfg.n_gates + cur; comb[rg * 8 + 7] = r; wsum[rg] = ws; }
-            cur = first;
-            const size_t rg = (size_t)ray * cfg.n_gates + cur;
-            r = comb[rg * 8 + 7]; ws = wsum[rg];
-        }
-        if (!isnan(f.y)) { r -= f.y * f.w; ws -= f.w; }
-        if (!isnan(f.z)) { r += f.z * f.w; ws += f.w; }
-    }
-    if (cur >= 0) { const size_t rg = (size_t)ray * cfg.n_gates + cur; comb[rg * 8 + 7] = r; wsum[rg] = ws; }
 }

@@ -2452,7 +2452,9 @@ struct K3Args {
     const double *sub_weight;
     const float *ray_nyquist;
     float *comb;        // [ray][gate][8]: b c p q kd s9 s11 rvel
-    const float *wsum;  // fused pipeline: comb[7] holds sum(rv w) and this the sum of the weights; else null
+    float *wsum;        // fused pipeline: comb[7] holds sum(rv w) and this the sum of the weights; else null
+    const float4 *ice_part;   // fused pipeline with numeric fall-speed moments: [ray][sub][span][2] partial sums (k_gate_fused), else null
+    int n_spans;
     const float *wraw, *wsz;   // integration scheme 'ml': per-gate weights [sbg] (raw, and normalised by their sum over the sub-beams)
     float *out;         // [N_OUT+1][ray][gate]
     float *model_out;   // [NVP][ray][gate]
@@ -2585,6 +2587,50 @@ k_ray_epilogue(const __grid_constant__ DevConfig cfg, K3Args A)
     const float dr_km = cfg.radial_res / 1000.f;
     float carry_phi = 0.f, carry_h = 1.f, carry_v = 1.f;
     const float nyq = A.ray_nyquist ? A.ray_nyquist[ray] : 0.f;
+    if (A.ice_part) {
+        // The total of the numeric fall-speed moments of a sub-beam lands on its first gate with ice (IceParticle.integrate_V
+        // sums over ALL gates, hydrometeors.py:1256-1275).  The lanes add the spans' partial sums of their sub-beams in span
+        // order; lane 0 then replaces the contributions of those gates to the velocity sums in sub-beam order (a fixed
+        // order: several sub-beams may share their first icy gate) before the gates are read below.
+        int cur = -1;
+        float r = 0.f, ws = 0.f;
+        for (int q0 = 0; q0 < cfg.n_sub; q0 += 32) {
+            const int q = q0 + lane;
+            int first = -1;
+            float rv_old = 0.f, rv_new = 0.f, w = 0.f;
+            if (q < cfg.n_sub) {
+                const float4 *p = A.ice_part + ((size_t)ray * cfg.n_sub + q) * A.n_spans * 2;
+                float V = 0.f, N = 0.f;
+                float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+                for (int sp = 0; sp < A.n_spans; ++sp) {
+                    const float4 x = __ldg(p + 2 * sp);
+                    V += x.x; N += x.y;
+                    if (first < 0 && __float_as_int(x.z) >= 0) { first = __float_as_int(x.z); a0 = x; a1 = __ldg(p + 2 * sp + 1); }
+                }
+                const float wind = a0.w, sinth = a1.x, vs = a1.y, ns = a1.z;
+                w = a1.w;
+                rv_old = wind - (vs / ns) * sinth;
+                rv_new = wind - ((vs + V) / (ns + N)) * sinth;
+            }
+            const int nq = min(32, cfg.n_sub - q0);
+            for (int j = 0; j < nq; ++j) {
+                const int f = __shfl_sync(0xffffffffu, first, j);
+                const float o = __shfl_sync(0xffffffffu, rv_old, j), n = __shfl_sync(0xffffffffu, rv_new, j);
+                const float wj = __shfl_sync(0xffffffffu, w, j);
+                if (lane != 0 || f < 0) continue;
+                if (f != cur) {                    // sub-beams of a ray mostly share the gate: keep it in registers
+                    if (cur >= 0) { const size_t rg = (size_t)ray * ng + cur; A.comb[rg * 8 + 7] = r; A.wsum[rg] = ws; }
+                    cur = f;
+                    const size_t rg = (size_t)ray * ng + cur;
+                    r = A.comb[rg * 8 + 7]; ws = A.wsum[rg];
+                }
+                if (!isnan(o)) { r -= o * wj; ws -= wj; }
+                if (!isnan(n)) { r += n * wj; ws += wj; }
+            }
+        }
+        if (lane == 0 && cur >= 0) { const size_t rg = (size_t)ray * ng + cur; A.comb[rg * 8 + 7] = r; A.wsum[rg] = ws; }
+        __syncwarp();
+    }
     for (int g0 = 0; g0 < ng; g0 += 32) {
         int g = g0 + lane;
         bool ok = g < ng;
@@ -2806,11 +2852,15 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
     float *s_col0 = reinterpret_cast<float *>(s_k4);            // b D^mu dD
     float *s_auxp = s_col0 + nd_max;                            // D^nu or D^0.6357
     float *s_colm = s_auxp + nd_max;                            // a D^b dD (1-mom ice)
-    const size_t per_warp = (size_t)nd_max * 4 + 128 * 8 + (size_t)((nvel + 1) & ~1) * 4;
+    // s_C: the prefix of sample k of lane l = k / cpl sits at (k % cpl) * 33 + l -- rows of 32 lanes padded to 33 words, so
+    // that both the stores of phase 2 (one row, all lanes) and the gathers of phase 3 (neighbouring k of one lane) spread
+    // over the banks (the unpadded layout put all samples of a lane into ONE bank: 7e8 conflict cycles per volume)
+    const size_t c_words = ((size_t)(nd_max >> 5) * 33 + 1) & ~(size_t)1;
+    const size_t per_warp = c_words * 4 + 128 * 8 + (size_t)((nvel + 1) & ~1) * 4;
     unsigned char *wbase = reinterpret_cast<unsigned char *>(s_colm + nd_max) + (size_t)wid * per_warp;
     double *s_base = reinterpret_cast<double *>(wbase);         // [32 lanes][SPEC_SUB] exclusive bases
     float *s_C = reinterpret_cast<float *>(wbase + 128 * 8);    // local inclusive prefix
-    float *s_D = s_C + nd_max;                                  // diameters at the velocity edges
+    float *s_D = s_C + c_words;                                 // diameters at the velocity edges
     const float zfac3 = (float)((double)cfg.wavelength * cfg.wavelength * cfg.wavelength * cfg.wavelength /
                                 (306.0196847852814 * (double)cfg.k_squared * (double)cfg.k_squared));   // pi^5
     int staged_bin = -1;
@@ -2920,7 +2970,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                             const float phi = fmaf(s_auxp[ad], E2[u], E1[u]);
                             mass = fmaf(s_colm[ad], phi, mass);
                             loc[u] = fmaf(s_col0[ad], phi, loc[u]);
-                            s_C[ad] = loc[u];
+                            s_C[ad + (u * sub + ii)] = loc[u];
                             E1[u] *= r1; E2[u] *= r2;
                         }
                     }
@@ -2938,7 +2988,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                         for (int u = 0; u < SPEC_SUB; ++u) {
                             const int ad = (u * sub + ii) * 32 + lane;
                             loc[u] = fmaf(s_col0[ad], E[u], loc[u]);
-                            s_C[ad] = loc[u];
+                            s_C[ad + (u * sub + ii)] = loc[u];
                             E[u] *= r;
                         }
                     }
@@ -2949,7 +2999,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                         for (int u = 0; u < SPEC_SUB; ++u) {
                             const int ad = (u * sub + ii) * 32 + lane;
                             loc[u] = fmaf(s_col0[ad], ex2f_approx(a * s_auxp[ad]), loc[u]);
-                            s_C[ad] = loc[u];
+                            s_C[ad + (u * sub + ii)] = loc[u];
                         }
                     }
                 }
@@ -2993,8 +3043,8 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     const int kb = ib - 1, ka = ia - 1;
                     // chain index = k / sub; position in shared memory (k % cpl) * 32 + k / cpl
                     const int cb = kb / sub, ca = (ka >= 0) ? ka / sub : -1;
-                    const double vb = (double)s_C[(kb % cpl) * 32 + kb / cpl];
-                    const double va = (ka >= 0) ? (double)s_C[(ka % cpl) * 32 + ka / cpl] : 0.0;
+                    const double vb = (double)s_C[(kb % cpl) * 33 + kb / cpl];
+                    const double va = (ka >= 0) ? (double)s_C[(ka % cpl) * 33 + ka / cpl] : 0.0;
                     double diff;
                     if (ca == cb) diff = vb - va;               // same chain: one running sum
                     else {

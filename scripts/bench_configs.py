@@ -30,6 +30,10 @@ def base_conf(freq=5.6, nh=3, nv=3, doppler=1, fft=128):
     return c
 
 
+# ncu --set full of k_spectrum at cfg5s (profiles/r02d_k_spectrum_full.txt): 1.716e10 warp instructions for 2.661e7 pairs
+SPECTRUM_NCU = {'warp_instructions_per_pair': 1.716e10 / 2.661e7, 'issue_active_pct': 48.6, 'sm_mhz': 1965.0, 'dram_bytes': 2.06e9,
+                'source': 'profiles/r02d_k_spectrum_full.txt'}
+
 CONFIGS = {
     'cfg1': dict(conf=base_conf(), scheme='1mom', rays='ppi', what='PPI 1.0 deg, C-band, 1-mom, 360 x 500 x 3x3'),
     'cfg2': dict(conf=base_conf(freq=9.41), scheme='2mom', rays='ppi', what='PPI 1.0 deg, X-band, 2-mom R/S/G/H/I, 360 x 500 x 3x3'),
@@ -99,6 +103,21 @@ def run(name, steps):
             'algorithmic_tflops_integrate': 28672.0 * st['n_active_pairs'] / (st['ms_integrate'] * 1e-3) / 1e12 if st['ms_integrate'] else None,
             'host_s': {'synthetic_inputs': t_gen, 'one_time_upload': t_up}, 'steps': steps,
             'checksum_ZH': float(np.nansum(arrays['ZH'][::7]))}
+    if st['ms_spectrum'] > 0.01 and spec['conf']['doppler']['scheme'] == 3:
+        # k_spectrum (K4b) dominates scheme 3.  Its bound is instruction issue + the shared-memory pipe, not HBM or FP32:
+        # figures of the ncu --set full capture named below (same command, cfg5s) beside the live stage time.
+        pairs = float(st['n_active_pairs'])
+        ncu = SPECTRUM_NCU
+        issue_floor_ms = ncu['warp_instructions_per_pair'] * pairs / (148 * 4 * ncu['sm_mhz'] * 1e3)
+        line['roofline_spectrum'] = {
+            'kernel': 'k_spectrum (+ k_beam_attenuation, k_spectrum_finish in the stage time)', 'bound': 'issue',
+            'stage_ms': st['ms_spectrum'], 'pairs': pairs, 'ns_per_pair': st['ms_spectrum'] * 1e6 / pairs,
+            'warp_instructions_per_pair': ncu['warp_instructions_per_pair'], 'issue_active_pct': ncu['issue_active_pct'],
+            'issue_floor_ms': issue_floor_ms, 'frac_of_issue_floor': issue_floor_ms / st['ms_spectrum'],
+            'shared_bytes_per_pair': 8192 + 4096 * 0.35 * 2, 'dram_bytes_per_launch': ncu['dram_bytes'],
+            'algorithmic': 'per pair: 1024 samples N(D) sigma(D) dD prefix-summed (1 FFMA + 1 store each), <= 129 velocity-bin '
+                           'edges mapped to diameters (float64 power law), <= 128 float64 atomics into [ray][gate][n_vel]',
+            'source': ncu['source']}
     print(json.dumps(line))
     sys.stdout.flush()
     op.close()
