@@ -53,11 +53,13 @@ METRIC = 'sub-beam gates/sec for a 20-elevation volume scan'
 UNIT = 'sub-beam gates/s'
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_interp_psd launch at cfg 3 (ncu --set full, profiles/)
 K1_TRAFFIC = 1.3000e9
-# the same for one k_gate_fused launch (profiles/r02b_k_gate_fused_full.txt: 98 MB read + 456 MB written) and the
+# the same for one k_gate_fused launch (profiles/r02f_k_gate_fused_full.txt: 90.7 MB read + 229.6 MB written) and the
 # issue-side figures of that capture (ncu cannot run inside a timed bench: these are constants of the committed profile)
-FUSED_TRAFFIC = 5.54e8
-FUSED_NCU = {'warp_instructions_per_launch': 2.0e9, 'issue_active_pct': 43.0, 'l1_lsu_wavefronts_pct': 79.0, 'sm_mhz': 1920.0,
-             'source': 'profiles/r02b_k_gate_fused_full.txt'}
+FUSED_TRAFFIC = 3.203e8
+FUSED_NCU = {'warp_instructions_per_launch': 1.848e9, 'issue_active_pct': 44.7, 'l1_lsu_wavefronts_pct': 80.8, 'sm_mhz': 1957.0,
+             'limiter': 'L1 data pipe: l1tex__data_pipe_lsu_wavefronts 80.8 % of peak (per-lane gathers of field values and table '
+                        'coefficients, register spills); long_scoreboard 47 % of the stall samples',
+             'source': 'profiles/r02f_k_gate_fused_full.txt'}
 
 
 def volume_config():
@@ -577,10 +579,10 @@ def run_ours(args):
                     'issue_floor_ms': FUSED_NCU['warp_instructions_per_launch'] / (148 * 4 * FUSED_NCU['sm_mhz'] * 1e3),
                 }),
                 'note': 'achieved = ALGORITHMIC bytes (SURVEY.md 8d) / launch time of k_gate_fused, timed live with CUDA events on the '
-                        'launching stream.  The DRAM traffic of the launch is 6x smaller than the algorithmic bytes (model cells are '
+                        'launching stream.  The DRAM traffic of the launch is 30x smaller than the algorithmic bytes (model cells are '
                         'shared by neighbouring gates and sub-beams in L1/L2; nothing per sub-beam gate is written), so HBM is not the '
                         'bound: the kernel issues ~2.0e9 warp instructions (bit-exact float32 interpolation, float64 PSD logs, table '
-                        'polynomials) and its LSU wavefronts (local-memory spills + table coefficients) keep the L1 data pipe ~80 % busy.',
+                        'polynomials) and its LSU wavefronts (gathers, table coefficients, local-memory spills) keep the L1 data pipe 81 % busy.',
                 'hbm_floor_ms': alg_bytes / (hbm_peak * 1e9) * 1e3,
                 'algorithmic_fp32_floor_ms': flops / (sustained * 1e12) * 1e3,
                 'direct_integration': dsec,

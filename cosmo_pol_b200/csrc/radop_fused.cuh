@@ -202,6 +202,45 @@ __device__ __forceinline__ float lt_col(const float *__restrict__ base, float x,
     return ex2f_approx(L) * R;
 }
 
+// The signed ratio R of column K at x (see lt_col): the constant +-1 from the mask word, or its polynomial.
+template <int NC, int K>
+__device__ __forceinline__ float lt_ratio(const float *__restrict__ base, float x, unsigned mask, unsigned all_const)
+{
+    float R = __int_as_float(0x3f800000 | ((mask << (15 - K)) & 0x80000000u));
+    if (!(all_const & (1u << K))) {               // warp-uniform
+        if (!(mask & (1u << K))) {
+            const float2 *r = reinterpret_cast<const float2 *>(base + 6 * NC + 6 * K);
+            const float2 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
+            R = r2.y;
+            R = fmaf(R, x, r2.x);
+            R = fmaf(R, x, r1.y);
+            R = fmaf(R, x, r1.x);
+            R = fmaf(R, x, r0.y);
+            R = fmaf(R, x, r0.x);
+        }
+    }
+    return R;
+}
+
+// Columns K and K + 1 (K even) at once: their twelve envelope coefficients are 48 contiguous, 16-byte aligned bytes,
+// read with three 16-byte loads instead of six 8-byte ones -- the kernel is bound by the L1 wavefronts of exactly
+// these loads (every distinct piece among the 32 lanes costs one wavefront per load instruction).
+template <int NC, int K>
+__device__ __forceinline__ float2 lt_col_pair(const float *__restrict__ base, float x, unsigned mask, unsigned all_const)
+{
+    static_assert((K & 1) == 0 && K + 1 < NC, "pairs start at even columns");
+    const float4 *l = reinterpret_cast<const float4 *>(base + 6 * K);
+    const float4 a = __ldg(l), b = __ldg(l + 1), c = __ldg(l + 2);
+    float L0 = b.y, L1 = c.w;
+    L0 = fmaf(L0, x, b.x); L1 = fmaf(L1, x, c.z);
+    L0 = fmaf(L0, x, a.w); L1 = fmaf(L1, x, c.y);
+    L0 = fmaf(L0, x, a.z); L1 = fmaf(L1, x, c.x);
+    L0 = fmaf(L0, x, a.y); L1 = fmaf(L1, x, b.w);
+    L0 = fmaf(L0, x, a.x); L1 = fmaf(L1, x, b.z);
+    return make_float2(ex2f_approx(L0) * lt_ratio<NC, K>(base, x, mask, all_const),
+                       ex2f_approx(L1) * lt_ratio<NC, K + 1>(base, x, mask, all_const));
+}
+
 // v * 2^e: one exact multiplication for the exponents the tables really hold (|e| <= 126), else the two-factor form
 __device__ __forceinline__ float scale2(float v, int e)
 {
@@ -364,12 +403,21 @@ __device__ __forceinline__ void species_tab(const DevConfig &cfg, const FusedArg
     // the seven columns of get_pol_from_sz, one at a time
     const int4 e03 = __ldg(reinterpret_cast<const int4 *>(ew));
     const int4 e47 = __ldg(reinterpret_cast<const int4 *>(ew) + 1);
-    acc[0] += tab ? scale2(lt_col<NC, 0>(base, x, mask, all_const) * pre, e03.x - e_off) : 0.f;
-    acc[1] += tab ? scale2(lt_col<NC, 1>(base, x, mask, all_const) * pre, e03.y - e_off) : 0.f;
-    acc[2] += tab ? scale2(lt_col<NC, 2>(base, x, mask, all_const) * pre, e03.z - e_off) : 0.f;
-    acc[3] += tab ? scale2(lt_col<NC, 3>(base, x, mask, all_const) * pre, e03.w - e_off) : 0.f;
-    acc[4] += tab ? scale2(lt_col<NC, 4>(base, x, mask, all_const) * pre, e47.x - e_off) : 0.f;
-    acc[5] += tab ? scale2(lt_col<NC, 5>(base, x, mask, all_const) * pre, e47.y - e_off) : 0.f;
+    {
+        const float2 f = lt_col_pair<NC, 0>(base, x, mask, all_const);
+        acc[0] += tab ? scale2(f.x * pre, e03.x - e_off) : 0.f;
+        acc[1] += tab ? scale2(f.y * pre, e03.y - e_off) : 0.f;
+    }
+    {
+        const float2 f = lt_col_pair<NC, 2>(base, x, mask, all_const);
+        acc[2] += tab ? scale2(f.x * pre, e03.z - e_off) : 0.f;
+        acc[3] += tab ? scale2(f.y * pre, e03.w - e_off) : 0.f;
+    }
+    {
+        const float2 f = lt_col_pair<NC, 4>(base, x, mask, all_const);
+        acc[4] += tab ? scale2(f.x * pre, e47.x - e_off) : 0.f;
+        acc[5] += tab ? scale2(f.y * pre, e47.y - e_off) : 0.f;
+    }
     acc[6] += tab ? scale2(lt_col<NC, 6>(base, x, mask, all_const) * pre, e47.z - e_off) : 0.f;
 }
 

@@ -3003,6 +3003,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                         }
                     }
                 }
+                double pair_total = 0.0;
                 {   // exclusive scan of the lane totals, then the bases of the four chains
                     const double tot = ((double)loc[0] + (double)loc[1]) + ((double)loc[2] + (double)loc[3]);
                     double x = tot;
@@ -3012,6 +3013,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                         if (lane >= d) x += t;
                     }
                     const double prev = __shfl_up_sync(0xffffffffu, x, 1);
+                    pair_total = __shfl_sync(0xffffffffu, x, 31);
                     double bs = lane ? prev : 0.0;
 #pragma unroll
                     for (int u = 0; u < SPEC_SUB; ++u) { s_base[lane * SPEC_SUB + u] = bs; bs += (double)loc[u]; }
@@ -3026,8 +3028,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                 // sums, but it may be the only power of the gate -- and then decides whether RVEL is a number (the reference
                 // sums the samples of a bin directly, doppler_c.c:23-30, and keeps 1e-22 of a bin as it keeps 1e+3).
                 bool any_power = false;
-                for (int pass = 0; pass < 2; ++pass) {
-                const bool direct = A.sub_acc != nullptr || pass == 1;
+                const bool direct = A.sub_acc != nullptr;
                 for (int j = j_a + lane; j < j_b; j += 32) {
                     const float Dj = s_D[j];
                     if (isnan(Dj)) continue;
@@ -3077,7 +3078,51 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     const double val = diff * scale;
                     if (val != 0.0) { atomicAdd(dst + j, val); any_power = true; }
                 }
-                if (direct || __any_sync(0xffffffffu, any_power)) break;
+                // (a pair whose 1024 samples sum to zero in float32 has nothing a float32 spectrum could hold)
+                if (!direct && pair_total > 0.0 && !__any_sync(0xffffffffu, any_power)) {
+                    // the second pass, by the whole warp: bin by bin, the lanes stride over the samples of the bin
+                    // (a bin at the flat end of the fall-speed law can hold hundreds of samples)
+                    const float lam = rec.p0;
+                    const float ea = -LOG2E * lam;
+                    const float a1 = -20.78f * LOG2E * lam, a2 = -3.290f * LOG2E * lam;
+                    const float c2 = (S.mode == MODE_ICE1) ? 17.46f * exp2f(0.6357f * log2f(lam)) : 0.f;
+                    for (int j0 = j_a; j0 < j_b; j0 += 32) {
+                        const int j = j0 + lane;
+                        int ia = 0, ib = 0;
+                        if (j < j_b && !isnan(s_D[j])) {
+                            int jn = j + 1;
+                            while (jn <= j_b && isnan(s_D[jn])) ++jn;
+                            if (jn <= j_b) {
+                                const float Dj = s_D[j], Dn = s_D[jn];
+                                const float Da = fminf(Dj, Dn), Db = fmaxf(Dj, Dn);
+                                ia = (int)__fdiv_rn(__fsub_rn(Da, S.d_min), S.spec_step);
+                                ib = min((int)__fdiv_rn(__fsub_rn(Db, S.d_min), S.spec_step), nd);
+                                if (ia < 0) ib = ia;
+                            }
+                        }
+                        float mine = 0.f;
+                        const int nb = min(32, j_b - j0);
+                        for (int t = 0; t < nb; ++t) {
+                            const int ka = __shfl_sync(0xffffffffu, ia, t), kb = __shfl_sync(0xffffffffu, ib, t);
+                            if (kb <= ka) continue;
+                            float acc = 0.f;
+                            for (int k = ka + lane; k < kb; k += 32) {
+                                const int ad = (k % cpl) * 32 + k / cpl;
+                                float shape;
+                                if (S.mode == MODE_ICE1) {
+                                    const float Dk = __ldg(S.aux + k);
+                                    shape = fmaf(s_auxp[ad], c2 * exp2f(a2 * Dk), 490.6f * exp2f(a1 * Dk));
+                                } else if (S.mode == MODE_GEO8) shape = exp2f(ea * __ldg(S.aux + k));
+                                else shape = exp2f(ea * s_auxp[ad]);
+                                acc = fmaf(s_col0[ad], shape, acc);
+                            }
+#pragma unroll
+                            for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+                            if (lane == t) mine = acc;
+                        }
+                        const double val = (double)mine * scale;
+                        if (j < j_b && val != 0.0) atomicAdd(dst + j, val);
+                    }
                 }
                 __syncwarp();
             }
