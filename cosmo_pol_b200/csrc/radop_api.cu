@@ -73,7 +73,7 @@ struct RadopHandle_ {
     float z_dmin = 0.f, z_dmax = 0.f;
     bool z_dpos = false;
     float var_nmax[RADOP_NVAR_MAX], var_nmin[RADOP_NVAR_MAX];
-    DevBuf z_t, fields, stage, lev_guess;
+    DevBuf z_t, fields, stage, lev_guess, z_tb;
     int search_mode = 0;         // 0: guessed window + bisection when it misses, 1: bisection always
     LutHost lut[RADOP_NSPECIES_MAX];   // indexed by RADOP_SP_*
     // scan
@@ -198,7 +198,7 @@ int radop_destroy(RadopHandle *h)
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     cudaStreamSynchronize(h->copy_stream);
-    DevBuf *bufs[] = {&h->lt_stat, &h->ml_wraw, &h->ml_wsz, &h->traj_sc, &h->traj_ie, &h->f_wsum, &h->f_ice, &h->f_cnt, &h->lev_guess, &h->geo_poly, &h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
+    DevBuf *bufs[] = {&h->lt_stat, &h->ml_wraw, &h->ml_wsz, &h->traj_sc, &h->traj_ie, &h->f_wsum, &h->f_ice, &h->f_cnt, &h->lev_guess, &h->z_tb, &h->geo_poly, &h->geo, &h->z_t, &h->fields, &h->stage, &h->scan_blob, &h->mask, &h->active, &h->wind, &h->sinth,
                       &h->vsum, &h->nsum, &h->key, &h->p0, &h->p1, &h->vals, &h->lat, &h->lon, &h->hist, &h->flags,
                       &h->bin_start, &h->tile_start, &h->cost_start, &h->cursor, &h->totals, &h->rec, &h->sz_out,
                       &h->ice_vn, &h->dop_vn, &h->ice_tot, &h->d3_uh, &h->d3_w, &h->d3_rho, &h->d3_st, &h->attw, &h->spec_pre, &h->spec_acc, &h->spec_out, &h->d3_std, &h->sub_acc, &h->brd_flag, &h->comb, &h->out, &h->model_out, &h->dbg_cell, &h->dbg_level,
@@ -263,6 +263,9 @@ int radop_upload_grid(RadopHandle *h, int nz, int ny, int nx, const float *zleve
     CU(h, cudaMemsetAsync(h->fields.p, 0, n * RADOP_NVP * 4, h->stream));
     CU(h, cudaMemcpyAsync(h->stage.p, zlevels, n * 4, cudaMemcpyHostToDevice, h->stream));
     k_pack_zlevels<<<h->n_sm * 8, 256, 0, h->stream>>>(h->stage.as<float>(), h->z_t.as<float>(), nz, ny, nx);
+    CU(h, cudaGetLastError());
+    CU(h, h->z_tb.reserve((size_t)ny * nx * 8));
+    k_pack_topbot<<<h->n_sm * 8, 256, 0, h->stream>>>(h->z_t.as<float>(), nz, (size_t)ny * nx, h->z_tb.as<float2>());
     CU(h, cudaGetLastError());
     {   // strictly descending columns allow the fast column search of k_interp_psd
         CU(h, h->flags.reserve(16));
@@ -613,6 +616,7 @@ static int prepare(RadopHandle *h)
         c.div_exact = ok ? 1 : 0;
     }
     c.lev_guess = (h->search_mode == 0 && h->nz >= 8 && h->nz <= 256) ? h->lev_guess.as<uint8_t>() : nullptr;
+    c.z_tb = h->z_tb.as<float2>();
     c.n_species = p.n_species;
     c.two_moment = p.two_moment; c.doppler_scheme = p.doppler_scheme; c.with_attenuation = p.with_attenuation;
     c.sensitivity_mode = p.sensitivity_mode; c.output_model_vars = p.output_model_vars; c.keep_debug = p.keep_debug;

@@ -321,7 +321,8 @@ __device__ __forceinline__ void species_tab(const DevConfig &cfg, const FusedArg
     // lanes without a servable pair read piece 0 of their bin (valid memory); their result is discarded
     const float *base = S.lamtab + (size_t)(bl * LT_NP + piece) * STR;
     const int *ew = reinterpret_cast<const int *>(base) + 12 * NC;        // NC exponent words, then the mask word
-    if (have && !why && __ldg(ew) == LT_BAD) why = 1;
+    const int4 e03 = __ldg(reinterpret_cast<const int4 *>(ew));          // exponents of columns 0..3 (word 0 doubles as the reject mark)
+    if (have && !why && e03.x == LT_BAD) why = 1;
     const unsigned need = __ballot_sync(0xffffffffu, why != 0);
     const bool tab = have && !why;
     if (need) {
@@ -341,7 +342,8 @@ __device__ __forceinline__ void species_tab(const DevConfig &cfg, const FusedArg
             }
         }
     }
-    const unsigned mask = (unsigned)__ldg(ew + NC);
+    const int4 e47 = __ldg(reinterpret_cast<const int4 *>(ew) + 1);      // columns 4..7; with 7 columns word 7 IS the mask word
+    const unsigned mask = NC == 7 ? (unsigned)e47.w : (unsigned)__ldg(ew + NC);
     const unsigned all_const = __reduce_and_sync(0xffffffffu, tab ? mask : 0xffffffffu);
     if (!__any_sync(0xffffffffu, tab)) return;
     float pre;
@@ -401,8 +403,6 @@ __device__ __forceinline__ void species_tab(const DevConfig &cfg, const FusedArg
     }
     if (!tab) pre = 0.f;          // lanes without a table pair add exact zeros
     // the seven columns of get_pol_from_sz, one at a time
-    const int4 e03 = __ldg(reinterpret_cast<const int4 *>(ew));
-    const int4 e47 = __ldg(reinterpret_cast<const int4 *>(ew) + 1);
     {
         const float2 f = lt_col_pair<NC, 0>(base, x, mask, all_const);
         acc[0] += tab ? scale2(f.x * pre, e03.x - e_off) : 0.f;
@@ -517,7 +517,7 @@ k_gate_fused(const __grid_constant__ DevConfig cfg, const ScanDev scan, const fl
                 // SWIG typemap casts the coordinates to float32 (interpolation_c.i:16)
                 pos0 = div_const(__fsub_rn((float)rlat, cfg.llc[1]), cfg.res[1], cfg.rres[1]);
                 pos1 = div_const(__fsub_rn((float)rlon, cfg.llc[0]), cfg.res[0], cfg.rres[0]);
-                locate_cell(z_t, cfg.nz, cfg.ny, cfg.nx, pos0, pos1, h_g, cfg.z_strict != 0, c, cfg.lev_guess);
+                locate_cell(z_t, cfg.nz, cfg.ny, cfg.nx, pos0, pos1, h_g, cfg.z_strict != 0, c, cfg.lev_guess, cfg.z_tb);
             }
             const float mask_q = in_range ? (float)c.status : 0.f;
             const bool live = in_range && c.status == 0;

@@ -568,10 +568,17 @@ struct CellGeom {
 // binary search (interpolation_c.c:108-135) then returns the largest index i <= nz-2 with
 // col[i] >= h (an exact match is always probed, the last level never is), which the four
 // neighbour columns find together in ceil(log2(nz-1)) rounds of independent loads.
+// (top, bottom) of every column of the transposed level array
+__global__ void k_pack_topbot(const float *__restrict__ z_t, int nz, size_t n_cols, float2 *__restrict__ out)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_cols; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = make_float2(z_t[i * nz], z_t[i * nz + nz - 1]);
+}
+
 #define RADOP_NGUESS 1024
 __device__ __forceinline__ void locate_cell(const float *__restrict__ z_t, int nz, int ny, int nx, float pos0,
                                             float pos1, float h, bool strict, CellGeom &c,
-                                            const uint8_t *__restrict__ guess = nullptr)
+                                            const uint8_t *__restrict__ guess = nullptr, const float2 *__restrict__ tb = nullptr)
 {
     c.iy = (int)floorf(pos0);
     c.ix = (int)floorf(pos1);
@@ -585,8 +592,15 @@ __device__ __forceinline__ void locate_cell(const float *__restrict__ z_t, int n
     c.y0 = y0; c.y1 = y1; c.x0 = x0; c.x1 = x1;
     const float *col[4] = {z_t + ((size_t)y0 * nx + x0) * nz, z_t + ((size_t)y0 * nx + x1) * nz,
                            z_t + ((size_t)y1 * nx + x0) * nz, z_t + ((size_t)y1 * nx + x1) * nz};
-    float t0 = __ldg(col[0] + nz - 1), t1 = __ldg(col[1] + nz - 1);
-    float t2 = __ldg(col[2] + nz - 1), t3 = __ldg(col[3] + nz - 1);
+    float t0, t1, t2, t3, top0 = 0.f, top1 = 0.f, top2 = 0.f, top3 = 0.f;
+    if (tb) {
+        const float2 e0 = __ldg(tb + (size_t)y0 * nx + x0), e1 = __ldg(tb + (size_t)y0 * nx + x1);
+        const float2 e2 = __ldg(tb + (size_t)y1 * nx + x0), e3 = __ldg(tb + (size_t)y1 * nx + x1);
+        top0 = e0.x; t0 = e0.y; top1 = e1.x; t1 = e1.y; top2 = e2.x; t2 = e2.y; top3 = e3.x; t3 = e3.y;
+    } else {
+        t0 = __ldg(col[0] + nz - 1); t1 = __ldg(col[1] + nz - 1);
+        t2 = __ldg(col[2] + nz - 1); t3 = __ldg(col[3] + nz - 1);
+    }
     // interp_topo = dx*dy*v0 + x*v2*dy + dx*v1*y + x*y*v3   (left to right, no contraction)
     float topo = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(__fmul_rn(c.dx, c.dy), t0),
                                                __fmul_rn(__fmul_rn(c.x, t2), c.dy)),
@@ -596,7 +610,7 @@ __device__ __forceinline__ void locate_cell(const float *__restrict__ z_t, int n
     if (!(topo < h)) { c.status = -1; return; }
     c.status = 0;
     if (strict) {
-        const float top0 = __ldg(col[0]), top1 = __ldg(col[1]), top2 = __ldg(col[2]), top3 = __ldg(col[3]);
+        if (!tb) { top0 = __ldg(col[0]); top1 = __ldg(col[1]); top2 = __ldg(col[2]); top3 = __ldg(col[3]); }
         if (h > top0 || h > top1 || h > top2 || h > top3) { c.status = 1; return; }
         const float bot[4] = {t0, t1, t2, t3};
         int idx[4] = {0, 0, 0, 0};
@@ -619,6 +633,8 @@ __device__ __forceinline__ void locate_cell(const float *__restrict__ z_t, int n
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const float *w = col[k] + a[k];
+                // (keeping these four heights for the interpolation instead of loading its two again was measured: the eight
+                //  extra live registers spill and the kernel loses 8 %)
                 const int cnt = (__ldg(w) >= h) + (__ldg(w + 1) >= h) + (__ldg(w + 2) >= h) + (__ldg(w + 3) >= h);
                 const bool ok = (cnt >= 1 || a[k] == 0) && (cnt <= 3 || a[k] + 3 >= nz - 2);
                 if (ok) {
@@ -3016,7 +3032,9 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     pair_total = __shfl_sync(0xffffffffu, x, 31);
                     double bs = lane ? prev : 0.0;
 #pragma unroll
-                    for (int u = 0; u < SPEC_SUB; ++u) { s_base[lane * SPEC_SUB + u] = bs; bs += (double)loc[u]; }
+                    // chain c = lane * SPEC_SUB + u lives at u * 32 + lane (lane-major rows: the 8-byte stores of a warp
+                    // and the gathers below spread over the banks; [lane][u] cost 6e8 conflict cycles per volume)
+                    for (int u = 0; u < SPEC_SUB; ++u) { s_base[u * 32 + lane] = bs; bs += (double)loc[u]; }
                 }
                 __syncwarp();
                 // ---- 3. velocity bins -----------------------------------------------------------
@@ -3049,11 +3067,12 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     double diff;
                     if (ca == cb) diff = vb - va;               // same chain: one running sum
                     else {
-                        const double hi = s_base[cb] + vb, lo = (ka >= 0) ? s_base[ca] + va : 0.0;
+                        const double hi = s_base[(cb % SPEC_SUB) * 32 + cb / SPEC_SUB] + vb;
+                        const double lo = (ka >= 0) ? s_base[(ca % SPEC_SUB) * 32 + ca / SPEC_SUB] + va : 0.0;
                         diff = hi - lo;
                         if (fabs(diff) < 2e-15 * fabs(hi)) diff = 0.0;      // rounding of the bases
                     }
-                    if (direct && !(diff > 1e-6 * (s_base[cb] + vb))) {
+                    if (direct && !(diff > 1e-6 * (s_base[(cb % SPEC_SUB) * 32 + cb / SPEC_SUB] + vb))) {
                         // Broadening turns a sub-beam spectrum without power into NaN (0 / 0,
                         // doppler_scatter.py:799), so "tiny" and "zero" are not the same thing here:
                         // where the prefix difference has lost the value (far PSD tail), the samples
@@ -3106,14 +3125,17 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                             const int ka = __shfl_sync(0xffffffffu, ia, t), kb = __shfl_sync(0xffffffffu, ib, t);
                             if (kb <= ka) continue;
                             float acc = 0.f;
-                            for (int k = ka + lane; k < kb; k += 32) {
+                            // every lane sums ITS samples of the bin (the cpl consecutive ones it owns in shared memory:
+                            // column = lane, no bank conflicts)
+                            const int k_hi = min(kb, (lane + 1) * cpl);
+                            for (int k = max(ka, lane * cpl); k < k_hi; ++k) {
                                 const int ad = (k % cpl) * 32 + k / cpl;
                                 float shape;
                                 if (S.mode == MODE_ICE1) {
                                     const float Dk = __ldg(S.aux + k);
-                                    shape = fmaf(s_auxp[ad], c2 * exp2f(a2 * Dk), 490.6f * exp2f(a1 * Dk));
-                                } else if (S.mode == MODE_GEO8) shape = exp2f(ea * __ldg(S.aux + k));
-                                else shape = exp2f(ea * s_auxp[ad]);
+                                    shape = fmaf(s_auxp[ad], c2 * ex2f_approx(a2 * Dk), 490.6f * ex2f_approx(a1 * Dk));
+                                } else if (S.mode == MODE_GEO8) shape = ex2f_approx(ea * __ldg(S.aux + k));
+                                else shape = ex2f_approx(ea * s_auxp[ad]);      // flushes below 2^-126: a float32 spectrum cannot hold what that loses
                                 acc = fmaf(s_col0[ad], shape, acc);
                             }
 #pragma unroll

@@ -76,6 +76,8 @@ struct DevConfig {
     int div_exact;              // 1: every quotient of the vertical interpolation of this grid and these fields takes the
                                 // shared-reciprocal path exactly (bounds taken at upload, k_level_diff_bounds): no range checks
     const uint8_t *lev_guess;   // [1024] level of a reference column against the normalised height, or null
+    const float2 *z_tb;         // [ny][nx] (top, bottom) level height of every column: the two ends the search and the topography test
+                                // need, in ONE compact array (neighbouring columns share a cache line; in z_t they are nz floats apart)
     int output_model_vars, keep_debug, ice_numeric;   // ice_numeric: species index with numeric v,n or -1
     float wavelength, k_squared, radial_res;
     float sens0, sens1;
