@@ -3045,7 +3045,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                 // the velocity window: its power sits in the far tail of the PSD, below the float32 resolution of the running
                 // sums, but it may be the only power of the gate -- and then decides whether RVEL is a number (the reference
                 // sums the samples of a bin directly, doppler_c.c:23-30, and keeps 1e-22 of a bin as it keeps 1e+3).
-                bool any_power = false;
+                bool any_power = false, any_samples = false;
                 const bool direct = A.sub_acc != nullptr;
                 for (int j = j_a + lane; j < j_b; j += 32) {
                     const float Dj = s_D[j];
@@ -3059,6 +3059,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     const int ia = (int)__fdiv_rn(__fsub_rn(Da, S.d_min), S.spec_step);
                     const int ib = min((int)__fdiv_rn(__fsub_rn(Db, S.d_min), S.spec_step), nd);
                     if (ib <= ia || ia < 0) continue;
+                    any_samples = true;
                     const int kb = ib - 1, ka = ia - 1;
                     // chain index = k / sub; position in shared memory (k % cpl) * 32 + k / cpl
                     const int cb = kb / sub, ca = (ka >= 0) ? ka / sub : -1;
@@ -3098,7 +3099,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     if (val != 0.0) { atomicAdd(dst + j, val); any_power = true; }
                 }
                 // (a pair whose 1024 samples sum to zero in float32 has nothing a float32 spectrum could hold)
-                if (!direct && pair_total > 0.0 && !__any_sync(0xffffffffu, any_power)) {
+                if (!direct && pair_total > 0.0 && __ballot_sync(0xffffffffu, any_samples) && !__any_sync(0xffffffffu, any_power)) {
                     // the second pass, by the whole warp: bin by bin, the lanes stride over the samples of the bin
                     // (a bin at the flat end of the fall-speed law can hold hundreds of samples)
                     const float lam = rec.p0;

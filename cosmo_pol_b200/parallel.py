@@ -369,13 +369,22 @@ class HostExchange(object):
             except Exception:
                 pass
         buf = np.ndarray((max(8, int(nbytes)),), dtype=np.uint8, buffer=seg.buf)
-        pinned = bool(self._register(buf)) if (pin and self._register is not None) else False
-        self._segments.append((seg, buf, pinned))
+        self._segments.append([seg, buf, False, bool(pin)])
         return buf
 
-    def ensure(self, spec):
+    def _pin_segments(self):
+        """Page-lock the segments that want it (after the first touch: registering faults every page in on the node of the
+        registering process)."""
+        for ent in self._segments:
+            if ent[3] and not ent[2] and self._register is not None:
+                ent[2] = bool(self._register(ent[1]))
+
+    def ensure(self, spec, first_touch=None):
         """spec: list of (name, row shape tuple, dtype) with a common number of rows `n_rows` given as the first
-        element of each shape.  (Re)allocates the two array sets when the spec changes (a collective call)."""
+        element of each shape.  (Re)allocates the two array sets when the spec changes (a collective call).
+        first_touch(arrays): called on every new array set BEFORE it is page-locked, so that a rank can write its own rows
+        first and have their pages allocated on its own NUMA node (the rank is bound to the cores next to its GPU): the
+        device -> host copies of the far socket's GPUs then do not cross the inter-socket link."""
         spec = [(n, tuple(int(x) for x in shp), np.dtype(dt).str) for n, shp, dt in spec]
         if spec == self._spec:
             return
@@ -389,10 +398,16 @@ class HostExchange(object):
                 import torch.distributed as dist
                 dist.barrier()                       # the zeroed flags are visible before anybody uses them
         sizes = [int(np.prod(shp)) * np.dtype(dt).itemsize for _, shp, dt in spec]
-        offs = np.concatenate([[0], np.cumsum([(s + 255) // 256 * 256 for s in sizes])])
+        offs = np.concatenate([[0], np.cumsum([(s + 4095) // 4096 * 4096 for s in sizes])])
         for k in range(2):
             buf = self._share(int(offs[-1]))
             self._sets[k] = {n: buf[offs[i]:offs[i] + sizes[i]].view(dt).reshape(shp) for i, (n, shp, dt) in enumerate(spec)}
+            if first_touch is not None:
+                first_touch(self._sets[k])
+        if first_touch is not None and self.world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        self._pin_segments()
         self._spec = spec
 
     def arrays(self):
@@ -433,7 +448,7 @@ class HostExchange(object):
         self._spec = None
         if not keep_flags:
             self._flags = None
-        for seg, buf, pinned in doomed:
+        for seg, buf, pinned, _pin in doomed:
             if pinned and self._unregister is not None:
                 try:
                     self._unregister(buf)

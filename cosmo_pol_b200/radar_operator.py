@@ -466,7 +466,11 @@ class RadarOperator(object):
             spec += [(n, (n_total, ng), np.float32) for n in sorted(eng.model_output_slots())]
         if [(n, tuple(s), np.dtype(d).str) for n, s, d in spec] != X._spec:
             self._latlon_sets = [None, None]
-        X.ensure(spec)
+        def first_touch(arrs):                   # this rank's rows first: their pages land on this rank's NUMA node
+            if n_loc:
+                for a_ in arrs.values():
+                    a_[mine] = 0
+        X.ensure(spec, first_touch=first_touch)
         arrays = X.arrays()
         which = X.calls % 2
         full_scan = self.build_scan(ray_az, ray_el)
