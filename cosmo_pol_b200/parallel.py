@@ -30,7 +30,7 @@ def shard_bounds(n_items, rank, world):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
-RAY_BLOCK = 4
+RAY_BLOCK = int(os.environ.get('RADOP_RAY_BLOCK', 4))      # consecutive rays per dealt block (the environment variable is for experiments)
 
 
 def shard_indices(n_items, rank, world, block=RAY_BLOCK):

@@ -1,7 +1,7 @@
 """End-to-end (radop_simulate, host buffers) and device step time of configuration 3 against the chunk size."""
 import os, sys, json, time
 import numpy as np
-ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), '..', '..'))
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), '..'))
 sys.path.insert(0, ROOT)
 import bench
 import torch
@@ -13,6 +13,7 @@ op.set_lut(luts); op.load_model(model)
 eng = op._prepare_engine()
 az, el = bench.volume_rays()
 scan = op.build_scan(az, el)
+eng.reuse_staged = False            # the scan is uploaded with every call, as in bench.py's e2e leg
 for chunk in (16000000, 8000000, 5400000, 4000000, 2700000, 2000000, 1350000, 1000000):
     eng.set_chunk(chunk)
     for _ in range(3):
