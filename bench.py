@@ -53,13 +53,13 @@ METRIC = 'sub-beam gates/sec for a 20-elevation volume scan'
 UNIT = 'sub-beam gates/s'
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_interp_psd launch at cfg 3 (ncu --set full, profiles/)
 K1_TRAFFIC = 1.3000e9
-# the same for one k_gate_fused launch (profiles/r02f_k_gate_fused_full.txt: 90.7 MB read + 229.6 MB written) and the
+# the same for one k_gate_fused launch (profiles/r02h_k_gate_fused_full.txt: 91.8 MB read + 253.0 MB written) and the
 # issue-side figures of that capture (ncu cannot run inside a timed bench: these are constants of the committed profile)
-FUSED_TRAFFIC = 3.203e8
-FUSED_NCU = {'warp_instructions_per_launch': 1.848e9, 'issue_active_pct': 44.7, 'l1_lsu_wavefronts_pct': 80.8, 'sm_mhz': 1957.0,
-             'limiter': 'L1 data pipe: l1tex__data_pipe_lsu_wavefronts 80.8 % of peak (per-lane gathers of field values and table '
-                        'coefficients, register spills); long_scoreboard 47 % of the stall samples',
-             'source': 'profiles/r02f_k_gate_fused_full.txt'}
+FUSED_TRAFFIC = 3.448e8
+FUSED_NCU = {'warp_instructions_per_launch': 1.839e9, 'issue_active_pct': 48.3, 'l1_lsu_wavefronts_pct': 76.8, 'sm_mhz': 1953.0,
+             'limiter': 'L1 data pipe: l1tex__data_pipe_lsu_wavefronts 76.8 % of peak (per-lane gathers of field values and table '
+                        'coefficients, register spills); long_scoreboard 43 % of the stall samples',
+             'source': 'profiles/r02h_k_gate_fused_full.txt'}
 
 
 def volume_config():
@@ -582,7 +582,7 @@ def run_ours(args):
                         'launching stream.  The DRAM traffic of the launch is 30x smaller than the algorithmic bytes (model cells are '
                         'shared by neighbouring gates and sub-beams in L1/L2; nothing per sub-beam gate is written), so HBM is not the '
                         'bound: the kernel issues ~2.0e9 warp instructions (bit-exact float32 interpolation, float64 PSD logs, table '
-                        'polynomials) and its LSU wavefronts (gathers, table coefficients, local-memory spills) keep the L1 data pipe 81 % busy.',
+                        'polynomials) and its LSU wavefronts (gathers, table coefficients, local-memory spills) keep the L1 data pipe 77 % busy.',
                 'hbm_floor_ms': alg_bytes / (hbm_peak * 1e9) * 1e3,
                 'algorithmic_fp32_floor_ms': flops / (sustained * 1e12) * 1e3,
                 'direct_integration': dsec,

@@ -57,7 +57,7 @@ struct RadopHandle_ {
     int device = 0;
     cudaStream_t stream = nullptr, copy_stream = nullptr;
     std::vector<cudaEvent_t> chunk_done;
-    long long chunk_sbg = 8000000;   // sub-beam gates per chunk (0: one chunk)
+    long long chunk_sbg = -1;        // sub-beam gates per chunk (0: one chunk; -1: the default of the pipeline that runs)
     int n_chunks = 1, n_exec_timed = 0;
     std::string err;
     int n_sm = 148;
@@ -812,7 +812,11 @@ static int run_scan(RadopHandle *h, const RadopOut *out)
         for (int v = 0; v < RADOP_NVAR_MAX; ++v) if (out->model[v]) d2h_bytes += n_rg * 4;
     }
     const bool overlap_copies = out && d2h_bytes >= h->overlap_min_bytes;
-    long long target = overlap_copies ? h->chunk_sbg : 8 * h->chunk_sbg;
+    // default chunk: 3e6 sub-beam gates for the fused kernel (a chunk costs it little, and many short copies keep the copy
+    // engine busy from early on: 4.75 ms end to end at cfg 3 against 5.22 ms with 8e6, scripts/chunk_sweep.py), 8e6 for the
+    // staged pipeline (every chunk costs it a pass over the bin table and partial tiles)
+    const long long chunk_sbg = h->chunk_sbg >= 0 ? h->chunk_sbg : (fused ? 3000000LL : 8000000LL);
+    long long target = overlap_copies ? chunk_sbg : 8 * (h->chunk_sbg >= 0 ? h->chunk_sbg : 8000000LL);
     if (c.brd_mode) {
         // the sub-beam spectra of a chunk are kept in float64: at most ~4 GB of them
         const long long cap = std::max<long long>(per_ray, (4LL << 30) / ((long long)c.n_vel * 8));
@@ -1356,7 +1360,7 @@ int radop_simulate(RadopHandle *h, const RadopScan *scan, const RadopOut *out)
 int radop_set_chunk(RadopHandle *h, int64_t subbeam_gates_per_chunk)
 {
     if (!h) return RADOP_ERR_ARG;
-    h->chunk_sbg = subbeam_gates_per_chunk;
+    h->chunk_sbg = subbeam_gates_per_chunk < 0 ? -1 : subbeam_gates_per_chunk;
     return RADOP_OK;
 }
 

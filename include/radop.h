@@ -220,9 +220,10 @@ int radop_stage_scan(RadopHandle *h, const RadopScan *scan);   /* H2D           
 int radop_execute(RadopHandle *h);                              /* kernels, asynchronous  */
 int radop_fetch(RadopHandle *h, const RadopOut *out);           /* sync + D2H             */
 int radop_synchronize(RadopHandle *h);
-/* The ray list is processed in chunks of about this many sub-beam gates (default 8e6; 0 = one
- * chunk): work memory is sized for one chunk and, in radop_simulate, the device -> host copies
- * of a chunk overlap the kernels of the next one.  Results do not depend on the chunking. */
+/* The ray list is processed in chunks of about this many sub-beam gates (0 = one chunk; negative = the
+ * default: 3e6 where the fused kernel runs, 8e6 for the staged pipeline): work memory is sized for one
+ * chunk and, in radop_simulate, the device -> host copies of a chunk overlap the kernels of the next
+ * one.  Results do not depend on the chunking. */
 int radop_set_chunk(RadopHandle *h, int64_t subbeam_gates_per_chunk);
 /* radop_simulate splits the scan into chunks only when the requested outputs are at least this large
  * (default 32 MiB): every chunk costs a pass over the bin table and partial tiles, which only pays when

@@ -43,6 +43,7 @@ def margins(out, ref, nyq=0.0):
     return rep
 
 
+_stdout, sys.stdout = sys.stdout, sys.stderr          # the host layer prints like the reference does: keep stdout for the JSON
 report = {'oracle_f64': {}, 'goldens': {}}
 for scheme, freq in (('1mom', 5.6), ('2mom', 9.41)):
     for dop in (1, 2):
@@ -62,11 +63,12 @@ for scheme, freq in (('1mom', 5.6), ('2mom', 9.41)):
 from cosmo_pol_b200 import RadarOperator
 for name, scheme, freq in (('c1mom', '1mom', 5.6), ('c2mom', '2mom', 9.41), ('c1mom_thr', '1mom', 5.6),
                            ('c1mom_nyq', '1mom', 5.6), ('c1mom_dop2', '1mom', 5.6), ('c1mom_quad2', '1mom', 5.6),
+                           ('c1mom_quad3', '1mom', 5.6), ('c1mom_quad5', '1mom', 5.6),
                            ('c1mom_melt', '1mom', 5.6), ('c1mom_melt_dop2', '1mom', 5.6), ('c1mom_ml', '1mom', 5.6),
                            ('c1mom_dop3', '1mom', 5.6), ('c1mom_dop3_turb', '1mom', 5.6), ('c1mom_dop3_mot', '1mom', 5.6)):
     try:
         g, cfg, kw = load_golden_case(name)
-        model, luts = synthetic_inputs(scheme, freq, **kw)
+        model, luts = synthetic_inputs(scheme, freq, with_melting=bool(cfg['microphysics'].get('with_melting', 0)), **kw)
         conf = copy.deepcopy(cfg)
         conf['radar']['sensitivity'] = [-200, 10000]
         op = RadarOperator(conf, output_variables='only_radar', device=0)
@@ -80,4 +82,5 @@ for name, scheme, freq in (('c1mom', '1mom', 5.6), ('c2mom', '2mom', 9.41), ('c1
         op.close()
     except Exception as e:                     # a golden whose configuration the plain call does not cover
         report['goldens'][name] = {'skipped': '{}: {}'.format(type(e).__name__, e)[:200]}
+sys.stdout = _stdout
 print(json.dumps(report, indent=1))
