@@ -509,6 +509,9 @@ def run_ours(args):
     os.dup2(fd_out, 1)
     os.close(fd_out)
     if rank != 0:
+        sys.stdout = quiet
+        op.close()                  # unmaps this rank's view of the shared host segments
+        sys.stdout = sys.__stdout__
         if world > 1:
             dist.destroy_process_group()
         return 0
@@ -653,6 +656,9 @@ def run_ours(args):
                                 'sample': 'timed at N=1 only'}
     print(json.dumps(line))
     sys.stdout.flush()
+    sys.stdout = quiet
+    op.close()                      # releases the shared host segments (rank 0 unlinks them) and the device memory
+    sys.stdout = sys.__stdout__
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -348,6 +348,8 @@ class HostExchange(object):
         self._flags = None
         self._seq = 0
         self.calls = 0
+        import atexit
+        atexit.register(self.close)            # rank 0 unlinks the segments even when the owner forgets to close()
 
     # -- segments ---------------------------------------------------------------------------------
     def _share(self, nbytes, pin=True):
