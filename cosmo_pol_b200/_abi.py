@@ -402,13 +402,14 @@ class Engine(object):
         shape = (scan.n_rays, scan.n_gates)
         out = RadopOut()
         arrays = {}
+        # observables and mask in ONE pinned block: equally spaced planes let the library copy a chunk of all of them
+        # with a single strided device -> host copy (copy_outputs)
+        block = self._host_buffer('obs+mask', (len(OUT_NAMES) + 1,) + shape, np.float32)
         for i, name in enumerate(OUT_NAMES):
-            a = self._host_buffer(('obs', i), shape, np.float32)
-            arrays[name] = a
-            out.obs[i] = a.ctypes.data
-        a = self._host_buffer('mask', shape, np.float32)
-        arrays['mask'] = a
-        out.mask = a.ctypes.data
+            arrays[name] = block[i]
+            out.obs[i] = block[i].ctypes.data
+        arrays['mask'] = block[len(OUT_NAMES)]
+        out.mask = arrays['mask'].ctypes.data
         if want_latlon:
             for k in ('lat', 'lon'):
                 a = self._host_buffer(k, shape, np.float64)

@@ -1,6 +1,6 @@
 import os, sys, json, time
 import numpy as np
-ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), '..', '..'))
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), '..'))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, 'scripts'))
 import bench, bench_configs
 from cosmo_pol_b200 import RadarOperator, synthetic

@@ -1,7 +1,7 @@
 """Where the end-to-end call (radop_simulate, host buffers) spends its time at cfg 3: device time of the chunks
 (CUDA events, summed) against the wall clock of the call, for a few chunk sizes."""
 import os, sys, json, time
-ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), '..', '..'))
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), '..'))
 sys.path.insert(0, ROOT)
 import bench
 from cosmo_pol_b200 import RadarOperator
