@@ -1,5 +1,5 @@
 #!/bin/bash
-# Multi-GPU record of the round: usage  gpurun --gpus N -- bash scripts/gpu_round2_multi.sh "1 2"   (list of world sizes)
+# Multi-GPU record of the round: usage  gpurun --gpus N -- bash scripts/gpu_scaling.sh "1 2"   (list of world sizes)
 mkdir -p gpurun_out
 NS=${1:-"1 2"}
 NG=$(nvidia-smi -L | wc -l)
