@@ -2979,6 +2979,33 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                         E1[u] = 490.6f * ex2f_approx(a1 * d0);
                         E2[u] = c2 * ex2f_approx(a2 * d0);
                     }
+                    if (ND1024) {
+                        // as for the geometric shapes below: the table values of two chains and four samples (24 loads) first
+#pragma unroll
+                        for (int h2 = 0; h2 < SPEC_SUB / 2; ++h2)
+#pragma unroll
+                            for (int q4 = 0; q4 < 2; ++q4) {
+                                float c0v[2][4], axv[2][4], cmv[2][4];
+#pragma unroll
+                                for (int v = 0; v < 2; ++v)
+#pragma unroll
+                                    for (int i4 = 0; i4 < 4; ++i4) {
+                                        const int ad = ((h2 * 2 + v) * 8 + q4 * 4 + i4) * 32 + lane;
+                                        c0v[v][i4] = s_col0[ad]; axv[v][i4] = s_auxp[ad]; cmv[v][i4] = s_colm[ad];
+                                    }
+#pragma unroll
+                                for (int i4 = 0; i4 < 4; ++i4)
+#pragma unroll
+                                    for (int v = 0; v < 2; ++v) {
+                                        const int u = h2 * 2 + v, row = u * 8 + q4 * 4 + i4;
+                                        const float phi = fmaf(axv[v][i4], E2[u], E1[u]);
+                                        mass = fmaf(cmv[v][i4], phi, mass);
+                                        loc[u] = fmaf(c0v[v][i4], phi, loc[u]);
+                                        s_C[row * 33 + lane] = loc[u];
+                                        E1[u] *= r1; E2[u] *= r2;
+                                    }
+                            }
+                    } else
                     for (int ii = 0; ii < sub; ++ii) {
 #pragma unroll
                         for (int u = 0; u < SPEC_SUB; ++u) {
@@ -2999,6 +3026,27 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     float E[SPEC_SUB];
 #pragma unroll
                     for (int u = 0; u < SPEC_SUB; ++u) E[u] = ex2f_approx(a * __ldg(Dax + u * sub));
+                    if (ND1024) {
+                        // two chains at a time, their sixteen table values loaded first: the loads are then in flight
+                        // together instead of each multiply-add waiting for its own (this line held 17 % of the stall samples)
+#pragma unroll
+                        for (int h2 = 0; h2 < SPEC_SUB / 2; ++h2) {
+                            float cv[2][8];
+#pragma unroll
+                            for (int v = 0; v < 2; ++v)
+#pragma unroll
+                                for (int ii = 0; ii < 8; ++ii) cv[v][ii] = s_col0[((h2 * 2 + v) * 8 + ii) * 32 + lane];
+#pragma unroll
+                            for (int ii = 0; ii < 8; ++ii)
+#pragma unroll
+                                for (int v = 0; v < 2; ++v) {
+                                    const int u = h2 * 2 + v, row = u * 8 + ii;
+                                    loc[u] = fmaf(cv[v][ii], E[u], loc[u]);
+                                    s_C[row * 33 + lane] = loc[u];
+                                    E[u] *= r;
+                                }
+                        }
+                    } else
                     for (int ii = 0; ii < sub; ++ii) {
 #pragma unroll
                         for (int u = 0; u < SPEC_SUB; ++u) {
