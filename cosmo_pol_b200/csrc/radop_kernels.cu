@@ -2916,6 +2916,10 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
             __syncthreads();
         }
         const float spec_scale = (float)((double)S.spec_step / (double)S.dD_ref);
+        // diameters at the starts of this lane's four prefix chains: the same for every pair of the unit
+        float d_chain[SPEC_SUB];
+#pragma unroll
+        for (int u = 0; u < SPEC_SUB; ++u) d_chain[u] = __ldg(S.aux + lane * cpl + u * sub);
         for (int jt = j0; jt < j1; ++jt) {
             const int first = A.bin_start[b] + jt * RADOP_TILE;
             const int n_here = min(RADOP_TILE, cnt - jt * RADOP_TILE);
@@ -2966,7 +2970,6 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
 #pragma unroll
                 for (int u = 0; u < SPEC_SUB; ++u) loc[u] = 0.f;
                 float n0 = rec.p1;
-                const float *Dax = S.aux + lane * cpl;          // diameters of this lane's samples
                 if (S.mode == MODE_ICE1) {
                     const float lam = rec.p0;
                     const float a1 = -20.78f * LOG2E * lam, a2 = -3.290f * LOG2E * lam;
@@ -2975,7 +2978,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     float E1[SPEC_SUB], E2[SPEC_SUB], mass = 0.f;
 #pragma unroll
                     for (int u = 0; u < SPEC_SUB; ++u) {
-                        const float d0 = __ldg(Dax + u * sub);
+                        const float d0 = d_chain[u];
                         E1[u] = 490.6f * ex2f_approx(a1 * d0);
                         E2[u] = c2 * ex2f_approx(a2 * d0);
                     }
@@ -3025,7 +3028,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     const float r = ex2f_approx(a * S.dD_geo);
                     float E[SPEC_SUB];
 #pragma unroll
-                    for (int u = 0; u < SPEC_SUB; ++u) E[u] = ex2f_approx(a * __ldg(Dax + u * sub));
+                    for (int u = 0; u < SPEC_SUB; ++u) E[u] = ex2f_approx(a * d_chain[u]);
                     if (ND1024) {
                         // two chains at a time, their sixteen table values loaded first: the loads are then in flight
                         // together instead of each multiply-add waiting for its own (this line held 17 % of the stall samples)
@@ -3085,6 +3088,13 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                     for (int u = 0; u < SPEC_SUB; ++u) { s_base[u * 32 + lane] = bs; bs += (double)loc[u]; }
                 }
                 __syncwarp();
+                // the next pair of this warp: its per sub-beam gate record and activity mask are random accesses (an L2 round
+                // trip each at the head of the pair's dependency chain); asked for now, they are in L1 when it starts
+                if (i + SPEC_WARPS < n_here) {
+                    const uint32_t sbg_n = A.rec[first + i + SPEC_WARPS].sbg;
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(A.pre + sbg_n));
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(A.active + sbg_n));
+                }
                 // ---- 3. velocity bins -----------------------------------------------------------
                 const double scale = 6.283185307179586 * (double)n0 * (double)zfac3 * (double)spec_scale *
                                      (A.sub_acc ? 1.0 : (double)P.attw);
