@@ -2983,6 +2983,7 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                         E2[u] = c2 * ex2f_approx(a2 * d0);
                     }
                     if (ND1024) {
+                        float2 mass2 = make_float2(0.f, 0.f);
                         // as for the geometric shapes below: the table values of two chains and four samples (24 loads) first
 #pragma unroll
                         for (int h2 = 0; h2 < SPEC_SUB / 2; ++h2)
@@ -2996,18 +2997,24 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                                         const int ad = ((h2 * 2 + v) * 8 + q4 * 4 + i4) * 32 + lane;
                                         c0v[v][i4] = s_col0[ad]; axv[v][i4] = s_auxp[ad]; cmv[v][i4] = s_colm[ad];
                                     }
+                                // the two chains advance as the halves of packed FFMA2 / FMUL2 (the kernel is issue bound)
+                                const int u0 = h2 * 2, u1 = u0 + 1;
+                                float2 e1 = make_float2(E1[u0], E1[u1]), e2 = make_float2(E2[u0], E2[u1]);
+                                float2 lc = make_float2(loc[u0], loc[u1]);
 #pragma unroll
-                                for (int i4 = 0; i4 < 4; ++i4)
-#pragma unroll
-                                    for (int v = 0; v < 2; ++v) {
-                                        const int u = h2 * 2 + v, row = u * 8 + q4 * 4 + i4;
-                                        const float phi = fmaf(axv[v][i4], E2[u], E1[u]);
-                                        mass = fmaf(cmv[v][i4], phi, mass);
-                                        loc[u] = fmaf(c0v[v][i4], phi, loc[u]);
-                                        s_C[row * 33 + lane] = loc[u];
-                                        E1[u] *= r1; E2[u] *= r2;
-                                    }
+                                for (int i4 = 0; i4 < 4; ++i4) {
+                                    const int ii = q4 * 4 + i4;
+                                    const float2 phi = ffma2(make_float2(axv[0][i4], axv[1][i4]), e2, e1);
+                                    mass2 = ffma2(make_float2(cmv[0][i4], cmv[1][i4]), phi, mass2);
+                                    lc = ffma2(make_float2(c0v[0][i4], c0v[1][i4]), phi, lc);
+                                    s_C[(u0 * 8 + ii) * 33 + lane] = lc.x;
+                                    s_C[(u1 * 8 + ii) * 33 + lane] = lc.y;
+                                    e1 = fmul2(e1, bcast2(r1)); e2 = fmul2(e2, bcast2(r2));
+                                }
+                                E1[u0] = e1.x; E1[u1] = e1.y; E2[u0] = e2.x; E2[u1] = e2.y;
+                                loc[u0] = lc.x; loc[u1] = lc.y;
                             }
+                        mass = mass2.x + mass2.y;
                     } else
                     for (int ii = 0; ii < sub; ++ii) {
 #pragma unroll
@@ -3039,15 +3046,16 @@ k_spectrum(const __grid_constant__ DevConfig cfg, K4Args A)
                             for (int v = 0; v < 2; ++v)
 #pragma unroll
                                 for (int ii = 0; ii < 8; ++ii) cv[v][ii] = s_col0[((h2 * 2 + v) * 8 + ii) * 32 + lane];
+                            const int u0 = h2 * 2, u1 = u0 + 1;
+                            float2 ev = make_float2(E[u0], E[u1]), lc = make_float2(loc[u0], loc[u1]);
 #pragma unroll
-                            for (int ii = 0; ii < 8; ++ii)
-#pragma unroll
-                                for (int v = 0; v < 2; ++v) {
-                                    const int u = h2 * 2 + v, row = u * 8 + ii;
-                                    loc[u] = fmaf(cv[v][ii], E[u], loc[u]);
-                                    s_C[row * 33 + lane] = loc[u];
-                                    E[u] *= r;
-                                }
+                            for (int ii = 0; ii < 8; ++ii) {
+                                lc = ffma2(make_float2(cv[0][ii], cv[1][ii]), ev, lc);
+                                s_C[(u0 * 8 + ii) * 33 + lane] = lc.x;
+                                s_C[(u1 * 8 + ii) * 33 + lane] = lc.y;
+                                ev = fmul2(ev, bcast2(r));
+                            }
+                            loc[u0] = lc.x; loc[u1] = lc.y;
                         }
                     } else
                     for (int ii = 0; ii < sub; ++ii) {
