@@ -817,7 +817,7 @@ def test_fused_pipeline_against_staged_and_oracle(scheme, freq, doppler):
     """The fused kernel (k_gate_fused: the default whenever the configuration allows it) against the staged pipeline
     (k_interp_psd -> k_integrate_tab -> k_reduce_subbeams) on the same scan, and both against the float64 oracle:
     masks, NaN patterns and gate positions identical, observables within a small multiple of float32 rounding of
-    each other and within the north-star tolerances of the oracle; launch-shape independence bit for bit."""
+    each other and within the north-star tolerances of the oracle; launch shapes and chunking."""
     conf = copy.deepcopy(CONF_1MOM)
     conf['doppler'] = {'scheme': doppler}
     conf['radar']['nyquist_velocity'] = None
@@ -854,13 +854,21 @@ def test_fused_pipeline_against_staged_and_oracle(scheme, freq, doppler):
         assert np.array_equal(np.isnan(f['RVEL'][r]), ~okv)
         if okv.any():
             assert np.max(np.abs(f['RVEL'][r][okv] - ref['RVEL'][0][okv])) < 2e-3
-    # results do not depend on the launch shape (warps per CTA) nor on the chunking
+    # launch shape (warps per CTA) and chunking.  One warp per sub-beam (the default for 9 sub-beams) and one warp for all
+    # of them add the sub-beams in the same order: bit for bit.  Other shapes group the sub-beams differently (warp w takes
+    # q = w, w + W, ...): float32 rounding of the sums.
     base = copy.deepcopy(eng.simulate(scan))
     for w in (1, 2, 5, 9):
         eng.set_tuning('fused_warps', w)
         alt = eng.simulate(scan)
         for k in base:
-            assert np.array_equal(base[k], alt[k], equal_nan=True) or w != 9 or True
+            if w in (1, 9):
+                assert np.array_equal(base[k], alt[k], equal_nan=True), (w, k)
+            else:
+                assert np.array_equal(np.isnan(base[k]), np.isnan(alt[k])), (w, k)
+                ok = np.isfinite(base[k])
+                big = {'RVEL': 2e-4, 'DELTA_HV': 2e-4, 'PHIDP': 2e-4}.get(k, 3e-5)
+                assert np.all(np.abs(alt[k][ok] - base[k][ok]) <= big * (np.abs(base[k][ok]) + 1e-2)), (w, k)
     eng.set_tuning('fused_warps', 0)
     eng.set_overlap_threshold(0)
     eng.set_chunk(3 * 9 * scan.n_gates)
