@@ -504,7 +504,8 @@ def run_ours(args):
     st_e2e = None
     if world > 1:
         # itemised cost of the product call on rank 0 (wall clock, one extra call): where e2e goes beyond the kernels
-        st_e2e = e2e_breakdown(op, eng, az_full, el_full, rank, world, local)
+        st_e2e = (e2e_breakdown(op, eng, az_full, el_full, rank, world, local) if op._exchange is not None else
+                  {'note': 'shared host memory unavailable on this box: shards gathered over NCCL (RadarOperator fell back)'})
     sys.stdout = stdout
     os.dup2(fd_out, 1)
     os.close(fd_out)

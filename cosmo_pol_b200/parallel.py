@@ -318,6 +318,10 @@ def all_gather_rays(local, n_total, group=None):
 # ---------------------------------------------------------------------------------------------
 # delivery through host memory shared by the ranks (the default of RadarOperator under torchrun)
 # ---------------------------------------------------------------------------------------------
+class SharedMemoryUnavailable(RuntimeError):
+    """Rank 0 could not create the shared host segment (raised on every rank)."""
+
+
 class HostExchange(object):
     """Host arrays of the WHOLE scan, shared by the ranks of one box (POSIX shared memory), plus a barrier in the same
     segment.
@@ -359,10 +363,18 @@ class HostExchange(object):
         name = [None]
         seg = None
         if self.rank == 0:
-            seg = shared_memory.SharedMemory(create=True, size=max(8, int(nbytes)))
-            name[0] = seg.name
+            try:
+                st = os.statvfs('/dev/shm')
+                if st.f_bavail * st.f_frsize < int(nbytes) + (64 << 20):
+                    raise OSError('/dev/shm has {} MB free, {} MB needed'.format(st.f_bavail * st.f_frsize >> 20, int(nbytes) >> 20))
+                seg = shared_memory.SharedMemory(create=True, size=max(8, int(nbytes)))
+                name[0] = seg.name
+            except Exception as e:               # noqa: BLE001 -- told to every rank below, so that all of them fall back together
+                name[0] = 'ERROR: {}'.format(e)
         if self.world > 1:
             dist.broadcast_object_list(name, src=0)
+        if name[0] is None or str(name[0]).startswith('ERROR'):
+            raise SharedMemoryUnavailable(str(name[0]))
         if self.rank != 0:
             seg = shared_memory.SharedMemory(name=name[0])
             try:        # the creator unlinks; keep the resource tracker of the attaching processes out of it

@@ -470,7 +470,15 @@ class RadarOperator(object):
             if n_loc:
                 for a_ in arrs.values():
                     a_[mine] = 0
-        X.ensure(spec, first_touch=first_touch)
+        try:
+            X.ensure(spec, first_touch=first_touch)
+        except parallel.SharedMemoryUnavailable as e:
+            # every rank gets here together (rank 0 tells the others): gather over NCCL from now on
+            print('shared host memory is not available ({}): gathering the shards over NCCL instead'.format(e))
+            X.close()
+            self._exchange = None
+            self.gather_transport = 'nccl'
+            return self._simulate_sharded(eng, ray_az, ray_el, rank, world, want_model, copy)
         arrays = X.arrays()
         which = X.calls % 2
         full_scan = self.build_scan(ray_az, ray_el)

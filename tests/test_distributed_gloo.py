@@ -178,3 +178,18 @@ def test_host_exchange_gloo_world2(n_total):
         p.join(timeout=60)
     assert sorted(r[0] for r in res) == [0, 1]
     assert all(r[1] for r in res), res
+
+
+def test_host_exchange_reports_missing_shared_memory(monkeypatch):
+    """Rank 0 failing to create the segment raises SharedMemoryUnavailable (on every rank: the name travels by broadcast),
+    which RadarOperator turns into the NCCL gather."""
+    from cosmo_pol_b200 import parallel
+    from multiprocessing import shared_memory
+
+    def boom(*a, **k):
+        raise OSError('no space left on device')
+    monkeypatch.setattr(shared_memory, 'SharedMemory', boom)
+    X = parallel.HostExchange(0, 1)
+    with pytest.raises(parallel.SharedMemoryUnavailable):
+        X.ensure([('ZH', (4, 3), np.float32)])
+    X.close()
