@@ -30,9 +30,9 @@ def base_conf(freq=5.6, nh=3, nv=3, doppler=1, fft=128):
     return c
 
 
-# ncu --set full of k_spectrum at cfg5s (profiles/r02k_k_spectrum_full.txt): 1.799e10 warp instructions for 2.661e7 pairs
-SPECTRUM_NCU = {'warp_instructions_per_pair': 1.799e10 / 2.661e7, 'issue_active_pct': 74.2, 'sm_mhz': 1962.0, 'dram_bytes': 2.09e9,
-                'source': 'profiles/r02k_k_spectrum_full.txt'}
+# ncu --set full of k_spectrum at cfg5s (profiles/r02l_k_spectrum_full.txt): 1.707e10 warp instructions for 2.661e7 pairs
+SPECTRUM_NCU = {'warp_instructions_per_pair': 1.707e10 / 2.661e7, 'issue_active_pct': 73.2, 'sm_mhz': 1962.0, 'dram_bytes': 2.09e9,
+                'source': 'profiles/r02l_k_spectrum_full.txt'}
 
 CONFIGS = {
     'cfg1': dict(conf=base_conf(), scheme='1mom', rays='ppi', what='PPI 1.0 deg, C-band, 1-mom, 360 x 500 x 3x3'),
